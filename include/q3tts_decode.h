@@ -1,0 +1,122 @@
+/* libq3tts_decode.so — C-ABI of the B200-native Qwen3-TTS-Tokenizer-12Hz decode path.
+ *
+ * The reference (kritsanan1/Qwen3-TTS) has no FFI for this path: its boundary is a set of Python
+ * classes.  Each entry point below replaces the body of one reference method; the Python shim in
+ * qwen3_tts_b200/ keeps the reference's class names and signatures and calls these through ctypes
+ * (INTEGRATION.md shows the binding).  "modeling" =
+ * qwen_tts/core/tokenizer_12hz/modeling_qwen3_tts_tokenizer_v2.py, "wrapper" =
+ * qwen_tts/inference/qwen3_tts_tokenizer.py.
+ *
+ * Conventions: every function returns 0 on success or a negative q3tts_status; the message of the
+ * last failure on a handle is q3tts_last_error(h).  Plain pointers and sizes only.  A handle is
+ * bound to one CUDA device and is NOT thread-safe (one handle per device per worker).  Device
+ * pointers are borrowed for the duration of the call; every launch goes to the caller's stream
+ * (cudaStream_t passed as void*; NULL = default stream).  No allocation happens after
+ * q3tts_reserve() unless a call needs more frames than were reserved.
+ */
+#ifndef Q3TTS_DECODE_H_
+#define Q3TTS_DECODE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct q3tts_handle q3tts_handle;
+
+typedef enum {
+  Q3TTS_OK = 0,
+  Q3TTS_BAD_SHAPE = -1,         /* Python: ValueError (modeling :869-870) */
+  Q3TTS_BAD_CONFIG = -2,        /* Python: ValueError */
+  Q3TTS_CODE_OUT_OF_RANGE = -3, /* Python: IndexError (F.embedding would assert) */
+  Q3TTS_CUDA_ERROR = -4,        /* Python: RuntimeError */
+  Q3TTS_OOM = -5,               /* Python: MemoryError */
+  Q3TTS_BAD_STREAM = -6,        /* Python: KeyError */
+  Q3TTS_BAD_KEY = -7,           /* Python: KeyError (unknown / missing state_dict key) */
+  Q3TTS_NOT_READY = -8          /* Python: RuntimeError (weights not finalized) */
+} q3tts_status;
+
+/* Fields the reference decoder reads from Qwen3TTSTokenizerV2DecoderConfig
+ * (configuration_qwen3_tts_tokenizer_v2.py:72-114) plus codebook_dim / head_dim, which reach the
+ * reference through **kwargs (modeling :288, :830). */
+typedef struct {
+  int32_t codebook_size;      /* 2048 */
+  int32_t codebook_dim;       /* 512 (RVQ rows are codebook_dim/2 wide) */
+  int32_t hidden_size;        /* 1024 */
+  int32_t latent_dim;         /* 1024 */
+  int32_t num_attention_heads; /* 16 */
+  int32_t num_key_value_heads; /* 16 */
+  int32_t head_dim;           /* 64 */
+  int32_t sliding_window;     /* 72 */
+  int32_t intermediate_size;  /* 3072 */
+  int32_t num_hidden_layers;  /* 8 */
+  int32_t num_quantizers;     /* 16 */
+  int32_t decoder_dim;        /* 1536 */
+  int32_t num_upsample_rates;
+  int32_t upsample_rates[8];  /* 8,5,4,3 */
+  int32_t num_upsampling_ratios;
+  int32_t upsampling_ratios[4]; /* 2,2 */
+  int32_t max_position_embeddings; /* 8000 */
+  float rms_norm_eps;         /* 1e-5 */
+  float rope_theta;           /* 10000 */
+} q3tts_config;
+
+enum { Q3TTS_MODE_FP16 = 0, Q3TTS_MODE_BF16 = 1 }; /* tensor-core operand type; accumulation is fp32 in both */
+enum { Q3TTS_ENGINE_TC = 0, Q3TTS_ENGINE_SIMT = 1 }; /* SIMT = debug cross-check kernels, not a product path */
+
+/* Lifetime.  Replaces Qwen3TTSTokenizerV2Decoder.__init__ (modeling :824-866). */
+int q3tts_create(const q3tts_config* cfg, int device, q3tts_handle** out);
+void q3tts_destroy(q3tts_handle* h);
+const char* q3tts_last_error(q3tts_handle* h);
+
+/* Weights.  Replaces nn.Module.load_state_dict for the decoder: `key` is a reference
+ * Qwen3TTSTokenizerV2Decoder.state_dict() key (SURVEY §8(b) lists them), `data` is fp32, host
+ * (on_device = 0) or device (on_device = 1) memory, copied before the call returns. */
+int q3tts_load_tensor(q3tts_handle* h, const char* key, const float* data, int ndim, const int64_t* shape, int on_device);
+/* Repack everything into tensor-core operand layouts (16-bit K-major, folded RVQ tables, exp'd
+ * Snake parameters).  Fails with Q3TTS_BAD_KEY if a tensor is missing or mis-shaped. */
+int q3tts_finalize_weights(q3tts_handle* h, int compute_mode);
+int q3tts_reserve(q3tts_handle* h, int max_frames_per_launch);
+int q3tts_set_engine(q3tts_handle* h, int engine);
+
+/* Sizes (pure host arithmetic). */
+int64_t q3tts_forward_num_samples(q3tts_handle* h, int T);                          /* T*1920 - 555 */
+int64_t q3tts_chunked_num_samples(q3tts_handle* h, int T, int chunk, int left_ctx); /* T*1920 - 555*nchunks */
+
+/* SplitResidualVectorQuantizer.decode (modeling :814-820): codes [B,Q,T] int64 (device) ->
+ * out [B,codebook_dim,T] fp32 (device). */
+int q3tts_rvq_decode(q3tts_handle* h, const int64_t* codes, int B, int T, float* out, void* stream);
+
+/* Qwen3TTSTokenizerV2Decoder.forward (modeling :868-883): codes [B,Q,T] int64 (device) ->
+ * wav [B, T*1920-555] fp32 (device), clamped to [-1,1]. */
+int q3tts_forward(q3tts_handle* h, const int64_t* codes, int B, int T, float* wav, void* stream);
+
+/* Qwen3TTSTokenizerV2Decoder.chunked_decode (modeling :885-895): codes [B,Q,T] (device) ->
+ * wav [B, q3tts_chunked_num_samples] fp32 (device). */
+int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, int chunk, int left_ctx, float* wav, void* stream);
+
+/* Qwen3TTSTokenizerV2Model.decode + the wrapper's H2D/D2H (modeling :1012-1015, wrapper :329, :364):
+ * codes [B,T,Q] int64 in HOST memory (padded with 0 like pad_sequence) -> wav_host [B, wav_stride]
+ * fp32 HOST memory, lengths[b] = min((codes[b,:,0] > 0).sum()*upsample, chunked length).  Only the
+ * first lengths[b] samples of each row are written.  Synchronises the stream before returning. */
+int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
+                      void* stream);
+
+/* Parity probe: run forward() up to the stage named `stage` (an oracle tap name such as
+ * "pre_conv", "pre_transformer", "upsample.0.1", "decoder.2.block.3", "decoder.0.snake") and write
+ * that activation as fp32 [B,C,L] to `out` (device, `capacity` floats).  *C and *L receive the shape. */
+int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, const char* stage, float* out, int64_t capacity, int* C, int* L,
+                        void* stream);
+
+/* Bench support: number of kernel launches issued by this handle since creation. */
+int64_t q3tts_launch_count(q3tts_handle* h);
+
+/* Standalone GEMM self-test of the tcgen05 implicit-GEMM kernel against the SIMT cross-check
+ * (device-side, no host math): returns max |tc - simt| over a [rows,n] problem via *max_abs_diff. */
+int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dilation, int bf16, float* max_abs_diff, float* max_abs_ref);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* Q3TTS_DECODE_H_ */

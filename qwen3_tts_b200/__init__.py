@@ -1,0 +1,24 @@
+"""B200-native Qwen3-TTS-Tokenizer-12Hz decode path (codes -> 24 kHz waveform).
+
+Public surface mirrors the reference package for this path (qwen_tts/__init__.py:21-22,
+qwen_tts/core/tokenizer_12hz): Qwen3TTSTokenizer, Qwen3TTSTokenizerV2Model,
+Qwen3TTSTokenizerV2Decoder and their configs.  All arithmetic runs in the in-tree CUDA
+library lib/libq3tts_decode.so (hand-written sm_100a kernels behind a C-ABI)."""
+from .configuration import Qwen3TTSTokenizerV2Config, Qwen3TTSTokenizerV2DecoderConfig
+from .modeling import (Qwen3TTSTokenizerV2Decoder, Qwen3TTSTokenizerV2DecoderOutput,
+                       Qwen3TTSTokenizerV2Model)
+from .tokenizer import Qwen3TTSTokenizer
+
+
+def synthetic_model(seed: int = 0, device="cuda:0", compute_mode: str = "fp16", state_dict=None):
+    """Model with the seeded random-init weights of the named architecture (no checkpoint is mounted)."""
+    from .synthetic import make_decoder_state_dict
+    cfg = Qwen3TTSTokenizerV2Config()
+    model = Qwen3TTSTokenizerV2Model(cfg, device=device, compute_mode=compute_mode)
+    sd = state_dict if state_dict is not None else make_decoder_state_dict(cfg.decoder_config, seed)
+    model.decoder.load_state_dict(sd)
+    return model
+
+
+__all__ = ["Qwen3TTSTokenizer", "Qwen3TTSTokenizerV2Model", "Qwen3TTSTokenizerV2Decoder", "Qwen3TTSTokenizerV2DecoderOutput",
+           "Qwen3TTSTokenizerV2Config", "Qwen3TTSTokenizerV2DecoderConfig", "synthetic_model"]

@@ -1,0 +1,148 @@
+// extern "C" run-time entry points: rvq_decode / forward / chunked_decode / decode_host / probe / selftest.
+#include <cstring>
+#include <vector>
+
+#include "engine.h"
+#include "kernels.h"
+
+using namespace q3;
+
+namespace {
+
+int ready(Engine& e, const void* codes, int B, int T) {
+  if (!e.finalized) return e.fail(Q3TTS_NOT_READY, "weights not finalized");
+  if (!codes || B < 1 || T < 1) return e.fail(Q3TTS_BAD_SHAPE, "codes must be [B>=1, Q, T>=1]");
+  return 0;
+}
+
+// chunk loop of Qwen3TTSTokenizerV2Decoder.chunked_decode (reference modeling :887-894); codes addressed by strides
+int chunked(Engine& e, const long long* codes, long long sb, long long sk, long long st, int B, int T, int chunk, int left_ctx, float* wav,
+            long long wav_stride, cudaStream_t s) {
+  int start = 0;
+  long long out_off = 0;
+  while (start < T) {
+    const int end = (start + chunk < T) ? start + chunk : T;
+    const int ctx = (start - left_ctx > 0) ? left_ctx : start;
+    const int lo = start - ctx;
+    const int Tc = end - lo;
+    const long long emitted = (long long)(end - start) * e.total_up - e.lookahead;
+    if (emitted > 0) {
+      int rc = engine_forward_batched(&e, codes + lo * st, sb, sk, st, B, Tc, wav + out_off, wav_stride, ctx * e.total_up, s);
+      if (rc) return rc;
+      out_off += emitted;
+    }
+    start = end;
+  }
+  return Q3TTS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int q3tts_rvq_decode(q3tts_handle* h, const int64_t* codes, int B, int T, float* out, void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (int rc = ready(e, codes, B, T)) return rc;
+  if (!out) return e.fail(Q3TTS_BAD_SHAPE, "rvq_decode: null output");
+  DeviceGuard g(e.device);
+  const int Q = e.cfg.num_quantizers;
+  cudaError_t err = rvq_decode((const long long*)codes, (long long)Q * T, T, 1, e.rvq_tables, nullptr, out, B, Q, T, e.cfg.codebook_size,
+                               e.cfg.codebook_dim, e.bf16, (cudaStream_t)stream);
+  ++e.launches;
+  if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("rvq_decode: ") + cudaGetErrorString(err));
+  return Q3TTS_OK;
+}
+
+int q3tts_forward(q3tts_handle* h, const int64_t* codes, int B, int T, float* wav, void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (int rc = ready(e, codes, B, T)) return rc;
+  if (!wav) return e.fail(Q3TTS_BAD_SHAPE, "forward: null output");
+  DeviceGuard g(e.device);
+  const int Q = e.cfg.num_quantizers;
+  const long long n = (long long)T * e.total_up - e.lookahead;
+  if (n <= 0) return e.fail(Q3TTS_BAD_SHAPE, "forward: sequence too short");
+  return engine_forward_batched(&e, (const long long*)codes, (long long)Q * T, T, 1, B, T, wav, n, 0, (cudaStream_t)stream);
+}
+
+int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, int chunk, int left_ctx, float* wav, void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (int rc = ready(e, codes, B, T)) return rc;
+  if (!wav || chunk < 1 || left_ctx < 0) return e.fail(Q3TTS_BAD_SHAPE, "chunked_decode: bad arguments");
+  DeviceGuard g(e.device);
+  const int Q = e.cfg.num_quantizers;
+  const long long total = q3tts_chunked_num_samples(h, T, chunk, left_ctx);
+  return chunked(e, (const long long*)codes, (long long)Q * T, T, 1, B, T, chunk, left_ctx, wav, total, (cudaStream_t)stream);
+}
+
+int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
+                      void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (int rc = ready(e, codes_host, B, T)) return rc;
+  if (!wav_host || !lengths) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: null output");
+  DeviceGuard g(e.device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int Q = e.cfg.num_quantizers;
+  const int chunk = 300, left_ctx = 25;  // Qwen3TTSTokenizerV2Model.decode uses chunked_decode's defaults (modeling :1012)
+  const long long total = q3tts_chunked_num_samples(h, T, chunk, left_ctx);
+  const size_t ncodes = (size_t)B * T * Q;
+  if (ncodes > e.codes_stage_elems) {
+    cudaStreamSynchronize(s);
+    if (e.codes_stage) cudaFree(e.codes_stage);
+    e.codes_stage = nullptr; e.codes_stage_elems = 0;
+    if (cudaMalloc((void**)&e.codes_stage, ncodes * sizeof(long long)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: codes staging"); }
+    e.codes_stage_elems = ncodes;
+  }
+  const size_t nwav = (size_t)B * (size_t)(total > 0 ? total : 0);
+  if (nwav > e.wav_stage_elems) {
+    cudaStreamSynchronize(s);
+    if (e.wav_stage) cudaFree(e.wav_stage);
+    e.wav_stage = nullptr; e.wav_stage_elems = 0;
+    if (cudaMalloc((void**)&e.wav_stage, nwav * sizeof(float)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: wav staging"); }
+    e.wav_stage_elems = nwav;
+  }
+  cudaError_t err = cudaMemcpyAsync(e.codes_stage, codes_host, ncodes * sizeof(long long), cudaMemcpyHostToDevice, s);
+  if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: H2D: ") + cudaGetErrorString(err));
+  // audio_lengths = (audio_codes[..., 0] > 0).sum(1) * decode_upsample_rate, then a[:l] (modeling :1014-1015)
+  for (int b = 0; b < B; ++b) {
+    long long cnt = 0;
+    for (int t = 0; t < T; ++t) cnt += codes_host[((size_t)b * T + t) * Q] > 0 ? 1 : 0;
+    long long l = cnt * e.total_up;
+    if (l > total) l = total;
+    if (l < 0) l = 0;
+    lengths[b] = l;
+  }
+  if (total > 0) {
+    // codes are [B,T,Q] here (wrapper layout): strides b = T*Q, k = 1, t = Q
+    int rc = chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
+    if (rc) return rc;
+    for (int b = 0; b < B; ++b) {
+      if (lengths[b] <= 0) continue;
+      if (lengths[b] > wav_stride) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: wav_stride smaller than an output row");
+      err = cudaMemcpyAsync(wav_host + (size_t)b * wav_stride, e.wav_stage + (size_t)b * total, (size_t)lengths[b] * sizeof(float),
+                            cudaMemcpyDeviceToHost, s);
+      if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: D2H: ") + cudaGetErrorString(err));
+    }
+  }
+  err = cudaStreamSynchronize(s);
+  if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: ") + cudaGetErrorString(err));
+  return Q3TTS_OK;
+}
+
+int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, const char* stage, float* out, int64_t capacity, int* C, int* L,
+                        void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (int rc = ready(e, codes, B, T)) return rc;
+  if (!stage || !out) return e.fail(Q3TTS_BAD_SHAPE, "forward_probe: null argument");
+  DeviceGuard g(e.device);
+  Plan* plan = nullptr;
+  if (int rc = engine_get_plan(&e, B, T, &plan)) return rc;
+  const int Q = e.cfg.num_quantizers;
+  return engine_run(&e, plan, (const long long*)codes, (long long)Q * T, T, 1, nullptr, 0, 0, stage, out, capacity, C, L, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,132 @@
+// Host-side engine: weight store, per-(B,T) launch plans, workspace.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/q3tts_decode.h"
+#include "conv_gemm.h"
+
+namespace q3 {
+
+struct RawTensor {
+  std::vector<int64_t> shape;
+  float* d = nullptr;  // fp32 device copy
+  long long numel = 0;
+};
+
+// One packed conv / linear operand set for the implicit-GEMM kernel.
+struct ConvW {
+  void* w = nullptr;  // [taps][n_total][cin] 16-bit
+  int taps = 0, n_total = 0, cin = 0, ncol_mod = 0;
+  int tap_off[8] = {0};
+  const float* bias = nullptr;  // fp32 [ncol_mod] or null
+  int bn = 0, kb = 0;
+  int out_rows_per_row = 1;  // transposed conv: s output rows per accumulator row
+};
+
+struct SnakeP { const float* a = nullptr; const float* ib = nullptr; };
+
+struct LayerW {
+  ConvW qkv, o, gateup, down;
+  const float *ln1 = nullptr, *ln2 = nullptr, *ls1 = nullptr, *ls2 = nullptr;
+};
+struct UpsampleW {
+  ConvW tconv, pw1, pw2;
+  const float *dww = nullptr, *dwb = nullptr, *lnw = nullptr, *lnb = nullptr, *gamma = nullptr;
+};
+struct UnitW { ConvW conv7, conv1; SnakeP act1, act2; };
+struct BlockW { SnakeP act0; ConvW tconv; UnitW unit[3]; int stride = 0, cin = 0, cout = 0; };
+
+enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL };
+
+struct Op {
+  OpType type = OP_GEMM;
+  GemmOp g;
+  const void* in = nullptr;
+  void* out = nullptr;
+  const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;
+  int B = 0, L = 0, C = 0;
+  // probe: the buffer that holds an oracle tap once this op has run
+  std::string tag;
+  const void* probe_ptr = nullptr;
+  bool probe_f32 = false;
+  int probe_C = 0, probe_L = 0;
+};
+
+struct Plan {
+  int B = 0, T = 0;
+  std::vector<Op> ops;
+  int out_len = 0;  // samples per item of the forward output
+};
+
+struct Engine {
+  q3tts_config cfg{};
+  int device = 0;
+  std::string err;
+  bool finalized = false;
+  bool bf16 = false;
+  int engine = ENGINE_TC;
+  int total_up = 1920;
+  int lookahead = 555;
+  long long launches = 0;
+
+  std::map<std::string, RawTensor> raw;
+  std::vector<void*> owned;  // packed allocations
+
+  // packed weights
+  float* rvq_tables = nullptr;  // [Q][codes][D] fp32, output_proj folded in
+  ConvW pre_conv, in_proj, out_proj, dec0;
+  std::vector<LayerW> layers;
+  const float* final_norm = nullptr;
+  std::vector<UpsampleW> ups;
+  std::vector<BlockW> blocks;
+  SnakeP tail_act;
+  float* tail_w = nullptr;  // [7][C]
+  float tail_bias = 0.f;
+  int tail_c = 0;
+  float *rope_cos = nullptr, *rope_sin = nullptr;
+  int rope_max = 0;
+
+  // workspace
+  uint8_t* ws = nullptr;
+  size_t ws_bytes = 0;
+  int max_frames = 8192;
+  std::map<std::pair<int, int>, Plan> plans;
+  long long* codes_stage = nullptr;  // device staging for decode_host
+  size_t codes_stage_elems = 0;
+  float* wav_stage = nullptr;
+  size_t wav_stage_elems = 0;
+
+  int fail(int code, const std::string& msg) { err = msg; return code; }
+};
+
+int engine_finalize(Engine* e, int mode);
+int engine_get_plan(Engine* e, int B, int T, Plan** out);
+size_t engine_plan_bytes(const Engine* e, int B, int T);
+int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
+               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s);
+int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
+                           long long wav_stride, int skip, cudaStream_t s);
+void engine_free(Engine* e);
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace q3
+
+struct q3tts_handle {
+  q3::Engine e;
+};

@@ -1,0 +1,290 @@
+// Per-(B,T) launch plans for Qwen3TTSTokenizerV2Decoder.forward (reference modeling :868-883).
+#include <cstring>
+
+#include "engine.h"
+#include "kernels.h"
+
+namespace q3 {
+
+namespace {
+
+struct Builder {
+  Engine* e;
+  Plan* plan;
+  uint8_t* base;
+  size_t off = 0;
+  bool dry;  // size pass only
+  int rc = 0;
+
+  void* alloc(size_t bytes) {
+    off = (off + 1023) & ~(size_t)1023;
+    void* p = dry ? nullptr : base + off;
+    off += bytes;
+    return p;
+  }
+  // GEMM: in [batches][rows][cin] -> accumulator rows_valid per batch item
+  Op& gemm(const ConvW& w, const void* in, int batches, int rows, int rows_valid) {
+    plan->ops.emplace_back();
+    Op& op = plan->ops.back();
+    op.type = OP_GEMM;
+    GemmParams& p = op.g.p;
+    memset(&p, 0, sizeof(p));
+    p.batches = batches; p.rows = rows; p.rows_valid = rows_valid;
+    p.cin = w.cin; p.ntaps = w.taps;
+    for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
+    p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
+    p.bias = w.bias; p.bf16 = e->bf16 ? 1 : 0;
+    p.a_ptr = in; p.w_ptr = w.w;
+    p.out_row_stride = w.n_total;
+    p.out_batch_stride = (long long)rows_valid * w.n_total;
+    if (!dry) {
+      if (make_tmap_3d(&op.g.tmA, in, (uint64_t)w.cin, (uint64_t)rows, (uint64_t)batches, (uint32_t)w.kb, 128, e->bf16) ||
+          make_tmap_3d(&op.g.tmB, w.w, (uint64_t)w.cin, (uint64_t)w.n_total, (uint64_t)w.taps, (uint32_t)w.kb, (uint32_t)w.bn, e->bf16))
+        rc = e->fail(Q3TTS_CUDA_ERROR, "cuTensorMapEncodeTiled failed");
+    }
+    return op;
+  }
+  void tag(Op& op, const char* name, const void* ptr, bool f32, int C, int L) {
+    op.tag = name; op.probe_ptr = ptr; op.probe_f32 = f32; op.probe_C = C; op.probe_L = L;
+  }
+};
+
+int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
+  const q3tts_config& c = e->cfg;
+  Builder b{e, plan, e->ws, 0, dry};
+  plan->B = B; plan->T = T; plan->ops.clear();
+  const int H = c.hidden_size, Lat = c.latent_dim, I = c.intermediate_size, D = c.codebook_dim;
+  const int M = B * T;
+  const size_t es = 2;  // 16-bit activations
+
+  // ---- RVQ -> E [B,T,D]
+  void* E = b.alloc((size_t)M * D * es);
+  {
+    plan->ops.emplace_back();
+    Op& op = plan->ops.back();
+    op.type = OP_RVQ; op.out = E; op.B = B; op.L = T; op.C = D;
+    b.tag(op, "quantizer", E, false, D, T);
+  }
+  // ---- pre_conv (k=3 causal) -> P [B,T,Lat]
+  void* P = b.alloc((size_t)M * Lat * es);
+  {
+    Op& op = b.gemm(e->pre_conv, E, B, T, T);
+    op.g.p.out_raw = P;
+    b.tag(op, "pre_conv", P, false, Lat, T);
+  }
+  // ---- transformer (reference modeling :500-574); rows = all tokens, residual stream in fp32
+  float* X = (float*)b.alloc((size_t)M * H * 4);
+  void* Hn = b.alloc((size_t)M * H * es);
+  void* QKV = b.alloc((size_t)M * 3 * H * es);
+  void* AO = b.alloc((size_t)M * H * es);
+  void* MI = b.alloc((size_t)M * I * es);
+  void* TO = b.alloc((size_t)M * Lat * es);
+  {
+    Op& op = b.gemm(e->in_proj, P, 1, M, M);
+    op.g.p.out_f32 = X;
+  }
+  for (int l = 0; l < c.num_hidden_layers; ++l) {
+    const LayerW& W = e->layers[l];
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H; }
+    { Op& op = b.gemm(W.qkv, Hn, 1, M, M); op.g.p.out_raw = QKV; }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = T; }
+    { Op& op = b.gemm(W.o, AO, 1, M, M); op.g.p.scale = W.ls1; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H; }
+    {
+      Op& op = b.gemm(W.gateup, Hn, 1, M, M);
+      op.g.p.act = ACT_GLU; op.g.p.out_raw = MI; op.g.p.out_row_stride = I; op.g.p.out_batch_stride = (long long)M * I;
+    }
+    { Op& op = b.gemm(W.down, MI, 1, M, M); op.g.p.scale = W.ls2; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
+  }
+  { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; }
+  {
+    Op& op = b.gemm(e->out_proj, Hn, 1, M, M);
+    op.g.p.out_raw = TO;
+    b.tag(op, "pre_transformer", TO, false, Lat, T);
+  }
+  // ---- upsample: [TransConv k=s ; ConvNeXt] x n (reference modeling :877-879, :226-242)
+  const void* cur = TO;
+  int L = T;
+  for (size_t i = 0; i < e->ups.size(); ++i) {
+    const UpsampleW& U = e->ups[i];
+    const int r = c.upsampling_ratios[i];
+    const int Lo = L * r;
+    void* Uo = b.alloc((size_t)B * Lo * Lat * es);
+    void* Nn = b.alloc((size_t)B * Lo * Lat * es);
+    void* G = b.alloc((size_t)B * Lo * 4 * Lat * es);
+    void* V = b.alloc((size_t)B * Lo * Lat * es);
+    {
+      Op& op = b.gemm(U.tconv, cur, 1, B * L, B * L);  // k == stride: rows are independent, flatten the batch
+      op.g.p.out_raw = Uo;
+      const std::string t = "upsample." + std::to_string(i) + ".0";
+      b.tag(op, t.c_str(), Uo, false, Lat, Lo);
+    }
+    {
+      plan->ops.emplace_back();
+      Op& op = plan->ops.back();
+      op.type = OP_DWLN; op.in = Uo; op.out = Nn; op.w0 = U.dww; op.w1 = U.dwb; op.w2 = U.lnw; op.w3 = U.lnb; op.B = B; op.L = Lo; op.C = Lat;
+    }
+    { Op& op = b.gemm(U.pw1, Nn, 1, B * Lo, B * Lo); op.g.p.act = ACT_GELU; op.g.p.out_raw = G; }
+    {
+      Op& op = b.gemm(U.pw2, G, 1, B * Lo, B * Lo);
+      op.g.p.scale = U.gamma; op.g.p.res = Uo; op.g.p.out_raw = V;
+      const std::string t = "upsample." + std::to_string(i) + ".1";
+      b.tag(op, t.c_str(), V, false, Lat, Lo);
+    }
+    cur = V; L = Lo;
+  }
+  // ---- vocoder: three rotating buffers sized for the largest stage
+  size_t big = (size_t)B * L * c.decoder_dim;
+  {
+    int Lb = L;
+    for (size_t i = 0; i < e->blocks.size(); ++i) {
+      Lb = (Lb - 1) * e->blocks[i].stride;
+      if (Lb < 0) Lb = 0;
+      const size_t n = (size_t)B * Lb * e->blocks[i].cout;
+      if (n > big) big = n;
+    }
+  }
+  void* R[3];
+  for (int i = 0; i < 3; ++i) R[i] = b.alloc(big * es + 4096);
+  int ia = 0, iy = 1, ifree = 2;  // ia: Snake'd conv input, iy: raw residual stream, ifree: scratch
+  {
+    // decoder[0]: conv7 Lat -> decoder_dim, epilogue applies block 1's input Snake (modeling :856, :645)
+    Op& op = b.gemm(e->dec0, cur, B, L, L);
+    op.g.p.out_snake = R[ia];
+    if (!e->blocks.empty()) { op.g.p.snake_a = e->blocks[0].act0.a; op.g.p.snake_ib = e->blocks[0].act0.ib; }
+    b.tag(op, "decoder.0.snake", R[ia], false, c.decoder_dim, L);
+  }
+  for (size_t i = 0; i < e->blocks.size(); ++i) {
+    const BlockW& K = e->blocks[i];
+    const int Lo = L > 0 ? (L - 1) * K.stride : 0;
+    {
+      // transposed conv: accumulator row q -> output rows q*s .. q*s+s-1 (modeling :200-207)
+      Op& op = b.gemm(K.tconv, R[ia], B, L, L - 1);
+      op.g.p.out_batch_stride = (long long)Lo * K.cout;
+      op.g.p.out_raw = R[iy];
+      op.g.p.out_snake = R[ifree];
+      op.g.p.snake_a = K.unit[0].act1.a; op.g.p.snake_ib = K.unit[0].act1.ib;
+      const std::string t = "decoder." + std::to_string(i + 1) + ".block.1";
+      b.tag(op, t.c_str(), R[iy], false, K.cout, Lo);
+      std::swap(ia, ifree);
+    }
+    L = Lo;
+    for (int j = 0; j < 3; ++j) {
+      const UnitW& U = K.unit[j];
+      {
+        Op& op = b.gemm(U.conv7, R[ia], B, L, L);
+        op.g.p.out_snake = R[ifree]; op.g.p.snake_a = U.act2.a; op.g.p.snake_ib = U.act2.ib;
+        std::swap(ia, ifree);
+      }
+      {
+        Op& op = b.gemm(U.conv1, R[ia], B, L, L);
+        op.g.p.res = R[iy]; op.g.p.out_raw = R[iy];
+        const SnakeP& nx = j < 2 ? K.unit[j + 1].act1 : (i + 1 < e->blocks.size() ? e->blocks[i + 1].act0 : e->tail_act);
+        op.g.p.out_snake = R[ifree]; op.g.p.snake_a = nx.a; op.g.p.snake_ib = nx.ib;
+        const std::string t = "decoder." + std::to_string(i + 1) + ".block." + std::to_string(j + 2);
+        b.tag(op, t.c_str(), R[iy], false, K.cout, L);
+        std::swap(ia, ifree);
+      }
+    }
+  }
+  {
+    plan->ops.emplace_back();
+    Op& op = plan->ops.back();
+    op.type = OP_TAIL; op.in = R[ia]; op.B = B; op.L = L; op.C = e->tail_c;
+    op.tag = "wav";
+  }
+  plan->out_len = L;
+  if (bytes) *bytes = b.off + 1024;
+  return b.rc;
+}
+
+}  // namespace
+
+size_t engine_plan_bytes(const Engine* e, int B, int T) {
+  Plan tmp;
+  size_t bytes = 0;
+  build(const_cast<Engine*>(e), &tmp, B, T, true, &bytes);
+  return bytes;
+}
+
+int engine_get_plan(Engine* e, int B, int T, Plan** out) {
+  auto key = std::make_pair(B, T);
+  auto it = e->plans.find(key);
+  if (it != e->plans.end()) { *out = &it->second; return 0; }
+  const size_t need = engine_plan_bytes(e, B, T);
+  if (need > e->ws_bytes) {
+    cudaDeviceSynchronize();
+    if (e->ws) cudaFree(e->ws);
+    e->ws = nullptr; e->ws_bytes = 0;
+    e->plans.clear();  // tensor maps point into the old workspace
+    if (cudaMalloc((void**)&e->ws, need) != cudaSuccess) { cudaGetLastError(); return e->fail(Q3TTS_OOM, "workspace cudaMalloc failed"); }
+    e->ws_bytes = need;
+  }
+  Plan& p = e->plans[key];
+  const int rc = build(e, &p, B, T, false, nullptr);
+  if (rc) { e->plans.erase(key); return rc; }
+  *out = &p;
+  return 0;
+}
+
+int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
+               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s) {
+  const q3tts_config& c = e->cfg;
+  for (Op& op : plan->ops) {
+    cudaError_t err = cudaSuccess;
+    switch (op.type) {
+      case OP_RVQ:
+        err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s);
+        break;
+      case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
+      case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s); break;
+      case OP_ATTN:
+        err = sliding_attention(op.in, e->rope_cos, e->rope_sin, op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->bf16, s);
+        break;
+      case OP_DWLN: err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s); break;
+      case OP_TAIL:
+        if (wav) err = tail_conv_clamp(op.in, e->tail_w, e->tail_bias, wav, wav_stride, op.B, op.L, op.C, skip, e->bf16, s);
+        break;
+    }
+    ++e->launches;
+    if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(err));
+    if (probe_stage && !op.tag.empty() && op.tag == probe_stage && op.type != OP_TAIL) {
+      const long long n = (long long)plan->B * op.probe_C * op.probe_L;
+      if (n > probe_cap) return e->fail(Q3TTS_BAD_SHAPE, "probe buffer too small");
+      err = to_channels_first_f32(op.probe_ptr, op.probe_f32, probe_out, plan->B, op.probe_L, op.probe_C, e->bf16, s);
+      if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("probe failed: ") + cudaGetErrorString(err));
+      if (pc) *pc = op.probe_C;
+      if (pl) *pl = op.probe_L;
+      return Q3TTS_OK;
+    }
+  }
+  if (probe_stage) return e->fail(Q3TTS_BAD_KEY, std::string("unknown probe stage: ") + probe_stage);
+  return Q3TTS_OK;
+}
+
+// forward over B items, split along the batch so that no launch exceeds the reserved frame budget
+int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
+                           long long wav_stride, int skip, cudaStream_t s) {
+  if (T > e->rope_max) return e->fail(Q3TTS_BAD_SHAPE, "T exceeds max_position_embeddings");
+  int per = e->max_frames / (T > 0 ? T : 1);
+  if (per < 1) per = 1;
+  for (int b0 = 0; b0 < B; b0 += per) {
+    const int nb = (B - b0) < per ? (B - b0) : per;
+    Plan* plan = nullptr;
+    int rc = engine_get_plan(e, nb, T, &plan);
+    if (rc) return rc;
+    rc = engine_run(e, plan, codes + b0 * sb, sb, sk, st, wav + (long long)b0 * wav_stride, wav_stride, skip, nullptr, nullptr, 0, nullptr, nullptr, s);
+    if (rc) return rc;
+  }
+  return Q3TTS_OK;
+}
+
+void engine_free(Engine* e) {
+  for (void* p : e->owned) cudaFree(p);
+  for (auto& kv : e->raw) cudaFree(kv.second.d);
+  if (e->ws) cudaFree(e->ws);
+  if (e->codes_stage) cudaFree(e->codes_stage);
+  if (e->wav_stage) cudaFree(e->wav_stage);
+}
+
+}  // namespace q3

@@ -1,0 +1,256 @@
+// Load-time repacking: reference state_dict tensors (fp32) -> tensor-core operand layouts.
+#include <cstdio>
+
+#include "engine.h"
+#include "kernels.h"
+
+namespace q3 {
+
+namespace {
+
+struct Fin {
+  Engine* e;
+  int rc = 0;
+  cudaStream_t s = 0;
+
+  const RawTensor* get(const std::string& key, std::initializer_list<int64_t> shape) {
+    if (rc) return nullptr;
+    auto it = e->raw.find(key);
+    if (it == e->raw.end()) { rc = e->fail(Q3TTS_BAD_KEY, "missing tensor: " + key); return nullptr; }
+    std::vector<int64_t> want(shape);
+    if (it->second.shape != want) {
+      std::string got;
+      for (auto v : it->second.shape) got += std::to_string(v) + ",";
+      rc = e->fail(Q3TTS_BAD_KEY, "bad shape for " + key + ": got [" + got + "]");
+      return nullptr;
+    }
+    return &it->second;
+  }
+  void* alloc(size_t bytes) {
+    if (rc) return nullptr;
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { rc = e->fail(Q3TTS_OOM, "cudaMalloc failed while packing weights"); return nullptr; }
+    e->owned.push_back(p);
+    return p;
+  }
+  void check(cudaError_t err, const char* what) {
+    if (!rc && err != cudaSuccess) rc = e->fail(Q3TTS_CUDA_ERROR, std::string(what) + ": " + cudaGetErrorString(err));
+  }
+  static int choose_bn(int n) {
+    for (int bn = 256; bn >= 16; bn -= 16)
+      if (n % bn == 0) return bn;
+    return 0;
+  }
+  void tiles(ConvW& w) {
+    w.bn = choose_bn(w.n_total);
+    w.kb = (w.cin % 64 == 0) ? 64 : 32;
+    if (!rc && (w.bn == 0 || w.cin % w.kb != 0 || w.ncol_mod % 16 != 0))
+      rc = e->fail(Q3TTS_BAD_CONFIG, "layer shape not tileable: n=" + std::to_string(w.n_total) + " cin=" + std::to_string(w.cin));
+  }
+  // Conv1d [cout][cin][k], dilation d, causal
+  ConvW conv(const std::string& prefix, int cout, int cin, int k, int dil, bool has_bias = true) {
+    ConvW w;
+    const RawTensor* t = get(prefix + ".weight", {cout, cin, k});
+    const RawTensor* b = has_bias ? get(prefix + ".bias", {cout}) : nullptr;
+    if (rc) return w;
+    w.taps = k; w.n_total = cout; w.cin = cin; w.ncol_mod = cout;
+    for (int j = 0; j < k; ++j) w.tap_off[j] = -(k - 1 - j) * dil;
+    w.bias = b ? b->d : nullptr;
+    w.w = alloc((size_t)cout * cin * k * 2);
+    if (!rc) check(pack_conv_weight(t->d, w.w, cout, cin, k, e->bf16, s), "pack_conv_weight");
+    tiles(w);
+    return w;
+  }
+  // Linear [n][k]
+  ConvW linear(const std::string& prefix, int n, int k, bool has_bias) {
+    ConvW w;
+    const RawTensor* t = get(prefix + ".weight", {n, k});
+    const RawTensor* b = has_bias ? get(prefix + ".bias", {n}) : nullptr;
+    if (rc) return w;
+    w.taps = 1; w.n_total = n; w.cin = k; w.ncol_mod = n;
+    w.bias = b ? b->d : nullptr;
+    w.w = alloc((size_t)n * k * 2);
+    if (!rc) check(pack_cast(t->d, w.w, (long long)n * k, e->bf16, s), "pack_cast");
+    tiles(w);
+    return w;
+  }
+  // ConvTranspose1d [cin][cout][k], stride st (k == 2*st or k == st)
+  ConvW tconv(const std::string& prefix, int cin, int cout, int k, int st) {
+    ConvW w;
+    const RawTensor* t = get(prefix + ".weight", {cin, cout, k});
+    const RawTensor* b = get(prefix + ".bias", {cout});
+    if (rc) return w;
+    if (k != st && k != 2 * st) { rc = e->fail(Q3TTS_BAD_CONFIG, "transposed conv needs k == stride or k == 2*stride"); return w; }
+    w.taps = k / st; w.n_total = st * cout; w.cin = cin; w.ncol_mod = cout;
+    w.tap_off[0] = 0; w.tap_off[1] = 1;
+    w.bias = b->d;
+    w.out_rows_per_row = st;
+    w.w = alloc((size_t)cin * cout * k * 2);
+    if (!rc) check(pack_transconv_weight(t->d, w.w, cin, cout, k, st, e->bf16, s), "pack_transconv_weight");
+    tiles(w);
+    return w;
+  }
+  SnakeP snake(const std::string& prefix, int c) {
+    SnakeP p;
+    const RawTensor* a = get(prefix + ".alpha", {c});
+    const RawTensor* b = get(prefix + ".beta", {c});
+    if (rc) return p;
+    float* buf = (float*)alloc((size_t)2 * c * sizeof(float));
+    if (rc) return p;
+    check(pack_snake(a->d, b->d, buf, buf + c, c, s), "pack_snake");
+    p.a = buf; p.ib = buf + c;
+    return p;
+  }
+  const float* vec(const std::string& key, int n) {
+    const RawTensor* t = get(key, {n});
+    return t ? t->d : nullptr;
+  }
+};
+
+}  // namespace
+
+int engine_finalize(Engine* e, int mode) {
+  if (mode != Q3TTS_MODE_FP16 && mode != Q3TTS_MODE_BF16) return e->fail(Q3TTS_BAD_CONFIG, "unknown compute mode");
+  const q3tts_config& c = e->cfg;
+  if (c.head_dim != 64) return e->fail(Q3TTS_BAD_CONFIG, "attention kernel is specialised for head_dim 64");
+  if (c.num_key_value_heads != c.num_attention_heads) return e->fail(Q3TTS_BAD_CONFIG, "GQA (kv heads != heads) not supported");
+  if (c.latent_dim != 1024 || c.hidden_size != c.num_attention_heads * c.head_dim)
+    return e->fail(Q3TTS_BAD_CONFIG, "latent_dim must be 1024 and hidden_size = heads*head_dim");
+  if (c.codebook_dim % 4 != 0 || c.codebook_dim > 4096) return e->fail(Q3TTS_BAD_CONFIG, "codebook_dim must be a multiple of 4");
+  for (void* p : e->owned) cudaFree(p);
+  e->owned.clear();
+  e->plans.clear();
+  e->finalized = false;
+  e->bf16 = (mode == Q3TTS_MODE_BF16);
+  if (gemm_setup(e->device)) return e->fail(Q3TTS_CUDA_ERROR, "gemm_setup failed (cuTensorMapEncodeTiled unavailable or smem opt-in rejected)");
+
+  Fin f{e};
+  const int H = c.hidden_size, Lat = c.latent_dim, I = c.intermediate_size, D = c.codebook_dim, dq = D / 2, Q = c.num_quantizers;
+  // ---- RVQ: fold output_proj into the codebooks (fp32)
+  e->rvq_tables = (float*)f.alloc((size_t)Q * c.codebook_size * D * sizeof(float));
+  for (int k = 0; k < Q && !f.rc; ++k) {
+    const std::string name = k == 0 ? "rvq_first" : "rvq_rest";
+    const int li = k == 0 ? 0 : k - 1;
+    const std::string cb = "quantizer." + name + ".vq.layers." + std::to_string(li) + "._codebook.";
+    const RawTensor* es = f.get(cb + "embedding_sum", {c.codebook_size, dq});
+    const RawTensor* cu = f.get(cb + "cluster_usage", {c.codebook_size});
+    const RawTensor* wo = f.get("quantizer." + name + ".output_proj.weight", {D, dq, 1});
+    if (f.rc) break;
+    f.check(fold_codebook(es->d, cu->d, wo->d, e->rvq_tables + (size_t)k * c.codebook_size * D, c.codebook_size, dq, D, f.s), "fold_codebook");
+  }
+  // ---- pre_conv + transformer
+  e->pre_conv = f.conv("pre_conv.conv", Lat, D, 3, 1);
+  e->in_proj = f.linear("pre_transformer.input_proj", H, Lat, true);
+  e->out_proj = f.linear("pre_transformer.output_proj", Lat, H, true);
+  e->final_norm = f.vec("pre_transformer.norm.weight", H);
+  e->layers.assign(c.num_hidden_layers, LayerW());
+  for (int l = 0; l < c.num_hidden_layers && !f.rc; ++l) {
+    const std::string p = "pre_transformer.layers." + std::to_string(l) + ".";
+    LayerW& L = e->layers[l];
+    const RawTensor* q = f.get(p + "self_attn.q_proj.weight", {H, H});
+    const RawTensor* k = f.get(p + "self_attn.k_proj.weight", {H, H});
+    const RawTensor* v = f.get(p + "self_attn.v_proj.weight", {H, H});
+    if (f.rc) break;
+    L.qkv.taps = 1; L.qkv.n_total = 3 * H; L.qkv.cin = H; L.qkv.ncol_mod = 3 * H;
+    L.qkv.w = f.alloc((size_t)3 * H * H * 2);
+    if (f.rc) break;
+    f.check(pack_cast(q->d, L.qkv.w, (long long)H * H, e->bf16, f.s), "pack q");
+    f.check(pack_cast(k->d, (uint8_t*)L.qkv.w + (size_t)H * H * 2, (long long)H * H, e->bf16, f.s), "pack k");
+    f.check(pack_cast(v->d, (uint8_t*)L.qkv.w + (size_t)2 * H * H * 2, (long long)H * H, e->bf16, f.s), "pack v");
+    f.tiles(L.qkv);
+    L.o = f.linear(p + "self_attn.o_proj", H, H, false);
+    const RawTensor* g = f.get(p + "mlp.gate_proj.weight", {I, H});
+    const RawTensor* u = f.get(p + "mlp.up_proj.weight", {I, H});
+    if (f.rc) break;
+    L.gateup.taps = 1; L.gateup.n_total = 2 * I; L.gateup.cin = H; L.gateup.ncol_mod = 2 * I;
+    L.gateup.w = f.alloc((size_t)2 * I * H * 2);
+    if (f.rc) break;
+    f.check(pack_interleave2(g->d, u->d, L.gateup.w, I, H, e->bf16, f.s), "pack gate/up");
+    f.tiles(L.gateup);
+    L.down = f.linear(p + "mlp.down_proj", H, I, false);
+    L.ln1 = f.vec(p + "input_layernorm.weight", H);
+    L.ln2 = f.vec(p + "post_attention_layernorm.weight", H);
+    L.ls1 = f.vec(p + "self_attn_layer_scale.scale", H);
+    L.ls2 = f.vec(p + "mlp_layer_scale.scale", H);
+  }
+  // ---- upsample stages
+  e->ups.assign(c.num_upsampling_ratios, UpsampleW());
+  for (int i = 0; i < c.num_upsampling_ratios && !f.rc; ++i) {
+    const std::string p = "upsample." + std::to_string(i) + ".";
+    const int r = c.upsampling_ratios[i];
+    UpsampleW& U = e->ups[i];
+    U.tconv = f.tconv(p + "0.conv", Lat, Lat, r, r);
+    const RawTensor* dw = f.get(p + "1.dwconv.conv.weight", {Lat, 1, 7});
+    if (f.rc) break;
+    float* dww = (float*)f.alloc((size_t)7 * Lat * sizeof(float));
+    if (f.rc) break;
+    f.check(pack_dw_weight(dw->d, dww, Lat, 7, f.s), "pack_dw_weight");
+    U.dww = dww;
+    U.dwb = f.vec(p + "1.dwconv.conv.bias", Lat);
+    U.lnw = f.vec(p + "1.norm.weight", Lat);
+    U.lnb = f.vec(p + "1.norm.bias", Lat);
+    U.gamma = f.vec(p + "1.gamma", Lat);
+    U.pw1 = f.linear(p + "1.pwconv1", 4 * Lat, Lat, true);
+    U.pw2 = f.linear(p + "1.pwconv2", Lat, 4 * Lat, true);
+  }
+  // ---- vocoder
+  const int Dd = c.decoder_dim;
+  e->dec0 = f.conv("decoder.0.conv", Dd, Lat, 7, 1);
+  e->blocks.assign(c.num_upsample_rates, BlockW());
+  int total_up = 1, look = 0;
+  for (int i = 0; i < c.num_upsampling_ratios; ++i) total_up *= c.upsampling_ratios[i];
+  for (int i = 0; i < c.num_upsample_rates && !f.rc; ++i) {
+    BlockW& Bk = e->blocks[i];
+    Bk.cin = Dd >> i; Bk.cout = Dd >> (i + 1); Bk.stride = c.upsample_rates[i];
+    const std::string p = "decoder." + std::to_string(i + 1) + ".block.";
+    Bk.act0 = f.snake(p + "0", Bk.cin);
+    Bk.tconv = f.tconv(p + "1.conv", Bk.cin, Bk.cout, 2 * Bk.stride, Bk.stride);
+    const int dil[3] = {1, 3, 9};
+    for (int j = 0; j < 3 && !f.rc; ++j) {
+      const std::string u = p + std::to_string(j + 2) + ".";
+      Bk.unit[j].act1 = f.snake(u + "act1", Bk.cout);
+      Bk.unit[j].conv7 = f.conv(u + "conv1.conv", Bk.cout, Bk.cout, 7, dil[j]);
+      Bk.unit[j].act2 = f.snake(u + "act2", Bk.cout);
+      Bk.unit[j].conv1 = f.conv(u + "conv2.conv", Bk.cout, Bk.cout, 1, 1);
+    }
+    total_up *= Bk.stride;
+    look = look * Bk.stride + Bk.stride;  // each k=2s transposed conv drops s samples at its own rate
+  }
+  e->total_up = total_up;
+  e->lookahead = look;
+  const int n = c.num_upsample_rates;
+  const int Cl = Dd >> n;
+  e->tail_c = Cl;
+  e->tail_act = f.snake("decoder." + std::to_string(n + 1), Cl);
+  {
+    const RawTensor* tw = f.get("decoder." + std::to_string(n + 2) + ".conv.weight", {1, Cl, 7});
+    const RawTensor* tb = f.get("decoder." + std::to_string(n + 2) + ".conv.bias", {1});
+    if (!f.rc) {
+      e->tail_w = (float*)f.alloc((size_t)7 * Cl * sizeof(float));
+      if (!f.rc) f.check(pack_dw_weight(tw->d, e->tail_w, Cl, 7, f.s), "pack tail");
+      if (!f.rc) f.check(cudaMemcpy(&e->tail_bias, tb->d, sizeof(float), cudaMemcpyDeviceToHost), "tail bias");
+    }
+  }
+  // ---- RoPE table
+  if (!f.rc) {
+    e->rope_max = c.max_position_embeddings;
+    e->rope_cos = (float*)f.alloc((size_t)e->rope_max * 32 * sizeof(float));
+    e->rope_sin = (float*)f.alloc((size_t)e->rope_max * 32 * sizeof(float));
+    if (!f.rc) f.check(rope_table(e->rope_cos, e->rope_sin, e->rope_max, c.head_dim, c.rope_theta, f.s), "rope_table");
+  }
+  if (!f.rc) f.check(cudaDeviceSynchronize(), "finalize sync");
+  if (f.rc) return f.rc;
+  // big fp32 sources are no longer needed; keep vectors (biases, norms, scales) that kernels read directly
+  for (auto it = e->raw.begin(); it != e->raw.end();) {
+    if (it->second.shape.size() >= 2) {
+      cudaFree(it->second.d);
+      it = e->raw.erase(it);
+    } else {
+      ++it;
+    }
+  }
+  e->finalized = true;
+  return Q3TTS_OK;
+}
+
+}  // namespace q3

@@ -1,0 +1,54 @@
+// Parameters of the implicit-GEMM causal conv / transposed conv / linear kernel.
+//
+//   D[b, t, n] = sum_{tap} sum_{ci} A[b, t + tap_off[tap], ci] * W[tap, n, ci]         (fp32 accumulate)
+//
+// A is a channels-last activation [batches][rows][cin]; rows outside [0, rows) read as zero
+// (TMA out-of-bounds fill), which IS the reference's causal left padding
+// (modeling_qwen3_tts_tokenizer_v2.py:189-192).  A k-tap dilated causal conv uses
+// tap_off = -(k-1-j)*dil; a stride-s, kernel-2s transposed conv with the reference's symmetric
+// trim (modeling :200-207) is the same GEMM with two taps {0, +1} and N = s*Cout, because
+//   y[q*s + p, co] = x[q] . W[:, co, p + s] + x[q+1] . W[:, co, p]
+// so one accumulator row q holds s consecutive output rows (out_row_stride = s*Cout).
+//
+// Epilogue, applied per element in this order:
+//   v = acc + bias[n % ncol_mod]; act (GELU erf | GLU silu(g)*u on interleaved column pairs);
+//   v *= scale[n % ncol_mod]; v += res[b, t, n];
+//   out_raw / out_f32 <- v;  out_snake <- v + snake_ib[c] * sin^2(snake_a[c] * v)   (SnakeBeta of the NEXT layer,
+//   modeling :601-615, with a = exp(alpha), ib = 1/(exp(beta)+1e-9) precomputed at load).
+#pragma once
+#include <stdint.h>
+
+namespace q3 {
+
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2 };
+
+struct GemmParams {
+  int batches;
+  int rows;        // A rows per batch item
+  int rows_valid;  // accumulator rows per batch item that are stored
+  int cin;
+  int ntaps;
+  int tap_off[8];
+  int n_total;
+  int bn;  // N tile, multiple of 16, <= 256, divides n_total
+  int kb;  // K block in elements: 64 (SWIZZLE_128B) or 32 (SWIZZLE_64B)
+  int ncol_mod;
+  int act;
+  int res_f32;
+  int bf16;
+  const float* bias;
+  const float* scale;
+  const void* res;
+  void* out_raw;
+  float* out_f32;
+  void* out_snake;
+  const float* snake_a;
+  const float* snake_ib;
+  long long out_batch_stride;  // elements
+  long long out_row_stride;    // elements
+  // raw operand pointers, used only by the SIMT cross-check kernel
+  const void* a_ptr;
+  const void* w_ptr;
+};
+
+}  // namespace q3

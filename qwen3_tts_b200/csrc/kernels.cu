@@ -1,0 +1,126 @@
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace q3 {
+
+static inline int nblocks(long long n, int threads, int cap = 148 * 32) {
+  long long b = (n + threads - 1) / threads;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+#define Q3_DISPATCH(bf16, ...)                                   \
+  do {                                                            \
+    if (bf16) { using T = __nv_bfloat16; __VA_ARGS__; }           \
+    else { using T = __half; __VA_ARGS__; }                       \
+  } while (0)
+
+// ============================================================================================ packers
+template <typename T>
+__global__ void k_pack_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int k) {
+  const long long n = (long long)cout * cin * k;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % cin);
+    const int co = (int)((i / cin) % cout);
+    const int j = (int)(i / ((long long)cin * cout));
+    dst[i] = Elem<T>::from_f(src[((long long)co * cin + ci) * k + j]);
+  }
+}
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s) {
+  const long long n = (long long)cout * cin * k;
+  Q3_DISPATCH(bf16, (k_pack_conv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cout, cin, k)));
+  return cudaGetLastError();
+}
+
+template <typename T>
+__global__ void k_pack_transconv(const float* __restrict__ src, T* __restrict__ dst, int cin, int cout, int k, int st) {
+  const int taps = k / st;  // 2 (k = 2*st) or 1 (k = st)
+  const long long n = (long long)taps * st * cout * cin;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % cin);
+    const long long r = i / cin;
+    const int co = (int)(r % cout);
+    const int p = (int)((r / cout) % st);
+    const int tap = (int)(r / ((long long)cout * st));
+    // tap 0 multiplies x[q]; for k = 2*st that is kernel index p + st, tap 1 (x[q+1]) is index p
+    const int kk = (taps == 2) ? (tap == 0 ? p + st : p) : p;
+    dst[i] = Elem<T>::from_f(src[((long long)ci * cout + co) * k + kk]);
+  }
+}
+cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s) {
+  const long long n = (long long)cin * cout * k;
+  Q3_DISPATCH(bf16, (k_pack_transconv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cin, cout, k, st)));
+  return cudaGetLastError();
+}
+
+template <typename T>
+__global__ void k_pack_interleave2(const float* __restrict__ a, const float* __restrict__ b, T* __restrict__ dst, int n, int k) {
+  const long long tot = 2ll * n * k;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < tot; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % k);
+    const long long r = i / k;
+    const float* src = (r & 1) ? b : a;
+    dst[i] = Elem<T>::from_f(src[(r >> 1) * k + c]);
+  }
+}
+cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s) {
+  Q3_DISPATCH(bf16, (k_pack_interleave2<T><<<nblocks(2ll * n * k, 256), 256, 0, s>>>(a, b, (T*)dst, n, k)));
+  return cudaGetLastError();
+}
+
+template <typename T>
+__global__ void k_pack_cast(const float* __restrict__ src, T* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = Elem<T>::from_f(src[i]);
+}
+cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaStream_t s) {
+  Q3_DISPATCH(bf16, (k_pack_cast<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, n)));
+  return cudaGetLastError();
+}
+
+__global__ void k_pack_snake(const float* alpha, const float* beta, float* a, float* ib, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    a[i] = expf(alpha[i]);
+    ib[i] = 1.0f / (expf(beta[i]) + 1e-9f);
+  }
+}
+cudaError_t pack_snake(const float* alpha, const float* beta, float* a, float* ib, int n, cudaStream_t s) {
+  k_pack_snake<<<(n + 127) / 128, 128, 0, s>>>(alpha, beta, a, ib, n);
+  return cudaGetLastError();
+}
+
+__global__ void k_pack_dw(const float* __restrict__ src, float* __restrict__ dst, int C, int k) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < C * k) {
+    const int c = i % C, j = i / C;
+    dst[i] = src[c * k + j];
+  }
+}
+cudaError_t pack_dw_weight(const float* src, float* dst, int C, int k, cudaStream_t s) {
+  k_pack_dw<<<(C * k + 127) / 128, 128, 0, s>>>(src, dst, C, k);
+  return cudaGetLastError();
+}
+
+// folded[code][d] = sum_j (es[code][j] / max(usage[code], 1e-5)) * wout[d][j]; one block per code.
+__global__ void k_fold_codebook(const float* __restrict__ es, const float* __restrict__ usage, const float* __restrict__ wout,
+                                float* __restrict__ folded, int dq, int d) {
+  extern __shared__ float row[];
+  const int code = blockIdx.x;
+  const float u = fmaxf(usage[code], 1e-5f);
+  for (int j = threadIdx.x; j < dq; j += blockDim.x) row[j] = es[(long long)code * dq + j] / u;
+  __syncthreads();
+  for (int o = threadIdx.x; o < d; o += blockDim.x) {
+    const float* w = wout + (long long)o * dq;
+    float acc = 0.f;
+    for (int j = 0; j < dq; ++j) acc = fmaf(row[j], w[j], acc);
+    folded[(long long)code * d + o] = acc;
+  }
+}
+cudaError_t fold_codebook(const float* es, const float* usage, const float* wout, float* folded, int ncodes, int dq, int d, cudaStream_t s) {
+  k_fold_codebook<<<ncodes, 256, dq * sizeof(float), s>>>(es, usage, wout, folded, dq, d);
+  return cudaGetLastError();
+}
+
+}  // namespace q3

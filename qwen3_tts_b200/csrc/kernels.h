@@ -1,0 +1,48 @@
+// Bandwidth-bound SIMT kernels of the decode path and the load-time weight packers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace q3 {
+
+// ---- load-time packers (fp32 reference layouts -> 16-bit K-major GEMM operands)
+// Conv1d weight [Cout][Cin][k] -> [k][Cout][Cin]
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s);
+// ConvTranspose1d weight [Cin][Cout][k], stride st.  k == 2*st: two taps, tap0 (x[q]) = W[..., p+st],
+// tap1 (x[q+1]) = W[..., p]; k == st: one tap W[..., p].  dst [taps][st*Cout][Cin], row = p*Cout + co.
+cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s);
+// rows of `a` and `b` ([n][k] each) interleaved: dst[2i] = a[i], dst[2i+1] = b[i]
+cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s);
+// plain cast [n] fp32 -> 16-bit
+cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaStream_t s);
+// Snake: a = exp(alpha), ib = 1/(exp(beta)+1e-9)
+cudaError_t pack_snake(const float* alpha, const float* beta, float* a, float* ib, int n, cudaStream_t s);
+// RVQ: folded[code][d] = sum_j (embedding_sum[code][j] / max(cluster_usage[code],1e-5)) * Wout[d][j]   (fp32)
+cudaError_t fold_codebook(const float* embedding_sum, const float* cluster_usage, const float* wout, float* folded, int ncodes, int dq, int d,
+                          cudaStream_t s);
+
+// ---- hot-path SIMT kernels
+// codes int64 addressed as codes[b*sb + k*sk + t*st]; tables [Q][ncodes][D] fp32; out_act [B][T][D] 16-bit (optional);
+// out_f32 [B][D][T] (optional)
+cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
+                       int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s);
+// x fp32 [M][H] -> 16-bit [M][H]: w * x * rsqrt(mean(x^2) + eps)
+cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s);
+// rope table [maxT][hd/2] cos, sin (fp32)
+cudaError_t rope_table(float* cos_t, float* sin_t, int maxT, int hd, float theta, cudaStream_t s);
+// qkv 16-bit [B*T][3*nh*hd] (q | k | v), RoPE applied on the fly with position = t; causal, kv > q - window.
+cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* sin_t, void* out, int B, int T, int nh, int hd, int window,
+                              bool bf16, cudaStream_t s);
+// ConvNeXt front half: depthwise causal conv k=7 + bias, LayerNorm(eps) over C.  x,out 16-bit [B][L][C]; dw weight [7][C] fp32.
+cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
+                             float eps, bool bf16, cudaStream_t s);
+// tail: x 16-bit [B][L][C] (already Snake'd), w [7][C] fp32, bias -> clamp(conv, -1, 1); sample l >= skip is written to
+// out[b*out_batch_stride + l - skip] (skip drops a chunk's left-context samples, reference modeling :893)
+cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* out, long long out_batch_stride, int B, int L, int C, int skip,
+                            bool bf16, cudaStream_t s);
+// probes: activation [B][L][C] (16-bit or fp32) -> fp32 [B][C][L]
+cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s);
+// dw weight [C][1][7] -> [7][C]
+cudaError_t pack_dw_weight(const float* src, float* dst, int C, int k, cudaStream_t s);
+
+}  // namespace q3

@@ -1,0 +1,224 @@
+// Bandwidth-bound stages of the decode path: RVQ gather-sum, RMSNorm, RoPE + sliding-window
+// attention, depthwise conv + LayerNorm, tail conv + clamp, layout probes.
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace q3 {
+
+#define Q3_DISPATCH(bf16, ...)                                   \
+  do {                                                            \
+    if (bf16) { using T = __nv_bfloat16; __VA_ARGS__; }           \
+    else { using T = __half; __VA_ARGS__; }                       \
+  } while (0)
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ============================================================================================ RVQ
+// One block per frame; thread i owns 4 consecutive channels.  Book 0 (rvq_first) plus the
+// left-to-right sum of books 1..Q-1 (rvq_rest), as the reference sums them (modeling :720-726, :817-819).
+template <typename T>
+__global__ void k_rvq(const long long* __restrict__ codes, long long sb, long long sk, long long st, const float* __restrict__ tables,
+                      T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D) {
+  const int t = blockIdx.x, b = blockIdx.y;
+  const int d = threadIdx.x * 4;
+  if (d >= D) return;
+  float4 first = make_float4(0.f, 0.f, 0.f, 0.f), rest = first;
+  for (int k = 0; k < Q; ++k) {
+    long long c = codes[b * sb + k * sk + t * st];
+    c = c < 0 ? 0 : (c >= ncodes ? ncodes - 1 : c);  // never fault on a bad code; range errors are reported by the checked entry
+    const float4 e = __ldg(reinterpret_cast<const float4*>(tables + ((long long)k * ncodes + c) * D + d));
+    if (k == 0) first = e;
+    else { rest.x += e.x; rest.y += e.y; rest.z += e.z; rest.w += e.w; }
+  }
+  const float4 v = make_float4(first.x + rest.x, first.y + rest.y, first.z + rest.z, first.w + rest.w);
+  if (out_act) {
+    uint2 o;
+    o.x = Elem<T>::pack2(v.x, v.y);
+    o.y = Elem<T>::pack2(v.z, v.w);
+    *reinterpret_cast<uint2*>(out_act + ((long long)b * Tn + t) * D + d) = o;
+  }
+  if (out_f32) {
+    float* o = out_f32 + ((long long)b * D + d) * Tn + t;
+    o[0] = v.x; o[Tn] = v.y; o[2ll * Tn] = v.z; o[3ll * Tn] = v.w;
+  }
+}
+cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
+                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s) {
+  if (B <= 0 || Tn <= 0) return cudaSuccess;
+  dim3 grid(Tn, B);
+  const int threads = ((D / 4 + 31) / 32) * 32;
+  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D)));
+  return cudaGetLastError();
+}
+
+// ============================================================================================ RMSNorm
+// One warp per row (reference modeling :382-387, computed in fp32).
+template <typename T>
+__global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__ w, T* __restrict__ out, int M, int H, float eps) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + (long long)row * H);
+  const int n4 = H >> 2;
+  float ss = 0.f;
+  for (int i = lane; i < n4; i += 32) {
+    const float4 v = xr[i];
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = warp_sum(ss);
+  const float r = rsqrtf(ss / (float)H + eps);
+  const float4* wr = reinterpret_cast<const float4*>(w);
+  for (int i = lane; i < n4; i += 32) {
+    const float4 v = xr[i];
+    const float4 g = __ldg(wr + i);
+    uint2 o;
+    o.x = Elem<T>::pack2(g.x * (v.x * r), g.y * (v.y * r));
+    o.y = Elem<T>::pack2(g.z * (v.z * r), g.w * (v.w * r));
+    *reinterpret_cast<uint2*>(out + (long long)row * H + i * 4) = o;
+  }
+}
+cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s) {
+  if (M <= 0) return cudaSuccess;
+  Q3_DISPATCH(bf16, (k_rmsnorm<T><<<(M + 7) / 8, 256, 0, s>>>(x, w, (T*)out, M, H, eps)));
+  return cudaGetLastError();
+}
+
+// ============================================================================================ RoPE table
+// cos/sin of pos * theta^(-2i/hd), fp32, as DecoderRotatoryEmbedding computes them (modeling :268-276).
+__global__ void k_rope_table(float* cos_t, float* sin_t, int maxT, int half, float theta, int hd) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= maxT * half) return;
+  const int pos = i / half, j = i % half;
+  const float inv = 1.0f / powf(theta, (float)(2 * j) / (float)hd);
+  const float f = (float)pos * inv;
+  cos_t[i] = cosf(f);
+  sin_t[i] = sinf(f);
+}
+cudaError_t rope_table(float* cos_t, float* sin_t, int maxT, int hd, float theta, cudaStream_t s) {
+  const int n = maxT * (hd / 2);
+  k_rope_table<<<(n + 255) / 256, 256, 0, s>>>(cos_t, sin_t, maxT, hd / 2, theta, hd);
+  return cudaGetLastError();
+}
+
+// ============================================================================================ attention
+// Block = (32-query tile, head, batch item); 8 warps x 4 queries.  K (RoPE applied) and V of the
+// <= window-1+32 keys a tile can see are staged in shared memory; scores use one lane per key,
+// softmax in fp32 (reference modeling :134-141), mask = kv <= q && kv > q - window.
+static constexpr int ATT_QT = 32;
+static constexpr int ATT_HD = 64;
+static constexpr int ATT_KSTR = ATT_HD + 2;  // 33-word row pitch: conflict-free lane-per-key reads
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t, T* __restrict__ out, int Tn, int nh,
+            int window) {
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  const int q0 = blockIdx.x * ATT_QT, h = blockIdx.y, b = blockIdx.z;
+  const int k_lo = max(0, q0 - window + 1);
+  const int k_hi = min(Tn, q0 + ATT_QT);  // exclusive
+  const int nk = k_hi - k_lo;
+  const int maxk = window - 1 + ATT_QT;
+  T* sK = reinterpret_cast<T*>(att_smem);
+  T* sV = sK + (((size_t)maxk * ATT_KSTR + 7) & ~(size_t)7);  // keep V rows 16-byte aligned
+  float* sQ = reinterpret_cast<float*>(sV + (size_t)maxk * ATT_HD);  // [8 warps][64]
+  float* sP = sQ + 8 * ATT_HD;                                        // [8 warps][maxk rounded to 32]
+  const int pstride = ((maxk + 31) / 32) * 32;
+  const int ld = 3 * nh * ATT_HD;
+  const T* base = qkv + (long long)b * Tn * ld;
+  // stage K with RoPE: item = (key, d < 32) handles the pair (d, d + 32)
+  for (int i = threadIdx.x; i < nk * 32; i += blockDim.x) {
+    const int kk = i >> 5, d = i & 31;
+    const int t = k_lo + kk;
+    const T* kr = base + (long long)t * ld + nh * ATT_HD + h * ATT_HD;
+    const float x1 = Elem<T>::to_f(kr[d]), x2 = Elem<T>::to_f(kr[d + 32]);
+    const float c = cos_t[t * 32 + d], sn = sin_t[t * 32 + d];
+    sK[kk * ATT_KSTR + d] = Elem<T>::from_f(x1 * c - x2 * sn);
+    sK[kk * ATT_KSTR + d + 32] = Elem<T>::from_f(x2 * c + x1 * sn);
+  }
+  for (int i = threadIdx.x; i < nk * 8; i += blockDim.x) {
+    const int kk = i >> 3, c8 = i & 7;
+    const T* vr = base + (long long)(k_lo + kk) * ld + 2 * nh * ATT_HD + h * ATT_HD;
+    reinterpret_cast<uint4*>(sV + (size_t)kk * ATT_HD)[c8] = reinterpret_cast<const uint4*>(vr)[c8];
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* q = sQ + warp * ATT_HD;
+  float* pr = sP + warp * pstride;
+  for (int qi = warp; qi < ATT_QT; qi += 8) {
+    const int tq = q0 + qi;
+    if (tq >= Tn) break;
+    {
+      const T* qr = base + (long long)tq * ld + h * ATT_HD;
+      const float x1 = Elem<T>::to_f(qr[lane]), x2 = Elem<T>::to_f(qr[lane + 32]);
+      const float c = cos_t[tq * 32 + lane], sn = sin_t[tq * 32 + lane];
+      q[lane] = x1 * c - x2 * sn;
+      q[lane + 32] = x2 * c + x1 * sn;
+    }
+    __syncwarp();
+    const int lo = max(0, tq - window + 1);  // first visible key
+    const int nvis = tq - lo + 1;
+    float mx = -INFINITY;
+    for (int j0 = 0; j0 < nvis; j0 += 32) {
+      const int j = j0 + lane;
+      float sc = -INFINITY;
+      if (j < nvis) {
+        const uint32_t* kr = reinterpret_cast<const uint32_t*>(sK + (size_t)(lo - k_lo + j) * ATT_KSTR);
+        float acc = 0.f;
+#pragma unroll
+        for (int d2 = 0; d2 < 32; ++d2) {
+          const float2 kv = Elem<T>::unpack2(kr[d2]);
+          acc = fmaf(q[2 * d2], kv.x, acc);
+          acc = fmaf(q[2 * d2 + 1], kv.y, acc);
+        }
+        sc = acc * 0.125f;
+      }
+      pr[j] = sc;
+      mx = fmaxf(mx, sc);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int j0 = 0; j0 < nvis; j0 += 32) {
+      const int j = j0 + lane;
+      if (j < nvis) {
+        const float e = __expf(pr[j] - mx);
+        pr[j] = e;
+        sum += e;
+      }
+    }
+    sum = warp_sum(sum);
+    __syncwarp();
+    const float inv = 1.0f / sum;
+    float o0 = 0.f, o1 = 0.f;
+    const uint32_t* vb = reinterpret_cast<const uint32_t*>(sV + (size_t)(lo - k_lo) * ATT_HD) + lane;
+    for (int j = 0; j < nvis; ++j) {
+      const float pj = pr[j];
+      const float2 vv = Elem<T>::unpack2(vb[j * (ATT_HD / 2)]);
+      o0 = fmaf(pj, vv.x, o0);
+      o1 = fmaf(pj, vv.y, o1);
+    }
+    reinterpret_cast<uint32_t*>(out + ((long long)b * Tn + tq) * (nh * ATT_HD) + h * ATT_HD)[lane] = Elem<T>::pack2(o0 * inv, o1 * inv);
+    __syncwarp();
+  }
+}
+cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* sin_t, void* out, int B, int Tn, int nh, int hd, int window,
+                              bool bf16, cudaStream_t s) {
+  if (hd != ATT_HD) return cudaErrorInvalidValue;
+  if (B <= 0 || Tn <= 0) return cudaSuccess;
+  const int maxk = window - 1 + ATT_QT;
+  const int pstride = ((maxk + 31) / 32) * 32;
+  const size_t smem = ((((size_t)maxk * ATT_KSTR + 7) & ~(size_t)7) + (size_t)maxk * ATT_HD) * 2 + 8 * ATT_HD * 4 + 8 * pstride * 4;
+  dim3 grid((Tn + ATT_QT - 1) / ATT_QT, nh, B);
+  Q3_DISPATCH(bf16, (k_attention<T><<<grid, 256, smem, s>>>((const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
+  return cudaGetLastError();
+}
+
+}  // namespace q3

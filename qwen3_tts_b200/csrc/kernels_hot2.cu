@@ -1,0 +1,159 @@
+// ConvNeXt depthwise conv + LayerNorm, tail 96->1 conv + clamp, layout probes.
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace q3 {
+
+#define Q3_DISPATCH(bf16, ...)                                   \
+  do {                                                            \
+    if (bf16) { using T = __nv_bfloat16; __VA_ARGS__; }           \
+    else { using T = __half; __VA_ARGS__; }                       \
+  } while (0)
+
+__device__ __forceinline__ float warp_sum2(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ============================================================================================ dwconv + LN
+// One warp per output row; lane owns channels {4*lane + 128*i .. +3}.  Depthwise causal conv k=7
+// (left zero padding, reference modeling :213-219, :189-192) then LayerNorm over C (modeling :220, :231).
+template <typename T, int NI>
+__global__ void __launch_bounds__(256)
+k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float* __restrict__ dwb, const float* __restrict__ lnw,
+            const float* __restrict__ lnb, T* __restrict__ out, int B, int L, int C, float eps) {
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= (long long)B * L) return;
+  const int l = (int)(row % L);
+  float acc[NI][4];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(dwb + 4 * lane + 128 * i));
+    acc[i][0] = bb.x; acc[i][1] = bb.y; acc[i][2] = bb.z; acc[i][3] = bb.w;
+  }
+#pragma unroll
+  for (int j = 0; j < 7; ++j) {
+    const int lt = l - 6 + j;
+    if (lt < 0) continue;
+    const T* xr = x + (row - 6 + j) * C;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = 4 * lane + 128 * i;
+      const uint2 u = *reinterpret_cast<const uint2*>(xr + c);
+      const float2 a = Elem<T>::unpack2(u.x), bq = Elem<T>::unpack2(u.y);
+      const float4 w = __ldg(reinterpret_cast<const float4*>(dww + (long long)j * C + c));
+      acc[i][0] = fmaf(w.x, a.x, acc[i][0]);
+      acc[i][1] = fmaf(w.y, a.y, acc[i][1]);
+      acc[i][2] = fmaf(w.z, bq.x, acc[i][2]);
+      acc[i][3] = fmaf(w.w, bq.y, acc[i][3]);
+    }
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NI; ++i) s += acc[i][0] + acc[i][1] + acc[i][2] + acc[i][3];
+  const float mean = warp_sum2(s) / (float)C;
+  float v = 0.f;
+#pragma unroll
+  for (int i = 0; i < NI; ++i)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { const float d = acc[i][e] - mean; v = fmaf(d, d, v); }
+  const float rstd = rsqrtf(warp_sum2(v) / (float)C + eps);
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const int c = 4 * lane + 128 * i;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(lnw + c));
+    const float4 bt = __ldg(reinterpret_cast<const float4*>(lnb + c));
+    uint2 o;
+    o.x = Elem<T>::pack2((acc[i][0] - mean) * rstd * g.x + bt.x, (acc[i][1] - mean) * rstd * g.y + bt.y);
+    o.y = Elem<T>::pack2((acc[i][2] - mean) * rstd * g.z + bt.z, (acc[i][3] - mean) * rstd * g.w + bt.w);
+    *reinterpret_cast<uint2*>(out + row * C + c) = o;
+  }
+}
+cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
+                             float eps, bool bf16, cudaStream_t s) {
+  if (C != 1024) return cudaErrorInvalidValue;  // NI = C / 128 is a compile-time unroll
+  const long long rows = (long long)B * L;
+  if (rows <= 0) return cudaSuccess;
+  const int blocks = (int)((rows + 7) / 8);
+  Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps)));
+  return cudaGetLastError();
+}
+
+// ============================================================================================ tail conv
+// decoder[6]: Conv1d(C -> 1, k=7) on the Snake'd activation, then clamp(-1, 1) (modeling :862, :883).
+// Block = 256 consecutive samples of one batch item; the (256+6) x C input slab sits in shared
+// memory with an odd word pitch so lane-per-sample reads are conflict free.
+static constexpr int TAIL_TILE = 256;
+template <typename T>
+__global__ void __launch_bounds__(TAIL_TILE)
+k_tail(const T* __restrict__ x, const float* __restrict__ w, float bias, float* __restrict__ out, long long obs, int L, int C, int skip) {
+  extern __shared__ __align__(16) uint8_t tail_smem[];
+  const int cw = C / 2;        // 32-bit words per row
+  const int pitch = cw | 1;    // odd
+  uint32_t* sx = reinterpret_cast<uint32_t*>(tail_smem);
+  float* sw = reinterpret_cast<float*>(sx + (size_t)(TAIL_TILE + 6) * pitch);
+  const int b = blockIdx.y;
+  const int l0 = blockIdx.x * TAIL_TILE;
+  const uint32_t* xb = reinterpret_cast<const uint32_t*>(x + (long long)b * L * C);
+  for (int i = threadIdx.x; i < (TAIL_TILE + 6) * cw; i += blockDim.x) {
+    const int r = i / cw, c = i % cw;
+    const int lt = l0 - 6 + r;
+    sx[r * pitch + c] = (lt >= 0 && lt < L) ? xb[(long long)lt * cw + c] : 0u;
+  }
+  for (int i = threadIdx.x; i < 7 * C; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int l = l0 + threadIdx.x;
+  if (l >= L || l < skip) return;
+  float acc = bias;
+  for (int j = 0; j < 7; ++j) {
+    const uint32_t* xr = sx + (threadIdx.x + j) * pitch;
+    const float* wr = sw + j * C;
+    for (int c = 0; c < cw; ++c) {
+      const float2 v = Elem<T>::unpack2(xr[c]);
+      acc = fmaf(v.x, wr[2 * c], acc);
+      acc = fmaf(v.y, wr[2 * c + 1], acc);
+    }
+  }
+  out[(long long)b * obs + (l - skip)] = fminf(1.0f, fmaxf(-1.0f, acc));
+}
+cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* out, long long obs, int B, int L, int C, int skip, bool bf16,
+                            cudaStream_t s) {
+  if (B <= 0 || L <= 0) return cudaSuccess;
+  const int pitch = (C / 2) | 1;
+  const size_t smem = (size_t)(TAIL_TILE + 6) * pitch * 4 + (size_t)7 * C * 4;
+  dim3 grid((L + TAIL_TILE - 1) / TAIL_TILE, B);
+  Q3_DISPATCH(bf16, (k_tail<T><<<grid, TAIL_TILE, smem, s>>>((const T*)x, w, bias, out, obs, L, C, skip)));
+  return cudaGetLastError();
+}
+
+// ============================================================================================ probes
+template <typename T>
+__global__ void k_to_cf(const void* __restrict__ x, bool is_f32, float* __restrict__ out, int L, int C) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int l0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int l = l0 + r, c = c0 + threadIdx.x;
+    float v = 0.f;
+    if (l < L && c < C) {
+      const long long idx = ((long long)b * L + l) * C + c;
+      v = is_f32 ? reinterpret_cast<const float*>(x)[idx] : Elem<T>::to_f(reinterpret_cast<const T*>(x)[idx]);
+    }
+    tile[r][threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int c = c0 + r, l = l0 + threadIdx.x;
+    if (l < L && c < C) out[((long long)b * C + c) * L + l] = tile[threadIdx.x][r];
+  }
+}
+cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s) {
+  if (B <= 0 || L <= 0) return cudaSuccess;
+  dim3 grid((L + 31) / 32, (C + 31) / 32, B), block(32, 8);
+  Q3_DISPATCH(bf16, (k_to_cf<T><<<grid, block, 0, s>>>(x, is_f32, out, L, C)));
+  return cudaGetLastError();
+}
+
+}  // namespace q3

@@ -1,0 +1,260 @@
+"""Host-side mirror of the reference's Tokenizer-12Hz decoder classes over the CUDA C-ABI.
+
+Same class names, argument meaning and error behaviour as
+qwen_tts/core/tokenizer_12hz/modeling_qwen3_tts_tokenizer_v2.py ("modeling" below):
+  Qwen3TTSTokenizerV2Decoder.forward / chunked_decode   (modeling :868, :885)
+  Qwen3TTSTokenizerV2Model.decode + getters             (modeling :945-958, :992-1022)
+PyTorch is used for device memory and streams only; all arithmetic runs in libq3tts_decode.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import glob
+import json
+import os
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Union
+
+import torch
+
+from . import _capi
+from .configuration import Qwen3TTSTokenizerV2Config, Qwen3TTSTokenizerV2DecoderConfig
+
+
+@dataclass
+class Qwen3TTSTokenizerV2DecoderOutput:
+    """audio_values: List[FloatTensor (segment_length_i,)] — reference modeling :63-72."""
+    audio_values: List[torch.Tensor] = None
+
+    def __getitem__(self, i):
+        return (self.audio_values,)[i]
+
+    def to_tuple(self):
+        return (self.audio_values,)
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
+class _Quantizer:
+    """`decoder.quantizer.decode(codes)` — SplitResidualVectorQuantizer.decode (modeling :814-820)."""
+
+    def __init__(self, dec: "Qwen3TTSTokenizerV2Decoder"):
+        self._dec = dec
+
+    def decode(self, codes: torch.Tensor) -> torch.Tensor:
+        d = self._dec
+        codes = d._check_codes(codes)
+        B, _, T = codes.shape
+        out = torch.empty((B, d.config.codebook_dim, T), dtype=torch.float32, device=d.device)
+        rc = d._lib.q3tts_rvq_decode(d._h, codes.data_ptr(), B, T, out.data_ptr(), _stream_ptr(d.device))
+        _capi.check(d._h, rc, "rvq_decode")
+        return out
+
+
+class Qwen3TTSTokenizerV2Decoder:
+    """Drop-in for the reference decoder module (modeling :823-895), inference only."""
+
+    def __init__(self, config: Qwen3TTSTokenizerV2DecoderConfig, device: Union[str, torch.device] = "cuda:0",
+                 compute_mode: str = "fp16"):
+        self.config = config
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("Qwen3TTSTokenizerV2Decoder (B200-native) needs a CUDA device; there is no CPU fallback")
+        if not torch.cuda.is_available():
+            raise RuntimeError("CUDA is not available; the B200-native decoder has no CPU fallback")
+        self.total_upsample = config.total_upsample
+        self.compute_mode = {"fp16": _capi.MODE_FP16, "bf16": _capi.MODE_BF16}[compute_mode]
+        self._lib = _capi.load_library()
+        self._h = C.c_void_p()
+        dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", dev_index)
+        cs = _capi.make_config_struct(config)
+        rc = self._lib.q3tts_create(C.byref(cs), dev_index, C.byref(self._h))
+        if rc != _capi.OK:
+            raise RuntimeError(f"q3tts_create failed ({rc}): needs an sm_100 (B200) device and a valid config")
+        self.quantizer = _Quantizer(self)
+        self._ready = False
+
+    # ------------------------------------------------------------------ weights
+    def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True):
+        """Consumes reference `Qwen3TTSTokenizerV2Decoder.state_dict()` keys."""
+        any_dev = False
+        for key, t in state_dict.items():
+            if key.endswith("inv_freq") or (key.startswith("quantizer.") and ".input_proj." in key):
+                continue  # non-persistent rope buffer; RVQ input_proj is unused on decode (modeling :757-759)
+            t = t.detach()
+            if t.dtype != torch.float32:
+                t = t.to(torch.float32)
+            t = t.contiguous()
+            on_dev = 1 if t.is_cuda else 0
+            any_dev = any_dev or t.is_cuda
+            if t.is_cuda:
+                if t.device != self.device:
+                    t = t.to(self.device)
+                torch.cuda.current_stream(self.device).synchronize()
+            shape = (C.c_int64 * t.dim())(*t.shape)
+            rc = self._lib.q3tts_load_tensor(self._h, key.encode(), t.data_ptr(), t.dim(), shape, on_dev)
+            _capi.check(self._h, rc, f"load_tensor({key})")
+        if any_dev:
+            torch.cuda.synchronize(self.device)
+        rc = self._lib.q3tts_finalize_weights(self._h, self.compute_mode)
+        _capi.check(self._h, rc, "finalize_weights")
+        self._ready = True
+        return self
+
+    def reserve(self, max_frames_per_launch: int):
+        _capi.check(self._h, self._lib.q3tts_reserve(self._h, int(max_frames_per_launch)), "reserve")
+
+    def set_engine(self, engine: str):
+        _capi.check(self._h, self._lib.q3tts_set_engine(self._h, {"tc": _capi.ENGINE_TC, "simt": _capi.ENGINE_SIMT}[engine]), "set_engine")
+
+    def launch_count(self) -> int:
+        return int(self._lib.q3tts_launch_count(self._h))
+
+    # ------------------------------------------------------------------ forward paths
+    def _check_codes(self, codes: torch.Tensor) -> torch.Tensor:
+        if codes.dim() != 3 or codes.shape[1] != self.config.num_quantizers:
+            got = codes.shape[1] if codes.dim() >= 2 else "?"
+            raise ValueError(f"Expected {self.config.num_quantizers} layer of codes, got {got}")  # modeling :869-870
+        if not self._ready:
+            raise RuntimeError("decoder weights are not loaded")
+        return codes.to(device=self.device, dtype=torch.int64).contiguous()
+
+    def forward(self, codes: torch.Tensor) -> torch.Tensor:
+        """codes [B, Q, T] int64 -> wav [B, 1, T*1920-555] fp32, clamped (modeling :868-883)."""
+        codes = self._check_codes(codes)
+        B, _, T = codes.shape
+        n = int(self._lib.q3tts_forward_num_samples(self._h, T))
+        wav = torch.empty((B, 1, n), dtype=torch.float32, device=self.device)
+        rc = self._lib.q3tts_forward(self._h, codes.data_ptr(), B, T, wav.data_ptr(), _stream_ptr(self.device))
+        _capi.check(self._h, rc, "forward")
+        return wav
+
+    __call__ = forward
+
+    def chunked_decode(self, codes: torch.Tensor, chunk_size: int = 300, left_context_size: int = 25) -> torch.Tensor:
+        """modeling :885-895."""
+        codes = self._check_codes(codes)
+        B, _, T = codes.shape
+        n = int(self._lib.q3tts_chunked_num_samples(self._h, T, chunk_size, left_context_size))
+        wav = torch.empty((B, 1, n), dtype=torch.float32, device=self.device)
+        rc = self._lib.q3tts_chunked_decode(self._h, codes.data_ptr(), B, T, int(chunk_size), int(left_context_size), wav.data_ptr(),
+                                            _stream_ptr(self.device))
+        _capi.check(self._h, rc, "chunked_decode")
+        return wav
+
+    def probe(self, codes: torch.Tensor, stage: str) -> torch.Tensor:
+        """Parity probe: activation after `stage` as fp32 [B, C, L] (oracle tap names)."""
+        codes = self._check_codes(codes)
+        B, _, T = codes.shape
+        cap = B * T * self.total_upsample * 96 + 1024
+        cap = max(cap, B * T * 4 * 4096)
+        buf = torch.empty(cap, dtype=torch.float32, device=self.device)
+        c, l = C.c_int(0), C.c_int(0)
+        rc = self._lib.q3tts_forward_probe(self._h, codes.data_ptr(), B, T, stage.encode(), buf.data_ptr(), cap, C.byref(c), C.byref(l),
+                                           _stream_ptr(self.device))
+        _capi.check(self._h, rc, f"forward_probe({stage})")
+        return buf[: B * c.value * l.value].view(B, c.value, l.value)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) and self._h.value:
+                self._lib.q3tts_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+
+class Qwen3TTSTokenizerV2Model:
+    """Drop-in for the reference model shell (modeling :927-1022): decode() + the five getters.
+
+    encode() (wav -> codes, HF MimiModel) is outside the hot path this package accelerates."""
+
+    def __init__(self, config: Qwen3TTSTokenizerV2Config, device: Union[str, torch.device] = "cuda:0", compute_mode: str = "fp16"):
+        self.config = config
+        self.encoder_valid_num_quantizers = config.encoder_valid_num_quantizers
+        self.input_sample_rate = config.input_sample_rate
+        self.output_sample_rate = config.output_sample_rate
+        self.decode_upsample_rate = config.decode_upsample_rate
+        self.encode_downsample_rate = config.encode_downsample_rate
+        self.decoder = Qwen3TTSTokenizerV2Decoder(config.decoder_config, device=device, compute_mode=compute_mode)
+        self.device = self.decoder.device
+        self.dtype = torch.float32
+
+    # ---- getters (modeling :945-958)
+    def get_model_type(self):
+        return self.config.model_type
+
+    def get_input_sample_rate(self):
+        return self.input_sample_rate
+
+    def get_output_sample_rate(self):
+        return self.output_sample_rate
+
+    def get_encode_downsample_rate(self):
+        return self.encode_downsample_rate
+
+    def get_decode_upsample_rate(self):
+        return self.decode_upsample_rate
+
+    def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True):
+        """Accepts the reference model's state_dict: `decoder.*` keys are consumed, `encoder.*` ignored."""
+        dec = {k[len("decoder."):]: v for k, v in state_dict.items() if k.startswith("decoder.")}
+        if not dec:  # already decoder-level keys
+            dec = {k: v for k, v in state_dict.items() if not k.startswith("encoder.")}
+        self.decoder.load_state_dict(dec, strict=strict)
+        return self
+
+    @classmethod
+    def from_pretrained(cls, path: str, device_map: Union[str, torch.device, None] = None, dtype=None, **kwargs):
+        """Reads `<path>/config.json` and `*.safetensors` like AutoModel.from_pretrained would (wrapper :88).
+        dtype=torch.bfloat16 selects bf16 tensor-core operands; anything else the fp16 parity mode."""
+        from safetensors import safe_open
+
+        config = Qwen3TTSTokenizerV2Config.from_pretrained(path)
+        device = device_map if device_map not in (None, "auto") else "cuda:0"
+        mode = "bf16" if dtype is torch.bfloat16 else "fp16"
+        model = cls(config, device=device, compute_mode=mode)
+        sd: Dict[str, torch.Tensor] = {}
+        files = sorted(glob.glob(os.path.join(path, "*.safetensors")))
+        if not files:
+            raise FileNotFoundError(f"no .safetensors under {path}")
+        for f in files:
+            with safe_open(f, framework="pt", device="cpu") as sf:
+                for k in sf.keys():
+                    if k.startswith("decoder."):
+                        sd[k] = sf.get_tensor(k)
+        model.load_state_dict(sd)
+        return model
+
+    def encode(self, *args, **kwargs):
+        raise NotImplementedError("encode (wav -> codes) is outside the decode hot path; use the reference encoder")
+
+    def decode(self, audio_codes: torch.Tensor, return_dict: Optional[bool] = None):
+        """audio_codes [B, T, Q] -> Qwen3TTSTokenizerV2DecoderOutput(audio_values=List[Tensor]) (modeling :992-1022)."""
+        return_dict = return_dict if return_dict is not None else self.config.return_dict
+        audio_values = self.decoder.chunked_decode(audio_codes.transpose(1, 2)).squeeze(1)
+        audio_lengths = (audio_codes[..., 0] > 0).sum(1) * self.decode_upsample_rate
+        audio_values = [a[:l] for a, l in zip(audio_values, audio_lengths.tolist())]
+        if not return_dict:
+            return (audio_values,)
+        return Qwen3TTSTokenizerV2DecoderOutput(audio_values)
+
+    def decode_host(self, audio_codes_cpu: torch.Tensor):
+        """End-to-end path used by Qwen3TTSTokenizer.decode: HOST codes [B,T,Q] -> list of HOST fp32
+        waveforms, with the H2D / D2H copies and the length rule inside one C call."""
+        import numpy as np
+        codes = audio_codes_cpu.to(torch.int64).contiguous()
+        if codes.dim() != 3 or codes.shape[2] != self.config.decoder_config.num_quantizers:
+            raise ValueError(f"Expected {self.config.decoder_config.num_quantizers} layer of codes, got {codes.shape[-1]}")
+        B, T, _ = codes.shape
+        d = self.decoder
+        total = int(d._lib.q3tts_chunked_num_samples(d._h, T, 300, 25))
+        wav = torch.empty((B, max(total, 1)), dtype=torch.float32, pin_memory=True)
+        lengths = (C.c_int64 * B)()
+        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), wav.shape[1], lengths, _stream_ptr(d.device))
+        _capi.check(d._h, rc, "decode_host")
+        arr = wav.numpy()
+        return [np.array(arr[b, : lengths[b]], dtype=np.float32, copy=True) for b in range(B)]

@@ -1,0 +1,171 @@
+"""Seeded synthetic weights and codes for the Tokenizer-12Hz decoder.
+
+No checkpoint is mounted on the build or GPU boxes, so throughput and parity are measured on
+random-init weights of the named architecture.  A freshly constructed reference decoder outputs
+exact silence (embedding_sum = 0, Snake alpha = beta = 0, LayerScale 0.01, gamma 1e-6;
+reference modeling :673, :596-597, :224), so every parameter is overwritten here with a seeded
+draw whose gains keep the pre-clamp waveform inside (-1, 1).
+
+Keys are the reference `Qwen3TTSTokenizerV2Decoder.state_dict()` keys (no `decoder.` prefix);
+shapes follow reference modeling :823-866.  Each tensor is drawn from its own generator seeded
+by (seed, crc32(key)) so the result does not depend on iteration order.
+"""
+from __future__ import annotations
+
+import math
+import zlib
+from collections import OrderedDict
+from typing import Dict, List, Tuple
+
+import torch
+
+from .configuration import Qwen3TTSTokenizerV2DecoderConfig
+
+
+def decoder_param_shapes(cfg: Qwen3TTSTokenizerV2DecoderConfig) -> "OrderedDict[str, Tuple[int, ...]]":
+    """All persistent tensors of the reference decoder, in module order."""
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    H, Lat, I = cfg.hidden_size, cfg.latent_dim, cfg.intermediate_size
+    nh, nkv, hd = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim
+    D, dq = cfg.codebook_dim, cfg.codebook_dim // 2
+    # pre_transformer (modeling :481-493)
+    for l in range(cfg.num_hidden_layers):
+        p = f"pre_transformer.layers.{l}."
+        s[p + "self_attn.q_proj.weight"] = (nh * hd, H)
+        s[p + "self_attn.k_proj.weight"] = (nkv * hd, H)
+        s[p + "self_attn.v_proj.weight"] = (nkv * hd, H)
+        s[p + "self_attn.o_proj.weight"] = (H, nh * hd)
+        s[p + "mlp.gate_proj.weight"] = (I, H)
+        s[p + "mlp.up_proj.weight"] = (I, H)
+        s[p + "mlp.down_proj.weight"] = (H, I)
+        s[p + "input_layernorm.weight"] = (H,)
+        s[p + "post_attention_layernorm.weight"] = (H,)
+        s[p + "self_attn_layer_scale.scale"] = (H,)
+        s[p + "mlp_layer_scale.scale"] = (H,)
+    s["pre_transformer.norm.weight"] = (H,)
+    s["pre_transformer.input_proj.weight"] = (H, Lat)
+    s["pre_transformer.input_proj.bias"] = (H,)
+    s["pre_transformer.output_proj.weight"] = (Lat, H)
+    s["pre_transformer.output_proj.bias"] = (Lat,)
+    # quantizer (modeling :829-836, :757-770)
+    for name, nq in (("rvq_first", 1), ("rvq_rest", cfg.num_quantizers - 1)):
+        s[f"quantizer.{name}.input_proj.weight"] = (dq, D, 1)
+        s[f"quantizer.{name}.output_proj.weight"] = (D, dq, 1)
+        for k in range(nq):
+            s[f"quantizer.{name}.vq.layers.{k}._codebook.cluster_usage"] = (cfg.codebook_size,)
+            s[f"quantizer.{name}.vq.layers.{k}._codebook.embedding_sum"] = (cfg.codebook_size, dq)
+    # pre_conv (modeling :838-842)
+    s["pre_conv.conv.weight"] = (Lat, D, 3)
+    s["pre_conv.conv.bias"] = (Lat,)
+    # upsample (modeling :844-854, :210-224)
+    for i, f in enumerate(cfg.upsampling_ratios):
+        p = f"upsample.{i}."
+        s[p + "0.conv.weight"] = (Lat, Lat, f)
+        s[p + "0.conv.bias"] = (Lat,)
+        s[p + "1.dwconv.conv.weight"] = (Lat, 1, 7)
+        s[p + "1.dwconv.conv.bias"] = (Lat,)
+        s[p + "1.norm.weight"] = (Lat,)
+        s[p + "1.norm.bias"] = (Lat,)
+        s[p + "1.pwconv1.weight"] = (4 * Lat, Lat)
+        s[p + "1.pwconv1.bias"] = (4 * Lat,)
+        s[p + "1.pwconv2.weight"] = (Lat, 4 * Lat)
+        s[p + "1.pwconv2.bias"] = (Lat,)
+        s[p + "1.gamma"] = (Lat,)
+    # decoder (modeling :856-864, :637-657, :618-634)
+    Dd = cfg.decoder_dim
+    s["decoder.0.conv.weight"] = (Dd, Lat, 7)
+    s["decoder.0.conv.bias"] = (Dd,)
+    for i, r in enumerate(cfg.upsample_rates):
+        cin, cout = Dd // 2 ** i, Dd // 2 ** (i + 1)
+        p = f"decoder.{i + 1}.block."
+        s[p + "0.alpha"] = (cin,)
+        s[p + "0.beta"] = (cin,)
+        s[p + "1.conv.weight"] = (cin, cout, 2 * r)
+        s[p + "1.conv.bias"] = (cout,)
+        for j in (2, 3, 4):
+            s[p + f"{j}.act1.alpha"] = (cout,)
+            s[p + f"{j}.act1.beta"] = (cout,)
+            s[p + f"{j}.conv1.conv.weight"] = (cout, cout, 7)
+            s[p + f"{j}.conv1.conv.bias"] = (cout,)
+            s[p + f"{j}.act2.alpha"] = (cout,)
+            s[p + f"{j}.act2.beta"] = (cout,)
+            s[p + f"{j}.conv2.conv.weight"] = (cout, cout, 1)
+            s[p + f"{j}.conv2.conv.bias"] = (cout,)
+    n = len(cfg.upsample_rates)
+    cl = Dd // 2 ** n
+    s[f"decoder.{n + 1}.alpha"] = (cl,)
+    s[f"decoder.{n + 1}.beta"] = (cl,)
+    s[f"decoder.{n + 2}.conv.weight"] = (1, cl, 7)
+    s[f"decoder.{n + 2}.conv.bias"] = (1,)
+    return s
+
+
+def _gen(seed: int, key: str) -> torch.Generator:
+    g = torch.Generator(device="cpu")
+    g.manual_seed((int(seed) * 1000003 + zlib.crc32(key.encode())) % (2 ** 63 - 1))
+    return g
+
+
+def _fan_in(key: str, shape: Tuple[int, ...]) -> int:
+    if key.endswith("1.conv.weight") and ".block." in key:  # ConvTranspose1d [Cin, Cout, k]: 2 taps hit each output
+        return shape[0] * 2
+    if key.startswith("upsample.") and key.endswith("0.conv.weight"):  # k = stride: 1 tap per output
+        return shape[0]
+    if len(shape) == 3:
+        return shape[1] * shape[2]
+    return shape[1]
+
+
+def make_decoder_state_dict(cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0) -> Dict[str, torch.Tensor]:
+    """Deterministic fp32 CPU state dict with reference key names."""
+    out: Dict[str, torch.Tensor] = OrderedDict()
+    for key, shape in decoder_param_shapes(cfg).items():
+        g = _gen(seed, key)
+        if key.endswith("embedding_sum"):
+            t = torch.randn(shape, generator=g)
+        elif key.endswith("cluster_usage"):
+            t = torch.rand(shape, generator=g) * 2.0 + 0.5
+        elif key.endswith(".alpha") or key.endswith(".beta"):
+            t = torch.randn(shape, generator=g) * 0.3
+        elif key.endswith("gamma") or key.endswith("layer_scale.scale"):
+            t = torch.rand(shape, generator=g) * 0.5 + 0.25
+        elif key.endswith("layernorm.weight") or key.endswith("norm.weight"):
+            t = 1.0 + 0.1 * torch.randn(shape, generator=g)
+        elif key.endswith("norm.bias") or key.endswith(".bias"):
+            t = 0.02 * torch.randn(shape, generator=g)
+        elif key.endswith(".weight"):
+            gain = _GAIN(key)
+            t = torch.randn(shape, generator=g) * (gain / math.sqrt(_fan_in(key, shape)))
+        else:  # pragma: no cover
+            raise KeyError(key)
+        out[key] = t.contiguous()
+    return out
+
+
+def _GAIN(key: str) -> float:
+    # Gains chosen so activations stay O(1) through the stack and the pre-clamp waveform stays
+    # inside (-1, 1) (a naive gain-1 fan-in init clamps ~90 % of samples).
+    if key.startswith("quantizer.") and "output_proj" in key:
+        return 0.35  # sum of up to 15 unit-variance codebook rows feeds this
+    if key.startswith("decoder.") and ".block." in key and "conv2.conv" in key:
+        return 0.35
+    if key.startswith("decoder.") and ".block." in key and "conv1.conv" in key:
+        return 0.5
+    if key.startswith("decoder.") and key.endswith("conv.weight") and ".block." not in key and key != "decoder.0.conv.weight":
+        return 0.07  # final 96 -> 1 projection
+    return 1.0
+
+
+def make_codes(batch: int, frames: int, cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0,
+               lengths: List[int] | None = None) -> torch.Tensor:
+    """[B, T, Q] int64.  Codebook 0 is drawn from [1, size) because the reference counts a 0 in
+    codebook 0 as padding (modeling :1014); padding frames (t >= lengths[b]) are all-zero like
+    `pad_sequence(padding_value=0)` in the wrapper (qwen3_tts_tokenizer.py:329)."""
+    g = _gen(seed, f"codes/{batch}/{frames}")
+    q = cfg.num_quantizers
+    codes = torch.randint(0, cfg.codebook_size, (batch, frames, q), generator=g, dtype=torch.int64)
+    codes[..., 0] = torch.randint(1, cfg.codebook_size, (batch, frames), generator=g, dtype=torch.int64)
+    if lengths is not None:
+        for b, n in enumerate(lengths):
+            codes[b, int(n):] = 0
+    return codes

@@ -1,0 +1,101 @@
+"""`Qwen3TTSTokenizer` — drop-in for qwen_tts/inference/qwen3_tts_tokenizer.py ("wrapper"), decode side.
+
+Same constructor-less class, `from_pretrained`, `decode(encoded) -> (List[np.float32 1-D], sr)` accepting
+the reference's payload forms (wrapper :298-329) and the five getters (wrapper :367-411).  `encode`
+and audio I/O (librosa / soundfile) are outside the accelerated hot path and are not provided here.
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import numpy as np
+import torch
+from torch.nn.utils.rnn import pad_sequence
+
+from .configuration import Qwen3TTSTokenizerV2Config
+from .modeling import Qwen3TTSTokenizerV2Model
+
+
+class Qwen3TTSTokenizer:
+    def __init__(self):
+        self.model = None
+        self.feature_extractor = None
+        self.config = None
+        self.device = None
+
+    @classmethod
+    def from_pretrained(cls, pretrained_model_name_or_path: str, **kwargs) -> "Qwen3TTSTokenizer":
+        """kwargs as the reference forwards to AutoModel.from_pretrained: device_map, dtype (wrapper :64-97)."""
+        inst = cls()
+        inst.model = Qwen3TTSTokenizerV2Model.from_pretrained(
+            pretrained_model_name_or_path, device_map=kwargs.get("device_map"), dtype=kwargs.get("dtype", kwargs.get("torch_dtype")))
+        inst.config = inst.model.config
+        inst.device = inst.model.device
+        return inst
+
+    @classmethod
+    def from_model(cls, model: Qwen3TTSTokenizerV2Model) -> "Qwen3TTSTokenizer":
+        """Wrap an already-built model (synthetic weights, tests, benches)."""
+        inst = cls()
+        inst.model = model
+        inst.config = model.config
+        inst.device = model.device
+        return inst
+
+    def encode(self, *args, **kwargs):
+        raise NotImplementedError("encode (wav -> codes) is outside the decode hot path this package accelerates")
+
+    def decode(self, encoded) -> Tuple[List[np.ndarray], int]:
+        """Decode back to waveform (wrapper :259-365)."""
+        model_type = self.model.get_model_type()
+
+        def _to_tensor(x, dtype=None):
+            if isinstance(x, torch.Tensor):
+                return x
+            t = torch.from_numpy(np.asarray(x))
+            return t.to(dtype) if dtype is not None else t
+
+        if hasattr(encoded, "audio_codes"):
+            audio_codes_list = encoded.audio_codes
+        elif isinstance(encoded, dict):
+            audio_codes_list = encoded["audio_codes"]
+        elif isinstance(encoded, list):
+            audio_codes_list = [e["audio_codes"] for e in encoded]
+        else:
+            raise TypeError("`encoded` must be an encode output, a dict, or a list of dicts.")
+
+        if isinstance(audio_codes_list, torch.Tensor):
+            t = audio_codes_list
+            if t.dim() == 2:  # single sample (T, Q) -> (1, T, Q)
+                t = t.unsqueeze(0)
+            audio_codes_padded = t
+        else:
+            audio_codes_list = [_to_tensor(c, dtype=torch.long) for c in audio_codes_list]
+            audio_codes_padded = pad_sequence(audio_codes_list, batch_first=True, padding_value=0)
+
+        if model_type != "qwen3_tts_tokenizer_12hz":
+            raise ValueError(f"Unknown model type: {model_type}")
+
+        with torch.inference_mode():
+            if audio_codes_padded.is_cuda:
+                dec = self.model.decode(audio_codes_padded, return_dict=True)
+                wavs = [w.to(torch.float32).detach().cpu().numpy() for w in dec.audio_values]
+            else:
+                # host payload: one C call does H2D, chunked decode, the length rule and D2H
+                wavs = self.model.decode_host(audio_codes_padded)
+        return wavs, int(self.model.get_output_sample_rate())
+
+    def get_model_type(self) -> str:
+        return self.model.get_model_type()
+
+    def get_input_sample_rate(self) -> int:
+        return int(self.model.get_input_sample_rate())
+
+    def get_output_sample_rate(self) -> int:
+        return int(self.model.get_output_sample_rate())
+
+    def get_encode_downsample_rate(self) -> int:
+        return int(self.model.get_encode_downsample_rate())
+
+    def get_decode_upsample_rate(self) -> int:
+        return int(self.model.get_decode_upsample_rate())
