@@ -1,0 +1,263 @@
+#!/usr/bin/env python
+"""Benchmark of the Tokenizer-12Hz decode path (codes -> 24 kHz waveform).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+A "step" is one bulk decode of BASELINE.json config 2: 64 utterances x 10 s (125 code frames, 16
+codebooks) of seeded synthetic codes through Qwen3TTSTokenizerV2Model.decode semantics
+(chunked_decode(300, 25) + the length rule) on seeded random-init weights of the named
+architecture (no checkpoint is mounted).  With N > 1 every rank decodes its own 64 utterances
+(weak scaling, no data-path collective; NCCL is used only for the timing barrier / max).
+
+  value  : audio-seconds decoded per second, codes already resident in HBM (CUDA events)
+  e2e    : same metric through the public API Qwen3TTSTokenizer.decode with HOST codes in pinned
+           memory: pad, H2D, decode, length rule, D2H into host float32 arrays, every step
+  roofline / cpu_baseline / clocks / gpu_launches : see DESIGN.md "Measurement"
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+B_UTT, T_FRAMES = 64, 125
+FRAME_SEC = 0.08
+GFLOP_PER_FRAME = 5.1226  # 2 x 2561.30 MMAC per emitted code frame
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tflops_burst": d["bf16_tflops"], "tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(steps: int, warmup: int, utterances: int = 1):
+    """The reference's algorithm on the host cores: the oracle port (oracle/decoder_oracle.py, pinned to the
+    unmodified reference by tests/golden) decoding `utterances` x 10 s of the same workload per step."""
+    import torch
+
+    from oracle import decoder_oracle as O
+    from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
+    from qwen3_tts_b200.synthetic import make_codes, make_decoder_state_dict
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = Qwen3TTSTokenizerV2DecoderConfig()
+    sd = make_decoder_state_dict(cfg, seed=0)
+    codes = make_codes(B_UTT, T_FRAMES, cfg, seed=1)[:utterances]
+    times = []
+    with torch.inference_mode():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            out = O.model_decode(sd, cfg, codes)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    assert out[0].shape[0] == 239445
+    sec = statistics.median(times)
+    return {"value": utterances * T_FRAMES * FRAME_SEC / sec, "sec_per_step": sec, "cores": torch.get_num_threads(),
+            "sample": f"{utterances} of the {B_UTT} utterances x 10 s per step, median of {steps} after {warmup} warm-up"}
+
+
+def run_reference(args, rank: int):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores (oracle port:
+    the reference is a Python package that cannot travel to the GPU box, tests/golden pins the port to it)."""
+    if rank != 0:
+        return
+    r = cpu_reference_run(steps=args.steps, warmup=min(args.warmup, 1), utterances=1)
+    line = {"impl": "reference", "metric": "audio-sec decoded per sec (codes->24kHz)", "value": r["value"], "unit": "audio-s/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["sec_per_step"] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": "Tokenizer-12Hz bulk decode, batch 64 x 10 s synthetic codes (config 2); bounded sample: 1 utterance per step"},
+            "cpu_baseline": {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16"], help="tensor-core operand type (fp32 accumulate)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+
+    from qwen3_tts_b200 import Qwen3TTSTokenizer, synthetic_model
+    from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
+    from qwen3_tts_b200.synthetic import make_codes, make_decoder_state_dict
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the decode path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    cfg = Qwen3TTSTokenizerV2DecoderConfig()
+    sd = make_decoder_state_dict(cfg, seed=0)
+    model = synthetic_model(state_dict=sd, device=dev, compute_mode=args.mode)
+    del sd
+    dec = model.decoder
+    dec.reserve(B_UTT * T_FRAMES)
+    tok = Qwen3TTSTokenizer.from_model(model)
+    codes_host = make_codes(B_UTT, T_FRAMES, cfg, seed=1 + rank)            # [B,T,Q] int64
+    codes_dev = codes_host.to(dev).transpose(1, 2).contiguous()              # [B,Q,T] resident in HBM
+    host_items = [{"audio_codes": codes_host[b].clone().pin_memory()} for b in range(B_UTT)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)            # > 126 MB L2
+
+    def step_device():
+        return dec.chunked_decode(codes_dev)
+
+    # ---------------- device-resident throughput
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    l0 = dec.launch_count()
+    for a, b in ev:
+        flush.zero_()                                                       # L2 flush between timed iterations (untimed)
+        a.record()
+        wav = step_device()
+        b.record()
+    barrier()
+    launches = dec.launch_count() - l0
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    # ---------------- end to end through the public API (host codes -> host float32 waveforms)
+    for _ in range(2):
+        tok.decode(host_items)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        wavs, sr = tok.decode(host_items)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    assert sr == 24000 and len(wavs) == B_UTT and wavs[0].shape == (239445,) and tuple(wav.shape) == (B_UTT, 1, 239445)
+    if world > 1:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)                             # max over ranks
+        ms, e2e_s = t[0].item(), t[1].item()
+    audio_s = world * B_UTT * T_FRAMES * FRAME_SEC * args.steps
+    value = audio_s / (ms / 1e3)
+    e2e_value = audio_s / e2e_s
+    # ---------------- per-kernel profile of one step (separate, untimed pass)
+    dec.set_profile(True)
+    step_device()
+    prof = dec.get_profile()
+    dec.set_profile(False)
+    gemm_ms = sum(p[1] for p in prof if p[0] == 1)
+    gemm_fl = sum(p[2] for p in prof if p[0] == 1)
+    tot_ms = sum(p[1] for p in prof)
+    names = {0: "rvq_gather", 1: "tcgen05_conv_gemm", 2: "rmsnorm", 3: "attention", 4: "dwconv_ln", 5: "tail_conv"}
+    by_kernel = {}
+    for ty, t_ms, _fl, by in prof:
+        k = by_kernel.setdefault(names[ty], {"ms": 0.0, "launches": 0, "min_bytes": 0.0})
+        k["ms"] += t_ms; k["launches"] += 1; k["min_bytes"] += by
+    peaks = load_peaks()
+    gemm_launches = by_kernel["tcgen05_conv_gemm"]["launches"]
+    roof = {"bound": "tensor", "kernel": "conv_gemm_tc_kernel (tcgen05 implicit-GEMM conv/linear, all layers)",
+            "achieved": gemm_fl / gemm_launches / (gemm_ms / gemm_launches * 1e-3) / 1e12,
+            "peak": peaks["tflops_sustained"], "unit": "TFLOP/s", "traffic": None,
+            "peak_source": f"{peaks['source']} sustained bf16 cuBLAS (kernel timed inside a long step)",
+            "share_of_step": gemm_ms / tot_ms, "flops_per_launch_avg": gemm_fl / gemm_launches, "ms_per_launch_avg": gemm_ms / gemm_launches}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    path_frac = (B_UTT * T_FRAMES * GFLOP_PER_FRAME * 1e9) / (ms / args.steps * 1e-3) / 1e12 / peaks["tflops_sustained"]
+    for k in by_kernel.values():
+        k["ms"] = round(k["ms"], 4)
+        k["min_hbm_gbs"] = round(k.pop("min_bytes") / max(k["ms"], 1e-9) / 1e6, 1)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {"metric": "audio-sec decoded per sec (codes->24kHz)", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": f"{args.mode} operands, fp32 accumulate", "data": "synthetic",
+            "config": {"workload": "Tokenizer-12Hz non-streaming bulk decode, batch 64 x 10 s synthetic 16-codebook codes per GPU (BASELINE config 2)",
+                       "frames_per_step_per_gpu": B_UTT * T_FRAMES, "weights": "seeded random-init, reference architecture (195.08 M params)",
+                       "l2": "flushed between timed steps (256 MiB write, untimed); activations per step >> 126 MB L2",
+                       "parallelism": f"utterance-sharded x{world}, no collective"},
+            "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": world * B_UTT * T_FRAMES * 16 * 8,
+                    "d2h_bytes_per_step": world * B_UTT * 239445 * 4, "ms_per_step": e2e_s / args.steps * 1e3,
+                    "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [125,16]}) -> host float32 arrays"},
+            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "path_frac_of_tensor_roofline": path_frac, "kernels": by_kernel}
+    if not args.no_cpu_baseline and world == 1:
+        r = cpu_reference_run(steps=3, warmup=1, utterances=1)
+        line["cpu_baseline"] = {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

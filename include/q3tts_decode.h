@@ -112,6 +112,14 @@ int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, con
 /* Bench support: number of kernel launches issued by this handle since creation. */
 int64_t q3tts_launch_count(q3tts_handle* h);
 
+/* Per-op profile of the LAST engine launch (one forward on one sub-batch) when profiling is on:
+ * a CUDA-event pair is recorded around every op on the launch stream.  q3tts_get_profile
+ * synchronises the device and returns the number of ops; types[i] is 0 RVQ gather, 1 tcgen05 GEMM,
+ * 2 RMSNorm, 3 attention, 4 dwconv+LayerNorm, 5 tail conv; flops[i] = algorithmic 2*MACs (GEMM ops),
+ * bytes[i] = minimum HBM bytes (operands and outputs once). */
+int q3tts_set_profile(q3tts_handle* h, int on);
+int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes);
+
 /* Standalone GEMM self-test of the tcgen05 implicit-GEMM kernel against the SIMT cross-check
  * (device-side, no host math): returns max |tc - simt| over a [rows,n] problem via *max_abs_diff. */
 int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dilation, int bf16, float* max_abs_diff, float* max_abs_ref);

@@ -131,4 +131,24 @@ int64_t q3tts_chunked_num_samples(q3tts_handle* h, int T, int chunk, int left_ct
 
 int64_t q3tts_launch_count(q3tts_handle* h) { return h ? h->e.launches : 0; }
 
+int q3tts_set_profile(q3tts_handle* h, int on) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  h->e.profile = on != 0;
+  return Q3TTS_OK;
+}
+
+int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  DeviceGuard g(e.device);
+  if (cudaDeviceSynchronize() != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, "get_profile: sync failed");
+  const int n = (int)e.prof_type.size();
+  for (int i = 0; i < n && i < max_ops; ++i) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, e.prof_events[2 * i], e.prof_events[2 * i + 1]);
+    types[i] = e.prof_type[i]; ms[i] = t; flops[i] = e.prof_flops[i]; bytes[i] = e.prof_bytes[i];
+  }
+  return n;
+}
+
 }  // extern "C"

@@ -73,6 +73,11 @@ struct Engine {
   int total_up = 1920;
   int lookahead = 555;
   long long launches = 0;
+  bool profile = false;                 // record a CUDA event pair around every op
+  std::vector<cudaEvent_t> prof_events;  // 2 per op of the last profiled run
+  std::vector<int> prof_type;
+  std::vector<double> prof_flops;       // algorithmic FLOPs (2 * MACs) of GEMM ops, 0 otherwise
+  std::vector<double> prof_bytes;       // minimum HBM bytes of the op (operands + outputs once)
 
   std::map<std::string, RawTensor> raw;
   std::vector<void*> owned;  // packed allocations

@@ -230,8 +230,18 @@ int engine_get_plan(Engine* e, int B, int T, Plan** out) {
 int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
                int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s) {
   const q3tts_config& c = e->cfg;
+  size_t pi = 0;
+  if (e->profile) {
+    while (e->prof_events.size() < 2 * plan->ops.size()) {
+      cudaEvent_t ev;
+      cudaEventCreate(&ev);
+      e->prof_events.push_back(ev);
+    }
+    e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear();
+  }
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
+    if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
     switch (op.type) {
       case OP_RVQ:
         err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s);
@@ -247,6 +257,25 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
         break;
     }
     ++e->launches;
+    if (e->profile) {
+      cudaEventRecord(e->prof_events[2 * pi + 1], s);
+      double fl = 0.0, by = 0.0;
+      if (op.type == OP_GEMM) {
+        const GemmParams& p = op.g.p;
+        const double rows = (double)p.batches * p.rows_valid;
+        fl = 2.0 * rows * p.n_total * p.cin * p.ntaps;
+        by = 2.0 * ((double)p.batches * p.rows * p.cin + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
+        const double outw = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
+        if (p.out_raw) by += 2.0 * rows * outw;
+        if (p.out_snake) by += 2.0 * rows * outw;
+        if (p.out_f32) by += 4.0 * rows * outw;
+        if (p.res) by += (p.res_f32 ? 4.0 : 2.0) * rows * outw;
+      }
+      e->prof_type.push_back((int)op.type);
+      e->prof_flops.push_back(fl);
+      e->prof_bytes.push_back(by);
+      ++pi;
+    }
     if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(err));
     if (probe_stage && !op.tag.empty() && op.tag == probe_stage && op.type != OP_TAIL) {
       const long long n = (long long)plan->B * op.probe_C * op.probe_L;
@@ -280,6 +309,7 @@ int engine_forward_batched(Engine* e, const long long* codes, long long sb, long
 }
 
 void engine_free(Engine* e) {
+  for (cudaEvent_t ev : e->prof_events) cudaEventDestroy(ev);
   for (void* p : e->owned) cudaFree(p);
   for (auto& kv : e->raw) cudaFree(kv.second.d);
   if (e->ws) cudaFree(e->ws);

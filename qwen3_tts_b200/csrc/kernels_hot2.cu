@@ -124,6 +124,13 @@ cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* ou
   const int pitch = (C / 2) | 1;
   const size_t smem = (size_t)(TAIL_TILE + 6) * pitch * 4 + (size_t)7 * C * 4;
   dim3 grid((L + TAIL_TILE - 1) / TAIL_TILE, B);
+  static bool attr_done = false;
+  if (!attr_done) {  // the slab exceeds the 48 KB default for C = 96
+    cudaFuncSetAttribute(k_tail<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaFuncSetAttribute(k_tail<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    attr_done = true;
+  }
+  if (smem > 160 * 1024) return cudaErrorInvalidValue;
   Q3_DISPATCH(bf16, (k_tail<T><<<grid, TAIL_TILE, smem, s>>>((const T*)x, w, bias, out, obs, L, C, skip)));
   return cudaGetLastError();
 }

@@ -113,6 +113,19 @@ class Qwen3TTSTokenizerV2Decoder:
     def launch_count(self) -> int:
         return int(self._lib.q3tts_launch_count(self._h))
 
+    def set_profile(self, on: bool):
+        _capi.check(self._h, self._lib.q3tts_set_profile(self._h, 1 if on else 0), "set_profile")
+
+    def get_profile(self):
+        """[(type, ms, flops, bytes)] for every op of the last launch (profiling must be on)."""
+        n = 512
+        ty, ms = (C.c_int32 * n)(), (C.c_float * n)()
+        fl, by = (C.c_double * n)(), (C.c_double * n)()
+        k = self._lib.q3tts_get_profile(self._h, n, ty, ms, fl, by)
+        if k < 0:
+            _capi.check(self._h, k, "get_profile")
+        return [(int(ty[i]), float(ms[i]), float(fl[i]), float(by[i])) for i in range(min(k, n))]
+
     # ------------------------------------------------------------------ forward paths
     def _check_codes(self, codes: torch.Tensor) -> torch.Tensor:
         if codes.dim() != 3 or codes.shape[1] != self.config.num_quantizers:
@@ -256,5 +269,5 @@ class Qwen3TTSTokenizerV2Model:
         lengths = (C.c_int64 * B)()
         rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), wav.shape[1], lengths, _stream_ptr(d.device))
         _capi.check(d._h, rc, "decode_host")
-        arr = wav.numpy()
-        return [np.array(arr[b, : lengths[b]], dtype=np.float32, copy=True) for b in range(B)]
+        arr = wav.numpy()  # fresh pinned buffer per call: the returned rows are views that keep it alive, no extra host copy
+        return [arr[b, : lengths[b]] for b in range(B)]

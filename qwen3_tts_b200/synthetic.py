@@ -125,8 +125,14 @@ def make_decoder_state_dict(cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0
             t = torch.randn(shape, generator=g)
         elif key.endswith("cluster_usage"):
             t = torch.rand(shape, generator=g) * 2.0 + 0.5
-        elif key.endswith(".alpha") or key.endswith(".beta"):
+        elif key.endswith(".alpha"):
             t = torch.randn(shape, generator=g) * 0.3
+        elif key.endswith(".beta"):
+            # log-scale magnitude parameter; mean +1 keeps the periodic term's slope a*ib*sin(2ax) well
+            # below 1 so the random-init stack amplifies perturbations about as little as the survey's
+            # reference run did (fp32 vs fp64 ~ 113-121 dB) -- with mean 0 it is chaotic
+            # (fp32 vs fp64 only 99 dB) and no 16-bit operand scheme can be compared meaningfully.
+            t = 1.0 + torch.randn(shape, generator=g) * 0.3
         elif key.endswith("gamma") or key.endswith("layer_scale.scale"):
             t = torch.rand(shape, generator=g) * 0.5 + 0.25
         elif key.endswith("layernorm.weight") or key.endswith("norm.weight"):
@@ -152,7 +158,7 @@ def _GAIN(key: str) -> float:
     if key.startswith("decoder.") and ".block." in key and "conv1.conv" in key:
         return 0.5
     if key.startswith("decoder.") and key.endswith("conv.weight") and ".block." not in key and key != "decoder.0.conv.weight":
-        return 0.07  # final 96 -> 1 projection
+        return 0.09  # final 96 -> 1 projection
     return 1.0
 
 
