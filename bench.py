@@ -220,7 +220,7 @@ def main():
     tot_ms = sum(p[1] for p in prof)
     names = {0: "rvq_gather", 1: "tcgen05_conv_gemm", 2: "rmsnorm", 3: "attention", 4: "dwconv_ln", 5: "tail_conv"}
     by_kernel = {}
-    for ty, t_ms, _fl, by in prof:
+    for ty, t_ms, _fl, by, _dims in prof:
         k = by_kernel.setdefault(names[ty], {"ms": 0.0, "launches": 0, "min_bytes": 0.0})
         k["ms"] += t_ms; k["launches"] += 1; k["min_bytes"] += by
     peaks = load_peaks()

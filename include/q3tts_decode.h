@@ -116,9 +116,10 @@ int64_t q3tts_launch_count(q3tts_handle* h);
  * a CUDA-event pair is recorded around every op on the launch stream.  q3tts_get_profile
  * synchronises the device and returns the number of ops; types[i] is 0 RVQ gather, 1 tcgen05 GEMM,
  * 2 RMSNorm, 3 attention, 4 dwconv+LayerNorm, 5 tail conv; flops[i] = algorithmic 2*MACs (GEMM ops),
- * bytes[i] = minimum HBM bytes (operands and outputs once). */
+ * bytes[i] = minimum HBM bytes (operands and outputs once); dims (optional, 4 per op) = rows over all batch
+ * items, N, Cin, taps for GEMM ops. */
 int q3tts_set_profile(q3tts_handle* h, int on);
-int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes);
+int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes, int32_t* dims);
 
 /* Standalone GEMM self-test of the tcgen05 implicit-GEMM kernel against the SIMT cross-check
  * (device-side, no host math): returns max |tc - simt| over a [rows,n] problem via *max_abs_diff. */

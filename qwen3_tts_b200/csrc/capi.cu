@@ -137,7 +137,7 @@ int q3tts_set_profile(q3tts_handle* h, int on) {
   return Q3TTS_OK;
 }
 
-int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes) {
+int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes, int32_t* dims) {
   if (!h) return Q3TTS_BAD_CONFIG;
   Engine& e = h->e;
   DeviceGuard g(e.device);
@@ -147,6 +147,7 @@ int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, d
     float t = 0.f;
     cudaEventElapsedTime(&t, e.prof_events[2 * i], e.prof_events[2 * i + 1]);
     types[i] = e.prof_type[i]; ms[i] = t; flops[i] = e.prof_flops[i]; bytes[i] = e.prof_bytes[i];
+    if (dims) for (int d = 0; d < 4; ++d) dims[4 * i + d] = e.prof_dims[4 * i + d];
   }
   return n;
 }

@@ -77,6 +77,7 @@ struct Engine {
   std::vector<cudaEvent_t> prof_events;  // 2 per op of the last profiled run
   std::vector<int> prof_type;
   std::vector<double> prof_flops;       // algorithmic FLOPs (2 * MACs) of GEMM ops, 0 otherwise
+  std::vector<int> prof_dims;           // 4 per op: rows (all batch items), n_total, cin, ntaps
   std::vector<double> prof_bytes;       // minimum HBM bytes of the op (operands + outputs once)
 
   std::map<std::string, RawTensor> raw;

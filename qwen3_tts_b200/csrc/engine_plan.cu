@@ -237,7 +237,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       cudaEventCreate(&ev);
       e->prof_events.push_back(ev);
     }
-    e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear();
+    e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear(); e->prof_dims.clear();
   }
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
@@ -260,9 +260,11 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
     if (e->profile) {
       cudaEventRecord(e->prof_events[2 * pi + 1], s);
       double fl = 0.0, by = 0.0;
+      int dims[4] = {op.B * (op.L > 0 ? op.L : 1), op.C, 0, 0};
       if (op.type == OP_GEMM) {
         const GemmParams& p = op.g.p;
         const double rows = (double)p.batches * p.rows_valid;
+        dims[0] = p.batches * p.rows_valid; dims[1] = p.n_total; dims[2] = p.cin; dims[3] = p.ntaps;
         fl = 2.0 * rows * p.n_total * p.cin * p.ntaps;
         by = 2.0 * ((double)p.batches * p.rows * p.cin + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
         const double outw = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
@@ -274,6 +276,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       e->prof_type.push_back((int)op.type);
       e->prof_flops.push_back(fl);
       e->prof_bytes.push_back(by);
+      for (int d = 0; d < 4; ++d) e->prof_dims.push_back(dims[d]);
       ++pi;
     }
     if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(err));

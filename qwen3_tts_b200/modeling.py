@@ -117,14 +117,15 @@ class Qwen3TTSTokenizerV2Decoder:
         _capi.check(self._h, self._lib.q3tts_set_profile(self._h, 1 if on else 0), "set_profile")
 
     def get_profile(self):
-        """[(type, ms, flops, bytes)] for every op of the last launch (profiling must be on)."""
+        """[(type, ms, flops, bytes, (rows, n, cin, taps))] for every op of the last launch (profiling must be on)."""
         n = 512
         ty, ms = (C.c_int32 * n)(), (C.c_float * n)()
         fl, by = (C.c_double * n)(), (C.c_double * n)()
-        k = self._lib.q3tts_get_profile(self._h, n, ty, ms, fl, by)
+        dm = (C.c_int32 * (4 * n))()
+        k = self._lib.q3tts_get_profile(self._h, n, ty, ms, fl, by, dm)
         if k < 0:
             _capi.check(self._h, k, "get_profile")
-        return [(int(ty[i]), float(ms[i]), float(fl[i]), float(by[i])) for i in range(min(k, n))]
+        return [(int(ty[i]), float(ms[i]), float(fl[i]), float(by[i]), tuple(dm[4 * i: 4 * i + 4])) for i in range(min(k, n))]
 
     # ------------------------------------------------------------------ forward paths
     def _check_codes(self, codes: torch.Tensor) -> torch.Tensor:
