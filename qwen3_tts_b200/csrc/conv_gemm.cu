@@ -1,55 +1,51 @@
 // Implicit-GEMM causal conv / transposed conv / linear on tcgen05 tensor cores (sm_100a).
 //
-// Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread
-// tcgen05.mma issuer, warps 2..5 = epilogue (TMEM -> registers -> fused epilogue -> global).
-// One CTA per SM; accumulators are double-buffered in TMEM (2 x 256 fp32 columns) so the
-// epilogue of tile i overlaps the MMAs of tile i+1.  Operand tiles are K-major, written by TMA
-// with 128B (KB=64) or 64B (KB=32, the Cin=96 layers) swizzle; conv taps are time-shifted TMA
-// boxes of the same channels-last activation, with out-of-range rows zero-filled by TMA.
+// Two kernels share one warp-role layout (warp 0 = TMA producer, warp 1 = TMEM allocator +
+// single-thread tcgen05.mma issuer, warps 2..5 = asynchronous epilogue, tc_epilogue.cuh), one CTA
+// per SM, persistent over tiles, accumulators double-buffered in TMEM (2 x 256 fp32 columns):
+//
+//  conv_gemm_tc_kernel  general: pipeline stage = one (K block, tap) pair: a time-shifted 128-row
+//                       activation box plus the tap's weight tile.  Used when weights are too big
+//                       to stay resident (C >= 192).
+//  ws_conv_kernel       weight-stationary: all taps' weights are loaded into shared memory once per
+//                       CTA; per tile ONE activation slab (128 + halo rows) is loaded and every tap
+//                       reads it through a row-offset UMMA descriptor, so L2->smem traffic per tile
+//                       is the slab alone.  Used for the C = 96 layers and the 96 -> 1 output conv.
+//
+// Operand tiles are K-major, written by TMA with 128B (KB = 64) or 64B (KB = 32) swizzle; rows
+// outside [0, rows) are zero-filled by TMA (= the reference's causal left padding).
 #include "conv_gemm.h"
-#include "epilogue.cuh"
+#include "tc_epilogue.cuh"
+
+#include <cstdlib>
 
 namespace q3 {
 
 static constexpr int BM = 128;
-static constexpr int kGemmThreads = 192;
+static constexpr int kMaxGemmThreads = 64 + 32 * kMaxEpiWarps;
 static constexpr int kMaxStages = 8;
+static constexpr int kMaxSlabs = 4;
 
 struct __align__(8) GemmBarriers {
   uint64_t full[kMaxStages];
   uint64_t empty[kMaxStages];
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
+  uint64_t res_bar[kMaxEpiWarps][kMaxResDepth];
+  uint64_t w_full;
   uint32_t tmem_base;
   uint32_t pad;
+  uint32_t a_tab[64];  // ws kernel: per (K block, tap) A descriptor offset (>> 4) inside a slab
+  uint32_t b_tab[64];  // ws kernel: per (K block, tap) B descriptor low word
 };
 
-template <typename T>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmParams p, const int nstages) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int KB = p.kb;
-  const uint32_t a_bytes = BM * KB * 2;
-  const uint32_t b_bytes = p.bn * KB * 2;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
-  GemmBarriers* bars = reinterpret_cast<GemmBarriers*>(smem + (size_t)nstages * stage_bytes);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  const int m_tiles = (p.rows_valid + BM - 1) / BM;
-  const int n_tiles = p.n_total / p.bn;
-  const int total_tiles = p.batches * m_tiles * n_tiles;
-  const int kblocks = p.cin / KB;
-  const int ksteps = kblocks * p.ntaps;
-
+__device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int warp, int epi_warps) {
   if (threadIdx.x == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-    for (int s = 0; s < nstages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], 4); }
+    for (int s = 0; s < nring; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], epi_warps); }
+    for (int w = 0; w < kMaxEpiWarps; ++w)
+      for (int s = 0; s < kMaxResDepth; ++s) mbar_init(&bars->res_bar[w][s], 1);
+    mbar_init(&bars->w_full, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -59,16 +55,65 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+}
+
+template <typename T>
+__device__ __forceinline__ void epilogue_role(const GemmParams& p, const CUtensorMap* tmRes, const CUtensorMap* tmRaw, const CUtensorMap* tmSnake,
+                                              const CUtensorMap* tmF32, uint8_t* epi, GemmBarriers* bars, const TileSched& ts, uint32_t tmem_base,
+                                              int warp, int lane) {
+  const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+  const int ew = warp - 2;
+  EpiWarp<T> ep(p, tmRes, tmRaw, tmSnake, tmF32, epi + (size_t)ew * epi_slots_per_warp(p) * kEpiSlot, bars->res_bar[ew], ts, lane, quad, ew >> 2,
+                p.epi_warps >> 2);
+  ep.start();
+  int it = 0;
+  for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+    int nt, mt, b;
+    ts.decode(tile, nt, mt, b);
+    const int buf = it & 1;
+    mbar_wait(&bars->tmem_full[buf], (it >> 1) & 1);
+    tc_fence_after();
+    ep.tile(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * 256, it, nt, mt, b);
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+  }
+  ep.finish();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kMaxGemmThreads, 1)
+conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw,
+                    const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
+                    const GemmParams p, const int nstages) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int KB = p.kb;
+  const uint32_t a_bytes = BM * KB * 2;
+  const uint32_t b_bytes = p.bn * KB * 2;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  uint8_t* epi = smem + (size_t)nstages * stage_bytes;
+  GemmBarriers* bars = reinterpret_cast<GemmBarriers*>(epi + (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  TileSched ts;
+  ts.m_tiles = (p.rows_valid + BM - 1) / BM;
+  ts.n_tiles = p.n_total / p.bn;
+  ts.total_tiles = p.batches * ts.m_tiles * ts.n_tiles;
+  const int kblocks = p.cin / KB;
+  const int ksteps = kblocks * p.ntaps;
+  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  init_common(bars, nstages, warp, p.epi_warps);
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
       int s = 0; uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int nt = tile % n_tiles;
-        const int mt = (tile / n_tiles) % m_tiles;
-        const int b = tile / (n_tiles * m_tiles);
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
+        int nt, mt, b;
+        ts.decode(tile, nt, mt, b);
         const int m0 = mt * BM, n0 = nt * p.bn;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
@@ -86,23 +131,27 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ------------------------------------------------------------ MMA issuer (one thread)
     if (elect_one()) {
       const uint32_t idesc = umma_idesc(BM, p.bn, p.bf16 != 0);
-      const uint32_t span = KB * 2;
+      const uint32_t hi = umma_desc_hi(KB * 2);
+      const uint32_t a_lo0 = umma_desc_lo(smem_u32(smem)), b_off = a_bytes >> 4, st_off = stage_bytes >> 4;
+      const bool k4 = KB == 64;
       int s = 0; uint32_t ph = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
-        const uint32_t tph = (it >> 1) & 1;
-        mbar_wait(&bars->tmem_empty[buf], tph ^ 1);
+        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         for (int ks = 0; ks < ksteps; ++ks) {
           mbar_wait(&bars->full[s], ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint64_t ad = umma_smem_desc(sa, span);
-          const uint64_t bd = umma_smem_desc(sa + a_bytes, span);
-          for (int k = 0; k < KB / 16; ++k) {
-            // advance 16 elements (32 bytes) along K inside the swizzle span: +2 in the >>4 address field
-            umma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (ks | k) != 0);
+          const uint32_t a = a_lo0 + (uint32_t)s * st_off, b = a + b_off;
+          if (!(p.dbg & 2)) {
+            // +2 in the >>4 address field advances 16 elements (32 bytes) along K inside the swizzle span
+            umma_f16_lohi(d_tmem, a, b, hi, idesc, ks != 0);
+            umma_f16_lohi(d_tmem, a + 2, b + 2, hi, idesc, 1);
+            if (k4) {
+              umma_f16_lohi(d_tmem, a + 4, b + 4, hi, idesc, 1);
+              umma_f16_lohi(d_tmem, a + 6, b + 6, hi, idesc, 1);
+            }
           }
           umma_commit(&bars->empty[s]);
           if (++s == nstages) { s = 0; ph ^= 1; }
@@ -111,35 +160,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else {
-    // ------------------------------------------------------------ epilogue warps
-    const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    int it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int nt = tile % n_tiles;
-      const int mt = (tile / n_tiles) % m_tiles;
-      const int b = tile / (n_tiles * m_tiles);
-      const int buf = it & 1;
-      const uint32_t tph = (it >> 1) & 1;
-      const int row = mt * BM + quad * 32 + lane;
-      const bool row_ok = row < p.rows_valid;
-      mbar_wait(&bars->tmem_full[buf], tph);
-      tc_fence_after();
-      const uint32_t t0 = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * 256;
-      for (int c = 0; c < p.bn; c += 16) {
-        uint32_t r[16];
-        tmem_ld16(t0 + c, r);
-        tmem_ld_wait();
-        if (row_ok) {
-          float v[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-          epilogue16<T>(p, v, b, row, nt * p.bn + c);
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
-    }
+    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane);
   }
   tc_fence_before();
   __syncthreads();
@@ -149,8 +170,108 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 }
 
-// SIMT cross-check: same math, same epilogue, no tensor cores / TMA.  Debug engine only
-// (Q3TTS_ENGINE=simt); one thread per (row, 16-column group).
+// Weight-stationary slab kernel (single N tile: bn == n_total; all tap offsets <= 0).
+//   smem: [ntaps*nkb weight sub-tiles of bn x KB][nslabs x nkb slab sub-blocks of srp x KB][epilogue slots][barriers]
+// The slab row for output row m and tap j is m + tap_off[j] + halo; the UMMA descriptor of a tap simply
+// starts (tap_off[j] + halo) rows into the slab sub-block -- the swizzle is a function of the shared-memory
+// address bits, so a row-shifted start address reads the rows TMA wrote.
+template <typename T>
+__global__ void __launch_bounds__(kMaxGemmThreads, 1)
+ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw,
+               const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
+               const GemmParams p, const int nslabs, const int srp) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int KB = p.kb;
+  const int nkb = p.cin / KB;
+  const int halo = -p.tap_off[0];
+  const uint32_t wsub = p.bn * KB * 2;
+  const uint32_t ssub = srp * KB * 2;
+  const uint32_t w_bytes = p.ntaps * nkb * wsub;
+  const uint32_t slab_bytes = nkb * ssub;
+  uint8_t* wsm = smem;
+  uint8_t* slabs = smem + w_bytes;
+  uint8_t* epi = slabs + (size_t)nslabs * slab_bytes;
+  GemmBarriers* bars = reinterpret_cast<GemmBarriers*>(epi + (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  TileSched ts;
+  ts.m_tiles = (p.rows_valid + BM - 1) / BM;
+  ts.n_tiles = 1;
+  ts.total_tiles = p.batches * ts.m_tiles;
+  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  init_common(bars, nslabs, warp, p.epi_warps);
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      mbar_expect_tx(&bars->w_full, w_bytes);
+      for (int tap = 0; tap < p.ntaps; ++tap)
+        for (int kb = 0; kb < nkb; ++kb) tma_load_3d(wsm + (size_t)(tap * nkb + kb) * wsub, &tmB, &bars->w_full, kb * KB, 0, tap);
+      int s = 0; uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
+        int nt, mt, b;
+        ts.decode(tile, nt, mt, b);
+        mbar_wait(&bars->empty[s], ph ^ 1);
+        mbar_expect_tx(&bars->full[s], slab_bytes);
+        for (int kb = 0; kb < nkb; ++kb)
+          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], kb * KB, mt * BM - halo, b);
+        if (++s == nslabs) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc(BM, p.bn, p.bf16 != 0);
+      const uint32_t span = KB * 2;
+      const uint32_t hi = umma_desc_hi(span);
+      const int nsteps = nkb * p.ntaps;
+      // descriptor tables: everything that does not depend on the slab slot is computed once
+      for (int kb = 0; kb < nkb; ++kb)
+        for (int tap = 0; tap < p.ntaps; ++tap) {
+          bars->a_tab[kb * p.ntaps + tap] = (kb * ssub + (uint32_t)(p.tap_off[tap] + halo) * span) >> 4;
+          bars->b_tab[kb * p.ntaps + tap] = umma_desc_lo(smem_u32(wsm) + (uint32_t)(tap * nkb + kb) * wsub);
+        }
+      const bool k4 = KB == 64;
+      mbar_wait(&bars->w_full, 0);
+      int s = 0; uint32_t ph = 0; int it = 0;
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * 256;
+        const uint32_t slab_lo = umma_desc_lo(smem_u32(slabs + (size_t)s * slab_bytes));
+        if (!(p.dbg & 2)) {
+#pragma unroll 4
+          for (int i = 0; i < nsteps; ++i) {
+            const uint32_t a = slab_lo + bars->a_tab[i], b = bars->b_tab[i];
+            umma_f16_lohi(d_tmem, a, b, hi, idesc, i != 0);
+            umma_f16_lohi(d_tmem, a + 2, b + 2, hi, idesc, 1);
+            if (k4) {
+              umma_f16_lohi(d_tmem, a + 4, b + 4, hi, idesc, 1);
+              umma_f16_lohi(d_tmem, a + 6, b + 6, hi, idesc, 1);
+            }
+          }
+        }
+        umma_commit(&bars->empty[s]);
+        umma_commit(&bars->tmem_full[buf]);
+        if (++s == nslabs) { s = 0; ph ^= 1; }
+      }
+    }
+  } else {
+    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// SIMT cross-check: same math, direct global I/O, no tensor cores / TMA.  Debug engine only
+// (Q3TTS_ENGINE_SIMT); one thread per (row, 16-column group).
 template <typename T>
 __global__ void conv_gemm_simt_kernel(const GemmParams p) {
   const int ngroups = p.n_total / 16;
@@ -176,6 +297,11 @@ __global__ void conv_gemm_simt_kernel(const GemmParams p) {
         for (int i = 0; i < 16; ++i) acc[i] = fmaf(av, Elem<T>::to_f(w[(long long)i * p.cin + k]), acc[i]);
       }
     }
+    if (p.act == ACT_TAIL) {
+      if (row >= p.tail_skip)
+        p.out_f32[(long long)b * p.out_batch_stride + (row - p.tail_skip)] = fminf(1.0f, fmaxf(-1.0f, acc[0] + p.bias[0]));
+      continue;
+    }
     epilogue16<T>(p, acc, b, row, n);
   }
 }
@@ -193,28 +319,88 @@ int tmap_init() {
   return 0;
 }
 
-// 3-D tensor map over a 16-bit tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0].
-int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16) {
+int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1,
+                         uint64_t stride2, uint32_t box0, uint32_t box1) {
   if (tmap_init()) return -1;
-  cuuint64_t dims[3] = {d0, d1, d2};
-  cuuint64_t strides[2] = {d0 * 2, d0 * d1 * 2};
+  const uint64_t esz = etype == 2 ? 4 : 2;
+  cuuint64_t dims[3] = {d0, d1 ? d1 : 1, d2 ? d2 : 1};
+  cuuint64_t strides[2] = {stride1 * esz, stride2 * esz};
+  if (strides[1] == 0) strides[1] = strides[0] * dims[1];
   cuuint32_t box[3] = {box0, box1, 1};
   cuuint32_t estr[3] = {1, 1, 1};
-  CUtensorMapSwizzle sw = box0 * 2 == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (box0 * 2 == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-  CUresult r = g_encode(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims,
-                        strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const uint32_t inner = box0 * (uint32_t)esz;
+  CUtensorMapSwizzle sw = inner == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (inner == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  CUtensorMapDataType dt = etype == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : (etype == 1 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+  CUresult r = g_encode(out, dt, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+// 3-D tensor map over a dense 16-bit tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0].
+int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16) {
+  return make_tmap_3d_strided(out, base, bf16 ? 1 : 0, d0, d1, d2, d0, d0 * d1, box0, box1);
 }
 
 static int g_num_sms = 0;
 static int g_smem_optin = 0;
 
+static size_t epi_bytes(const GemmParams& p) { return (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot; }
+
 int gemm_stage_count(const GemmParams& p) {
   const int stage = (BM + p.bn) * p.kb * 2;
-  int n = (g_smem_optin - 1024 - (int)sizeof(GemmBarriers) - 1024) / stage;
+  int n = (int)((g_smem_optin - 1024 - (long long)epi_bytes(p) - (long long)sizeof(GemmBarriers) - 256) / stage);
   if (n > kMaxStages) n = kMaxStages;
   return n;
+}
+
+// Weight-stationary eligibility: single N tile, causal taps, weights + >= 2 slabs + epilogue slots fit in shared memory.
+static void plan_ws(GemmOp* op) {
+  const GemmParams& p = op->p;
+  op->ws = 0; op->nslabs = 0; op->srp = 0;
+  if (getenv("Q3TTS_NO_WS")) return;
+  if (p.n_total != p.bn || p.ntaps < 1) return;
+  for (int j = 0; j < p.ntaps; ++j)
+    if (p.tap_off[j] > 0 || p.tap_off[j] < p.tap_off[0]) return;
+  const int halo = -p.tap_off[0];
+  const int srp = (BM + halo + 15) / 16 * 16;
+  if (srp > 256) return;
+  const long long w_bytes = (long long)p.ntaps * p.cin * p.bn * 2;
+  const long long slab = (long long)srp * p.cin * 2;
+  const long long avail = (long long)g_smem_optin - 1024 - w_bytes - (long long)epi_bytes(p) - (long long)sizeof(GemmBarriers) - 256;
+  if (avail < 2 * slab) return;
+  int ns = (int)(avail / slab);
+  if (ns > kMaxSlabs) ns = kMaxSlabs;
+  op->ws = 1; op->nslabs = ns; op->srp = srp;
+}
+
+// Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths), choose the kernel
+// variant and (for the weight-stationary variant) rebuild the activation map with a slab-sized box.
+int gemm_make_epilogue_maps(GemmOp* op) {
+  {
+    GemmParams& q = op->p;
+    const char* ew = getenv("Q3TTS_EPI_WARPS");
+    q.epi_warps = ew ? atoi(ew) : 8;
+    if (q.epi_warps != 4 && q.epi_warps != 8) q.epi_warps = 8;
+    q.res_depth = q.res ? 4 : 0;
+    // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
+    if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
+  }
+  const GemmParams& p = op->p;
+  const int et = p.bf16 ? 1 : 0;
+  const uint64_t width = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
+  const uint64_t rows = p.rows_valid, nb = p.batches;
+  const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
+  op->tmRes = op->tmA; op->tmRaw = op->tmA; op->tmSnake = op->tmA; op->tmF32 = op->tmA;  // valid placeholders
+  int rc = 0;
+  if (p.act != ACT_TAIL) {
+    if (p.res) rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, bs, p.res_f32 ? 16 : 32, 32);
+    if (p.out_raw) rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, 32);
+    if (p.out_snake) rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, bs, 32, 32);
+    if (p.out_f32) rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32);
+  }
+  plan_ws(op);
+  if (op->ws) rc |= make_tmap_3d(&op->tmA, p.a_ptr, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint32_t)p.kb, (uint32_t)op->srp, p.bf16 != 0);
+  return rc;
 }
 
 int gemm_setup(int device) {
@@ -224,7 +410,9 @@ int gemm_setup(int device) {
   g_smem_optin = (int)prop.sharedMemPerBlockOptin;
   cudaError_t e1 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  if (e1 != cudaSuccess || e2 != cudaSuccess) return -2;
+  cudaError_t e3 = cudaFuncSetAttribute(ws_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e4 = cudaFuncSetAttribute(ws_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess) return -2;
   return tmap_init();
 }
 
@@ -241,15 +429,31 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
     else conv_gemm_simt_kernel<__half><<<blocks, 128, 0, stream>>>(p);
     return cudaGetLastError();
   }
+  // epilogue slot geometry: 16-bit tensors move in 32-column boxes, GLU in 64 accumulator columns
+  const bool t16 = (p.res && !p.res_f32) || p.out_raw || p.out_snake;
+  if (p.res && !p.res_f32 && p.out_f32 && p.act != ACT_TAIL) return cudaErrorInvalidConfiguration;  // 16-bit residual with fp32 output: unused combination
+  if (t16 && p.ncol_mod % 32) return cudaErrorInvalidConfiguration;
+  if ((t16 && p.bn % 32) || (p.act == ACT_GLU && p.bn % 64) || p.bn % 16 || p.bn > 256) return cudaErrorInvalidConfiguration;
   const int m_tiles = (p.rows_valid + BM - 1) / BM;
   const int total_tiles = p.batches * m_tiles * (p.n_total / p.bn);
   if (total_tiles <= 0) return cudaSuccess;
   const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
+  const int threads = 64 + 32 * p.epi_warps;
+  if (op.ws) {
+    const size_t smem = (size_t)p.ntaps * p.cin * p.bn * 2 + (size_t)op.nslabs * op.srp * p.cin * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+    if (p.bf16)
+      ws_conv_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
+    else
+      ws_conv_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
+    return cudaGetLastError();
+  }
   const int nstages = gemm_stage_count(p);
   if (nstages < 2) return cudaErrorInvalidConfiguration;
-  const size_t smem = (size_t)nstages * (BM + p.bn) * p.kb * 2 + sizeof(GemmBarriers) + 1024;
-  if (p.bf16) conv_gemm_tc_kernel<__nv_bfloat16><<<grid, kGemmThreads, smem, stream>>>(op.tmA, op.tmB, p, nstages);
-  else conv_gemm_tc_kernel<__half><<<grid, kGemmThreads, smem, stream>>>(op.tmA, op.tmB, p, nstages);
+  const size_t smem = (size_t)nstages * (BM + p.bn) * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+  if (p.bf16)
+    conv_gemm_tc_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+  else
+    conv_gemm_tc_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
   return cudaGetLastError();
 }
 

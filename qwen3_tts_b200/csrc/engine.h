@@ -85,7 +85,7 @@ struct Engine {
 
   // packed weights
   float* rvq_tables = nullptr;  // [Q][codes][D] fp32, output_proj folded in
-  ConvW pre_conv, in_proj, out_proj, dec0;
+  ConvW pre_conv, in_proj, out_proj, dec0, tail;
   std::vector<LayerW> layers;
   const float* final_norm = nullptr;
   std::vector<UpsampleW> ups;

@@ -1,4 +1,5 @@
 // Per-(B,T) launch plans for Qwen3TTSTokenizerV2Decoder.forward (reference modeling :868-883).
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.h"
@@ -34,6 +35,7 @@ struct Builder {
     for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
     p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
     p.bias = w.bias; p.bf16 = e->bf16 ? 1 : 0;
+    { const char* d = getenv("Q3TTS_DBG"); p.dbg = d ? atoi(d) : 0; }
     p.a_ptr = in; p.w_ptr = w.w;
     p.out_row_stride = w.n_total;
     p.out_batch_stride = (long long)rows_valid * w.n_total;
@@ -188,12 +190,18 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     }
   }
   {
-    plan->ops.emplace_back();
-    Op& op = plan->ops.back();
-    op.type = OP_TAIL; op.in = R[ia]; op.B = B; op.L = L; op.C = e->tail_c;
+    // decoder[6] + clamp on the tensor cores (N padded to 16); out pointer / stride / skip are patched per call
+    Op& op = b.gemm(e->tail, R[ia], B, L, L);
+    op.type = OP_TAIL;
+    op.g.p.act = ACT_TAIL;
+    op.B = B; op.L = L; op.C = e->tail_c;
     op.tag = "wav";
   }
   plan->out_len = L;
+  if (!dry) {
+    for (Op& op : plan->ops)
+      if ((op.type == OP_GEMM || op.type == OP_TAIL) && gemm_make_epilogue_maps(&op.g)) b.rc = e->fail(Q3TTS_CUDA_ERROR, "epilogue tensor map failed");
+  }
   if (bytes) *bytes = b.off + 1024;
   return b.rc;
 }
@@ -253,7 +261,10 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
         break;
       case OP_DWLN: err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s); break;
       case OP_TAIL:
-        if (wav) err = tail_conv_clamp(op.in, e->tail_w, e->tail_bias, wav, wav_stride, op.B, op.L, op.C, skip, e->bf16, s);
+        if (wav) {
+          op.g.p.out_f32 = wav; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
+          err = launch_conv_gemm(op.g, e->engine, s);
+        }
         break;
     }
     ++e->launches;
@@ -261,7 +272,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       cudaEventRecord(e->prof_events[2 * pi + 1], s);
       double fl = 0.0, by = 0.0;
       int dims[4] = {op.B * (op.L > 0 ? op.L : 1), op.C, 0, 0};
-      if (op.type == OP_GEMM) {
+      if (op.type == OP_GEMM || op.type == OP_TAIL) {
         const GemmParams& p = op.g.p;
         const double rows = (double)p.batches * p.rows_valid;
         dims[0] = p.batches * p.rows_valid; dims[1] = p.n_total; dims[2] = p.cin; dims[3] = p.ntaps;

@@ -36,13 +36,14 @@ struct Fin {
   void check(cudaError_t err, const char* what) {
     if (!rc && err != cudaSuccess) rc = e->fail(Q3TTS_CUDA_ERROR, std::string(what) + ": " + cudaGetErrorString(err));
   }
-  static int choose_bn(int n) {
-    for (int bn = 256; bn >= 16; bn -= 16)
+  // N tile: the epilogue moves 16-bit tensors in 32-column boxes (64 accumulator columns for the GLU epilogue)
+  static int choose_bn(int n, int step) {
+    for (int bn = 256 / step * step; bn >= step; bn -= step)
       if (n % bn == 0) return bn;
     return 0;
   }
-  void tiles(ConvW& w) {
-    w.bn = choose_bn(w.n_total);
+  void tiles(ConvW& w, int step = 32) {
+    w.bn = choose_bn(w.n_total, step);
     w.kb = (w.cin % 64 == 0) ? 64 : 32;
     if (!rc && (w.bn == 0 || w.cin % w.kb != 0 || w.ncol_mod % 16 != 0))
       rc = e->fail(Q3TTS_BAD_CONFIG, "layer shape not tileable: n=" + std::to_string(w.n_total) + " cin=" + std::to_string(w.cin));
@@ -166,7 +167,7 @@ int engine_finalize(Engine* e, int mode) {
     L.gateup.w = f.alloc((size_t)2 * I * H * 2);
     if (f.rc) break;
     f.check(pack_interleave2(g->d, u->d, L.gateup.w, I, H, e->bf16, f.s), "pack gate/up");
-    f.tiles(L.gateup);
+    f.tiles(L.gateup, 64);
     L.down = f.linear(p + "mlp.down_proj", H, I, false);
     L.ln1 = f.vec(p + "input_layernorm.weight", H);
     L.ln2 = f.vec(p + "post_attention_layernorm.weight", H);
@@ -229,6 +230,22 @@ int engine_finalize(Engine* e, int mode) {
       e->tail_w = (float*)f.alloc((size_t)7 * Cl * sizeof(float));
       if (!f.rc) f.check(pack_dw_weight(tw->d, e->tail_w, Cl, 7, f.s), "pack tail");
       if (!f.rc) f.check(cudaMemcpy(&e->tail_bias, tb->d, sizeof(float), cudaMemcpyDeviceToHost), "tail bias");
+      // tensor-core form: N padded 1 -> 16 (smallest UMMA N at M = 128); only output column 0 is stored
+      ConvW& t = e->tail;
+      t.taps = 7; t.n_total = 16; t.cin = Cl; t.ncol_mod = 16; t.bn = 16; t.kb = (Cl % 64 == 0) ? 64 : 32;
+      for (int j = 0; j < 7; ++j) t.tap_off[j] = -(6 - j);
+      void* tmp = f.alloc((size_t)7 * Cl * 2);
+      t.w = f.alloc((size_t)7 * 16 * Cl * 2);
+      float* tbias = (float*)f.alloc(16 * sizeof(float));
+      if (!f.rc) {
+        f.check(cudaMemset(t.w, 0, (size_t)7 * 16 * Cl * 2), "tail memset");
+        f.check(cudaMemset(tbias, 0, 16 * sizeof(float)), "tail bias memset");
+        f.check(pack_conv_weight(tw->d, tmp, 1, Cl, 7, e->bf16, f.s), "pack tail gemm");
+        f.check(cudaMemcpy2D(t.w, (size_t)16 * Cl * 2, tmp, (size_t)Cl * 2, (size_t)Cl * 2, 7, cudaMemcpyDeviceToDevice), "tail scatter");
+        f.check(cudaMemcpy(tbias, tb->d, sizeof(float), cudaMemcpyDeviceToDevice), "tail bias copy");
+        t.bias = tbias;
+        if (Cl % t.kb) f.rc = e->fail(Q3TTS_BAD_CONFIG, "tail channels not tileable");
+      }
     }
   }
   // ---- RoPE table

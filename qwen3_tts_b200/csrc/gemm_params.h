@@ -20,7 +20,9 @@
 
 namespace q3 {
 
-enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2 };
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3 };
+// ACT_TAIL: accumulator column 0 + bias[0], clamp(-1, 1), stored as fp32 to out_f32[b*out_batch_stride + row - tail_skip]
+// for row >= tail_skip (the 96 -> 1 output conv + clamp, reference modeling :862, :883; skip = chunk left context).
 
 struct GemmParams {
   int batches;
@@ -36,6 +38,10 @@ struct GemmParams {
   int act;
   int res_f32;
   int bf16;
+  int tail_skip;
+  int epi_warps;  // 4 or 8 epilogue warps (8: two per TMEM lane quadrant)
+  int res_depth;  // residual prefetch ring depth per warp (2, 4 or 8 slots)
+  int dbg;  // debug experiments (env Q3TTS_DBG): bit 0 = epilogue only drains TMEM, bit 1 = MMA thread issues no MMAs
   const float* bias;
   const float* scale;
   const void* res;

@@ -79,11 +79,19 @@ extern "C" int q3tts_selftest_gemm(int device, int rows, int cin, int n, int nta
     if (make_tmap_3d(&op.tmA, A, cin, rows, batches, kb, 128, bf16 != 0) || make_tmap_3d(&op.tmB, W, cin, n, ntaps, kb, bn, bf16 != 0)) {
       rc = Q3TTS_CUDA_ERROR;
     } else {
-      p.out_f32 = o1;
-      cudaError_t e1 = launch_conv_gemm(op, ENGINE_TC, 0);
       p.out_f32 = o2;
       cudaError_t e2 = launch_conv_gemm(op, ENGINE_SIMT, 0);
+      p.out_f32 = o1;
+      gemm_make_epilogue_maps(&op);  // picks the weight-stationary slab kernel when the shape allows it
+      cudaError_t e1 = launch_conv_gemm(op, ENGINE_TC, 0);
       k_maxdiff<<<296, 256>>>(o1, o2, (long long)no, res);
+      if (op.ws && e1 == cudaSuccess) {  // also exercise the general (per-tap TMA box) kernel on the same problem
+        op.ws = 0;
+        make_tmap_3d(&op.tmA, A, cin, rows, batches, kb, 128, bf16 != 0);
+        cudaMemsetAsync(o1, 0xff, no * 4, 0);
+        e1 = launch_conv_gemm(op, ENGINE_TC, 0);
+        k_maxdiff<<<296, 256>>>(o1, o2, (long long)no, res);
+      }
       float hres[2] = {0.f, 0.f};
       cudaError_t e3 = cudaMemcpy(hres, res, 8, cudaMemcpyDeviceToHost);
       if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) rc = Q3TTS_CUDA_ERROR;

@@ -1,0 +1,325 @@
+// Asynchronous per-warp epilogue shared by the tcgen05 kernels.
+//
+// 4 or 8 epilogue warps.  A warp may only read its TMEM lane quadrant (warp % 4), i.e. 32 accumulator
+// rows; with 8 warps the two warps of a quadrant split a tile's columns item by item.  A work item is
+// 32 accumulator columns (two independent 16-column halves, for instruction-level parallelism), 64 for
+// the GLU epilogue, 16 when an fp32 tensor is involved.  Every warp has a private ring of 2 KB
+// shared-memory slots (32 rows x 64 bytes, SWIZZLE_64B) and private mbarriers: residual tiles arrive by
+// TMA, prefetched `res_depth` slots ahead across tile boundaries; results are staged in slots and leave
+// by TMA store.  Nothing blocks on a global load or store; rows/columns past the end of a tensor are
+// clipped by the tensor maps.
+#pragma once
+#include "epilogue.cuh"
+
+namespace q3 {
+
+static constexpr int kEpiSlot = 2048;  // 32 rows x 64 bytes
+static constexpr int kMaxEpiWarps = 8;
+static constexpr int kMaxResDepth = 8;
+
+__host__ __device__ inline int epi_res_depth(const GemmParams& p) { return p.res ? (p.res_depth > 0 ? p.res_depth : 4) : 0; }
+// slots per warp for a given epilogue configuration
+__host__ __device__ inline int epi_slots_per_warp(const GemmParams& p) {
+  if (p.act == ACT_TAIL) return 0;
+  int n = epi_res_depth(p);
+  if (p.act == ACT_GLU) return n + 2;
+  if (p.out_raw) n += 2;
+  if (p.out_snake) n += 2;
+  if (p.out_f32) n += 4;
+  return n;
+}
+
+// 16-byte chunk `c` of row `lane` inside a 32-row x 64-byte SWIZZLE_64B slot
+__device__ __forceinline__ uint32_t slot_off(int lane, int c) { return (uint32_t)(lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4)); }
+
+struct TileSched {
+  int m_tiles, n_tiles, total_tiles;
+  __device__ __forceinline__ void decode(long long tile, int& nt, int& mt, int& b) const {
+    nt = (int)(tile % n_tiles);
+    mt = (int)((tile / n_tiles) % m_tiles);
+    b = (int)(tile / ((long long)n_tiles * m_tiles));
+  }
+};
+
+template <typename T>
+struct EpiWarp {
+  const GemmParams& p;
+  const CUtensorMap* tmRes; const CUtensorMap* tmRaw; const CUtensorMap* tmSnake; const CUtensorMap* tmF32;
+  uint8_t* eb;        // this warp's slots
+  uint64_t* rbar;     // this warp's residual barriers
+  TileSched ts;
+  int lane, quad, half, nsplit;
+  bool has_res, rf32, glu, tail, of32, o16;
+  int units, item_units, nitems, rd;
+  int s_raw, s_snake, s_f32;  // first slot of each output ring
+  uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
+  int pf_it = 0, pf_item = 0;  // residual prefetch cursor (tile iteration, item)
+  bool pf_done = false;
+
+  __device__ EpiWarp(const GemmParams& p_, const CUtensorMap* r, const CUtensorMap* a, const CUtensorMap* s, const CUtensorMap* f,
+                     uint8_t* eb_, uint64_t* rbar_, TileSched ts_, int lane_, int quad_, int half_, int nsplit_)
+      : p(p_), tmRes(r), tmRaw(a), tmSnake(s), tmF32(f), eb(eb_), rbar(rbar_), ts(ts_), lane(lane_), quad(quad_), half(half_), nsplit(nsplit_) {
+    has_res = p.res != nullptr && !(p.dbg & 8);
+    rf32 = p.res_f32 != 0;
+    glu = p.act == ACT_GLU;
+    tail = p.act == ACT_TAIL;
+    of32 = p.out_f32 != nullptr && !tail;
+    o16 = !glu && (p.out_raw != nullptr || p.out_snake != nullptr);
+    units = p.bn >> 4;
+    item_units = glu ? 4 : ((of32 || (has_res && rf32) || tail) ? 1 : 2);
+    nitems = units / item_units;
+    rd = epi_res_depth(p);
+    int nslot = rd;
+    s_raw = nslot;
+    if (glu || p.out_raw) nslot += 2;
+    s_snake = nslot;
+    if (!glu && p.out_snake) nslot += 2;
+    s_f32 = nslot;
+  }
+
+  // first item this warp owns in tile iteration `it` (the two warps of a quadrant alternate so odd item counts balance)
+  __device__ __forceinline__ int first_item(int it) const { return (half + nsplit - (it % nsplit)) % nsplit; }
+
+  __device__ __forceinline__ void prefetch_one() {  // warp-uniform control flow; lane 0 issues
+    if (pf_done) return;
+    while (pf_item >= nitems) {
+      ++pf_it;
+      pf_item = first_item(pf_it);
+      if ((long long)blockIdx.x + (long long)pf_it * gridDim.x >= ts.total_tiles) { pf_done = true; return; }
+    }
+    const long long tile = (long long)blockIdx.x + (long long)pf_it * gridDim.x;
+    if (tile >= ts.total_tiles) { pf_done = true; return; }
+    if (lane == 0) {
+      int nt, mt, b;
+      ts.decode(tile, nt, mt, b);
+      const uint32_t slot = rb_issue % rd;
+      mbar_expect_tx(&rbar[slot], kEpiSlot);
+      tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, mt * 128 + quad * 32, b);
+    }
+    ++rb_issue;
+    pf_item += nsplit;
+  }
+
+  __device__ __forceinline__ void start() {
+    if (has_res && !(p.dbg & 1)) {
+      pf_it = 0;
+      pf_item = first_item(0);
+      for (int i = 0; i < rd; ++i) prefetch_one();
+    }
+  }
+
+  __device__ __forceinline__ void pack_store(uint8_t* o8, int cb, const float (&v)[16]) {
+    uint4 a, c;
+    a.x = Elem<T>::pack2(v[0], v[1]);   a.y = Elem<T>::pack2(v[2], v[3]);
+    a.z = Elem<T>::pack2(v[4], v[5]);   a.w = Elem<T>::pack2(v[6], v[7]);
+    c.x = Elem<T>::pack2(v[8], v[9]);   c.y = Elem<T>::pack2(v[10], v[11]);
+    c.z = Elem<T>::pack2(v[12], v[13]); c.w = Elem<T>::pack2(v[14], v[15]);
+    *reinterpret_cast<uint4*>(o8 + slot_off(lane, cb)) = a;
+    *reinterpret_cast<uint4*>(o8 + slot_off(lane, cb + 1)) = c;
+  }
+  __device__ __forceinline__ void load_res16(const uint8_t* rbuf, int cb, float (&rs)[16]) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const uint4 t = *reinterpret_cast<const uint4*>(rbuf + slot_off(lane, cb + c));
+      const uint32_t w4[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = Elem<T>::unpack2(w4[i]);
+        rs[8 * c + 2 * i] = f.x; rs[8 * c + 2 * i + 1] = f.y;
+      }
+    }
+  }
+  // bias -> (GELU) -> scale -> + residual
+  __device__ __forceinline__ void math_unit(float (&v)[16], const float (&rs)[16], int c0) {
+    if (p.bias && !(p.dbg & 16)) {
+      float t[16]; load16f(p.bias + c0, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += t[i];
+    }
+    if (p.act == ACT_GELU) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+    }
+    if (p.scale) {
+      float t[16]; load16f(p.scale + c0, t);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] *= t[i];
+    }
+    if (has_res) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] += rs[i];
+    }
+  }
+  __device__ __forceinline__ void snake_unit(float (&v)[16], int c0) {
+    float sa[16], sib[16];
+    if (p.dbg & 16) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { sa[i] = 1.0f; sib[i] = 0.5f; }
+    } else {
+      load16f(p.snake_a + c0, sa);
+      load16f(p.snake_ib + c0, sib);
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = snake(v[i], sa[i], sib[i]);
+  }
+  __device__ __forceinline__ void res_consumed() {  // slot fully read by every lane: refill it rd slots ahead
+    __syncwarp();
+    prefetch_one();
+    ++rb_cons;
+  }
+
+  // ---- 16-bit flow: 32 accumulator columns, residual / outputs all 16-bit
+  __device__ __forceinline__ void item_pair(uint32_t t0, int nt, int row0, int b, int item) {
+    const int u0 = item * 2;
+    const int n0 = nt * p.bn + u0 * 16;
+    const int c0 = n0 % p.ncol_mod;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
+    uint32_t ra[16], rb[16];
+    tmem_ld16(t0 + u0 * 16, ra);
+    tmem_ld16(t0 + u0 * 16 + 16, rb);
+    float rsa[16], rsb[16];
+    if (has_res) {
+      const uint32_t slot = rb_cons % rd;
+      mbar_wait(&rbar[slot], (rb_cons / rd) & 1);
+      const uint8_t* rbuf = eb + slot * kEpiSlot;
+      load_res16(rbuf, 0, rsa);
+      load_res16(rbuf, 2, rsb);
+      res_consumed();
+    }
+    tmem_ld_wait();
+    float va[16], vb[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(ra[i]); vb[i] = __uint_as_float(rb[i]); }
+    math_unit(va, rsa, c0);
+    math_unit(vb, rsb, c0 + 16);
+    const uint32_t sl = ob & 1;
+    const bool st = !(p.dbg & 4);
+    if (st) {
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+    }
+    if (p.out_raw) {
+      pack_store(eb + (s_raw + sl) * kEpiSlot, 0, va);
+      pack_store(eb + (s_raw + sl) * kEpiSlot, 2, vb);
+    }
+    if (p.out_snake) {
+      snake_unit(va, c0);
+      snake_unit(vb, c0 + 16);
+      pack_store(eb + (s_snake + sl) * kEpiSlot, 0, va);
+      pack_store(eb + (s_snake + sl) * kEpiSlot, 2, vb);
+    }
+    if (st) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (p.out_raw) tma_store_3d(tmRaw, eb + (s_raw + sl) * kEpiSlot, n0, row0, b);
+        if (p.out_snake) tma_store_3d(tmSnake, eb + (s_snake + sl) * kEpiSlot, n0, row0, b);
+        tma_store_commit();
+      }
+    }
+    ++ob;
+  }
+
+  // ---- fp32 flow: 16 accumulator columns; residual and/or output are fp32 (transformer residual stream)
+  __device__ __forceinline__ void item_f32(uint32_t t0, int nt, int row0, int b, int item) {
+    const int n0 = nt * p.bn + item * 16;
+    const int c0 = n0 % p.ncol_mod;
+    uint32_t r[16];
+    tmem_ld16(t0 + item * 16, r);
+    float rs[16];
+    if (has_res) {
+      const uint32_t slot = rb_cons % rd;
+      mbar_wait(&rbar[slot], (rb_cons / rd) & 1);
+      const uint8_t* rbuf = eb + slot * kEpiSlot;
+      if (rf32) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const float4 t = *reinterpret_cast<const float4*>(rbuf + slot_off(lane, c));
+          rs[4 * c] = t.x; rs[4 * c + 1] = t.y; rs[4 * c + 2] = t.z; rs[4 * c + 3] = t.w;
+        }
+      } else {
+        load_res16(rbuf, 0, rs);  // a 16-bit residual box of 16 columns sits in chunks 0..1
+      }
+      res_consumed();
+    }
+    tmem_ld_wait();
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+    if (tail) {
+      if (p.bias) v[0] += __ldg(p.bias);
+      const int row = row0 + lane;
+      if (row < p.rows_valid && row >= p.tail_skip)
+        p.out_f32[(long long)b * p.out_batch_stride + (row - p.tail_skip)] = fminf(1.0f, fmaxf(-1.0f, v[0]));
+      return;
+    }
+    math_unit(v, rs, c0);
+    if (of32) {
+      uint8_t* o8 = eb + (s_f32 + (fb & 3)) * kEpiSlot;
+      if (lane == 0) tma_store_wait_read<3>();
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        *reinterpret_cast<float4*>(o8 + slot_off(lane, c)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_3d(tmF32, o8, n0, row0, b);
+        tma_store_commit();
+      }
+      ++fb;
+    }
+  }
+
+  // ---- GLU flow: 64 interleaved (gate, up) accumulator columns -> 32 outputs (reference modeling :367-369)
+  __device__ __forceinline__ uint4 glu8(const uint32_t (&r)[16]) {
+    uint4 o;
+    o.x = Elem<T>::pack2(silu(__uint_as_float(r[0])) * __uint_as_float(r[1]), silu(__uint_as_float(r[2])) * __uint_as_float(r[3]));
+    o.y = Elem<T>::pack2(silu(__uint_as_float(r[4])) * __uint_as_float(r[5]), silu(__uint_as_float(r[6])) * __uint_as_float(r[7]));
+    o.z = Elem<T>::pack2(silu(__uint_as_float(r[8])) * __uint_as_float(r[9]), silu(__uint_as_float(r[10])) * __uint_as_float(r[11]));
+    o.w = Elem<T>::pack2(silu(__uint_as_float(r[12])) * __uint_as_float(r[13]), silu(__uint_as_float(r[14])) * __uint_as_float(r[15]));
+    return o;
+  }
+  __device__ __forceinline__ void item_glu(uint32_t t0, int nt, int row0, int b, int item) {
+    const int u0 = item * 4;
+    uint8_t* o8 = eb + (s_raw + (ob & 1)) * kEpiSlot;
+    if (lane == 0) tma_store_wait_read<1>();
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t ra[16], rb[16];
+      tmem_ld16(t0 + (u0 + 2 * h) * 16, ra);
+      tmem_ld16(t0 + (u0 + 2 * h) * 16 + 16, rb);
+      tmem_ld_wait();
+      *reinterpret_cast<uint4*>(o8 + slot_off(lane, 2 * h)) = glu8(ra);
+      *reinterpret_cast<uint4*>(o8 + slot_off(lane, 2 * h + 1)) = glu8(rb);
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_3d(tmRaw, o8, (nt * p.bn + u0 * 16) >> 1, row0, b);
+      tma_store_commit();
+    }
+    ++ob;
+  }
+
+  // one accumulator tile: t0 = TMEM address of (this warp's lane quadrant, first column of the tile)
+  __device__ __forceinline__ void tile(uint32_t t0, int it, int nt, int mt, int b) {
+    const int row0 = mt * 128 + quad * 32;
+    if (p.dbg & 1) {
+      uint32_t r[16];
+      for (int u = half; u < units; u += nsplit) { tmem_ld16(t0 + u * 16, r); tmem_ld_wait(); }
+      return;
+    }
+    for (int item = first_item(it); item < nitems; item += nsplit) {
+      if (glu) item_glu(t0, nt, row0, b, item);
+      else if (item_units == 2) item_pair(t0, nt, row0, b, item);
+      else item_f32(t0, nt, row0, b, item);
+    }
+  }
+
+  __device__ __forceinline__ void finish() {
+    if (lane == 0) tma_store_wait<0>();
+  }
+};
+
+}  // namespace q3

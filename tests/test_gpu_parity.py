@@ -133,7 +133,8 @@ def test_wrapper_decode_payload_forms_and_length_rule(gpu_model):
         np.testing.assert_array_equal(a, b)
     # single (T, Q) tensor -> batch of one
     w1, _ = tok.decode({"audio_codes": codes[1, :lengths[1]]})
-    assert len(w1) == 1 and w1[0].shape == want[1].shape
+    # decoded alone the 9-frame item is NOT padded to 14, so it ends 555 samples early (look-ahead of the transposed convs)
+    assert len(w1) == 1 and w1[0].shape == (lengths[1] * 1920 - 555,)
 
     class _Out:
         audio_codes = [codes[0]]
