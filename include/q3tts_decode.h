@@ -125,6 +125,11 @@ int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, d
  * (device-side, no host math): returns max |tc - simt| over a [rows,n] problem via *max_abs_diff. */
 int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dilation, int bf16, float* max_abs_diff, float* max_abs_ref);
 
+/* Self-test of the fused residual-unit kernel (conv7 -> Snake -> conv1 + residual in one launch, intermediate kept in
+ * tensor memory) against two launches of the SIMT cross-check: out4 = {max|y-y_ref|, max|y_ref|, max|s-s_ref|, max|s_ref|}.
+ * Returns Q3TTS_BAD_CONFIG when the channel count cannot be fused. */
+int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4);
+
 #ifdef __cplusplus
 }
 #endif

@@ -33,6 +33,8 @@ struct __align__(8) GemmBarriers {
   uint64_t tmem_empty[2];
   uint64_t res_bar[kMaxEpiWarps][kMaxResDepth];
   uint64_t w_full;
+  uint64_t sfull[kMaxSlabs];   // slab-stream kernel: activation slab ring
+  uint64_t sempty[kMaxSlabs];
   uint32_t tmem_base;
   uint32_t pad;
   uint32_t a_tab[64];  // ws kernel: per (K block, tap) A descriptor offset (>> 4) inside a slab
@@ -46,6 +48,7 @@ __device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int w
     for (int w = 0; w < kMaxEpiWarps; ++w)
       for (int s = 0; s < kMaxResDepth; ++s) mbar_init(&bars->res_bar[w][s], 1);
     mbar_init(&bars->w_full, 1);
+    for (int s = 0; s < kMaxSlabs; ++s) { mbar_init(&bars->sfull[s], 1); mbar_init(&bars->sempty[s], 1); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -270,6 +273,111 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
+
+// Slab-stream kernel (multi-tap convs whose weights do not fit in shared memory: C >= 192).
+//   smem: [nslabs x (srp x KB) activation slabs][nstages x (bn x KB) weight tiles][epilogue slots][barriers]
+// Per (tile, K block) ONE activation slab (128 + halo rows, time-shifted taps read it through row-offset UMMA
+// descriptors exactly like ws_conv_kernel) and ntaps weight tiles are loaded, so the L2 -> shared-memory
+// traffic per MMA drops from (128 + bn) to (srp / ntaps + bn) rows of K: the general kernel re-loads the
+// activation box once per tap and is bound by that traffic, not by the tensor pipe (profiles/r1_*).
+// slab_lo = rows of halo before the tile (-min tap_off), so it also serves the {0, +1} taps of a transposed conv.
+template <typename T>
+__global__ void __launch_bounds__(kMaxGemmThreads, 1)
+slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw,
+                 const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
+                 const GemmParams p, const int nslabs, const int nstages, const int srp, const int slab_lo) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int KB = p.kb;
+  const int nkb = p.cin / KB;
+  const uint32_t wsub = p.bn * KB * 2;
+  const uint32_t ssub = srp * KB * 2;
+  uint8_t* slabs = smem;
+  uint8_t* wst = smem + (size_t)nslabs * ssub;
+  uint8_t* epi = wst + (size_t)nstages * wsub;
+  GemmBarriers* bars = reinterpret_cast<GemmBarriers*>(epi + (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  TileSched ts;
+  ts.m_tiles = (p.rows_valid + BM - 1) / BM;
+  ts.n_tiles = p.n_total / p.bn;
+  ts.total_tiles = p.batches * ts.m_tiles * ts.n_tiles;
+  if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+  init_common(bars, nstages, warp, p.epi_warps);
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int s = 0, ss = 0; uint32_t ph = 0, sph = 0;
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
+        int nt, mt, b;
+        ts.decode(tile, nt, mt, b);
+        const int n0 = nt * p.bn;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&bars->sempty[ss], sph ^ 1);
+          mbar_expect_tx(&bars->sfull[ss], ssub);
+          tma_load_3d(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * BM - slab_lo, b);
+          if (++ss == nslabs) { ss = 0; sph ^= 1; }
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            mbar_wait(&bars->empty[s], ph ^ 1);
+            mbar_expect_tx(&bars->full[s], wsub);
+            tma_load_3d(wst + (size_t)s * wsub, &tmB, &bars->full[s], kb * KB, n0, tap);
+            if (++s == nstages) { s = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc(BM, p.bn, p.bf16 != 0);
+      const uint32_t span = KB * 2;
+      const uint32_t hi = umma_desc_hi(span);
+      for (int tap = 0; tap < p.ntaps; ++tap) bars->a_tab[tap] = ((uint32_t)(p.tap_off[tap] + slab_lo) * span) >> 4;
+      const uint32_t w_lo0 = umma_desc_lo(smem_u32(wst)), w_off = wsub >> 4;
+      const uint32_t s_lo0 = umma_desc_lo(smem_u32(slabs)), s_off = ssub >> 4;
+      const bool k4 = KB == 64;
+      int s = 0, ss = 0; uint32_t ph = 0, sph = 0; int it = 0;
+      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * 256;
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(&bars->sfull[ss], sph);
+          const uint32_t slab_lo_desc = s_lo0 + (uint32_t)ss * s_off;
+          for (int tap = 0; tap < p.ntaps; ++tap) {
+            mbar_wait(&bars->full[s], ph);
+            tc_fence_after();
+            const uint32_t a = slab_lo_desc + bars->a_tab[tap], b = w_lo0 + (uint32_t)s * w_off;
+            if (!(p.dbg & 2)) {
+              umma_f16_lohi(d_tmem, a, b, hi, idesc, (kb | tap) != 0);
+              umma_f16_lohi(d_tmem, a + 2, b + 2, hi, idesc, 1);
+              if (k4) {
+                umma_f16_lohi(d_tmem, a + 4, b + 4, hi, idesc, 1);
+                umma_f16_lohi(d_tmem, a + 6, b + 6, hi, idesc, 1);
+              }
+            }
+            umma_commit(&bars->empty[s]);
+            if (++s == nstages) { s = 0; ph ^= 1; }
+          }
+          umma_commit(&bars->sempty[ss]);
+          if (++ss == nslabs) { ss = 0; sph ^= 1; }
+        }
+        umma_commit(&bars->tmem_full[buf]);
+      }
+    }
+  } else {
+    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // SIMT cross-check: same math, direct global I/O, no tensor cores / TMA.  Debug engine only
 // (Q3TTS_ENGINE_SIMT); one thread per (row, 16-column group).
 template <typename T>
@@ -353,29 +461,46 @@ int gemm_stage_count(const GemmParams& p) {
   return n;
 }
 
-// Weight-stationary eligibility: single N tile, causal taps, weights + >= 2 slabs + epilogue slots fit in shared memory.
-static void plan_ws(GemmOp* op) {
+// Kernel variant: weight-stationary (single N tile, causal taps, weights + >= 2 slabs + epilogue slots fit in shared
+// memory), else slab-stream (any multi-tap conv), else the general per-stage kernel (1-tap GEMMs).
+static void plan_variant(GemmOp* op, int allow) {
   const GemmParams& p = op->p;
-  op->ws = 0; op->nslabs = 0; op->srp = 0;
-  if (getenv("Q3TTS_NO_WS")) return;
-  if (p.n_total != p.bn || p.ntaps < 1) return;
-  for (int j = 0; j < p.ntaps; ++j)
-    if (p.tap_off[j] > 0 || p.tap_off[j] < p.tap_off[0]) return;
-  const int halo = -p.tap_off[0];
-  const int srp = (BM + halo + 15) / 16 * 16;
-  if (srp > 256) return;
-  const long long w_bytes = (long long)p.ntaps * p.cin * p.bn * 2;
-  const long long slab = (long long)srp * p.cin * 2;
-  const long long avail = (long long)g_smem_optin - 1024 - w_bytes - (long long)epi_bytes(p) - (long long)sizeof(GemmBarriers) - 256;
-  if (avail < 2 * slab) return;
-  int ns = (int)(avail / slab);
-  if (ns > kMaxSlabs) ns = kMaxSlabs;
-  op->ws = 1; op->nslabs = ns; op->srp = srp;
+  op->ws = 0; op->nslabs = 0; op->srp = 0; op->variant = 0; op->nstages = 0; op->slab_lo = 0;
+  int lo = 0, hi = 0;
+  for (int j = 0; j < p.ntaps; ++j) {
+    if (-p.tap_off[j] > lo) lo = -p.tap_off[j];
+    if (p.tap_off[j] > hi) hi = p.tap_off[j];
+  }
+  const long long fixed = 1024 + (long long)epi_bytes(p) + (long long)sizeof(GemmBarriers) + 256;
+  if ((allow & 2) && !getenv("Q3TTS_NO_WS") && p.n_total == p.bn && p.ntaps >= 1 && hi == 0 && lo == -p.tap_off[0]) {
+    const int srp = (BM + lo + 15) / 16 * 16;
+    const long long w_bytes = (long long)p.ntaps * p.cin * p.bn * 2;
+    const long long slab = (long long)srp * p.cin * 2;
+    const long long avail = (long long)g_smem_optin - fixed - w_bytes;
+    if (srp <= 256 && avail >= 2 * slab && p.ntaps * (p.cin / p.kb) <= 64) {
+      int ns = (int)(avail / slab);
+      if (ns > kMaxSlabs) ns = kMaxSlabs;
+      op->ws = 1; op->variant = 1; op->nslabs = ns; op->srp = srp; op->slab_lo = lo;
+      return;
+    }
+  }
+  if ((allow & 4) && !getenv("Q3TTS_NO_SLAB") && p.ntaps >= 2) {
+    const int srp = (BM + lo + hi + 15) / 16 * 16;
+    const long long slab = (long long)srp * p.kb * 2, wst = (long long)p.bn * p.kb * 2;
+    const long long avail = (long long)g_smem_optin - fixed;
+    if (srp <= 256) {
+      int ns = 3;
+      int nst = (int)((avail - ns * slab) / wst);
+      if (nst < 4) { ns = 2; nst = (int)((avail - ns * slab) / wst); }
+      if (nst > kMaxStages) nst = kMaxStages;
+      if (nst >= 2) { op->variant = 2; op->nslabs = ns; op->nstages = nst; op->srp = srp; op->slab_lo = lo; }
+    }
+  }
 }
 
 // Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths), choose the kernel
 // variant and (for the weight-stationary variant) rebuild the activation map with a slab-sized box.
-int gemm_make_epilogue_maps(GemmOp* op) {
+int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   {
     GemmParams& q = op->p;
     const char* ew = getenv("Q3TTS_EPI_WARPS");
@@ -398,8 +523,8 @@ int gemm_make_epilogue_maps(GemmOp* op) {
     if (p.out_snake) rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, bs, 32, 32);
     if (p.out_f32) rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32);
   }
-  plan_ws(op);
-  if (op->ws) rc |= make_tmap_3d(&op->tmA, p.a_ptr, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint32_t)p.kb, (uint32_t)op->srp, p.bf16 != 0);
+  plan_variant(op, allow);
+  rc |= make_tmap_3d(&op->tmA, p.a_ptr, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint32_t)p.kb, (uint32_t)(op->variant ? op->srp : BM), p.bf16 != 0);
   return rc;
 }
 
@@ -412,11 +537,14 @@ int gemm_setup(int device) {
   cudaError_t e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e3 = cudaFuncSetAttribute(ws_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e4 = cudaFuncSetAttribute(ws_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess) return -2;
+  cudaError_t e5 = cudaFuncSetAttribute(slab_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e6 = cudaFuncSetAttribute(slab_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess || e5 != cudaSuccess || e6 != cudaSuccess) return -2;
   return tmap_init();
 }
 
 int gemm_num_sms() { return g_num_sms; }
+int gemm_smem_optin() { return g_smem_optin; }
 
 cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) {
   const GemmParams& p = op.p;
@@ -445,6 +573,16 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
       ws_conv_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
     else
       ws_conv_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
+    return cudaGetLastError();
+  }
+  if (op.variant == 2) {
+    const size_t smem = (size_t)op.nslabs * op.srp * p.kb * 2 + (size_t)op.nstages * p.bn * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+    if (p.bf16)
+      slab_conv_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages,
+                                                                       op.srp, op.slab_lo);
+    else
+      slab_conv_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp,
+                                                                op.slab_lo);
     return cudaGetLastError();
   }
   const int nstages = gemm_stage_count(p);

@@ -20,16 +20,44 @@ struct GemmOp {
   CUtensorMap tmSnake; // 16-bit Snake'd output stores
   CUtensorMap tmF32;   // fp32 output stores
   GemmParams p;
-  int ws = 0;      // 1: weight-stationary slab kernel
-  int nslabs = 0;  // slab ring depth
-  int srp = 0;     // slab rows (128 + halo, rounded up to 16)
+  int ws = 0;       // 1: weight-stationary slab kernel
+  int variant = 0;  // 0 general (one TMA box pair per (K block, tap)), 1 weight-stationary, 2 slab-stream
+  int nslabs = 0;   // slab ring depth
+  int nstages = 0;  // slab-stream: weight tile ring depth
+  int srp = 0;      // slab rows (128 + halo, rounded up to 16)
+  int slab_lo = 0;  // slab rows before the tile's first row (-min tap_off)
 };
 
+
+// Fused vocoder residual unit (reference modeling :618-634):  y = x + W1 . snake2(W7 (*) a1 + b7) + b1,
+// a1 = snake1(x) written by the producing kernel's epilogue.  One launch replaces the conv7 and conv1 launches:
+// the conv7 accumulator is Snake'd and packed back into tensor memory, where the 1x1 conv reads it as its A operand
+// (tcgen05.mma with A in TMEM), so the C x L intermediate never touches shared or global memory.
+struct UnitOp {
+  CUtensorMap tmA;     // a1 slab loads (box kb x slab_box_rows)
+  CUtensorMap tmW7;    // [7][C][C] K-major, box kb x C
+  CUtensorMap tmW1;    // [1][C][C]
+  CUtensorMap tmRes, tmRaw, tmSnake;
+  GemmParams p;        // describes the 1x1 conv epilogue (bias = b1, res = x, out_raw = y, out_snake = next a1)
+  const float* bias7 = nullptr;
+  const float* snake2_a = nullptr;
+  const float* snake2_ib = nullptr;
+  int C = 0, dil = 1, ms = 1;         // ms: 128-row sub-tiles per CTA tile (2 for C <= 96)
+  int srows = 0, nbox = 1;            // slab rows per K block (128*ms + 6*dil rounded up), TMA boxes per slab
+  int nslabs = 0, nstages = 0;        // ring depths
+  int enabled = 0;
+};
+// Fills the maps and ring sizes; returns 0 when the shape can be fused (enabled = 1), 1 when it cannot, < 0 on error.
+int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows);
+cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream);
+
 // Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths).
-int gemm_make_epilogue_maps(GemmOp* op);
+// `allow` = bit mask of kernel variants that may be chosen (bit 0 general, bit 1 weight-stationary, bit 2 slab-stream); also (re)builds tmA.
+int gemm_make_epilogue_maps(GemmOp* op, int allow = 7);
 
 int gemm_setup(int device);
 int gemm_num_sms();
+int gemm_smem_optin();
 int tmap_init();
 int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16);
 // general 3-D map: element type 0 = fp16, 1 = bf16, 2 = fp32; strides in elements

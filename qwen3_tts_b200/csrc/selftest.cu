@@ -82,15 +82,17 @@ extern "C" int q3tts_selftest_gemm(int device, int rows, int cin, int n, int nta
       p.out_f32 = o2;
       cudaError_t e2 = launch_conv_gemm(op, ENGINE_SIMT, 0);
       p.out_f32 = o1;
-      gemm_make_epilogue_maps(&op);  // picks the weight-stationary slab kernel when the shape allows it
+      gemm_make_epilogue_maps(&op);  // picks weight-stationary / slab-stream / general as the shape allows
       cudaError_t e1 = launch_conv_gemm(op, ENGINE_TC, 0);
       k_maxdiff<<<296, 256>>>(o1, o2, (long long)no, res);
-      if (op.ws && e1 == cudaSuccess) {  // also exercise the general (per-tap TMA box) kernel on the same problem
-        op.ws = 0;
-        make_tmap_3d(&op.tmA, A, cin, rows, batches, kb, 128, bf16 != 0);
+      // also exercise every lower-priority variant on the same problem: ws -> slab-stream -> general
+      int allow = op.variant == 1 ? 5 : (op.variant == 2 ? 1 : 0);
+      while (allow && e1 == cudaSuccess) {
+        gemm_make_epilogue_maps(&op, allow);
         cudaMemsetAsync(o1, 0xff, no * 4, 0);
         e1 = launch_conv_gemm(op, ENGINE_TC, 0);
         k_maxdiff<<<296, 256>>>(o1, o2, (long long)no, res);
+        allow = op.variant == 2 ? 1 : 0;
       }
       float hres[2] = {0.f, 0.f};
       cudaError_t e3 = cudaMemcpy(hres, res, 8, cudaMemcpyDeviceToHost);
@@ -101,4 +103,102 @@ extern "C" int q3tts_selftest_gemm(int device, int rows, int cin, int n, int nta
   }
   cudaFree(A); cudaFree(W); cudaFree(o1); cudaFree(o2); cudaFree(res);
   return rc;
+}
+
+namespace {
+
+template <typename T>
+__global__ void k_maxdiff16(const T* a, const T* b, long long n, float* out) {
+  float md = 0.f, mr = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float x = Elem<T>::to_f(a[i]), y = Elem<T>::to_f(b[i]);
+    float d = fabsf(x - y);
+    if (!(d == d)) d = INFINITY;
+    md = fmaxf(md, d);
+    mr = fmaxf(mr, fabsf(y));
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    md = fmaxf(md, __shfl_xor_sync(0xffffffffu, md, o));
+    mr = fmaxf(mr, __shfl_xor_sync(0xffffffffu, mr, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(reinterpret_cast<int*>(out), __float_as_int(md));
+    atomicMax(reinterpret_cast<int*>(out) + 1, __float_as_int(mr));
+  }
+}
+
+__global__ void k_fillf(float* p, int n, uint32_t seed, float lo, float hi) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t x = (uint32_t)i * 2654435761u + seed;
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  p[i] = lo + (hi - lo) * ((float)(x & 0xFFFFFF) / 16777216.0f);
+}
+
+template <typename T>
+int run_unit_selftest(int rows, int C, int dil, float* out4) {
+  const bool bf16 = Elem<T>::kBf16;
+  const int batches = 3;
+  const size_t nact = (size_t)batches * rows * C;
+  T *a1 = nullptr, *x = nullptr, *w7 = nullptr, *w1 = nullptr, *a2 = nullptr, *y0 = nullptr, *s0 = nullptr, *y1 = nullptr, *s1 = nullptr;
+  float *fv = nullptr, *res = nullptr;
+  int rc = Q3TTS_OK;
+  if (cudaMalloc((void**)&a1, nact * 2) || cudaMalloc((void**)&x, nact * 2) || cudaMalloc((void**)&a2, nact * 2) || cudaMalloc((void**)&y0, nact * 2) ||
+      cudaMalloc((void**)&s0, nact * 2) || cudaMalloc((void**)&y1, nact * 2) || cudaMalloc((void**)&s1, nact * 2) ||
+      cudaMalloc((void**)&w7, (size_t)7 * C * C * 2) || cudaMalloc((void**)&w1, (size_t)C * C * 2) || cudaMalloc((void**)&fv, (size_t)6 * C * 4) ||
+      cudaMalloc((void**)&res, 16)) {
+    rc = Q3TTS_OOM;
+  } else {
+    k_fill<T><<<592, 256>>>(a1, (long long)nact, 1u, 2.0f);
+    k_fill<T><<<592, 256>>>(x, (long long)nact, 3u, 2.0f);
+    k_fill<T><<<592, 256>>>(w7, (long long)7 * C * C, 7u, 1.5f / sqrtf(7.0f * C));
+    k_fill<T><<<592, 256>>>(w1, (long long)C * C, 9u, 3.0f / sqrtf((float)C));
+    float *b7 = fv, *b1 = fv + C, *s2a = fv + 2 * C, *s2ib = fv + 3 * C, *sna = fv + 4 * C, *snib = fv + 5 * C;
+    k_fillf<<<(C + 127) / 128, 128>>>(b7, C, 11u, -0.1f, 0.1f);
+    k_fillf<<<(C + 127) / 128, 128>>>(b1, C, 12u, -0.1f, 0.1f);
+    k_fillf<<<(C + 127) / 128, 128>>>(s2a, C, 13u, 0.6f, 1.6f);
+    k_fillf<<<(C + 127) / 128, 128>>>(s2ib, C, 14u, 0.5f, 1.5f);
+    k_fillf<<<(C + 127) / 128, 128>>>(sna, C, 15u, 0.6f, 1.6f);
+    k_fillf<<<(C + 127) / 128, 128>>>(snib, C, 16u, 0.5f, 1.5f);
+    cudaMemset(res, 0, 16);
+    cudaMemset(y1, 0xff, nact * 2);
+    cudaMemset(s1, 0xff, nact * 2);
+    // reference: the two SIMT cross-check launches
+    GemmOp g;
+    GemmParams& p = g.p;
+    memset(&p, 0, sizeof(p));
+    p.batches = batches; p.rows = rows; p.rows_valid = rows; p.cin = C; p.ntaps = 7;
+    for (int j = 0; j < 7; ++j) p.tap_off[j] = -(6 - j) * dil;
+    p.n_total = C; p.bn = C; p.kb = C % 64 == 0 ? 64 : 32; p.ncol_mod = C; p.bf16 = bf16;
+    p.out_row_stride = C; p.out_batch_stride = (long long)rows * C;
+    p.a_ptr = a1; p.w_ptr = w7; p.bias = b7; p.out_snake = a2; p.snake_a = s2a; p.snake_ib = s2ib;
+    cudaError_t e1 = launch_conv_gemm(g, ENGINE_SIMT, 0);
+    p.ntaps = 1; p.tap_off[0] = 0; p.a_ptr = a2; p.w_ptr = w1; p.bias = b1; p.res = x; p.out_raw = y0; p.out_snake = s0; p.snake_a = sna; p.snake_ib = snib;
+    cudaError_t e2 = launch_conv_gemm(g, ENGINE_SIMT, 0);
+    // fused unit kernel
+    UnitOp op;
+    memset(&op.p, 0, sizeof(op.p));
+    op.C = C; op.dil = dil; op.bias7 = b7; op.snake2_a = s2a; op.snake2_ib = s2ib;
+    op.p.bf16 = bf16; op.p.bias = b1; op.p.res = x; op.p.out_raw = y1; op.p.out_snake = s1; op.p.snake_a = sna; op.p.snake_ib = snib;
+    const int mk = unit_make(&op, a1, w7, w1, batches, rows);
+    cudaError_t e3 = mk == 0 ? launch_unit(op, 0) : cudaErrorInvalidConfiguration;
+    k_maxdiff16<T><<<296, 256>>>(y1, y0, (long long)nact, res);
+    k_maxdiff16<T><<<296, 256>>>(s1, s0, (long long)nact, res + 2);
+    cudaError_t e4 = cudaMemcpy(out4, res, 16, cudaMemcpyDeviceToHost);
+    if (mk != 0) rc = Q3TTS_BAD_CONFIG;
+    else if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess) rc = Q3TTS_CUDA_ERROR;
+  }
+  cudaFree(a1); cudaFree(x); cudaFree(a2); cudaFree(y0); cudaFree(s0); cudaFree(y1); cudaFree(s1); cudaFree(w7); cudaFree(w1); cudaFree(fv); cudaFree(res);
+  return rc;
+}
+
+}  // namespace
+
+// Fused residual-unit kernel vs the two SIMT cross-check launches (conv7 + Snake, conv1 + residual + Snake).
+// out4 = {max|y - y_ref|, max|y_ref|, max|s - s_ref|, max|s_ref|} over 16-bit outputs.
+extern "C" int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4) {
+  if (rows < 1 || channels < 32 || dilation < 1 || !out4) return Q3TTS_BAD_SHAPE;
+  if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
+  if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
+  return bf16 ? run_unit_selftest<__nv_bfloat16>(rows, channels, dilation, out4) : run_unit_selftest<__half>(rows, channels, dilation, out4);
 }

@@ -55,6 +55,7 @@ struct EpiWarp {
   uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
   int pf_it = 0, pf_item = 0;  // residual prefetch cursor (tile iteration, item)
   bool pf_done = false;
+  int mt_mul = 1, mt_add = 0;  // 128-row block of a scheduler tile: mt * mt_mul + mt_add (fused unit kernel: 2 blocks per tile)
 
   __device__ EpiWarp(const GemmParams& p_, const CUtensorMap* r, const CUtensorMap* a, const CUtensorMap* s, const CUtensorMap* f,
                      uint8_t* eb_, uint64_t* rbar_, TileSched ts_, int lane_, int quad_, int half_, int nsplit_)
@@ -94,7 +95,7 @@ struct EpiWarp {
       ts.decode(tile, nt, mt, b);
       const uint32_t slot = rb_issue % rd;
       mbar_expect_tx(&rbar[slot], kEpiSlot);
-      tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, mt * 128 + quad * 32, b);
+      tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, (mt * mt_mul + mt_add) * 128 + quad * 32, b);
     }
     ++rb_issue;
     pf_item += nsplit;

@@ -1,0 +1,106 @@
+"""`Qwen3TTSModel` — the decode hand-off of qwen_tts/inference/qwen3_tts_model.py ("model wrapper").
+
+The reference wrapper does three things: text templating / validation, `self.model.generate(...)` (talker LM +
+code predictor, talker :2022-2292) and `self.model.speech_tokenizer.decode([...])` with the voice-clone prefix
+handling (model wrapper :612-631, :727, :838).  Only the last one is on the accelerated hot path.  This class keeps
+the three public `generate_*` names and their `(wavs: List[np.ndarray], sample_rate)` return, takes the talker as an
+injected object (the unmodified reference `Qwen3TTSForConditionalGeneration`, or anything with the same
+`generate(...) -> (List[LongTensor (T_i,16)], _)`), and owns the hand-off to the B200 tokenizer.
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+import torch
+
+
+class Qwen3TTSModel:
+    def __init__(self, model, processor=None, generate_defaults: Optional[Dict[str, Any]] = None, speech_tokenizer=None,
+                 tokenize: Optional[Callable[[List[str]], List[torch.Tensor]]] = None):
+        """`model`: talker with `.generate(**kw) -> (codes_list, _)`; its `.speech_tokenizer` is replaced by
+        `speech_tokenizer` (a qwen3_tts_b200.Qwen3TTSTokenizer) when one is given.  `tokenize`: texts -> input ids
+        (the reference builds them with its processor, model wrapper :278-285); optional for pre-tokenised calls."""
+        self.model = model
+        self.processor = processor
+        self.generate_defaults = generate_defaults or {}
+        if speech_tokenizer is not None:
+            self.model.speech_tokenizer = speech_tokenizer
+        self._tokenize = tokenize
+        self.device = getattr(model, "device", None)
+
+    @classmethod
+    def wrap(cls, reference_wrapper, speech_tokenizer) -> "Qwen3TTSModel":
+        """Take a loaded reference `qwen_tts.Qwen3TTSModel` and route its decode through the B200 tokenizer."""
+        tok = getattr(reference_wrapper, "_tokenize_texts", None)
+        inst = cls(reference_wrapper.model, getattr(reference_wrapper, "processor", None),
+                   getattr(reference_wrapper, "generate_defaults", None), speech_tokenizer, tok)
+        inst._ref = reference_wrapper
+        return inst
+
+    # ------------------------------------------------------------------ the hot-path hand-off
+    def decode_talker_codes(self, talker_codes_list: Sequence[torch.Tensor],
+                            ref_code_list: Optional[Sequence[Optional[torch.Tensor]]] = None) -> Tuple[List[np.ndarray], int]:
+        """model wrapper :612-631: prepend each sample's reference codes (voice clone), decode once, then cut the
+        proportional prefix `int(ref_len / total_len * n_samples)` off the front.  Without ref codes it is
+        model wrapper :727 / :838: one `speech_tokenizer.decode([{"audio_codes": c}, ...])`."""
+        codes_for_decode = []
+        for i, codes in enumerate(talker_codes_list):
+            if ref_code_list is not None and ref_code_list[i] is not None:
+                codes_for_decode.append(torch.cat([ref_code_list[i].to(codes.device), codes], dim=0))
+            else:
+                codes_for_decode.append(codes)
+        wavs_all, fs = self.model.speech_tokenizer.decode([{"audio_codes": c} for c in codes_for_decode])
+        wavs_out: List[np.ndarray] = []
+        for i, wav in enumerate(wavs_all):
+            if ref_code_list is not None and ref_code_list[i] is not None:
+                ref_len = int(ref_code_list[i].shape[0])
+                total_len = int(codes_for_decode[i].shape[0])
+                cut = int(ref_len / max(total_len, 1) * wav.shape[0])
+                wavs_out.append(wav[cut:])
+            else:
+                wavs_out.append(wav)
+        return wavs_out, fs
+
+    # ------------------------------------------------------------------ generate_* (talker side injected)
+    def _ids(self, texts: Union[str, List[str]]):
+        texts = texts if isinstance(texts, list) else [texts]
+        if self._tokenize is None:
+            raise RuntimeError("no text front-end: construct with tokenize=... or Qwen3TTSModel.wrap(reference_wrapper, tokenizer)")
+        return self._tokenize(texts)
+
+    def _merged(self, kwargs):
+        out = dict(self.generate_defaults)
+        out.update({k: v for k, v in kwargs.items() if v is not None})
+        return out
+
+    @torch.no_grad()
+    def generate_custom_voice(self, text, speaker=None, language=None, instruct=None, non_streaming_mode: bool = True, **kwargs):
+        """model wrapper :732-839."""
+        if getattr(self, "_ref", None) is not None:
+            return self._ref.generate_custom_voice(text=text, speaker=speaker, language=language, instruct=instruct,
+                                                   non_streaming_mode=non_streaming_mode, **kwargs)
+        codes, _ = self.model.generate(input_ids=self._ids(text), speakers=speaker, languages=language, instruct_ids=instruct,
+                                       non_streaming_mode=non_streaming_mode, **self._merged(kwargs))
+        return self.decode_talker_codes(codes)
+
+    @torch.no_grad()
+    def generate_voice_design(self, text, instruct, language=None, non_streaming_mode: bool = True, **kwargs):
+        """model wrapper :637-728."""
+        if getattr(self, "_ref", None) is not None:
+            return self._ref.generate_voice_design(text=text, instruct=instruct, language=language, non_streaming_mode=non_streaming_mode, **kwargs)
+        codes, _ = self.model.generate(input_ids=self._ids(text), instruct_ids=instruct, languages=language,
+                                       non_streaming_mode=non_streaming_mode, **self._merged(kwargs))
+        return self.decode_talker_codes(codes)
+
+    @torch.no_grad()
+    def generate_voice_clone(self, text, language=None, voice_clone_prompt: Optional[Dict[str, Any]] = None,
+                             non_streaming_mode: bool = False, **kwargs):
+        """model wrapper :470-633.  `voice_clone_prompt["ref_code"]` (list of LongTensor (T_ref,16) or None) drives the prefix cut."""
+        if getattr(self, "_ref", None) is not None:
+            return self._ref.generate_voice_clone(text=text, language=language, voice_clone_prompt=voice_clone_prompt,
+                                                  non_streaming_mode=non_streaming_mode, **kwargs)
+        prompt = voice_clone_prompt or {}
+        codes, _ = self.model.generate(input_ids=self._ids(text), voice_clone_prompt=prompt, languages=language,
+                                       non_streaming_mode=non_streaming_mode, **self._merged(kwargs))
+        return self.decode_talker_codes(codes, prompt.get("ref_code", None))
