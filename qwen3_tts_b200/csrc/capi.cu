@@ -113,6 +113,7 @@ int q3tts_reserve(q3tts_handle* h, int max_frames_per_launch) {
 int q3tts_set_engine(q3tts_handle* h, int engine) {
   if (!h) return Q3TTS_BAD_CONFIG;
   if (engine != Q3TTS_ENGINE_TC && engine != Q3TTS_ENGINE_SIMT) return h->e.fail(Q3TTS_BAD_CONFIG, "unknown engine");
+  if (h->e.engine != engine) h->e.plans.clear();  // fused ops are TC-only: plans depend on the engine
   h->e.engine = engine;
   return Q3TTS_OK;
 }

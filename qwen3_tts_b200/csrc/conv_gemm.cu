@@ -120,7 +120,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m0 = mt * BM, n0 = nt * p.bn;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
-            mbar_wait(&bars->empty[s], ph ^ 1);
+            mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
             mbar_expect_tx(&bars->full[s], stage_bytes);
             tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.tap_off[tap], b);
@@ -140,11 +140,11 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int s = 0; uint32_t ph = 0; int it = 0;
       for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
-        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         for (int ks = 0; ks < ksteps; ++ks) {
-          mbar_wait(&bars->full[s], ph);
+          mbar_wait_backoff(&bars->full[s], ph);
           tc_fence_after();
           const uint32_t a = a_lo0 + (uint32_t)s * st_off, b = a + b_off;
           if (!(p.dbg & 2)) {
@@ -216,7 +216,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
         int nt, mt, b;
         ts.decode(tile, nt, mt, b);
-        mbar_wait(&bars->empty[s], ph ^ 1);
+        mbar_wait_backoff(&bars->empty[s], ph ^ 1);
         mbar_expect_tx(&bars->full[s], slab_bytes);
         for (int kb = 0; kb < nkb; ++kb)
           tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], kb * KB, mt * BM - halo, b);
@@ -236,12 +236,12 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           bars->b_tab[kb * p.ntaps + tap] = umma_desc_lo(smem_u32(wsm) + (uint32_t)(tap * nkb + kb) * wsub);
         }
       const bool k4 = KB == 64;
-      mbar_wait(&bars->w_full, 0);
+      mbar_wait_backoff(&bars->w_full, 0);
       int s = 0; uint32_t ph = 0; int it = 0;
       for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
-        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
-        mbar_wait(&bars->full[s], ph);
+        mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        mbar_wait_backoff(&bars->full[s], ph);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         const uint32_t slab_lo = umma_desc_lo(smem_u32(slabs + (size_t)s * slab_bytes));
@@ -315,12 +315,12 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         ts.decode(tile, nt, mt, b);
         const int n0 = nt * p.bn;
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->sempty[ss], sph ^ 1);
+          mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
           mbar_expect_tx(&bars->sfull[ss], ssub);
           tma_load_3d(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * BM - slab_lo, b);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
-            mbar_wait(&bars->empty[s], ph ^ 1);
+            mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             mbar_expect_tx(&bars->full[s], wsub);
             tma_load_3d(wst + (size_t)s * wsub, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
@@ -340,14 +340,14 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int s = 0, ss = 0; uint32_t ph = 0, sph = 0; int it = 0;
       for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
         const int buf = it & 1;
-        mbar_wait(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->sfull[ss], sph);
+          mbar_wait_backoff(&bars->sfull[ss], sph);
           const uint32_t slab_lo_desc = s_lo0 + (uint32_t)ss * s_off;
           for (int tap = 0; tap < p.ntaps; ++tap) {
-            mbar_wait(&bars->full[s], ph);
+            mbar_wait_backoff(&bars->full[s], ph);
             tc_fence_after();
             const uint32_t a = slab_lo_desc + bars->a_tab[tap], b = w_lo0 + (uint32_t)s * w_off;
             if (!(p.dbg & 2)) {

@@ -47,6 +47,8 @@ struct UnitOp {
   int nslabs = 0, nstages = 0;        // ring depths
   int enabled = 0;
 };
+// Shape test only (no device work): true when unit_make can fuse C channels.
+bool unit_fusable(int C);
 // Fills the maps and ring sizes; returns 0 when the shape can be fused (enabled = 1), 1 when it cannot, < 0 on error.
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows);
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream);

@@ -41,11 +41,12 @@ struct UpsampleW {
 struct UnitW { ConvW conv7, conv1; SnakeP act1, act2; };
 struct BlockW { SnakeP act0; ConvW tconv; UnitW unit[3]; int stride = 0, cin = 0, cout = 0; };
 
-enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL };
+enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT };
 
 struct Op {
   OpType type = OP_GEMM;
   GemmOp g;
+  UnitOp u;  // OP_UNIT: fused residual unit (conv7 -> Snake -> conv1 + residual)
   const void* in = nullptr;
   void* out = nullptr;
   const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;

@@ -173,6 +173,33 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     L = Lo;
     for (int j = 0; j < 3; ++j) {
       const UnitW& U = K.unit[j];
+      const SnakeP& nx = j < 2 ? K.unit[j + 1].act1 : (i + 1 < e->blocks.size() ? e->blocks[i + 1].act0 : e->tail_act);
+      const std::string t = "decoder." + std::to_string(i + 1) + ".block." + std::to_string(j + 2);
+      {
+        // fused unit: one launch, the Snake'd conv7 output stays in tensor memory (C <= 192); x is updated in place
+        UnitOp u;
+        memset(&u.p, 0, sizeof(u.p));
+        u.C = K.cout; u.dil = -U.conv7.tap_off[0] / 6;
+        u.bias7 = U.conv7.bias; u.snake2_a = U.act2.a; u.snake2_ib = U.act2.ib;
+        u.p.bf16 = e->bf16 ? 1 : 0; u.p.bias = U.conv1.bias; u.p.res = R[iy]; u.p.out_raw = R[iy]; u.p.out_snake = R[ifree];
+        u.p.snake_a = nx.a; u.p.snake_ib = nx.ib;
+        u.p.w_ptr = U.conv7.w;
+        const bool shape_ok = e->engine == ENGINE_TC && U.conv7.taps == 7 && U.conv1.taps == 1 && unit_fusable(K.cout);
+        int mk = 1;
+        if (shape_ok) {
+          if (dry) mk = 0;
+          else mk = unit_make(&u, R[ia], U.conv7.w, U.conv1.w, B, L);
+          if (mk < 0) b.rc = e->fail(Q3TTS_CUDA_ERROR, "fused unit tensor maps failed");
+        }
+        if (mk == 0) {
+          plan->ops.emplace_back();
+          Op& op = plan->ops.back();
+          op.type = OP_UNIT; op.u = u; op.B = B; op.L = L; op.C = K.cout;
+          b.tag(op, t.c_str(), R[iy], false, K.cout, L);
+          std::swap(ia, ifree);
+          continue;
+        }
+      }
       {
         Op& op = b.gemm(U.conv7, R[ia], B, L, L);
         op.g.p.out_snake = R[ifree]; op.g.p.snake_a = U.act2.a; op.g.p.snake_ib = U.act2.ib;
@@ -181,9 +208,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
       {
         Op& op = b.gemm(U.conv1, R[ia], B, L, L);
         op.g.p.res = R[iy]; op.g.p.out_raw = R[iy];
-        const SnakeP& nx = j < 2 ? K.unit[j + 1].act1 : (i + 1 < e->blocks.size() ? e->blocks[i + 1].act0 : e->tail_act);
         op.g.p.out_snake = R[ifree]; op.g.p.snake_a = nx.a; op.g.p.snake_ib = nx.ib;
-        const std::string t = "decoder." + std::to_string(i + 1) + ".block." + std::to_string(j + 2);
         b.tag(op, t.c_str(), R[iy], false, K.cout, L);
         std::swap(ia, ifree);
       }
@@ -255,6 +280,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
         err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s);
         break;
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
+      case OP_UNIT: err = launch_unit(op.u, s); break;
       case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s); break;
       case OP_ATTN:
         err = sliding_attention(op.in, e->rope_cos, e->rope_sin, op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->bf16, s);
@@ -283,6 +309,11 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
         if (p.out_snake) by += 2.0 * rows * outw;
         if (p.out_f32) by += 4.0 * rows * outw;
         if (p.res) by += (p.res_f32 ? 4.0 : 2.0) * rows * outw;
+      } else if (op.type == OP_UNIT) {
+        const double rows = (double)op.B * op.L, C = op.C;
+        dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
+        fl = 2.0 * rows * C * C * 8.0;
+        by = 2.0 * (4.0 * rows * C + 8.0 * C * C);  // a1 + x in, y + snake(y) out, weights once
       }
       e->prof_type.push_back((int)op.type);
       e->prof_flops.push_back(fl);

@@ -53,6 +53,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (++spins > (1u << 24)) __trap();
   }
 }
+// Same wait for the single-thread producer / MMA roles: after a few failed polls the thread sleeps between polls so that
+// its spin loop stops competing with the epilogue warps of the same SM sub-partition for issue slots (ncu: the two
+// spinning threads issued 22 % of all instructions of an epilogue-bound launch).
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > 4) __nanosleep(64);
+    if (spins > (1u << 22)) __trap();
+  }
+}
 
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* map) {

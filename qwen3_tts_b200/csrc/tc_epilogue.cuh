@@ -34,10 +34,12 @@ __device__ __forceinline__ uint32_t slot_off(int lane, int c) { return (uint32_t
 
 struct TileSched {
   int m_tiles, n_tiles, total_tiles;
-  __device__ __forceinline__ void decode(long long tile, int& nt, int& mt, int& b) const {
-    nt = (int)(tile % n_tiles);
-    mt = (int)((tile / n_tiles) % m_tiles);
-    b = (int)(tile / ((long long)n_tiles * m_tiles));
+  __device__ __forceinline__ void decode(int tile, int& nt, int& mt, int& b) const {  // 32-bit: total_tiles < 2^31
+    int q = tile;
+    nt = 0;
+    if (n_tiles > 1) { q = tile / n_tiles; nt = tile - q * n_tiles; }
+    b = q / m_tiles;
+    mt = q - b * m_tiles;
   }
 };
 
@@ -50,7 +52,8 @@ struct EpiWarp {
   TileSched ts;
   int lane, quad, half, nsplit;
   bool has_res, rf32, glu, tail, of32, o16;
-  int units, item_units, nitems, rd;
+  int units, item_units, nitems, rd, rd_shift;
+  bool wraps;  // a tile's columns can wrap around ncol_mod (transposed convs: n_total = stride * cout)
   int s_raw, s_snake, s_f32;  // first slot of each output ring
   uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
   int pf_it = 0, pf_item = 0;  // residual prefetch cursor (tile iteration, item)
@@ -69,7 +72,9 @@ struct EpiWarp {
     units = p.bn >> 4;
     item_units = glu ? 4 : ((of32 || (has_res && rf32) || tail) ? 1 : 2);
     nitems = units / item_units;
-    rd = epi_res_depth(p);
+    rd = epi_res_depth(p);  // 2, 4 or 8
+    rd_shift = rd == 8 ? 3 : (rd == 4 ? 2 : 1);
+    wraps = p.ncol_mod != p.n_total;
     int nslot = rd;
     s_raw = nslot;
     if (glu || p.out_raw) nslot += 2;
@@ -79,21 +84,21 @@ struct EpiWarp {
   }
 
   // first item this warp owns in tile iteration `it` (the two warps of a quadrant alternate so odd item counts balance)
-  __device__ __forceinline__ int first_item(int it) const { return (half + nsplit - (it % nsplit)) % nsplit; }
+  __device__ __forceinline__ int first_item(int it) const { return (half - it) & (nsplit - 1); }  // nsplit is 1 or 2
 
   __device__ __forceinline__ void prefetch_one() {  // warp-uniform control flow; lane 0 issues
     if (pf_done) return;
     while (pf_item >= nitems) {
       ++pf_it;
       pf_item = first_item(pf_it);
-      if ((long long)blockIdx.x + (long long)pf_it * gridDim.x >= ts.total_tiles) { pf_done = true; return; }
+      if ((int)blockIdx.x + pf_it * (int)gridDim.x >= ts.total_tiles) { pf_done = true; return; }
     }
-    const long long tile = (long long)blockIdx.x + (long long)pf_it * gridDim.x;
+    const int tile = (int)blockIdx.x + pf_it * (int)gridDim.x;
     if (tile >= ts.total_tiles) { pf_done = true; return; }
     if (lane == 0) {
       int nt, mt, b;
       ts.decode(tile, nt, mt, b);
-      const uint32_t slot = rb_issue % rd;
+      const uint32_t slot = rb_issue & (rd - 1);
       mbar_expect_tx(&rbar[slot], kEpiSlot);
       tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, (mt * mt_mul + mt_add) * 128 + quad * 32, b);
     }
@@ -173,14 +178,14 @@ struct EpiWarp {
   __device__ __forceinline__ void item_pair(uint32_t t0, int nt, int row0, int b, int item) {
     const int u0 = item * 2;
     const int n0 = nt * p.bn + u0 * 16;
-    const int c0 = n0 % p.ncol_mod;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
+    const int c0 = wraps ? n0 % p.ncol_mod : n0;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
     uint32_t ra[16], rb[16];
     tmem_ld16(t0 + u0 * 16, ra);
     tmem_ld16(t0 + u0 * 16 + 16, rb);
     float rsa[16], rsb[16];
     if (has_res) {
-      const uint32_t slot = rb_cons % rd;
-      mbar_wait(&rbar[slot], (rb_cons / rd) & 1);
+      const uint32_t slot = rb_cons & (rd - 1);
+      mbar_wait(&rbar[slot], (rb_cons >> rd_shift) & 1);
       const uint8_t* rbuf = eb + slot * kEpiSlot;
       load_res16(rbuf, 0, rsa);
       load_res16(rbuf, 2, rsb);
@@ -223,13 +228,13 @@ struct EpiWarp {
   // ---- fp32 flow: 16 accumulator columns; residual and/or output are fp32 (transformer residual stream)
   __device__ __forceinline__ void item_f32(uint32_t t0, int nt, int row0, int b, int item) {
     const int n0 = nt * p.bn + item * 16;
-    const int c0 = n0 % p.ncol_mod;
+    const int c0 = wraps ? n0 % p.ncol_mod : n0;
     uint32_t r[16];
     tmem_ld16(t0 + item * 16, r);
     float rs[16];
     if (has_res) {
-      const uint32_t slot = rb_cons % rd;
-      mbar_wait(&rbar[slot], (rb_cons / rd) & 1);
+      const uint32_t slot = rb_cons & (rd - 1);
+      mbar_wait(&rbar[slot], (rb_cons >> rd_shift) & 1);
       const uint8_t* rbuf = eb + slot * kEpiSlot;
       if (rf32) {
 #pragma unroll

@@ -93,20 +93,20 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         int nt, mt, b;
         ts.decode(tile, nt, mt, b);
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->sempty[ss], sph ^ 1);
+          mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
           mbar_expect_tx(&bars->sfull[ss], ssub);
           for (int bx = 0; bx < u.nbox; ++bx)
             tma_load_3d(slabs + (size_t)ss * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss], kb * KB, mt * TM - halo + bx * boxrows, b);
           if (++ss == u.nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < 7; ++tap) {
-            mbar_wait(&bars->wempty[ws], wph ^ 1);
+            mbar_wait_backoff(&bars->wempty[ws], wph ^ 1);
             mbar_expect_tx(&bars->wfull[ws], wsub);
             tma_load_3d(wst + (size_t)ws * wsub, &tmW7, &bars->wfull[ws], kb * KB, 0, tap);
             if (++ws == u.nstages) { ws = 0; wph ^= 1; }
           }
         }
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->wempty[ws], wph ^ 1);
+          mbar_wait_backoff(&bars->wempty[ws], wph ^ 1);
           mbar_expect_tx(&bars->wfull[ws], wsub);
           tma_load_3d(wst + (size_t)ws * wsub, &tmW1, &bars->wfull[ws], kb * KB, 0, 0);
           if (++ws == u.nstages) { ws = 0; wph ^= 1; }
@@ -125,10 +125,10 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
         // ---- MMA1: dilated conv7 into acc1 (acc1 is free: a2_full of the previous tile was waited on before its MMA2)
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->sfull[ss], sph);
+          mbar_wait_backoff(&bars->sfull[ss], sph);
           const uint32_t slab = s_lo0 + (uint32_t)ss * s_off;
           for (int tap = 0; tap < 7; ++tap) {
-            mbar_wait(&bars->wfull[ws], wph);
+            mbar_wait_backoff(&bars->wfull[ws], wph);
             tc_fence_after();
             const uint32_t b = w_lo0 + (uint32_t)ws * w_off;
             for (int ms = 0; ms < MS; ++ms) {
@@ -145,11 +145,11 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         umma_commit(&bars->acc1_full);
         // ---- MMA2: 1x1 conv, A = Snake'd conv7 output packed in tensor memory by epilogue phase 1
-        mbar_wait(&bars->a2_full, it & 1);
-        mbar_wait(&bars->acc2_empty, (it & 1) ^ 1);
+        mbar_wait_backoff(&bars->a2_full, it & 1);
+        mbar_wait_backoff(&bars->acc2_empty, (it & 1) ^ 1);
         tc_fence_after();
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&bars->wfull[ws], wph);
+          mbar_wait_backoff(&bars->wfull[ws], wph);
           tc_fence_after();
           const uint32_t b = w_lo0 + (uint32_t)ws * w_off;
           for (int ms = 0; ms < MS; ++ms) {
@@ -236,6 +236,13 @@ static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
   return (size_t)op.nslabs * op.srows * span + (size_t)op.nstages * op.C * span + (size_t)8 * epi_slots_per_warp(op.p) * kEpiSlot +
          sizeof(UnitBarriers) + 1024;
+}
+
+bool unit_fusable(int C) {
+  if (getenv("Q3TTS_NO_FUSE")) return false;
+  if (C % 32 || C > 256 || C < 32) return false;
+  const int ms = C <= 96 ? 2 : 1;
+  return 5 * ms * C / 2 <= 512;
 }
 
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows) {

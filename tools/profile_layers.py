@@ -23,7 +23,7 @@ dec.set_profile(True)
 dec(codes)
 prof = dec.get_profile()
 dec.set_profile(False)
-names = {0: "rvq", 1: "gemm", 2: "rmsnorm", 3: "attn", 4: "dwln", 5: "tail"}
+names = {0: "rvq", 1: "gemm", 2: "rmsnorm", 3: "attn", 4: "dwln", 5: "tail", 6: "unit"}
 tot = sum(p[1] for p in prof)
 print(f"B={B} T={T} mode={mode} total {tot:.3f} ms over {len(prof)} launches")
 print(f"{'#':>3} {'op':8} {'rows':>9} {'N':>5} {'Cin':>5} {'k':>2} {'ms':>8} {'%':>5} {'TFLOP/s':>8} {'minGB/s':>8}")
