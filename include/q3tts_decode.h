@@ -130,6 +130,17 @@ int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dil
  * Returns Q3TTS_BAD_CONFIG when the channel count cannot be fused. */
 int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4);
 
+/* Debug timeline of the fused unit kernel (env Q3TTS_DBG bit 5): clock64 stamps [16 tiles][16 events] of CTA 0. */
+int q3tts_unit_trace(long long* out256);
+
+/* tcgen05.mma issue-rate microbenchmark (design evidence): SM cycles per MMA (M = 128, K = 16, fp16) for an N, operand form
+ * (0 = A,B in shared memory, 1 = A in tensor memory), swizzle span (64 / 128 bytes), A row shift, accumulator count, and a tcgen05.commit / mbarrier wait every k groups of 8 MMAs. */
+int q3tts_bench_mma(int device, int n, int span, int a_row_shift, int form, int nacc, int commit_every, int wait_every, float* clk_per_mma);
+
+/* TMA box-shape microbenchmark (design evidence, DESIGN.md "Epilogue boxes"): aggregate GB/s of `warps` warps per SM moving
+ * [box_rows x box_cols] 16-bit boxes between shared memory and a channels-last [rows][C] tensor. */
+int q3tts_bench_tma(int device, int C, int box_cols, int box_rows, int is_load, int warps, int iters, float* gbps);
+
 #ifdef __cplusplus
 }
 #endif

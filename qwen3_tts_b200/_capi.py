@@ -61,6 +61,9 @@ EXPORTS = {
     "q3tts_launch_count": (C.c_int64, [C.c_void_p]),
     "q3tts_set_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "q3tts_get_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
+    "q3tts_unit_trace": (C.c_int, [C.POINTER(C.c_longlong)]),
+    "q3tts_bench_mma": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
+    "q3tts_bench_tma": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "q3tts_selftest_unit": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "q3tts_selftest_gemm": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
 }

@@ -45,6 +45,8 @@ struct UnitOp {
   int C = 0, dil = 1, ms = 1;         // ms: 128-row sub-tiles per CTA tile (2 for C <= 96)
   int srows = 0, nbox = 1;            // slab rows per K block (128*ms + 6*dil rounded up), TMA boxes per slab
   int nslabs = 0, nstages = 0;        // ring depths
+  int ks = 1, nbuf = 1;               // K blocks per slab / weight stage; TMEM stages
+  int variant = 0;                    // compiled instance (unit_kernel.cu: 0 = C 96, 1 / 2 = C 192 with 4 / 3 weight stages)
   int enabled = 0;
 };
 // Shape test only (no device work): true when unit_make can fuse C channels.
@@ -52,6 +54,7 @@ bool unit_fusable(int C);
 // Fills the maps and ring sizes; returns 0 when the shape can be fused (enabled = 1), 1 when it cannot, < 0 on error.
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows);
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream);
+int unit_trace_read(long long* out256);
 
 // Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths).
 // `allow` = bit mask of kernel variants that may be chosen (bit 0 general, bit 1 weight-stationary, bit 2 slab-stream); also (re)builds tmA.

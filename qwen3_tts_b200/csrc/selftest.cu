@@ -1,5 +1,6 @@
 // Device-side self-test of the tcgen05 implicit-GEMM kernel against the SIMT cross-check kernel.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -179,6 +180,7 @@ int run_unit_selftest(int rows, int C, int dil, float* out4) {
     UnitOp op;
     memset(&op.p, 0, sizeof(op.p));
     op.C = C; op.dil = dil; op.bias7 = b7; op.snake2_a = s2a; op.snake2_ib = s2ib;
+    { const char* d = getenv("Q3TTS_DBG"); op.p.dbg = d ? atoi(d) : 0; }
     op.p.bf16 = bf16; op.p.bias = b1; op.p.res = x; op.p.out_raw = y1; op.p.out_snake = s1; op.p.snake_a = sna; op.p.snake_ib = snib;
     const int mk = unit_make(&op, a1, w7, w1, batches, rows);
     cudaError_t e3 = mk == 0 ? launch_unit(op, 0) : cudaErrorInvalidConfiguration;
@@ -201,4 +203,173 @@ extern "C" int q3tts_selftest_unit(int device, int rows, int channels, int dilat
   if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
   if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
   return bf16 ? run_unit_selftest<__nv_bfloat16>(rows, channels, dilation, out4) : run_unit_selftest<__half>(rows, channels, dilation, out4);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// TMA box-shape microbenchmark: every warp of every CTA moves [box_rows x box_cols] 16-bit boxes between its shared-memory
+// slot and a channels-last tensor [rows][C] (stores, or loads with an mbarrier), 2 slots in flight per warp.
+// Reports aggregate GB/s.  Used to pick the epilogue box shape (DESIGN.md "Epilogue boxes").
+namespace {
+
+__global__ void __launch_bounds__(512, 1) k_tma_bench(const __grid_constant__ CUtensorMap tm, int C, int box_cols, int box_rows, int rows_total,
+                                                       int is_load, int iters) {
+  extern __shared__ __align__(1024) uint8_t sm_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(sm_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t bars[16][2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const uint32_t box_bytes = (uint32_t)box_cols * box_rows * 2;
+  const uint32_t slot_bytes = (box_bytes + 1023) & ~1023u;
+  uint8_t* my = sm + (size_t)warp * 2 * slot_bytes;
+  if (lane == 0) { mbar_init(&bars[warp][0], 1); mbar_init(&bars[warp][1], 1); fence_barrier_init(); }
+  for (uint32_t i = lane; i < 2 * slot_bytes / 4; i += 32) reinterpret_cast<uint32_t*>(my)[i] = i;
+  fence_proxy_async_smem();
+  __syncthreads();
+  const int col_boxes = C / box_cols;
+  const int row_boxes = rows_total / box_rows;
+  long long g = ((long long)blockIdx.x * nwarps + warp);
+  const long long stride = (long long)gridDim.x * nwarps;
+  if (lane == 0) {
+    for (int i = 0; i < iters; ++i, g += stride) {
+      const int cb = (int)(g % col_boxes), rb = (int)((g / col_boxes) % row_boxes);
+      const int slot = i & 1;
+      if (is_load) {
+        if (i >= 2) mbar_wait(&bars[warp][slot], ((i >> 1) - 1) & 1);
+        mbar_expect_tx(&bars[warp][slot], box_bytes);
+        tma_load_3d(my + slot * slot_bytes, &tm, &bars[warp][slot], cb * box_cols, rb * box_rows, 0);
+      } else {
+        tma_store_wait_read<1>();
+        tma_store_3d(&tm, my + slot * slot_bytes, cb * box_cols, rb * box_rows, 0);
+        tma_store_commit();
+      }
+    }
+    if (is_load) {
+      for (int i = iters > 2 ? iters - 2 : 0; i < iters; ++i) mbar_wait(&bars[warp][i & 1], (i >> 1) & 1);
+    } else {
+      tma_store_wait<0>();
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int q3tts_bench_tma(int device, int C, int box_cols, int box_rows, int is_load, int warps, int iters, float* gbps) {
+  if (!gbps || C < 16 || box_cols < 8 || C % box_cols || box_rows < 1 || box_rows > 256 || warps < 1 || warps > 16) return Q3TTS_BAD_SHAPE;
+  if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
+  if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
+  const int rows_total = 1 << 22;
+  void* buf = nullptr;
+  if (cudaMalloc(&buf, (size_t)rows_total * C * 2) != cudaSuccess) return Q3TTS_OOM;
+  cudaMemset(buf, 0, (size_t)rows_total * C * 2);
+  CUtensorMap tm;
+  int rc = Q3TTS_OK;
+  if (make_tmap_3d_strided(&tm, buf, 0, (uint64_t)C, (uint64_t)rows_total, 1, (uint64_t)C, (uint64_t)rows_total * C, (uint32_t)box_cols, (uint32_t)box_rows)) {
+    rc = Q3TTS_CUDA_ERROR;
+  } else {
+    const uint32_t slot = ((uint32_t)box_cols * box_rows * 2 + 1023) & ~1023u;
+    const size_t smem = (size_t)warps * 2 * slot + 1024;
+    if (smem + 1024 > (size_t)gemm_smem_optin() ||
+        cudaFuncSetAttribute(k_tma_bench, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) rc = Q3TTS_BAD_SHAPE;
+    else {
+      cudaEvent_t e0, e1;
+      cudaEventCreate(&e0); cudaEventCreate(&e1);
+      k_tma_bench<<<gemm_num_sms(), warps * 32, smem>>>(tm, C, box_cols, box_rows, rows_total, is_load, 64);
+      cudaEventRecord(e0);
+      k_tma_bench<<<gemm_num_sms(), warps * 32, smem>>>(tm, C, box_cols, box_rows, rows_total, is_load, iters);
+      cudaEventRecord(e1);
+      if (cudaGetLastError() != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) rc = Q3TTS_CUDA_ERROR;
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, e0, e1);
+      *gbps = (float)((double)gemm_num_sms() * warps * iters * box_cols * box_rows * 2.0 / (ms * 1e6));
+      cudaEventDestroy(e0); cudaEventDestroy(e1);
+    }
+  }
+  cudaFree(buf);
+  return rc;
+}
+
+extern "C" int q3tts_unit_trace(long long* out256) { return unit_trace_read(out256); }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// tcgen05.mma issue-rate microbenchmark: one CTA per SM, one thread issues `iters` x 8 MMAs (M = 128, K = 16, fp16) on
+// whatever bytes are in shared memory (results are never read) and reports cycles per MMA.
+//   form 0: A and B from shared memory (SWIZZLE_128B or 64B K-major descriptors), a_row_shift = rows the A start is shifted
+//   form 1: A from tensor memory, B from shared memory
+namespace {
+
+__global__ void __launch_bounds__(128, 1) k_mma_bench(int n, int span, int a_row_shift, int form, int iters, int nacc, int commit_every, int wait_every,
+                                                       long long* out) {
+  extern __shared__ __align__(1024) uint8_t sm_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(sm_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ __align__(8) uint64_t bar, bar2, bar3;
+  __shared__ uint32_t tbase;
+  for (uint32_t i = threadIdx.x; i < 96 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(sm)[i] = 0;
+  if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&bar2, 1); mbar_init(&bar3, 1); fence_barrier_init(); }
+  if (threadIdx.x < 32) { tmem_alloc(&tbase, 512); tmem_relinquish(); }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  // `wait_every` doubles as the number of issuing warps when commit_every < 0 (multi-issuer experiment)
+  const int issuers = commit_every < 0 ? wait_every : 1;
+  __shared__ __align__(8) uint64_t ibar[4];
+  if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) mbar_init(&ibar[i], 1); fence_barrier_init(); }
+  __syncthreads();
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0 && w < issuers) {
+    const uint32_t idesc = umma_idesc(128, n, false);
+    const uint32_t hi = umma_desc_hi(span);
+    const uint32_t a0 = umma_desc_lo(smem_u32(sm) + (uint32_t)a_row_shift * span + (uint32_t)w * 8192);
+    const uint32_t b0 = umma_desc_lo(smem_u32(sm) + 48 * 1024 + (uint32_t)w * 8192);
+    const uint32_t d0 = tbase + (uint32_t)(w * n);
+    const long long t0 = clock64();
+    if (commit_every < 0) {
+      for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) umma_f16_lohi(d0, a0 + 2 * (j & 3), b0 + 2 * (j & 3), hi, idesc, 1);
+      }
+    } else {
+      // per group of 8 MMAs: bit 0 of commit_every = tcgen05.commit, bit 1 = mbarrier wait that passes at once, bit 2 = tcgen05.fence::after_thread_sync
+      for (int i = 0; i < iters; ++i) {
+        if (form == 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) umma_f16_lohi(d0, a0 + 2 * (j & 3), b0 + 2 * (j & 3), hi, idesc, 1);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) umma_f16_ts(d0, tbase + 480 + 8 * (j & 3), b0 + 2 * (j & 3), hi, idesc, 1);
+        }
+        if (commit_every & 1) umma_commit(&bar2);
+        if (commit_every & 2) mbar_wait(&bar3, 1);  // bar3 never completes a phase: parity 1 passes at once
+        if (commit_every & 4) tc_fence_after();
+      }
+    }
+    umma_commit(&ibar[w]);
+    mbar_wait(&ibar[w], 0);
+    const long long t1 = clock64();
+    if (blockIdx.x == 0 && w == 0) out[0] = t1 - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) { tc_fence_after(); tmem_dealloc(tbase, 512); }
+}
+
+}  // namespace
+
+extern "C" int q3tts_bench_mma(int device, int n, int span, int a_row_shift, int form, int nacc, int commit_every, int wait_every, float* clk_per_mma) {
+  if (!clk_per_mma || n < 16 || n > 256 || n % 16 || (span != 64 && span != 128) || nacc < 1 || nacc * n > 480 || (commit_every < 0 && (wait_every < 1 || wait_every > 4 || wait_every * n > 480)))
+    return Q3TTS_BAD_SHAPE;
+  if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
+  if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
+  long long* out = nullptr;
+  if (cudaMalloc((void**)&out, 8) != cudaSuccess) return Q3TTS_OOM;
+  const int iters = 2000;
+  const size_t smem = 97 * 1024 + 1024;
+  cudaFuncSetAttribute(k_mma_bench, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  k_mma_bench<<<gemm_num_sms(), 128, smem>>>(n, span, a_row_shift, form, 50, nacc, commit_every, wait_every, out);
+  k_mma_bench<<<gemm_num_sms(), 128, smem>>>(n, span, a_row_shift, form, iters, nacc, commit_every, wait_every, out);
+  long long h = 0;
+  int rc = Q3TTS_OK;
+  if (cudaGetLastError() != cudaSuccess || cudaMemcpy(&h, out, 8, cudaMemcpyDeviceToHost) != cudaSuccess) rc = Q3TTS_CUDA_ERROR;
+  *clk_per_mma = (float)((double)h / (8.0 * iters));
+  cudaFree(out);
+  return rc;
 }

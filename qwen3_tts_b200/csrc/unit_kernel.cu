@@ -3,225 +3,418 @@
 // a1 = snake1(x) and x arrive as two 16-bit channels-last tensors; y and the next layer's Snake'd copy leave the same way.
 //
 // Warp roles (one CTA per SM, persistent over tiles of 128*MS rows of one batch item):
-//   warp 0      TMA producer: per K block one a1 slab (tile rows + 6*dil halo rows), then the 7 tap weight tiles;
-//               after the conv7 operands the K blocks of W1.  Two rings: slabs and weight tiles.
-//   warp 1      TMEM allocator + single-thread MMA issuer:
-//                 MMA1  acc1[ms] += slab(rows shifted by the tap) . W7[tap]      (A and B in shared memory)
-//                 MMA2  acc2[ms]  = A2[ms] . W1                                  (A in TENSOR MEMORY, B in shared memory)
-//   warps 2..9  epilogue, two phases per tile:
-//                 phase 1  acc1 -> + b7 -> SnakeBeta -> 16-bit pairs -> tcgen05.st into A2 (never leaves the SM)
-//                 phase 2  acc2 -> + b1 + residual x (TMA ring) -> y (TMA store) and snake_next(y) (TMA store)
-// TMEM columns: MS * (C fp32 acc1 + C fp32 acc2 + C/2 packed A2) = 2.5 * MS * C <= 512  (C = 96: MS = 2; C = 192: MS = 1).
-// Accumulators are single-buffered, so the tensor pipe idles during phase 1 of every tile; phase 2 overlaps the next
-// tile's MMA1.  The layer is bound by HBM / epilogue ALU at C = 96 and is ~88 % tensor-busy at C = 192.
+//   warp 0        TMA producer: activation slabs (tile rows + 6*dil halo rows) and weight stages (one tap of W7, or W1),
+//                 each covering KS K blocks; two rings.
+//   warp 1        TMEM allocator + single-thread MMA issuer:
+//                   MMA1  acc1[ms] += slab(rows shifted by the tap) . W7[tap]    (A and B in shared memory)
+//                   MMA2  acc2[ms]  = A2[ms] . W1                                (A in TENSOR MEMORY, B in shared memory)
+//   warps 2..9    phase 1: acc1 -> + b7 -> SnakeBeta -> 16-bit pairs -> tcgen05.st into A2 (never leaves the SM)
+//   warps 10..17  phase 2: acc2 -> + b1 + residual x (TMA ring) -> y (TMA store) and snake_next(y) (TMA store)
+// TMEM: one stage = MS * (C fp32 acc1 + C fp32 acc2 + C/2 packed A2) = 2.5 * MS * C columns.
+//   C = 96:  MS = 1, TWO stages (2 x 256 columns): MMA1 of tile i+1 runs while phase 1 of tile i converts, so the tensor
+//            pipe never waits for the epilogue; the two warp groups of each phase alternate tiles (group = stage).
+//   C = 192: MS = 1, one stage (480 columns): the tensor pipe idles during phase 1; the two warp groups split the columns.
+// Measured (tools/mma_bench.py): a tcgen05.mma with M = 128, K = 16 occupies the pipe for >= 117.5 cycles whatever N is,
+// so a C = 96 layer cannot exceed 41 % of the tensor peak in this operand arrangement; the kernel is built to sit on
+// that floor (DESIGN.md "Fused residual unit").
 #include "conv_gemm.h"
 #include "tc_epilogue.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 namespace q3 {
 
 static constexpr int U_BM = 128;
-static constexpr int kUnitThreads = 64 + 32 * 8;
+static constexpr int kP1Warps = 8, kP2Warps = 8;
+static constexpr int kUnitThreads = 64 + 32 * (kP1Warps + kP2Warps);
 static constexpr int kUMaxSlabs = 6;
 static constexpr int kUMaxStages = 12;
+static constexpr int kURes = 2;                      // residual ring depth per phase-2 warp
+static constexpr int kUSlotsPerWarp = kURes + 2;     // + 1 raw + 1 Snake'd output slot (single-buffered: results wait in registers)
 
 struct __align__(8) UnitBarriers {
   uint64_t sfull[kUMaxSlabs], sempty[kUMaxSlabs];
   uint64_t wfull[kUMaxStages], wempty[kUMaxStages];
-  uint64_t acc1_full, a2_full, acc2_full, acc2_empty;
-  uint64_t res_bar[kMaxEpiWarps][kMaxResDepth];
+  uint64_t acc1_full[2], a2_full[2], acc2_full[2], acc2_empty[2];
+  uint64_t res_bar[kP2Warps][kURes];
   uint32_t tmem_base;
   uint32_t pad;
 };
+
+// Debug timeline (Q3TTS_DBG bit 5): clock64 stamps of CTA 0, first 16 tiles: [tile][event]
+__device__ long long g_unit_trace[16 * 16];
+#define UTRACE(it, ev) do { if ((p.dbg & 32) && blockIdx.x == 0 && (it) < 16) g_unit_trace[(it) * 16 + (ev)] = clock64(); } while (0)
 
 struct UnitArgs {
   const float* bias7;
   const float* s2a;
   const float* s2ib;
   int C, dil, ms, srows, nbox, nslabs, nstages;
+  int ks;    // K blocks per slab / weight stage
+  int nbuf;  // TMEM stages (1 or 2)
 };
 
-template <typename T>
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_s(uint32_t smem_dst, const void* map, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d_s(const void* map, uint32_t smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(reinterpret_cast<uint64_t>(map)),
+               "r"(smem_src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
+// Compile-time shape of one fused-unit instance.  Everything the MMA-issuing thread touches is a constant so that its code is
+// straight-line: tools/mma_bench.py shows the tensor pipe retires an N = 96 MMA every 56 cycles and an N = 192 MMA every 96,
+// but only if the single issuing thread spends no more than that per MMA (a passing mbarrier wait alone costs ~180 cycles).
+template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_>
+struct UnitCfg {
+  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_;
+  static constexpr int NKB = C / KB, NKG = NKB / KS, KSTEPS = KB / 16;
+  static constexpr int SPAN = KB * 2;
+  static constexpr int M1_STAGES = NKG * 7, M2_STAGES = NKG, TILE_STAGES = M1_STAGES + M2_STAGES;
+  static constexpr uint32_t WSUB = C * SPAN, STAGE_BYTES = KS * WSUB;
+  static_assert(TILE_STAGES % NST == 0 && (TILE_STAGES / NST) % 2 == 0, "weight ring slots and parities must be static per tile");
+  static_assert(NKG % NSL == 0 || NSL % NKG == 0, "slab ring");
+  static_assert(NBUF == 1 || 5 * C / 2 <= 256, "two TMEM stages need 2.5*C <= 256 columns");
+};
+
+template <typename T, typename Cfg>
 __global__ void __launch_bounds__(kUnitThreads, 1)
 unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW7, const __grid_constant__ CUtensorMap tmW1,
             const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmSnake,
             const GemmParams p, const UnitArgs u) {
+  constexpr int C = Cfg::C, KB = Cfg::KB, KS = Cfg::KS, NST = Cfg::NST, NSL = Cfg::NSL, NBUF = Cfg::NBUF, NKG = Cfg::NKG, KSTEPS = Cfg::KSTEPS;
+  constexpr uint32_t span = Cfg::SPAN, wsub = Cfg::WSUB, stage_bytes = Cfg::STAGE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int KB = p.kb, C = u.C, MS = u.ms;
-  const int nkb = C / KB;
   const int halo = 6 * u.dil;
-  const int TM = U_BM * MS;
-  const uint32_t span = KB * 2;
-  const uint32_t ssub = u.srows * span;  // one slab sub-block (all rows of one K block)
-  const uint32_t wsub = C * span;        // one weight tile (C output channels x KB)
-  uint8_t* slabs = smem;
-  uint8_t* wst = slabs + (size_t)u.nslabs * ssub;
-  uint8_t* epi = wst + (size_t)u.nstages * wsub;
-  UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(epi + (size_t)8 * epi_slots_per_warp(p) * kEpiSlot);
+  constexpr int TM = U_BM;
+  const uint32_t ssub = u.srows * span;  // one K block of a slab
+  const uint32_t slab_bytes = KS * ssub;
+  uint8_t* wst = smem;                                   // weight ring first: its slot addresses are compile-time offsets
+  uint8_t* slabs = wst + (size_t)NST * stage_bytes;
+  uint8_t* epi = slabs + (size_t)NSL * slab_bytes;
+  float* prm = reinterpret_cast<float*>(epi + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot);  // [6][C]: b7, s2a, s2ib, b1, sna, snib
+  UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(prm + 6 * C);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  TileSched ts;
-  ts.m_tiles = (p.rows_valid + TM - 1) / TM;
-  ts.n_tiles = 1;
-  ts.total_tiles = p.batches * ts.m_tiles;
+  const int m_tiles = (p.rows_valid + TM - 1) / TM;
+  const int total_tiles = p.batches * m_tiles;
+  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  constexpr int grp_warps = NBUF == 2 ? 4 : 8;  // epilogue warps that serve one TMEM stage
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW7); tma_prefetch_desc(&tmW1);
-    for (int s = 0; s < u.nslabs; ++s) { mbar_init(&bars->sfull[s], 1); mbar_init(&bars->sempty[s], 1); }
-    for (int s = 0; s < u.nstages; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
-    mbar_init(&bars->acc1_full, 1); mbar_init(&bars->a2_full, 8); mbar_init(&bars->acc2_full, 1); mbar_init(&bars->acc2_empty, 8);
-    for (int w = 0; w < kMaxEpiWarps; ++w)
-      for (int s = 0; s < kMaxResDepth; ++s) mbar_init(&bars->res_bar[w][s], 1);
+    tma_prefetch_desc(&tmRes); tma_prefetch_desc(&tmRaw); tma_prefetch_desc(&tmSnake);
+    for (int s = 0; s < NSL; ++s) { mbar_init(&bars->sfull[s], 1); mbar_init(&bars->sempty[s], 1); }
+    for (int s = 0; s < NST; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps);
+      mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], grp_warps);
+    }
+    for (int w = 0; w < kP2Warps; ++w)
+      for (int s = 0; s < kURes; ++s) mbar_init(&bars->res_bar[w][s], 1);
     fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    prm[i] = u.bias7[i]; prm[C + i] = u.s2a[i]; prm[2 * C + i] = u.s2ib[i];
+    prm[3 * C + i] = p.bias ? p.bias[i] : 0.f; prm[4 * C + i] = p.snake_a[i]; prm[5 * C + i] = p.snake_ib[i];
   }
   if (warp == 1) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
-  // TMEM column map
-  const uint32_t c_acc1 = 0, c_acc2 = (uint32_t)(MS * C), c_a2 = (uint32_t)(2 * MS * C);
+  // TMEM column map inside one stage; stage s starts at column s * 256
+  constexpr uint32_t c_acc1 = 0, c_acc2 = C, c_a2 = 2 * C;
 
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+    // ------------------------------------------------------------------ TMA producer (same order as the MMA issuer consumes)
     if (elect_one()) {
       int ss = 0, ws = 0; uint32_t sph = 0, wph = 0;
       const int boxrows = u.srows / u.nbox;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
-        int nt, mt, b;
-        ts.decode(tile, nt, mt, b);
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
-          mbar_expect_tx(&bars->sfull[ss], ssub);
-          for (int bx = 0; bx < u.nbox; ++bx)
-            tma_load_3d(slabs + (size_t)ss * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss], kb * KB, mt * TM - halo + bx * boxrows, b);
-          if (++ss == u.nslabs) { ss = 0; sph ^= 1; }
+      auto load_m1 = [&](int j) {  // slabs and W7 stages of this CTA's j-th tile
+        const int tile = (int)blockIdx.x + j * (int)gridDim.x;
+        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        for (int kg = 0; kg < NKG; ++kg) {
+          mbar_wait(&bars->sempty[ss], sph ^ 1);
+          mbar_expect_tx(&bars->sfull[ss], slab_bytes);
+          for (int kk = 0; kk < KS; ++kk)
+            for (int bx = 0; bx < u.nbox; ++bx)
+              tma_load_3d(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
+                          (kg * KS + kk) * KB, mt * TM - halo + bx * boxrows, b);
+          if (++ss == NSL) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < 7; ++tap) {
-            mbar_wait_backoff(&bars->wempty[ws], wph ^ 1);
-            mbar_expect_tx(&bars->wfull[ws], wsub);
-            tma_load_3d(wst + (size_t)ws * wsub, &tmW7, &bars->wfull[ws], kb * KB, 0, tap);
-            if (++ws == u.nstages) { ws = 0; wph ^= 1; }
+            mbar_wait(&bars->wempty[ws], wph ^ 1);
+            mbar_expect_tx(&bars->wfull[ws], stage_bytes);
+            for (int kk = 0; kk < KS; ++kk)
+              tma_load_3d(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW7, &bars->wfull[ws], (kg * KS + kk) * KB, 0, tap);
+            if (++ws == NST) { ws = 0; wph ^= 1; }
           }
         }
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait_backoff(&bars->wempty[ws], wph ^ 1);
-          mbar_expect_tx(&bars->wfull[ws], wsub);
-          tma_load_3d(wst + (size_t)ws * wsub, &tmW1, &bars->wfull[ws], kb * KB, 0, 0);
-          if (++ws == u.nstages) { ws = 0; wph ^= 1; }
+      };
+      auto load_m2 = [&]() {
+        for (int kg = 0; kg < NKG; ++kg) {
+          mbar_wait(&bars->wempty[ws], wph ^ 1);
+          mbar_expect_tx(&bars->wfull[ws], stage_bytes);
+          for (int kk = 0; kk < KS; ++kk)
+            tma_load_3d(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW1, &bars->wfull[ws], (kg * KS + kk) * KB, 0, 0);
+          if (++ws == NST) { ws = 0; wph ^= 1; }
         }
+      };
+      if (my_tiles > 0) load_m1(0);
+      for (int j = 0; j < my_tiles; ++j) {
+        if (NBUF == 2 && j + 1 < my_tiles) load_m1(j + 1);
+        load_m2();
+        if (NBUF == 1 && j + 1 < my_tiles) load_m1(j + 1);
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (one thread)
+    // ------------------------------------------------------------------ MMA issuer (one thread, straight-line per tile)
     if (elect_one()) {
       const uint32_t idesc = umma_idesc(U_BM, C, p.bf16 != 0);
       const uint32_t hi = umma_desc_hi(span);
-      const uint32_t s_lo0 = umma_desc_lo(smem_u32(slabs)), s_off = ssub >> 4;
-      const uint32_t w_lo0 = umma_desc_lo(smem_u32(wst)), w_off = wsub >> 4;
-      const int ksteps = KB / 16;  // MMAs (K = 16) per stage
-      int ss = 0, ws = 0; uint32_t sph = 0, wph = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
-        // ---- MMA1: dilated conv7 into acc1 (acc1 is free: a2_full of the previous tile was waited on before its MMA2)
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait_backoff(&bars->sfull[ss], sph);
-          const uint32_t slab = s_lo0 + (uint32_t)ss * s_off;
+      const uint32_t w_lo0 = umma_desc_lo(smem_u32(wst));
+      const uint32_t s_lo0 = umma_desc_lo(smem_u32(slabs)), s_off = slab_bytes >> 4, sk_off = ssub >> 4;
+      const uint32_t tap_step = ((uint32_t)u.dil * span) >> 4;  // descriptor offset of one tap: dil rows
+      // `g` = index of a weight stage inside the (prologue + steady-state) sequence; slot and parity follow from it at compile time
+      // MMA1 of this CTA's j-th tile: dilated conv7 into acc1 of TMEM stage j % NBUF (free: a2_full of tile j - NBUF was waited
+      // on before its MMA2, which was issued earlier).  G0 = first weight-stage index of this call.
+      auto mma1 = [&](int j, auto g0_tag) {
+        constexpr int G0 = decltype(g0_tag)::value;
+        const uint32_t d = tmem_base + (uint32_t)((j % NBUF) * 256) + c_acc1;
+        UTRACE(j, 0);
+#pragma unroll
+        for (int kg = 0; kg < NKG; ++kg) {
+          int sl; uint32_t spar;
+          if (NKG % NSL == 0) { sl = kg % NSL; spar = (uint32_t)(j * (NKG / NSL) + kg / NSL) & 1u; }
+          else { constexpr int R = NSL / NKG; sl = (j % R) * NKG + kg; spar = (uint32_t)(j / R) & 1u; }
+          mbar_wait(&bars->sfull[sl], spar);
+          const uint32_t slab = s_lo0 + (uint32_t)sl * s_off;
+#pragma unroll
           for (int tap = 0; tap < 7; ++tap) {
-            mbar_wait_backoff(&bars->wfull[ws], wph);
-            tc_fence_after();
-            const uint32_t b = w_lo0 + (uint32_t)ws * w_off;
-            for (int ms = 0; ms < MS; ++ms) {
-              // rows of this sub-tile for this tap start (ms*128 + halo - (6 - tap)*dil) rows into the slab
-              const uint32_t a = slab + (((uint32_t)(ms * U_BM + halo - (6 - tap) * u.dil) * span) >> 4);
-              const uint32_t d = tmem_base + c_acc1 + (uint32_t)(ms * C);
-              for (int k = 0; k < ksteps; ++k) umma_f16_lohi(d, a + 2 * k, b + 2 * k, hi, idesc, (kb | tap | k) != 0);
+            const int g = G0 + kg * 7 + tap;          // compile-time after unrolling
+            const int ws = g % NST;
+            const uint32_t par = (uint32_t)(g / NST) & 1u;
+            mbar_wait(&bars->wfull[ws], par);
+            const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
+            const uint32_t at = slab + (uint32_t)tap * tap_step;
+#pragma unroll
+            for (int kk = 0; kk < KS; ++kk) {
+#pragma unroll
+              for (int k = 0; k < KSTEPS; ++k)
+                umma_f16_lohi(d, at + (uint32_t)kk * sk_off + 2 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, idesc, (kg | tap | kk | k) != 0);
             }
             umma_commit(&bars->wempty[ws]);
-            if (++ws == u.nstages) { ws = 0; wph ^= 1; }
           }
-          umma_commit(&bars->sempty[ss]);
-          if (++ss == u.nslabs) { ss = 0; sph ^= 1; }
+          umma_commit(&bars->sempty[sl]);
         }
-        umma_commit(&bars->acc1_full);
-        // ---- MMA2: 1x1 conv, A = Snake'd conv7 output packed in tensor memory by epilogue phase 1
-        mbar_wait_backoff(&bars->a2_full, it & 1);
-        mbar_wait_backoff(&bars->acc2_empty, (it & 1) ^ 1);
+        umma_commit(&bars->acc1_full[j % NBUF]);
+        UTRACE(j, 2);
+      };
+      // MMA2: 1x1 conv, A = Snake'd conv7 output packed in tensor memory by the phase-1 warps
+      auto mma2 = [&](int j, auto g0_tag) {
+        constexpr int G0 = decltype(g0_tag)::value;
+        const int sb = j % NBUF;
+        const uint32_t use = (uint32_t)(j / NBUF);  // how many times this TMEM stage has been used before
+        const uint32_t st = tmem_base + (uint32_t)(sb * 256);
+        mbar_wait_backoff(&bars->a2_full[sb], use & 1);
+        UTRACE(j, 3);
+        mbar_wait_backoff(&bars->acc2_empty[sb], (use & 1) ^ 1);
         tc_fence_after();
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait_backoff(&bars->wfull[ws], wph);
-          tc_fence_after();
-          const uint32_t b = w_lo0 + (uint32_t)ws * w_off;
-          for (int ms = 0; ms < MS; ++ms) {
-            const uint32_t d = tmem_base + c_acc2 + (uint32_t)(ms * C);
-            const uint32_t a = tmem_base + c_a2 + (uint32_t)(ms * (C / 2)) + (uint32_t)(kb * (KB / 2));
-            for (int k = 0; k < ksteps; ++k) umma_f16_ts(d, a + 8 * k, b + 2 * k, hi, idesc, (kb | k) != 0);
+        UTRACE(j, 4);
+#pragma unroll
+        for (int kg = 0; kg < NKG; ++kg) {
+          const int g = G0 + kg;
+          const int ws = g % NST;
+          const uint32_t par = (uint32_t)(g / NST) & 1u;
+          mbar_wait(&bars->wfull[ws], par);
+          const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
+#pragma unroll
+          for (int kk = 0; kk < KS; ++kk) {
+#pragma unroll
+            for (int k = 0; k < KSTEPS; ++k)
+              umma_f16_ts(st + c_acc2, st + c_a2 + (uint32_t)((kg * KS + kk) * (KB / 2)) + 8 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, idesc,
+                          (kg | kk | k) != 0);
           }
           umma_commit(&bars->wempty[ws]);
-          if (++ws == u.nstages) { ws = 0; wph ^= 1; }
         }
-        umma_commit(&bars->acc2_full);
+        umma_commit(&bars->acc2_full[sb]);
+        UTRACE(j, 5);
+      };
+      // Weight-stage indices: prologue MMA1(0) uses [0, M1); steady state per tile is TILE_STAGES stages, so the index modulo
+      // (2 * NST) -- all the slot / parity arithmetic needs -- is the same in every iteration (TILE_STAGES % (2*NST) == 0).
+      constexpr int M1S = Cfg::M1_STAGES;
+      if (my_tiles > 0) mma1(0, std::integral_constant<int, 0>{});
+      for (int j = 0; j < my_tiles; ++j) {
+        if (NBUF == 2) {
+          if (j + 1 < my_tiles) { mma1(j + 1, std::integral_constant<int, M1S>{}); mma2(j, std::integral_constant<int, 2 * M1S>{}); }
+          else mma2(j, std::integral_constant<int, M1S>{});
+        } else {
+          mma2(j, std::integral_constant<int, M1S>{});
+          if (j + 1 < my_tiles) mma1(j + 1, std::integral_constant<int, M1S + Cfg::M2_STAGES>{});
+        }
       }
     }
-  } else {
-    // ------------------------------------------------------------------ epilogue warps
-    const int quad = warp & 3, ew = warp - 2, half = ew >> 2;
+  } else if (warp < 2 + kP1Warps) {
+    // ------------------------------------------------------------------ phase-1 warps: acc1 -> + b7 -> SnakeBeta -> 16-bit pairs -> A2 (TMEM)
+    const int quad = warp & 3, grp = (warp - 2) >> 2;
+    constexpr int ncols = NBUF == 2 ? C : C / 2;  // columns this warp serves (a multiple of 32)
+    const uint32_t tcol = NBUF == 2 ? 0u : (uint32_t)(grp * ncols);  // one TMEM stage: the two warp groups split the columns
+    const int pcol0 = NBUF == 2 ? 0 : grp * ncols;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
-    // phase-2 machinery (residual prefetch ring, TMA stores) is the shared asynchronous epilogue
-    EpiWarp<T> ep(p, &tmRes, &tmRaw, &tmSnake, &tmRaw, epi + (size_t)ew * epi_slots_per_warp(p) * kEpiSlot, bars->res_bar[ew], ts, lane, quad,
-                  MS == 2 ? 0 : half, MS == 2 ? 1 : 2);
-    if (MS == 2) { ep.mt_mul = 2; ep.mt_add = half; }
-    ep.start();
-    const int units = C >> 4;
-    const int ms1 = MS == 2 ? half : 0;                        // sub-tile this warp serves
-    const int u_lo = MS == 2 ? 0 : half * (units / 2);         // 16-column units of phase 1
-    const int u_hi = MS == 2 ? units : u_lo + units / 2;
-    int it = 0;
-    for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
-      int nt, mt, b;
-      ts.decode(tile, nt, mt, b);
-      // ---- phase 1
-      mbar_wait(&bars->acc1_full, it & 1);
+    const uint32_t st = tmem_base + lane_base + (NBUF == 2 ? (uint32_t)(grp * 256) : 0u);
+    const uint32_t src = st + c_acc1 + tcol;
+    const uint32_t dst = st + c_a2 + (tcol >> 1);
+    const uint32_t prm_s = smem_u32(prm);
+    const int sb = NBUF == 2 ? grp : 0;
+    for (int j = NBUF == 2 ? grp : 0; j < my_tiles; j += NBUF) {
+      mbar_wait(&bars->acc1_full[sb], (uint32_t)(j / NBUF) & 1);
       tc_fence_after();
-      {
-        const uint32_t src = tmem_base + lane_base + c_acc1 + (uint32_t)(ms1 * C);
-        const uint32_t dst = tmem_base + lane_base + c_a2 + (uint32_t)(ms1 * (C / 2));
-        for (int uu = u_lo; uu < u_hi; uu += 2) {
-          uint32_t ra[16], rb[16];
-          tmem_ld16(src + uu * 16, ra);
-          tmem_ld16(src + uu * 16 + 16, rb);
-          float ba[16], bb[16], sa[16], sb[16], ia[16], ib[16];
-          load16f(u.bias7 + uu * 16, ba); load16f(u.bias7 + uu * 16 + 16, bb);
-          load16f(u.s2a + uu * 16, sa); load16f(u.s2a + uu * 16 + 16, sb);
-          load16f(u.s2ib + uu * 16, ia); load16f(u.s2ib + uu * 16 + 16, ib);
-          tmem_ld_wait();
-          uint32_t pa[8], pb[8];
+      if (quad == 2 && lane == 0) UTRACE(j, 6);
+      for (int g = 0; g < ncols; g += 32) {
+        uint32_t ra[16], rb[16];
+        tmem_ld16(src + g, ra);
+        tmem_ld16(src + g + 16, rb);
+        tmem_ld_wait();
+        uint32_t pk[16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float a0 = snake(__uint_as_float(ra[2 * i]) + ba[2 * i], sa[2 * i], ia[2 * i]);
-            const float a1 = snake(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], sa[2 * i + 1], ia[2 * i + 1]);
-            const float b0 = snake(__uint_as_float(rb[2 * i]) + bb[2 * i], sb[2 * i], ib[2 * i]);
-            const float b1 = snake(__uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1], sb[2 * i + 1], ib[2 * i + 1]);
-            pa[i] = Elem<T>::pack2(a0, a1);
-            pb[i] = Elem<T>::pack2(b0, b1);
-          }
-          tmem_st8(dst + uu * 8, pa);
-          tmem_st8(dst + uu * 8 + 8, pb);
+        for (int q = 0; q < 8; ++q) {
+          const uint32_t pa = prm_s + (uint32_t)(pcol0 + g + 4 * q) * 4u;
+          const float4 b = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
+          const uint32_t* r = q < 4 ? &ra[4 * q] : &rb[4 * (q - 4)];
+          const float v0 = snake(__uint_as_float(r[0]) + b.x, a.x, ib.x), v1 = snake(__uint_as_float(r[1]) + b.y, a.y, ib.y);
+          const float v2 = snake(__uint_as_float(r[2]) + b.z, a.z, ib.z), v3 = snake(__uint_as_float(r[3]) + b.w, a.w, ib.w);
+          pk[2 * q] = Elem<T>::pack2(v0, v1);
+          pk[2 * q + 1] = Elem<T>::pack2(v2, v3);
         }
-        tmem_st_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bars->a2_full);
+        const uint32_t (&p0)[8] = *reinterpret_cast<const uint32_t (*)[8]>(&pk[0]);
+        const uint32_t (&p1)[8] = *reinterpret_cast<const uint32_t (*)[8]>(&pk[8]);
+        tmem_st8(dst + (g >> 1), p0);
+        tmem_st8(dst + (g >> 1) + 8, p1);
       }
-      // ---- phase 2
-      mbar_wait(&bars->acc2_full, it & 1);
-      tc_fence_after();
-      ep.tile(tmem_base + lane_base + c_acc2 + (uint32_t)(ms1 * C), it, 0, mt * MS + (MS == 2 ? half : 0), b);
+      tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->acc2_empty);
+      if (lane == 0) mbar_arrive(&bars->a2_full[sb]);
+      if (quad == 2 && lane == 0) UTRACE(j, 7);
     }
-    ep.finish();
+  } else {
+    // ------------------------------------------------------------------ phase-2 warps: acc2 + b1 + x -> y, snake_next(y) (TMA in / out)
+    const int pw = warp - 2 - kP1Warps;
+    const int quad = warp & 3, grp = pw >> 2;
+    constexpr int ncols = NBUF == 2 ? C : C / 2;
+    constexpr int nitems = ncols >> 5;
+    const uint32_t tcol = NBUF == 2 ? 0u : (uint32_t)(grp * ncols);
+    const int pcol0 = NBUF == 2 ? 0 : grp * ncols;
+    const int rsub = quad * 32;  // row offset of this warp inside a tile
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const uint32_t acc = tmem_base + lane_base + (NBUF == 2 ? (uint32_t)(grp * 256) : 0u) + c_acc2 + tcol;
+    const uint32_t prm_s = smem_u32(prm);
+    const uint32_t eb = smem_u32(epi) + (uint32_t)pw * kUSlotsPerWarp * kEpiSlot;  // [kURes residual][raw][snake] slots of 2 KB
+    const uint32_t rbar = smem_u32(&bars->res_bar[pw][0]);
+    const int sb = NBUF == 2 ? grp : 0;
+    const int j0 = NBUF == 2 ? grp : 0;
+    uint32_t off[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) off[c] = (uint32_t)(lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4));
+    // residual prefetch cursor over this warp's (tile, item) sequence
+    int pf_j = j0, pf_item = 0;
+    uint32_t issued = 0, cons = 0, ob = 0;
+    auto prefetch = [&]() {
+      if (pf_j >= my_tiles) return;
+      if (lane == 0) {
+        const int tile = (int)blockIdx.x + pf_j * (int)gridDim.x;
+        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        const uint32_t slot = issued & (kURes - 1);
+        const uint32_t bar = rbar + slot * 8u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)kEpiSlot) : "memory");
+        tma_load_3d_s(eb + slot * kEpiSlot, &tmRes, bar, pcol0 + 32 * pf_item, mt * TM + rsub, b);
+      }
+      ++issued;
+      if (++pf_item == nitems) { pf_item = 0; pf_j += NBUF; }
+    };
+    for (int i = 0; i < kURes; ++i) prefetch();
+    for (int j = j0; j < my_tiles; j += NBUF) {
+      const int tile = (int)blockIdx.x + j * (int)gridDim.x;
+      const int b = tile / m_tiles, mt = tile - b * m_tiles;
+      const int row0 = mt * TM + rsub;
+      mbar_wait(&bars->acc2_full[sb], (uint32_t)(j / NBUF) & 1);
+      tc_fence_after();
+      if (quad == 2 && lane == 0) UTRACE(j, 8);
+      for (int item = 0; item < nitems; ++item) {
+        uint32_t ra[16], rb[16];
+        tmem_ld16(acc + 32 * item, ra);
+        tmem_ld16(acc + 32 * item + 16, rb);
+        const uint32_t slot = cons & (kURes - 1);
+        mbar_wait(&bars->res_bar[pw][slot], (cons / kURes) & 1);
+        const uint32_t rs = eb + slot * kEpiSlot;
+        uint4 res[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) res[c] = lds_u4(rs + off[c]);
+        ++cons;
+        const uint32_t raw_s = eb + kURes * kEpiSlot, snk_s = eb + (kURes + 1) * kEpiSlot;
+        __syncwarp();  // every lane has read the residual slot
+        prefetch();
+        tmem_ld_wait();
+        uint32_t oraw[16], osnk[16];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {  // chunk c = 8 columns
+          const uint32_t* r = c < 2 ? &ra[8 * c] : &rb[8 * (c - 2)];
+          const uint32_t rw[4] = {res[c].x, res[c].y, res[c].z, res[c].w};
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const uint32_t pa = prm_s + (uint32_t)(3 * C + pcol0 + 32 * item + 8 * c + 4 * q) * 4u;
+            const float4 bb = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
+            const float2 x0 = Elem<T>::unpack2(rw[2 * q]), x1 = Elem<T>::unpack2(rw[2 * q + 1]);
+            const float y0 = __uint_as_float(r[4 * q]) + bb.x + x0.x, y1 = __uint_as_float(r[4 * q + 1]) + bb.y + x0.y;
+            const float y2 = __uint_as_float(r[4 * q + 2]) + bb.z + x1.x, y3 = __uint_as_float(r[4 * q + 3]) + bb.w + x1.y;
+            oraw[4 * c + 2 * q] = Elem<T>::pack2(y0, y1);
+            oraw[4 * c + 2 * q + 1] = Elem<T>::pack2(y2, y3);
+            osnk[4 * c + 2 * q] = Elem<T>::pack2(snake(y0, a.x, ib.x), snake(y1, a.y, ib.y));
+            osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(snake(y2, a.z, ib.z), snake(y3, a.w, ib.w));
+          }
+        }
+        if (lane == 0) tma_store_wait_read<0>();  // the previous item's stores have read the output slots (long done: they overlap the math above)
+        __syncwarp();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          sts_u4(raw_s + off[c], oraw[4 * c], oraw[4 * c + 1], oraw[4 * c + 2], oraw[4 * c + 3]);
+          sts_u4(snk_s + off[c], osnk[4 * c], osnk[4 * c + 1], osnk[4 * c + 2], osnk[4 * c + 3]);
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
+          tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
+          tma_store_commit();
+        }
+        ++ob;
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->acc2_empty[sb]);
+      if (quad == 2 && lane == 0) UTRACE(j, 9);
+    }
+    if (lane == 0) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();
@@ -232,50 +425,50 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------- host
+using Cfg96 = UnitCfg<96, 32, 3, 4, 2, 2>;       // one weight stage = one tap over all of K (18 KB), whole-tile slabs, two TMEM stages
+using Cfg192a = UnitCfg<192, 64, 1, 4, 3, 1>;    // stage = (K block, tap) 24 KB; 4 stages when the slabs are small (dilation 1, 3)
+using Cfg192b = UnitCfg<192, 64, 1, 3, 3, 1>;    // 3 stages for the dilation-9 slabs
+
 static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
-  return (size_t)op.nslabs * op.srows * span + (size_t)op.nstages * op.C * span + (size_t)8 * epi_slots_per_warp(op.p) * kEpiSlot +
-         sizeof(UnitBarriers) + 1024;
+  return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * op.C * span + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot +
+         (size_t)6 * op.C * sizeof(float) + sizeof(UnitBarriers) + 1024;
 }
 
 bool unit_fusable(int C) {
   if (getenv("Q3TTS_NO_FUSE")) return false;
-  if (C % 32 || C > 256 || C < 32) return false;
-  const int ms = C <= 96 ? 2 : 1;
-  return 5 * ms * C / 2 <= 512;
+  return C == 96 || C == 192;  // instantiated shapes (the vocoder's two HBM-bound levels)
 }
 
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows) {
   GemmParams& p = op->p;
   op->enabled = 0;
   const int C = op->C;
-  if (getenv("Q3TTS_NO_FUSE")) return 1;
-  if (C % 32 || C > 256 || C < 32) return 1;
-  op->ms = C <= 96 ? 2 : 1;
-  if (5 * op->ms * C / 2 > 512) return 1;  // TMEM columns: acc1 + acc2 + packed A2
-  p.kb = (C % 64 == 0) ? 64 : 32;
+  if (!unit_fusable(C)) return 1;
+  op->ms = 1;
+  p.kb = C == 96 ? 32 : 64;
   p.epi_warps = 8;
   p.res_depth = 2;
   p.batches = batches; p.rows = rows; p.rows_valid = rows; p.cin = C; p.ntaps = 1; p.tap_off[0] = 0;
   p.n_total = C; p.bn = C; p.ncol_mod = C; p.act = ACT_NONE; p.res_f32 = 0; p.out_f32 = nullptr; p.scale = nullptr;
   p.out_row_stride = C; p.out_batch_stride = (long long)rows * C;
   p.a_ptr = a1;
-  if (!p.res || !p.out_raw || !p.out_snake) return 1;
+  if (!p.res || !p.out_raw || !p.out_snake || !p.snake_a || !p.snake_ib) return 1;
   const int span = p.kb * 2;
-  const int need = U_BM * op->ms + 6 * op->dil;
-  op->srows = (need + 15) / 16 * 16;
-  op->nbox = op->srows > 256 ? 2 : 1;
-  if (op->srows / op->nbox > 256 || (op->srows / op->nbox) % 8) return 1;
-  const long long fixed = 1024 + (long long)8 * epi_slots_per_warp(p) * kEpiSlot + (long long)sizeof(UnitBarriers) + 256;
-  const long long avail = (long long)gemm_smem_optin() - fixed;
-  const long long slab = (long long)op->srows * span, wst = (long long)C * span;
-  const int want_st = wst >= 16384 ? 3 : 6;
-  op->nslabs = 0;
-  for (int ns = 4; ns >= 2; --ns) {
-    long long st = (avail - ns * slab) / wst;
-    if (st >= want_st) { op->nslabs = ns; op->nstages = (int)(st > kUMaxStages ? kUMaxStages : st); break; }
+  const int need = U_BM + 6 * op->dil;
+  op->srows = (need + 7) / 8 * 8;
+  op->nbox = 1;
+  if (op->srows > 256) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
+  if (C == 96) { op->ks = Cfg96::KS; op->nstages = Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = 0; }
+  else {
+    op->ks = 1; op->nslabs = 3; op->nbuf = 1;
+    op->nstages = 4; op->variant = 1;
+    if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = 3; op->variant = 2; }
   }
-  if (!op->nslabs) return 1;
+  if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) {
+    if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: smem %zu > %d (C %d dil %d srows %d)\n", unit_smem_bytes(*op), gemm_smem_optin(), C, op->dil, op->srows);
+    return 1;
+  }
   const int et = p.bf16 ? 1 : 0;
   int rc = 0;
   rc |= make_tmap_3d(&op->tmA, a1, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, (uint32_t)p.kb, (uint32_t)(op->srows / op->nbox), p.bf16 != 0);
@@ -285,32 +478,48 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   rc |= make_tmap_3d_strided(&op->tmRes, p.res, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
   rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
   rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
-  if (rc) return -1;
+  if (rc) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: tensor map failed (C %d dil %d srows %d)\n", C, op->dil, op->srows); return -1; }
   static bool attr_done = false;
   if (!attr_done) {
-    if (cudaFuncSetAttribute(unit_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess ||
-        cudaFuncSetAttribute(unit_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess)
-      return -2;
+    const int mx = gemm_smem_optin();
+    cudaError_t e = cudaSuccess;
+    auto set = [&](const void* f) { if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx); };
+    set((const void*)unit_kernel<__half, Cfg96>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96>);
+    set((const void*)unit_kernel<__half, Cfg192a>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192a>);
+    set((const void*)unit_kernel<__half, Cfg192b>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192b>);
+    if (e != cudaSuccess) return -2;
     attr_done = true;
   }
   op->enabled = 1;
   return 0;
 }
 
+// Copies the debug timeline of the last traced launch (Q3TTS_DBG bit 5) to the host.
+int unit_trace_read(long long* out256) { return cudaMemcpyFromSymbol(out256, g_unit_trace, sizeof(long long) * 256) == cudaSuccess ? 0 : -1; }
+
+template <typename Cfg>
+static cudaError_t launch_cfg(const UnitOp& op, const UnitArgs& u, int grid, size_t smem, cudaStream_t stream) {
+  const GemmParams& p = op.p;
+  if (p.bf16)
+    unit_kernel<__nv_bfloat16, Cfg><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
+  else
+    unit_kernel<__half, Cfg><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
   if (!op.enabled) return cudaErrorInvalidConfiguration;
   const GemmParams& p = op.p;
-  const int TM = U_BM * op.ms;
-  const int tiles = p.batches * ((p.rows_valid + TM - 1) / TM);
+  const int tiles = p.batches * ((p.rows_valid + U_BM - 1) / U_BM);
   if (tiles <= 0) return cudaSuccess;
   const int grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
-  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages};
+  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf};
   const size_t smem = unit_smem_bytes(op);
-  if (p.bf16)
-    unit_kernel<__nv_bfloat16><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
-  else
-    unit_kernel<__half><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
-  return cudaGetLastError();
+  switch (op.variant) {
+    case 0: return launch_cfg<Cfg96>(op, u, grid, smem, stream);
+    case 1: return launch_cfg<Cfg192a>(op, u, grid, smem, stream);
+    default: return launch_cfg<Cfg192b>(op, u, grid, smem, stream);
+  }
 }
 
 }  // namespace q3

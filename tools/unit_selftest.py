@@ -8,7 +8,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 CASES = [(1000, 96, 1, 0), (1000, 96, 9, 0), (5000, 96, 3, 0), (700, 192, 1, 0), (700, 192, 9, 0), (3000, 192, 3, 1), (255, 96, 9, 1),
-         (1, 96, 1, 0), (129, 192, 3, 0), (40000, 96, 9, 0), (40000, 192, 9, 0)]
+         (1, 96, 1, 0), (129, 192, 3, 0), (257, 96, 3, 0), (40000 * 148 // 100, 96, 1, 0), (40000, 96, 9, 0), (40000, 192, 9, 0)]
 
 if len(sys.argv) > 1:
     from qwen3_tts_b200 import _capi
