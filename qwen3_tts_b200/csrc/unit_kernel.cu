@@ -209,12 +209,15 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           else { constexpr int R = NSL / NKG; sl = (j % R) * NKG + kg; spar = (uint32_t)(j / R) & 1u; }
           mbar_wait(&bars->sfull[sl], spar);
           const uint32_t slab = s_lo0 + (uint32_t)sl * s_off;
+          bool ready = false;  // result of the early poll of this tap's weight stage (issued before the previous tap's MMAs)
 #pragma unroll
           for (int tap = 0; tap < 7; ++tap) {
             const int g = G0 + kg * 7 + tap;          // compile-time after unrolling
             const int ws = g % NST;
             const uint32_t par = (uint32_t)(g / NST) & 1u;
-            mbar_wait(&bars->wfull[ws], par);
+            if (!ready) mbar_wait(&bars->wfull[ws], par);
+            // poll the next tap's stage now: the ~180-cycle latency of a passing mbarrier test then overlaps the MMA issue below
+            if (tap + 1 < 7 && !(p.dbg & 256)) ready = mbar_try_wait(&bars->wfull[(g + 1) % NST], (uint32_t)((g + 1) / NST) & 1u);
             const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
             const uint32_t at = slab + (uint32_t)tap * tap_step;
 #pragma unroll
