@@ -85,18 +85,29 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     Op& op = b.gemm(e->in_proj, P, 1, M, M);
     op.g.p.out_f32 = X;
   }
+  {
+    Op& op0 = plan->ops.back();
+    b.tag(op0, "transformer.in", X, true, H, T);
+  }
   for (int l = 0; l < c.num_hidden_layers; ++l) {
     const LayerW& W = e->layers[l];
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H; }
-    { Op& op = b.gemm(W.qkv, Hn, 1, M, M); op.g.p.out_raw = QKV; }
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = T; }
-    { Op& op = b.gemm(W.o, AO, 1, M, M); op.g.p.scale = W.ls1; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H; }
+    const std::string L = "transformer." + std::to_string(l) + ".";  // debug probe taps (not oracle taps)
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H;
+      b.tag(op, (L + "ln1").c_str(), Hn, false, H, T); }
+    { Op& op = b.gemm(W.qkv, Hn, 1, M, M); op.g.p.out_raw = QKV; b.tag(op, (L + "qkv").c_str(), QKV, false, 3 * H, T); }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = T;
+      b.tag(op, (L + "attn").c_str(), AO, false, H, T); }
+    { Op& op = b.gemm(W.o, AO, 1, M, M); op.g.p.scale = W.ls1; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X;
+      b.tag(op, (L + "o").c_str(), X, true, H, T); }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H;
+      b.tag(op, (L + "ln2").c_str(), Hn, false, H, T); }
     {
       Op& op = b.gemm(W.gateup, Hn, 1, M, M);
       op.g.p.act = ACT_GLU; op.g.p.out_raw = MI; op.g.p.out_row_stride = I; op.g.p.out_batch_stride = (long long)M * I;
+      b.tag(op, (L + "gateup").c_str(), MI, false, I, T);
     }
-    { Op& op = b.gemm(W.down, MI, 1, M, M); op.g.p.scale = W.ls2; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
+    { Op& op = b.gemm(W.down, MI, 1, M, M); op.g.p.scale = W.ls2; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X;
+      b.tag(op, (L + "down").c_str(), X, true, H, T); }
   }
   { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; }
   {
@@ -265,6 +276,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
                int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s) {
   const q3tts_config& c = e->cfg;
   size_t pi = 0;
+  static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
   if (e->profile) {
     while (e->prof_events.size() < 2 * plan->ops.size()) {
       cudaEvent_t ev;
@@ -295,6 +307,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
         break;
     }
     ++e->launches;
+    if (sync_each) cudaStreamSynchronize(s);
     if (e->profile) {
       cudaEventRecord(e->prof_events[2 * pi + 1], s);
       double fl = 0.0, by = 0.0;

@@ -179,9 +179,6 @@ struct EpiWarp {
     const int u0 = item * 2;
     const int n0 = nt * p.bn + u0 * 16;
     const int c0 = wraps ? n0 % p.ncol_mod : n0;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
-    uint32_t ra[16], rb[16];
-    tmem_ld16(t0 + u0 * 16, ra);
-    tmem_ld16(t0 + u0 * 16 + 16, rb);
     float rsa[16], rsb[16];
     if (has_res) {
       const uint32_t slot = rb_cons & (rd - 1);
@@ -189,8 +186,13 @@ struct EpiWarp {
       const uint8_t* rbuf = eb + slot * kEpiSlot;
       load_res16(rbuf, 0, rsa);
       load_res16(rbuf, 2, rsb);
-      res_consumed();
     }
+    // The asynchronous TMEM loads and their wait stay adjacent: the compiler treats the destination registers as defined
+    // by the load statement, so any code in between could copy them before the data has arrived (seen as a rare glitch).
+    uint32_t ra[16], rb[16];
+    __syncwarp();  // tcgen05.ld is .sync.aligned: reconverge after the lane-0 branches / barrier spin loops above
+    tmem_ld16(t0 + u0 * 16, ra);
+    tmem_ld16(t0 + u0 * 16 + 16, rb);
     tmem_ld_wait();
     float va[16], vb[16];
 #pragma unroll
@@ -222,6 +224,10 @@ struct EpiWarp {
         tma_store_commit();
       }
     }
+    // Hand the residual slot back to the TMA engine only now: the st.shared above consumed values computed from the residual
+    // registers, and a warp issues in order, so every ld.shared of the slot has returned its data.  (Refilling right after
+    // the loads were ISSUED let the asynchronous-proxy write overtake a queued load: a rare one-chunk glitch.)
+    if (has_res) res_consumed();
     ++ob;
   }
 
@@ -229,8 +235,6 @@ struct EpiWarp {
   __device__ __forceinline__ void item_f32(uint32_t t0, int nt, int row0, int b, int item) {
     const int n0 = nt * p.bn + item * 16;
     const int c0 = wraps ? n0 % p.ncol_mod : n0;
-    uint32_t r[16];
-    tmem_ld16(t0 + item * 16, r);
     float rs[16];
     if (has_res) {
       const uint32_t slot = rb_cons & (rd - 1);
@@ -245,13 +249,25 @@ struct EpiWarp {
       } else {
         load_res16(rbuf, 0, rs);  // a 16-bit residual box of 16 columns sits in chunks 0..1
       }
-      res_consumed();
+      if ((p.dbg & 512) && rf32) {  // debug: residual straight from global memory (race localisation)
+        const int row = row0 + lane;
+        if (row < p.rows_valid) {
+          const float4* g = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.res) + (long long)b * p.out_batch_stride +
+                                                            (long long)row * p.out_row_stride + n0);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) { const float4 t = g[c]; rs[4 * c] = t.x; rs[4 * c + 1] = t.y; rs[4 * c + 2] = t.z; rs[4 * c + 3] = t.w; }
+        }
+      }
     }
+    uint32_t r[16];
+    __syncwarp();                  // .sync.aligned instruction: the warp must be converged
+    tmem_ld16(t0 + item * 16, r);  // load and wait adjacent (see item_pair)
     tmem_ld_wait();
     float v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
     if (tail) {
+      if (has_res) res_consumed();
       if (p.bias) v[0] += __ldg(p.bias);
       const int row = row0 + lane;
       if (row < p.rows_valid && row >= p.tail_skip)
@@ -259,6 +275,16 @@ struct EpiWarp {
       return;
     }
     math_unit(v, rs, c0);
+    if (of32 && (p.dbg & 1024)) {  // debug: output straight to global memory (race localisation)
+      const int row = row0 + lane;
+      if (row < p.rows_valid) {
+        float4* g = reinterpret_cast<float4*>(p.out_f32 + (long long)b * p.out_batch_stride + (long long)row * p.out_row_stride + n0);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) g[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+      }
+      if (has_res) res_consumed();
+      return;
+    }
     if (of32) {
       uint8_t* o8 = eb + (s_f32 + (fb & 3)) * kEpiSlot;
       if (lane == 0) tma_store_wait_read<3>();
@@ -274,6 +300,7 @@ struct EpiWarp {
       }
       ++fb;
     }
+    if (has_res) res_consumed();  // after the st.shared that consumed the residual (see item_pair)
   }
 
   // ---- GLU flow: 64 interleaved (gate, up) accumulator columns -> 32 outputs (reference modeling :367-369)
@@ -293,6 +320,7 @@ struct EpiWarp {
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       uint32_t ra[16], rb[16];
+      __syncwarp();
       tmem_ld16(t0 + (u0 + 2 * h) * 16, ra);
       tmem_ld16(t0 + (u0 + 2 * h) * 16 + 16, rb);
       tmem_ld_wait();

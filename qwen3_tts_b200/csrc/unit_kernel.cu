@@ -295,6 +295,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (quad == 2 && lane == 0) UTRACE(j, 6);
       for (int g = 0; g < ncols; g += 32) {
         uint32_t ra[16], rb[16];
+        __syncwarp();  // .sync.aligned: reconverge after the barrier spin loop
         tmem_ld16(src + g, ra);
         tmem_ld16(src + g + 16, rb);
         tmem_ld_wait();
@@ -364,9 +365,6 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 8);
       for (int item = 0; item < nitems; ++item) {
-        uint32_t ra[16], rb[16];
-        tmem_ld16(acc + 32 * item, ra);
-        tmem_ld16(acc + 32 * item + 16, rb);
         const uint32_t slot = cons & (kURes - 1);
         mbar_wait(&bars->res_bar[pw][slot], (cons / kURes) & 1);
         const uint32_t rs = eb + slot * kEpiSlot;
@@ -375,8 +373,11 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int c = 0; c < 4; ++c) res[c] = lds_u4(rs + off[c]);
         ++cons;
         const uint32_t raw_s = eb + kURes * kEpiSlot, snk_s = eb + (kURes + 1) * kEpiSlot;
-        __syncwarp();  // every lane has read the residual slot
-        prefetch();
+        // asynchronous TMEM loads and their wait stay adjacent: nothing may touch the destination registers in between
+        uint32_t ra[16], rb[16];
+        __syncwarp();  // .sync.aligned: reconverge after the lane-0 branch in prefetch()
+        tmem_ld16(acc + 32 * item, ra);
+        tmem_ld16(acc + 32 * item + 16, rb);
         tmem_ld_wait();
         uint32_t oraw[16], osnk[16];
 #pragma unroll
@@ -410,6 +411,9 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
           tma_store_commit();
         }
+        // refill the residual slot only now: the st.shared above consumed the residual registers (in-order issue), so every
+        // ld.shared of the slot has returned and the __syncwarp() above covers all lanes
+        prefetch();
         ++ob;
       }
       tc_fence_before();
