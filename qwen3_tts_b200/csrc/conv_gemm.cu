@@ -123,7 +123,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
             mbar_expect_tx(&bars->full[s], stage_bytes);
-            tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.tap_off[tap], b);
+            tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
             tma_load_3d(sa + a_bytes, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
           }
@@ -219,7 +219,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait_backoff(&bars->empty[s], ph ^ 1);
         mbar_expect_tx(&bars->full[s], slab_bytes);
         for (int kb = 0; kb < nkb; ++kb)
-          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], kb * KB, mt * BM - halo, b);
+          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], kb * KB, mt * BM + p.a_row0 - halo, b);
         if (++s == nslabs) { s = 0; ph ^= 1; }
       }
     }
@@ -317,7 +317,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
           mbar_expect_tx(&bars->sfull[ss], ssub);
-          tma_load_3d(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * BM - slab_lo, b);
+          tma_load_3d(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * BM + p.a_row0 - slab_lo, b);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
@@ -395,9 +395,9 @@ __global__ void conv_gemm_simt_kernel(const GemmParams p) {
     const T* A = reinterpret_cast<const T*>(p.a_ptr);
     const T* W = reinterpret_cast<const T*>(p.w_ptr);
     for (int tap = 0; tap < p.ntaps; ++tap) {
-      const int r = row + p.tap_off[tap];
+      const int r = row + p.a_row0 + p.tap_off[tap];
       if (r < 0 || r >= p.rows) continue;
-      const T* a = A + ((long long)b * p.rows + r) * p.cin;
+      const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * p.cin) + (long long)r * p.cin;
       const T* w = W + ((long long)tap * p.n_total + n) * p.cin;
       for (int k = 0; k < p.cin; ++k) {
         const float av = Elem<T>::to_f(a[k]);
@@ -519,13 +519,14 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   op->tmRes = op->tmA; op->tmRaw = op->tmA; op->tmSnake = op->tmA; op->tmF32 = op->tmA;  // valid placeholders
   int rc = 0;
   if (p.act != ACT_TAIL) {
-    if (p.res) rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, bs, p.res_f32 ? 16 : 32, 32);
+    if (p.res) rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, 32);
     if (p.out_raw) rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, 32);
-    if (p.out_snake) rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, bs, 32, 32);
+    if (p.out_snake) rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, 32);
     if (p.out_f32) rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32);
   }
   plan_variant(op, allow);
-  rc |= make_tmap_3d(&op->tmA, p.a_ptr, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint32_t)p.kb, (uint32_t)(op->variant ? op->srp : BM), p.bf16 != 0);
+  rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
+                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb, (uint32_t)(op->variant ? op->srp : BM));
   return rc;
 }
 

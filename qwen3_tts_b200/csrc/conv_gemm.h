@@ -46,6 +46,9 @@ struct UnitOp {
   int srows = 0, nbox = 1;            // slab rows per K block (128*ms + 6*dil rounded up), TMA boxes per slab
   int nslabs = 0, nstages = 0;        // ring depths
   int ks = 1, nbuf = 1;               // K blocks per slab / weight stage; TMEM stages
+  // streaming (history-prefixed a1 buffer): rows of a1 per batch item, row of output row 0, strides (0 = dense)
+  int a_rows = 0, a_row0 = 0;
+  long long a_batch_stride = 0, snake_batch_stride = 0;
   int variant = 0;                    // compiled instance (unit_kernel.cu: 0 = C 96, 1 / 2 = C 192 with 4 / 3 weight stages)
   int enabled = 0;
 };

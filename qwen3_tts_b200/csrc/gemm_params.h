@@ -26,7 +26,8 @@ enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3 };
 
 struct GemmParams {
   int batches;
-  int rows;        // A rows per batch item
+  int rows;        // A rows per batch item (streaming: history rows + new rows)
+  int a_row0;      // A row of accumulator row 0 (streaming: the history rows in front of the new ones; 0 otherwise)
   int rows_valid;  // accumulator rows per batch item that are stored
   int cin;
   int ntaps;
@@ -51,6 +52,9 @@ struct GemmParams {
   const float* snake_a;
   const float* snake_ib;
   long long out_batch_stride;  // elements
+  long long a_batch_stride;    // elements between batch items of A (0: rows * cin)
+  long long res_batch_stride;  // residual tensor (0: same as out_batch_stride)
+  long long snake_batch_stride;  // Snake'd output tensor (0: same as out_batch_stride)
   long long out_row_stride;    // elements
   // raw operand pointers, used only by the SIMT cross-check kernel
   const void* a_ptr;

@@ -55,6 +55,7 @@ struct UnitArgs {
   int C, dil, ms, srows, nbox, nslabs, nstages;
   int ks;    // K blocks per slab / weight stage
   int nbuf;  // TMEM stages (1 or 2)
+  int a_row0;  // row of the a1 tensor that belongs to output row 0 (streaming history rows in front)
 };
 
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -160,7 +161,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           for (int kk = 0; kk < KS; ++kk)
             for (int bx = 0; bx < u.nbox; ++bx)
               tma_load_3d(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
-                          (kg * KS + kk) * KB, mt * TM - halo + bx * boxrows, b);
+                          (kg * KS + kk) * KB, mt * TM - halo + u.a_row0 + bx * boxrows, b);
           if (++ss == NSL) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < 7; ++tap) {
             mbar_wait(&bars->wempty[ws], wph ^ 1);
@@ -478,13 +479,16 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   }
   const int et = p.bf16 ? 1 : 0;
   int rc = 0;
-  rc |= make_tmap_3d(&op->tmA, a1, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, (uint32_t)p.kb, (uint32_t)(op->srows / op->nbox), p.bf16 != 0);
+  const uint64_t a_rows = op->a_rows ? (uint64_t)op->a_rows : (uint64_t)rows;
+  rc |= make_tmap_3d_strided(&op->tmA, a1, et, (uint64_t)C, a_rows, (uint64_t)batches, (uint64_t)C,
+                             op->a_batch_stride ? (uint64_t)op->a_batch_stride : a_rows * C, (uint32_t)p.kb, (uint32_t)(op->srows / op->nbox));
   rc |= make_tmap_3d(&op->tmW7, w7, (uint64_t)C, (uint64_t)C, 7, (uint32_t)p.kb, (uint32_t)C, p.bf16 != 0);
   rc |= make_tmap_3d(&op->tmW1, w1, (uint64_t)C, (uint64_t)C, 1, (uint32_t)p.kb, (uint32_t)C, p.bf16 != 0);
   const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
   rc |= make_tmap_3d_strided(&op->tmRes, p.res, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
   rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
-  rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
+  rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs,
+                             op->snake_batch_stride ? (uint64_t)op->snake_batch_stride : bs, 32, 32);
   if (rc) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: tensor map failed (C %d dil %d srows %d)\n", C, op->dil, op->srows); return -1; }
   static bool attr_done = false;
   if (!attr_done) {
@@ -520,7 +524,7 @@ cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
   const int tiles = p.batches * ((p.rows_valid + U_BM - 1) / U_BM);
   if (tiles <= 0) return cudaSuccess;
   const int grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
-  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf};
+  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf, op.a_row0};
   const size_t smem = unit_smem_bytes(op);
   switch (op.variant) {
     case 0: return launch_cfg<Cfg96>(op, u, grid, smem, stream);
