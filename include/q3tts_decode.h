@@ -103,6 +103,28 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
 int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
                       void* stream);
 
+/* ---- Streaming: stateful per-packet decode.  The reference has NO counterpart: its only streaming-shaped call is
+ * chunked_decode's `forward(codes[..., s-25:e])[..., 25*1920:]` (modeling :889-893), which re-decodes 25 frames of left
+ * context per chunk and is only approximately equal to the whole-sequence decode.  These entry points keep, per stream, the
+ * history rows of every causal conv, the last input of every transposed conv and a 72-window K/V cache per transformer
+ * layer, so that the concatenation of the step outputs EQUALS Decoder.forward(whole sequence) (same arithmetic, same
+ * rounding; oracle = modeling :868-883).  A stream's first step emits P*1920-555 samples (the look-ahead of the four
+ * k = 2s transposed convs), every later step P*1920; the last 555 samples of the sequence are never emitted, as in the
+ * reference.  Used by the talker's Dual-Track packet generation (model wrapper :838 hands codes to decode()).
+ *
+ * q3tts_stream_reserve sizes everything (state, K/V rings, workspace for max_streams x max_frames_per_step <= 57); no
+ * allocation happens in q3tts_stream_step for shapes within the reservation. */
+int q3tts_stream_reserve(q3tts_handle* h, int max_streams, int max_frames_per_step);
+int q3tts_stream_open(q3tts_handle* h, int* stream_id, void* stream);
+int q3tts_stream_reset(q3tts_handle* h, int stream_id, void* stream);
+int q3tts_stream_close(q3tts_handle* h, int stream_id);
+int64_t q3tts_stream_frames(q3tts_handle* h, int stream_id);   /* frames decoded so far, -1 = not open */
+int64_t q3tts_stream_state_bytes(q3tts_handle* h);              /* device bytes of state per stream */
+/* One step: stream_ids[S] (host), codes [S,Q,P] int64 (device), wav [S, wav_stride] fp32 (device, wav_stride >= P*1920),
+ * n_valid[S] (host, optional) = samples written per row.  All launches go to `stream`; returns without synchronising. */
+int q3tts_stream_step(q3tts_handle* h, const int32_t* stream_ids, int S, const int64_t* codes, int P, float* wav, int64_t wav_stride,
+                      int32_t* n_valid, void* stream);
+
 /* Parity probe: run forward() up to the stage named `stage` (an oracle tap name such as
  * "pre_conv", "pre_transformer", "upsample.0.1", "decoder.2.block.3", "decoder.0.snake") and write
  * that activation as fp32 [B,C,L] to `out` (device, `capacity` floats).  *C and *L receive the shape. */

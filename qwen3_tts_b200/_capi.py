@@ -58,6 +58,13 @@ EXPORTS = {
     "q3tts_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "q3tts_forward_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.c_int64,
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p]),
+    "q3tts_stream_reserve": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "q3tts_stream_open": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.c_void_p]),
+    "q3tts_stream_reset": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "q3tts_stream_close": (C.c_int, [C.c_void_p, C.c_int]),
+    "q3tts_stream_frames": (C.c_int64, [C.c_void_p, C.c_int]),
+    "q3tts_stream_state_bytes": (C.c_int64, [C.c_void_p]),
+    "q3tts_stream_step": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.c_void_p]),
     "q3tts_launch_count": (C.c_int64, [C.c_void_p]),
     "q3tts_set_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "q3tts_get_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int32)]),

@@ -145,4 +145,75 @@ int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, con
   return engine_run(&e, plan, (const long long*)codes, (long long)Q * T, T, 1, nullptr, 0, 0, stage, out, capacity, C, L, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------------------------------------ streaming
+int q3tts_stream_reserve(q3tts_handle* h, int max_streams, int max_frames_per_step) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (!e.finalized) return e.fail(Q3TTS_NOT_READY, "stream_reserve: weights not finalized");
+  if (max_streams < 1 || max_frames_per_step < 1) return e.fail(Q3TTS_BAD_SHAPE, "stream_reserve: sizes must be positive");
+  DeviceGuard g(e.device);
+  return engine_stream_reserve(&e, max_streams, max_frames_per_step);
+}
+
+static int stream_clear_slot(Engine& e, int id, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (cudaMemsetAsync(e.stream_state + (size_t)id * e.state_bytes, 0, (size_t)e.state_bytes, s) != cudaSuccess ||
+      cudaMemsetAsync(e.d_slot_pos + id, 0, sizeof(int), s) != cudaSuccess)
+    return e.fail(Q3TTS_CUDA_ERROR, "stream: state reset failed");
+  e.slot_frames[id] = 0;
+  return Q3TTS_OK;
+}
+
+int q3tts_stream_open(q3tts_handle* h, int* stream_id, void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (!stream_id) return e.fail(Q3TTS_BAD_SHAPE, "stream_open: null output");
+  if (!e.max_slots) return e.fail(Q3TTS_BAD_STREAM, "stream_open: call q3tts_stream_reserve first");
+  DeviceGuard g(e.device);
+  for (int i = 0; i < e.max_slots; ++i)
+    if (e.slot_frames[i] < 0) {
+      *stream_id = i;
+      return stream_clear_slot(e, i, stream);
+    }
+  return e.fail(Q3TTS_BAD_STREAM, "stream_open: all reserved stream slots are in use");
+}
+
+int q3tts_stream_reset(q3tts_handle* h, int stream_id, void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (stream_id < 0 || stream_id >= e.max_slots || e.slot_frames[stream_id] < 0) return e.fail(Q3TTS_BAD_STREAM, "stream_reset: unknown stream id");
+  DeviceGuard g(e.device);
+  return stream_clear_slot(e, stream_id, stream);
+}
+
+int q3tts_stream_close(q3tts_handle* h, int stream_id) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (stream_id < 0 || stream_id >= e.max_slots || e.slot_frames[stream_id] < 0) return e.fail(Q3TTS_BAD_STREAM, "stream_close: unknown stream id");
+  e.slot_frames[stream_id] = -1;
+  return Q3TTS_OK;
+}
+
+int64_t q3tts_stream_frames(q3tts_handle* h, int stream_id) {
+  if (!h || stream_id < 0 || stream_id >= h->e.max_slots) return -1;
+  return h->e.slot_frames[stream_id];
+}
+
+int64_t q3tts_stream_state_bytes(q3tts_handle* h) {
+  if (!h) return 0;
+  return h->e.state_bytes + (int64_t)2 * h->e.cfg.num_hidden_layers * h->e.kv_ring * h->e.cfg.hidden_size * 2;
+}
+
+int q3tts_stream_step(q3tts_handle* h, const int32_t* stream_ids, int S, const int64_t* codes, int P, float* wav, int64_t wav_stride, int32_t* n_valid,
+                      void* stream) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  Engine& e = h->e;
+  if (!e.finalized) return e.fail(Q3TTS_NOT_READY, "weights not finalized");
+  if (!stream_ids || !codes || !wav) return e.fail(Q3TTS_BAD_SHAPE, "stream_step: null argument");
+  if (wav_stride < (int64_t)P * e.total_up) return e.fail(Q3TTS_BAD_SHAPE, "stream_step: wav_stride smaller than P * upsample");
+  DeviceGuard g(e.device);
+  const int Q = e.cfg.num_quantizers;
+  return engine_stream_step(&e, stream_ids, S, (const long long*)codes, (long long)Q * P, P, 1, P, wav, wav_stride, n_valid, (cudaStream_t)stream);
+}
+
 }  // extern "C"

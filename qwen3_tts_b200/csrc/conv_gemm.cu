@@ -516,17 +516,22 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   const uint64_t width = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
   const uint64_t rows = p.rows_valid, nb = p.batches;
   const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
-  op->tmRes = op->tmA; op->tmRaw = op->tmA; op->tmSnake = op->tmA; op->tmF32 = op->tmA;  // valid placeholders
   int rc = 0;
+  bool has_res = false, has_raw = false, has_snake = false, has_f32 = false;
   if (p.act != ACT_TAIL) {
-    if (p.res) rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, 32);
-    if (p.out_raw) rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, 32);
-    if (p.out_snake) rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, 32);
-    if (p.out_f32) rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32);
+    if (p.res) { has_res = true; rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, 32); }
+    if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, 32); }
+    if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, 32); }
+    if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32); }
   }
   plan_variant(op, allow);
   rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
                              p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb, (uint32_t)(op->variant ? op->srp : BM));
+  // unused maps hold a valid placeholder (the kernels take all of them as __grid_constant__ arguments)
+  if (!has_res) op->tmRes = op->tmA;
+  if (!has_raw) op->tmRaw = op->tmA;
+  if (!has_snake) op->tmSnake = op->tmA;
+  if (!has_f32) op->tmF32 = op->tmA;
   return rc;
 }
 

@@ -9,6 +9,7 @@
 
 #include "../../include/q3tts_decode.h"
 #include "conv_gemm.h"
+#include "kernels.h"
 
 namespace q3 {
 
@@ -41,7 +42,7 @@ struct UpsampleW {
 struct UnitW { ConvW conv7, conv1; SnakeP act1, act2; };
 struct BlockW { SnakeP act0; ConvW tconv; UnitW unit[3]; int stride = 0, cin = 0, cout = 0; };
 
-enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT };
+enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT, OP_STREAM_ATTN, OP_STATE_LOAD, OP_STATE_SAVE, OP_POS_ADVANCE };
 
 struct Op {
   OpType type = OP_GEMM;
@@ -51,6 +52,7 @@ struct Op {
   void* out = nullptr;
   const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;
   int B = 0, L = 0, C = 0;
+  int aux0 = 0, aux1 = 0;  // streaming: RVQ output batch stride in rows / dwconv (input batch stride in rows, history rows) / attention layer
   // probe: the buffer that holds an oracle tap once this op has run
   std::string tag;
   const void* probe_ptr = nullptr;
@@ -62,6 +64,21 @@ struct Plan {
   int B = 0, T = 0;
   std::vector<Op> ops;
   int out_len = 0;  // samples per item of the forward output
+};
+
+// One launch plan of the streaming path: S streams x P new frames, `fresh` = first packet of every stream in the group.
+struct StreamPlan {
+  int S = 0, P = 0;
+  bool fresh = false;
+  std::vector<Op> ops;
+  std::vector<StreamBufDesc> descs;
+  StreamBufDesc* d_descs = nullptr;  // device copy, the plan's own allocation: the arena is scratch shared by every plan
+  int out_len = 0;                    // samples emitted per stream
+  float* wav_tmp = nullptr;           // dense [S][out_len] staging when the caller's rows are not the identity
+  StreamPlan() = default;
+  StreamPlan(const StreamPlan&) = delete;
+  StreamPlan& operator=(const StreamPlan&) = delete;
+  ~StreamPlan() { if (d_descs) cudaFree(d_descs); }
 };
 
 struct Engine {
@@ -108,6 +125,20 @@ struct Engine {
   float* wav_stage = nullptr;
   size_t wav_stage_elems = 0;
 
+  // ---- streaming state (q3tts_stream_*)
+  int max_slots = 0, stream_max_frames = 0, kv_ring = 128;
+  long long state_bytes = 0;             // history rows of every stage, per slot
+  unsigned char* stream_state = nullptr;  // [max_slots][state_bytes]
+  std::vector<void*> kcache, vcache;      // per layer: [max_slots][kv_ring][hidden] 16-bit
+  int* d_slot_pos = nullptr;              // [max_slots] frames decoded so far
+  int* d_slot_ids = nullptr;              // [2][max_slots] staging of the step's slot ids (continuing group, fresh group)
+  int* d_row_index = nullptr;             // [2][max_slots] caller row of every group member
+  int* h_stage = nullptr;                 // pinned host staging for the two arrays above
+  std::vector<int> slot_frames;           // host mirror of d_slot_pos; -1 = closed
+  uint8_t* sws = nullptr;                 // streaming workspace arena
+  size_t sws_bytes = 0;
+  std::map<std::pair<std::pair<int, int>, int>, StreamPlan> splans;  // ((S, P), fresh)
+
   int fail(int code, const std::string& msg) { err = msg; return code; }
 };
 
@@ -119,6 +150,10 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
 int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
                            long long wav_stride, int skip, cudaStream_t s);
 void engine_free(Engine* e);
+int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);
+int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long long* codes, long long sb, long long sk, long long st, int P, float* wav,
+                       long long wav_stride, int32_t* n_valid, cudaStream_t s);
+void engine_stream_free(Engine* e);
 
 struct DeviceGuard {
   int prev = -1;

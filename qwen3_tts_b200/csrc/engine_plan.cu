@@ -368,6 +368,7 @@ int engine_forward_batched(Engine* e, const long long* codes, long long sb, long
 }
 
 void engine_free(Engine* e) {
+  engine_stream_free(e);
   for (cudaEvent_t ev : e->prof_events) cudaEventDestroy(ev);
   for (void* p : e->owned) cudaFree(p);
   for (auto& kv : e->raw) cudaFree(kv.second.d);

@@ -25,7 +25,7 @@ cudaError_t fold_codebook(const float* embedding_sum, const float* cluster_usage
 // codes int64 addressed as codes[b*sb + k*sk + t*st]; tables [Q][ncodes][D] fp32; out_act [B][T][D] 16-bit (optional);
 // out_f32 [B][D][T] (optional)
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
-                       int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s);
+                       int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows = 0, const int* src_index = nullptr);
 // x fp32 [M][H] -> 16-bit [M][H]: w * x * rsqrt(mean(x^2) + eps)
 cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s);
 // rope table [maxT][hd/2] cos, sin (fp32)
@@ -35,11 +35,30 @@ cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* 
                               bool bf16, cudaStream_t s);
 // ConvNeXt front half: depthwise causal conv k=7 + bias, LayerNorm(eps) over C.  x,out 16-bit [B][L][C]; dw weight [7][C] fp32.
 cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
-                             float eps, bool bf16, cudaStream_t s);
+                             float eps, bool bf16, cudaStream_t s, int in_bs_rows = 0, int hist = 0);
 // tail: x 16-bit [B][L][C] (already Snake'd), w [7][C] fp32, bias -> clamp(conv, -1, 1); sample l >= skip is written to
 // out[b*out_batch_stride + l - skip] (skip drops a chunk's left-context samples, reference modeling :893)
 cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* out, long long out_batch_stride, int B, int L, int C, int skip,
                             bool bf16, cudaStream_t s);
+// ---- streaming (stateful per-packet decode; no counterpart in the reference, oracle = Decoder.forward on the whole sequence)
+// qkv 16-bit [S*P][3*nh*hd] of the P new tokens of S streams; K (RoPE applied) and V are appended to the per-slot ring caches
+// kc / vc [slots][ring][nh*hd] at (pos & (ring-1)); query i of stream s sits at absolute position slot_pos[slot_ids[s]] + i and sees
+// keys kv <= q && kv > q - window.  ring >= window - 1 + P.
+cudaError_t stream_attention(const void* qkv, void* kc, void* vc, const int* slot_ids, const int* slot_pos, const float* cos_t, const float* sin_t,
+                             int rope_max, float theta, void* out, int S, int P, int nh, int hd, int window, int ring, bool bf16, cudaStream_t s);
+// History rows of the streaming buffers <-> per-slot state.  descs (device): one StreamBufDesc per buffer.
+struct StreamBufDesc {
+  unsigned char* ptr;        // buffer base: [S][H + n][row_bytes]
+  long long batch_stride;    // bytes between streams
+  long long state_off;       // byte offset of this buffer's history inside a slot's state block
+  int H, n, row_bytes, pad;
+};
+// save = 0: state -> rows [0, H) of every buffer;  save = 1: rows [n, n + H) -> state
+cudaError_t stream_state_copy(const StreamBufDesc* descs, int ndesc, unsigned char* state, long long state_bytes, const int* slot_ids, int S, int save,
+                              cudaStream_t s);
+cudaError_t stream_advance_pos(int* slot_pos, const int* slot_ids, int S, int P, cudaStream_t s);
+// out[index[b]][0:len] = in[b][0:len]  (fp32 rows)
+cudaError_t scatter_rows_f32(const float* in, long long in_stride, float* out, long long out_stride, const int* index, int B, long long len, cudaStream_t s);
 // probes: activation [B][L][C] (16-bit or fp32) -> fp32 [B][C][L]
 cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s);
 // dw weight [C][1][7] -> [7][C]

@@ -27,13 +27,15 @@ __device__ __forceinline__ float warp_max(float v) {
 // left-to-right sum of books 1..Q-1 (rvq_rest), as the reference sums them (modeling :720-726, :817-819).
 template <typename T>
 __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long long sk, long long st, const float* __restrict__ tables,
-                      T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D) {
+                      T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D, int out_bs_rows,
+                      const int* __restrict__ src_index) {
   const int t = blockIdx.x, b = blockIdx.y;
+  const int bs = src_index ? src_index[b] : b;  // row of the caller's codes tensor this batch item reads
   const int d = threadIdx.x * 4;
   if (d >= D) return;
   float4 first = make_float4(0.f, 0.f, 0.f, 0.f), rest = first;
   for (int k = 0; k < Q; ++k) {
-    long long c = codes[b * sb + k * sk + t * st];
+    long long c = codes[bs * sb + k * sk + t * st];
     c = c < 0 ? 0 : (c >= ncodes ? ncodes - 1 : c);  // never fault on a bad code; range errors are reported by the checked entry
     const float4 e = __ldg(reinterpret_cast<const float4*>(tables + ((long long)k * ncodes + c) * D + d));
     if (k == 0) first = e;
@@ -44,7 +46,7 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
     uint2 o;
     o.x = Elem<T>::pack2(v.x, v.y);
     o.y = Elem<T>::pack2(v.z, v.w);
-    *reinterpret_cast<uint2*>(out_act + ((long long)b * Tn + t) * D + d) = o;
+    *reinterpret_cast<uint2*>(out_act + ((long long)b * out_bs_rows + t) * D + d) = o;
   }
   if (out_f32) {
     float* o = out_f32 + ((long long)b * D + d) * Tn + t;
@@ -52,11 +54,12 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
   }
 }
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
-                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s) {
+                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows, const int* src_index) {
   if (B <= 0 || Tn <= 0) return cudaSuccess;
+  if (out_bs_rows <= 0) out_bs_rows = Tn;
   dim3 grid(Tn, B);
   const int threads = ((D / 4 + 31) / 32) * 32;
-  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D)));
+  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index)));
   return cudaGetLastError();
 }
 

@@ -22,11 +22,12 @@ __device__ __forceinline__ float warp_sum2(float v) {
 template <typename T, int NI>
 __global__ void __launch_bounds__(256)
 k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float* __restrict__ dwb, const float* __restrict__ lnw,
-            const float* __restrict__ lnb, T* __restrict__ out, int B, int L, int C, float eps) {
+            const float* __restrict__ lnb, T* __restrict__ out, int B, int L, int C, float eps, int in_bs_rows, int hist) {
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= (long long)B * L) return;
   const int l = (int)(row % L);
+  const long long in_row = (row / L) * in_bs_rows + hist + l;  // row of x that holds sample l of this item (history rows in front)
   float acc[NI][4];
 #pragma unroll
   for (int i = 0; i < NI; ++i) {
@@ -35,9 +36,9 @@ k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float*
   }
 #pragma unroll
   for (int j = 0; j < 7; ++j) {
-    const int lt = l - 6 + j;
+    const int lt = hist + l - 6 + j;
     if (lt < 0) continue;
-    const T* xr = x + (row - 6 + j) * C;
+    const T* xr = x + (in_row - 6 + j) * C;
 #pragma unroll
     for (int i = 0; i < NI; ++i) {
       const int c = 4 * lane + 128 * i;
@@ -72,12 +73,13 @@ k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float*
   }
 }
 cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
-                             float eps, bool bf16, cudaStream_t s) {
+                             float eps, bool bf16, cudaStream_t s, int in_bs_rows, int hist) {
+  if (in_bs_rows <= 0) in_bs_rows = L;
   if (C != 1024) return cudaErrorInvalidValue;  // NI = C / 128 is a compile-time unroll
   const long long rows = (long long)B * L;
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)((rows + 7) / 8);
-  Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps)));
+  Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
   return cudaGetLastError();
 }
 

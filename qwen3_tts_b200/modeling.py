@@ -159,6 +159,48 @@ class Qwen3TTSTokenizerV2Decoder:
         _capi.check(self._h, rc, "chunked_decode")
         return wav
 
+    # ------------------------------------------------------------------ streaming (additive API, see include/q3tts_decode.h)
+    def reserve_streams(self, max_streams: int, max_frames_per_step: int = 4):
+        """Allocates per-stream state (conv history rows, K/V rings) and the step workspace."""
+        _capi.check(self._h, self._lib.q3tts_stream_reserve(self._h, int(max_streams), int(max_frames_per_step)), "stream_reserve")
+
+    def open_stream(self) -> int:
+        sid = C.c_int(-1)
+        _capi.check(self._h, self._lib.q3tts_stream_open(self._h, C.byref(sid), _stream_ptr(self.device)), "stream_open")
+        return int(sid.value)
+
+    def reset_stream(self, stream_id: int):
+        _capi.check(self._h, self._lib.q3tts_stream_reset(self._h, int(stream_id), _stream_ptr(self.device)), "stream_reset")
+
+    def close_stream(self, stream_id: int):
+        _capi.check(self._h, self._lib.q3tts_stream_close(self._h, int(stream_id)), "stream_close")
+
+    def stream_frames(self, stream_id: int) -> int:
+        return int(self._lib.q3tts_stream_frames(self._h, int(stream_id)))
+
+    def stream_state_bytes(self) -> int:
+        return int(self._lib.q3tts_stream_state_bytes(self._h))
+
+    def decode_step(self, stream_ids, codes: torch.Tensor, out: Optional[torch.Tensor] = None):
+        """One packet for each of S streams: codes [S, Q, P] int64 -> (wav [S, P*1920] fp32 on the device, n_valid list).
+
+        Concatenating wav[i, :n_valid[i]] over the steps of a stream equals forward(all its codes) (the first step of a
+        stream emits P*1920-555 samples, later steps P*1920)."""
+        codes = self._check_codes(codes)
+        S, _, P = codes.shape
+        ids = (C.c_int32 * S)(*[int(i) for i in stream_ids])
+        if len(stream_ids) != S:
+            raise ValueError(f"{len(stream_ids)} stream ids for {S} code rows")
+        stride = P * self.total_upsample
+        if out is None:
+            out = torch.empty((S, stride), dtype=torch.float32, device=self.device)
+        elif out.shape != (S, stride) or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError("out must be a contiguous float32 [S, P*upsample] tensor")
+        nv = (C.c_int32 * S)()
+        rc = self._lib.q3tts_stream_step(self._h, ids, S, codes.data_ptr(), P, out.data_ptr(), stride, nv, _stream_ptr(self.device))
+        _capi.check(self._h, rc, "stream_step")
+        return out, [int(v) for v in nv]
+
     def probe(self, codes: torch.Tensor, stage: str) -> torch.Tensor:
         """Parity probe: activation after `stage` as fp32 [B, C, L] (oracle tap names)."""
         codes = self._check_codes(codes)

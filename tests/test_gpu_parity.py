@@ -180,6 +180,63 @@ def test_full_size_batch_properties(gpu_model, sd, cfg):
         assert mx <= MAX_ABS and snr >= MIN_SNR
 
 
+def test_streaming_equals_whole_sequence_forward(gpu_model, cfg):
+    """Stateful per-packet decode (q3tts_stream_*): concatenated stream output == Decoder.forward(whole sequence) on
+    [0, T*1920-555), for packet sizes 1, 3 and 5, streams that start at different steps, and a reset."""
+    from qwen3_tts_b200.synthetic import make_codes
+    dec = gpu_model.decoder
+    T = 30
+    codes = make_codes(3, T, cfg, seed=11).cuda().transpose(1, 2).contiguous()    # [3, Q, T]
+    whole = dec(codes)[:, 0]                                                          # [3, T*1920-555]
+    dec.reserve_streams(4, 5)
+    for P in (1, 3, 5):
+        ids = [dec.open_stream() for _ in range(3)]
+        got = [[] for _ in range(3)]
+        # stream 2 joins one step late: a step then mixes first-packet and continuing streams
+        t = [0, 0, -P]
+        while min(t) < T:
+            rows = [i for i in range(3) if 0 <= t[i] < T]
+            if rows:
+                pk = torch.stack([codes[i, :, t[i]:t[i] + P] for i in rows])
+                wav, nv = dec.decode_step([ids[i] for i in rows], pk)
+                for k, i in enumerate(rows):
+                    got[i].append(wav[k, :nv[k]].clone())
+            t = [x + P for x in t]
+        for i in range(3):
+            w = torch.cat(got[i])
+            assert w.shape == (T * 1920 - 555,), (P, i, w.shape)
+            mx, snr = _stats(whole[i], w)
+            assert mx <= 1e-5, (P, i, mx, snr)
+            assert dec.stream_frames(ids[i]) == T
+        # reset: the same stream decodes the same codes to the same samples again
+        dec.reset_stream(ids[0])
+        wav, nv = dec.decode_step([ids[0]], codes[0:1, :, :P])
+        assert nv[0] == P * 1920 - 555 and torch.equal(wav[0, :nv[0]], got[0][0])
+        for i in ids:
+            dec.close_stream(i)
+    with pytest.raises(KeyError):
+        dec.decode_step([0], codes[0:1, :, :1])      # closed stream
+
+
+def test_streaming_matches_reference_golden(gpu_model):
+    """Streamed in packets of 2 frames, the golden batch must meet the same tolerance as the bulk decode vs the fp32 reference."""
+    g = load_golden("forward_B2_T12.npz")
+    codes = torch.from_numpy(g["codes"]).transpose(1, 2).contiguous().cuda()
+    dec = gpu_model.decoder
+    dec.reserve_streams(2, 2)
+    ids = [dec.open_stream(), dec.open_stream()]
+    parts = []
+    for t in range(0, 12, 2):
+        wav, nv = dec.decode_step(ids, codes[:, :, t:t + 2])
+        assert nv[0] == nv[1]
+        parts.append(wav[:, :nv[0]].clone())
+    w = torch.cat(parts, dim=1)
+    assert w.shape == (2, 12 * 1920 - 555)
+    mx, snr = _stats(g["wav"][:, 0], w)
+    print(f"streamed B2 T12 (P=2): max-abs {mx:.3e} snr {snr:.1f} dB")
+    assert mx <= MAX_ABS and snr >= MIN_SNR
+
+
 def test_bulk_decode_is_bitwise_reproducible(gpu_model, cfg):
     """Regression for a shared-memory slot hand-back race (DESIGN.md "Residual ring"): every run of the same batch must be
     bit-identical.  The race showed up in ~1 of 10 runs as a one-chunk glitch in the fp32 residual stream."""
