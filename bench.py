@@ -124,6 +124,49 @@ def run_reference(args, rank: int):
     print(json.dumps(line), flush=True)
 
 
+def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup: int):
+    """BASELINE config 3: `streams` concurrent streams, one packet of `packet` frames each per step, left-context state on the device.
+
+    Per step: device time of q3tts_stream_step (CUDA events) and host wall time of the whole chunk (pinned codes -> device, step, waveform
+    -> pinned host, synchronize).  The timed steps are steady-state (continuing) steps that cross the K/V ring wrap."""
+    import torch
+
+    from qwen3_tts_b200.synthetic import make_codes
+    total = warmup + steps
+    codes_h = make_codes(streams, total * packet, cfg, seed=77).transpose(1, 2).contiguous()    # [S,Q,T]
+    pk_h = [codes_h[:, :, i * packet:(i + 1) * packet].contiguous().pin_memory() for i in range(total)]
+    pk_d = torch.empty_like(pk_h[0], device=dev)
+    wav_d = torch.empty((streams, packet * 1920), dtype=torch.float32, device=dev)
+    wav_h = torch.empty((streams, packet * 1920), dtype=torch.float32).pin_memory()
+    ids = [dec.open_stream() for _ in range(streams)]
+    dev_ms, host_ms = [], []
+    l0 = dec.launch_count()
+    for i in range(total):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        pk_d.copy_(pk_h[i], non_blocking=True)
+        a.record()
+        dec.decode_step(ids, pk_d, out=wav_d)
+        b.record()
+        wav_h.copy_(wav_d, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        t1 = time.perf_counter()
+        if i >= warmup:
+            dev_ms.append(a.elapsed_time(b)); host_ms.append((t1 - t0) * 1e3)
+    launches = (dec.launch_count() - l0) // total
+    for i in ids:
+        dec.close_stream(i)
+    q = lambda v, f: float(sorted(v)[min(len(v) - 1, int(f * len(v)))])
+    chunk_audio_s = packet * FRAME_SEC
+    return {"streams": streams, "frames_per_packet": packet, "chunk_audio_ms": chunk_audio_s * 1e3, "steps": steps, "warmup": warmup,
+            "device_ms": {"p50": q(dev_ms, 0.5), "p99": q(dev_ms, 0.99), "max": max(dev_ms)},
+            "e2e_ms": {"p50": q(host_ms, 0.5), "p99": q(host_ms, 0.99), "max": max(host_ms),
+                       "includes": "pinned codes h2d, step, waveform d2h to pinned host, synchronize"},
+            "realtime_factor_p50": streams * chunk_audio_s / (q(host_ms, 0.5) * 1e-3), "launches_per_step": launches,
+            "h2d_bytes_per_step": streams * 16 * packet * 8, "d2h_bytes_per_step": streams * packet * 1920 * 4}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -132,6 +175,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16"], help="tensor-core operand type (fp32 accumulate)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-streaming", action="store_true", help="skip the streaming-chunk latency section (BASELINE config 3)")
+    ap.add_argument("--stream-only", action="store_true", help="print only the streaming-chunk latency section")
+    ap.add_argument("--streams", type=int, default=256)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -166,6 +212,11 @@ def main():
     model = synthetic_model(state_dict=sd, device=dev, compute_mode=args.mode)
     del sd
     dec = model.decoder
+    if args.stream_only:
+        dec.reserve_streams(args.streams, 4)
+        out = {"streaming": [stream_latency(dec, cfg, dev, args.streams, P, steps=200, warmup=40) for P in (1, 2, 4)]}
+        print(json.dumps(out), flush=True)
+        return
     dec.reserve(B_UTT * T_FRAMES)
     tok = Qwen3TTSTokenizer.from_model(model)
     codes_host = make_codes(B_UTT, T_FRAMES, cfg, seed=1 + rank)            # [B,T,Q] int64
@@ -254,6 +305,10 @@ def main():
                     "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [125,16]}) -> host float32 arrays"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
             "path_frac_of_tensor_roofline": path_frac, "kernels": by_kernel}
+    if not args.no_streaming and world == 1:
+        # BASELINE config 3 rides along as its own section: it is a latency, not the throughput metric of this line
+        dec.reserve_streams(args.streams, 4)
+        line["streaming"] = [stream_latency(dec, cfg, dev, args.streams, P, steps=200, warmup=40) for P in (1, 4)]
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference_run(steps=3, warmup=1, utterances=1)
         line["cpu_baseline"] = {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]}

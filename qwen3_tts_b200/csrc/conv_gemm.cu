@@ -101,9 +101,9 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   TileSched ts;
-  ts.m_tiles = (p.rows_valid + BM - 1) / BM;
+  ts.m_tiles = p.pack_mode ? 1 : (p.rows_valid + BM - 1) / BM;  // packed: decode() returns the tile index as "batch"
   ts.n_tiles = p.n_total / p.bn;
-  ts.total_tiles = p.batches * ts.m_tiles * ts.n_tiles;
+  ts.total_tiles = gemm_m_tiles_total(p) * ts.n_tiles;
   const int kblocks = p.cin / KB;
   const int ksteps = kblocks * p.ntaps;
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
@@ -118,12 +118,20 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int nt, mt, b;
         ts.decode(tile, nt, mt, b);
         const int m0 = mt * BM, n0 = nt * p.bn;
+        int cr[4] = {0, 0, 0, 0}, cb[4] = {0, 0, 0, 0};
+        if (p.pack_mode)
+          for (int q = 0; q < 4; ++q) gemm_chunk_coords(p, b, q, cr[q], cb[q]);
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
             mbar_expect_tx(&bars->full[s], stage_bytes);
-            tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
+            if (p.pack_mode) {  // four 32-row chunk boxes fill the 128-row A tile
+              for (int q = 0; q < 4; ++q)
+                tma_load_3d(sa + q * (a_bytes >> 2), &tmA, &bars->full[s], kb * KB, cr[q] + p.a_row0 + p.tap_off[tap], cb[q]);
+            } else {
+              tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
+            }
             tma_load_3d(sa + a_bytes, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
           }
@@ -428,13 +436,13 @@ int tmap_init() {
 }
 
 int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1,
-                         uint64_t stride2, uint32_t box0, uint32_t box1) {
+                         uint64_t stride2, uint32_t box0, uint32_t box1, uint32_t box2) {
   if (tmap_init()) return -1;
   const uint64_t esz = etype == 2 ? 4 : 2;
   cuuint64_t dims[3] = {d0, d1 ? d1 : 1, d2 ? d2 : 1};
   cuuint64_t strides[2] = {stride1 * esz, stride2 * esz};
   if (strides[1] == 0) strides[1] = strides[0] * dims[1];
-  cuuint32_t box[3] = {box0, box1, 1};
+  cuuint32_t box[3] = {box0, box1, box2 ? box2 : 1};
   cuuint32_t estr[3] = {1, 1, 1};
   const uint32_t inner = box0 * (uint32_t)esz;
   CUtensorMapSwizzle sw = inner == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
@@ -447,7 +455,7 @@ int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t
 
 // 3-D tensor map over a dense 16-bit tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0].
 int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16) {
-  return make_tmap_3d_strided(out, base, bf16 ? 1 : 0, d0, d1, d2, d0, d0 * d1, box0, box1);
+  return make_tmap_3d_strided(out, base, bf16 ? 1 : 0, d0, d1, d2, d0, d0 * d1, box0, box1, 1);
 }
 
 static int g_num_sms = 0;
@@ -467,6 +475,7 @@ int gemm_stage_count(const GemmParams& p) {
 static void plan_variant(GemmOp* op, int allow) {
   const GemmParams& p = op->p;
   op->ws = 0; op->nslabs = 0; op->srp = 0; op->variant = 0; op->nstages = 0; op->slab_lo = 0;
+  if (p.pack_mode) return;  // packed tiles exist in the general kernel only
   int lo = 0, hi = 0;
   for (int j = 0; j < p.ntaps; ++j) {
     if (-p.tap_off[j] > lo) lo = -p.tap_off[j];
@@ -511,22 +520,39 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
     if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
   }
+  {  // packed tiles when a batch item's rows would fill less than 60 % of its 128-row tiles
+    GemmParams& q = op->p;
+    q.pack_mode = 0; q.pack_rshift = 0; q.pack_cpb = 1;
+    const int mt = (q.rows_valid + BM - 1) / BM;
+    if (q.act != ACT_TAIL && q.batches > 1 && q.rows_valid > 0 && !getenv("Q3TTS_NO_PACK") && q.rows_valid * 10 < mt * BM * 6) {
+      if (q.rows_valid <= 16) {
+        q.pack_mode = 1;
+        while ((1 << q.pack_rshift) < q.rows_valid) ++q.pack_rshift;
+      } else {
+        q.pack_mode = 2;
+        q.pack_cpb = (q.rows_valid + 31) / 32;
+      }
+    }
+  }
   const GemmParams& p = op->p;
   const int et = p.bf16 ? 1 : 0;
   const uint64_t width = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
   const uint64_t rows = p.rows_valid, nb = p.batches;
   const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
+  // epilogue boxes: 32 accumulator rows = one batch item's rows, or (packed mode 1) all rows of 32 >> rshift batch items
+  const uint32_t br = p.pack_mode == 1 ? (1u << p.pack_rshift) : 32u, bb = p.pack_mode == 1 ? (32u >> p.pack_rshift) : 1u;
   int rc = 0;
   bool has_res = false, has_raw = false, has_snake = false, has_f32 = false;
   if (p.act != ACT_TAIL) {
-    if (p.res) { has_res = true; rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, 32); }
-    if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, 32); }
-    if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, 32); }
-    if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, 32); }
+    if (p.res) { has_res = true; rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, br, bb); }
+    if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, br, bb); }
+    if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, br, bb); }
+    if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, br, bb); }
   }
   plan_variant(op, allow);
   rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
-                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb, (uint32_t)(op->variant ? op->srp : BM));
+                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb,
+                             p.pack_mode ? br : (uint32_t)(op->variant ? op->srp : BM), bb);
   // unused maps hold a valid placeholder (the kernels take all of them as __grid_constant__ arguments)
   if (!has_res) op->tmRes = op->tmA;
   if (!has_raw) op->tmRaw = op->tmA;
@@ -569,8 +595,7 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
   if (p.res && !p.res_f32 && p.out_f32 && p.act != ACT_TAIL) return cudaErrorInvalidConfiguration;  // 16-bit residual with fp32 output: unused combination
   if (t16 && p.ncol_mod % 32) return cudaErrorInvalidConfiguration;
   if ((t16 && p.bn % 32) || (p.act == ACT_GLU && p.bn % 64) || p.bn % 16 || p.bn > 256) return cudaErrorInvalidConfiguration;
-  const int m_tiles = (p.rows_valid + BM - 1) / BM;
-  const int total_tiles = p.batches * m_tiles * (p.n_total / p.bn);
+  const int total_tiles = gemm_m_tiles_total(p) * (p.n_total / p.bn);
   if (total_tiles <= 0) return cudaSuccess;
   const int grid = total_tiles < g_num_sms ? total_tiles : g_num_sms;
   const int threads = 64 + 32 * p.epi_warps;

@@ -70,7 +70,7 @@ int tmap_init();
 int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16);
 // general 3-D map: element type 0 = fp16, 1 = bf16, 2 = fp32; strides in elements
 int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1, uint64_t stride2,
-                         uint32_t box0, uint32_t box1);
+                         uint32_t box0, uint32_t box1, uint32_t box2 = 1);
 int gemm_stage_count(const GemmParams& p);
 cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream);
 

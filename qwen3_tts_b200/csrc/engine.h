@@ -150,6 +150,8 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
 int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
                            long long wav_stride, int skip, cudaStream_t s);
 void engine_free(Engine* e);
+void prof_reset(Engine* e, size_t nops);
+void prof_account(Engine* e, const Op& op);
 int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);
 int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long long* codes, long long sb, long long sk, long long st, int P, float* wav,
                        long long wav_stride, int32_t* n_valid, cudaStream_t s);

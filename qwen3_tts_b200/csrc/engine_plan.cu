@@ -272,19 +272,48 @@ int engine_get_plan(Engine* e, int B, int T, Plan** out) {
   return 0;
 }
 
+void prof_reset(Engine* e, size_t nops) {
+  while (e->prof_events.size() < 2 * nops) {
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    e->prof_events.push_back(ev);
+  }
+  e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear(); e->prof_dims.clear();
+}
+
+// algorithmic FLOPs and minimum HBM bytes of one op, appended to the profile of the current run
+void prof_account(Engine* e, const Op& op) {
+  double fl = 0.0, by = 0.0;
+  int dims[4] = {op.B * (op.L > 0 ? op.L : 1), op.C, 0, 0};
+  if (op.type == OP_GEMM || op.type == OP_TAIL) {
+    const GemmParams& p = op.g.p;
+    const double rows = (double)p.batches * p.rows_valid;
+    dims[0] = p.batches * p.rows_valid; dims[1] = p.n_total; dims[2] = p.cin; dims[3] = p.ntaps;
+    fl = 2.0 * rows * p.n_total * p.cin * p.ntaps;
+    by = 2.0 * ((double)p.batches * p.rows * p.cin + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
+    const double outw = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
+    if (p.out_raw) by += 2.0 * rows * outw;
+    if (p.out_snake) by += 2.0 * rows * outw;
+    if (p.out_f32) by += 4.0 * rows * outw;
+    if (p.res) by += (p.res_f32 ? 4.0 : 2.0) * rows * outw;
+  } else if (op.type == OP_UNIT) {
+    const double rows = (double)op.B * op.L, C = op.C;
+    dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
+    fl = 2.0 * rows * C * C * 8.0;
+    by = 2.0 * (4.0 * rows * C + 8.0 * C * C);  // a1 + x in, y + snake(y) out, weights once
+  }
+  e->prof_type.push_back((int)op.type);
+  e->prof_flops.push_back(fl);
+  e->prof_bytes.push_back(by);
+  for (int d = 0; d < 4; ++d) e->prof_dims.push_back(dims[d]);
+}
+
 int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
                int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s) {
   const q3tts_config& c = e->cfg;
   size_t pi = 0;
   static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
-  if (e->profile) {
-    while (e->prof_events.size() < 2 * plan->ops.size()) {
-      cudaEvent_t ev;
-      cudaEventCreate(&ev);
-      e->prof_events.push_back(ev);
-    }
-    e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear(); e->prof_dims.clear();
-  }
+  if (e->profile) prof_reset(e, plan->ops.size());
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
@@ -310,29 +339,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
     if (sync_each) cudaStreamSynchronize(s);
     if (e->profile) {
       cudaEventRecord(e->prof_events[2 * pi + 1], s);
-      double fl = 0.0, by = 0.0;
-      int dims[4] = {op.B * (op.L > 0 ? op.L : 1), op.C, 0, 0};
-      if (op.type == OP_GEMM || op.type == OP_TAIL) {
-        const GemmParams& p = op.g.p;
-        const double rows = (double)p.batches * p.rows_valid;
-        dims[0] = p.batches * p.rows_valid; dims[1] = p.n_total; dims[2] = p.cin; dims[3] = p.ntaps;
-        fl = 2.0 * rows * p.n_total * p.cin * p.ntaps;
-        by = 2.0 * ((double)p.batches * p.rows * p.cin + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
-        const double outw = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
-        if (p.out_raw) by += 2.0 * rows * outw;
-        if (p.out_snake) by += 2.0 * rows * outw;
-        if (p.out_f32) by += 4.0 * rows * outw;
-        if (p.res) by += (p.res_f32 ? 4.0 : 2.0) * rows * outw;
-      } else if (op.type == OP_UNIT) {
-        const double rows = (double)op.B * op.L, C = op.C;
-        dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
-        fl = 2.0 * rows * C * C * 8.0;
-        by = 2.0 * (4.0 * rows * C + 8.0 * C * C);  // a1 + x in, y + snake(y) out, weights once
-      }
-      e->prof_type.push_back((int)op.type);
-      e->prof_flops.push_back(fl);
-      e->prof_bytes.push_back(by);
-      for (int d = 0; d < 4; ++d) e->prof_dims.push_back(dims[d]);
+      prof_account(e, op);
       ++pi;
     }
     if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(err));

@@ -272,8 +272,11 @@ int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long lo
   float* tail_out = identity_rows ? wav : plan->wav_tmp;
   const long long tail_stride = identity_rows ? wav_stride : plan->out_len;
   static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debugging: attribute an asynchronous fault to its op
+  size_t pi = 0;
+  if (e->profile) prof_reset(e, plan->ops.size());  // the profile holds the last plan that ran
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
+    if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
     switch (op.type) {
       case OP_STATE_LOAD:
         err = stream_state_copy(plan->d_descs, (int)plan->descs.size(), e->stream_state, e->state_bytes, d_ids, plan->S, 0, s);
@@ -303,6 +306,11 @@ int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long lo
       default: break;
     }
     ++e->launches;
+    if (e->profile) {
+      cudaEventRecord(e->prof_events[2 * pi + 1], s);
+      prof_account(e, op);
+      ++pi;
+    }
     if (err == cudaSuccess && sync_each) err = cudaStreamSynchronize(s);
     if (err != cudaSuccess)
       return e->fail(Q3TTS_CUDA_ERROR, "stream launch failed (op " + std::to_string(&op - plan->ops.data()) + " type " + std::to_string((int)op.type) + " S " +

@@ -42,6 +42,11 @@ struct GemmParams {
   int tail_skip;
   int epi_warps;  // 4 or 8 epilogue warps (8: two per TMEM lane quadrant)
   int res_depth;  // residual prefetch ring depth per warp (2, 4 or 8 slots)
+  // Packed tiles (streaming steps: many batch items with few rows each).  A 128-row tile is four 32-row chunks; chunk gc maps to
+  //   mode 1 (rows_valid <= 16, padded to a power of two 1 << pack_rshift): 32 >> pack_rshift whole batch items, rows [0, 1 << pack_rshift)
+  //   mode 2: batch item gc / pack_cpb, rows [(gc % pack_cpb) * 32, +32)
+  // so a tile is filled with real rows instead of one batch item's few rows plus padding.  0 = one batch item per tile.
+  int pack_mode, pack_rshift, pack_cpb;
   int dbg;  // debug experiments (env Q3TTS_DBG): bit 0 = epilogue only drains TMEM, bit 1 = MMA thread issues no MMAs
   const float* bias;
   const float* scale;
@@ -60,5 +65,21 @@ struct GemmParams {
   const void* a_ptr;
   const void* w_ptr;
 };
+
+// number of 128-row tiles over all batch items
+__host__ __device__ inline int gemm_m_tiles_total(const GemmParams& p) {
+  if (p.pack_mode == 1) {
+    const int per_chunk = 32 >> p.pack_rshift;
+    return ((p.batches + per_chunk - 1) / per_chunk + 3) / 4;
+  }
+  if (p.pack_mode == 2) return (p.batches * p.pack_cpb + 3) / 4;
+  return p.batches * ((p.rows_valid + 127) / 128);
+}
+// 32-row chunk q of packed tile `mtile` -> first accumulator row and first batch item
+__host__ __device__ inline void gemm_chunk_coords(const GemmParams& p, int mtile, int q, int& row0, int& b) {
+  const int gc = mtile * 4 + q;
+  if (p.pack_mode == 1) { row0 = 0; b = gc << (5 - p.pack_rshift); }
+  else { b = gc / p.pack_cpb; row0 = (gc - b * p.pack_cpb) * 32; }
+}
 
 }  // namespace q3

@@ -100,7 +100,9 @@ struct EpiWarp {
       ts.decode(tile, nt, mt, b);
       const uint32_t slot = rb_issue & (rd - 1);
       mbar_expect_tx(&rbar[slot], kEpiSlot);
-      tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, (mt * mt_mul + mt_add) * 128 + quad * 32, b);
+      int row0 = (mt * mt_mul + mt_add) * 128 + quad * 32;
+      if (p.pack_mode) gemm_chunk_coords(p, b, quad, row0, b);
+      tma_load_3d(eb + slot * kEpiSlot, tmRes, &rbar[slot], nt * p.bn + pf_item * item_units * 16, row0, b);
     }
     ++rb_issue;
     pf_item += nsplit;
@@ -338,7 +340,8 @@ struct EpiWarp {
 
   // one accumulator tile: t0 = TMEM address of (this warp's lane quadrant, first column of the tile)
   __device__ __forceinline__ void tile(uint32_t t0, int it, int nt, int mt, int b) {
-    const int row0 = mt * 128 + quad * 32;
+    int row0 = mt * 128 + quad * 32;
+    if (p.pack_mode) gemm_chunk_coords(p, b, quad, row0, b);  // packed tiles: the scheduler's "batch" is the tile index
     if (p.dbg & 1) {
       uint32_t r[16];
       for (int u = half; u < units; u += nsplit) { tmem_ld16(t0 + u * 16, r); tmem_ld_wait(); }
