@@ -511,15 +511,6 @@ static void plan_variant(GemmOp* op, int allow) {
 // Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths), choose the kernel
 // variant and (for the weight-stationary variant) rebuild the activation map with a slab-sized box.
 int gemm_make_epilogue_maps(GemmOp* op, int allow) {
-  {
-    GemmParams& q = op->p;
-    const char* ew = getenv("Q3TTS_EPI_WARPS");
-    q.epi_warps = ew ? atoi(ew) : 8;
-    if (q.epi_warps != 4 && q.epi_warps != 8) q.epi_warps = 8;
-    q.res_depth = q.res ? 4 : 0;
-    // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
-    if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
-  }
   {  // packed tiles when a batch item's rows would fill less than 60 % of its 128-row tiles
     GemmParams& q = op->p;
     q.pack_mode = 0; q.pack_rshift = 0; q.pack_cpb = 1;
@@ -533,6 +524,34 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
         q.pack_cpb = (q.rows_valid + 31) / 32;
       }
     }
+    // Small-M steps: a handful of 128 x bn tiles leaves most SMs idle and each CTA walks all of K alone, so shrink the N tile
+    // until the grid covers the SMs (the A panel is re-read from L2 by more CTAs, which is cheap at these sizes).
+    if (op->retile && q.act != ACT_TAIL && !getenv("Q3TTS_NO_RETILE")) {
+      const int step = q.act == ACT_GLU ? 64 : ((q.out_raw || q.out_snake || (q.res && !q.res_f32)) ? 32 : 16);
+      const int mtt = gemm_m_tiles_total(q);
+      // cost model (operand-load bound): waves over the SMs x bytes a CTA loads per K block
+      int best = q.bn;
+      long long best_cost = -1;
+      for (int bn = q.bn; bn >= step; bn -= step) {
+        if (q.n_total % bn) continue;
+        const long long tiles = (long long)mtt * (q.n_total / bn);
+        const long long cost = ((tiles + g_num_sms - 1) / g_num_sms) * (BM + bn);
+        if (best_cost < 0 || cost < best_cost) { best = bn; best_cost = cost; }
+      }
+      if (best != q.bn) {
+        q.bn = best;
+        if (make_tmap_3d(&op->tmB, q.w_ptr, (uint64_t)q.cin, (uint64_t)q.n_total, (uint64_t)q.ntaps, (uint32_t)q.kb, (uint32_t)q.bn, q.bf16 != 0)) return -3;
+      }
+    }
+  }
+  {
+    GemmParams& q = op->p;
+    const char* ew = getenv("Q3TTS_EPI_WARPS");
+    q.epi_warps = ew ? atoi(ew) : 8;
+    if (q.epi_warps != 4 && q.epi_warps != 8) q.epi_warps = 8;
+    q.res_depth = q.res ? 4 : 0;
+    // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
+    if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
   }
   const GemmParams& p = op->p;
   const int et = p.bf16 ? 1 : 0;

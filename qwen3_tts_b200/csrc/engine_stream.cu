@@ -46,6 +46,7 @@ struct SBuilder {
     plan->ops.emplace_back();
     Op& op = plan->ops.back();
     op.type = OP_GEMM;
+    op.g.retile = 1;
     GemmParams& p = op.g.p;
     memset(&p, 0, sizeof(p));
     p.batches = batches; p.rows = a_rows; p.a_row0 = a_row0; p.rows_valid = rows_valid;
