@@ -133,8 +133,10 @@ def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup:
 
     from qwen3_tts_b200.synthetic import make_codes
     total = warmup + steps
-    codes_h = make_codes(streams, total * packet, cfg, seed=77).transpose(1, 2).contiguous()    # [S,Q,T]
-    pk_h = [codes_h[:, :, i * packet:(i + 1) * packet].contiguous().pin_memory() for i in range(total)]
+    frames = 1000                                                                                   # SURVEY cfg 3: (256, 16, 1000) seeded codes, cycled
+    codes_h = make_codes(streams, frames, cfg, seed=77).transpose(1, 2).contiguous()               # [S,Q,1000]
+    ring = [codes_h[:, :, t:t + packet].contiguous().pin_memory() for t in range(0, frames - packet + 1, packet)]
+    pk_h = [ring[i % len(ring)] for i in range(total)]
     pk_d = torch.empty_like(pk_h[0], device=dev)
     wav_d = torch.empty((streams, packet * 1920), dtype=torch.float32, device=dev)
     wav_h = torch.empty((streams, packet * 1920), dtype=torch.float32).pin_memory()
@@ -214,7 +216,7 @@ def main():
     dec = model.decoder
     if args.stream_only:
         dec.reserve_streams(args.streams, 4)
-        out = {"streaming": [stream_latency(dec, cfg, dev, args.streams, P, steps=200, warmup=40) for P in (1, 2, 4)]}
+        out = {"streaming": [stream_latency(dec, cfg, dev, args.streams, P, steps=2000 // P, warmup=200 // P) for P in (1, 2, 4)]}
         print(json.dumps(out), flush=True)
         return
     dec.reserve(B_UTT * T_FRAMES)
@@ -308,7 +310,8 @@ def main():
     if not args.no_streaming and world == 1:
         # BASELINE config 3 rides along as its own section: it is a latency, not the throughput metric of this line
         dec.reserve_streams(args.streams, 4)
-        line["streaming"] = [stream_latency(dec, cfg, dev, args.streams, P, steps=200, warmup=40) for P in (1, 4)]
+        line["streaming"] = [stream_latency(dec, cfg, dev, args.streams, 1, steps=2000, warmup=200),
+                             stream_latency(dec, cfg, dev, args.streams, 4, steps=500, warmup=50)]
     if not args.no_cpu_baseline and world == 1:
         r = cpu_reference_run(steps=3, warmup=1, utterances=1)
         line["cpu_baseline"] = {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]}
