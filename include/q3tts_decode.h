@@ -98,8 +98,9 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
 
 /* Qwen3TTSTokenizerV2Model.decode + the wrapper's H2D/D2H (modeling :1012-1015, wrapper :329, :364):
  * codes [B,T,Q] int64 in HOST memory (padded with 0 like pad_sequence) -> wav_host [B, wav_stride]
- * fp32 HOST memory, lengths[b] = min((codes[b,:,0] > 0).sum()*upsample, chunked length).  Only the
- * first lengths[b] samples of each row are written.  Synchronises the stream before returning. */
+ * fp32 HOST memory, lengths[b] = min((codes[b,:,0] > 0).sum()*upsample, chunked length).  The first
+ * lengths[b] samples of row b are its waveform; columns up to the longest row's length may be written
+ * too (one strided copy for the batch).  Synchronises the stream before returning. */
 int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
                       void* stream);
 

@@ -119,11 +119,14 @@ int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, 
     // codes are [B,T,Q] here (wrapper layout): strides b = T*Q, k = 1, t = Q
     int rc = chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
     if (rc) return rc;
-    for (int b = 0; b < B; ++b) {
-      if (lengths[b] <= 0) continue;
-      if (lengths[b] > wav_stride) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: wav_stride smaller than an output row");
-      err = cudaMemcpyAsync(wav_host + (size_t)b * wav_stride, e.wav_stage + (size_t)b * total, (size_t)lengths[b] * sizeof(float),
-                            cudaMemcpyDeviceToHost, s);
+    // one strided copy for the whole batch: rows are cut to their length by the caller's views, so the columns between a
+    // row's length and the longest row may be written too (the host buffer has wav_stride >= that many columns per row)
+    long long maxlen = 0;
+    for (int b = 0; b < B; ++b) maxlen = lengths[b] > maxlen ? lengths[b] : maxlen;
+    if (maxlen > wav_stride) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: wav_stride smaller than an output row");
+    if (maxlen > 0) {
+      err = cudaMemcpy2DAsync(wav_host, (size_t)wav_stride * sizeof(float), e.wav_stage, (size_t)total * sizeof(float), (size_t)maxlen * sizeof(float),
+                              (size_t)B, cudaMemcpyDeviceToHost, s);
       if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: D2H: ") + cudaGetErrorString(err));
     }
   }
