@@ -158,6 +158,10 @@ int q3tts_unit_trace(long long* out256);
 
 /* tcgen05.mma issue-rate microbenchmark (design evidence): SM cycles per MMA (M = 128, K = 16, fp16) for an N, operand form
  * (0 = A,B in shared memory, 1 = A in tensor memory), swizzle span (64 / 128 bytes), A row shift, accumulator count, and a tcgen05.commit / mbarrier wait every k groups of 8 MMAs. */
+/* CTA-pair (tcgen05 cta_group::2) building blocks: D[256,n] = A[256,k] . W[n,k]^T on one 2-CTA cluster; ts != 0 also runs
+ * the tensor-memory A operand form (k == n <= 128).  iters > 0: throughput run on every SM pair instead of a comparison.
+ * out4 = {max |D - ref|, max |D2 - ref2|, cycles per M = 256 MMA, 0}. */
+int q3tts_selftest_pair(int device, int n, int k, int iters, int ts, float* out4);
 int q3tts_bench_mma(int device, int n, int span, int a_row_shift, int form, int nacc, int commit_every, int wait_every, float* clk_per_mma);
 
 /* TMA box-shape microbenchmark (design evidence, DESIGN.md "Epilogue boxes"): aggregate GB/s of `warps` warps per SM moving

@@ -1,0 +1,219 @@
+// Self-test and microbenchmark of the CTA-pair (tcgen05 cta_group::2) building blocks used by the paired kernels:
+// cluster launch, TMA loads counted on the leader's mbarrier, M = 256 MMAs (A and B from shared memory, and A from tensor
+// memory), multicast commit, paired TMEM allocation.  D[256, N] = A[256, K] . W[N, K]^T, fp16 in, fp32 out.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include <cuda_fp16.h>
+
+#include "../../include/q3tts_decode.h"
+#include "conv_gemm.h"
+#include "pair_ptx.cuh"
+
+namespace q3 {
+namespace {
+
+struct __align__(8) PairBars {
+  uint64_t full;       // leader: both CTAs' operand tiles have landed
+  uint64_t tfull;      // each CTA: accumulator complete (multicast commit)
+  uint64_t a2_full;    // leader: both CTAs have written their A operand into tensor memory (TS form)
+  uint64_t t2full;     // each CTA: second accumulator complete
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+
+// smem: [kblocks][128 rows][64] A | [kblocks][N/2 rows][64] W half | bars.  192 threads: warp 0 TMA, warp 1 MMA, warps 2..5 epilogue.
+// ts != 0: also D2 = fp16(D) . W2^T through the tensor-memory A operand form (requires K == N: W is reused as W2).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+k_pair_gemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, float* __restrict__ D, float* __restrict__ D2, int N, int K,
+            int iters, int ts, long long* clk) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int kblocks = K / 64;
+  const uint32_t a_sub = 128 * 128, w_sub = (uint32_t)(N / 2) * 128;
+  uint8_t* sA = smem;
+  uint8_t* sW = sA + (size_t)kblocks * a_sub;
+  PairBars* bars = reinterpret_cast<PairBars*>(sW + (size_t)kblocks * w_sub);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;  // every pair computes the same product (the benchmark wants all SMs busy)
+  if (threadIdx.x == 0) {
+    mbar_init(&bars->full, 1);
+    mbar_init(&bars->tfull, 1);
+    mbar_init(&bars->a2_full, 8);  // 4 epilogue warps x 2 CTAs
+    mbar_init(&bars->t2full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) { tmem_alloc2(&bars->tmem_base, 512); tmem_relinquish2(); }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+  const uint32_t c_acc = 0, c_a2 = 256, c_acc2 = 256 + 128;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      const uint32_t lbar = leader_addr(smem_u32(&bars->full));
+      if (rank == 0) mbar_expect_tx(&bars->full, 2u * (uint32_t)kblocks * (a_sub + w_sub));
+      for (int kb = 0; kb < kblocks; ++kb) {
+        tma_load_3d_pair(smem_u32(sA + (size_t)kb * a_sub), &tmA, lbar, kb * 64, (int)rank * 128, 0);
+        tma_load_3d_pair(smem_u32(sW + (size_t)kb * w_sub), &tmW, lbar, kb * 64, (int)rank * (N / 2), 0);
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      const uint32_t idesc = umma_idesc(256, N, false);
+      const uint32_t hi = umma_desc_hi(128);
+      const uint32_t a0 = umma_desc_lo(smem_u32(sA)), w0 = umma_desc_lo(smem_u32(sW));
+      mbar_wait_cluster(&bars->full, 0);
+      tc_fence_after();
+      for (int kb = 0; kb < kblocks; ++kb)
+        for (int k = 0; k < 4; ++k)
+          umma2_f16_lohi(tmem_base + c_acc, a0 + (uint32_t)kb * (a_sub >> 4) + 2 * k, w0 + (uint32_t)kb * (w_sub >> 4) + 2 * k, hi, idesc, (kb | k) != 0);
+      umma2_commit(&bars->tfull);
+      if (ts) {
+        mbar_wait_cluster(&bars->a2_full, 0);
+        tc_fence_after();
+        for (int kb = 0; kb < kblocks; ++kb)
+          for (int k = 0; k < 4; ++k)
+            umma2_f16_ts(tmem_base + c_acc2, tmem_base + c_a2 + (uint32_t)(kb * 32 + 8 * k), w0 + (uint32_t)kb * (w_sub >> 4) + 2 * k, hi, idesc, (kb | k) != 0);
+        umma2_commit(&bars->t2full);
+      }
+      if (iters > 0) {  // throughput: `iters` passes over the same operands, accumulating
+        mbar_wait(&bars->tfull, 0);
+        if (ts) mbar_wait(&bars->t2full, 0);
+        tc_fence_after();
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; ++i)
+          for (int kb = 0; kb < kblocks; ++kb)
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma2_f16_lohi(tmem_base + c_acc, a0 + (uint32_t)kb * (a_sub >> 4) + 2 * k, w0 + (uint32_t)kb * (w_sub >> 4) + 2 * k, hi, idesc, 1);
+        umma2_commit(&bars->full);  // reuse: phase 1 of `full`
+        mbar_wait(&bars->full, 1);
+        const long long t1 = clock64();
+        if (blockIdx.x == 0) clk[0] = t1 - t0;
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const int row = (int)rank * 128 + quad * 32 + lane;
+    mbar_wait(&bars->tfull, 0);
+    tc_fence_after();
+    for (int c = 0; c < N; c += 16) {
+      uint32_t r[16];
+      __syncwarp();
+      tmem_ld16(tmem_base + lane_base + c_acc + c, r);
+      tmem_ld_wait();
+      if (pair == 0)
+        for (int i = 0; i < 16; ++i) D[(size_t)row * N + c + i] = __uint_as_float(r[i]);
+      if (ts) {  // pack fp16 pairs into the A operand columns: column j holds K elements 2j, 2j+1
+        uint32_t pk[8];
+        for (int i = 0; i < 8; ++i) {
+          __half2 h = __floats2half2_rn(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
+          pk[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        tmem_st8(tmem_base + lane_base + c_a2 + (c >> 1), pk);
+      }
+    }
+    if (ts) {
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&bars->a2_full);
+      mbar_wait(&bars->t2full, 0);
+      tc_fence_after();
+      for (int c = 0; c < N; c += 16) {
+        uint32_t r[16];
+        __syncwarp();
+        tmem_ld16(tmem_base + lane_base + c_acc2 + c, r);
+        tmem_ld_wait();
+        if (pair == 0)
+          for (int i = 0; i < 16; ++i) D2[(size_t)row * N + c + i] = __uint_as_float(r[i]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's MMAs read this CTA's shared and tensor memory until the last commit
+  if (warp == 1) { tc_fence_after(); tmem_dealloc2(tmem_base, 512); }
+}
+
+}  // namespace
+}  // namespace q3
+
+using namespace q3;
+
+// out4: [0] max |D - ref|, [1] max |D2 - ref2| (ts form, 0 when not run), [2] cycles per M=256 MMA, [3] unused
+extern "C" int q3tts_selftest_pair(int device, int n, int k, int iters, int ts, float* out4) {
+  if (!out4 || n < 32 || n > 256 || n % 32 || k < 64 || k > 256 || k % 64 || (ts && (k != n || n > 128))) return Q3TTS_BAD_SHAPE;
+  if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
+  if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
+  std::vector<__half> hA((size_t)256 * k), hW((size_t)n * k);
+  uint32_t seed = 12345u;
+  auto rnd = [&]() { seed = seed * 1664525u + 1013904223u; return ((seed >> 9) & 0xFFFF) / 65536.0f - 0.5f; };
+  for (auto& v : hA) v = __float2half_rn(rnd());
+  for (auto& v : hW) v = __float2half_rn(rnd() * 0.25f);
+  __half *dA = nullptr, *dW = nullptr;
+  float *dD = nullptr, *dD2 = nullptr;
+  long long* dclk = nullptr;
+  int rc = Q3TTS_OK;
+  if (cudaMalloc((void**)&dA, hA.size() * 2) != cudaSuccess || cudaMalloc((void**)&dW, hW.size() * 2) != cudaSuccess ||
+      cudaMalloc((void**)&dD, (size_t)256 * n * 4) != cudaSuccess || cudaMalloc((void**)&dD2, (size_t)256 * n * 4) != cudaSuccess ||
+      cudaMalloc((void**)&dclk, 8) != cudaSuccess)
+    rc = Q3TTS_OOM;
+  CUtensorMap tmA, tmW;
+  if (!rc) {
+    cudaMemcpy(dA, hA.data(), hA.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemcpy(dW, hW.data(), hW.size() * 2, cudaMemcpyHostToDevice);
+    cudaMemset(dD, 0, (size_t)256 * n * 4);
+    cudaMemset(dD2, 0, (size_t)256 * n * 4);
+    cudaMemset(dclk, 0, 8);
+    if (make_tmap_3d(&tmA, dA, (uint64_t)k, 256, 1, 64, 128, false) || make_tmap_3d(&tmW, dW, (uint64_t)k, (uint64_t)n, 1, 64, (uint32_t)(n / 2), false))
+      rc = Q3TTS_CUDA_ERROR;
+  }
+  if (!rc) {
+    const size_t smem = (size_t)(k / 64) * (128 * 128 + (n / 2) * 128) + sizeof(PairBars) + 1024;
+    cudaFuncSetAttribute(k_pair_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const int grid = iters > 0 ? (gemm_num_sms() / 2) * 2 : 2;
+    k_pair_gemm<<<grid, 192, smem>>>(tmA, tmW, dD, dD2, n, k, iters, ts, dclk);
+    cudaError_t err = cudaDeviceSynchronize();
+    if (err != cudaSuccess) { fprintf(stderr, "pair selftest: %s\n", cudaGetErrorString(err)); rc = Q3TTS_CUDA_ERROR; }
+  }
+  if (!rc) {
+    std::vector<float> hD((size_t)256 * n), hD2((size_t)256 * n);
+    long long clk = 0;
+    cudaMemcpy(hD.data(), dD, hD.size() * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(hD2.data(), dD2, hD2.size() * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&clk, dclk, 8, cudaMemcpyDeviceToHost);
+    double md = 0.0, md2 = 0.0;
+    std::vector<float> ref((size_t)256 * n);
+    for (int r = 0; r < 256; ++r)
+      for (int c = 0; c < n; ++c) {
+        float acc = 0.f;
+        for (int j = 0; j < k; ++j) acc += __half2float(hA[(size_t)r * k + j]) * __half2float(hW[(size_t)c * k + j]);
+        ref[(size_t)r * n + c] = acc;
+        const double d = fabs((double)acc - hD[(size_t)r * n + c]);
+        if (d > md) md = d;
+      }
+    if (ts) {
+      for (int r = 0; r < 256; ++r)
+        for (int c = 0; c < n; ++c) {
+          float acc = 0.f;
+          for (int j = 0; j < k; ++j) acc += __half2float(__float2half_rn(hD[(size_t)r * n + j])) * __half2float(hW[(size_t)c * k + j]);
+          const double d = fabs((double)acc - hD2[(size_t)r * n + c]);
+          if (d > md2) md2 = d;
+        }
+    }
+    if (iters > 0) md = md2 = -1.0;  // timing runs keep accumulating into D: no comparison
+    out4[0] = (float)md; out4[1] = (float)md2;
+    out4[2] = iters > 0 ? (float)((double)clk / ((double)iters * (k / 64) * 4)) : 0.f;
+    out4[3] = 0.f;
+  }
+  cudaFree(dA); cudaFree(dW); cudaFree(dD); cudaFree(dD2); cudaFree(dclk);
+  return rc;
+}
