@@ -50,7 +50,8 @@ struct UnitOp {
   // streaming (history-prefixed a1 buffer): rows of a1 per batch item, row of output row 0, strides (0 = dense)
   int a_rows = 0, a_row0 = 0;
   long long a_batch_stride = 0, snake_batch_stride = 0;
-  int variant = 0;                    // compiled instance (unit_kernel.cu: 0 = C 96, 1 / 2 = C 192 with 4 / 3 weight stages)
+  int variant = 0;                    // compiled instance (unit_kernel.cu: 0 = C 96, 1 / 2 = C 192 with 4 / 3 weight stages, 3..5 = CTA-pair forms)
+  int pair = 0;                       // 1: CTA-pair form (2-CTA clusters, 256-row tiles, tcgen05 cta_group::2)
   int enabled = 0;
 };
 // Shape test only (no device work): true when unit_make can fuse C channels.

@@ -18,6 +18,7 @@
 // so a C = 96 layer cannot exceed 41 % of the tensor peak in this operand arrangement; the kernel is built to sit on
 // that floor (DESIGN.md "Fused residual unit").
 #include "conv_gemm.h"
+#include "pair_ptx.cuh"
 #include "tc_epilogue.cuh"
 
 #include <cstdio>
@@ -33,7 +34,8 @@ static constexpr int kUnitThreads = 64 + 32 * (kP1Warps + kP2Warps);
 static constexpr int kUMaxSlabs = 6;
 static constexpr int kUMaxStages = 12;
 static constexpr int kURes = 2;                      // residual ring depth per phase-2 warp
-static constexpr int kUSlotsPerWarp = kURes + 2;     // + 1 raw + 1 Snake'd output slot (single-buffered: results wait in registers)
+static constexpr int kUOutBufs = 1;                  // output slot pairs per phase-2 warp: the TMA stores of item i drain while item i+1 is computed
+static constexpr int kUSlotsPerWarp = kURes + 2 * kUOutBufs;  // residual ring + (raw, Snake'd) output slots
 
 struct __align__(8) UnitBarriers {
   uint64_t sfull[kUMaxSlabs], sempty[kUMaxSlabs];
@@ -86,14 +88,19 @@ __device__ __forceinline__ void tma_store_3d_s(const void* map, uint32_t smem_sr
 // Compile-time shape of one fused-unit instance.  Everything the MMA-issuing thread touches is a constant so that its code is
 // straight-line: tools/mma_bench.py shows the tensor pipe retires an N = 96 MMA every 56 cycles and an N = 192 MMA every 96,
 // but only if the single issuing thread spends no more than that per MMA (a passing mbarrier wait alone costs ~180 cycles).
-template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_>
+// PAIR_ = 1: the CTA-pair form.  A 2-CTA cluster works on 256-row tiles with one M = 256 tcgen05.mma.cta_group::2 stream issued by
+// the even CTA; each CTA keeps its own 128 rows (slab, tensor memory, phase-1/2 warps) and loads only HALF of every weight stage
+// (its C/2 output channels).  Weight re-streaming is what bounds the single-CTA form (C = 192: 590 KB of weights per 128-row tile
+// against ~43 B/clk of L2->SM fill), so halving it per SM is the point.
+template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0>
 struct UnitCfg {
-  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_;
+  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_;
   static constexpr int NKB = C / KB, NKG = NKB / KS, KSTEPS = KB / 16;
   static constexpr int SPAN = KB * 2;
   static constexpr int M1_STAGES = NKG * 7, M2_STAGES = NKG, TILE_STAGES = M1_STAGES + M2_STAGES;
-  static constexpr uint32_t WSUB = C * SPAN, STAGE_BYTES = KS * WSUB;
-  static_assert(TILE_STAGES % NST == 0 && (TILE_STAGES / NST) % 2 == 0, "weight ring slots and parities must be static per tile");
+  static constexpr uint32_t WSUB = (PAIR ? C / 2 : C) * SPAN, STAGE_BYTES = KS * WSUB;  // bytes this CTA holds
+  static_assert(TILE_STAGES % NST == 0, "weight ring slots must be static per tile");
+  static constexpr bool PAR_FLIPS = (TILE_STAGES / NST) % 2 != 0;  // ring parity alternates from tile to tile (else it is static too)
   static_assert(NKG % NSL == 0 || NSL % NKG == 0, "slab ring");
   static_assert(NBUF == 1 || 5 * C / 2 <= 256, "two TMEM stages need 2.5*C <= 256 columns");
 };
@@ -104,11 +111,17 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw, const __grid_constant__ CUtensorMap tmSnake,
             const GemmParams p, const UnitArgs u) {
   constexpr int C = Cfg::C, KB = Cfg::KB, KS = Cfg::KS, NST = Cfg::NST, NSL = Cfg::NSL, NBUF = Cfg::NBUF, NKG = Cfg::NKG, KSTEPS = Cfg::KSTEPS;
+  constexpr bool PAIR = Cfg::PAIR != 0;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;               // 0 = leader (issues the MMAs of both CTAs)
+  const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;  // worker (CTA or CTA pair) index
+  const int nworkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  constexpr uint32_t NCTA = PAIR ? 2u : 1u;
   constexpr uint32_t span = Cfg::SPAN, wsub = Cfg::WSUB, stage_bytes = Cfg::STAGE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int halo = 6 * u.dil;
-  constexpr int TM = U_BM;
+  constexpr int TM = PAIR ? 2 * U_BM : U_BM;  // rows of a scheduler tile
+  const int rrow = rank * U_BM;               // this CTA's rows inside a tile
   const uint32_t ssub = u.srows * span;  // one K block of a slab
   const uint32_t slab_bytes = KS * ssub;
   uint8_t* wst = smem;                                   // weight ring first: its slot addresses are compile-time offsets
@@ -119,7 +132,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (p.rows_valid + TM - 1) / TM;
   const int total_tiles = p.batches * m_tiles;
-  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int my_tiles = total_tiles > wid ? (total_tiles - wid + nworkers - 1) / nworkers : 0;
   constexpr int grp_warps = NBUF == 2 ? 4 : 8;  // epilogue warps that serve one TMEM stage
 
   if (threadIdx.x == 0) {
@@ -128,8 +141,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     for (int s = 0; s < NSL; ++s) { mbar_init(&bars->sfull[s], 1); mbar_init(&bars->sempty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps);
-      mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], grp_warps);
+      mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps * NCTA);  // pair: both CTAs' warps arrive on the leader's copy
+      mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], grp_warps * NCTA);
     }
     for (int w = 0; w < kP2Warps; ++w)
       for (int s = 0; s < kURes; ++s) mbar_init(&bars->res_bar[w][s], 1);
@@ -139,9 +152,13 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     prm[i] = u.bias7[i]; prm[C + i] = u.s2a[i]; prm[2 * C + i] = u.s2ib[i];
     prm[3 * C + i] = p.bias ? p.bias[i] : 0.f; prm[4 * C + i] = p.snake_a[i]; prm[5 * C + i] = p.snake_ib[i];
   }
-  if (warp == 1) { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+  if (warp == 1) {
+    if (PAIR) { tmem_alloc2(&bars->tmem_base, 512); tmem_relinquish2(); }
+    else { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
+  }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_base;
   // TMEM column map inside one stage; stage s starts at column s * 256
@@ -152,22 +169,29 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (elect_one()) {
       int ss = 0, ws = 0; uint32_t sph = 0, wph = 0;
       const int boxrows = u.srows / u.nbox;
+      // pair: every load lands in this CTA's shared memory but is counted on the LEADER's full barrier (it issues the MMAs);
+      // the leader expects both CTAs' bytes.  The empty barriers are per CTA (multicast commit by the leader's MMA thread).
+      auto load = [&](uint8_t* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_pair(smem_u32(dst), map, leader_addr(smem_u32(bar)), c0, c1, c2);
+        else tma_load_3d(dst, map, bar, c0, c1, c2);
+      };
+      const int wrow = PAIR ? rank * (C / 2) : 0;  // this CTA's output-channel rows of a weight stage
       auto load_m1 = [&](int j) {  // slabs and W7 stages of this CTA's j-th tile
-        const int tile = (int)blockIdx.x + j * (int)gridDim.x;
+        const int tile = wid + j * nworkers;
         const int b = tile / m_tiles, mt = tile - b * m_tiles;
         for (int kg = 0; kg < NKG; ++kg) {
           mbar_wait(&bars->sempty[ss], sph ^ 1);
-          mbar_expect_tx(&bars->sfull[ss], slab_bytes);
+          if (rank == 0) mbar_expect_tx(&bars->sfull[ss], slab_bytes * NCTA);
           for (int kk = 0; kk < KS; ++kk)
             for (int bx = 0; bx < u.nbox; ++bx)
-              tma_load_3d(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
-                          (kg * KS + kk) * KB, mt * TM - halo + u.a_row0 + bx * boxrows, b);
+              load(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
+                   (kg * KS + kk) * KB, mt * TM + rrow - halo + u.a_row0 + bx * boxrows, b);
           if (++ss == NSL) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < 7; ++tap) {
             mbar_wait(&bars->wempty[ws], wph ^ 1);
-            mbar_expect_tx(&bars->wfull[ws], stage_bytes);
+            if (rank == 0) mbar_expect_tx(&bars->wfull[ws], stage_bytes * NCTA);
             for (int kk = 0; kk < KS; ++kk)
-              tma_load_3d(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW7, &bars->wfull[ws], (kg * KS + kk) * KB, 0, tap);
+              load(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW7, &bars->wfull[ws], (kg * KS + kk) * KB, wrow, tap);
             if (++ws == NST) { ws = 0; wph ^= 1; }
           }
         }
@@ -175,9 +199,9 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       auto load_m2 = [&]() {
         for (int kg = 0; kg < NKG; ++kg) {
           mbar_wait(&bars->wempty[ws], wph ^ 1);
-          mbar_expect_tx(&bars->wfull[ws], stage_bytes);
+          if (rank == 0) mbar_expect_tx(&bars->wfull[ws], stage_bytes * NCTA);
           for (int kk = 0; kk < KS; ++kk)
-            tma_load_3d(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW1, &bars->wfull[ws], (kg * KS + kk) * KB, 0, 0);
+            load(wst + (size_t)ws * stage_bytes + (size_t)kk * wsub, &tmW1, &bars->wfull[ws], (kg * KS + kk) * KB, wrow, 0);
           if (++ws == NST) { ws = 0; wph ^= 1; }
         }
       };
@@ -190,8 +214,15 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread, straight-line per tile)
-    if (elect_one()) {
-      const uint32_t idesc = umma_idesc(U_BM, C, p.bf16 != 0);
+    if (rank == 0 && elect_one()) {
+      const uint32_t idesc = umma_idesc(PAIR ? 2 * U_BM : U_BM, C, p.bf16 != 0);
+      auto mma_ss = [&](uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t hi_, uint32_t acc) {
+        if (PAIR) umma2_f16_lohi(d, a_lo, b_lo, hi_, idesc, acc); else umma_f16_lohi(d, a_lo, b_lo, hi_, idesc, acc);
+      };
+      auto mma_ts = [&](uint32_t d, uint32_t a_t, uint32_t b_lo, uint32_t hi_, uint32_t acc) {
+        if (PAIR) umma2_f16_ts(d, a_t, b_lo, hi_, idesc, acc); else umma_f16_ts(d, a_t, b_lo, hi_, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) { if (PAIR) umma2_commit(bar); else umma_commit(bar); };  // pair: arrives in both CTAs
       const uint32_t hi = umma_desc_hi(span);
       const uint32_t w_lo0 = umma_desc_lo(smem_u32(wst));
       const uint32_t s_lo0 = umma_desc_lo(smem_u32(slabs)), s_off = slab_bytes >> 4, sk_off = ssub >> 4;
@@ -199,7 +230,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // `g` = index of a weight stage inside the (prologue + steady-state) sequence; slot and parity follow from it at compile time
       // MMA1 of this CTA's j-th tile: dilated conv7 into acc1 of TMEM stage j % NBUF (free: a2_full of tile j - NBUF was waited
       // on before its MMA2, which was issued earlier).  G0 = first weight-stage index of this call.
-      auto mma1 = [&](int j, auto g0_tag) {
+      auto mma1 = [&](int j, auto g0_tag, uint32_t flip) {
         constexpr int G0 = decltype(g0_tag)::value;
         const uint32_t d = tmem_base + (uint32_t)((j % NBUF) * 256) + c_acc1;
         UTRACE(j, 0);
@@ -215,66 +246,66 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           for (int tap = 0; tap < 7; ++tap) {
             const int g = G0 + kg * 7 + tap;          // compile-time after unrolling
             const int ws = g % NST;
-            const uint32_t par = (uint32_t)(g / NST) & 1u;
+            const uint32_t par = ((uint32_t)(g / NST) & 1u) ^ flip;
             if (!ready) mbar_wait(&bars->wfull[ws], par);
             // poll the next tap's stage now: the ~180-cycle latency of a passing mbarrier test then overlaps the MMA issue below
-            if (tap + 1 < 7 && !(p.dbg & 256)) ready = mbar_try_wait(&bars->wfull[(g + 1) % NST], (uint32_t)((g + 1) / NST) & 1u);
+            if (tap + 1 < 7 && !(p.dbg & 256)) ready = mbar_try_wait(&bars->wfull[(g + 1) % NST], ((uint32_t)((g + 1) / NST) & 1u) ^ flip);
             const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
             const uint32_t at = slab + (uint32_t)tap * tap_step;
 #pragma unroll
             for (int kk = 0; kk < KS; ++kk) {
 #pragma unroll
               for (int k = 0; k < KSTEPS; ++k)
-                umma_f16_lohi(d, at + (uint32_t)kk * sk_off + 2 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, idesc, (kg | tap | kk | k) != 0);
+                mma_ss(d, at + (uint32_t)kk * sk_off + 2 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, (kg | tap | kk | k) != 0);
             }
-            umma_commit(&bars->wempty[ws]);
+            commit(&bars->wempty[ws]);
           }
-          umma_commit(&bars->sempty[sl]);
+          commit(&bars->sempty[sl]);
         }
-        umma_commit(&bars->acc1_full[j % NBUF]);
+        commit(&bars->acc1_full[j % NBUF]);
         UTRACE(j, 2);
       };
       // MMA2: 1x1 conv, A = Snake'd conv7 output packed in tensor memory by the phase-1 warps
-      auto mma2 = [&](int j, auto g0_tag) {
+      auto mma2 = [&](int j, auto g0_tag, uint32_t flip) {
         constexpr int G0 = decltype(g0_tag)::value;
         const int sb = j % NBUF;
         const uint32_t use = (uint32_t)(j / NBUF);  // how many times this TMEM stage has been used before
         const uint32_t st = tmem_base + (uint32_t)(sb * 256);
-        mbar_wait_backoff(&bars->a2_full[sb], use & 1);
+        if (PAIR) mbar_wait_cluster(&bars->a2_full[sb], use & 1); else mbar_wait_backoff(&bars->a2_full[sb], use & 1);
         UTRACE(j, 3);
-        mbar_wait_backoff(&bars->acc2_empty[sb], (use & 1) ^ 1);
+        if (PAIR) mbar_wait_cluster(&bars->acc2_empty[sb], (use & 1) ^ 1); else mbar_wait_backoff(&bars->acc2_empty[sb], (use & 1) ^ 1);
         tc_fence_after();
         UTRACE(j, 4);
 #pragma unroll
         for (int kg = 0; kg < NKG; ++kg) {
           const int g = G0 + kg;
           const int ws = g % NST;
-          const uint32_t par = (uint32_t)(g / NST) & 1u;
+          const uint32_t par = ((uint32_t)(g / NST) & 1u) ^ flip;
           mbar_wait(&bars->wfull[ws], par);
           const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
 #pragma unroll
           for (int kk = 0; kk < KS; ++kk) {
 #pragma unroll
             for (int k = 0; k < KSTEPS; ++k)
-              umma_f16_ts(st + c_acc2, st + c_a2 + (uint32_t)((kg * KS + kk) * (KB / 2)) + 8 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, idesc,
-                          (kg | kk | k) != 0);
+              mma_ts(st + c_acc2, st + c_a2 + (uint32_t)((kg * KS + kk) * (KB / 2)) + 8 * k, wb + (uint32_t)kk * (wsub >> 4) + 2 * k, hi, (kg | kk | k) != 0);
           }
-          umma_commit(&bars->wempty[ws]);
+          commit(&bars->wempty[ws]);
         }
-        umma_commit(&bars->acc2_full[sb]);
+        commit(&bars->acc2_full[sb]);
         UTRACE(j, 5);
       };
       // Weight-stage indices: prologue MMA1(0) uses [0, M1); steady state per tile is TILE_STAGES stages, so the index modulo
       // (2 * NST) -- all the slot / parity arithmetic needs -- is the same in every iteration (TILE_STAGES % (2*NST) == 0).
       constexpr int M1S = Cfg::M1_STAGES;
-      if (my_tiles > 0) mma1(0, std::integral_constant<int, 0>{});
+      if (my_tiles > 0) mma1(0, std::integral_constant<int, 0>{}, 0u);
       for (int j = 0; j < my_tiles; ++j) {
+        const uint32_t flip = Cfg::PAR_FLIPS ? (uint32_t)(j & 1) : 0u;  // global stage index = j * TILE_STAGES + (index inside the iteration)
         if (NBUF == 2) {
-          if (j + 1 < my_tiles) { mma1(j + 1, std::integral_constant<int, M1S>{}); mma2(j, std::integral_constant<int, 2 * M1S>{}); }
-          else mma2(j, std::integral_constant<int, M1S>{});
+          if (j + 1 < my_tiles) { mma1(j + 1, std::integral_constant<int, M1S>{}, flip); mma2(j, std::integral_constant<int, 2 * M1S>{}, flip); }
+          else mma2(j, std::integral_constant<int, M1S>{}, flip);
         } else {
-          mma2(j, std::integral_constant<int, M1S>{});
-          if (j + 1 < my_tiles) mma1(j + 1, std::integral_constant<int, M1S + Cfg::M2_STAGES>{});
+          mma2(j, std::integral_constant<int, M1S>{}, flip);
+          if (j + 1 < my_tiles) mma1(j + 1, std::integral_constant<int, M1S + Cfg::M2_STAGES>{}, flip);
         }
       }
     }
@@ -319,7 +350,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->a2_full[sb]);
+      if (lane == 0) { if (PAIR) mbar_arrive_leader(&bars->a2_full[sb]); else mbar_arrive(&bars->a2_full[sb]); }
       if (quad == 2 && lane == 0) UTRACE(j, 7);
     }
   } else {
@@ -330,7 +361,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     constexpr int nitems = ncols >> 5;
     const uint32_t tcol = NBUF == 2 ? 0u : (uint32_t)(grp * ncols);
     const int pcol0 = NBUF == 2 ? 0 : grp * ncols;
-    const int rsub = quad * 32;  // row offset of this warp inside a tile
+    const int rsub = rrow + quad * 32;  // row offset of this warp inside a tile
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const uint32_t acc = tmem_base + lane_base + (NBUF == 2 ? (uint32_t)(grp * 256) : 0u) + c_acc2 + tcol;
     const uint32_t prm_s = smem_u32(prm);
@@ -345,9 +376,9 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int pf_j = j0, pf_item = 0;
     uint32_t issued = 0, cons = 0, ob = 0;
     auto prefetch = [&]() {
-      if (pf_j >= my_tiles) return;
+      if (pf_j >= my_tiles || (p.dbg & 128)) return;
       if (lane == 0) {
-        const int tile = (int)blockIdx.x + pf_j * (int)gridDim.x;
+        const int tile = wid + pf_j * nworkers;
         const int b = tile / m_tiles, mt = tile - b * m_tiles;
         const uint32_t slot = issued & (kURes - 1);
         const uint32_t bar = rbar + slot * 8u;
@@ -359,7 +390,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     };
     for (int i = 0; i < kURes; ++i) prefetch();
     for (int j = j0; j < my_tiles; j += NBUF) {
-      const int tile = (int)blockIdx.x + j * (int)gridDim.x;
+      const int tile = wid + j * nworkers;
       const int b = tile / m_tiles, mt = tile - b * m_tiles;
       const int row0 = mt * TM + rsub;
       mbar_wait(&bars->acc2_full[sb], (uint32_t)(j / NBUF) & 1);
@@ -367,13 +398,13 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (quad == 2 && lane == 0) UTRACE(j, 8);
       for (int item = 0; item < nitems; ++item) {
         const uint32_t slot = cons & (kURes - 1);
-        mbar_wait(&bars->res_bar[pw][slot], (cons / kURes) & 1);
+        if (!(p.dbg & 128)) mbar_wait(&bars->res_bar[pw][slot], (cons / kURes) & 1);  // debug bit 7: phase 2 without residual loads
         const uint32_t rs = eb + slot * kEpiSlot;
         uint4 res[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) res[c] = lds_u4(rs + off[c]);
         ++cons;
-        const uint32_t raw_s = eb + kURes * kEpiSlot, snk_s = eb + (kURes + 1) * kEpiSlot;
+        const uint32_t raw_s = eb + (kURes + 2 * (ob & (kUOutBufs - 1))) * kEpiSlot, snk_s = raw_s + kEpiSlot;
         // asynchronous TMEM loads and their wait stay adjacent: nothing may touch the destination registers in between
         uint32_t ra[16], rb[16];
         __syncwarp();  // .sync.aligned: reconverge after the lane-0 branch in prefetch()
@@ -398,19 +429,24 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(snake(y2, a.z, ib.z), snake(y3, a.w, ib.w));
           }
         }
-        if (lane == 0) tma_store_wait_read<0>();  // the previous item's stores have read the output slots (long done: they overlap the math above)
-        __syncwarp();
+        const bool do_store = !(p.dbg & 64);  // debug: phase 2 without its output stores
+        if (do_store) {
+          if (lane == 0) tma_store_wait_read<kUOutBufs - 1>();  // the stores that last used this slot pair have read it
+          __syncwarp();
+        }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           sts_u4(raw_s + off[c], oraw[4 * c], oraw[4 * c + 1], oraw[4 * c + 2], oraw[4 * c + 3]);
           sts_u4(snk_s + off[c], osnk[4 * c], osnk[4 * c + 1], osnk[4 * c + 2], osnk[4 * c + 3]);
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
-          tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
-          tma_store_commit();
+        if (do_store) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
+            tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
+            tma_store_commit();
+          }
         }
         // refill the residual slot only now: the st.shared above consumed the residual registers (in-order issue), so every
         // ld.shared of the slot has returned and the __syncwarp() above covers all lanes
@@ -419,16 +455,17 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->acc2_empty[sb]);
+      if (lane == 0) { if (PAIR) mbar_arrive_leader(&bars->acc2_empty[sb]); else mbar_arrive(&bars->acc2_empty[sb]); }
       if (quad == 2 && lane == 0) UTRACE(j, 9);
     }
     if (lane == 0) tma_store_wait<0>();
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the leader's MMAs read the peer's shared and tensor memory until its last commit
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -436,10 +473,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 using Cfg96 = UnitCfg<96, 32, 3, 4, 2, 2>;       // one weight stage = one tap over all of K (18 KB), whole-tile slabs, two TMEM stages
 using Cfg192a = UnitCfg<192, 64, 1, 4, 3, 1>;    // stage = (K block, tap) 24 KB; 4 stages when the slabs are small (dilation 1, 3)
 using Cfg192b = UnitCfg<192, 64, 1, 3, 3, 1>;    // 3 stages for the dilation-9 slabs
+// CTA-pair forms (variants 3..5): half-size weight stages (9 KB / 12 KB), so the ring can be deeper
+using Cfg96p = UnitCfg<96, 32, 3, 8, 2, 2, 1>;
+using Cfg192pa = UnitCfg<192, 64, 1, 6, 3, 1, 1>;
+using Cfg192pb = UnitCfg<192, 64, 1, 4, 3, 1, 1>;
 
 static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
-  return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * op.C * span + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot +
+  return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * (op.pair ? op.C / 2 : op.C) * span + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot +
          (size_t)6 * op.C * sizeof(float) + sizeof(UnitBarriers) + 1024;
 }
 
@@ -467,8 +508,13 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   op->srows = (need + 7) / 8 * 8;
   op->nbox = 1;
   if (op->srows > 256) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
-  if (C == 96) { op->ks = Cfg96::KS; op->nstages = Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = 0; }
-  else {
+  op->pair = getenv("Q3TTS_NO_PAIR") ? 0 : 1;
+  if (C == 96) { op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0; }
+  else if (op->pair) {
+    op->ks = 1; op->nslabs = 3; op->nbuf = 1;
+    op->nstages = Cfg192pa::NST; op->variant = 4;
+    if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = Cfg192pb::NST; op->variant = 5; }
+  } else {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = 4; op->variant = 1;
     if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = 3; op->variant = 2; }
@@ -482,8 +528,9 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   const uint64_t a_rows = op->a_rows ? (uint64_t)op->a_rows : (uint64_t)rows;
   rc |= make_tmap_3d_strided(&op->tmA, a1, et, (uint64_t)C, a_rows, (uint64_t)batches, (uint64_t)C,
                              op->a_batch_stride ? (uint64_t)op->a_batch_stride : a_rows * C, (uint32_t)p.kb, (uint32_t)(op->srows / op->nbox));
-  rc |= make_tmap_3d(&op->tmW7, w7, (uint64_t)C, (uint64_t)C, 7, (uint32_t)p.kb, (uint32_t)C, p.bf16 != 0);
-  rc |= make_tmap_3d(&op->tmW1, w1, (uint64_t)C, (uint64_t)C, 1, (uint32_t)p.kb, (uint32_t)C, p.bf16 != 0);
+  const uint32_t wbox = (uint32_t)(op->pair ? C / 2 : C);  // pair: each CTA loads its half of the output channels
+  rc |= make_tmap_3d(&op->tmW7, w7, (uint64_t)C, (uint64_t)C, 7, (uint32_t)p.kb, wbox, p.bf16 != 0);
+  rc |= make_tmap_3d(&op->tmW1, w1, (uint64_t)C, (uint64_t)C, 1, (uint32_t)p.kb, wbox, p.bf16 != 0);
   const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
   rc |= make_tmap_3d_strided(&op->tmRes, p.res, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
   rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
@@ -498,6 +545,9 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     set((const void*)unit_kernel<__half, Cfg96>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96>);
     set((const void*)unit_kernel<__half, Cfg192a>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192a>);
     set((const void*)unit_kernel<__half, Cfg192b>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192b>);
+    set((const void*)unit_kernel<__half, Cfg96p>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96p>);
+    set((const void*)unit_kernel<__half, Cfg192pa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pa>);
+    set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
     if (e != cudaSuccess) return -2;
     attr_done = true;
   }
@@ -508,28 +558,39 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
 // Copies the debug timeline of the last traced launch (Q3TTS_DBG bit 5) to the host.
 int unit_trace_read(long long* out256) { return cudaMemcpyFromSymbol(out256, g_unit_trace, sizeof(long long) * 256) == cudaSuccess ? 0 : -1; }
 
+template <typename T, typename Cfg>
+static cudaError_t launch_one(const UnitOp& op, const UnitArgs& u, int grid, size_t smem, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kUnitThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = Cfg::PAIR ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, unit_kernel<T, Cfg>, op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, op.p, u);
+}
 template <typename Cfg>
 static cudaError_t launch_cfg(const UnitOp& op, const UnitArgs& u, int grid, size_t smem, cudaStream_t stream) {
-  const GemmParams& p = op.p;
-  if (p.bf16)
-    unit_kernel<__nv_bfloat16, Cfg><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
-  else
-    unit_kernel<__half, Cfg><<<grid, kUnitThreads, smem, stream>>>(op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, p, u);
-  return cudaGetLastError();
+  return op.p.bf16 ? launch_one<__nv_bfloat16, Cfg>(op, u, grid, smem, stream) : launch_one<__half, Cfg>(op, u, grid, smem, stream);
 }
 
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
   if (!op.enabled) return cudaErrorInvalidConfiguration;
   const GemmParams& p = op.p;
-  const int tiles = p.batches * ((p.rows_valid + U_BM - 1) / U_BM);
+  const int tm = op.pair ? 2 * U_BM : U_BM;
+  const int tiles = p.batches * ((p.rows_valid + tm - 1) / tm);
   if (tiles <= 0) return cudaSuccess;
-  const int grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
+  int grid;
+  if (op.pair) { const int pairs = gemm_num_sms() / 2; grid = 2 * (tiles < pairs ? tiles : pairs); }
+  else grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
   UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf, op.a_row0};
   const size_t smem = unit_smem_bytes(op);
   switch (op.variant) {
     case 0: return launch_cfg<Cfg96>(op, u, grid, smem, stream);
     case 1: return launch_cfg<Cfg192a>(op, u, grid, smem, stream);
-    default: return launch_cfg<Cfg192b>(op, u, grid, smem, stream);
+    case 2: return launch_cfg<Cfg192b>(op, u, grid, smem, stream);
+    case 3: return launch_cfg<Cfg96p>(op, u, grid, smem, stream);
+    case 4: return launch_cfg<Cfg192pa>(op, u, grid, smem, stream);
+    default: return launch_cfg<Cfg192pb>(op, u, grid, smem, stream);
   }
 }
 
