@@ -73,6 +73,22 @@ int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, u
 // general 3-D map: element type 0 = fp16, 1 = bf16, 2 = fp32; strides in elements
 int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t stride1, uint64_t stride2,
                          uint32_t box0, uint32_t box1, uint32_t box2 = 1);
+// Output conv C -> 1 (k = 7) + clamp with the taps as the N dimension (tail_kernel.cu)
+struct TailParams {
+  int batches, rows_valid, a_row0, C, tail_skip, bf16;
+  float bias;
+  float* out;                  // [batches][out_batch_stride] fp32, row t - tail_skip
+  long long out_batch_stride;
+};
+struct TailOp {
+  CUtensorMap tmA, tmW;
+  TailParams p;
+  int nstages = 0;
+  int enabled = 0;
+};
+bool tail_supported(int C);
+int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_rows, long long a_batch_stride, int C, bool bf16);
+cudaError_t launch_tail(const TailOp& op, cudaStream_t stream);
 int gemm_stage_count(const GemmParams& p);
 cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream);
 

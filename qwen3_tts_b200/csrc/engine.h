@@ -48,6 +48,7 @@ struct Op {
   OpType type = OP_GEMM;
   GemmOp g;
   UnitOp u;  // OP_UNIT: fused residual unit (conv7 -> Snake -> conv1 + residual)
+  TailOp t;  // OP_TAIL: taps-as-N output conv (used when enabled, else the N = 16 implicit GEMM in g)
   const void* in = nullptr;
   void* out = nullptr;
   const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;
@@ -111,6 +112,7 @@ struct Engine {
   SnakeP tail_act;
   float* tail_w = nullptr;  // [7][C]
   float tail_bias = 0.f;
+  void* tail_w16 = nullptr;  // [16][C] 16-bit, rows 0..6 = the 7 taps (taps-as-N form of the output conv)
   int tail_c = 0;
   float *rope_cos = nullptr, *rope_sin = nullptr;
   int rope_max = 0;

@@ -233,6 +233,10 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     op.g.p.act = ACT_TAIL;
     op.B = B; op.L = L; op.C = e->tail_c;
     op.tag = "wav";
+    if (!dry && tail_supported(e->tail_c)) {
+      if (tail_make(&op.t, R[ia], e->tail_w16, B, L, 0, e->tail_c, e->bf16) < 0) b.rc = e->fail(Q3TTS_CUDA_ERROR, "tail tensor maps failed");
+      op.t.p.rows_valid = L; op.t.p.a_row0 = 0; op.t.p.bias = e->tail_bias;
+    }
   }
   plan->out_len = L;
   if (!dry) {
@@ -330,8 +334,13 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       case OP_DWLN: err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s); break;
       case OP_TAIL:
         if (wav) {
-          op.g.p.out_f32 = wav; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
-          err = launch_conv_gemm(op.g, e->engine, s);
+          if (op.t.enabled && e->engine == ENGINE_TC) {
+            op.t.p.out = wav; op.t.p.out_batch_stride = wav_stride; op.t.p.tail_skip = skip;
+            err = launch_tail(op.t, s);
+          } else {
+            op.g.p.out_f32 = wav; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
+            err = launch_conv_gemm(op.g, e->engine, s);
+          }
         }
         break;
     }

@@ -224,6 +224,10 @@ int build_stream(Engine* e, StreamPlan* plan, int S, int P, bool fresh, bool dry
     op.type = OP_TAIL;
     op.g.p.act = ACT_TAIL;
     op.B = S; op.L = L; op.C = e->tail_c;
+    if (!dry && tail_supported(e->tail_c)) {
+      if (tail_make(&op.t, tail_in, e->tail_w16, S, 6 + L, 0, e->tail_c, e->bf16) < 0) b.rc = e->fail(Q3TTS_CUDA_ERROR, "tail tensor maps failed");
+      op.t.p.rows_valid = L; op.t.p.a_row0 = 6; op.t.p.bias = e->tail_bias;
+    }
   }
   b.simple(OP_STATE_SAVE);
   b.simple(OP_POS_ADVANCE);
@@ -301,8 +305,13 @@ int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long lo
         err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s, op.aux0, op.aux1);
         break;
       case OP_TAIL:
-        op.g.p.out_f32 = tail_out; op.g.p.out_batch_stride = tail_stride; op.g.p.tail_skip = 0;
-        err = launch_conv_gemm(op.g, ENGINE_TC, s);
+        if (op.t.enabled) {
+          op.t.p.out = tail_out; op.t.p.out_batch_stride = tail_stride; op.t.p.tail_skip = 0;
+          err = launch_tail(op.t, s);
+        } else {
+          op.g.p.out_f32 = tail_out; op.g.p.out_batch_stride = tail_stride; op.g.p.tail_skip = 0;
+          err = launch_conv_gemm(op.g, ENGINE_TC, s);
+        }
         break;
       default: break;
     }

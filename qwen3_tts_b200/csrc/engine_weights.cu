@@ -236,11 +236,14 @@ int engine_finalize(Engine* e, int mode) {
       for (int j = 0; j < 7; ++j) t.tap_off[j] = -(6 - j);
       void* tmp = f.alloc((size_t)7 * Cl * 2);
       t.w = f.alloc((size_t)7 * 16 * Cl * 2);
+      e->tail_w16 = f.alloc((size_t)16 * Cl * 2);
       float* tbias = (float*)f.alloc(16 * sizeof(float));
       if (!f.rc) {
         f.check(cudaMemset(t.w, 0, (size_t)7 * 16 * Cl * 2), "tail memset");
         f.check(cudaMemset(tbias, 0, 16 * sizeof(float)), "tail bias memset");
-        f.check(pack_conv_weight(tw->d, tmp, 1, Cl, 7, e->bf16, f.s), "pack tail gemm");
+        f.check(pack_conv_weight(tw->d, tmp, 1, Cl, 7, e->bf16, f.s), "pack tail gemm");  // [7 taps][1][Cl]
+        f.check(cudaMemset(e->tail_w16, 0, (size_t)16 * Cl * 2), "tail w16 memset");
+        f.check(cudaMemcpy(e->tail_w16, tmp, (size_t)7 * Cl * 2, cudaMemcpyDeviceToDevice), "tail w16 copy");
         f.check(cudaMemcpy2D(t.w, (size_t)16 * Cl * 2, tmp, (size_t)Cl * 2, (size_t)Cl * 2, 7, cudaMemcpyDeviceToDevice), "tail scatter");
         f.check(cudaMemcpy(tbias, tb->d, sizeof(float), cudaMemcpyDeviceToDevice), "tail bias copy");
         t.bias = tbias;
