@@ -15,6 +15,7 @@
 // Operand tiles are K-major, written by TMA with 128B (KB = 64) or 64B (KB = 32) swizzle; rows
 // outside [0, rows) are zero-filled by TMA (= the reference's causal left padding).
 #include "conv_gemm.h"
+#include "pair_ptx.cuh"
 #include "tc_epilogue.cuh"
 
 #include <cstdlib>
@@ -41,10 +42,11 @@ struct __align__(8) GemmBarriers {
   uint32_t b_tab[64];  // ws kernel: per (K block, tap) B descriptor low word
 };
 
-__device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int warp, int epi_warps) {
+// pair: CTA-pair form (2-CTA cluster, tcgen05 cta_group::2): the leader's tmem_empty collects both CTAs' epilogue warps
+__device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int warp, int epi_warps, bool pair = false) {
   if (threadIdx.x == 0) {
     for (int s = 0; s < nring; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], epi_warps); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&bars->tmem_full[s], 1); mbar_init(&bars->tmem_empty[s], pair ? 2 * epi_warps : epi_warps); }
     for (int w = 0; w < kMaxEpiWarps; ++w)
       for (int s = 0; s < kMaxResDepth; ++s) mbar_init(&bars->res_bar[w][s], 1);
     mbar_init(&bars->w_full, 1);
@@ -52,25 +54,27 @@ __device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int w
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&bars->tmem_base, 512);
-    tmem_relinquish();
+    if (pair) { tmem_alloc2(&bars->tmem_base, 512); tmem_relinquish2(); }
+    else { tmem_alloc(&bars->tmem_base, 512); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
+  if (pair) cluster_sync_all();  // the peer's barriers exist before anything arrives on them
   tc_fence_after();
 }
 
 template <typename T>
 __device__ __forceinline__ void epilogue_role(const GemmParams& p, const CUtensorMap* tmRes, const CUtensorMap* tmRaw, const CUtensorMap* tmSnake,
                                               const CUtensorMap* tmF32, uint8_t* epi, GemmBarriers* bars, const TileSched& ts, uint32_t tmem_base,
-                                              int warp, int lane) {
+                                              int warp, int lane, bool pair = false, int rank = 0) {
   const int quad = warp & 3;  // TMEM lane quadrant this warp may access
   const int ew = warp - 2;
   EpiWarp<T> ep(p, tmRes, tmRaw, tmSnake, tmF32, epi + (size_t)ew * epi_slots_per_warp(p) * kEpiSlot, bars->res_bar[ew], ts, lane, quad, ew >> 2,
                 p.epi_warps >> 2);
+  if (pair) { ep.mt_mul = 2; ep.mt_add = rank; ep.tile0 = (int)(blockIdx.x >> 1); ep.tile_stride = (int)(gridDim.x >> 1); }
   ep.start();
   int it = 0;
-  for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+  for (int tile = ep.tile0; tile < ts.total_tiles; tile += ep.tile_stride, ++it) {
     int nt, mt, b;
     ts.decode(tile, nt, mt, b);
     const int buf = it & 1;
@@ -79,7 +83,7 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& p, const CUtenso
     ep.tile(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * 256, it, nt, mt, b);
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(&bars->tmem_empty[buf]);
+    if (lane == 0) { if (pair) mbar_arrive_leader(&bars->tmem_empty[buf]); else mbar_arrive(&bars->tmem_empty[buf]); }
   }
   ep.finish();
 }
@@ -289,7 +293,11 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // traffic per MMA drops from (128 + bn) to (srp / ntaps + bn) rows of K: the general kernel re-loads the
 // activation box once per tap and is bound by that traffic, not by the tensor pipe (profiles/r1_*).
 // slab_lo = rows of halo before the tile (-min tap_off), so it also serves the {0, +1} taps of a transposed conv.
-template <typename T>
+// PAIR: CTA-pair form.  A 2-CTA cluster works on 256-row tiles: each CTA loads its own 128-row slabs and HALF of every weight
+// tile (bn/2 output channels); the even CTA issues one M = 256 tcgen05.mma.cta_group::2 stream for both.  The single-CTA form is
+// bound by shared-memory fill (one weight tile per 128 rows: 70 B/clk wanted at C = 384, ~43 B/clk available); halving the
+// weight bytes per SM moves these layers back to the tensor pipe.
+template <typename T, bool PAIR>
 __global__ void __launch_bounds__(kMaxGemmThreads, 1)
 slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw,
@@ -299,8 +307,14 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int KB = p.kb;
   const int nkb = p.cin / KB;
-  const uint32_t wsub = p.bn * KB * 2;
+  const int bn_cta = PAIR ? p.bn / 2 : p.bn;   // weight rows this CTA holds
+  const uint32_t wsub = bn_cta * KB * 2;
   const uint32_t ssub = srp * KB * 2;
+  constexpr uint32_t NCTA = PAIR ? 2u : 1u;
+  constexpr int TM = PAIR ? 2 * BM : BM;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nworkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   uint8_t* slabs = smem;
   uint8_t* wst = smem + (size_t)nslabs * ssub;
   uint8_t* epi = wst + (size_t)nstages * wsub;
@@ -308,47 +322,57 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   TileSched ts;
-  ts.m_tiles = (p.rows_valid + BM - 1) / BM;
+  ts.m_tiles = (p.rows_valid + TM - 1) / TM;
   ts.n_tiles = p.n_total / p.bn;
   ts.total_tiles = p.batches * ts.m_tiles * ts.n_tiles;
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
-  init_common(bars, nstages, warp, p.epi_warps);
+  init_common(bars, nstages, warp, p.epi_warps, PAIR);
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
     if (elect_one()) {
+      // pair: loads land in this CTA's shared memory and are counted on the leader's full barriers (it issues the MMAs)
+      auto load = [&](uint8_t* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_pair(smem_u32(dst), map, leader_addr(smem_u32(bar)), c0, c1, c2);
+        else tma_load_3d(dst, map, bar, c0, c1, c2);
+      };
       int s = 0, ss = 0; uint32_t ph = 0, sph = 0;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
+      for (int tile = wid; tile < ts.total_tiles; tile += nworkers) {
         int nt, mt, b;
         ts.decode(tile, nt, mt, b);
-        const int n0 = nt * p.bn;
+        const int n0 = nt * p.bn + rank * bn_cta;
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
-          mbar_expect_tx(&bars->sfull[ss], ssub);
-          tma_load_3d(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * BM + p.a_row0 - slab_lo, b);
+          if (rank == 0) mbar_expect_tx(&bars->sfull[ss], ssub * NCTA);
+          load(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * TM + rank * BM + p.a_row0 - slab_lo, b);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
-            mbar_expect_tx(&bars->full[s], wsub);
-            tma_load_3d(wst + (size_t)s * wsub, &tmB, &bars->full[s], kb * KB, n0, tap);
+            if (rank == 0) mbar_expect_tx(&bars->full[s], wsub * NCTA);
+            load(wst + (size_t)s * wsub, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {
-      const uint32_t idesc = umma_idesc(BM, p.bn, p.bf16 != 0);
+    if (rank == 0 && elect_one()) {
+      const uint32_t idesc = umma_idesc(TM, p.bn, p.bf16 != 0);
       const uint32_t span = KB * 2;
       const uint32_t hi = umma_desc_hi(span);
       for (int tap = 0; tap < p.ntaps; ++tap) bars->a_tab[tap] = ((uint32_t)(p.tap_off[tap] + slab_lo) * span) >> 4;
       const uint32_t w_lo0 = umma_desc_lo(smem_u32(wst)), w_off = wsub >> 4;
       const uint32_t s_lo0 = umma_desc_lo(smem_u32(slabs)), s_off = ssub >> 4;
       const bool k4 = KB == 64;
+      auto mma = [&](uint32_t d, uint32_t a, uint32_t b, uint32_t acc) {
+        if (PAIR) umma2_f16_lohi(d, a, b, hi, idesc, acc); else umma_f16_lohi(d, a, b, hi, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) { if (PAIR) umma2_commit(bar); else umma_commit(bar); };
       int s = 0, ss = 0; uint32_t ph = 0, sph = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = wid; tile < ts.total_tiles; tile += nworkers, ++it) {
         const int buf = it & 1;
-        mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        if (PAIR) mbar_wait_cluster(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        else mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         for (int kb = 0; kb < nkb; ++kb) {
@@ -359,30 +383,31 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const uint32_t a = slab_lo_desc + bars->a_tab[tap], b = w_lo0 + (uint32_t)s * w_off;
             if (!(p.dbg & 2)) {
-              umma_f16_lohi(d_tmem, a, b, hi, idesc, (kb | tap) != 0);
-              umma_f16_lohi(d_tmem, a + 2, b + 2, hi, idesc, 1);
+              mma(d_tmem, a, b, (kb | tap) != 0);
+              mma(d_tmem, a + 2, b + 2, 1);
               if (k4) {
-                umma_f16_lohi(d_tmem, a + 4, b + 4, hi, idesc, 1);
-                umma_f16_lohi(d_tmem, a + 6, b + 6, hi, idesc, 1);
+                mma(d_tmem, a + 4, b + 4, 1);
+                mma(d_tmem, a + 6, b + 6, 1);
               }
             }
-            umma_commit(&bars->empty[s]);
+            commit(&bars->empty[s]);
             if (++s == nstages) { s = 0; ph ^= 1; }
           }
-          umma_commit(&bars->sempty[ss]);
+          commit(&bars->sempty[ss]);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
         }
-        umma_commit(&bars->tmem_full[buf]);
+        commit(&bars->tmem_full[buf]);
       }
     }
-  } else {
-    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane);
+  } else if (warp >= 2) {
+    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane, PAIR, rank);
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the leader's MMAs read the peer's shared and tensor memory until its last commit
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -474,7 +499,7 @@ int gemm_stage_count(const GemmParams& p) {
 // memory), else slab-stream (any multi-tap conv), else the general per-stage kernel (1-tap GEMMs).
 static void plan_variant(GemmOp* op, int allow) {
   const GemmParams& p = op->p;
-  op->ws = 0; op->nslabs = 0; op->srp = 0; op->variant = 0; op->nstages = 0; op->slab_lo = 0;
+  op->ws = 0; op->nslabs = 0; op->srp = 0; op->variant = 0; op->nstages = 0; op->slab_lo = 0; op->pair = 0;
   if (p.pack_mode) return;  // packed tiles exist in the general kernel only
   int lo = 0, hi = 0;
   for (int j = 0; j < p.ntaps; ++j) {
@@ -496,8 +521,14 @@ static void plan_variant(GemmOp* op, int allow) {
   }
   if ((allow & 4) && !getenv("Q3TTS_NO_SLAB") && p.ntaps >= 2) {
     const int srp = (BM + lo + hi + 15) / 16 * 16;
-    const long long slab = (long long)srp * p.kb * 2, wst = (long long)p.bn * p.kb * 2;
+    // CTA pairs (256-row tiles, half a weight tile per SM) when a batch item's rows fill 256-row tiles well
+    const int mt2 = (p.rows_valid + 2 * BM - 1) / (2 * BM);
+    // ... and the tile has enough K work for the weight traffic to matter: short-K layers (the last two transposed convs) are
+    // bound by their Snake epilogue and HBM, and the cross-CTA handshakes only cost them time (measured: 1.88 -> 2.03 ms, 2.97 -> 3.32 ms).
+    const bool pair = !getenv("Q3TTS_NO_PAIR") && p.bn % 32 == 0 && p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 1536;
+    const long long slab = (long long)srp * p.kb * 2, wst = (long long)(pair ? p.bn / 2 : p.bn) * p.kb * 2;
     const long long avail = (long long)g_smem_optin - fixed;
+    op->pair = pair ? 1 : 0;
     if (srp <= 256) {
       int ns = 3;
       int nst = (int)((avail - ns * slab) / wst);
@@ -569,6 +600,9 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, br, bb); }
   }
   plan_variant(op, allow);
+  if (op->variant != 2) op->pair = 0;
+  // the weight map follows the plan: a CTA of a pair loads half of a weight tile
+  if (make_tmap_3d(&op->tmB, p.w_ptr, (uint64_t)p.cin, (uint64_t)p.n_total, (uint64_t)p.ntaps, (uint32_t)p.kb, (uint32_t)(op->pair ? p.bn / 2 : p.bn), p.bf16 != 0)) rc |= 1;
   rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
                              p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb,
                              p.pack_mode ? br : (uint32_t)(op->variant ? op->srp : BM), bb);
@@ -589,8 +623,10 @@ int gemm_setup(int device) {
   cudaError_t e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e3 = cudaFuncSetAttribute(ws_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e4 = cudaFuncSetAttribute(ws_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  cudaError_t e5 = cudaFuncSetAttribute(slab_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  cudaError_t e6 = cudaFuncSetAttribute(slab_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e5 = cudaFuncSetAttribute(slab_conv_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e6 = cudaFuncSetAttribute(slab_conv_kernel<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e5 == cudaSuccess) e5 = cudaFuncSetAttribute(slab_conv_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e6 == cudaSuccess) e6 = cudaFuncSetAttribute(slab_conv_kernel<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess || e4 != cudaSuccess || e5 != cudaSuccess || e6 != cudaSuccess) return -2;
   return tmap_init();
 }
@@ -627,13 +663,26 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
     return cudaGetLastError();
   }
   if (op.variant == 2) {
-    const size_t smem = (size_t)op.nslabs * op.srp * p.kb * 2 + (size_t)op.nstages * p.bn * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+    const size_t smem = (size_t)op.nslabs * op.srp * p.kb * 2 + (size_t)op.nstages * (op.pair ? p.bn / 2 : p.bn) * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+    if (op.pair) {
+      const int tiles2 = p.batches * ((p.rows_valid + 2 * BM - 1) / (2 * BM)) * (p.n_total / p.bn);
+      const int pairs = g_num_sms / 2;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)(2 * (tiles2 < pairs ? tiles2 : pairs))); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      if (p.bf16)
+        return cudaLaunchKernelEx(&cfg, slab_conv_kernel<__nv_bfloat16, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+      return cudaLaunchKernelEx(&cfg, slab_conv_kernel<__half, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+    }
     if (p.bf16)
-      slab_conv_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages,
-                                                                       op.srp, op.slab_lo);
+      slab_conv_kernel<__nv_bfloat16, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages,
+                                                                              op.srp, op.slab_lo);
     else
-      slab_conv_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp,
-                                                                op.slab_lo);
+      slab_conv_kernel<__half, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp,
+                                                                       op.slab_lo);
     return cudaGetLastError();
   }
   const int nstages = gemm_stage_count(p);

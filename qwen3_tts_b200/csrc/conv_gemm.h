@@ -26,6 +26,7 @@ struct GemmOp {
   int nstages = 0;  // slab-stream: weight tile ring depth
   int srp = 0;      // slab rows (128 + halo, rounded up to 16)
   int slab_lo = 0;  // slab rows before the tile's first row (-min tap_off)
+  int pair = 0;     // slab-stream variant on CTA pairs (2-CTA clusters, 256-row tiles, tcgen05 cta_group::2)
   int retile = 0;   // 1: gemm_make_epilogue_maps may shrink the N tile until the grid covers the SMs (small-M streaming steps)
 };
 

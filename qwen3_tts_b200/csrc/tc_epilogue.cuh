@@ -58,7 +58,8 @@ struct EpiWarp {
   uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
   int pf_it = 0, pf_item = 0;  // residual prefetch cursor (tile iteration, item)
   bool pf_done = false;
-  int mt_mul = 1, mt_add = 0;  // 128-row block of a scheduler tile: mt * mt_mul + mt_add (fused unit kernel: 2 blocks per tile)
+  int mt_mul = 1, mt_add = 0;  // 128-row block of a scheduler tile: mt * mt_mul + mt_add (CTA pairs: 2 blocks per tile, one per CTA)
+  int tile0 = (int)blockIdx.x, tile_stride = (int)gridDim.x;  // this worker's tiles: tile0 + it * tile_stride (CTA pairs: pair index / count)
 
   __device__ EpiWarp(const GemmParams& p_, const CUtensorMap* r, const CUtensorMap* a, const CUtensorMap* s, const CUtensorMap* f,
                      uint8_t* eb_, uint64_t* rbar_, TileSched ts_, int lane_, int quad_, int half_, int nsplit_)
@@ -91,9 +92,9 @@ struct EpiWarp {
     while (pf_item >= nitems) {
       ++pf_it;
       pf_item = first_item(pf_it);
-      if ((int)blockIdx.x + pf_it * (int)gridDim.x >= ts.total_tiles) { pf_done = true; return; }
+      if (tile0 + pf_it * tile_stride >= ts.total_tiles) { pf_done = true; return; }
     }
-    const int tile = (int)blockIdx.x + pf_it * (int)gridDim.x;
+    const int tile = tile0 + pf_it * tile_stride;
     if (tile >= ts.total_tiles) { pf_done = true; return; }
     if (lane == 0) {
       int nt, mt, b;
@@ -340,7 +341,7 @@ struct EpiWarp {
 
   // one accumulator tile: t0 = TMEM address of (this warp's lane quadrant, first column of the tile)
   __device__ __forceinline__ void tile(uint32_t t0, int it, int nt, int mt, int b) {
-    int row0 = mt * 128 + quad * 32;
+    int row0 = (mt * mt_mul + mt_add) * 128 + quad * 32;
     if (p.pack_mode) gemm_chunk_coords(p, b, quad, row0, b);  // packed tiles: the scheduler's "batch" is the tile index
     if (p.dbg & 1) {
       uint32_t r[16];
