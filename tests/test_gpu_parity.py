@@ -180,6 +180,31 @@ def test_full_size_batch_properties(gpu_model, sd, cfg):
         assert mx <= MAX_ABS and snr >= MIN_SNR
 
 
+def test_long_form_and_sharded_shapes(gpu_model, cfg):
+    """BASELINE config 4 (32 x 60 s: chunks 300 / 25+300 / 25+150) and the config 5 utterance shape (T = 375: 300 / 25+75),
+    through size-independent properties: sample counts, batch independence across chunk boundaries, and the
+    chunk seam rule wav(chunked)[start*1920 - k*555 ...] == forward(codes[start-25:end])[25*1920:]."""
+    from qwen3_tts_b200.synthetic import make_codes
+    dec = gpu_model.decoder
+    codes = make_codes(32, 750, cfg, seed=9).cuda()
+    out = gpu_model.decode(codes, return_dict=True).audio_values
+    assert len(out) == 32 and all(w.shape == (750 * 1920 - 3 * 555,) for w in out)            # 1 438 335
+    assert all(bool(torch.isfinite(w).all()) and w.abs().max().item() <= 1.0 for w in out)
+    solo = gpu_model.decode(codes[7:8], return_dict=True).audio_values[0]
+    assert torch.equal(solo, out[7])
+    # second chunk of item 3 re-decoded by hand, the way chunked_decode defines it (modeling :889-893)
+    c = codes[3:4].transpose(1, 2).contiguous()
+    seam = dec(c[..., 275:600])[0, 0, 25 * 1920:]
+    lo = 300 * 1920 - 555
+    assert torch.equal(seam, out[3][lo:lo + seam.numel()])
+    # config 5 shape, a few utterances of different true lengths (padding rule: codes[..., 0] > 0)
+    c5 = make_codes(6, 375, cfg, seed=10)
+    c5[4, 200:] = 0
+    got = gpu_model.decode(c5.cuda(), return_dict=True).audio_values
+    assert [w.numel() for w in got] == [375 * 1920 - 2 * 555] * 4 + [200 * 1920] + [375 * 1920 - 2 * 555]
+    assert torch.equal(got[4], gpu_model.decode(c5[4:5].cuda(), return_dict=True).audio_values[0])
+
+
 def test_streaming_equals_whole_sequence_forward(gpu_model, cfg):
     """Stateful per-packet decode (q3tts_stream_*): concatenated stream output == Decoder.forward(whole sequence) on
     [0, T*1920-555), for packet sizes 1, 3 and 5, streams that start at different steps, and a reset."""
