@@ -88,7 +88,9 @@ __device__ __forceinline__ void epilogue_role(const GemmParams& p, const CUtenso
   ep.finish();
 }
 
-template <typename T>
+// PAIR: CTA-pair form (see slab_conv_kernel): 256-row tiles, each CTA loads its 128 rows of A and half of the weight tile, the
+// even CTA issues M = 256 tcgen05.mma.cta_group::2.  Not combined with packed tiles.
+template <typename T, bool PAIR>
 __global__ void __launch_bounds__(kMaxGemmThreads, 1)
 conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmRaw,
@@ -97,62 +99,77 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int KB = p.kb;
+  constexpr uint32_t NCTA = PAIR ? 2u : 1u;
+  constexpr int TM = PAIR ? 2 * BM : BM;
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int nworkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int bn_cta = PAIR ? p.bn / 2 : p.bn;
   const uint32_t a_bytes = BM * KB * 2;
-  const uint32_t b_bytes = p.bn * KB * 2;
+  const uint32_t b_bytes = bn_cta * KB * 2;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   uint8_t* epi = smem + (size_t)nstages * stage_bytes;
   GemmBarriers* bars = reinterpret_cast<GemmBarriers*>(epi + (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   TileSched ts;
-  ts.m_tiles = p.pack_mode ? 1 : (p.rows_valid + BM - 1) / BM;  // packed: decode() returns the tile index as "batch"
+  ts.m_tiles = p.pack_mode ? 1 : (p.rows_valid + TM - 1) / TM;  // packed: decode() returns the tile index as "batch"
   ts.n_tiles = p.n_total / p.bn;
-  ts.total_tiles = gemm_m_tiles_total(p) * ts.n_tiles;
+  ts.total_tiles = (PAIR ? p.batches * ts.m_tiles : gemm_m_tiles_total(p)) * ts.n_tiles;
   const int kblocks = p.cin / KB;
   const int ksteps = kblocks * p.ntaps;
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
-  init_common(bars, nstages, warp, p.epi_warps);
+  init_common(bars, nstages, warp, p.epi_warps, PAIR);
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
+      auto load = [&](uint8_t* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_pair(smem_u32(dst), map, leader_addr(smem_u32(bar)), c0, c1, c2);
+        else tma_load_3d(dst, map, bar, c0, c1, c2);
+      };
       int s = 0; uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x) {
+      for (int tile = wid; tile < ts.total_tiles; tile += nworkers) {
         int nt, mt, b;
         ts.decode(tile, nt, mt, b);
-        const int m0 = mt * BM, n0 = nt * p.bn;
+        const int m0 = mt * TM + rank * BM, n0 = nt * p.bn + rank * bn_cta;
         int cr[4] = {0, 0, 0, 0}, cb[4] = {0, 0, 0, 0};
-        if (p.pack_mode)
+        if (!PAIR && p.pack_mode)
           for (int q = 0; q < 4; ++q) gemm_chunk_coords(p, b, q, cr[q], cb[q]);
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&bars->full[s], stage_bytes);
-            if (p.pack_mode) {  // four 32-row chunk boxes fill the 128-row A tile
+            if (rank == 0) mbar_expect_tx(&bars->full[s], stage_bytes * NCTA);
+            if (!PAIR && p.pack_mode) {  // four 32-row chunk boxes fill the 128-row A tile
               for (int q = 0; q < 4; ++q)
                 tma_load_3d(sa + q * (a_bytes >> 2), &tmA, &bars->full[s], kb * KB, cr[q] + p.a_row0 + p.tap_off[tap], cb[q]);
             } else {
-              tma_load_3d(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
+              load(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
             }
-            tma_load_3d(sa + a_bytes, &tmB, &bars->full[s], kb * KB, n0, tap);
+            load(sa + a_bytes, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------ MMA issuer (one thread)
-    if (elect_one()) {
-      const uint32_t idesc = umma_idesc(BM, p.bn, p.bf16 != 0);
+    // ------------------------------------------------------------ MMA issuer (one thread; pair: of the even CTA only)
+    if (rank == 0 && elect_one()) {
+      const uint32_t idesc = umma_idesc(TM, p.bn, p.bf16 != 0);
       const uint32_t hi = umma_desc_hi(KB * 2);
       const uint32_t a_lo0 = umma_desc_lo(smem_u32(smem)), b_off = a_bytes >> 4, st_off = stage_bytes >> 4;
       const bool k4 = KB == 64;
+      auto mma = [&](uint32_t d, uint32_t a, uint32_t b, uint32_t acc) {
+        if (PAIR) umma2_f16_lohi(d, a, b, hi, idesc, acc); else umma_f16_lohi(d, a, b, hi, idesc, acc);
+      };
+      auto commit = [&](uint64_t* bar) { if (PAIR) umma2_commit(bar); else umma_commit(bar); };
       int s = 0; uint32_t ph = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < ts.total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = wid; tile < ts.total_tiles; tile += nworkers, ++it) {
         const int buf = it & 1;
-        mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        if (PAIR) mbar_wait_cluster(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
+        else mbar_wait_backoff(&bars->tmem_empty[buf], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         for (int ks = 0; ks < ksteps; ++ks) {
@@ -161,27 +178,28 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t a = a_lo0 + (uint32_t)s * st_off, b = a + b_off;
           if (!(p.dbg & 2)) {
             // +2 in the >>4 address field advances 16 elements (32 bytes) along K inside the swizzle span
-            umma_f16_lohi(d_tmem, a, b, hi, idesc, ks != 0);
-            umma_f16_lohi(d_tmem, a + 2, b + 2, hi, idesc, 1);
+            mma(d_tmem, a, b, ks != 0);
+            mma(d_tmem, a + 2, b + 2, 1);
             if (k4) {
-              umma_f16_lohi(d_tmem, a + 4, b + 4, hi, idesc, 1);
-              umma_f16_lohi(d_tmem, a + 6, b + 6, hi, idesc, 1);
+              mma(d_tmem, a + 4, b + 4, 1);
+              mma(d_tmem, a + 6, b + 6, 1);
             }
           }
-          umma_commit(&bars->empty[s]);
+          commit(&bars->empty[s]);
           if (++s == nstages) { s = 0; ph ^= 1; }
         }
-        umma_commit(&bars->tmem_full[buf]);
+        commit(&bars->tmem_full[buf]);
       }
     }
   } else {
-    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane);
+    epilogue_role<T>(p, &tmRes, &tmRaw, &tmSnake, &tmF32, epi, bars, ts, tmem_base, warp, lane, PAIR, rank);
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (PAIR) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -488,8 +506,8 @@ static int g_smem_optin = 0;
 
 static size_t epi_bytes(const GemmParams& p) { return (size_t)p.epi_warps * epi_slots_per_warp(p) * kEpiSlot; }
 
-int gemm_stage_count(const GemmParams& p) {
-  const int stage = (BM + p.bn) * p.kb * 2;
+int gemm_stage_count(const GemmParams& p, bool pair) {
+  const int stage = (BM + (pair ? p.bn / 2 : p.bn)) * p.kb * 2;
   int n = (int)((g_smem_optin - 1024 - (long long)epi_bytes(p) - (long long)sizeof(GemmBarriers) - 256) / stage);
   if (n > kMaxStages) n = kMaxStages;
   return n;
@@ -600,7 +618,13 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, br, bb); }
   }
   plan_variant(op, allow);
-  if (op->variant != 2) op->pair = 0;
+  if (op->variant == 1) op->pair = 0;
+  if (op->variant == 0) {
+    // general kernel on CTA pairs: long-K GEMMs whose rows fill 256-row tiles (transformer and 1x1 conv layers in bulk decode)
+    const int mt2 = (p.rows_valid + 2 * BM - 1) / (2 * BM);
+    op->pair = (!getenv("Q3TTS_NO_PAIR") && !getenv("Q3TTS_NO_PAIR_GEMM") && !p.pack_mode && p.act != ACT_TAIL && p.bn % 32 == 0 &&
+                p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 3072) ? 1 : 0;  // measured: -32 % at K = 3072, neutral or worse at K <= 1024
+  }
   // the weight map follows the plan: a CTA of a pair loads half of a weight tile
   if (make_tmap_3d(&op->tmB, p.w_ptr, (uint64_t)p.cin, (uint64_t)p.n_total, (uint64_t)p.ntaps, (uint32_t)p.kb, (uint32_t)(op->pair ? p.bn / 2 : p.bn), p.bf16 != 0)) rc |= 1;
   rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
@@ -619,8 +643,10 @@ int gemm_setup(int device) {
   if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return -1;
   g_num_sms = prop.multiProcessorCount;
   g_smem_optin = (int)prop.sharedMemPerBlockOptin;
-  cudaError_t e1 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
-  cudaError_t e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e1 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  cudaError_t e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
+  if (e2 == cudaSuccess) e2 = cudaFuncSetAttribute(conv_gemm_tc_kernel<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e3 = cudaFuncSetAttribute(ws_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e4 = cudaFuncSetAttribute(ws_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
   cudaError_t e5 = cudaFuncSetAttribute(slab_conv_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_smem_optin);
@@ -685,13 +711,25 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
                                                                        op.slab_lo);
     return cudaGetLastError();
   }
-  const int nstages = gemm_stage_count(p);
+  const int nstages = gemm_stage_count(p, op.pair != 0);
   if (nstages < 2) return cudaErrorInvalidConfiguration;
-  const size_t smem = (size_t)nstages * (BM + p.bn) * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+  const size_t smem = (size_t)nstages * (BM + (op.pair ? p.bn / 2 : p.bn)) * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+  if (op.pair) {
+    const int tiles2 = p.batches * ((p.rows_valid + 2 * BM - 1) / (2 * BM)) * (p.n_total / p.bn);
+    const int pairs = g_num_sms / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * (tiles2 < pairs ? tiles2 : pairs))); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    if (p.bf16) return cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel<__nv_bfloat16, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+    return cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel<__half, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+  }
   if (p.bf16)
-    conv_gemm_tc_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+    conv_gemm_tc_kernel<__nv_bfloat16, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
   else
-    conv_gemm_tc_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+    conv_gemm_tc_kernel<__half, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
   return cudaGetLastError();
 }
 

@@ -90,7 +90,7 @@ struct TailOp {
 bool tail_supported(int C);
 int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_rows, long long a_batch_stride, int C, bool bf16);
 cudaError_t launch_tail(const TailOp& op, cudaStream_t stream);
-int gemm_stage_count(const GemmParams& p);
+int gemm_stage_count(const GemmParams& p, bool pair = false);
 cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream);
 
 }  // namespace q3
