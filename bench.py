@@ -307,6 +307,21 @@ def main():
                     "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [125,16]}) -> host float32 arrays"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
             "path_frac_of_tensor_roofline": path_frac, "kernels": by_kernel}
+    if world == 1:
+        # SURVEY 8f-3 wire formats (additive API, informational): int16 code frames in, PCM16 out, conversion fused into the output conv
+        items16 = [{"audio_codes": codes_host[b].to(torch.int16)} for b in range(B_UTT)]
+        for _ in range(2):
+            tok.decode_pcm16(items16)
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pcm, _sr = tok.decode_pcm16(items16)
+        torch.cuda.synchronize(dev)
+        t16 = time.perf_counter() - t0
+        assert len(pcm) == B_UTT and pcm[0].shape == (239445,) and str(pcm[0].dtype) == "int16"
+        line["e2e_pcm16"] = {"value": B_UTT * T_FRAMES * FRAME_SEC * args.steps / t16, "unit": "audio-s/s", "ms_per_step": t16 / args.steps * 1e3,
+                             "h2d_bytes_per_step": B_UTT * T_FRAMES * 16 * 2, "d2h_bytes_per_step": B_UTT * 239445 * 2,
+                             "api": "Qwen3TTSTokenizer.decode_pcm16(list of {'audio_codes': int16 [125,16]}) -> host int16 PCM arrays"}
     if not args.no_streaming and world == 1:
         # BASELINE config 3 rides along as its own section: it is a latency, not the throughput metric of this line
         dec.reserve_streams(args.streams, 4)

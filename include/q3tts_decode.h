@@ -104,6 +104,13 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
 int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
                       void* stream);
 
+/* Same call with the wire formats of SURVEY 8f-3: int16 code frames in (a 2048-entry codebook index fits; the reference
+ * keeps codes as JSON lists / numpy payloads, finetuning/prepare_data.py:49, examples/test_tokenizer_12hz.py:54-58) and PCM16
+ * out, pcm = lrintf(clamp(wav, -1, 1) * 32767): what `sf.write(path, wav, sr)` stores for a float waveform (examples :33).
+ * The conversion is fused into the output conv, so host traffic is 4x / 2x smaller.  Strides in int16 elements. */
+int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, int T, int16_t* pcm_host, int64_t pcm_stride, int64_t* lengths,
+                            void* stream);
+
 /* ---- Streaming: stateful per-packet decode.  The reference has NO counterpart: its only streaming-shaped call is
  * chunked_decode's `forward(codes[..., s-25:e])[..., 25*1920:]` (modeling :889-893), which re-decodes 25 frames of left
  * context per chunk and is only approximately equal to the whole-sequence decode.  These entry points keep, per stream, the

@@ -56,6 +56,7 @@ EXPORTS = {
     "q3tts_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_chunked_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "q3tts_decode_host_pcm16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "q3tts_forward_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.c_int64,
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p]),
     "q3tts_stream_reserve": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),

@@ -27,7 +27,8 @@ int chunked(Engine& e, const long long* codes, long long sb, long long sk, long 
     const int Tc = end - lo;
     const long long emitted = (long long)(end - start) * e.total_up - e.lookahead;
     if (emitted > 0) {
-      int rc = engine_forward_batched(&e, codes + lo * st, sb, sk, st, B, Tc, wav + out_off, wav_stride, ctx * e.total_up, s);
+      float* dst = e.out_pcm16 ? reinterpret_cast<float*>(reinterpret_cast<short*>(wav) + out_off) : wav + out_off;
+      int rc = engine_forward_batched(&e, codes + lo * st, sb, sk, st, B, Tc, dst, wav_stride, ctx * e.total_up, s);
       if (rc) return rc;
       out_off += emitted;
     }
@@ -77,8 +78,9 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
   return chunked(e, (const long long*)codes, (long long)Q * T, T, 1, B, T, chunk, left_ctx, wav, total, (cudaStream_t)stream);
 }
 
-int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
-                      void* stream) {
+// codes16 != 0: codes_host is int16 [B,T,Q]; pcm16 != 0: wav_host is int16 PCM (strides in elements of the output type)
+static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16, int B, int T, void* wav_host, int pcm16, int64_t wav_stride,
+                            int64_t* lengths, void* stream) {
   if (!h) return Q3TTS_BAD_CONFIG;
   Engine& e = h->e;
   if (int rc = ready(e, codes_host, B, T)) return rc;
@@ -96,6 +98,13 @@ int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, 
     if (cudaMalloc((void**)&e.codes_stage, ncodes * sizeof(long long)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: codes staging"); }
     e.codes_stage_elems = ncodes;
   }
+  if (codes16 && ncodes > e.codes16_stage_elems) {
+    cudaStreamSynchronize(s);
+    if (e.codes16_stage) cudaFree(e.codes16_stage);
+    e.codes16_stage = nullptr; e.codes16_stage_elems = 0;
+    if (cudaMalloc((void**)&e.codes16_stage, ncodes * sizeof(short)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: int16 codes staging"); }
+    e.codes16_stage_elems = ncodes;
+  }
   const size_t nwav = (size_t)B * (size_t)(total > 0 ? total : 0);
   if (nwav > e.wav_stage_elems) {
     cudaStreamSynchronize(s);
@@ -104,12 +113,21 @@ int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, 
     if (cudaMalloc((void**)&e.wav_stage, nwav * sizeof(float)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: wav staging"); }
     e.wav_stage_elems = nwav;
   }
-  cudaError_t err = cudaMemcpyAsync(e.codes_stage, codes_host, ncodes * sizeof(long long), cudaMemcpyHostToDevice, s);
+  cudaError_t err;
+  if (codes16) {
+    err = cudaMemcpyAsync(e.codes16_stage, codes_host, ncodes * sizeof(short), cudaMemcpyHostToDevice, s);
+    if (err == cudaSuccess) err = widen_codes_i16(e.codes16_stage, e.codes_stage, (long long)ncodes, s);
+  } else {
+    err = cudaMemcpyAsync(e.codes_stage, codes_host, ncodes * sizeof(long long), cudaMemcpyHostToDevice, s);
+  }
   if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: H2D: ") + cudaGetErrorString(err));
   // audio_lengths = (audio_codes[..., 0] > 0).sum(1) * decode_upsample_rate, then a[:l] (modeling :1014-1015)
   for (int b = 0; b < B; ++b) {
     long long cnt = 0;
-    for (int t = 0; t < T; ++t) cnt += codes_host[((size_t)b * T + t) * Q] > 0 ? 1 : 0;
+    for (int t = 0; t < T; ++t) {
+      const size_t i = ((size_t)b * T + t) * Q;
+      cnt += (codes16 ? (long long)static_cast<const int16_t*>(codes_host)[i] : (long long)static_cast<const int64_t*>(codes_host)[i]) > 0 ? 1 : 0;
+    }
     long long l = cnt * e.total_up;
     if (l > total) l = total;
     if (l < 0) l = 0;
@@ -117,7 +135,9 @@ int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, 
   }
   if (total > 0) {
     // codes are [B,T,Q] here (wrapper layout): strides b = T*Q, k = 1, t = Q
+    e.out_pcm16 = pcm16 != 0;  // the staging buffer is then int16 [B][total]
     int rc = chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
+    e.out_pcm16 = false;
     if (rc) return rc;
     // one strided copy for the whole batch: rows are cut to their length by the caller's views, so the columns between a
     // row's length and the longest row may be written too (the host buffer has wav_stride >= that many columns per row)
@@ -125,14 +145,24 @@ int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, 
     for (int b = 0; b < B; ++b) maxlen = lengths[b] > maxlen ? lengths[b] : maxlen;
     if (maxlen > wav_stride) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: wav_stride smaller than an output row");
     if (maxlen > 0) {
-      err = cudaMemcpy2DAsync(wav_host, (size_t)wav_stride * sizeof(float), e.wav_stage, (size_t)total * sizeof(float), (size_t)maxlen * sizeof(float),
-                              (size_t)B, cudaMemcpyDeviceToHost, s);
+      const size_t es = pcm16 ? sizeof(short) : sizeof(float);
+      err = cudaMemcpy2DAsync(wav_host, (size_t)wav_stride * es, e.wav_stage, (size_t)total * es, (size_t)maxlen * es, (size_t)B, cudaMemcpyDeviceToHost, s);
       if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: D2H: ") + cudaGetErrorString(err));
     }
   }
   err = cudaStreamSynchronize(s);
   if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: ") + cudaGetErrorString(err));
   return Q3TTS_OK;
+}
+
+int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
+                      void* stream) {
+  return decode_host_impl(h, codes_host, 0, B, T, wav_host, 0, wav_stride, lengths, stream);
+}
+
+int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, int T, int16_t* pcm_host, int64_t pcm_stride, int64_t* lengths,
+                            void* stream) {
+  return decode_host_impl(h, codes_host, 1, B, T, pcm_host, 1, pcm_stride, lengths, stream);
 }
 
 int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, const char* stage, float* out, int64_t capacity, int* C, int* L,

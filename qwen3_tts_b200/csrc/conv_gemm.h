@@ -79,6 +79,7 @@ struct TailParams {
   int batches, rows_valid, a_row0, C, tail_skip, bf16;
   float bias;
   float* out;                  // [batches][out_batch_stride] fp32, row t - tail_skip
+  short* out_i16;              // when set: PCM16 instead, lrintf(clamp(v) * 32767) (what libsndfile writes for a float waveform)
   long long out_batch_stride;
 };
 struct TailOp {

@@ -125,6 +125,9 @@ struct Engine {
   long long* codes_stage = nullptr;  // device staging for decode_host
   size_t codes_stage_elems = 0;
   float* wav_stage = nullptr;
+  bool out_pcm16 = false;       // transient (decode_host_pcm16): the `wav` argument of the run functions is an int16 buffer
+  short* codes16_stage = nullptr;  // device staging for int16 code frames
+  size_t codes16_stage_elems = 0;
   size_t wav_stage_elems = 0;
 
   // ---- streaming state (q3tts_stream_*)

@@ -335,8 +335,11 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       case OP_TAIL:
         if (wav) {
           if (op.t.enabled && e->engine == ENGINE_TC) {
-            op.t.p.out = wav; op.t.p.out_batch_stride = wav_stride; op.t.p.tail_skip = skip;
+            op.t.p.out = e->out_pcm16 ? nullptr : wav; op.t.p.out_i16 = e->out_pcm16 ? reinterpret_cast<short*>(wav) : nullptr;
+            op.t.p.out_batch_stride = wav_stride; op.t.p.tail_skip = skip;
             err = launch_tail(op.t, s);
+          } else if (e->out_pcm16) {
+            err = cudaErrorNotSupported;  // PCM16 output exists in the taps-as-N output conv only
           } else {
             op.g.p.out_f32 = wav; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
             err = launch_conv_gemm(op.g, e->engine, s);
@@ -377,7 +380,9 @@ int engine_forward_batched(Engine* e, const long long* codes, long long sb, long
     Plan* plan = nullptr;
     int rc = engine_get_plan(e, nb, T, &plan);
     if (rc) return rc;
-    rc = engine_run(e, plan, codes + b0 * sb, sb, sk, st, wav + (long long)b0 * wav_stride, wav_stride, skip, nullptr, nullptr, 0, nullptr, nullptr, s);
+    // PCM16 output: `wav` is an int16 buffer, offsets are in its elements
+    float* dst = e->out_pcm16 ? reinterpret_cast<float*>(reinterpret_cast<short*>(wav) + (long long)b0 * wav_stride) : wav + (long long)b0 * wav_stride;
+    rc = engine_run(e, plan, codes + b0 * sb, sb, sk, st, dst, wav_stride, skip, nullptr, nullptr, 0, nullptr, nullptr, s);
     if (rc) return rc;
   }
   return Q3TTS_OK;
@@ -391,6 +396,7 @@ void engine_free(Engine* e) {
   if (e->ws) cudaFree(e->ws);
   if (e->codes_stage) cudaFree(e->codes_stage);
   if (e->wav_stage) cudaFree(e->wav_stage);
+  if (e->codes16_stage) cudaFree(e->codes16_stage);
 }
 
 }  // namespace q3

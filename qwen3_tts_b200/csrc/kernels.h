@@ -24,6 +24,8 @@ cudaError_t fold_codebook(const float* embedding_sum, const float* cluster_usage
 // ---- hot-path SIMT kernels
 // codes int64 addressed as codes[b*sb + k*sk + t*st]; tables [Q][ncodes][D] fp32; out_act [B][T][D] 16-bit (optional);
 // out_f32 [B][D][T] (optional)
+// int16 code frames (packed codes on the wire) -> the int64 layout the gather kernel reads
+cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaStream_t s);
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
                        int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows = 0, const int* src_index = nullptr);
 // x fp32 [M][H] -> 16-bit [M][H]: w * x * rsqrt(mean(x^2) + eps)

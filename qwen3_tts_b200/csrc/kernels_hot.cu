@@ -63,6 +63,17 @@ cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long 
   return cudaGetLastError();
 }
 
+__global__ void k_widen_i16(const short* __restrict__ in, long long* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) out[i] = in[i];
+}
+cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  long long blocks = (n + 255) / 256;
+  if (blocks > 1184) blocks = 1184;
+  k_widen_i16<<<(int)blocks, 256, 0, s>>>(in, out, n);
+  return cudaGetLastError();
+}
+
 // ============================================================================================ RMSNorm
 // One warp per row (reference modeling :382-387, computed in fp32).
 template <typename T>

@@ -120,7 +120,12 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 7; ++j) v += P[j * T_PPITCH + i + j];
         const int t = t0 + i;
-        if (t < p.rows_valid && t >= p.tail_skip) p.out[(long long)b * p.out_batch_stride + (t - p.tail_skip)] = fminf(1.0f, fmaxf(-1.0f, v));
+        if (t < p.rows_valid && t >= p.tail_skip) {
+          const float c = fminf(1.0f, fmaxf(-1.0f, v));
+          const long long o = (long long)b * p.out_batch_stride + (t - p.tail_skip);
+          if (p.out_i16) p.out_i16[o] = (short)__float2int_rn(c * 32767.0f);
+          else p.out[o] = c;
+        }
       }
     }
   }
@@ -154,7 +159,7 @@ int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_row
       return -2;
     attr_done = true;
   }
-  op->p.C = C; op->p.bf16 = bf16 ? 1 : 0; op->p.batches = batches;
+  op->p.C = C; op->p.bf16 = bf16 ? 1 : 0; op->p.batches = batches; op->p.out = nullptr; op->p.out_i16 = nullptr;
   op->enabled = 1;
   return 0;
 }

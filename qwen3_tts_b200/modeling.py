@@ -314,3 +314,19 @@ class Qwen3TTSTokenizerV2Model:
         _capi.check(d._h, rc, "decode_host")
         arr = wav.numpy()  # fresh pinned buffer per call: the returned rows are views that keep it alive, no extra host copy
         return [arr[b, : lengths[b]] for b in range(B)]
+
+    def decode_host_pcm16(self, audio_codes_cpu: torch.Tensor):
+        """decode_host with the wire formats of SURVEY 8f-3: codes travel as int16, the result is PCM16
+        (np.int16 = rint(clamp(wav) * 32767), what sf.write stores for a float waveform), converted in the output conv."""
+        if audio_codes_cpu.dim() != 3 or audio_codes_cpu.shape[2] != self.config.decoder_config.num_quantizers:
+            raise ValueError(f"Expected {self.config.decoder_config.num_quantizers} layer of codes, got {audio_codes_cpu.shape[-1]}")
+        codes = audio_codes_cpu.to(torch.int16).contiguous()
+        B, T, _ = codes.shape
+        d = self.decoder
+        total = int(d._lib.q3tts_chunked_num_samples(d._h, T, 300, 25))
+        pcm = torch.empty((B, max(total, 1)), dtype=torch.int16, pin_memory=True)
+        lengths = (C.c_int64 * B)()
+        rc = d._lib.q3tts_decode_host_pcm16(d._h, codes.data_ptr(), B, T, pcm.data_ptr(), pcm.shape[1], lengths, _stream_ptr(d.device))
+        _capi.check(d._h, rc, "decode_host_pcm16")
+        arr = pcm.numpy()
+        return [arr[b, : lengths[b]] for b in range(B)]

@@ -85,6 +85,25 @@ class Qwen3TTSTokenizer:
                 wavs = self.model.decode_host(audio_codes_padded)
         return wavs, int(self.model.get_output_sample_rate())
 
+    def decode_pcm16(self, encoded) -> Tuple[List[np.ndarray], int]:
+        """Additive: same payload forms as decode(), result as PCM16 (np.int16) ready for a WAV writer."""
+        if hasattr(encoded, "audio_codes"):
+            lst = encoded.audio_codes
+        elif isinstance(encoded, dict):
+            lst = encoded["audio_codes"]
+        elif isinstance(encoded, list):
+            lst = [e["audio_codes"] for e in encoded]
+        else:
+            raise TypeError("`encoded` must be an encode output, a dict, or a list of dicts.")
+        if isinstance(lst, torch.Tensor):
+            padded = lst.unsqueeze(0) if lst.dim() == 2 else lst
+        else:
+            padded = pad_sequence([c if isinstance(c, torch.Tensor) else torch.from_numpy(np.asarray(c)) for c in lst], batch_first=True,
+                                  padding_value=0)
+        with torch.inference_mode():
+            pcm = self.model.decode_host_pcm16(padded.cpu())
+        return pcm, int(self.model.get_output_sample_rate())
+
     def get_model_type(self) -> str:
         return self.model.get_model_type()
 

@@ -145,6 +145,21 @@ def test_wrapper_decode_payload_forms_and_length_rule(gpu_model):
         24000, 24000, 1920, 1920)
 
 
+def test_pcm16_and_int16_codes_wire_formats(gpu_model, cfg):
+    """int16 code frames in, PCM16 out.  The int16 path must decode exactly what the int64 path decodes, and the
+    PCM16 samples must be rint(wav * 32767) of the float result (what sf.write stores), ragged lengths included."""
+    from qwen3_tts_b200 import Qwen3TTSTokenizer
+    from qwen3_tts_b200.synthetic import make_codes
+    tok = Qwen3TTSTokenizer.from_model(gpu_model)
+    items = [{"audio_codes": make_codes(1, T, cfg, seed=20 + i)[0]} for i, T in enumerate((40, 17, 33))]
+    wavs, sr = tok.decode(items)
+    pcm, sr2 = tok.decode_pcm16([{"audio_codes": it["audio_codes"].to(torch.int16).numpy()} for it in items])
+    assert sr == sr2 == 24000 and len(pcm) == 3
+    for w, q in zip(wavs, pcm):
+        assert q.dtype == np.int16 and q.shape == w.shape
+        assert np.array_equal(q, np.rint(np.clip(w, -1.0, 1.0) * np.float32(32767.0)).astype(np.int16))
+
+
 def test_error_behaviour_matches_reference(gpu_model):
     with pytest.raises(ValueError, match="Expected 16 layer of codes, got 15"):
         gpu_model.decoder(torch.zeros(1, 15, 4, dtype=torch.int64))
