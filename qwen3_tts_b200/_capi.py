@@ -10,6 +10,8 @@ from typing import Optional
 from .configuration import Qwen3TTSTokenizerV2DecoderConfig
 
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libq3tts_decode.so")
+if os.environ.get("Q3TTS_LIB"):  # same-box A/B of two builds of the library (tools/ab_layers.sh); still the CUDA library, never a fallback
+    _LIB_PATH = os.path.abspath(os.environ["Q3TTS_LIB"])
 _lib: Optional[C.CDLL] = None
 
 OK, BAD_SHAPE, BAD_CONFIG, CODE_OUT_OF_RANGE, CUDA_ERROR, OOM, BAD_STREAM, BAD_KEY, NOT_READY = 0, -1, -2, -3, -4, -5, -6, -7, -8

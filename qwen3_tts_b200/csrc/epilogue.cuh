@@ -8,10 +8,18 @@ namespace q3 {
 
 __device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f)); }
 __device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
-// SnakeBeta (reference modeling :601-615): x + 1/(exp(beta)+1e-9) * sin(x*exp(alpha))^2
-__device__ __forceinline__ float snake(float v, float a, float ib) {
-  float s = __sinf(v * a);
-  return fmaf(ib * s, s, v);
+// SnakeBeta (reference modeling :601-615): x + 1/(exp(beta)+1e-9) * sin(x*exp(alpha))^2, evaluated as
+//   (x + h) - h * cos(a2 * x),  a2 = 2 exp(alpha), h = (1/2) / (exp(beta)+1e-9)   (tables from pack_snake)
+// which is one multiply less per element and has a packed two-lane form (snake2) of FMUL2 / FADD2 / FFMA2.
+// Every kernel goes through these two functions, lane for lane the same operations, so bulk, streaming and the
+// SIMT cross-check stay bit-identical.
+__device__ __forceinline__ float snake(float v, float a2, float h) {
+  return fmaf(-h, __cosf(v * a2), v + h);
+}
+__device__ __forceinline__ float2 snake2(float2 v, float2 a2, float2 h) {
+  const float2 t = mul2(v, a2);
+  const float2 c = make_float2(__cosf(t.x), __cosf(t.y));
+  return fma2(make_float2(-h.x, -h.y), c, add2(v, h));
 }
 
 __device__ __forceinline__ void load16f(const float* __restrict__ p, float (&o)[16]) {

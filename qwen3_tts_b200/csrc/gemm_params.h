@@ -14,7 +14,8 @@
 //   v = acc + bias[n % ncol_mod]; act (GELU erf | GLU silu(g)*u on interleaved column pairs);
 //   v *= scale[n % ncol_mod]; v += res[b, t, n];
 //   out_raw / out_f32 <- v;  out_snake <- v + snake_ib[c] * sin^2(snake_a[c] * v)   (SnakeBeta of the NEXT layer,
-//   modeling :601-615, with a = exp(alpha), ib = 1/(exp(beta)+1e-9) precomputed at load).
+//   modeling :601-615; evaluated in the cosine form of epilogue.cuh snake() from the tables snake_a = 2 exp(alpha),
+//   snake_ib = (1/2) / (exp(beta)+1e-9) precomputed at load).
 #pragma once
 #include <stdint.h>
 

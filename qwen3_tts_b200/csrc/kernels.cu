@@ -82,8 +82,9 @@ cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaS
 __global__ void k_pack_snake(const float* alpha, const float* beta, float* a, float* ib, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
-    a[i] = expf(alpha[i]);
-    ib[i] = 1.0f / (expf(beta[i]) + 1e-9f);
+    // tables of the cosine form of SnakeBeta (epilogue.cuh snake()): 2*exp(alpha) and (1/2) / (exp(beta) + 1e-9)
+    a[i] = 2.0f * expf(alpha[i]);
+    ib[i] = 0.5f / (expf(beta[i]) + 1e-9f);
   }
 }
 cudaError_t pack_snake(const float* alpha, const float* beta, float* a, float* ib, int n, cudaStream_t s) {

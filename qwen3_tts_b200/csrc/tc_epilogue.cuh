@@ -143,7 +143,7 @@ struct EpiWarp {
     if (p.bias && !(p.dbg & 16)) {
       float t[16]; load16f(p.bias + c0, t);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] += t[i];
+      for (int i = 0; i < 16; i += 2) { const float2 r = add2(make_float2(v[i], v[i + 1]), make_float2(t[i], t[i + 1])); v[i] = r.x; v[i + 1] = r.y; }
     }
     if (p.act == ACT_GELU) {
 #pragma unroll
@@ -152,11 +152,11 @@ struct EpiWarp {
     if (p.scale) {
       float t[16]; load16f(p.scale + c0, t);
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] *= t[i];
+      for (int i = 0; i < 16; i += 2) { const float2 r = mul2(make_float2(v[i], v[i + 1]), make_float2(t[i], t[i + 1])); v[i] = r.x; v[i + 1] = r.y; }
     }
     if (has_res) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] += rs[i];
+      for (int i = 0; i < 16; i += 2) { const float2 r = add2(make_float2(v[i], v[i + 1]), make_float2(rs[i], rs[i + 1])); v[i] = r.x; v[i + 1] = r.y; }
     }
   }
   __device__ __forceinline__ void snake_unit(float (&v)[16], int c0) {
@@ -169,7 +169,10 @@ struct EpiWarp {
       load16f(p.snake_ib + c0, sib);
     }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = snake(v[i], sa[i], sib[i]);
+    for (int i = 0; i < 16; i += 2) {
+      const float2 r = snake2(make_float2(v[i], v[i + 1]), make_float2(sa[i], sa[i + 1]), make_float2(sib[i], sib[i + 1]));
+      v[i] = r.x; v[i + 1] = r.y;
+    }
   }
   __device__ __forceinline__ void res_consumed() {  // slot fully read by every lane: refill it rd slots ahead
     __syncwarp();

@@ -337,10 +337,12 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint32_t pa = prm_s + (uint32_t)(pcol0 + g + 4 * q) * 4u;
           const float4 b = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
           const uint32_t* r = q < 4 ? &ra[4 * q] : &rb[4 * (q - 4)];
-          const float v0 = snake(__uint_as_float(r[0]) + b.x, a.x, ib.x), v1 = snake(__uint_as_float(r[1]) + b.y, a.y, ib.y);
-          const float v2 = snake(__uint_as_float(r[2]) + b.z, a.z, ib.z), v3 = snake(__uint_as_float(r[3]) + b.w, a.w, ib.w);
-          pk[2 * q] = Elem<T>::pack2(v0, v1);
-          pk[2 * q + 1] = Elem<T>::pack2(v2, v3);
+          const float2 v01 = snake2(add2(make_float2(__uint_as_float(r[0]), __uint_as_float(r[1])), make_float2(b.x, b.y)),
+                                    make_float2(a.x, a.y), make_float2(ib.x, ib.y));
+          const float2 v23 = snake2(add2(make_float2(__uint_as_float(r[2]), __uint_as_float(r[3])), make_float2(b.z, b.w)),
+                                    make_float2(a.z, a.w), make_float2(ib.z, ib.w));
+          pk[2 * q] = Elem<T>::pack2(v01.x, v01.y);
+          pk[2 * q + 1] = Elem<T>::pack2(v23.x, v23.y);
         }
         const uint32_t (&p0)[8] = *reinterpret_cast<const uint32_t (*)[8]>(&pk[0]);
         const uint32_t (&p1)[8] = *reinterpret_cast<const uint32_t (*)[8]>(&pk[8]);
@@ -421,12 +423,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const uint32_t pa = prm_s + (uint32_t)(3 * C + pcol0 + 32 * item + 8 * c + 4 * q) * 4u;
             const float4 bb = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
             const float2 x0 = Elem<T>::unpack2(rw[2 * q]), x1 = Elem<T>::unpack2(rw[2 * q + 1]);
-            const float y0 = __uint_as_float(r[4 * q]) + bb.x + x0.x, y1 = __uint_as_float(r[4 * q + 1]) + bb.y + x0.y;
-            const float y2 = __uint_as_float(r[4 * q + 2]) + bb.z + x1.x, y3 = __uint_as_float(r[4 * q + 3]) + bb.w + x1.y;
-            oraw[4 * c + 2 * q] = Elem<T>::pack2(y0, y1);
-            oraw[4 * c + 2 * q + 1] = Elem<T>::pack2(y2, y3);
-            osnk[4 * c + 2 * q] = Elem<T>::pack2(snake(y0, a.x, ib.x), snake(y1, a.y, ib.y));
-            osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(snake(y2, a.z, ib.z), snake(y3, a.w, ib.w));
+            const float2 y01 = add2(add2(make_float2(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1])), make_float2(bb.x, bb.y)), x0);
+            const float2 y23 = add2(add2(make_float2(__uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])), make_float2(bb.z, bb.w)), x1);
+            oraw[4 * c + 2 * q] = Elem<T>::pack2(y01.x, y01.y);
+            oraw[4 * c + 2 * q + 1] = Elem<T>::pack2(y23.x, y23.y);
+            const float2 s01 = snake2(y01, make_float2(a.x, a.y), make_float2(ib.x, ib.y));
+            const float2 s23 = snake2(y23, make_float2(a.z, a.w), make_float2(ib.z, ib.w));
+            osnk[4 * c + 2 * q] = Elem<T>::pack2(s01.x, s01.y);
+            osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(s23.x, s23.y);
           }
         }
         const bool do_store = !(p.dbg & 64);  // debug: phase 2 without its output stores
