@@ -30,6 +30,13 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 B_UTT, T_FRAMES = 64, 125
+N_SAMPLES = 239445  # T*1920 - 555 per 300-frame chunk (modeling :885-895)
+WORKLOADS = {  # name -> (utterances per GPU per step, frames per utterance, BASELINE.json config it stands for)
+    "bulk10s": (64, 125, "Tokenizer-12Hz non-streaming bulk decode, batch 64 x 10 s synthetic 16-codebook codes per GPU (BASELINE config 2)"),
+    "longform60s": (32, 750, "Long-form decode, batch 32 x 60 s codes per GPU through chunked_decode (chunks 300 / 25+300 / 25+150; BASELINE config 4)"),
+    "bulk30s": (64, 375, "Offline bulk decode of 30 s utterances, one batch of 64 per GPU per step (4096 utterances = 64 such steps at N=1, "
+                         "utterance-sharded over N GPUs; chunks 300 / 25+75; BASELINE config 5)"),
+}
 FRAME_SEC = 0.08
 GFLOP_PER_FRAME = 5.1226  # 2 x 2561.30 MMAC per emitted code frame
 
@@ -144,10 +151,10 @@ def cpu_reference_run(steps: int, warmup: int, utterances: int = 1):
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
-    assert out[0].shape[0] == 239445
+    assert out[0].shape[0] == N_SAMPLES
     sec = statistics.median(times)
     return {"value": utterances * T_FRAMES * FRAME_SEC / sec, "sec_per_step": sec, "cores": torch.get_num_threads(),
-            "sample": f"{utterances} of the {B_UTT} utterances x 10 s per step, median of {steps} after {warmup} warm-up"}
+            "sample": f"{utterances} of the {B_UTT} utterances x {T_FRAMES * FRAME_SEC:g} s per step, median of {steps} after {warmup} warm-up"}
 
 
 def run_reference(args, rank: int):
@@ -159,7 +166,7 @@ def run_reference(args, rank: int):
     line = {"impl": "reference", "metric": "audio-sec decoded per sec (codes->24kHz)", "value": r["value"], "unit": "audio-s/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["sec_per_step"] * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": "Tokenizer-12Hz bulk decode, batch 64 x 10 s synthetic codes (config 2); bounded sample: 1 utterance per step"},
+            "config": {"workload": WORKLOADS[args.workload][2] + "; bounded sample: 1 utterance per step"},
             "cpu_baseline": {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -217,11 +224,17 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16"], help="tensor-core operand type (fp32 accumulate)")
+    ap.add_argument("--workload", default="bulk10s", choices=sorted(WORKLOADS), help="default = the configuration BASELINE.json's metric is quoted on")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true", help="skip the streaming-chunk latency section (BASELINE config 3)")
     ap.add_argument("--stream-only", action="store_true", help="print only the streaming-chunk latency section")
     ap.add_argument("--streams", type=int, default=256)
     args = ap.parse_args()
+    global B_UTT, T_FRAMES, N_SAMPLES
+    B_UTT, T_FRAMES, workload_name = WORKLOADS[args.workload]
+    N_SAMPLES = T_FRAMES * 1920 - 555 * ((T_FRAMES + 299) // 300)
+    if args.workload != "bulk10s":
+        args.no_streaming = True  # the streaming section rides on the default line only
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -260,7 +273,7 @@ def main():
         out = {"streaming": [stream_latency(dec, cfg, dev, args.streams, P, steps=2000 // P, warmup=200 // P) for P in (1, 2, 4)]}
         print(json.dumps(out), flush=True)
         return
-    dec.reserve(B_UTT * T_FRAMES)
+    dec.reserve(B_UTT * min(T_FRAMES, 325))                                  # largest single forward: 300-frame chunk + 25 of left context
     tok = Qwen3TTSTokenizer.from_model(model)
     codes_host = make_codes(B_UTT, T_FRAMES, cfg, seed=1 + rank)            # [B,T,Q] int64
     codes_dev = codes_host.to(dev).transpose(1, 2).contiguous()              # [B,Q,T] resident in HBM
@@ -296,7 +309,7 @@ def main():
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop()
-    assert sr == 24000 and len(wavs) == B_UTT and wavs[0].shape == (239445,) and tuple(wav.shape) == (B_UTT, 1, 239445)
+    assert sr == 24000 and len(wavs) == B_UTT and wavs[0].shape == (N_SAMPLES,) and tuple(wav.shape) == (B_UTT, 1, N_SAMPLES)
     if world > 1:
         t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)                             # max over ranks
@@ -339,13 +352,13 @@ def main():
     line = {"metric": "audio-sec decoded per sec (codes->24kHz)", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": f"{args.mode} operands, fp32 accumulate", "data": "synthetic",
-            "config": {"workload": "Tokenizer-12Hz non-streaming bulk decode, batch 64 x 10 s synthetic 16-codebook codes per GPU (BASELINE config 2)",
+            "config": {"workload": workload_name,
                        "frames_per_step_per_gpu": B_UTT * T_FRAMES, "weights": "seeded random-init, reference architecture (195.08 M params)",
                        "l2": "flushed between timed steps (256 MiB write, untimed); activations per step >> 126 MB L2",
                        "parallelism": f"utterance-sharded x{world}, no collective"},
             "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": world * B_UTT * T_FRAMES * 16 * 8,
-                    "d2h_bytes_per_step": world * B_UTT * 239445 * 4, "ms_per_step": e2e_s / args.steps * 1e3,
-                    "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [125,16]}) -> host float32 arrays"},
+                    "d2h_bytes_per_step": world * B_UTT * N_SAMPLES * 4, "ms_per_step": e2e_s / args.steps * 1e3,
+                    "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [T,16]}) -> host float32 arrays"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
             "path_frac_of_tensor_roofline": path_frac, "kernels": by_kernel}
     if world == 1:
@@ -359,10 +372,10 @@ def main():
             pcm, _sr = tok.decode_pcm16(items16)
         torch.cuda.synchronize(dev)
         t16 = time.perf_counter() - t0
-        assert len(pcm) == B_UTT and pcm[0].shape == (239445,) and str(pcm[0].dtype) == "int16"
+        assert len(pcm) == B_UTT and pcm[0].shape == (N_SAMPLES,) and str(pcm[0].dtype) == "int16"
         line["e2e_pcm16"] = {"value": B_UTT * T_FRAMES * FRAME_SEC * args.steps / t16, "unit": "audio-s/s", "ms_per_step": t16 / args.steps * 1e3,
-                             "h2d_bytes_per_step": B_UTT * T_FRAMES * 16 * 2, "d2h_bytes_per_step": B_UTT * 239445 * 2,
-                             "api": "Qwen3TTSTokenizer.decode_pcm16(list of {'audio_codes': int16 [125,16]}) -> host int16 PCM arrays"}
+                             "h2d_bytes_per_step": B_UTT * T_FRAMES * 16 * 2, "d2h_bytes_per_step": B_UTT * N_SAMPLES * 2,
+                             "api": "Qwen3TTSTokenizer.decode_pcm16(list of {'audio_codes': int16 [T,16]}) -> host int16 PCM arrays"}
     if not args.no_streaming and world == 1:
         # BASELINE config 3 rides along as its own section: it is a latency, not the throughput metric of this line
         dec.reserve_streams(args.streams, 4)
