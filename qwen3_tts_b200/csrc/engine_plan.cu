@@ -305,6 +305,18 @@ void prof_account(Engine* e, const Op& op) {
     dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
     fl = 2.0 * rows * C * C * 8.0;
     by = 2.0 * (4.0 * rows * C + 8.0 * C * C);  // a1 + x in, y + snake(y) out, weights once
+  } else if (op.type == OP_RVQ) {
+    // the 32 MiB of tables are L2-resident after warm-up, so the HBM floor is the codes in and the embeddings out
+    by = (double)op.B * op.L * (e->cfg.num_quantizers * 8.0 + 2.0 * op.C);
+  } else if (op.type == OP_RMSNORM) {
+    by = (double)op.B * op.C * (4.0 + 2.0);  // fp32 residual stream in, 16-bit normalised rows out (op.B = rows)
+  } else if (op.type == OP_ATTN) {
+    const double rows = (double)op.B * op.L, H = (double)e->cfg.num_attention_heads * e->cfg.head_dim;
+    dims[1] = (int)H;
+    fl = 4.0 * rows * H * e->cfg.sliding_window;  // QK^T and PV at a full window, as SURVEY 8(a) counts them
+    by = 2.0 * rows * 4.0 * H;                    // q, k, v in, o out (16-bit)
+  } else if (op.type == OP_DWLN) {
+    by = 2.0 * 2.0 * (double)op.B * op.L * op.C;  // one read and one write of the token tensor (16-bit)
   }
   e->prof_type.push_back((int)op.type);
   e->prof_flops.push_back(fl);

@@ -2,6 +2,7 @@
 // attention, depthwise conv + LayerNorm, tail conv + clamp, layout probes.
 #include "kernels.h"
 #include "ptx.cuh"
+#include "attention_mma.cuh"
 
 namespace q3 {
 
@@ -124,114 +125,75 @@ cudaError_t rope_table(float* cos_t, float* sin_t, int maxT, int hd, float theta
 }
 
 // ============================================================================================ attention
-// Block = (32-query tile, head, batch item); 8 warps x 4 queries.  K (RoPE applied) and V of the
-// <= window-1+32 keys a tile can see are staged in shared memory; scores use one lane per key,
-// softmax in fp32 (reference modeling :134-141), mask = kv <= q && kv > q - window.
-static constexpr int ATT_QT = 32;
-static constexpr int ATT_HD = 64;
-static constexpr int ATT_KSTR = ATT_HD + 2;  // 33-word row pitch: conflict-free lane-per-key reads
+// RoPE + sliding-window causal attention (modeling :281-353, mask :546-550).  Block = (64 queries, head, item), 4 warps of
+// 16 queries each on mma.sync tensor-core tiles (attention_mma.cuh).  K (RoPE applied) and V of the <= 71 + 64 visible keys
+// are staged once per block at row (t - kbase), kbase = 16-aligned; rows outside [k_lo, k_hi) are zero.
+static constexpr int ATT_QT = 64;
+static constexpr int ATT_ROWS = 160;  // ((64 + 71 - 1 + 15) | 15) + 1 key rows at most
 
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t, T* __restrict__ out, int Tn, int nh,
             int window) {
   extern __shared__ __align__(16) uint8_t att_smem[];
   const int q0 = blockIdx.x * ATT_QT, h = blockIdx.y, b = blockIdx.z;
   const int k_lo = max(0, q0 - window + 1);
   const int k_hi = min(Tn, q0 + ATT_QT);  // exclusive
-  const int nk = k_hi - k_lo;
-  const int maxk = window - 1 + ATT_QT;
+  const int kbase = k_lo & ~15;
+  const int nrows = ((k_hi - 1 - kbase) | 15) + 1;
   T* sK = reinterpret_cast<T*>(att_smem);
-  T* sV = sK + (((size_t)maxk * ATT_KSTR + 7) & ~(size_t)7);  // keep V rows 16-byte aligned
-  float* sQ = reinterpret_cast<float*>(sV + (size_t)maxk * ATT_HD);  // [8 warps][64]
-  float* sP = sQ + 8 * ATT_HD;                                        // [8 warps][maxk rounded to 32]
-  const int pstride = ((maxk + 31) / 32) * 32;
-  const int ld = 3 * nh * ATT_HD;
-  const T* base = qkv + (long long)b * Tn * ld;
-  // stage K with RoPE: item = (key, d < 32) handles the pair (d, d + 32)
-  for (int i = threadIdx.x; i < nk * 32; i += blockDim.x) {
-    const int kk = i >> 5, d = i & 31;
-    const int t = k_lo + kk;
-    const T* kr = base + (long long)t * ld + nh * ATT_HD + h * ATT_HD;
-    const float x1 = Elem<T>::to_f(kr[d]), x2 = Elem<T>::to_f(kr[d + 32]);
-    const float c = cos_t[t * 32 + d], sn = sin_t[t * 32 + d];
-    sK[kk * ATT_KSTR + d] = Elem<T>::from_f(x1 * c - x2 * sn);
-    sK[kk * ATT_KSTR + d + 32] = Elem<T>::from_f(x2 * c + x1 * sn);
+  T* sV = sK + ATT_ROWS * AM_PITCH;
+  T* sQ = sV + ATT_ROWS * AM_PITCH;
+  const int ld = 3 * nh * AM_HD;
+  const T* base = qkv + (long long)b * Tn * ld + h * AM_HD;
+  for (int i = threadIdx.x; i < nrows * 4; i += blockDim.x) {
+    const int r = i >> 2, part = i & 3, t = kbase + r;
+    if (t >= k_lo && t < k_hi) {
+      float cs[8], sn[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { cs[j] = cos_t[t * 32 + part * 8 + j]; sn[j] = sin_t[t * 32 + part * 8 + j]; }
+      rope_row8<T>(base + (long long)t * ld + nh * AM_HD, cs, sn, sK + r * AM_PITCH, part);
+      const uint4* vr = reinterpret_cast<const uint4*>(base + (long long)t * ld + 2 * nh * AM_HD);
+      reinterpret_cast<uint4*>(sV + r * AM_PITCH)[part] = vr[part];
+      reinterpret_cast<uint4*>(sV + r * AM_PITCH)[part + 4] = vr[part + 4];
+    } else {
+      zero_row8(sK + r * AM_PITCH, part);
+      zero_row8(sV + r * AM_PITCH, part);
+    }
   }
-  for (int i = threadIdx.x; i < nk * 8; i += blockDim.x) {
-    const int kk = i >> 3, c8 = i & 7;
-    const T* vr = base + (long long)(k_lo + kk) * ld + 2 * nh * ATT_HD + h * ATT_HD;
-    reinterpret_cast<uint4*>(sV + (size_t)kk * ATT_HD)[c8] = reinterpret_cast<const uint4*>(vr)[c8];
+  for (int i = threadIdx.x; i < ATT_QT * 4; i += blockDim.x) {
+    const int r = i >> 2, part = i & 3, t = q0 + r;
+    if (t < Tn) {
+      float cs[8], sn[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { cs[j] = cos_t[t * 32 + part * 8 + j]; sn[j] = sin_t[t * 32 + part * 8 + j]; }
+      rope_row8<T>(base + (long long)t * ld, cs, sn, sQ + r * AM_PITCH, part);
+    } else {
+      zero_row8(sQ + r * AM_PITCH, part);
+    }
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* q = sQ + warp * ATT_HD;
-  float* pr = sP + warp * pstride;
-  for (int qi = warp; qi < ATT_QT; qi += 8) {
-    const int tq = q0 + qi;
-    if (tq >= Tn) break;
-    {
-      const T* qr = base + (long long)tq * ld + h * ATT_HD;
-      const float x1 = Elem<T>::to_f(qr[lane]), x2 = Elem<T>::to_f(qr[lane + 32]);
-      const float c = cos_t[tq * 32 + lane], sn = sin_t[tq * 32 + lane];
-      q[lane] = x1 * c - x2 * sn;
-      q[lane + 32] = x2 * c + x1 * sn;
-    }
-    __syncwarp();
-    const int lo = max(0, tq - window + 1);  // first visible key
-    const int nvis = tq - lo + 1;
-    float mx = -INFINITY;
-    for (int j0 = 0; j0 < nvis; j0 += 32) {
-      const int j = j0 + lane;
-      float sc = -INFINITY;
-      if (j < nvis) {
-        const uint32_t* kr = reinterpret_cast<const uint32_t*>(sK + (size_t)(lo - k_lo + j) * ATT_KSTR);
-        float acc = 0.f;
-#pragma unroll
-        for (int d2 = 0; d2 < 32; ++d2) {
-          const float2 kv = Elem<T>::unpack2(kr[d2]);
-          acc = fmaf(q[2 * d2], kv.x, acc);
-          acc = fmaf(q[2 * d2 + 1], kv.y, acc);
-        }
-        sc = acc * 0.125f;
-      }
-      pr[j] = sc;
-      mx = fmaxf(mx, sc);
-    }
-    mx = warp_max(mx);
-    float sum = 0.f;
-    for (int j0 = 0; j0 < nvis; j0 += 32) {
-      const int j = j0 + lane;
-      if (j < nvis) {
-        const float e = __expf(pr[j] - mx);
-        pr[j] = e;
-        sum += e;
-      }
-    }
-    sum = warp_sum(sum);
-    __syncwarp();
-    const float inv = 1.0f / sum;
-    float o0 = 0.f, o1 = 0.f;
-    const uint32_t* vb = reinterpret_cast<const uint32_t*>(sV + (size_t)(lo - k_lo) * ATT_HD) + lane;
-    for (int j = 0; j < nvis; ++j) {
-      const float pj = pr[j];
-      const float2 vv = Elem<T>::unpack2(vb[j * (ATT_HD / 2)]);
-      o0 = fmaf(pj, vv.x, o0);
-      o1 = fmaf(pj, vv.y, o1);
-    }
-    reinterpret_cast<uint32_t*>(out + ((long long)b * Tn + tq) * (nh * ATT_HD) + h * ATT_HD)[lane] = Elem<T>::pack2(o0 * inv, o1 * inv);
-    __syncwarp();
-  }
+  const int warp = threadIdx.x >> 5;
+  const int tq0 = q0 + warp * 16;
+  const int nq = min(16, Tn - tq0);
+  if (nq > 0)
+    attn_warp16<T>(sQ + warp * 16 * AM_PITCH, sK, sV, tq0, nq, kbase, window, out + ((long long)b * Tn + tq0) * (nh * AM_HD) + h * AM_HD,
+                   (long long)nh * AM_HD);
 }
 cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* sin_t, void* out, int B, int Tn, int nh, int hd, int window,
                               bool bf16, cudaStream_t s) {
-  if (hd != ATT_HD) return cudaErrorInvalidValue;
+  if (hd != AM_HD || window < 1 || window > 72) return cudaErrorInvalidValue;  // AM_MAXCH chunks cover a window of at most 72
   if (B <= 0 || Tn <= 0) return cudaSuccess;
-  const int maxk = window - 1 + ATT_QT;
-  const int pstride = ((maxk + 31) / 32) * 32;
-  const size_t smem = ((((size_t)maxk * ATT_KSTR + 7) & ~(size_t)7) + (size_t)maxk * ATT_HD) * 2 + 8 * ATT_HD * 4 + 8 * pstride * 4;
+  const size_t smem = (size_t)(2 * ATT_ROWS + ATT_QT) * AM_PITCH * 2;
+  static bool attr_done[2] = {false, false};
+  if (!attr_done[bf16 ? 1 : 0]) {
+    cudaError_t e;
+    Q3_DISPATCH(bf16, (e = cudaFuncSetAttribute(k_attention<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
+    if (e != cudaSuccess) return e;
+    attr_done[bf16 ? 1 : 0] = true;
+  }
   dim3 grid((Tn + ATT_QT - 1) / ATT_QT, nh, B);
-  Q3_DISPATCH(bf16, (k_attention<T><<<grid, 256, smem, s>>>((const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
+  Q3_DISPATCH(bf16, (k_attention<T><<<grid, 128, smem, s>>>((const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
   return cudaGetLastError();
 }
 

@@ -4,6 +4,7 @@
 // Decoder.forward(whole sequence) (DESIGN.md "Streaming").
 #include "kernels.h"
 #include "ptx.cuh"
+#include "attention_mma.cuh"
 
 namespace q3 {
 
@@ -37,134 +38,94 @@ __device__ __forceinline__ void rope_cs(const float* __restrict__ cos_t, const f
   }
 }
 
-static constexpr int SA_HD = 64;
-static constexpr int SA_KSTR = SA_HD + 2;  // odd word pitch: conflict-free lane-per-key reads
-static constexpr int SA_WARPS = 4;
+static constexpr int SA_WARPS = 4;  // 16 queries per warp: P <= 64 new frames per step
 
 // Block = (head, stream).  Phase 1 appends the P new keys (RoPE applied) and values to the slot's ring cache, phase 2 stages the
-// visible keys / values in shared memory, phase 3: one warp per query, one lane per key, fp32 softmax (reference modeling :134-141).
+// visible keys / values in shared memory at row (t - kbase), kbase 16-aligned, phase 3 is the same warp-level tensor-core
+// routine as the bulk kernel (attention_mma.cuh) - same absolute key tiles, hence bit-identical results.
 template <typename T>
 __global__ void __launch_bounds__(SA_WARPS * 32)
 k_stream_attention(const T* __restrict__ qkv, T* __restrict__ kc, T* __restrict__ vc, const int* __restrict__ slot_ids, const int* __restrict__ slot_pos,
                    const float* __restrict__ cos_t, const float* __restrict__ sin_t, int rope_max, float theta, T* __restrict__ out, int P, int nh,
-                   int window, int ring) {
+                   int window, int ring, int krows) {
   extern __shared__ __align__(16) uint8_t sa_smem[];
   const int h = blockIdx.x, s = blockIdx.y;
   const int slot = slot_ids[s];
   const int pos0 = slot_pos[slot];
-  const int H = nh * SA_HD, ld = 3 * H;
-  const int maxk = window - 1 + P;
+  const int H = nh * AM_HD, ld = 3 * H;
   T* sK = reinterpret_cast<T*>(sa_smem);
-  T* sV = sK + (((size_t)maxk * SA_KSTR + 7) & ~(size_t)7);
-  float* sQ = reinterpret_cast<float*>(sV + (size_t)maxk * SA_HD);  // [warps][64]
-  const int pstride = ((maxk + 31) / 32) * 32;
-  float* sP = sQ + SA_WARPS * SA_HD;                                 // [warps][pstride]
-  const T* base = qkv + (long long)s * P * ld;
-  T* kslot = kc + (long long)slot * ring * H + h * SA_HD;
-  T* vslot = vc + (long long)slot * ring * H + h * SA_HD;
-  // ---- phase 1: append
-  for (int i = threadIdx.x; i < P * 32; i += blockDim.x) {
-    const int t = i >> 5, d = i & 31;
-    const int pos = pos0 + t;
-    const T* kr = base + (long long)t * ld + H + h * SA_HD;
-    const float x1 = Elem<T>::to_f(kr[d]), x2 = Elem<T>::to_f(kr[d + 32]);
-    float c, sn;
-    rope_cs(cos_t, sin_t, rope_max, theta, pos, d, c, sn);
-    T* dst = kslot + (long long)(pos & (ring - 1)) * H;
-    dst[d] = Elem<T>::from_f(x1 * c - x2 * sn);
-    dst[d + 32] = Elem<T>::from_f(x2 * c + x1 * sn);
-  }
-  for (int i = threadIdx.x; i < P * 8; i += blockDim.x) {
-    const int t = i >> 3, c8 = i & 7;
-    const T* vr = base + (long long)t * ld + 2 * H + h * SA_HD;
-    reinterpret_cast<uint4*>(vslot + (long long)((pos0 + t) & (ring - 1)) * H)[c8] = reinterpret_cast<const uint4*>(vr)[c8];
-  }
-  __syncthreads();
-  // ---- phase 2: stage the keys every new query can see
+  T* sV = sK + krows * AM_PITCH;
+  T* sQ = sV + krows * AM_PITCH;
+  const T* base = qkv + (long long)s * P * ld + h * AM_HD;
+  T* kslot = kc + (long long)slot * ring * H + h * AM_HD;
+  T* vslot = vc + (long long)slot * ring * H + h * AM_HD;
   const int k_lo = max(0, pos0 - window + 1);
-  const int nk = pos0 + P - k_lo;
-  for (int i = threadIdx.x; i < nk * 32; i += blockDim.x) {
-    const int kk = i >> 5, d2 = i & 31;
-    const uint32_t w = reinterpret_cast<const uint32_t*>(kslot + (long long)((k_lo + kk) & (ring - 1)) * H)[d2];
-    reinterpret_cast<uint32_t*>(sK + (size_t)kk * SA_KSTR)[d2] = w;
+  const int kbase = k_lo & ~15;
+  const int nrows = ((pos0 + P - 1 - kbase) | 15) + 1;
+  const int qrows = (P + 15) & ~15;
+  // ---- phase 1: the packet's keys (rotated) and values go to the ring and, in the same pass, to their shared-memory rows;
+  //      the packet's queries are rotated into sQ
+  for (int i = threadIdx.x; i < qrows * 4; i += blockDim.x) {
+    const int t = i >> 2, part = i & 3;
+    if (t < P) {
+      const int pos = pos0 + t;
+      float cs[8], sn[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rope_cs(cos_t, sin_t, rope_max, theta, pos, part * 8 + j, cs[j], sn[j]);
+      T* krow = sK + (pos - kbase) * AM_PITCH;
+      rope_row8<T>(base + (long long)t * ld + H, cs, sn, krow, part);
+      T* kdst = kslot + (long long)(pos & (ring - 1)) * H;
+      reinterpret_cast<uint4*>(kdst)[part] = reinterpret_cast<const uint4*>(krow)[part];
+      reinterpret_cast<uint4*>(kdst)[part + 4] = reinterpret_cast<const uint4*>(krow)[part + 4];
+      const uint4* vr = reinterpret_cast<const uint4*>(base + (long long)t * ld + 2 * H);
+      T* vdst = vslot + (long long)(pos & (ring - 1)) * H;
+      const uint4 v0 = vr[part], v1 = vr[part + 4];
+      reinterpret_cast<uint4*>(vdst)[part] = v0; reinterpret_cast<uint4*>(vdst)[part + 4] = v1;
+      reinterpret_cast<uint4*>(sV + (pos - kbase) * AM_PITCH)[part] = v0; reinterpret_cast<uint4*>(sV + (pos - kbase) * AM_PITCH)[part + 4] = v1;
+      rope_row8<T>(base + (long long)t * ld, cs, sn, sQ + t * AM_PITCH, part);
+    } else {
+      zero_row8(sQ + t * AM_PITCH, part);
+    }
   }
-  for (int i = threadIdx.x; i < nk * 8; i += blockDim.x) {
-    const int kk = i >> 3, c8 = i & 7;
-    reinterpret_cast<uint4*>(sV + (size_t)kk * SA_HD)[c8] = reinterpret_cast<const uint4*>(vslot + (long long)((k_lo + kk) & (ring - 1)) * H)[c8];
+  // ---- phase 2: older visible keys / values from the ring; rows outside [k_lo, pos0 + P) are zero
+  for (int i = threadIdx.x; i < nrows * 4; i += blockDim.x) {
+    const int r = i >> 2, part = i & 3, t = kbase + r;
+    if (t >= pos0 && t < pos0 + P) continue;  // written by phase 1
+    if (t >= k_lo && t < pos0) {
+      const uint4* kr = reinterpret_cast<const uint4*>(kslot + (long long)(t & (ring - 1)) * H);
+      const uint4* vr = reinterpret_cast<const uint4*>(vslot + (long long)(t & (ring - 1)) * H);
+      reinterpret_cast<uint4*>(sK + r * AM_PITCH)[part] = kr[part]; reinterpret_cast<uint4*>(sK + r * AM_PITCH)[part + 4] = kr[part + 4];
+      reinterpret_cast<uint4*>(sV + r * AM_PITCH)[part] = vr[part]; reinterpret_cast<uint4*>(sV + r * AM_PITCH)[part + 4] = vr[part + 4];
+    } else {
+      zero_row8(sK + r * AM_PITCH, part);
+      zero_row8(sV + r * AM_PITCH, part);
+    }
   }
   __syncthreads();
   // ---- phase 3
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* q = sQ + warp * SA_HD;
-  float* pr = sP + warp * pstride;
-  for (int qi = warp; qi < P; qi += SA_WARPS) {
-    const int tq = pos0 + qi;
-    {
-      const T* qr = base + (long long)qi * ld + h * SA_HD;
-      const float x1 = Elem<T>::to_f(qr[lane]), x2 = Elem<T>::to_f(qr[lane + 32]);
-      float c, sn;
-      rope_cs(cos_t, sin_t, rope_max, theta, tq, lane, c, sn);
-      q[lane] = x1 * c - x2 * sn;
-      q[lane + 32] = x2 * c + x1 * sn;
-    }
-    __syncwarp();
-    const int lo = max(0, tq - window + 1);
-    const int nvis = tq - lo + 1;
-    float mx = -INFINITY;
-    for (int j0 = 0; j0 < nvis; j0 += 32) {
-      const int j = j0 + lane;
-      float sc = -INFINITY;
-      if (j < nvis) {
-        const uint32_t* kr = reinterpret_cast<const uint32_t*>(sK + (size_t)(lo - k_lo + j) * SA_KSTR);
-        float acc = 0.f;
-#pragma unroll
-        for (int d2 = 0; d2 < 32; ++d2) {
-          const float2 kv = Elem<T>::unpack2(kr[d2]);
-          acc = fmaf(q[2 * d2], kv.x, acc);
-          acc = fmaf(q[2 * d2 + 1], kv.y, acc);
-        }
-        sc = acc * 0.125f;
-      }
-      pr[j] = sc;
-      mx = fmaxf(mx, sc);
-    }
-    mx = wmax(mx);
-    float sum = 0.f;
-    for (int j0 = 0; j0 < nvis; j0 += 32) {
-      const int j = j0 + lane;
-      if (j < nvis) {
-        const float e = __expf(pr[j] - mx);
-        pr[j] = e;
-        sum += e;
-      }
-    }
-    sum = wsum(sum);
-    __syncwarp();
-    const float inv = 1.0f / sum;
-    float o0 = 0.f, o1 = 0.f;
-    const uint32_t* vb = reinterpret_cast<const uint32_t*>(sV + (size_t)(lo - k_lo) * SA_HD) + lane;
-    for (int j = 0; j < nvis; ++j) {
-      const float pj = pr[j];
-      const float2 vv = Elem<T>::unpack2(vb[j * (SA_HD / 2)]);
-      o0 = fmaf(pj, vv.x, o0);
-      o1 = fmaf(pj, vv.y, o1);
-    }
-    reinterpret_cast<uint32_t*>(out + ((long long)s * P + qi) * H + h * SA_HD)[lane] = Elem<T>::pack2(o0 * inv, o1 * inv);
-    __syncwarp();
-  }
+  const int warp = threadIdx.x >> 5;
+  const int nq = min(16, P - warp * 16);
+  if (nq > 0)
+    attn_warp16<T>(sQ + warp * 16 * AM_PITCH, sK, sV, pos0 + warp * 16, nq, kbase, window,
+                   out + ((long long)s * P + warp * 16) * H + h * AM_HD, (long long)H);
 }
 
 cudaError_t stream_attention(const void* qkv, void* kc, void* vc, const int* slot_ids, const int* slot_pos, const float* cos_t, const float* sin_t,
                              int rope_max, float theta, void* out, int S, int P, int nh, int hd, int window, int ring, bool bf16, cudaStream_t s) {
-  if (hd != SA_HD || (ring & (ring - 1)) || ring < window - 1 + P) return cudaErrorInvalidValue;
+  if (hd != AM_HD || (ring & (ring - 1)) || ring < window - 1 + P || window < 1 || window > 72 || P > SA_WARPS * 16) return cudaErrorInvalidValue;
   if (S <= 0 || P <= 0) return cudaSuccess;
-  const int maxk = window - 1 + P;
-  const int pstride = ((maxk + 31) / 32) * 32;
-  const size_t smem = ((((size_t)maxk * SA_KSTR + 7) & ~(size_t)7) + (size_t)maxk * SA_HD) * 2 + SA_WARPS * SA_HD * 4 + (size_t)SA_WARPS * pstride * 4;
-  if (smem > 48 * 1024) return cudaErrorInvalidValue;
+  const int krows = ((window - 1 + P - 1 + 15) | 15) + 1;  // key rows at most: alignment slack + (window - 1) older keys + P new ones
+  const size_t smem = (size_t)(2 * krows + ((P + 15) & ~15)) * AM_PITCH * 2;
+  static size_t attr_smem[2] = {0, 0};
+  if (smem > 48 * 1024 && smem > attr_smem[bf16 ? 1 : 0]) {
+    cudaError_t e;
+    Q3_DISPATCH(bf16, (e = cudaFuncSetAttribute(k_stream_attention<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
+    if (e != cudaSuccess) return e;
+    attr_smem[bf16 ? 1 : 0] = smem;
+  }
   dim3 grid(nh, S);
   Q3_DISPATCH(bf16, (k_stream_attention<T><<<grid, SA_WARPS * 32, smem, s>>>((const T*)qkv, (T*)kc, (T*)vc, slot_ids, slot_pos, cos_t, sin_t, rope_max, theta,
-                                                                               (T*)out, P, nh, window, ring)));
+                                                                               (T*)out, P, nh, window, ring, krows)));
   return cudaGetLastError();
 }
 
