@@ -97,7 +97,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
                     const GemmParams p, const int nstages) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int KB = p.kb;
   constexpr uint32_t NCTA = PAIR ? 2u : 1u;
   constexpr int TM = PAIR ? 2 * BM : BM;
@@ -215,7 +215,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
                const GemmParams p, const int nslabs, const int srp) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int KB = p.kb;
   const int nkb = p.cin / KB;
   const int halo = -p.tap_off[0];
@@ -322,7 +322,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmSnake, const __grid_constant__ CUtensorMap tmF32,
                  const GemmParams p, const int nslabs, const int nstages, const int srp, const int slab_lo) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int KB = p.kb;
   const int nkb = p.cin / KB;
   const int bn_cta = PAIR ? p.bn / 2 : p.bn;   // weight rows this CTA holds

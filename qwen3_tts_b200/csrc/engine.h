@@ -53,6 +53,7 @@ struct Op {
   void* out = nullptr;
   const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;
   int B = 0, L = 0, C = 0;
+  bool drop_raw = false;   // last residual unit of a decoder block: its raw output is dead (only the Snake'd copy is read), skipped unless probing
   int aux0 = 0, aux1 = 0;  // streaming: RVQ output batch stride in rows / dwconv (input batch stride in rows, history rows) / attention layer
   // probe: the buffer that holds an oracle tap once this op has run
   std::string tag;

@@ -207,6 +207,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
           plan->ops.emplace_back();
           Op& op = plan->ops.back();
           op.type = OP_UNIT; op.u = u; op.B = B; op.L = L; op.C = K.cout;
+          op.drop_raw = j == 2;
           b.tag(op, t.c_str(), R[iy], false, K.cout, L);
           std::swap(ia, ifree);
           continue;
@@ -221,6 +222,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
         Op& op = b.gemm(U.conv1, R[ia], B, L, L);
         op.g.p.res = R[iy]; op.g.p.out_raw = R[iy];
         op.g.p.out_snake = R[ifree]; op.g.p.snake_a = nx.a; op.g.p.snake_ib = nx.ib;
+        op.drop_raw = j == 2;
         b.tag(op, t.c_str(), R[iy], false, K.cout, L);
         std::swap(ia, ifree);
       }
@@ -304,7 +306,7 @@ void prof_account(Engine* e, const Op& op) {
     const double rows = (double)op.B * op.L, C = op.C;
     dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
     fl = 2.0 * rows * C * C * 8.0;
-    by = 2.0 * (4.0 * rows * C + 8.0 * C * C);  // a1 + x in, y + snake(y) out, weights once
+    by = 2.0 * ((op.u.p.skip_raw ? 3.0 : 4.0) * rows * C + 8.0 * C * C);  // a1 + x in, y (unless dead) + snake(y) out, weights once
   } else if (op.type == OP_RVQ) {
     // the 32 MiB of tables are L2-resident after warm-up, so the HBM floor is the codes in and the embeddings out
     by = (double)op.B * op.L * (e->cfg.num_quantizers * 8.0 + 2.0 * op.C);
@@ -329,10 +331,16 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
   const q3tts_config& c = e->cfg;
   size_t pi = 0;
   static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
+  static const bool keep_raw = getenv("Q3TTS_KEEP_RAW") != nullptr;  // debug / A-B: store the dead raw outputs too
   if (e->profile) prof_reset(e, plan->ops.size());
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
+    // dead raw output of a block's last residual unit: not written (a probe of that stage still needs it)
+    const bool drop = op.drop_raw && !probe_stage && !keep_raw;
+    void* const saved_raw = op.g.p.out_raw;
+    if (op.type == OP_UNIT) op.u.p.skip_raw = drop ? 1 : 0;
+    else if (op.type == OP_GEMM && drop) op.g.p.out_raw = nullptr;
     switch (op.type) {
       case OP_RVQ:
         err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s);
@@ -366,6 +374,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       prof_account(e, op);
       ++pi;
     }
+    op.g.p.out_raw = saved_raw;
     if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("launch failed: ") + cudaGetErrorString(err));
     if (probe_stage && !op.tag.empty() && op.tag == probe_stage && op.type != OP_TAIL) {
       const long long n = (long long)plan->B * op.probe_C * op.probe_L;

@@ -48,6 +48,7 @@ struct GemmParams {
   //   mode 2: batch item gc / pack_cpb, rows [(gc % pack_cpb) * 32, +32)
   // so a tile is filled with real rows instead of one batch item's few rows plus padding.  0 = one batch item per tile.
   int pack_mode, pack_rshift, pack_cpb;
+  int skip_raw;  // fused unit kernel: y is not stored (last unit of a block: only snake_next(y) is read downstream)
   int dbg;  // debug experiments (env Q3TTS_DBG): bit 0 = epilogue only drains TMEM, bit 1 = MMA thread issues no MMAs
   const float* bias;
   const float* scale;

@@ -30,7 +30,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
 k_pair_gemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, float* __restrict__ D, float* __restrict__ D2, int N, int K,
             int iters, int ts, long long* clk) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int kblocks = K / 64;
   const uint32_t a_sub = 128 * 128, w_sub = (uint32_t)(N / 2) * 128;
   uint8_t* sA = smem;

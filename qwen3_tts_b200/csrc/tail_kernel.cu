@@ -34,7 +34,7 @@ template <typename T>
 __global__ void __launch_bounds__(192, 1)
 tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const TailParams p, const int nstages) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int KS = p.C / 32;                     // K blocks of 32 channels (64-byte rows, SWIZZLE_64B)
   const uint32_t a_sub = T_ROWS * 64, stage_bytes = (uint32_t)KS * a_sub;
   uint8_t* sW = smem;                          // [KS][16 rows][64 B], 1 KB per K block

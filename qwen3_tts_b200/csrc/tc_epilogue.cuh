@@ -140,7 +140,7 @@ struct EpiWarp {
   }
   // bias -> (GELU) -> scale -> + residual
   __device__ __forceinline__ void math_unit(float (&v)[16], const float (&rs)[16], int c0) {
-    if (p.bias && !(p.dbg & 16)) {
+    if (p.bias) {
       float t[16]; load16f(p.bias + c0, t);
 #pragma unroll
       for (int i = 0; i < 16; i += 2) { const float2 r = add2(make_float2(v[i], v[i + 1]), make_float2(t[i], t[i + 1])); v[i] = r.x; v[i + 1] = r.y; }
@@ -161,13 +161,8 @@ struct EpiWarp {
   }
   __device__ __forceinline__ void snake_unit(float (&v)[16], int c0) {
     float sa[16], sib[16];
-    if (p.dbg & 16) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) { sa[i] = 1.0f; sib[i] = 0.5f; }
-    } else {
-      load16f(p.snake_a + c0, sa);
-      load16f(p.snake_ib + c0, sib);
-    }
+    load16f(p.snake_a + c0, sa);
+    load16f(p.snake_ib + c0, sib);
 #pragma unroll
     for (int i = 0; i < 16; i += 2) {
       const float2 r = snake2(make_float2(v[i], v[i + 1]), make_float2(sa[i], sa[i + 1]), make_float2(sib[i], sib[i + 1]));

@@ -118,7 +118,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr uint32_t NCTA = PAIR ? 2u : 1u;
   constexpr uint32_t span = Cfg::SPAN, wsub = Cfg::WSUB, stage_bytes = Cfg::STAGE_BYTES;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // offset on the shared array: keeps LDS / STS (a uintptr_t round trip makes every access generic)
   const int halo = 6 * u.dil;
   constexpr int TM = PAIR ? 2 * U_BM : U_BM;  // rows of a scheduler tile
   const int rrow = rank * U_BM;               // this CTA's rows inside a tile
@@ -371,6 +371,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t rbar = smem_u32(&bars->res_bar[pw][0]);
     const int sb = NBUF == 2 ? grp : 0;
     const int j0 = NBUF == 2 ? grp : 0;
+    const bool wr_raw = p.skip_raw == 0;  // the last unit of a block stores only snake_next(y)
     uint32_t off[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) off[c] = (uint32_t)(lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4));
@@ -440,14 +441,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          sts_u4(raw_s + off[c], oraw[4 * c], oraw[4 * c + 1], oraw[4 * c + 2], oraw[4 * c + 3]);
+          if (wr_raw) sts_u4(raw_s + off[c], oraw[4 * c], oraw[4 * c + 1], oraw[4 * c + 2], oraw[4 * c + 3]);
           sts_u4(snk_s + off[c], osnk[4 * c], osnk[4 * c + 1], osnk[4 * c + 2], osnk[4 * c + 3]);
         }
         if (do_store) {
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
+            if (wr_raw) tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
             tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
             tma_store_commit();
           }
