@@ -41,6 +41,16 @@ FRAME_SEC = 0.08
 GFLOP_PER_FRAME = 5.1226  # 2 x 2561.30 MMAC per emitted code frame
 
 
+def ncu_traffic(family: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch (average over the family's launches of one forward of this workload)
+    from the committed ncu capture profiles/r1_dram_traffic_forward.json (tools/gpu_round_h.sh); None when there is no capture."""
+    p = os.path.join(ROOT, "profiles", "r1_dram_traffic_forward.json")
+    key = {"tcgen05_conv_gemm": "_tcgen05_conv_gemm_family", "tcgen05_fused_unit": "unit_kernel"}.get(family)
+    if B_UTT != 64 or T_FRAMES != 125 or key is None or not os.path.isfile(p):
+        return None
+    return json.load(open(p)).get(key, {}).get("dram_bytes_per_launch_avg")
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -336,7 +346,7 @@ def main():
     d = by_kernel[dom]
     roof = {"bound": "tensor", "kernel": kernel_fn[dom],
             "achieved": d["flops"] / (d["ms"] * 1e-3) / 1e12,
-            "peak": peaks["tflops_sustained"], "unit": "TFLOP/s", "traffic": None,
+            "peak": peaks["tflops_sustained"], "unit": "TFLOP/s", "traffic": ncu_traffic(dom),
             "peak_source": f"{peaks['source']} sustained bf16 cuBLAS (kernel timed inside a long step)",
             "share_of_step": d["ms"] / tot_ms, "flops_per_launch_avg": d["flops"] / d["launches"], "ms_per_launch_avg": d["ms"] / d["launches"]}
     roof["frac"] = roof["achieved"] / roof["peak"]
