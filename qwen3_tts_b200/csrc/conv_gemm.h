@@ -53,10 +53,18 @@ struct UnitOp {
   long long a_batch_stride = 0, snake_batch_stride = 0;
   int variant = 0;                    // compiled instance (unit_kernel.cu: 0 = C 96, 1 / 2 = C 192 with 4 / 3 weight stages, 3..5 = CTA-pair forms)
   int pair = 0;                       // 1: CTA-pair form (2-CTA clusters, 256-row tiles, tcgen05 cta_group::2)
+  // xin = 1: the activation operand is the raw residual stream x (= p.res, read from a DIFFERENT buffer than p.out_raw: tiles read each
+  // other's halo rows); the kernel applies the input Snake (snake1_*) to each slab in shared memory and stores one tensor per launch:
+  // y, or snake_next(y) when p.skip_raw is set.  Two HBM passes per unit instead of four.
+  int xin = 0;
+  const float* snake1_a = nullptr;
+  const float* snake1_ib = nullptr;
   int enabled = 0;
 };
 // Shape test only (no device work): true when unit_make can fuse C channels.
 bool unit_fusable(int C);
+// true when the fused unit for C channels has the raw-input (xin) form
+bool unit_xin_available(int C);
 // Fills the maps and ring sizes; returns 0 when the shape can be fused (enabled = 1), 1 when it cannot, < 0 on error.
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows);
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream);

@@ -170,22 +170,49 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   for (size_t i = 0; i < e->blocks.size(); ++i) {
     const BlockW& K = e->blocks[i];
     const int Lo = L > 0 ? (L - 1) * K.stride : 0;
+    // raw-input units (C = 96): the block's tensors travel as x only, every unit applies its input Snake in shared memory
+    bool xin = e->engine == ENGINE_TC && unit_xin_available(K.cout);
+    for (int j = 0; j < 3 && xin; ++j) xin = K.unit[j].conv7.taps == 7 && K.unit[j].conv1.taps == 1 && 128 + 6 * (-K.unit[j].conv7.tap_off[0] / 6) <= 256;
     {
       // transposed conv: accumulator row q -> output rows q*s .. q*s+s-1 (modeling :200-207)
       Op& op = b.gemm(K.tconv, R[ia], B, L, L - 1);
       op.g.p.out_batch_stride = (long long)Lo * K.cout;
       op.g.p.out_raw = R[iy];
-      op.g.p.out_snake = R[ifree];
-      op.g.p.snake_a = K.unit[0].act1.a; op.g.p.snake_ib = K.unit[0].act1.ib;
       const std::string t = "decoder." + std::to_string(i + 1) + ".block.1";
+      if (!xin) {
+        op.g.p.out_snake = R[ifree];
+        op.g.p.snake_a = K.unit[0].act1.a; op.g.p.snake_ib = K.unit[0].act1.ib;
+      }
       b.tag(op, t.c_str(), R[iy], false, K.cout, Lo);
-      std::swap(ia, ifree);
+      if (!xin) std::swap(ia, ifree);
     }
     L = Lo;
     for (int j = 0; j < 3; ++j) {
       const UnitW& U = K.unit[j];
       const SnakeP& nx = j < 2 ? K.unit[j + 1].act1 : (i + 1 < e->blocks.size() ? e->blocks[i + 1].act0 : e->tail_act);
       const std::string t = "decoder." + std::to_string(i + 1) + ".block." + std::to_string(j + 2);
+      if (xin) {
+        // x in R[iy] -> y in R[ifree] (never in place: tiles read their neighbours' halo rows); the last unit leaves snake_next(y) in R[ia]
+        UnitOp u;
+        memset(&u.p, 0, sizeof(u.p));
+        u.C = K.cout; u.dil = -U.conv7.tap_off[0] / 6; u.xin = 1;
+        u.bias7 = U.conv7.bias; u.snake2_a = U.act2.a; u.snake2_ib = U.act2.ib;
+        u.snake1_a = U.act1.a; u.snake1_ib = U.act1.ib;
+        { const char* d = getenv("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
+        u.p.bf16 = e->bf16 ? 1 : 0; u.p.bias = U.conv1.bias; u.p.res = R[iy]; u.p.out_raw = R[ifree];
+        if (j == 2) { u.p.out_snake = R[ia]; u.p.snake_a = nx.a; u.p.snake_ib = nx.ib; }
+        u.p.w_ptr = U.conv7.w;
+        int mk = 0;
+        if (!dry) mk = unit_make(&u, R[iy], U.conv7.w, U.conv1.w, B, L);
+        if (mk != 0) { b.rc = e->fail(Q3TTS_CUDA_ERROR, "raw-input fused unit could not be built"); continue; }
+        plan->ops.emplace_back();
+        Op& op = plan->ops.back();
+        op.type = OP_UNIT; op.u = u; op.B = B; op.L = L; op.C = K.cout;
+        op.drop_raw = j == 2;
+        b.tag(op, t.c_str(), R[ifree], false, K.cout, L);
+        std::swap(iy, ifree);
+        continue;
+      }
       {
         // fused unit: one launch, the Snake'd conv7 output stays in tensor memory (C <= 192); x is updated in place
         UnitOp u;
@@ -306,7 +333,7 @@ void prof_account(Engine* e, const Op& op) {
     const double rows = (double)op.B * op.L, C = op.C;
     dims[0] = op.B * op.L; dims[1] = op.C; dims[2] = op.C; dims[3] = 8;  // 7 taps + the 1x1 conv
     fl = 2.0 * rows * C * C * 8.0;
-    by = 2.0 * ((op.u.p.skip_raw ? 3.0 : 4.0) * rows * C + 8.0 * C * C);  // a1 + x in, y (unless dead) + snake(y) out, weights once
+    by = 2.0 * ((op.u.xin ? 2.0 : (op.u.p.skip_raw ? 3.0 : 4.0)) * rows * C + 8.0 * C * C);  // a1 + x in, y (unless dead) + snake(y) out, weights once; raw-input form: x in, one tensor out
   } else if (op.type == OP_RVQ) {
     // the 32 MiB of tables are L2-resident after warm-up, so the HBM floor is the codes in and the embeddings out
     by = (double)op.B * op.L * (e->cfg.num_quantizers * 8.0 + 2.0 * op.C);

@@ -39,6 +39,7 @@ static constexpr int kUSlotsPerWarp = kURes + 2 * kUOutBufs;  // residual ring +
 
 struct __align__(8) UnitBarriers {
   uint64_t sfull[kUMaxSlabs], sempty[kUMaxSlabs];
+  uint64_t sland[kUMaxSlabs];  // XIN: a raw slab has landed in THIS CTA (its phase-1 warps then apply the input Snake in place)
   uint64_t wfull[kUMaxStages], wempty[kUMaxStages];
   uint64_t acc1_full[2], a2_full[2], acc2_full[2], acc2_empty[2];
   uint64_t res_bar[kP2Warps][kURes];
@@ -54,6 +55,8 @@ struct UnitArgs {
   const float* bias7;
   const float* s2a;
   const float* s2ib;
+  const float* s1a;   // XIN: tables of the unit's input Snake (act1)
+  const float* s1ib;
   int C, dil, ms, srows, nbox, nslabs, nstages;
   int ks;    // K blocks per slab / weight stage
   int nbuf;  // TMEM stages (1 or 2)
@@ -92,9 +95,12 @@ __device__ __forceinline__ void tma_store_3d_s(const void* map, uint32_t smem_sr
 // the even CTA; each CTA keeps its own 128 rows (slab, tensor memory, phase-1/2 warps) and loads only HALF of every weight stage
 // (its C/2 output channels).  Weight re-streaming is what bounds the single-CTA form (C = 192: 590 KB of weights per 128-row tile
 // against ~43 B/clk of L2->SM fill), so halving it per SM is the point.
-template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0>
+// XIN_ = 1: the activation operand is the RAW residual stream x; the phase-1 warps apply the input Snake to each slab in shared
+// memory before its MMAs, and phase 2 stores ONE tensor (y, or snake_next(y) for the last unit of a block).  HBM traffic of a unit
+// drops from four passes (a1 + x in, y + snake(y) out) to two.
+template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0, int XIN_ = 0>
 struct UnitCfg {
-  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_;
+  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_, XIN = XIN_;
   static constexpr int NKB = C / KB, NKG = NKB / KS, KSTEPS = KB / 16;
   static constexpr int SPAN = KB * 2;
   static constexpr int M1_STAGES = NKG * 7, M2_STAGES = NKG, TILE_STAGES = M1_STAGES + M2_STAGES;
@@ -112,6 +118,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const GemmParams p, const UnitArgs u) {
   constexpr int C = Cfg::C, KB = Cfg::KB, KS = Cfg::KS, NST = Cfg::NST, NSL = Cfg::NSL, NBUF = Cfg::NBUF, NKG = Cfg::NKG, KSTEPS = Cfg::KSTEPS;
   constexpr bool PAIR = Cfg::PAIR != 0;
+  constexpr bool XIN = Cfg::XIN != 0;
+  static_assert(!XIN || (NBUF == 2 && NKG == 1), "XIN: one slab per tile, two phase-1 groups");
   const int rank = PAIR ? (int)cluster_ctarank() : 0;               // 0 = leader (issues the MMAs of both CTAs)
   const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;  // worker (CTA or CTA pair) index
   const int nworkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
@@ -128,7 +136,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* slabs = wst + (size_t)NST * stage_bytes;
   uint8_t* epi = slabs + (size_t)NSL * slab_bytes;
   float* prm = reinterpret_cast<float*>(epi + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot);  // [6][C]: b7, s2a, s2ib, b1, sna, snib
-  UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(prm + 6 * C);
+  UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(prm + 8 * C);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (p.rows_valid + TM - 1) / TM;
   const int total_tiles = p.batches * m_tiles;
@@ -138,7 +146,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW7); tma_prefetch_desc(&tmW1);
     tma_prefetch_desc(&tmRes); tma_prefetch_desc(&tmRaw); tma_prefetch_desc(&tmSnake);
-    for (int s = 0; s < NSL; ++s) { mbar_init(&bars->sfull[s], 1); mbar_init(&bars->sempty[s], 1); }
+    // XIN: sfull counts the phase-1 warps (of both CTAs) that transformed the slab; the TMA bytes are counted on each CTA's own sland
+    for (int s = 0; s < NSL; ++s) { mbar_init(&bars->sfull[s], XIN ? 4 * NCTA : 1); mbar_init(&bars->sempty[s], 1); mbar_init(&bars->sland[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps * NCTA);  // pair: both CTAs' warps arrive on the leader's copy
@@ -150,7 +159,9 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
     prm[i] = u.bias7[i]; prm[C + i] = u.s2a[i]; prm[2 * C + i] = u.s2ib[i];
-    prm[3 * C + i] = p.bias ? p.bias[i] : 0.f; prm[4 * C + i] = p.snake_a[i]; prm[5 * C + i] = p.snake_ib[i];
+    prm[3 * C + i] = p.bias ? p.bias[i] : 0.f;
+    prm[4 * C + i] = p.snake_a ? p.snake_a[i] : 0.f; prm[5 * C + i] = p.snake_ib ? p.snake_ib[i] : 0.f;
+    if (XIN) { prm[6 * C + i] = u.s1a[i]; prm[7 * C + i] = u.s1ib[i]; }
   }
   if (warp == 1) {
     if (PAIR) { tmem_alloc2(&bars->tmem_base, 512); tmem_relinquish2(); }
@@ -180,13 +191,15 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int tile = wid + j * nworkers;
         const int b = tile / m_tiles, mt = tile - b * m_tiles;
         for (int kg = 0; kg < NKG; ++kg) {
-          mbar_wait(&bars->sempty[ss], sph ^ 1);
-          if (rank == 0) mbar_expect_tx(&bars->sfull[ss], slab_bytes * NCTA);
-          for (int kk = 0; kk < KS; ++kk)
-            for (int bx = 0; bx < u.nbox; ++bx)
-              load(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
-                   (kg * KS + kk) * KB, mt * TM + rrow - halo + u.a_row0 + bx * boxrows, b);
-          if (++ss == NSL) { ss = 0; sph ^= 1; }
+          if (!XIN) {
+            mbar_wait(&bars->sempty[ss], sph ^ 1);
+            if (rank == 0) mbar_expect_tx(&bars->sfull[ss], slab_bytes * NCTA);
+            for (int kk = 0; kk < KS; ++kk)
+              for (int bx = 0; bx < u.nbox; ++bx)
+                load(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sfull[ss],
+                     (kg * KS + kk) * KB, mt * TM + rrow - halo + u.a_row0 + bx * boxrows, b);
+            if (++ss == NSL) { ss = 0; sph ^= 1; }
+          }
           for (int tap = 0; tap < 7; ++tap) {
             mbar_wait(&bars->wempty[ws], wph ^ 1);
             if (rank == 0) mbar_expect_tx(&bars->wfull[ws], stage_bytes * NCTA);
@@ -195,6 +208,19 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (++ws == NST) { ws = 0; wph ^= 1; }
           }
         }
+      };
+      // XIN: raw slabs run two tiles ahead of the weight ring (a slab has to land AND be transformed by the phase-1 warps before its
+      // tile's MMAs), so they are issued on their own, not in MMA order; each lands on this CTA's own barrier.
+      auto load_slab_x = [&](int j) {
+        const int tile = wid + j * nworkers;
+        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        mbar_wait(&bars->sempty[ss], sph ^ 1);
+        mbar_expect_tx(&bars->sland[ss], slab_bytes);
+        for (int kk = 0; kk < KS; ++kk)
+          for (int bx = 0; bx < u.nbox; ++bx)
+            tma_load_3d(slabs + (size_t)ss * slab_bytes + (size_t)kk * ssub + (size_t)bx * boxrows * span, &tmA, &bars->sland[ss],
+                        kk * KB, mt * TM + rrow - halo + u.a_row0 + bx * boxrows, b);
+        if (++ss == NSL) { ss = 0; sph ^= 1; }
       };
       auto load_m2 = [&]() {
         for (int kg = 0; kg < NKG; ++kg) {
@@ -205,8 +231,10 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (++ws == NST) { ws = 0; wph ^= 1; }
         }
       };
+      if (XIN) { if (my_tiles > 0) load_slab_x(0); if (my_tiles > 1) load_slab_x(1); }
       if (my_tiles > 0) load_m1(0);
       for (int j = 0; j < my_tiles; ++j) {
+        if (XIN && j + 2 < my_tiles) load_slab_x(j + 2);
         if (NBUF == 2 && j + 1 < my_tiles) load_m1(j + 1);
         load_m2();
         if (NBUF == 1 && j + 1 < my_tiles) load_m1(j + 1);
@@ -239,7 +267,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           int sl; uint32_t spar;
           if (NKG % NSL == 0) { sl = kg % NSL; spar = (uint32_t)(j * (NKG / NSL) + kg / NSL) & 1u; }
           else { constexpr int R = NSL / NKG; sl = (j % R) * NKG + kg; spar = (uint32_t)(j / R) & 1u; }
-          mbar_wait(&bars->sfull[sl], spar);
+          if (XIN && PAIR) mbar_wait_cluster(&bars->sfull[sl], spar); else mbar_wait(&bars->sfull[sl], spar);
           const uint32_t slab = s_lo0 + (uint32_t)sl * s_off;
           bool ready = false;  // result of the early poll of this tap's weight stage (issued before the previous tap's MMAs)
 #pragma unroll
@@ -321,7 +349,56 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const uint32_t dst = st + c_a2 + (tcol >> 1);
     const uint32_t prm_s = smem_u32(prm);
     const int sb = NBUF == 2 ? grp : 0;
+    // XIN: input Snake of tile j's raw slab, in place, by the four warps of the group that owns the tile.  SWIZZLE_64B slab rows:
+    // the 16-byte chunk at physical position pch of row r holds channels 8 * (pch ^ ((r >> 1) & 3)) .. + 7 of its K block, and a
+    // thread walks rows r0, r0 + 32, ... so its channels (and their Snake tables) are fixed.  Zero rows (TMA fill outside the item)
+    // stay zero: snake(0) = 0.
+    auto transform = [&](int j) {
+      static_assert(!XIN || KB == 32, "XIN transform is written for 64-byte slab rows");
+      const int sl = j % NSL;
+      if (quad == 2 && lane == 0) UTRACE(j, 12);
+      mbar_wait(&bars->sland[sl], (uint32_t)(j / NSL) & 1u);
+      if (quad == 2 && lane == 0) UTRACE(j, 10);
+      const int tid = ((warp - 2) & 3) * 32 + lane;
+      const int pch = tid & 3, r0 = tid >> 2;
+      const int lc = pch ^ ((r0 >> 1) & 3);
+      const uint32_t sbase = smem_u32(slabs) + (uint32_t)sl * slab_bytes + (uint32_t)pch * 16u;
+#pragma unroll
+      for (int kk = 0; kk < KS; ++kk) {
+        const uint32_t pa = prm_s + (uint32_t)(6 * C + kk * KB + lc * 8) * 4u;
+        const float4 a0 = lds_f4(pa), a1 = lds_f4(pa + 16u), h0 = lds_f4(pa + (uint32_t)C * 4u), h1 = lds_f4(pa + (uint32_t)C * 4u + 16u);
+        auto chunk = [&](uint4 v) {
+          const float2 x0 = Elem<T>::unpack2(v.x), x1 = Elem<T>::unpack2(v.y), x2 = Elem<T>::unpack2(v.z), x3 = Elem<T>::unpack2(v.w);
+          const float2 y0 = snake2(x0, make_float2(a0.x, a0.y), make_float2(h0.x, h0.y));
+          const float2 y1 = snake2(x1, make_float2(a0.z, a0.w), make_float2(h0.z, h0.w));
+          const float2 y2 = snake2(x2, make_float2(a1.x, a1.y), make_float2(h1.x, h1.y));
+          const float2 y3 = snake2(x3, make_float2(a1.z, a1.w), make_float2(h1.z, h1.w));
+          return make_uint4(Elem<T>::pack2(y0.x, y0.y), Elem<T>::pack2(y1.x, y1.y), Elem<T>::pack2(y2.x, y2.y), Elem<T>::pack2(y3.x, y3.y));
+        };
+        const uint32_t kbase = sbase + (uint32_t)kk * ssub;
+        int r = r0;
+        for (; r + 96 < u.srows; r += 128) {  // four rows per pass: independent chains hide the ld.shared / MUFU latencies
+          const uint32_t ad = kbase + (uint32_t)r * 64u;
+          const uint4 v0 = lds_u4(ad), v1 = lds_u4(ad + 2048u), v2 = lds_u4(ad + 4096u), v3 = lds_u4(ad + 6144u);
+          const uint4 w0 = chunk(v0), w1 = chunk(v1), w2 = chunk(v2), w3 = chunk(v3);
+          sts_u4(ad, w0.x, w0.y, w0.z, w0.w); sts_u4(ad + 2048u, w1.x, w1.y, w1.z, w1.w);
+          sts_u4(ad + 4096u, w2.x, w2.y, w2.z, w2.w); sts_u4(ad + 6144u, w3.x, w3.y, w3.z, w3.w);
+        }
+        for (; r < u.srows; r += 32) {
+          const uint32_t ad = kbase + (uint32_t)r * 64u;
+          const uint4 w = chunk(lds_u4(ad));
+          sts_u4(ad, w.x, w.y, w.z, w.w);
+        }
+      }
+      fence_proxy_async_smem();  // the tensor core reads the slab through the asynchronous proxy
+      __syncwarp();
+      if (lane == 0) { if (PAIR) mbar_arrive_leader(&bars->sfull[sl]); else mbar_arrive(&bars->sfull[sl]); }
+      if (quad == 2 && lane == 0) UTRACE(j, 11);
+    };
+    if (XIN && grp < my_tiles) transform(grp);
     for (int j = NBUF == 2 ? grp : 0; j < my_tiles; j += NBUF) {
+      // the group's NEXT tile first: its slab lands while this tile's conv7 MMAs run, which is when these warps are idle
+      if (XIN && j + NBUF < my_tiles) transform(j + NBUF);
       mbar_wait(&bars->acc1_full[sb], (uint32_t)(j / NBUF) & 1);
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 6);
@@ -372,6 +449,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     const int sb = NBUF == 2 ? grp : 0;
     const int j0 = NBUF == 2 ? grp : 0;
     const bool wr_raw = p.skip_raw == 0;  // the last unit of a block stores only snake_next(y)
+    const bool wr_snk = XIN ? p.skip_raw != 0 : true;  // XIN: exactly one tensor leaves (the next unit applies its own input Snake)
     uint32_t off[4];
 #pragma unroll
     for (int c = 0; c < 4; ++c) off[c] = (uint32_t)(lane * 64 + ((c ^ ((lane >> 1) & 3)) << 4));
@@ -428,10 +506,12 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const float2 y23 = add2(add2(make_float2(__uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])), make_float2(bb.z, bb.w)), x1);
             oraw[4 * c + 2 * q] = Elem<T>::pack2(y01.x, y01.y);
             oraw[4 * c + 2 * q + 1] = Elem<T>::pack2(y23.x, y23.y);
-            const float2 s01 = snake2(y01, make_float2(a.x, a.y), make_float2(ib.x, ib.y));
-            const float2 s23 = snake2(y23, make_float2(a.z, a.w), make_float2(ib.z, ib.w));
-            osnk[4 * c + 2 * q] = Elem<T>::pack2(s01.x, s01.y);
-            osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(s23.x, s23.y);
+            if (wr_snk) {
+              const float2 s01 = snake2(y01, make_float2(a.x, a.y), make_float2(ib.x, ib.y));
+              const float2 s23 = snake2(y23, make_float2(a.z, a.w), make_float2(ib.z, ib.w));
+              osnk[4 * c + 2 * q] = Elem<T>::pack2(s01.x, s01.y);
+              osnk[4 * c + 2 * q + 1] = Elem<T>::pack2(s23.x, s23.y);
+            }
           }
         }
         const bool do_store = !(p.dbg & 64);  // debug: phase 2 without its output stores
@@ -442,14 +522,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           if (wr_raw) sts_u4(raw_s + off[c], oraw[4 * c], oraw[4 * c + 1], oraw[4 * c + 2], oraw[4 * c + 3]);
-          sts_u4(snk_s + off[c], osnk[4 * c], osnk[4 * c + 1], osnk[4 * c + 2], osnk[4 * c + 3]);
+          if (wr_snk) sts_u4(snk_s + off[c], osnk[4 * c], osnk[4 * c + 1], osnk[4 * c + 2], osnk[4 * c + 3]);
         }
         if (do_store) {
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
             if (wr_raw) tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
-            tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
+            if (wr_snk) tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
             tma_store_commit();
           }
         }
@@ -482,11 +562,22 @@ using Cfg192b = UnitCfg<192, 64, 1, 3, 3, 1>;    // 3 stages for the dilation-9 
 using Cfg96p = UnitCfg<96, 32, 3, 8, 2, 2, 1>;
 using Cfg192pa = UnitCfg<192, 64, 1, 6, 3, 1, 1>;
 using Cfg192pb = UnitCfg<192, 64, 1, 4, 3, 1, 1>;
+// raw-input form (variant 6): CTA pairs, three slabs in flight (a slab must land AND be transformed before its tile's MMAs), 4 weight stages
+using Cfg96x = UnitCfg<96, 32, 3, 4, 3, 2, 1, 1>;
 
 static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
   return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * (op.pair ? op.C / 2 : op.C) * span + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot +
-         (size_t)6 * op.C * sizeof(float) + sizeof(UnitBarriers) + 1024;
+         (size_t)8 * op.C * sizeof(float) + sizeof(UnitBarriers) + 1024;
+}
+
+// Opt-in experiment (Q3TTS_XIN=1), off by default: measured SLOWER than the two-tensor form on B200 (C = 96 units 8.9 -> 10.4-11.4 ms
+// per 64 x 10 s step, transposed conv 192 -> 96 2.8 -> 2.1 ms).  The unit is bound by its phase-2 warps, not by HBM, and
+// the in-kernel Snake adds CUDA-core work to the same schedulers.  The streaming plans keep the two-tensor form, so streaming output is
+// not bit-identical to bulk output while the switch is on.
+bool unit_xin_available(int C) {
+  static const bool on = getenv("Q3TTS_XIN") != nullptr && getenv("Q3TTS_XIN")[0] == '1';
+  return on && C == 96 && !getenv("Q3TTS_NO_FUSE") && !getenv("Q3TTS_NO_PAIR");
 }
 
 bool unit_fusable(int C) {
@@ -507,14 +598,18 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   p.n_total = C; p.bn = C; p.ncol_mod = C; p.act = ACT_NONE; p.res_f32 = 0; p.out_f32 = nullptr; p.scale = nullptr;
   p.out_row_stride = C; p.out_batch_stride = (long long)rows * C;
   p.a_ptr = a1;
-  if (!p.res || !p.out_raw || !p.out_snake || !p.snake_a || !p.snake_ib) return 1;
+  if (op->xin) {
+    if (!unit_xin_available(C) || !p.res || p.res != a1 || !p.out_raw || p.out_raw == p.res || !op->snake1_a || !op->snake1_ib) return 1;
+    if (p.out_snake && (!p.snake_a || !p.snake_ib)) return 1;
+  } else if (!p.res || !p.out_raw || !p.out_snake || !p.snake_a || !p.snake_ib) return 1;
   const int span = p.kb * 2;
   const int need = U_BM + 6 * op->dil;
   op->srows = (need + 7) / 8 * 8;
   op->nbox = 1;
   if (op->srows > 256) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
   op->pair = getenv("Q3TTS_NO_PAIR") ? 0 : 1;
-  if (C == 96) { op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0; }
+  if (op->xin) { op->pair = 1; op->ks = Cfg96x::KS; op->nstages = Cfg96x::NST; op->nslabs = Cfg96x::NSL; op->nbuf = Cfg96x::NBUF; op->variant = 6; }
+  else if (C == 96) { op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0; }
   else if (op->pair) {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = Cfg192pa::NST; op->variant = 4;
@@ -539,8 +634,10 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   const uint64_t rs = (uint64_t)p.out_row_stride, bs = (uint64_t)p.out_batch_stride;
   rc |= make_tmap_3d_strided(&op->tmRes, p.res, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
   rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs, bs, 32, 32);
-  rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs,
-                             op->snake_batch_stride ? (uint64_t)op->snake_batch_stride : bs, 32, 32);
+  if (p.out_snake)
+    rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs,
+                               op->snake_batch_stride ? (uint64_t)op->snake_batch_stride : bs, 32, 32);
+  else op->tmSnake = op->tmRaw;  // xin, not the last unit of its block: never stored through
   if (rc) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: tensor map failed (C %d dil %d srows %d)\n", C, op->dil, op->srows); return -1; }
   static bool attr_done = false;
   if (!attr_done) {
@@ -553,6 +650,7 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     set((const void*)unit_kernel<__half, Cfg96p>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96p>);
     set((const void*)unit_kernel<__half, Cfg192pa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pa>);
     set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
+    set((const void*)unit_kernel<__half, Cfg96x>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96x>);
     if (e != cudaSuccess) return -2;
     attr_done = true;
   }
@@ -587,7 +685,7 @@ cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
   int grid;
   if (op.pair) { const int pairs = gemm_num_sms() / 2; grid = 2 * (tiles < pairs ? tiles : pairs); }
   else grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
-  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf, op.a_row0};
+  UnitArgs u{op.bias7, op.snake2_a, op.snake2_ib, op.snake1_a, op.snake1_ib, op.C, op.dil, op.ms, op.srows, op.nbox, op.nslabs, op.nstages, op.ks, op.nbuf, op.a_row0};
   const size_t smem = unit_smem_bytes(op);
   switch (op.variant) {
     case 0: return launch_cfg<Cfg96>(op, u, grid, smem, stream);
@@ -595,6 +693,7 @@ cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
     case 2: return launch_cfg<Cfg192b>(op, u, grid, smem, stream);
     case 3: return launch_cfg<Cfg96p>(op, u, grid, smem, stream);
     case 4: return launch_cfg<Cfg192pa>(op, u, grid, smem, stream);
+    case 6: return launch_cfg<Cfg96x>(op, u, grid, smem, stream);
     default: return launch_cfg<Cfg192pb>(op, u, grid, smem, stream);
   }
 }
