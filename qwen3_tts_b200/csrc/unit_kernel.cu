@@ -42,7 +42,7 @@ struct __align__(8) UnitBarriers {
   uint64_t sland[kUMaxSlabs];  // XIN: a raw slab has landed in THIS CTA (its phase-1 warps then apply the input Snake in place)
   uint64_t wfull[kUMaxStages], wempty[kUMaxStages];
   uint64_t acc1_full[2], a2_full[2], acc2_full[2], acc2_empty[2];
-  uint64_t res_bar[kP2Warps][kURes];
+  uint64_t res_bar[12][kURes];  // up to 12 phase-2 warps (P2X form)
   uint32_t tmem_base;
   uint32_t pad;
 };
@@ -98,9 +98,16 @@ __device__ __forceinline__ void tma_store_3d_s(const void* map, uint32_t smem_sr
 // XIN_ = 1: the activation operand is the RAW residual stream x; the phase-1 warps apply the input Snake to each slab in shared
 // memory before its MMAs, and phase 2 stores ONE tensor (y, or snake_next(y) for the last unit of a block).  HBM traffic of a unit
 // drops from four passes (a1 + x in, y + snake(y) out) to two.
-template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0, int XIN_ = 0>
+// P2X_ = 1 (two TMEM stages only): 4 phase-1 warps serve every tile and 12 phase-2 warps own ONE 32-column item each (3 per TMEM lane
+// quadrant), so a tile's phase 2 is one item deep instead of three.  The timeline shows the unit waits on the
+// serial per-item chain of its phase-2 warps while the phase-1 warps idle 75 % of a tile period.
+template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0, int XIN_ = 0, int P2X_ = 0>
 struct UnitCfg {
-  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_, XIN = XIN_;
+  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_, XIN = XIN_, P2X = P2X_;
+  static constexpr int P1W = P2X ? 4 : kP1Warps, P2W = P2X ? 12 : kP2Warps;  // same thread count either way
+  static constexpr int URES = P2X ? 1 : kURes;                               // residual ring depth per phase-2 warp
+  static constexpr int USLOTS = URES + 2 * kUOutBufs;
+  static_assert(!P2X || (NBUF == 2 && C == 96 && !XIN), "P2X: C = 96 with two TMEM stages");
   static constexpr int NKB = C / KB, NKG = NKB / KS, KSTEPS = KB / 16;
   static constexpr int SPAN = KB * 2;
   static constexpr int M1_STAGES = NKG * 7, M2_STAGES = NKG, TILE_STAGES = M1_STAGES + M2_STAGES;
@@ -119,6 +126,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr int C = Cfg::C, KB = Cfg::KB, KS = Cfg::KS, NST = Cfg::NST, NSL = Cfg::NSL, NBUF = Cfg::NBUF, NKG = Cfg::NKG, KSTEPS = Cfg::KSTEPS;
   constexpr bool PAIR = Cfg::PAIR != 0;
   constexpr bool XIN = Cfg::XIN != 0;
+  constexpr bool P2X = Cfg::P2X != 0;
+  constexpr int P1W = Cfg::P1W, P2W = Cfg::P2W, URES = Cfg::URES, USLOTS = Cfg::USLOTS;
   static_assert(!XIN || (NBUF == 2 && NKG == 1), "XIN: one slab per tile, two phase-1 groups");
   const int rank = PAIR ? (int)cluster_ctarank() : 0;               // 0 = leader (issues the MMAs of both CTAs)
   const int wid = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;  // worker (CTA or CTA pair) index
@@ -135,7 +144,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* wst = smem;                                   // weight ring first: its slot addresses are compile-time offsets
   uint8_t* slabs = wst + (size_t)NST * stage_bytes;
   uint8_t* epi = slabs + (size_t)NSL * slab_bytes;
-  float* prm = reinterpret_cast<float*>(epi + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot);  // [6][C]: b7, s2a, s2ib, b1, sna, snib
+  float* prm = reinterpret_cast<float*>(epi + (size_t)P2W * USLOTS * kEpiSlot);  // [6][C]: b7, s2a, s2ib, b1, sna, snib
   UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(prm + 8 * C);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (p.rows_valid + TM - 1) / TM;
@@ -151,10 +160,10 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     for (int s = 0; s < NST; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps * NCTA);  // pair: both CTAs' warps arrive on the leader's copy
-      mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], grp_warps * NCTA);
+      mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], (P2X ? P2W : grp_warps) * NCTA);
     }
-    for (int w = 0; w < kP2Warps; ++w)
-      for (int s = 0; s < kURes; ++s) mbar_init(&bars->res_bar[w][s], 1);
+    for (int w = 0; w < P2W; ++w)
+      for (int s = 0; s < URES; ++s) mbar_init(&bars->res_bar[w][s], 1);
     fence_barrier_init();
   }
   for (int i = threadIdx.x; i < C; i += blockDim.x) {
@@ -337,18 +346,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
     }
-  } else if (warp < 2 + kP1Warps) {
+  } else if (warp < 2 + P1W) {
     // ------------------------------------------------------------------ phase-1 warps: acc1 -> + b7 -> SnakeBeta -> 16-bit pairs -> A2 (TMEM)
     const int quad = warp & 3, grp = (warp - 2) >> 2;
     constexpr int ncols = NBUF == 2 ? C : C / 2;  // columns this warp serves (a multiple of 32)
     const uint32_t tcol = NBUF == 2 ? 0u : (uint32_t)(grp * ncols);  // one TMEM stage: the two warp groups split the columns
     const int pcol0 = NBUF == 2 ? 0 : grp * ncols;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
-    const uint32_t st = tmem_base + lane_base + (NBUF == 2 ? (uint32_t)(grp * 256) : 0u);
-    const uint32_t src = st + c_acc1 + tcol;
-    const uint32_t dst = st + c_a2 + (tcol >> 1);
     const uint32_t prm_s = smem_u32(prm);
-    const int sb = NBUF == 2 ? grp : 0;
     // XIN: input Snake of tile j's raw slab, in place, by the four warps of the group that owns the tile.  SWIZZLE_64B slab rows:
     // the 16-byte chunk at physical position pch of row r holds channels 8 * (pch ^ ((r >> 1) & 3)) .. + 7 of its K block, and a
     // thread walks rows r0, r0 + 32, ... so its channels (and their Snake tables) are fixed.  Zero rows (TMA fill outside the item)
@@ -396,7 +401,11 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (quad == 2 && lane == 0) UTRACE(j, 11);
     };
     if (XIN && grp < my_tiles) transform(grp);
-    for (int j = NBUF == 2 ? grp : 0; j < my_tiles; j += NBUF) {
+    for (int j = (NBUF == 2 && !P2X) ? grp : 0; j < my_tiles; j += (P2X ? 1 : NBUF)) {
+      const int sb = NBUF == 2 ? (P2X ? (j & 1) : grp) : 0;  // TMEM stage of this tile
+      const uint32_t st = tmem_base + lane_base + (uint32_t)(sb * 256);
+      const uint32_t src = st + c_acc1 + tcol;
+      const uint32_t dst = st + c_a2 + (tcol >> 1);
       // the group's NEXT tile first: its slab lands while this tile's conv7 MMAs run, which is when these warps are idle
       if (XIN && j + NBUF < my_tiles) transform(j + NBUF);
       mbar_wait(&bars->acc1_full[sb], (uint32_t)(j / NBUF) & 1);
@@ -434,20 +443,20 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else {
     // ------------------------------------------------------------------ phase-2 warps: acc2 + b1 + x -> y, snake_next(y) (TMA in / out)
-    const int pw = warp - 2 - kP1Warps;
-    const int quad = warp & 3, grp = pw >> 2;
+    const int pw = warp - 2 - P1W;
+    const int quad = warp & 3, grp = pw >> 2;  // P2X: grp = the item (32 columns) this warp owns in every tile
     constexpr int ncols = NBUF == 2 ? C : C / 2;
-    constexpr int nitems = ncols >> 5;
+    constexpr int nitems = P2X ? 1 : ncols >> 5;
+    const int item0 = P2X ? grp : 0;
     const uint32_t tcol = NBUF == 2 ? 0u : (uint32_t)(grp * ncols);
     const int pcol0 = NBUF == 2 ? 0 : grp * ncols;
     const int rsub = rrow + quad * 32;  // row offset of this warp inside a tile
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
-    const uint32_t acc = tmem_base + lane_base + (NBUF == 2 ? (uint32_t)(grp * 256) : 0u) + c_acc2 + tcol;
     const uint32_t prm_s = smem_u32(prm);
-    const uint32_t eb = smem_u32(epi) + (uint32_t)pw * kUSlotsPerWarp * kEpiSlot;  // [kURes residual][raw][snake] slots of 2 KB
+    const uint32_t eb = smem_u32(epi) + (uint32_t)pw * USLOTS * kEpiSlot;  // [URES residual][raw][snake] slots of 2 KB
     const uint32_t rbar = smem_u32(&bars->res_bar[pw][0]);
-    const int sb = NBUF == 2 ? grp : 0;
-    const int j0 = NBUF == 2 ? grp : 0;
+    const int j0 = (NBUF == 2 && !P2X) ? grp : 0;
+    constexpr int jstep = P2X ? 1 : NBUF;
     const bool wr_raw = p.skip_raw == 0;  // the last unit of a block stores only snake_next(y)
     const bool wr_snk = XIN ? p.skip_raw != 0 : true;  // XIN: exactly one tensor leaves (the next unit applies its own input Snake)
     uint32_t off[4];
@@ -461,16 +470,18 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (lane == 0) {
         const int tile = wid + pf_j * nworkers;
         const int b = tile / m_tiles, mt = tile - b * m_tiles;
-        const uint32_t slot = issued & (kURes - 1);
+        const uint32_t slot = issued & (URES - 1);
         const uint32_t bar = rbar + slot * 8u;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)kEpiSlot) : "memory");
-        tma_load_3d_s(eb + slot * kEpiSlot, &tmRes, bar, pcol0 + 32 * pf_item, mt * TM + rsub, b);
+        tma_load_3d_s(eb + slot * kEpiSlot, &tmRes, bar, pcol0 + 32 * (item0 + pf_item), mt * TM + rsub, b);
       }
       ++issued;
-      if (++pf_item == nitems) { pf_item = 0; pf_j += NBUF; }
+      if (++pf_item == nitems) { pf_item = 0; pf_j += jstep; }
     };
-    for (int i = 0; i < kURes; ++i) prefetch();
-    for (int j = j0; j < my_tiles; j += NBUF) {
+    for (int i = 0; i < URES; ++i) prefetch();
+    for (int j = j0; j < my_tiles; j += jstep) {
+      const int sb = NBUF == 2 ? (P2X ? (j & 1) : grp) : 0;
+      const uint32_t acc = tmem_base + lane_base + (uint32_t)(sb * 256) + c_acc2 + tcol + (uint32_t)(32 * item0);
       const int tile = wid + j * nworkers;
       const int b = tile / m_tiles, mt = tile - b * m_tiles;
       const int row0 = mt * TM + rsub;
@@ -478,14 +489,14 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 8);
       for (int item = 0; item < nitems; ++item) {
-        const uint32_t slot = cons & (kURes - 1);
-        if (!(p.dbg & 128)) mbar_wait(&bars->res_bar[pw][slot], (cons / kURes) & 1);  // debug bit 7: phase 2 without residual loads
+        const uint32_t slot = cons & (URES - 1);
+        if (!(p.dbg & 128)) mbar_wait(&bars->res_bar[pw][slot], (cons / URES) & 1);  // debug bit 7: phase 2 without residual loads
         const uint32_t rs = eb + slot * kEpiSlot;
         uint4 res[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) res[c] = lds_u4(rs + off[c]);
         ++cons;
-        const uint32_t raw_s = eb + (kURes + 2 * (ob & (kUOutBufs - 1))) * kEpiSlot, snk_s = raw_s + kEpiSlot;
+        const uint32_t raw_s = eb + (URES + 2 * (ob & (kUOutBufs - 1))) * kEpiSlot, snk_s = raw_s + kEpiSlot;
         // asynchronous TMEM loads and their wait stay adjacent: nothing may touch the destination registers in between
         uint32_t ra[16], rb[16];
         __syncwarp();  // .sync.aligned: reconverge after the lane-0 branch in prefetch()
@@ -499,7 +510,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           const uint32_t rw[4] = {res[c].x, res[c].y, res[c].z, res[c].w};
 #pragma unroll
           for (int q = 0; q < 2; ++q) {
-            const uint32_t pa = prm_s + (uint32_t)(3 * C + pcol0 + 32 * item + 8 * c + 4 * q) * 4u;
+            const uint32_t pa = prm_s + (uint32_t)(3 * C + pcol0 + 32 * (item0 + item) + 8 * c + 4 * q) * 4u;
             const float4 bb = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
             const float2 x0 = Elem<T>::unpack2(rw[2 * q]), x1 = Elem<T>::unpack2(rw[2 * q + 1]);
             const float2 y01 = add2(add2(make_float2(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1])), make_float2(bb.x, bb.y)), x0);
@@ -528,8 +539,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            if (wr_raw) tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * item, row0, b);
-            if (wr_snk) tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * item, row0, b);
+            if (wr_raw) tma_store_3d_s(&tmRaw, raw_s, pcol0 + 32 * (item0 + item), row0, b);
+            if (wr_snk) tma_store_3d_s(&tmSnake, snk_s, pcol0 + 32 * (item0 + item), row0, b);
             tma_store_commit();
           }
         }
@@ -564,10 +575,12 @@ using Cfg192pa = UnitCfg<192, 64, 1, 6, 3, 1, 1>;
 using Cfg192pb = UnitCfg<192, 64, 1, 4, 3, 1, 1>;
 // raw-input form (variant 6): CTA pairs, three slabs in flight (a slab must land AND be transformed before its tile's MMAs), 4 weight stages
 using Cfg96x = UnitCfg<96, 32, 3, 4, 3, 2, 1, 1>;
+// phase 2 by item (variant 7): CTA pairs, 4 phase-1 + 12 phase-2 warps
+using Cfg96q = UnitCfg<96, 32, 3, 8, 2, 2, 1, 0, 1>;
 
 static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
-  return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * (op.pair ? op.C / 2 : op.C) * span + (size_t)kP2Warps * kUSlotsPerWarp * kEpiSlot +
+  return (size_t)op.nslabs * op.ks * op.srows * span + (size_t)op.nstages * op.ks * (op.pair ? op.C / 2 : op.C) * span + (size_t)(op.variant == 7 ? Cfg96q::P2W * Cfg96q::USLOTS : kP2Warps * kUSlotsPerWarp) * kEpiSlot +
          (size_t)8 * op.C * sizeof(float) + sizeof(UnitBarriers) + 1024;
 }
 
@@ -609,7 +622,10 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   if (op->srows > 256) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
   op->pair = getenv("Q3TTS_NO_PAIR") ? 0 : 1;
   if (op->xin) { op->pair = 1; op->ks = Cfg96x::KS; op->nstages = Cfg96x::NST; op->nslabs = Cfg96x::NSL; op->nbuf = Cfg96x::NBUF; op->variant = 6; }
-  else if (C == 96) { op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0; }
+  else if (C == 96) {
+    op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0;
+    if (op->pair && !getenv("Q3TTS_NO_P2X")) op->variant = 7;
+  }
   else if (op->pair) {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = Cfg192pa::NST; op->variant = 4;
@@ -651,6 +667,7 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     set((const void*)unit_kernel<__half, Cfg192pa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pa>);
     set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
     set((const void*)unit_kernel<__half, Cfg96x>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96x>);
+    set((const void*)unit_kernel<__half, Cfg96q>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96q>);
     if (e != cudaSuccess) return -2;
     attr_done = true;
   }
@@ -694,6 +711,7 @@ cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
     case 3: return launch_cfg<Cfg96p>(op, u, grid, smem, stream);
     case 4: return launch_cfg<Cfg192pa>(op, u, grid, smem, stream);
     case 6: return launch_cfg<Cfg96x>(op, u, grid, smem, stream);
+    case 7: return launch_cfg<Cfg96q>(op, u, grid, smem, stream);
     default: return launch_cfg<Cfg192pb>(op, u, grid, smem, stream);
   }
 }

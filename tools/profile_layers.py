@@ -19,9 +19,14 @@ dec = model.decoder
 codes = make_codes(B, T, cfg, seed=1).cuda().transpose(1, 2).contiguous()
 for _ in range(3):
     dec(codes)
+reps = int(os.environ.get("PROFILE_REPS", "1"))  # average over several profiled forwards (same-box A/B: cuts the run-to-run noise)
 dec.set_profile(True)
-dec(codes)
-prof = dec.get_profile()
+acc = None
+for _ in range(reps):
+    dec(codes)
+    pr = dec.get_profile()
+    acc = [list(x) for x in pr] if acc is None else [[a[0], a[1] + b[1], a[2], a[3], a[4]] for a, b in zip(acc, pr)]
+prof = [(a[0], a[1] / reps, a[2], a[3], a[4]) for a in acc]
 dec.set_profile(False)
 names = {0: "rvq", 1: "gemm", 2: "rmsnorm", 3: "attn", 4: "dwln", 5: "tail", 6: "unit"}
 tot = sum(p[1] for p in prof)
