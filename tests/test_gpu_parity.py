@@ -195,6 +195,28 @@ def test_full_size_batch_properties(gpu_model, sd, cfg):
         assert mx <= MAX_ABS and snr >= MIN_SNR
 
 
+@pytest.mark.parametrize("T", [1, 2, 17, 73, 130])
+def test_edge_lengths_match_oracle(gpu_model, sd, cfg, T):
+    """Shortest inputs and the attention corner cases against the CPU oracle: a single frame (every conv sees only its causal
+    padding; the transposed convs emit (L-1)*s rows), T = 73 (first query whose window of 72 drops key 0), T = 130 (queries in
+    three 64-query tiles, keys staged across tile boundaries), batch 2 with a zero-padded second item (length rule, modeling :1012-1015)."""
+    from qwen3_tts_b200.synthetic import make_codes
+    codes = make_codes(2, T, cfg, seed=100 + T)
+    if T > 2:
+        codes[1, T - T // 3:] = 0                                           # padded tail: decoded like any other codes, then cut by the length rule
+    got = gpu_model.decode(codes.cuda(), return_dict=True).audio_values
+    with torch.inference_mode():
+        ref = O.model_decode(sd, cfg, codes)
+    assert len(got) == len(ref) == 2
+    for b in range(2):
+        assert got[b].shape == ref[b].shape, (T, b, got[b].shape, ref[b].shape)
+        if ref[b].numel() == 0:
+            continue
+        mx, snr = _stats(ref[b], got[b])
+        print(f"T={T} item {b}: n={ref[b].numel()} max-abs {mx:.3e} snr {snr:.1f} dB")
+        assert mx <= MAX_ABS and snr >= MIN_SNR, (T, b, mx, snr)
+
+
 def test_long_form_and_sharded_shapes(gpu_model, cfg):
     """BASELINE config 4 (32 x 60 s: chunks 300 / 25+300 / 25+150) and the config 5 utterance shape (T = 375: 300 / 25+75),
     through size-independent properties: sample counts, batch independence across chunk boundaries, and the
