@@ -596,9 +596,13 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   {
     GemmParams& q = op->p;
     const char* ew = getenv("Q3TTS_EPI_WARPS");
-    q.epi_warps = ew ? atoi(ew) : 8;
-    if (q.epi_warps != 4 && q.epi_warps != 8) q.epi_warps = 8;
-    q.res_depth = q.res ? 4 : 0;
+    // 12 epilogue warps (three per TMEM lane quadrant) for short-K layers whose Snake epilogue outweighs their MMAs (the transposed conv
+    // 192 -> 96: 2.96 -> 2.56 ms; measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers)
+    q.epi_warps = ew ? atoi(ew) : (q.ntaps * q.cin <= 512 && q.out_snake ? 12 : 8);
+    if (q.epi_warps != 4 && q.epi_warps != 8 && q.epi_warps != 12) q.epi_warps = 8;
+    if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || q.res_f32 || q.pack_mode)) q.epi_warps = 8;  // 12 warps: 16-bit vocoder epilogues only
+    q.res_depth = q.res ? (q.epi_warps == 12 ? 2 : 4) : 0;
+    if (q.epi_warps == 12 && q.res && gemm_stage_count(q) < 3) { q.epi_warps = 8; q.res_depth = 4; }  // the extra slots would starve the operand pipeline
     // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
     if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
   }

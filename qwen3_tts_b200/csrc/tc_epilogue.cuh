@@ -14,7 +14,7 @@
 namespace q3 {
 
 static constexpr int kEpiSlot = 2048;  // 32 rows x 64 bytes
-static constexpr int kMaxEpiWarps = 8;
+static constexpr int kMaxEpiWarps = 12;
 static constexpr int kMaxResDepth = 8;
 
 __host__ __device__ inline int epi_res_depth(const GemmParams& p) { return p.res ? (p.res_depth > 0 ? p.res_depth : 4) : 0; }
@@ -85,7 +85,9 @@ struct EpiWarp {
   }
 
   // first item this warp owns in tile iteration `it` (the two warps of a quadrant alternate so odd item counts balance)
-  __device__ __forceinline__ int first_item(int it) const { return (half - it) & (nsplit - 1); }  // nsplit is 1 or 2
+  __device__ __forceinline__ int first_item(int it) const {  // nsplit is 1, 2 or 3
+    return nsplit == 3 ? (half + 2 * (it % 3)) % 3 : (half - it) & (nsplit - 1);
+  }
 
   __device__ __forceinline__ void prefetch_one() {  // warp-uniform control flow; lane 0 issues
     if (pf_done) return;
