@@ -596,8 +596,9 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   {
     GemmParams& q = op->p;
     const char* ew = getenv("Q3TTS_EPI_WARPS");
-    // 12 epilogue warps (three per TMEM lane quadrant) for short-K layers whose Snake epilogue outweighs their MMAs (the transposed conv
-    // 192 -> 96: 2.96 -> 2.56 ms; measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers)
+    // 12 epilogue warps (three per TMEM lane quadrant) for short-K layers whose Snake epilogue outweighs their MMAs: the transposed conv
+    // 192 -> 96 2.96 -> 2.56 ms, the 1x1 convs of the C = 384 units 3.63 -> 2.85 ms (with one output slot per tensor and warp, see
+    // epi_out_bufs); measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers.
     q.epi_warps = ew ? atoi(ew) : (q.ntaps * q.cin <= 512 && q.out_snake ? 12 : 8);
     if (q.epi_warps != 4 && q.epi_warps != 8 && q.epi_warps != 12) q.epi_warps = 8;
     if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || q.res_f32 || q.pack_mode)) q.epi_warps = 8;  // 12 warps: 16-bit vocoder epilogues only

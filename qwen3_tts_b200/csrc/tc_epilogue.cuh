@@ -18,13 +18,16 @@ static constexpr int kMaxEpiWarps = 12;
 static constexpr int kMaxResDepth = 8;
 
 __host__ __device__ inline int epi_res_depth(const GemmParams& p) { return p.res ? (p.res_depth > 0 ? p.res_depth : 4) : 0; }
+// output slots per 16-bit output tensor and warp: 2 (the stores of item i drain while item i+1 is computed); 1 with 12 epilogue warps
+// and a residual ring, so that the slots of 12 warps still leave room for three operand stages
+__host__ __device__ inline int epi_out_bufs(const GemmParams& p) { return (p.epi_warps == 12 && p.res && p.act != ACT_GLU) ? 1 : 2; }
 // slots per warp for a given epilogue configuration
 __host__ __device__ inline int epi_slots_per_warp(const GemmParams& p) {
   if (p.act == ACT_TAIL) return 0;
   int n = epi_res_depth(p);
   if (p.act == ACT_GLU) return n + 2;
-  if (p.out_raw) n += 2;
-  if (p.out_snake) n += 2;
+  if (p.out_raw) n += epi_out_bufs(p);
+  if (p.out_snake) n += epi_out_bufs(p);
   if (p.out_f32) n += 4;
   return n;
 }
@@ -55,6 +58,7 @@ struct EpiWarp {
   int units, item_units, nitems, rd, rd_shift;
   bool wraps;  // a tile's columns can wrap around ncol_mod (transposed convs: n_total = stride * cout)
   int s_raw, s_snake, s_f32;  // first slot of each output ring
+  int obufs = 2;              // slots per 16-bit output ring (item_pair)
   uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
   int pf_it = 0, pf_item = 0;  // residual prefetch cursor (tile iteration, item)
   bool pf_done = false;
@@ -78,9 +82,10 @@ struct EpiWarp {
     wraps = p.ncol_mod != p.n_total;
     int nslot = rd;
     s_raw = nslot;
-    if (glu || p.out_raw) nslot += 2;
+    obufs = epi_out_bufs(p);
+    if (glu || p.out_raw) nslot += glu ? 2 : obufs;
     s_snake = nslot;
-    if (!glu && p.out_snake) nslot += 2;
+    if (!glu && p.out_snake) nslot += obufs;
     s_f32 = nslot;
   }
 
@@ -202,10 +207,10 @@ struct EpiWarp {
     for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(ra[i]); vb[i] = __uint_as_float(rb[i]); }
     math_unit(va, rsa, c0);
     math_unit(vb, rsb, c0 + 16);
-    const uint32_t sl = ob & 1;
+    const uint32_t sl = ob & (uint32_t)(obufs - 1);
     const bool st = !(p.dbg & 4);
     if (st) {
-      if (lane == 0) tma_store_wait_read<1>();
+      if (lane == 0) { if (obufs == 1) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
       __syncwarp();
     }
     if (p.out_raw) {
