@@ -599,11 +599,23 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     // 12 epilogue warps (three per TMEM lane quadrant) for short-K layers whose Snake epilogue outweighs their MMAs: the transposed conv
     // 192 -> 96 2.96 -> 2.56 ms, the 1x1 convs of the C = 384 units 3.63 -> 2.85 ms (with one output slot per tensor and warp, see
     // epi_out_bufs); measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers.
-    q.epi_warps = ew ? atoi(ew) : (q.ntaps * q.cin <= 512 && q.out_snake ? 12 : 8);
+    // (1x1 conv C = 768: 1.62 -> 1.41 ms with the N tile narrowed 256 -> 192 so that three operand stages still fit)
+    const bool short_k = q.ntaps * q.cin <= 512 || (q.ntaps == 1 && q.cin <= 768);
+    q.epi_warps = ew ? atoi(ew) : (short_k && q.out_snake ? 12 : 8);
     if (q.epi_warps != 4 && q.epi_warps != 8 && q.epi_warps != 12) q.epi_warps = 8;
     if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || q.res_f32 || q.pack_mode)) q.epi_warps = 8;  // 12 warps: 16-bit vocoder epilogues only
     q.res_depth = q.res ? (q.epi_warps == 12 ? 2 : 4) : 0;
-    if (q.epi_warps == 12 && q.res && gemm_stage_count(q) < 3) { q.epi_warps = 8; q.res_depth = 4; }  // the extra slots would starve the operand pipeline
+    if (q.epi_warps == 12 && q.res && gemm_stage_count(q) < 3) {
+      // the extra slots would starve the operand pipeline: try a narrower N tile (three items per warp trio), else stay at 8 warps
+      const int bn0 = q.bn;
+      bool ok = false;
+      for (int bn = bn0 - 32; bn >= 96 && !ok; bn -= 32) {
+        if (q.n_total % bn || bn % 96) continue;
+        q.bn = bn;
+        ok = gemm_stage_count(q) >= 3;
+      }
+      if (!ok) { q.bn = bn0; q.epi_warps = 8; q.res_depth = 4; }
+    }
     // keep at least three pipeline stages for the general kernel: shrink the residual ring before the stage count
     if (q.res && gemm_stage_count(q) < 3) q.res_depth = 2;
   }
