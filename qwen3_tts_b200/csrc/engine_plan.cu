@@ -220,6 +220,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
         u.C = K.cout; u.dil = -U.conv7.tap_off[0] / 6;
         u.bias7 = U.conv7.bias; u.snake2_a = U.act2.a; u.snake2_ib = U.act2.ib;
         { const char* d = getenv("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
+        { const char* tc = getenv("Q3TTS_TRACE_C"); if (tc && atoi(tc) != K.cout) u.p.dbg &= ~32; }  // timeline of one channel count only
         u.p.bf16 = e->bf16 ? 1 : 0; u.p.bias = U.conv1.bias; u.p.res = R[iy]; u.p.out_raw = R[iy]; u.p.out_snake = R[ifree];
         u.p.snake_a = nx.a; u.p.snake_ib = nx.ib;
         u.p.w_ptr = U.conv7.w;
