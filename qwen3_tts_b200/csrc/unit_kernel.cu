@@ -101,9 +101,12 @@ __device__ __forceinline__ void tma_store_3d_s(const void* map, uint32_t smem_sr
 // P2X_ = 1 (two TMEM stages only): 4 phase-1 warps serve every tile and 12 phase-2 warps own ONE 32-column item each (3 per TMEM lane
 // quadrant), so a tile's phase 2 is one item deep instead of three.  The timeline shows the unit waits on the
 // serial per-item chain of its phase-2 warps while the phase-1 warps idle 75 % of a tile period.
-template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0, int XIN_ = 0, int P2X_ = 0>
+// P1A_ = 1 (one TMEM stage only, C = 192): the tensor pipe idles while phase 1 converts acc1, so ALL 16 epilogue warps take a 48-column
+// slice of it (the phase-2 warps finish the previous tile's phase 2 well inside the conv7 MMAs and are free by then).
+template <int C_, int KB_, int KS_, int NST_, int NSL_, int NBUF_, int PAIR_ = 0, int XIN_ = 0, int P2X_ = 0, int P1A_ = 0>
 struct UnitCfg {
-  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_, XIN = XIN_, P2X = P2X_;
+  static constexpr int C = C_, KB = KB_, KS = KS_, NST = NST_, NSL = NSL_, NBUF = NBUF_, PAIR = PAIR_, XIN = XIN_, P2X = P2X_, P1A = P1A_;
+  static_assert(!P1A || (NBUF == 1 && C % 64 == 0 && !XIN && !P2X), "P1A: single TMEM stage, four 16-column-aligned slices");
   static constexpr int P1W = P2X ? 4 : kP1Warps, P2W = P2X ? 12 : kP2Warps;  // same thread count either way
   static constexpr int URES = P2X ? 1 : kURes;                               // residual ring depth per phase-2 warp
   static constexpr int USLOTS = URES + 2 * kUOutBufs;
@@ -127,6 +130,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   constexpr bool PAIR = Cfg::PAIR != 0;
   constexpr bool XIN = Cfg::XIN != 0;
   constexpr bool P2X = Cfg::P2X != 0;
+  constexpr bool P1A = Cfg::P1A != 0;
   constexpr int P1W = Cfg::P1W, P2W = Cfg::P2W, URES = Cfg::URES, USLOTS = Cfg::USLOTS;
   static_assert(!XIN || (NBUF == 2 && NKG == 1), "XIN: one slab per tile, two phase-1 groups");
   const int rank = PAIR ? (int)cluster_ctarank() : 0;               // 0 = leader (issues the MMAs of both CTAs)
@@ -159,7 +163,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     for (int s = 0; s < NSL; ++s) { mbar_init(&bars->sfull[s], XIN ? 4 * NCTA : 1); mbar_init(&bars->sempty[s], 1); mbar_init(&bars->sland[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&bars->wfull[s], 1); mbar_init(&bars->wempty[s], 1); }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], grp_warps * NCTA);  // pair: both CTAs' warps arrive on the leader's copy
+      mbar_init(&bars->acc1_full[s], 1); mbar_init(&bars->a2_full[s], (P1A ? 16 : grp_warps) * NCTA);  // pair: both CTAs' warps arrive on the leader's copy
       mbar_init(&bars->acc2_full[s], 1); mbar_init(&bars->acc2_empty[s], (P2X ? P2W : grp_warps) * NCTA);
     }
     for (int w = 0; w < P2W; ++w)
@@ -183,6 +187,42 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t tmem_base = bars->tmem_base;
   // TMEM column map inside one stage; stage s starts at column s * 256
   constexpr uint32_t c_acc1 = 0, c_acc2 = C, c_a2 = 2 * C;
+  // P1A: phase 1 of one 48-column slice (slice cs of four) of this warp's 32 rows: acc1 -> + b7 -> SnakeBeta -> packed pairs -> A2
+  auto p1_slice = [&](int cs) {
+    constexpr int SL = C / 4;
+    const uint32_t lane_b = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t src = tmem_base + lane_b + c_acc1 + (uint32_t)(cs * SL);
+    const uint32_t dst = tmem_base + lane_b + c_a2 + (uint32_t)(cs * SL / 2);
+    const uint32_t prm_b = smem_u32(prm) + (uint32_t)(cs * SL) * 4u;
+    // all loads of the slice first, one wait: the slice is latency-bound (three serial ld -> math -> st chains took as long as six)
+    constexpr int NU = SL / 16;
+    uint32_t ra[NU][16];
+    __syncwarp();  // .sync.aligned
+#pragma unroll
+    for (int un = 0; un < NU; ++un) tmem_ld16(src + 16 * un, ra[un]);
+    tmem_ld_wait();
+#pragma unroll
+    for (int un = 0; un < NU; ++un) {
+      const int g = 16 * un;
+      uint32_t pk[8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t pa = prm_b + (uint32_t)(g + 4 * q) * 4u;
+        const float4 b = lds_f4(pa), a = lds_f4(pa + (uint32_t)C * 4u), ib = lds_f4(pa + (uint32_t)C * 8u);
+        const float2 v01 = snake2(add2(make_float2(__uint_as_float(ra[un][4 * q]), __uint_as_float(ra[un][4 * q + 1])), make_float2(b.x, b.y)),
+                                  make_float2(a.x, a.y), make_float2(ib.x, ib.y));
+        const float2 v23 = snake2(add2(make_float2(__uint_as_float(ra[un][4 * q + 2]), __uint_as_float(ra[un][4 * q + 3])), make_float2(b.z, b.w)),
+                                  make_float2(a.z, a.w), make_float2(ib.z, ib.w));
+        pk[2 * q] = Elem<T>::pack2(v01.x, v01.y);
+        pk[2 * q + 1] = Elem<T>::pack2(v23.x, v23.y);
+      }
+      tmem_st8(dst + (g >> 1), pk);
+    }
+    tmem_st_wait();
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) { if (PAIR) mbar_arrive_leader(&bars->a2_full[0]); else mbar_arrive(&bars->a2_full[0]); }
+  };
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (same order as the MMA issuer consumes)
@@ -411,6 +451,11 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_wait(&bars->acc1_full[sb], (uint32_t)(j / NBUF) & 1);
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 6);
+      if (P1A) {
+        p1_slice(grp);  // slices 0, 1 (the phase-2 warps take 2, 3)
+        if (quad == 2 && lane == 0) UTRACE(j, 7);
+        continue;
+      }
       for (int g = 0; g < ncols; g += 32) {
         uint32_t ra[16], rb[16];
         __syncwarp();  // .sync.aligned: reconverge after the barrier spin loop
@@ -485,6 +530,11 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int tile = wid + j * nworkers;
       const int b = tile / m_tiles, mt = tile - b * m_tiles;
       const int row0 = mt * TM + rsub;
+      if (P1A) {  // this warp's slice of phase 1 first: the tensor pipe waits for it
+        mbar_wait(&bars->acc1_full[0], (uint32_t)j & 1);
+        tc_fence_after();
+        p1_slice(2 + grp);
+      }
       mbar_wait(&bars->acc2_full[sb], (uint32_t)(j / NBUF) & 1);
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 8);
@@ -577,6 +627,9 @@ using Cfg192pb = UnitCfg<192, 64, 1, 4, 3, 1, 1>;
 using Cfg96x = UnitCfg<96, 32, 3, 4, 3, 2, 1, 1>;
 // phase 2 by item (variant 7): CTA pairs, 4 phase-1 + 12 phase-2 warps
 using Cfg96q = UnitCfg<96, 32, 3, 8, 2, 2, 1, 0, 1>;
+// phase 1 on all 16 epilogue warps (variants 8, 9): CTA pairs, C = 192
+using Cfg192qa = UnitCfg<192, 64, 1, 6, 3, 1, 1, 0, 0, 1>;
+using Cfg192qb = UnitCfg<192, 64, 1, 4, 3, 1, 1, 0, 0, 1>;
 
 static size_t unit_smem_bytes(const UnitOp& op) {
   const size_t span = (size_t)op.p.kb * 2;
@@ -630,6 +683,7 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = Cfg192pa::NST; op->variant = 4;
     if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = Cfg192pb::NST; op->variant = 5; }
+    if (!getenv("Q3TTS_NO_P1A")) op->variant += 4;  // 8 / 9: same rings, phase 1 on all 16 epilogue warps
   } else {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = 4; op->variant = 1;
@@ -668,6 +722,8 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
     set((const void*)unit_kernel<__half, Cfg96x>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96x>);
     set((const void*)unit_kernel<__half, Cfg96q>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96q>);
+    set((const void*)unit_kernel<__half, Cfg192qa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qa>);
+    set((const void*)unit_kernel<__half, Cfg192qb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qb>);
     if (e != cudaSuccess) return -2;
     attr_done = true;
   }
@@ -712,6 +768,8 @@ cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream) {
     case 4: return launch_cfg<Cfg192pa>(op, u, grid, smem, stream);
     case 6: return launch_cfg<Cfg96x>(op, u, grid, smem, stream);
     case 7: return launch_cfg<Cfg96q>(op, u, grid, smem, stream);
+    case 8: return launch_cfg<Cfg192qa>(op, u, grid, smem, stream);
+    case 9: return launch_cfg<Cfg192qb>(op, u, grid, smem, stream);
     default: return launch_cfg<Cfg192pb>(op, u, grid, smem, stream);
   }
 }
