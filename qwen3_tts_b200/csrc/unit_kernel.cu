@@ -188,7 +188,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   // TMEM column map inside one stage; stage s starts at column s * 256
   constexpr uint32_t c_acc1 = 0, c_acc2 = C, c_a2 = 2 * C;
   // P1A: phase 1 of one 48-column slice (slice cs of four) of this warp's 32 rows: acc1 -> + b7 -> SnakeBeta -> packed pairs -> A2
-  auto p1_slice = [&](int cs) {
+  auto p1_slice = [&](int cs, int jt) {
+    const bool tr = (warp & 3) == 2 && lane == 0 && cs < 2;
     constexpr int SL = C / 4;
     const uint32_t lane_b = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t src = tmem_base + lane_b + c_acc1 + (uint32_t)(cs * SL);
@@ -201,6 +202,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
     for (int un = 0; un < NU; ++un) tmem_ld16(src + 16 * un, ra[un]);
     tmem_ld_wait();
+    if (tr) UTRACE(jt, 13);
 #pragma unroll
     for (int un = 0; un < NU; ++un) {
       const int g = 16 * un;
@@ -218,7 +220,9 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       tmem_st8(dst + (g >> 1), pk);
     }
+    if (tr) UTRACE(jt, 14);
     tmem_st_wait();
+    if (tr) UTRACE(jt, 15);
     tc_fence_before();
     __syncwarp();
     if (lane == 0) { if (PAIR) mbar_arrive_leader(&bars->a2_full[0]); else mbar_arrive(&bars->a2_full[0]); }
@@ -452,7 +456,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tc_fence_after();
       if (quad == 2 && lane == 0) UTRACE(j, 6);
       if (P1A) {
-        p1_slice(grp);  // slices 0, 1 (the phase-2 warps take 2, 3)
+        p1_slice(grp, j);  // slices 0, 1 (the phase-2 warps take 2, 3)
         if (quad == 2 && lane == 0) UTRACE(j, 7);
         continue;
       }
@@ -533,7 +537,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (P1A) {  // this warp's slice of phase 1 first: the tensor pipe waits for it
         mbar_wait(&bars->acc1_full[0], (uint32_t)j & 1);
         tc_fence_after();
-        p1_slice(2 + grp);
+        p1_slice(2 + grp, j);
       }
       mbar_wait(&bars->acc2_full[sb], (uint32_t)(j / NBUF) & 1);
       tc_fence_after();

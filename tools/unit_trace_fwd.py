@@ -24,8 +24,8 @@ torch.cuda.synchronize()
 lib = _capi.load_library()
 tr = (C.c_longlong * 256)()
 lib.q3tts_unit_trace(tr)
-names = ["M1 start", "-", "M1 issued", "a2_full", "acc2_empty", "M2 issued", "P1 start", "P1 done", "P2 start", "P2 done", "S start", "S done", "S wait"]
+names = ["M1 start", "-", "M1 issued", "a2_full", "acc2_empty", "M2 issued", "P1 start", "P1 done", "P2 start", "P2 done", "S start", "S done", "S wait", "P1 ld", "P1 math+st", "P1 st wait"]
 t0 = tr[0]
 print("tile " + " ".join(f"{n[:10]:>10}" for n in names))
 for it in range(16):
-    print(f"{it:4d} " + " ".join(f"{(tr[it*16+e]-t0) if tr[it*16+e] else 0:10d}" for e in range(13)))
+    print(f"{it:4d} " + " ".join(f"{(tr[it*16+e]-t0) if tr[it*16+e] else 0:10d}" for e in range(16)))
