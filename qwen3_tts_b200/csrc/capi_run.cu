@@ -106,7 +106,18 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
     e.codes16_stage_elems = ncodes;
   }
   const size_t nwav = (size_t)B * (size_t)(total > 0 ? total : 0);
-  if (nwav > e.wav_stage_elems) {
+  // Pinned (page-locked) result buffer with room for whole rows: the output conv stores straight into it over PCIe (unified addressing
+  // gives the device an alias of the host pointer), so the waveform never exists in HBM and there is no separate device-to-host copy.
+  void* direct = nullptr;
+  {
+    static const bool off = getenv("Q3TTS_NO_DIRECT_D2H") != nullptr;
+    cudaPointerAttributes at;
+    if (!off && wav_stride >= total && cudaPointerGetAttributes(&at, wav_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+      direct = at.devicePointer;
+    else
+      cudaGetLastError();
+  }
+  if (!direct && nwav > e.wav_stage_elems) {
     cudaStreamSynchronize(s);
     if (e.wav_stage) cudaFree(e.wav_stage);
     e.wav_stage = nullptr; e.wav_stage_elems = 0;
@@ -136,7 +147,8 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
   if (total > 0) {
     // codes are [B,T,Q] here (wrapper layout): strides b = T*Q, k = 1, t = Q
     e.out_pcm16 = pcm16 != 0;  // the staging buffer is then int16 [B][total]
-    int rc = chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
+    int rc = direct ? chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, (float*)direct, wav_stride, s)
+                    : chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
     e.out_pcm16 = false;
     if (rc) return rc;
     // one strided copy for the whole batch: rows are cut to their length by the caller's views, so the columns between a
@@ -144,7 +156,7 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
     long long maxlen = 0;
     for (int b = 0; b < B; ++b) maxlen = lengths[b] > maxlen ? lengths[b] : maxlen;
     if (maxlen > wav_stride) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: wav_stride smaller than an output row");
-    if (maxlen > 0) {
+    if (maxlen > 0 && !direct) {
       const size_t es = pcm16 ? sizeof(short) : sizeof(float);
       err = cudaMemcpy2DAsync(wav_host, (size_t)wav_stride * es, e.wav_stage, (size_t)total * es, (size_t)maxlen * es, (size_t)B, cudaMemcpyDeviceToHost, s);
       if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: D2H: ") + cudaGetErrorString(err));

@@ -145,6 +145,33 @@ def test_wrapper_decode_payload_forms_and_length_rule(gpu_model):
         24000, 24000, 1920, 1920)
 
 
+def test_decode_host_pageable_and_pinned_buffers_agree(gpu_model, cfg):
+    """q3tts_decode_host with a pinned result buffer stores the waveform straight into it from the output conv; a pageable buffer
+    takes the staged device-to-host copy.  Same kernels, same bits; a row stride wider than the output keeps both paths honest."""
+    from qwen3_tts_b200 import _capi
+    from qwen3_tts_b200.modeling import _stream_ptr
+    from qwen3_tts_b200.synthetic import make_codes
+    d = gpu_model.decoder
+    B, T = 3, 11
+    codes = make_codes(B, T, cfg, seed=9).contiguous()
+    codes[2, 7:] = 0
+    total = T * 1920 - 555
+    stride = total + 37
+    outs = []
+    for pinned in (True, False):
+        wav = torch.full((B, stride), 7.0, dtype=torch.float32, pin_memory=pinned)
+        lengths = (C.c_int64 * B)()
+        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), stride, lengths, _stream_ptr(d.device))
+        _capi.check(d._h, rc, "decode_host")
+        assert [int(x) for x in lengths] == [total, total, 7 * 1920]
+        outs.append((wav, [int(x) for x in lengths]))
+    (a, la), (b, lb) = outs
+    for i in range(B):
+        assert torch.equal(a[i, :la[i]], b[i, :lb[i]])
+        assert a[i, :la[i]].abs().max().item() <= 1.0
+    assert torch.equal(a[:, total:], torch.full((B, stride - total), 7.0)) and torch.equal(b[:, total:], a[:, total:])  # padding columns untouched
+
+
 def test_pcm16_and_int16_codes_wire_formats(gpu_model, cfg):
     """int16 code frames in, PCM16 out.  The int16 path must decode exactly what the int64 path decodes, and the
     PCM16 samples must be rint(wav * 32767) of the float result (what sf.write stores), ragged lengths included."""
