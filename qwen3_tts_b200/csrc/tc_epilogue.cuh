@@ -57,6 +57,7 @@ struct EpiWarp {
   bool has_res, rf32, glu, tail, of32, o16;
   int units, item_units, nitems, rd, rd_shift;
   bool wraps;  // a tile's columns can wrap around ncol_mod (transposed convs: n_total = stride * cout)
+  int tile_c0 = 0;  // (first column of the current tile) % ncol_mod: one division per tile instead of one per item
   int s_raw, s_snake, s_f32;  // first slot of each output ring
   int obufs = 2;              // slots per 16-bit output ring (item_pair)
   uint32_t rb_issue = 0, rb_cons = 0, ob = 0, fb = 0;
@@ -186,7 +187,8 @@ struct EpiWarp {
   __device__ __forceinline__ void item_pair(uint32_t t0, int nt, int row0, int b, int item) {
     const int u0 = item * 2;
     const int n0 = nt * p.bn + u0 * 16;
-    const int c0 = wraps ? n0 % p.ncol_mod : n0;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
+    int c0 = n0;  // ncol_mod % 32 == 0 for every 16-bit flow, so the 32 columns never wrap
+    if (wraps) { c0 = tile_c0 + u0 * 16; while (c0 >= p.ncol_mod) c0 -= p.ncol_mod; }
     float rsa[16], rsb[16];
     if (has_res) {
       const uint32_t slot = rb_cons & (rd - 1);
@@ -347,6 +349,7 @@ struct EpiWarp {
   // one accumulator tile: t0 = TMEM address of (this warp's lane quadrant, first column of the tile)
   __device__ __forceinline__ void tile(uint32_t t0, int it, int nt, int mt, int b) {
     int row0 = (mt * mt_mul + mt_add) * 128 + quad * 32;
+    if (wraps) tile_c0 = (nt * p.bn) % p.ncol_mod;
     if (p.pack_mode) gemm_chunk_coords(p, b, quad, row0, b);  // packed tiles: the scheduler's "batch" is the tile index
     if (p.dbg & 1) {
       uint32_t r[16];
