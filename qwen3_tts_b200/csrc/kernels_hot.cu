@@ -150,8 +150,13 @@ k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const fl
     const int r = i >> 2, part = i & 3, t = kbase + r;
     if (t >= k_lo && t < k_hi) {
       float cs[8], sn[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { cs[j] = cos_t[t * 32 + part * 8 + j]; sn[j] = sin_t[t * 32 + part * 8 + j]; }
+      {
+        const float4* c4 = reinterpret_cast<const float4*>(cos_t + t * 32 + part * 8);
+        const float4* s4 = reinterpret_cast<const float4*>(sin_t + t * 32 + part * 8);
+        const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+        cs[0] = ca.x; cs[1] = ca.y; cs[2] = ca.z; cs[3] = ca.w; cs[4] = cb.x; cs[5] = cb.y; cs[6] = cb.z; cs[7] = cb.w;
+        sn[0] = sa.x; sn[1] = sa.y; sn[2] = sa.z; sn[3] = sa.w; sn[4] = sb.x; sn[5] = sb.y; sn[6] = sb.z; sn[7] = sb.w;
+      }
       rope_row8<T>(base + (long long)t * ld + nh * AM_HD, cs, sn, sK + r * AM_PITCH, part);
       const uint4* vr = reinterpret_cast<const uint4*>(base + (long long)t * ld + 2 * nh * AM_HD);
       reinterpret_cast<uint4*>(sV + r * AM_PITCH)[part] = vr[part];
@@ -165,8 +170,13 @@ k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const fl
     const int r = i >> 2, part = i & 3, t = q0 + r;
     if (t < Tn) {
       float cs[8], sn[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { cs[j] = cos_t[t * 32 + part * 8 + j]; sn[j] = sin_t[t * 32 + part * 8 + j]; }
+      {
+        const float4* c4 = reinterpret_cast<const float4*>(cos_t + t * 32 + part * 8);
+        const float4* s4 = reinterpret_cast<const float4*>(sin_t + t * 32 + part * 8);
+        const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+        cs[0] = ca.x; cs[1] = ca.y; cs[2] = ca.z; cs[3] = ca.w; cs[4] = cb.x; cs[5] = cb.y; cs[6] = cb.z; cs[7] = cb.w;
+        sn[0] = sa.x; sn[1] = sa.y; sn[2] = sa.z; sn[3] = sa.w; sn[4] = sb.x; sn[5] = sb.y; sn[6] = sb.z; sn[7] = sb.w;
+      }
       rope_row8<T>(base + (long long)t * ld, cs, sn, sQ + r * AM_PITCH, part);
     } else {
       zero_row8(sQ + r * AM_PITCH, part);
