@@ -70,8 +70,16 @@ k_stream_attention(const T* __restrict__ qkv, T* __restrict__ kc, T* __restrict_
     if (t < P) {
       const int pos = pos0 + t;
       float cs[8], sn[8];
+      if (pos < rope_max) {  // table rows as two float4 each (the same values the bulk kernel reads)
+        const float4* c4 = reinterpret_cast<const float4*>(cos_t + pos * 32 + part * 8);
+        const float4* s4 = reinterpret_cast<const float4*>(sin_t + pos * 32 + part * 8);
+        const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+        cs[0] = ca.x; cs[1] = ca.y; cs[2] = ca.z; cs[3] = ca.w; cs[4] = cb.x; cs[5] = cb.y; cs[6] = cb.z; cs[7] = cb.w;
+        sn[0] = sa.x; sn[1] = sa.y; sn[2] = sa.z; sn[3] = sa.w; sn[4] = sb.x; sn[5] = sb.y; sn[6] = sb.z; sn[7] = sb.w;
+      } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) rope_cs(cos_t, sin_t, rope_max, theta, pos, part * 8 + j, cs[j], sn[j]);
+        for (int j = 0; j < 8; ++j) rope_cs(cos_t, sin_t, rope_max, theta, pos, part * 8 + j, cs[j], sn[j]);
+      }
       T* krow = sK + (pos - kbase) * AM_PITCH;
       rope_row8<T>(base + (long long)t * ld + H, cs, sn, krow, part);
       T* kdst = kslot + (long long)(pos & (ring - 1)) * H;
