@@ -104,3 +104,58 @@ class Qwen3TTSModel:
         codes, _ = self.model.generate(input_ids=self._ids(text), voice_clone_prompt=prompt, languages=language,
                                        non_streaming_mode=non_streaming_mode, **self._merged(kwargs))
         return self.decode_talker_codes(codes, prompt.get("ref_code", None))
+
+
+class TalkerStreamSink:
+    """On-device hand-off from the talker's generation loop to the stateful streaming decoder.
+
+    The reference collects every step's `codec_ids` [B, 16] (talker :1681) into Python lists, stacks them after generation
+    (talker :2280) and only then decodes (model wrapper :838).  This sink takes the same per-step tensor while it is still on
+    the device, buffers `packet` frames per stream and runs one `decode_step` for all live streams when a packet is full, so
+    audio leaves `packet * 80 ms` after its codes exist.  The concatenated chunks of a stream equal
+    `Decoder.forward(all its codes)` on `[0, T*1920 - 555)` (the streaming contract); nothing here synchronises
+    with the host except the caller's own use of the returned chunk.
+    """
+
+    def __init__(self, decoder, batch: int, packet: int = 1, reserve: bool = True):
+        """`decoder`: a qwen3_tts_b200 Qwen3TTSTokenizerV2Decoder.  `reserve=False` when the caller has already sized the stream
+        pool with `decoder.reserve_streams(...)` (reserving again would drop the state of streams that are open)."""
+        if batch < 1 or packet < 1:
+            raise ValueError("batch and packet must be positive")
+        self.decoder = decoder
+        self.packet = int(packet)
+        self.Q = int(decoder.config.num_quantizers)
+        if reserve:
+            decoder.reserve_streams(batch, self.packet)
+        self.ids = [decoder.open_stream() for _ in range(batch)]
+        self.live = [True] * batch
+        self._buf = torch.zeros((batch, self.Q, self.packet), dtype=torch.int64, device=decoder.device)
+        self._fill = 0
+
+    def push(self, codec_ids: torch.Tensor):
+        """codec_ids: [B, 16] integer tensor on the decoder's device (one generated frame per stream, finished streams included:
+        their rows are ignored once `finish(i)` was called).  Returns None until a packet is full, then
+        `(rows, wav [len(rows), packet*1920] float32 on the device, n_valid)` for the live streams `rows`."""
+        if codec_ids.dim() != 2 or codec_ids.shape != (len(self.ids), self.Q):
+            raise ValueError(f"Expected codec_ids of shape ({len(self.ids)}, {self.Q}), got {tuple(codec_ids.shape)}")
+        self._buf[:, :, self._fill] = codec_ids.to(device=self._buf.device, dtype=torch.int64)
+        self._fill += 1
+        if self._fill < self.packet:
+            return None
+        self._fill = 0
+        rows = [i for i, ok in enumerate(self.live) if ok]
+        if not rows:
+            return None
+        codes = self._buf if len(rows) == len(self.ids) else self._buf[rows]
+        wav, n_valid = self.decoder.decode_step([self.ids[i] for i in rows], codes.contiguous())
+        return rows, wav, n_valid
+
+    def finish(self, row: int) -> None:
+        """Stream `row` has produced its stop token: its state is released, later frames of that row are ignored."""
+        if self.live[row]:
+            self.live[row] = False
+            self.decoder.close_stream(self.ids[row])
+
+    def close(self) -> None:
+        for i in range(len(self.ids)):
+            self.finish(i)

@@ -307,6 +307,38 @@ def test_streaming_equals_whole_sequence_forward(gpu_model, cfg):
         dec.decode_step([0], codes[0:1, :, :1])      # closed stream
 
 
+def test_talker_stream_sink_equals_whole_sequence_forward(gpu_model, cfg):
+    """SURVEY 8f-1 hand-off: the talker's per-step codec_ids [B, 16], pushed on the device one frame at a time, decode to the same
+    samples as Decoder.forward over the stacked sequence (bit for bit); a stream that finishes early stops emitting."""
+    from qwen3_tts_b200 import TalkerStreamSink
+    from qwen3_tts_b200.synthetic import make_codes
+    dec = gpu_model.decoder
+    B, T, P = 3, 10, 2
+    codes = make_codes(B, T, cfg, seed=21).cuda()                               # [B, T, Q] as the talker stacks them (talker :2280)
+    whole = dec(codes.transpose(1, 2).contiguous())[:, 0]                       # [B, T*1920-555]
+    short = dec(codes[2:3, :6].transpose(1, 2).contiguous())[0, 0]              # row 2 stops after 6 frames
+    sink = TalkerStreamSink(dec, batch=B, packet=P)
+    got = [[] for _ in range(B)]
+    for t in range(T):
+        if t == 6:
+            sink.finish(2)
+        out = sink.push(codes[:, t])
+        assert (out is None) == (t % P == 0)
+        if out is not None:
+            rows, wav, nv = out
+            assert rows == ([0, 1, 2] if t < 6 else [0, 1])
+            for k, r in enumerate(rows):
+                got[r].append(wav[k, :nv[k]].clone())
+    sink.close()
+    for r in (0, 1):
+        assert torch.equal(torch.cat(got[r]), whole[r])
+    assert torch.equal(torch.cat(got[2]), short)
+    bad = TalkerStreamSink(dec, batch=1, packet=1, reserve=False)
+    with pytest.raises(ValueError):
+        bad.push(codes[:, 0])                                                   # [3, 16] for a sink of one stream
+    bad.close()
+
+
 def test_streaming_matches_reference_golden(gpu_model):
     """Streamed in packets of 2 frames, the golden batch must meet the same tolerance as the bulk decode vs the fp32 reference."""
     g = load_golden("forward_B2_T12.npz")
