@@ -77,10 +77,26 @@ struct StreamPlan {
   StreamBufDesc* d_descs = nullptr;  // device copy, the plan's own allocation: the arena is scratch shared by every plan
   int out_len = 0;                    // samples emitted per stream
   float* wav_tmp = nullptr;           // dense [S][out_len] staging when the caller's rows are not the identity
+  // CUDA graphs of this plan's launch sequence, one per set of caller pointers (a step is ~96 small launches: launch-bound at few streams).
+  // A key seen twice in a row is captured; at most four are kept.
+  struct GraphEntry {
+    const void* codes = nullptr; long long sb = 0, sk = 0, st = 0;
+    float* wav = nullptr; long long stride = 0; bool identity = false;
+    cudaGraphExec_t exec = nullptr;
+    bool same(const GraphEntry& o) const {
+      return codes == o.codes && sb == o.sb && sk == o.sk && st == o.st && wav == o.wav && stride == o.stride && identity == o.identity;
+    }
+  };
+  std::vector<GraphEntry> graphs;
+  GraphEntry last;
+  bool last_valid = false, graph_off = false;
   StreamPlan() = default;
   StreamPlan(const StreamPlan&) = delete;
   StreamPlan& operator=(const StreamPlan&) = delete;
-  ~StreamPlan() { if (d_descs) cudaFree(d_descs); }
+  ~StreamPlan() {
+    for (GraphEntry& g : graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (d_descs) cudaFree(d_descs);
+  }
 };
 
 struct Engine {

@@ -271,8 +271,52 @@ int get_stream_plan(Engine* e, int S, int P, bool fresh, StreamPlan** out) {
   return 0;
 }
 
+int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long long sb, long long sk, long long st, const int* d_ids, const int* d_rows,
+                       bool identity_rows, float* wav, long long wav_stride, cudaStream_t s);
+
+// Runs the plan's launches directly, or as one CUDA graph once the same caller pointers have been seen twice in a row.
 int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long long sb, long long sk, long long st, const int* d_ids, const int* d_rows,
                     bool identity_rows, float* wav, long long wav_stride, cudaStream_t s) {
+  static const bool graphs_off = getenv("Q3TTS_STREAM_GRAPH") == nullptr || getenv("Q3TTS_NO_GRAPH") != nullptr || getenv("Q3TTS_SYNC") != nullptr;
+  if (graphs_off || plan->graph_off || e->profile) return launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
+  StreamPlan::GraphEntry key;
+  key.codes = codes; key.sb = sb; key.sk = sk; key.st = st; key.wav = wav; key.stride = wav_stride; key.identity = identity_rows;
+  for (StreamPlan::GraphEntry& g : plan->graphs)
+    if (g.same(key)) {
+      if (cudaGraphLaunch(g.exec, s) != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("stream graph launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+      e->launches += (long long)plan->ops.size() + ((!identity_rows && plan->out_len > 0) ? 1 : 0);
+      return Q3TTS_OK;
+    }
+  if (!(plan->last_valid && plan->last.same(key))) {  // first sight of these pointers: plain launches (also the warm-up of lazy attributes)
+    plan->last = key; plan->last_valid = true;
+    return launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
+  }
+  if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError(); plan->graph_off = true;
+    return launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
+  }
+  const long long launches0 = e->launches;
+  const int rc = launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(s, &graph);
+  cudaGraphExec_t exec = nullptr;
+  if (rc != Q3TTS_OK || ce != cudaSuccess || !graph || cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) {
+    cudaGetLastError();
+    if (graph) cudaGraphDestroy(graph);
+    plan->graph_off = true;  // this plan keeps to plain launches
+    e->launches = launches0;
+    return launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
+  }
+  cudaGraphDestroy(graph);
+  if (plan->graphs.size() >= 4) { cudaGraphExecDestroy(plan->graphs.front().exec); plan->graphs.erase(plan->graphs.begin()); }
+  key.exec = exec;
+  plan->graphs.push_back(key);
+  if (cudaGraphLaunch(exec, s) != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("stream graph launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  return Q3TTS_OK;  // e->launches was advanced by the capture pass
+}
+
+int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long long sb, long long sk, long long st, const int* d_ids, const int* d_rows,
+                       bool identity_rows, float* wav, long long wav_stride, cudaStream_t s) {
   const q3tts_config& c = e->cfg;
   float* tail_out = identity_rows ? wav : plan->wav_tmp;
   const long long tail_stride = identity_rows ? wav_stride : plan->out_len;
