@@ -14,17 +14,6 @@ namespace q3 {
     else { using T = __half; __VA_ARGS__; }                       \
   } while (0)
 
-__device__ __forceinline__ float wsum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-__device__ __forceinline__ float wmax(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
-}
-
 // cos/sin of pos * theta^(-2d/64): table below rope_max (bit-identical to the bulk path), direct evaluation above
 __device__ __forceinline__ void rope_cs(const float* __restrict__ cos_t, const float* __restrict__ sin_t, int rope_max, float theta, int pos, int d,
                                         float& c, float& s) {
