@@ -601,7 +601,8 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     // epi_out_bufs); measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers.
     // (1x1 conv C = 768: 1.62 -> 1.41 ms with the N tile narrowed 256 -> 192 so that three operand stages still fit)
     const bool short_k = q.ntaps * q.cin <= 512 || (q.ntaps == 1 && q.cin <= 768);
-    q.epi_warps = ew ? atoi(ew) : (short_k && q.out_snake ? 12 : 8);
+    // (ConvNeXt pw1: the erf GELU epilogue outweighs K = 1024 of MMAs per tile too: 0.70 -> 0.56 ms)
+    q.epi_warps = ew ? atoi(ew) : ((short_k && q.out_snake) || q.act == ACT_GELU ? 12 : 8);
     if (q.epi_warps != 4 && q.epi_warps != 8 && q.epi_warps != 12) q.epi_warps = 8;
     if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || q.res_f32 || q.pack_mode)) q.epi_warps = 8;  // 12 warps: 16-bit vocoder epilogues only
     q.res_depth = q.res ? (q.epi_warps == 12 ? 2 : 4) : 0;
