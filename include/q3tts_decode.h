@@ -100,16 +100,27 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
  * codes [B,T,Q] int64 in HOST memory (padded with 0 like pad_sequence) -> wav_host [B, wav_stride]
  * fp32 HOST memory, lengths[b] = min((codes[b,:,0] > 0).sum()*upsample, chunked length).  The first
  * lengths[b] samples of row b are its waveform; columns up to the longest row's length may be written
- * too (one strided copy for the batch).  Synchronises the stream before returning. */
+ * too (one strided copy for the batch).  Synchronises the stream before returning.
+ * Every code is range-checked on the host first: Q3TTS_CODE_OUT_OF_RANGE (Python IndexError) where the reference's F.embedding
+ * raises (modeling :675-678), before anything is launched.
+ * skip_samples (host, [B], may be NULL): the voice-clone prefix cut of Qwen3TTSModel.generate_voice_clone (model wrapper :612-631)
+ * folded into the decode.  The first skip_samples[b] samples of item b are never stored (the output conv skips them, chunks that
+ * lie wholly inside every item's cut are not computed); row b starts at its sample skip_samples[b] and lengths[b] is what is left. */
 int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
-                      void* stream);
+                      const int64_t* skip_samples, void* stream);
 
 /* Same call with the wire formats of SURVEY 8f-3: int16 code frames in (a 2048-entry codebook index fits; the reference
  * keeps codes as JSON lists / numpy payloads, finetuning/prepare_data.py:49, examples/test_tokenizer_12hz.py:54-58) and PCM16
  * out, pcm = lrintf(clamp(wav, -1, 1) * 32767): what `sf.write(path, wav, sr)` stores for a float waveform (examples :33).
  * The conversion is fused into the output conv, so host traffic is 4x / 2x smaller.  Strides in int16 elements. */
 int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, int T, int16_t* pcm_host, int64_t pcm_stride, int64_t* lengths,
-                            void* stream);
+                            const int64_t* skip_samples, void* stream);
+
+/* Opt-in range check for the entry points that take DEVICE codes (rvq_decode, forward, chunked_decode, stream_step).  The gather
+ * kernel never faults on a bad index (it decodes a clamped one and raises a device flag); with the check on, these calls read the
+ * flag after their launches - which synchronises the stream - and return Q3TTS_CODE_OUT_OF_RANGE, as the reference's F.embedding
+ * asserts (modeling :675-678).  Off by default: the hot path stays asynchronous ("check on request only"). */
+int q3tts_set_check_codes(q3tts_handle* h, int on);
 
 /* ---- Streaming: stateful per-packet decode.  The reference has NO counterpart: its only streaming-shaped call is
  * chunked_decode's `forward(codes[..., s-25:e])[..., 25*1920:]` (modeling :889-893), which re-decodes 25 frames of left
@@ -129,7 +140,8 @@ int q3tts_stream_close(q3tts_handle* h, int stream_id);
 int64_t q3tts_stream_frames(q3tts_handle* h, int stream_id);   /* frames decoded so far, -1 = not open */
 int64_t q3tts_stream_state_bytes(q3tts_handle* h);              /* device bytes of state per stream */
 /* One step: stream_ids[S] (host), codes [S,Q,P] int64 (device), wav [S, wav_stride] fp32 (device, wav_stride >= P*1920),
- * n_valid[S] (host, optional) = samples written per row.  All launches go to `stream`; returns without synchronising. */
+ * n_valid[S] (host, optional) = samples written per row.  All launches go to `stream`; returns without synchronising (the stream
+ * ids travel through a small ring of pinned staging blocks guarded by events, never through a stream synchronise). */
 int q3tts_stream_step(q3tts_handle* h, const int32_t* stream_ids, int S, const int64_t* codes, int P, float* wav, int64_t wav_stride,
                       int32_t* n_valid, void* stream);
 
@@ -150,30 +162,6 @@ int64_t q3tts_launch_count(q3tts_handle* h);
  * items, N, Cin, taps for GEMM ops. */
 int q3tts_set_profile(q3tts_handle* h, int on);
 int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes, int32_t* dims);
-
-/* Standalone GEMM self-test of the tcgen05 implicit-GEMM kernel against the SIMT cross-check
- * (device-side, no host math): returns max |tc - simt| over a [rows,n] problem via *max_abs_diff. */
-int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dilation, int bf16, float* max_abs_diff, float* max_abs_ref);
-
-/* Self-test of the fused residual-unit kernel (conv7 -> Snake -> conv1 + residual in one launch, intermediate kept in
- * tensor memory) against two launches of the SIMT cross-check: out4 = {max|y-y_ref|, max|y_ref|, max|s-s_ref|, max|s_ref|}.
- * Returns Q3TTS_BAD_CONFIG when the channel count cannot be fused. */
-int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4);
-
-/* Debug timeline of the fused unit kernel (env Q3TTS_DBG bit 5): clock64 stamps [16 tiles][16 events] of CTA 0. */
-int q3tts_unit_trace(long long* out256);
-
-/* tcgen05.mma issue-rate microbenchmark (design evidence): SM cycles per MMA (M = 128, K = 16, fp16) for an N, operand form
- * (0 = A,B in shared memory, 1 = A in tensor memory), swizzle span (64 / 128 bytes), A row shift, accumulator count, and a tcgen05.commit / mbarrier wait every k groups of 8 MMAs. */
-/* CTA-pair (tcgen05 cta_group::2) building blocks: D[256,n] = A[256,k] . W[n,k]^T on one 2-CTA cluster; ts != 0 also runs
- * the tensor-memory A operand form (k == n <= 128).  iters > 0: throughput run on every SM pair instead of a comparison.
- * out4 = {max |D - ref|, max |D2 - ref2|, cycles per M = 256 MMA, 0}. */
-int q3tts_selftest_pair(int device, int n, int k, int iters, int ts, float* out4);
-int q3tts_bench_mma(int device, int n, int span, int a_row_shift, int form, int nacc, int commit_every, int wait_every, float* clk_per_mma);
-
-/* TMA box-shape microbenchmark (design evidence, DESIGN.md "Epilogue boxes"): aggregate GB/s of `warps` warps per SM moving
- * [box_rows x box_cols] 16-bit boxes between shared memory and a channels-last [rows][C] tensor. */
-int q3tts_bench_tma(int device, int C, int box_cols, int box_rows, int is_load, int warps, int iters, float* gbps);
 
 #ifdef __cplusplus
 }

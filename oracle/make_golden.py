@@ -74,7 +74,10 @@ def main():
         # g4: the real two-chunk path (chunk 300, left context 25), B=1, T=310; waveform stored every 8th sample
         codes = make_codes(1, 310, cfg, seed=3)
         wav = dec.chunked_decode(codes.transpose(1, 2))
+        seam = 300 * 1920 - 555                      # first sample emitted by the second chunk
+        s0 = seam - 8192
         np.savez_compressed(os.path.join(OUT, "chunked_B1_T310.npz"), codes=codes.numpy(), wav_sub8=wav.numpy()[..., ::8],
+                            wav_seam=wav.numpy()[..., s0:s0 + 16384], seam_start=np.array(s0),
                             num_samples=np.array(wav.shape[-1]), weight_fingerprint=fp)
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)))

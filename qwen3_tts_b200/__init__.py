@@ -11,12 +11,12 @@ from .inference import Qwen3TTSModel, TalkerStreamSink
 from .tokenizer import Qwen3TTSTokenizer
 
 
-def synthetic_model(seed: int = 0, device="cuda:0", compute_mode: str = "fp16", state_dict=None):
+def synthetic_model(seed: int = 0, device="cuda:0", compute_mode: str = "fp16", state_dict=None, stress: bool = False):
     """Model with the seeded random-init weights of the named architecture (no checkpoint is mounted)."""
     from .synthetic import make_decoder_state_dict
     cfg = Qwen3TTSTokenizerV2Config()
     model = Qwen3TTSTokenizerV2Model(cfg, device=device, compute_mode=compute_mode)
-    sd = state_dict if state_dict is not None else make_decoder_state_dict(cfg.decoder_config, seed)
+    sd = state_dict if state_dict is not None else make_decoder_state_dict(cfg.decoder_config, seed, stress=stress)
     model.decoder.load_state_dict(sd)
     return model
 

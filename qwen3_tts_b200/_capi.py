@@ -10,9 +10,17 @@ from typing import Optional
 from .configuration import Qwen3TTSTokenizerV2DecoderConfig
 
 _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libq3tts_decode.so")
-if os.environ.get("Q3TTS_LIB"):  # same-box A/B of two builds of the library (tools/ab_layers.sh); still the CUDA library, never a fallback
-    _LIB_PATH = os.path.abspath(os.environ["Q3TTS_LIB"])
 _lib: Optional[C.CDLL] = None
+
+
+def set_library_path(path: str) -> None:
+    """tools/ only (same-box A/B of two builds, the -DQ3TTS_DEBUG build): load another build of the SAME CUDA library.
+    An explicit call, made before the first load; the product never reads an environment variable to find its library."""
+    global _LIB_PATH
+    if _lib is not None:
+        raise RuntimeError("the library is already loaded")
+    _LIB_PATH = os.path.abspath(path)
+
 
 OK, BAD_SHAPE, BAD_CONFIG, CODE_OUT_OF_RANGE, CUDA_ERROR, OOM, BAD_STREAM, BAD_KEY, NOT_READY = 0, -1, -2, -3, -4, -5, -6, -7, -8
 MODE_FP16, MODE_BF16 = 0, 1
@@ -57,8 +65,9 @@ EXPORTS = {
     "q3tts_rvq_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_chunked_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
-    "q3tts_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
-    "q3tts_decode_host_pcm16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "q3tts_decode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "q3tts_decode_host_pcm16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "q3tts_set_check_codes": (C.c_int, [C.c_void_p, C.c_int]),
     "q3tts_forward_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_void_p, C.c_int64,
                                       C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p]),
     "q3tts_stream_reserve": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
@@ -71,6 +80,11 @@ EXPORTS = {
     "q3tts_launch_count": (C.c_int64, [C.c_void_p]),
     "q3tts_set_profile": (C.c_int, [C.c_void_p, C.c_int]),
     "q3tts_get_profile": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
+}
+
+# include/q3tts_debug.h: self-tests, microbenchmarks, timeline (tests/ and tools/ only)
+DEBUG_EXPORTS = {
+    "q3tts_selftest_snake": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "q3tts_unit_trace": (C.c_int, [C.POINTER(C.c_longlong)]),
     "q3tts_bench_mma": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "q3tts_bench_tma": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),
@@ -94,7 +108,7 @@ def load_library() -> C.CDLL:
             f"{_LIB_PATH} is missing: build it with `python -m qwen3_tts_b200.build` (or __graft_entry__.build()). "
             "There is no CPU fallback for the decode path.")
     lib = C.CDLL(_LIB_PATH)
-    for name, (res, args) in EXPORTS.items():
+    for name, (res, args) in list(EXPORTS.items()) + list(DEBUG_EXPORTS.items()):
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         fn.restype = res
         fn.argtypes = args

@@ -16,8 +16,10 @@ int ready(Engine& e, const void* codes, int B, int T) {
 }
 
 // chunk loop of Qwen3TTSTokenizerV2Decoder.chunked_decode (reference modeling :887-894); codes addressed by strides
+// item_skip (device, optional): per-item count of leading samples that are never stored (voice-clone prefix, model wrapper :627-630);
+// min_skip = the smallest of them: a chunk that ends at or before it is not computed at all.
 int chunked(Engine& e, const long long* codes, long long sb, long long sk, long long st, int B, int T, int chunk, int left_ctx, float* wav,
-            long long wav_stride, cudaStream_t s) {
+            long long wav_stride, cudaStream_t s, const long long* item_skip = nullptr, long long min_skip = 0) {
   int start = 0;
   long long out_off = 0;
   while (start < T) {
@@ -27,9 +29,10 @@ int chunked(Engine& e, const long long* codes, long long sb, long long sk, long 
     const int Tc = end - lo;
     const long long emitted = (long long)(end - start) * e.total_up - e.lookahead;
     if (emitted > 0) {
-      float* dst = e.out_pcm16 ? reinterpret_cast<float*>(reinterpret_cast<short*>(wav) + out_off) : wav + out_off;
-      int rc = engine_forward_batched(&e, codes + lo * st, sb, sk, st, B, Tc, dst, wav_stride, ctx * e.total_up, s);
-      if (rc) return rc;
+      if (!(item_skip && out_off + emitted <= min_skip)) {
+        int rc = engine_forward_batched(&e, codes + lo * st, sb, sk, st, B, Tc, wav, wav_stride, ctx * e.total_up, s, out_off, item_skip);
+        if (rc) return rc;
+      }
       out_off += emitted;
     }
     start = end;
@@ -49,10 +52,10 @@ int q3tts_rvq_decode(q3tts_handle* h, const int64_t* codes, int B, int T, float*
   DeviceGuard g(e.device);
   const int Q = e.cfg.num_quantizers;
   cudaError_t err = rvq_decode((const long long*)codes, (long long)Q * T, T, 1, e.rvq_tables, nullptr, out, B, Q, T, e.cfg.codebook_size,
-                               e.cfg.codebook_dim, e.bf16, (cudaStream_t)stream);
+                               e.cfg.codebook_dim, e.bf16, (cudaStream_t)stream, 0, nullptr, e.d_bad_code);
   ++e.launches;
   if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("rvq_decode: ") + cudaGetErrorString(err));
-  return Q3TTS_OK;
+  return e.check_codes ? engine_check_codes(&e, (cudaStream_t)stream) : Q3TTS_OK;
 }
 
 int q3tts_forward(q3tts_handle* h, const int64_t* codes, int B, int T, float* wav, void* stream) {
@@ -64,7 +67,8 @@ int q3tts_forward(q3tts_handle* h, const int64_t* codes, int B, int T, float* wa
   const int Q = e.cfg.num_quantizers;
   const long long n = (long long)T * e.total_up - e.lookahead;
   if (n <= 0) return e.fail(Q3TTS_BAD_SHAPE, "forward: sequence too short");
-  return engine_forward_batched(&e, (const long long*)codes, (long long)Q * T, T, 1, B, T, wav, n, 0, (cudaStream_t)stream);
+  if (int rc = engine_forward_batched(&e, (const long long*)codes, (long long)Q * T, T, 1, B, T, wav, n, 0, (cudaStream_t)stream)) return rc;
+  return e.check_codes ? engine_check_codes(&e, (cudaStream_t)stream) : Q3TTS_OK;
 }
 
 int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, int chunk, int left_ctx, float* wav, void* stream) {
@@ -75,12 +79,14 @@ int q3tts_chunked_decode(q3tts_handle* h, const int64_t* codes, int B, int T, in
   DeviceGuard g(e.device);
   const int Q = e.cfg.num_quantizers;
   const long long total = q3tts_chunked_num_samples(h, T, chunk, left_ctx);
-  return chunked(e, (const long long*)codes, (long long)Q * T, T, 1, B, T, chunk, left_ctx, wav, total, (cudaStream_t)stream);
+  if (int rc = chunked(e, (const long long*)codes, (long long)Q * T, T, 1, B, T, chunk, left_ctx, wav, total, (cudaStream_t)stream)) return rc;
+  return e.check_codes ? engine_check_codes(&e, (cudaStream_t)stream) : Q3TTS_OK;
 }
 
 // codes16 != 0: codes_host is int16 [B,T,Q]; pcm16 != 0: wav_host is int16 PCM (strides in elements of the output type)
+// skip_samples (host, optional): leading samples of each item that are dropped (never stored); lengths[b] is what remains.
 static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16, int B, int T, void* wav_host, int pcm16, int64_t wav_stride,
-                            int64_t* lengths, void* stream) {
+                            int64_t* lengths, const int64_t* skip_samples, void* stream) {
   if (!h) return Q3TTS_BAD_CONFIG;
   Engine& e = h->e;
   if (int rc = ready(e, codes_host, B, T)) return rc;
@@ -91,6 +97,50 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
   const int chunk = 300, left_ctx = 25;  // Qwen3TTSTokenizerV2Model.decode uses chunked_decode's defaults (modeling :1012)
   const long long total = q3tts_chunked_num_samples(h, T, chunk, left_ctx);
   const size_t ncodes = (size_t)B * T * Q;
+  // One host pass over the codes before anything is launched: the range check the reference gets from F.embedding (an IndexError on
+  // CPU, a device assert on CUDA; modeling :675-678) and audio_lengths = (audio_codes[..., 0] > 0).sum(1) * decode_upsample_rate,
+  // then a[:l] (modeling :1014-1015).
+  const long long ncb = e.cfg.codebook_size;
+  bool any_skip = false;
+  long long min_skip = -1;
+  for (int b = 0; b < B; ++b) {
+    long long cnt = 0;
+    for (int t = 0; t < T; ++t) {
+      const size_t i = ((size_t)b * T + t) * Q;
+      for (int k = 0; k < Q; ++k) {
+        const long long c = codes16 ? (long long)static_cast<const int16_t*>(codes_host)[i + k] : (long long)static_cast<const int64_t*>(codes_host)[i + k];
+        if (c < 0 || c >= ncb)
+          return e.fail(Q3TTS_CODE_OUT_OF_RANGE, "decode_host: code " + std::to_string(c) + " at [" + std::to_string(b) + "," + std::to_string(t) + "," +
+                                                      std::to_string(k) + "] is outside [0, " + std::to_string(ncb) + ")");
+        if (k == 0) cnt += c > 0 ? 1 : 0;
+      }
+    }
+    long long l = cnt * e.total_up;
+    if (l > total) l = total;
+    if (l < 0) l = 0;
+    long long cut = skip_samples ? skip_samples[b] : 0;
+    if (cut < 0) return e.fail(Q3TTS_BAD_SHAPE, "decode_host: negative skip_samples");
+    if (cut > l) cut = l;
+    any_skip = any_skip || cut > 0;
+    if (min_skip < 0 || cut < min_skip) min_skip = cut;
+    lengths[b] = l - cut;
+  }
+  if (min_skip < 0) min_skip = 0;
+  if (any_skip) {
+    if ((size_t)B > e.item_skip_elems) {
+      cudaStreamSynchronize(s);
+      if (e.item_skip_stage) cudaFree(e.item_skip_stage);
+      e.item_skip_stage = nullptr; e.item_skip_elems = 0;
+      if (cudaMalloc((void**)&e.item_skip_stage, (size_t)B * sizeof(long long)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "decode_host: skip staging"); }
+      e.item_skip_elems = (size_t)B;
+    }
+    // the caller's array may be pageable and is only borrowed for this call: clamp into a small vector and copy synchronously
+    std::vector<long long> cuts((size_t)B);
+    for (int b = 0; b < B; ++b) { const long long c = skip_samples[b]; cuts[b] = c < 0 ? 0 : c; }
+    if (cudaMemcpyAsync(e.item_skip_stage, cuts.data(), (size_t)B * sizeof(long long), cudaMemcpyHostToDevice, s) != cudaSuccess ||
+        cudaStreamSynchronize(s) != cudaSuccess)
+      return e.fail(Q3TTS_CUDA_ERROR, "decode_host: skip upload failed");
+  }
   if (ncodes > e.codes_stage_elems) {
     cudaStreamSynchronize(s);
     if (e.codes_stage) cudaFree(e.codes_stage);
@@ -110,7 +160,7 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
   // gives the device an alias of the host pointer), so the waveform never exists in HBM and there is no separate device-to-host copy.
   void* direct = nullptr;
   {
-    static const bool off = getenv("Q3TTS_NO_DIRECT_D2H") != nullptr;
+    static const bool off = Q3_ENV("Q3TTS_NO_DIRECT_D2H") != nullptr;
     cudaPointerAttributes at;
     if (!off && wav_stride >= total && cudaPointerGetAttributes(&at, wav_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
       direct = at.devicePointer;
@@ -132,23 +182,12 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
     err = cudaMemcpyAsync(e.codes_stage, codes_host, ncodes * sizeof(long long), cudaMemcpyHostToDevice, s);
   }
   if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("decode_host: H2D: ") + cudaGetErrorString(err));
-  // audio_lengths = (audio_codes[..., 0] > 0).sum(1) * decode_upsample_rate, then a[:l] (modeling :1014-1015)
-  for (int b = 0; b < B; ++b) {
-    long long cnt = 0;
-    for (int t = 0; t < T; ++t) {
-      const size_t i = ((size_t)b * T + t) * Q;
-      cnt += (codes16 ? (long long)static_cast<const int16_t*>(codes_host)[i] : (long long)static_cast<const int64_t*>(codes_host)[i]) > 0 ? 1 : 0;
-    }
-    long long l = cnt * e.total_up;
-    if (l > total) l = total;
-    if (l < 0) l = 0;
-    lengths[b] = l;
-  }
   if (total > 0) {
     // codes are [B,T,Q] here (wrapper layout): strides b = T*Q, k = 1, t = Q
     e.out_pcm16 = pcm16 != 0;  // the staging buffer is then int16 [B][total]
-    int rc = direct ? chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, (float*)direct, wav_stride, s)
-                    : chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, e.wav_stage, total, s);
+    float* dst = direct ? (float*)direct : e.wav_stage;
+    const long long dst_stride = direct ? wav_stride : total;
+    int rc = chunked(e, e.codes_stage, (long long)T * Q, 1, Q, B, T, chunk, left_ctx, dst, dst_stride, s, any_skip ? e.item_skip_stage : nullptr, min_skip);
     e.out_pcm16 = false;
     if (rc) return rc;
     // one strided copy for the whole batch: rows are cut to their length by the caller's views, so the columns between a
@@ -168,13 +207,19 @@ static int decode_host_impl(q3tts_handle* h, const void* codes_host, int codes16
 }
 
 int q3tts_decode_host(q3tts_handle* h, const int64_t* codes_host, int B, int T, float* wav_host, int64_t wav_stride, int64_t* lengths,
-                      void* stream) {
-  return decode_host_impl(h, codes_host, 0, B, T, wav_host, 0, wav_stride, lengths, stream);
+                      const int64_t* skip_samples, void* stream) {
+  return decode_host_impl(h, codes_host, 0, B, T, wav_host, 0, wav_stride, lengths, skip_samples, stream);
 }
 
 int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, int T, int16_t* pcm_host, int64_t pcm_stride, int64_t* lengths,
-                            void* stream) {
-  return decode_host_impl(h, codes_host, 1, B, T, pcm_host, 1, pcm_stride, lengths, stream);
+                            const int64_t* skip_samples, void* stream) {
+  return decode_host_impl(h, codes_host, 1, B, T, pcm_host, 1, pcm_stride, lengths, skip_samples, stream);
+}
+
+int q3tts_set_check_codes(q3tts_handle* h, int on) {
+  if (!h) return Q3TTS_BAD_CONFIG;
+  h->e.check_codes = on != 0;
+  return Q3TTS_OK;
 }
 
 int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, const char* stage, float* out, int64_t capacity, int* C, int* L,
@@ -258,7 +303,9 @@ int q3tts_stream_step(q3tts_handle* h, const int32_t* stream_ids, int S, const i
   if (wav_stride < (int64_t)P * e.total_up) return e.fail(Q3TTS_BAD_SHAPE, "stream_step: wav_stride smaller than P * upsample");
   DeviceGuard g(e.device);
   const int Q = e.cfg.num_quantizers;
-  return engine_stream_step(&e, stream_ids, S, (const long long*)codes, (long long)Q * P, P, 1, P, wav, wav_stride, n_valid, (cudaStream_t)stream);
+  if (int rc = engine_stream_step(&e, stream_ids, S, (const long long*)codes, (long long)Q * P, P, 1, P, wav, wav_stride, n_valid, (cudaStream_t)stream))
+    return rc;
+  return e.check_codes ? engine_check_codes(&e, (cudaStream_t)stream) : Q3TTS_OK;  // opt-in: the check synchronises the stream
 }
 
 }  // extern "C"

@@ -176,7 +176,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait_backoff(&bars->full[s], ph);
           tc_fence_after();
           const uint32_t a = a_lo0 + (uint32_t)s * st_off, b = a + b_off;
-          if (!(p.dbg & 2)) {
+          if (!Q3_DBG(p, 2)) {
             // +2 in the >>4 address field advances 16 elements (32 bytes) along K inside the swizzle span
             mma(d_tmem, a, b, ks != 0);
             mma(d_tmem, a + 2, b + 2, 1);
@@ -275,7 +275,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * 256;
         const uint32_t slab_lo = umma_desc_lo(smem_u32(slabs + (size_t)s * slab_bytes));
-        if (!(p.dbg & 2)) {
+        if (!Q3_DBG(p, 2)) {
 #pragma unroll 4
           for (int i = 0; i < nsteps; ++i) {
             const uint32_t a = slab_lo + bars->a_tab[i], b = bars->b_tab[i];
@@ -400,7 +400,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_wait_backoff(&bars->full[s], ph);
             tc_fence_after();
             const uint32_t a = slab_lo_desc + bars->a_tab[tap], b = w_lo0 + (uint32_t)s * w_off;
-            if (!(p.dbg & 2)) {
+            if (!Q3_DBG(p, 2)) {
               mma(d_tmem, a, b, (kb | tap) != 0);
               mma(d_tmem, a + 2, b + 2, 1);
               if (k4) {
@@ -525,7 +525,7 @@ static void plan_variant(GemmOp* op, int allow) {
     if (p.tap_off[j] > hi) hi = p.tap_off[j];
   }
   const long long fixed = 1024 + (long long)epi_bytes(p) + (long long)sizeof(GemmBarriers) + 256;
-  if ((allow & 2) && !getenv("Q3TTS_NO_WS") && p.n_total == p.bn && p.ntaps >= 1 && hi == 0 && lo == -p.tap_off[0]) {
+  if ((allow & 2) && !Q3_ENV("Q3TTS_NO_WS") && p.n_total == p.bn && p.ntaps >= 1 && hi == 0 && lo == -p.tap_off[0]) {
     const int srp = (BM + lo + 15) / 16 * 16;
     const long long w_bytes = (long long)p.ntaps * p.cin * p.bn * 2;
     const long long slab = (long long)srp * p.cin * 2;
@@ -537,13 +537,13 @@ static void plan_variant(GemmOp* op, int allow) {
       return;
     }
   }
-  if ((allow & 4) && !getenv("Q3TTS_NO_SLAB") && p.ntaps >= 2) {
+  if ((allow & 4) && !Q3_ENV("Q3TTS_NO_SLAB") && p.ntaps >= 2) {
     const int srp = (BM + lo + hi + 15) / 16 * 16;
     // CTA pairs (256-row tiles, half a weight tile per SM) when a batch item's rows fill 256-row tiles well
     const int mt2 = (p.rows_valid + 2 * BM - 1) / (2 * BM);
     // ... and the tile has enough K work for the weight traffic to matter: short-K layers (the last two transposed convs) are
     // bound by their Snake epilogue and HBM, and the cross-CTA handshakes only cost them time (measured: 1.88 -> 2.03 ms, 2.97 -> 3.32 ms).
-    const bool pair = !getenv("Q3TTS_NO_PAIR") && p.bn % 32 == 0 && p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 1536;
+    const bool pair = !Q3_ENV("Q3TTS_NO_PAIR") && p.bn % 32 == 0 && p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 1536;
     const long long slab = (long long)srp * p.kb * 2, wst = (long long)(pair ? p.bn / 2 : p.bn) * p.kb * 2;
     const long long avail = (long long)g_smem_optin - fixed;
     op->pair = pair ? 1 : 0;
@@ -564,7 +564,7 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     GemmParams& q = op->p;
     q.pack_mode = 0; q.pack_rshift = 0; q.pack_cpb = 1;
     const int mt = (q.rows_valid + BM - 1) / BM;
-    if (q.act != ACT_TAIL && q.batches > 1 && q.rows_valid > 0 && !getenv("Q3TTS_NO_PACK") && q.rows_valid * 10 < mt * BM * 6) {
+    if (q.act != ACT_TAIL && q.batches > 1 && q.rows_valid > 0 && !Q3_ENV("Q3TTS_NO_PACK") && q.rows_valid * 10 < mt * BM * 6) {
       if (q.rows_valid <= 16) {
         q.pack_mode = 1;
         while ((1 << q.pack_rshift) < q.rows_valid) ++q.pack_rshift;
@@ -575,7 +575,7 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     }
     // Small-M steps: a handful of 128 x bn tiles leaves most SMs idle and each CTA walks all of K alone, so shrink the N tile
     // until the grid covers the SMs (the A panel is re-read from L2 by more CTAs, which is cheap at these sizes).
-    if (op->retile && q.act != ACT_TAIL && !getenv("Q3TTS_NO_RETILE")) {
+    if (op->retile && q.act != ACT_TAIL && !Q3_ENV("Q3TTS_NO_RETILE")) {
       const int step = q.act == ACT_GLU ? 64 : ((q.out_raw || q.out_snake || (q.res && !q.res_f32)) ? 32 : 16);
       const int mtt = gemm_m_tiles_total(q);
       // cost model (operand-load bound): waves over the SMs x bytes a CTA loads per K block
@@ -595,7 +595,7 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   }
   {
     GemmParams& q = op->p;
-    const char* ew = getenv("Q3TTS_EPI_WARPS");
+    const char* ew = Q3_ENV("Q3TTS_EPI_WARPS");
     // 12 epilogue warps (three per TMEM lane quadrant) for short-K layers whose Snake epilogue outweighs their MMAs: the transposed conv
     // 192 -> 96 2.96 -> 2.56 ms, the 1x1 convs of the C = 384 units 3.63 -> 2.85 ms (with one output slot per tensor and warp, see
     // epi_out_bufs); measured slower on the K >= 768 transposed convs, neutral on the MMA-bound conv7 layers.
@@ -640,7 +640,7 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   if (op->variant == 0) {
     // general kernel on CTA pairs: long-K GEMMs whose rows fill 256-row tiles (transformer and 1x1 conv layers in bulk decode)
     const int mt2 = (p.rows_valid + 2 * BM - 1) / (2 * BM);
-    op->pair = (!getenv("Q3TTS_NO_PAIR") && !getenv("Q3TTS_NO_PAIR_GEMM") && !p.pack_mode && p.act != ACT_TAIL && p.bn % 32 == 0 &&
+    op->pair = (!Q3_ENV("Q3TTS_NO_PAIR") && !Q3_ENV("Q3TTS_NO_PAIR_GEMM") && !p.pack_mode && p.act != ACT_TAIL && p.bn % 32 == 0 &&
                 p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 3072) ? 1 : 0;  // measured: -32 % at K = 3072, neutral or worse at K <= 1024
   }
   // the weight map follows the plan: a CTA of a pair loads half of a weight tile

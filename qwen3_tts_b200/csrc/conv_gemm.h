@@ -68,6 +68,7 @@ bool unit_xin_available(int C);
 // Fills the maps and ring sizes; returns 0 when the shape can be fused (enabled = 1), 1 when it cannot, < 0 on error.
 int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int batches, int rows);
 cudaError_t launch_unit(const UnitOp& op, cudaStream_t stream);
+int unit_setup();  // per-device shared-memory opt-in of every unit_kernel instance (engine_finalize)
 int unit_trace_read(long long* out256);
 
 // Fill the epilogue tensor maps from p (res / out_raw / out_snake / out_f32, strides, widths).
@@ -89,6 +90,10 @@ struct TailParams {
   float* out;                  // [batches][out_batch_stride] fp32, row t - tail_skip
   short* out_i16;              // when set: PCM16 instead, lrintf(clamp(v) * 32767) (what libsndfile writes for a float waveform)
   long long out_batch_stride;
+  // Voice-clone prefix cut folded into the decode (model wrapper :612-631): sample g = out_pos0 + (t - tail_skip) of item b is stored at
+  // out[b][g - item_skip[b]] and only when g >= item_skip[b], so the prefix audio is never written anywhere.  item_skip = null: no cut.
+  long long out_pos0;
+  const long long* item_skip;
 };
 struct TailOp {
   CUtensorMap tmA, tmW;
@@ -99,6 +104,7 @@ struct TailOp {
 bool tail_supported(int C);
 int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_rows, long long a_batch_stride, int C, bool bf16);
 cudaError_t launch_tail(const TailOp& op, cudaStream_t stream);
+int tail_setup();  // per-device shared-memory opt-in
 int gemm_stage_count(const GemmParams& p, bool pair = false);
 cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream);
 

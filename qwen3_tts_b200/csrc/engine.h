@@ -109,6 +109,11 @@ struct Engine {
   int total_up = 1920;
   int lookahead = 555;
   long long launches = 0;
+  // code range checking (reference: F.embedding asserts on an out-of-range index, modeling :675-678): the gather kernel raises this
+  // device flag; q3tts_decode_host always reads it (it synchronises anyway), the device-pointer entries read it when check_codes is on
+  int* d_bad_code = nullptr;
+  int* h_bad_code = nullptr;  // pinned
+  bool check_codes = false;
   bool profile = false;                 // record a CUDA event pair around every op
   std::vector<cudaEvent_t> prof_events;  // 2 per op of the last profiled run
   std::vector<int> prof_type;
@@ -146,6 +151,8 @@ struct Engine {
   short* codes16_stage = nullptr;  // device staging for int16 code frames
   size_t codes16_stage_elems = 0;
   size_t wav_stage_elems = 0;
+  long long* item_skip_stage = nullptr;  // device copy of decode_host's per-item skip_samples
+  size_t item_skip_elems = 0;
 
   // ---- streaming state (q3tts_stream_*)
   int max_slots = 0, stream_max_frames = 0, kv_ring = 128;
@@ -155,7 +162,13 @@ struct Engine {
   int* d_slot_pos = nullptr;              // [max_slots] frames decoded so far
   int* d_slot_ids = nullptr;              // [2][max_slots] staging of the step's slot ids (continuing group, fresh group)
   int* d_row_index = nullptr;             // [2][max_slots] caller row of every group member
-  int* h_stage = nullptr;                 // pinned host staging for the two arrays above
+  // pinned host staging for the two arrays above: a ring of kStageRing blocks, each guarded by an event recorded behind its
+  // H2D copies, so a step never waits for the stream (only for the copy that used the same block kStageRing steps ago)
+  static constexpr int kStageRing = 4;
+  int* h_stage = nullptr;                 // [kStageRing][4][max_slots]
+  cudaEvent_t stage_ev[kStageRing] = {nullptr, nullptr, nullptr, nullptr};
+  bool stage_used[kStageRing] = {false, false, false, false};
+  int stage_next = 0;
   std::vector<int> slot_frames;           // host mirror of d_slot_pos; -1 = closed
   uint8_t* sws = nullptr;                 // streaming workspace arena
   size_t sws_bytes = 0;
@@ -167,11 +180,15 @@ struct Engine {
 int engine_finalize(Engine* e, int mode);
 int engine_get_plan(Engine* e, int B, int T, Plan** out);
 size_t engine_plan_bytes(const Engine* e, int B, int T);
+// wav: base of the output rows; this forward's samples land at column out_pos0 - item_skip[b] (item_skip: device array or null)
 int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
-               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s);
+               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s,
+               long long out_pos0 = 0, const long long* item_skip = nullptr);
 int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
-                           long long wav_stride, int skip, cudaStream_t s);
+                           long long wav_stride, int skip, cudaStream_t s, long long out_pos0 = 0, const long long* item_skip = nullptr);
 void engine_free(Engine* e);
+// Reads and clears the bad-code flag; synchronises the stream.  Returns Q3TTS_CODE_OUT_OF_RANGE when a code was out of range.
+int engine_check_codes(Engine* e, cudaStream_t s);
 void prof_reset(Engine* e, size_t nops);
 void prof_account(Engine* e, const Op& op);
 int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);

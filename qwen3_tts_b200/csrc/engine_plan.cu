@@ -35,7 +35,7 @@ struct Builder {
     for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
     p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
     p.bias = w.bias; p.bf16 = e->bf16 ? 1 : 0;
-    { const char* d = getenv("Q3TTS_DBG"); p.dbg = d ? atoi(d) : 0; }
+    { const char* d = Q3_ENV("Q3TTS_DBG"); p.dbg = d ? atoi(d) : 0; }
     p.a_ptr = in; p.w_ptr = w.w;
     p.out_row_stride = w.n_total;
     p.out_batch_stride = (long long)rows_valid * w.n_total;
@@ -198,7 +198,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
         u.C = K.cout; u.dil = -U.conv7.tap_off[0] / 6; u.xin = 1;
         u.bias7 = U.conv7.bias; u.snake2_a = U.act2.a; u.snake2_ib = U.act2.ib;
         u.snake1_a = U.act1.a; u.snake1_ib = U.act1.ib;
-        { const char* d = getenv("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
+        { const char* d = Q3_ENV("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
         u.p.bf16 = e->bf16 ? 1 : 0; u.p.bias = U.conv1.bias; u.p.res = R[iy]; u.p.out_raw = R[ifree];
         if (j == 2) { u.p.out_snake = R[ia]; u.p.snake_a = nx.a; u.p.snake_ib = nx.ib; }
         u.p.w_ptr = U.conv7.w;
@@ -219,8 +219,8 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
         memset(&u.p, 0, sizeof(u.p));
         u.C = K.cout; u.dil = -U.conv7.tap_off[0] / 6;
         u.bias7 = U.conv7.bias; u.snake2_a = U.act2.a; u.snake2_ib = U.act2.ib;
-        { const char* d = getenv("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
-        { const char* tc = getenv("Q3TTS_TRACE_C"); if (tc && atoi(tc) != K.cout) u.p.dbg &= ~32; }  // timeline of one channel count only
+        { const char* d = Q3_ENV("Q3TTS_DBG"); u.p.dbg = d ? atoi(d) : 0; }
+        { const char* tc = Q3_ENV("Q3TTS_TRACE_C"); if (tc && atoi(tc) != K.cout) u.p.dbg &= ~32; }  // timeline of one channel count only
         u.p.bf16 = e->bf16 ? 1 : 0; u.p.bias = U.conv1.bias; u.p.res = R[iy]; u.p.out_raw = R[iy]; u.p.out_snake = R[ifree];
         u.p.snake_a = nx.a; u.p.snake_ib = nx.ib;
         u.p.w_ptr = U.conv7.w;
@@ -355,11 +355,12 @@ void prof_account(Engine* e, const Op& op) {
 }
 
 int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long long sk, long long st, float* wav, long long wav_stride,
-               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s) {
+               int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s,
+               long long out_pos0, const long long* item_skip) {
   const q3tts_config& c = e->cfg;
   size_t pi = 0;
-  static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
-  static const bool keep_raw = getenv("Q3TTS_KEEP_RAW") != nullptr;  // debug / A-B: store the dead raw outputs too
+  static const bool sync_each = Q3_ENV("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
+  static const bool keep_raw = Q3_ENV("Q3TTS_KEEP_RAW") != nullptr;  // debug / A-B: store the dead raw outputs too
   if (e->profile) prof_reset(e, plan->ops.size());
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
@@ -371,7 +372,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
     else if (op.type == OP_GEMM && drop) op.g.p.out_raw = nullptr;
     switch (op.type) {
       case OP_RVQ:
-        err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s);
+        err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s, 0, nullptr, e->d_bad_code);
         break;
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
@@ -385,11 +386,12 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
           if (op.t.enabled && e->engine == ENGINE_TC) {
             op.t.p.out = e->out_pcm16 ? nullptr : wav; op.t.p.out_i16 = e->out_pcm16 ? reinterpret_cast<short*>(wav) : nullptr;
             op.t.p.out_batch_stride = wav_stride; op.t.p.tail_skip = skip;
+            op.t.p.out_pos0 = out_pos0; op.t.p.item_skip = item_skip;
             err = launch_tail(op.t, s);
-          } else if (e->out_pcm16) {
-            err = cudaErrorNotSupported;  // PCM16 output exists in the taps-as-N output conv only
+          } else if (e->out_pcm16 || item_skip) {
+            err = cudaErrorNotSupported;  // PCM16 output and the per-item prefix cut exist in the taps-as-N output conv only
           } else {
-            op.g.p.out_f32 = wav; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
+            op.g.p.out_f32 = wav + out_pos0; op.g.p.out_batch_stride = wav_stride; op.g.p.tail_skip = skip;
             err = launch_conv_gemm(op.g, e->engine, s);
           }
         }
@@ -420,7 +422,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
 
 // forward over B items, split along the batch so that no launch exceeds the reserved frame budget
 int engine_forward_batched(Engine* e, const long long* codes, long long sb, long long sk, long long st, int B, int T, float* wav,
-                           long long wav_stride, int skip, cudaStream_t s) {
+                           long long wav_stride, int skip, cudaStream_t s, long long out_pos0, const long long* item_skip) {
   if (T > e->rope_max) return e->fail(Q3TTS_BAD_SHAPE, "T exceeds max_position_embeddings");
   int per = e->max_frames / (T > 0 ? T : 1);
   if (per < 1) per = 1;
@@ -431,10 +433,20 @@ int engine_forward_batched(Engine* e, const long long* codes, long long sb, long
     if (rc) return rc;
     // PCM16 output: `wav` is an int16 buffer, offsets are in its elements
     float* dst = e->out_pcm16 ? reinterpret_cast<float*>(reinterpret_cast<short*>(wav) + (long long)b0 * wav_stride) : wav + (long long)b0 * wav_stride;
-    rc = engine_run(e, plan, codes + b0 * sb, sb, sk, st, dst, wav_stride, skip, nullptr, nullptr, 0, nullptr, nullptr, s);
+    rc = engine_run(e, plan, codes + b0 * sb, sb, sk, st, dst, wav_stride, skip, nullptr, nullptr, 0, nullptr, nullptr, s, out_pos0,
+                    item_skip ? item_skip + b0 : nullptr);
     if (rc) return rc;
   }
   return Q3TTS_OK;
+}
+
+int engine_check_codes(Engine* e, cudaStream_t s) {
+  if (!e->d_bad_code || !e->h_bad_code) return Q3TTS_OK;
+  if (cudaMemcpyAsync(e->h_bad_code, e->d_bad_code, sizeof(int), cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess)
+    return e->fail(Q3TTS_CUDA_ERROR, std::string("code range check failed: ") + cudaGetErrorString(cudaGetLastError()));
+  if (*e->h_bad_code == 0) return Q3TTS_OK;
+  cudaMemsetAsync(e->d_bad_code, 0, sizeof(int), s);
+  return e->fail(Q3TTS_CODE_OUT_OF_RANGE, "a code index is outside [0, codebook_size): the reference's F.embedding would raise here (modeling :675-678)");
 }
 
 void engine_free(Engine* e) {
@@ -446,6 +458,9 @@ void engine_free(Engine* e) {
   if (e->codes_stage) cudaFree(e->codes_stage);
   if (e->wav_stage) cudaFree(e->wav_stage);
   if (e->codes16_stage) cudaFree(e->codes16_stage);
+  if (e->item_skip_stage) cudaFree(e->item_skip_stage);
+  if (e->d_bad_code) cudaFree(e->d_bad_code);
+  if (e->h_bad_code) cudaFreeHost(e->h_bad_code);
 }
 
 }  // namespace q3

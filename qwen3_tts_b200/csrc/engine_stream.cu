@@ -277,7 +277,7 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
 // Runs the plan's launches directly, or as one CUDA graph once the same caller pointers have been seen twice in a row.
 int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long long sb, long long sk, long long st, const int* d_ids, const int* d_rows,
                     bool identity_rows, float* wav, long long wav_stride, cudaStream_t s) {
-  static const bool graphs_off = getenv("Q3TTS_STREAM_GRAPH") == nullptr || getenv("Q3TTS_NO_GRAPH") != nullptr || getenv("Q3TTS_SYNC") != nullptr;
+  static const bool graphs_off = Q3_ENV("Q3TTS_STREAM_GRAPH") == nullptr || Q3_ENV("Q3TTS_NO_GRAPH") != nullptr || Q3_ENV("Q3TTS_SYNC") != nullptr;
   if (graphs_off || plan->graph_off || e->profile) return launch_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity_rows, wav, wav_stride, s);
   StreamPlan::GraphEntry key;
   key.codes = codes; key.sb = sb; key.sk = sk; key.st = st; key.wav = wav; key.stride = wav_stride; key.identity = identity_rows;
@@ -320,7 +320,7 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
   const q3tts_config& c = e->cfg;
   float* tail_out = identity_rows ? wav : plan->wav_tmp;
   const long long tail_stride = identity_rows ? wav_stride : plan->out_len;
-  static const bool sync_each = getenv("Q3TTS_SYNC") != nullptr;  // debugging: attribute an asynchronous fault to its op
+  static const bool sync_each = Q3_ENV("Q3TTS_SYNC") != nullptr;  // debugging: attribute an asynchronous fault to its op
   size_t pi = 0;
   if (e->profile) prof_reset(e, plan->ops.size());  // the profile holds the last plan that ran
   for (Op& op : plan->ops) {
@@ -336,7 +336,7 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
       case OP_POS_ADVANCE: err = stream_advance_pos(e->d_slot_pos, d_ids, plan->S, plan->P, s); break;
       case OP_RVQ:
         err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s,
-                         op.aux0, identity_rows ? nullptr : d_rows);
+                         op.aux0, identity_rows ? nullptr : d_rows, e->d_bad_code);
         break;
       case OP_GEMM: err = launch_conv_gemm(op.g, ENGINE_TC, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
@@ -405,7 +405,12 @@ int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step) {
   ok = ok && cudaMemset(e->d_slot_pos, 0, (size_t)max_streams * sizeof(int)) == cudaSuccess;
   ok = ok && cudaMalloc((void**)&e->d_slot_ids, (size_t)2 * max_streams * sizeof(int)) == cudaSuccess;
   ok = ok && cudaMalloc((void**)&e->d_row_index, (size_t)2 * max_streams * sizeof(int)) == cudaSuccess;
-  ok = ok && cudaMallocHost((void**)&e->h_stage, (size_t)4 * max_streams * sizeof(int)) == cudaSuccess;
+  ok = ok && cudaMallocHost((void**)&e->h_stage, (size_t)Engine::kStageRing * 4 * max_streams * sizeof(int)) == cudaSuccess;
+  for (int i = 0; i < Engine::kStageRing && ok; ++i) {
+    ok = cudaEventCreateWithFlags(&e->stage_ev[i], cudaEventDisableTiming) == cudaSuccess;
+    e->stage_used[i] = false;
+  }
+  e->stage_next = 0;
   if (!ok) {
     cudaGetLastError();
     engine_stream_free(e);
@@ -425,6 +430,10 @@ void engine_stream_free(Engine* e) {
   if (e->d_slot_ids) cudaFree(e->d_slot_ids);
   if (e->d_row_index) cudaFree(e->d_row_index);
   if (e->h_stage) cudaFreeHost(e->h_stage);
+  for (int i = 0; i < Engine::kStageRing; ++i) {
+    if (e->stage_ev[i]) cudaEventDestroy(e->stage_ev[i]);
+    e->stage_ev[i] = nullptr; e->stage_used[i] = false;
+  }
   if (e->sws) cudaFree(e->sws);
   e->stream_state = nullptr; e->kcache.clear(); e->vcache.clear(); e->d_slot_pos = nullptr; e->d_slot_ids = nullptr; e->d_row_index = nullptr;
   e->h_stage = nullptr; e->sws = nullptr; e->sws_bytes = 0; e->splans.clear(); e->slot_frames.clear(); e->max_slots = 0;
@@ -436,11 +445,14 @@ int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long l
   if (!e->max_slots) return e->fail(Q3TTS_BAD_STREAM, "stream_step: call q3tts_stream_reserve first");
   if (S < 1 || S > e->max_slots || P < 1 || P > e->stream_max_frames) return e->fail(Q3TTS_BAD_SHAPE, "stream_step: S or P outside the reserved range");
   const int ms = e->max_slots;
-  int* h_ids[2] = {e->h_stage, e->h_stage + ms};
-  int* h_rows[2] = {e->h_stage + 2 * ms, e->h_stage + 3 * ms};
+  // this step's block of the pinned staging ring; the only wait is for the copies that used it kStageRing steps ago
+  const int blk = e->stage_next;
+  if (e->stage_used[blk] && cudaEventSynchronize(e->stage_ev[blk]) != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, "stream_step: stream error");
+  int* hb = e->h_stage + (size_t)blk * 4 * ms;
+  int* h_ids[2] = {hb, hb + ms};
+  int* h_rows[2] = {hb + 2 * ms, hb + 3 * ms};
   int n[2] = {0, 0};
-  // the pinned staging block may still be read by the previous step's copies
-  if (cudaStreamSynchronize(s) != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, "stream_step: stream error");
+  // ---- validate everything and build both plans BEFORE anything is launched or any bookkeeping advances
   for (int i = 0; i < S; ++i) {
     const int id = stream_ids[i];
     if (id < 0 || id >= ms || e->slot_frames[id] < 0) return e->fail(Q3TTS_BAD_STREAM, "stream_step: unknown or closed stream id " + std::to_string(id));
@@ -449,17 +461,27 @@ int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long l
     const int g = e->slot_frames[id] == 0 ? 1 : 0;  // group 1 = fresh
     h_ids[g][n[g]] = id; h_rows[g][n[g]] = i; ++n[g];
   }
+  StreamPlan* plans[2] = {nullptr, nullptr};
+  for (int g = 0; g < 2; ++g)
+    if (n[g])
+      if (int rc = get_stream_plan(e, n[g], P, g == 1, &plans[g])) return rc;
+  // ---- upload the ids (the two groups' id / row arrays are adjacent: two copies per step), then launch
+  int* d_ids[2] = {e->d_slot_ids, e->d_slot_ids + ms};
+  int* d_rows[2] = {e->d_row_index, e->d_row_index + ms};
+  bool up_ok = true;
+  for (int g = 0; g < 2 && up_ok; ++g) {
+    if (!n[g]) continue;
+    up_ok = cudaMemcpyAsync(d_ids[g], h_ids[g], n[g] * sizeof(int), cudaMemcpyHostToDevice, s) == cudaSuccess &&
+            cudaMemcpyAsync(d_rows[g], h_rows[g], n[g] * sizeof(int), cudaMemcpyHostToDevice, s) == cudaSuccess;
+  }
+  if (!up_ok || cudaEventRecord(e->stage_ev[blk], s) != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, "stream_step: id upload failed");
+  e->stage_used[blk] = true;
+  e->stage_next = (blk + 1) % Engine::kStageRing;
   for (int g = 0; g < 2; ++g) {
     if (!n[g]) continue;
-    int* d_ids = e->d_slot_ids + g * ms;
-    int* d_rows = e->d_row_index + g * ms;
-    if (cudaMemcpyAsync(d_ids, h_ids[g], n[g] * sizeof(int), cudaMemcpyHostToDevice, s) != cudaSuccess ||
-        cudaMemcpyAsync(d_rows, h_rows[g], n[g] * sizeof(int), cudaMemcpyHostToDevice, s) != cudaSuccess)
-      return e->fail(Q3TTS_CUDA_ERROR, "stream_step: id upload failed");
-    StreamPlan* plan = nullptr;
-    if (int rc = get_stream_plan(e, n[g], P, g == 1, &plan)) return rc;
+    StreamPlan* plan = plans[g];
     const bool identity = n[g] == S;  // one group holds every row, in order
-    if (int rc = run_stream_plan(e, plan, codes, sb, sk, st, d_ids, d_rows, identity, wav, wav_stride, s)) return rc;
+    if (int rc = run_stream_plan(e, plan, codes, sb, sk, st, d_ids[g], d_rows[g], identity, wav, wav_stride, s)) return rc;
     for (int k = 0; k < n[g]; ++k) {
       if (n_valid) n_valid[h_rows[g][k]] = plan->out_len;
       e->slot_frames[h_ids[g][k]] += P;

@@ -123,8 +123,22 @@ int engine_finalize(Engine* e, int mode) {
   e->plans.clear();
   e->finalized = false;
   e->bf16 = (mode == Q3TTS_MODE_BF16);
+  // kernel attributes (shared-memory opt-ins) are per device: set them for THIS handle's device every time, so a second handle on
+  // another GPU of the same process launches with the same limits as the first
   if (gemm_setup(e->device)) return e->fail(Q3TTS_CUDA_ERROR, "gemm_setup failed (cuTensorMapEncodeTiled unavailable or smem opt-in rejected)");
+  if (unit_setup() || tail_setup() || attention_setup() != cudaSuccess || stream_attention_setup() != cudaSuccess) {
+    cudaGetLastError();
+    return e->fail(Q3TTS_CUDA_ERROR, "kernel shared-memory opt-in rejected");
+  }
 
+  if (!e->d_bad_code) {
+    if (cudaMalloc((void**)&e->d_bad_code, sizeof(int)) != cudaSuccess || cudaMemset(e->d_bad_code, 0, sizeof(int)) != cudaSuccess ||
+        cudaMallocHost((void**)&e->h_bad_code, sizeof(int)) != cudaSuccess) {
+      cudaGetLastError();
+      return e->fail(Q3TTS_OOM, "finalize: code-check flag allocation failed");
+    }
+    *e->h_bad_code = 0;
+  }
   Fin f{e};
   const int H = c.hidden_size, Lat = c.latent_dim, I = c.intermediate_size, D = c.codebook_dim, dq = D / 2, Q = c.num_quantizers;
   // ---- RVQ: fold output_proj into the codebooks (fp32)

@@ -19,6 +19,8 @@
 #pragma once
 #include <stdint.h>
 
+#include "debug_env.h"
+
 namespace q3 {
 
 enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3 };

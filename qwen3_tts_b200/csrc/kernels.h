@@ -27,7 +27,8 @@ cudaError_t fold_codebook(const float* embedding_sum, const float* cluster_usage
 // int16 code frames (packed codes on the wire) -> the int64 layout the gather kernel reads
 cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaStream_t s);
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
-                       int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows = 0, const int* src_index = nullptr);
+                       int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows = 0, const int* src_index = nullptr,
+                       int* bad_code = nullptr);  // bad_code (device int, optional): set to 1 when a code is outside [0, ncodes)
 // x fp32 [M][H] -> 16-bit [M][H]: w * x * rsqrt(mean(x^2) + eps)
 cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s);
 // rope table [maxT][hd/2] cos, sin (fp32)
@@ -38,10 +39,9 @@ cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* 
 // ConvNeXt front half: depthwise causal conv k=7 + bias, LayerNorm(eps) over C.  x,out 16-bit [B][L][C]; dw weight [7][C] fp32.
 cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
                              float eps, bool bf16, cudaStream_t s, int in_bs_rows = 0, int hist = 0);
-// tail: x 16-bit [B][L][C] (already Snake'd), w [7][C] fp32, bias -> clamp(conv, -1, 1); sample l >= skip is written to
-// out[b*out_batch_stride + l - skip] (skip drops a chunk's left-context samples, reference modeling :893)
-cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* out, long long out_batch_stride, int B, int L, int C, int skip,
-                            bool bf16, cudaStream_t s);
+// per-device opt-in to > 48 KB dynamic shared memory for the attention kernels (called once per handle by engine_finalize)
+cudaError_t attention_setup();
+cudaError_t stream_attention_setup();
 // ---- streaming (stateful per-packet decode; no counterpart in the reference, oracle = Decoder.forward on the whole sequence)
 // qkv 16-bit [S*P][3*nh*hd] of the P new tokens of S streams; K (RoPE applied) and V are appended to the per-slot ring caches
 // kc / vc [slots][ring][nh*hd] at (pos & (ring-1)); query i of stream s sits at absolute position slot_pos[slot_ids[s]] + i and sees

@@ -24,7 +24,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 template <typename T>
 __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long long sk, long long st, const float* __restrict__ tables,
                       T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D, int out_bs_rows,
-                      const int* __restrict__ src_index) {
+                      const int* __restrict__ src_index, int* __restrict__ bad_code) {
   const int t = blockIdx.x, b = blockIdx.y;
   const int bs = src_index ? src_index[b] : b;  // row of the caller's codes tensor this batch item reads
   const int d = threadIdx.x * 4;
@@ -32,7 +32,12 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
   float4 first = make_float4(0.f, 0.f, 0.f, 0.f), rest = first;
   for (int k = 0; k < Q; ++k) {
     long long c = codes[bs * sb + k * sk + t * st];
-    c = c < 0 ? 0 : (c >= ncodes ? ncodes - 1 : c);  // never fault on a bad code; range errors are reported by the checked entry
+    if (c < 0 || c >= ncodes) {
+      // never fault on a bad code (the reference's F.embedding would assert, modeling :675-678): decode a clamped index and raise the
+      // handle's device-side flag, which the checked entries (q3tts_set_check_codes, q3tts_decode_host) turn into Q3TTS_CODE_OUT_OF_RANGE
+      if (bad_code && threadIdx.x == 0) atomicMax(bad_code, 1);
+      c = c < 0 ? 0 : ncodes - 1;
+    }
     const float4 e = __ldg(reinterpret_cast<const float4*>(tables + ((long long)k * ncodes + c) * D + d));
     if (k == 0) first = e;
     else { rest.x += e.x; rest.y += e.y; rest.z += e.z; rest.w += e.w; }
@@ -50,12 +55,12 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
   }
 }
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
-                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows, const int* src_index) {
+                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows, const int* src_index, int* bad_code) {
   if (B <= 0 || Tn <= 0) return cudaSuccess;
   if (out_bs_rows <= 0) out_bs_rows = Tn;
   dim3 grid(Tn, B);
   const int threads = ((D / 4 + 31) / 32) * 32;
-  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index)));
+  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index, bad_code)));
   return cudaGetLastError();
 }
 
@@ -185,18 +190,18 @@ k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const fl
     attn_warp16<T>(sQ + warp * 16 * AM_PITCH, sK, sV, tq0, nq, kbase, window, out + ((long long)b * Tn + tq0) * (nh * AM_HD) + h * AM_HD,
                    (long long)nh * AM_HD);
 }
+static constexpr size_t ATT_SMEM = (size_t)(2 * ATT_ROWS + ATT_QT) * AM_PITCH * 2;
+// > 48 KB of dynamic shared memory: opt in per device (called from engine_finalize for the handle's device)
+cudaError_t attention_setup() {
+  cudaError_t e = cudaFuncSetAttribute(k_attention<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATT_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_attention<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATT_SMEM);
+  return e;
+}
 cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* sin_t, void* out, int B, int Tn, int nh, int hd, int window,
                               bool bf16, cudaStream_t s) {
   if (hd != AM_HD || window < 1 || window > 72) return cudaErrorInvalidValue;  // AM_MAXCH chunks cover a window of at most 72
   if (B <= 0 || Tn <= 0) return cudaSuccess;
-  const size_t smem = (size_t)(2 * ATT_ROWS + ATT_QT) * AM_PITCH * 2;
-  static bool attr_done[2] = {false, false};
-  if (!attr_done[bf16 ? 1 : 0]) {
-    cudaError_t e;
-    Q3_DISPATCH(bf16, (e = cudaFuncSetAttribute(k_attention<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
-    if (e != cudaSuccess) return e;
-    attr_done[bf16 ? 1 : 0] = true;
-  }
+  const size_t smem = ATT_SMEM;
   dim3 grid((Tn + ATT_QT - 1) / ATT_QT, nh, B);
   Q3_DISPATCH(bf16, (k_attention<T><<<grid, 128, smem, s>>>((const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
   return cudaGetLastError();

@@ -1,4 +1,4 @@
-// ConvNeXt depthwise conv + LayerNorm, tail 96->1 conv + clamp, layout probes.
+// ConvNeXt depthwise conv + LayerNorm, layout probes.
 #include "kernels.h"
 #include "ptx.cuh"
 
@@ -80,60 +80,6 @@ cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, 
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)((rows + 7) / 8);
   Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
-  return cudaGetLastError();
-}
-
-// ============================================================================================ tail conv
-// decoder[6]: Conv1d(C -> 1, k=7) on the Snake'd activation, then clamp(-1, 1) (modeling :862, :883).
-// Block = 256 consecutive samples of one batch item; the (256+6) x C input slab sits in shared
-// memory with an odd word pitch so lane-per-sample reads are conflict free.
-static constexpr int TAIL_TILE = 256;
-template <typename T>
-__global__ void __launch_bounds__(TAIL_TILE)
-k_tail(const T* __restrict__ x, const float* __restrict__ w, float bias, float* __restrict__ out, long long obs, int L, int C, int skip) {
-  extern __shared__ __align__(16) uint8_t tail_smem[];
-  const int cw = C / 2;        // 32-bit words per row
-  const int pitch = cw | 1;    // odd
-  uint32_t* sx = reinterpret_cast<uint32_t*>(tail_smem);
-  float* sw = reinterpret_cast<float*>(sx + (size_t)(TAIL_TILE + 6) * pitch);
-  const int b = blockIdx.y;
-  const int l0 = blockIdx.x * TAIL_TILE;
-  const uint32_t* xb = reinterpret_cast<const uint32_t*>(x + (long long)b * L * C);
-  for (int i = threadIdx.x; i < (TAIL_TILE + 6) * cw; i += blockDim.x) {
-    const int r = i / cw, c = i % cw;
-    const int lt = l0 - 6 + r;
-    sx[r * pitch + c] = (lt >= 0 && lt < L) ? xb[(long long)lt * cw + c] : 0u;
-  }
-  for (int i = threadIdx.x; i < 7 * C; i += blockDim.x) sw[i] = w[i];
-  __syncthreads();
-  const int l = l0 + threadIdx.x;
-  if (l >= L || l < skip) return;
-  float acc = bias;
-  for (int j = 0; j < 7; ++j) {
-    const uint32_t* xr = sx + (threadIdx.x + j) * pitch;
-    const float* wr = sw + j * C;
-    for (int c = 0; c < cw; ++c) {
-      const float2 v = Elem<T>::unpack2(xr[c]);
-      acc = fmaf(v.x, wr[2 * c], acc);
-      acc = fmaf(v.y, wr[2 * c + 1], acc);
-    }
-  }
-  out[(long long)b * obs + (l - skip)] = fminf(1.0f, fmaxf(-1.0f, acc));
-}
-cudaError_t tail_conv_clamp(const void* x, const float* w, float bias, float* out, long long obs, int B, int L, int C, int skip, bool bf16,
-                            cudaStream_t s) {
-  if (B <= 0 || L <= 0) return cudaSuccess;
-  const int pitch = (C / 2) | 1;
-  const size_t smem = (size_t)(TAIL_TILE + 6) * pitch * 4 + (size_t)7 * C * 4;
-  dim3 grid((L + TAIL_TILE - 1) / TAIL_TILE, B);
-  static bool attr_done = false;
-  if (!attr_done) {  // the slab exceeds the 48 KB default for C = 96
-    cudaFuncSetAttribute(k_tail<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    cudaFuncSetAttribute(k_tail<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    attr_done = true;
-  }
-  if (smem > 160 * 1024) return cudaErrorInvalidValue;
-  Q3_DISPATCH(bf16, (k_tail<T><<<grid, TAIL_TILE, smem, s>>>((const T*)x, w, bias, out, obs, L, C, skip)));
   return cudaGetLastError();
 }
 

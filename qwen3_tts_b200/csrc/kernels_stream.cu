@@ -107,19 +107,21 @@ k_stream_attention(const T* __restrict__ qkv, T* __restrict__ kc, T* __restrict_
                    out + ((long long)s * P + warp * 16) * H + h * AM_HD, (long long)H);
 }
 
+// shared memory of the largest step (P = 64 new frames): opted in per device by stream_attention_setup (engine_finalize)
+static constexpr int SA_KROWS_MAX = ((72 - 1 + SA_WARPS * 16 - 1 + 15) | 15) + 1;
+static constexpr size_t SA_SMEM_MAX = (size_t)(2 * SA_KROWS_MAX + SA_WARPS * 16) * AM_PITCH * 2;
+cudaError_t stream_attention_setup() {
+  cudaError_t e = cudaFuncSetAttribute(k_stream_attention<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SA_SMEM_MAX);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_stream_attention<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SA_SMEM_MAX);
+  return e;
+}
 cudaError_t stream_attention(const void* qkv, void* kc, void* vc, const int* slot_ids, const int* slot_pos, const float* cos_t, const float* sin_t,
                              int rope_max, float theta, void* out, int S, int P, int nh, int hd, int window, int ring, bool bf16, cudaStream_t s) {
   if (hd != AM_HD || (ring & (ring - 1)) || ring < window - 1 + P || window < 1 || window > 72 || P > SA_WARPS * 16) return cudaErrorInvalidValue;
   if (S <= 0 || P <= 0) return cudaSuccess;
   const int krows = ((window - 1 + P - 1 + 15) | 15) + 1;  // key rows at most: alignment slack + (window - 1) older keys + P new ones
   const size_t smem = (size_t)(2 * krows + ((P + 15) & ~15)) * AM_PITCH * 2;
-  static size_t attr_smem[2] = {0, 0};
-  if (smem > 48 * 1024 && smem > attr_smem[bf16 ? 1 : 0]) {
-    cudaError_t e;
-    Q3_DISPATCH(bf16, (e = cudaFuncSetAttribute(k_stream_attention<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)));
-    if (e != cudaSuccess) return e;
-    attr_smem[bf16 ? 1 : 0] = smem;
-  }
+  if (smem > SA_SMEM_MAX) return cudaErrorInvalidValue;
   dim3 grid(nh, S);
   Q3_DISPATCH(bf16, (k_stream_attention<T><<<grid, SA_WARPS * 32, smem, s>>>((const T*)qkv, (T*)kc, (T*)vc, slot_ids, slot_pos, cos_t, sin_t, rope_max, theta,
                                                                                (T*)out, P, nh, window, ring, krows)));

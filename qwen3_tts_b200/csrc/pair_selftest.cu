@@ -9,6 +9,7 @@
 #include <cuda_fp16.h>
 
 #include "../../include/q3tts_decode.h"
+#include "../../include/q3tts_debug.h"
 #include "conv_gemm.h"
 #include "pair_ptx.cuh"
 

@@ -5,7 +5,9 @@
 #include <vector>
 
 #include "../../include/q3tts_decode.h"
+#include "../../include/q3tts_debug.h"
 #include "conv_gemm.h"
+#include "epilogue.cuh"
 #include "ptx.cuh"
 
 using namespace q3;
@@ -201,7 +203,7 @@ int run_unit_selftest(int rows, int C, int dil, float* out4) {
 extern "C" int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4) {
   if (rows < 1 || channels < 32 || dilation < 1 || !out4) return Q3TTS_BAD_SHAPE;
   if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
-  if (gemm_setup(device)) return Q3TTS_CUDA_ERROR;
+  if (gemm_setup(device) || unit_setup()) return Q3TTS_CUDA_ERROR;
   return bf16 ? run_unit_selftest<__nv_bfloat16>(rows, channels, dilation, out4) : run_unit_selftest<__half>(rows, channels, dilation, out4);
 }
 
@@ -285,6 +287,26 @@ extern "C" int q3tts_bench_tma(int device, int C, int box_cols, int box_rows, in
   }
   cudaFree(buf);
   return rc;
+}
+
+// SnakeBeta as every epilogue evaluates it (epilogue.cuh snake(): cosine form on MUFU.COS) on n caller-supplied points:
+// out[i] = snake(x[i], a2, h).  The test compares with x + (1/(exp(beta)+1e-9)) sin^2(x exp(alpha)) in float64 for |x a2| up to 1e3.
+namespace {
+__global__ void k_snake_probe(const float* __restrict__ x, float a2, float h, float* __restrict__ out, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = q3::snake(x[i], a2, h);
+}
+}  // namespace
+extern "C" int q3tts_selftest_snake(int device, const float* x_host, int n, float a2, float h, float* out_host) {
+  if (!x_host || !out_host || n < 1) return Q3TTS_BAD_SHAPE;
+  if (cudaSetDevice(device) != cudaSuccess) return Q3TTS_CUDA_ERROR;
+  float *dx = nullptr, *dy = nullptr;
+  if (cudaMalloc((void**)&dx, (size_t)n * 4) != cudaSuccess || cudaMalloc((void**)&dy, (size_t)n * 4) != cudaSuccess) { cudaFree(dx); return Q3TTS_OOM; }
+  cudaMemcpy(dx, x_host, (size_t)n * 4, cudaMemcpyHostToDevice);
+  k_snake_probe<<<(n + 255) / 256, 256>>>(dx, a2, h, dy, n);
+  const cudaError_t e = cudaMemcpy(out_host, dy, (size_t)n * 4, cudaMemcpyDeviceToHost);
+  cudaFree(dx); cudaFree(dy);
+  return e == cudaSuccess ? Q3TTS_OK : Q3TTS_CUDA_ERROR;
 }
 
 extern "C" int q3tts_unit_trace(long long* out256) { return unit_trace_read(out256); }

@@ -102,6 +102,7 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int b = tile / tiles_per_item, t0 = (tile - b * tiles_per_item) * T_OUT;
       const int a = it & (T_NACC - 1);
+      const long long cut = p.item_skip ? __ldg(p.item_skip + b) : 0;
       mbar_wait(&bars->acc_full[a], (uint32_t)(it / T_NACC) & 1u);
       tc_fence_after();
       uint32_t r[16];
@@ -120,9 +121,10 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 7; ++j) v += P[j * T_PPITCH + i + j];
         const int t = t0 + i;
-        if (t < p.rows_valid && t >= p.tail_skip) {
+        const long long g = p.out_pos0 + (t - p.tail_skip);  // position in the item's whole (chunk-concatenated) waveform
+        if (t < p.rows_valid && t >= p.tail_skip && g >= cut) {
           const float c = fminf(1.0f, fmaxf(-1.0f, v));
-          const long long o = (long long)b * p.out_batch_stride + (t - p.tail_skip);
+          const long long o = (long long)b * p.out_batch_stride + (g - cut);
           if (p.out_i16) p.out_i16[o] = (short)__float2int_rn(c * 32767.0f);
           else p.out[o] = c;
         }
@@ -138,7 +140,7 @@ static size_t tail_smem(int C, int nstages) {
   return 8 * 1024 + (size_t)nstages * (C / 32) * T_ROWS * 64 + (size_t)2 * 7 * T_PPITCH * sizeof(float) + sizeof(TailBarriers) + 1024;
 }
 
-bool tail_supported(int C) { return C % 32 == 0 && C >= 32 && C <= 256 && !getenv("Q3TTS_OLD_TAIL"); }
+bool tail_supported(int C) { return C % 32 == 0 && C >= 32 && C <= 256 && !Q3_ENV("Q3TTS_OLD_TAIL"); }
 
 // a: [batches][a_rows][C] 16-bit (a_batch_stride elements between items, 0 = dense); w16: [16][C] 16-bit, rows 0..6 = taps, rest zero
 int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_rows, long long a_batch_stride, int C, bool bf16) {
@@ -152,15 +154,15 @@ int tail_make(TailOp* op, const void* a, const void* w16, int batches, int a_row
                                 a_batch_stride ? (uint64_t)a_batch_stride : (uint64_t)a_rows * C, 32, T_ROWS);
   rc |= make_tmap_3d(&op->tmW, w16, (uint64_t)C, 16, 1, 32, 16, bf16);
   if (rc) return -1;
-  static bool attr_done = false;
-  if (!attr_done) {
-    if (cudaFuncSetAttribute(tail_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess ||
-        cudaFuncSetAttribute(tail_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess)
-      return -2;
-    attr_done = true;
-  }
-  op->p.C = C; op->p.bf16 = bf16 ? 1 : 0; op->p.batches = batches; op->p.out = nullptr; op->p.out_i16 = nullptr;
+  op->p.C = C; op->p.bf16 = bf16 ? 1 : 0; op->p.batches = batches; op->p.out = nullptr; op->p.out_i16 = nullptr; op->p.out_pos0 = 0; op->p.item_skip = nullptr;
   op->enabled = 1;
+  return 0;
+}
+
+int tail_setup() {  // per device (see unit_setup)
+  if (cudaFuncSetAttribute(tail_conv_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess ||
+      cudaFuncSetAttribute(tail_conv_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm_smem_optin()) != cudaSuccess)
+    return -2;
   return 0;
 }
 

@@ -69,7 +69,7 @@ struct EpiWarp {
   __device__ EpiWarp(const GemmParams& p_, const CUtensorMap* r, const CUtensorMap* a, const CUtensorMap* s, const CUtensorMap* f,
                      uint8_t* eb_, uint64_t* rbar_, TileSched ts_, int lane_, int quad_, int half_, int nsplit_)
       : p(p_), tmRes(r), tmRaw(a), tmSnake(s), tmF32(f), eb(eb_), rbar(rbar_), ts(ts_), lane(lane_), quad(quad_), half(half_), nsplit(nsplit_) {
-    has_res = p.res != nullptr && !(p.dbg & 8);
+    has_res = p.res != nullptr && !Q3_DBG(p, 8);
     rf32 = p.res_f32 != 0;
     glu = p.act == ACT_GLU;
     tail = p.act == ACT_TAIL;
@@ -118,7 +118,7 @@ struct EpiWarp {
   }
 
   __device__ __forceinline__ void start() {
-    if (has_res && !(p.dbg & 1)) {
+    if (has_res && !Q3_DBG(p, 1)) {
       pf_it = 0;
       pf_item = first_item(0);
       for (int i = 0; i < rd; ++i) prefetch_one();
@@ -210,7 +210,7 @@ struct EpiWarp {
     math_unit(va, rsa, c0);
     math_unit(vb, rsb, c0 + 16);
     const uint32_t sl = ob & (uint32_t)(obufs - 1);
-    const bool st = !(p.dbg & 4);
+    const bool st = !Q3_DBG(p, 4);
     if (st) {
       if (lane == 0) { if (obufs == 1) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
       __syncwarp();
@@ -259,7 +259,7 @@ struct EpiWarp {
       } else {
         load_res16(rbuf, 0, rs);  // a 16-bit residual box of 16 columns sits in chunks 0..1
       }
-      if ((p.dbg & 512) && rf32) {  // debug: residual straight from global memory (race localisation)
+      if (Q3_DBG(p, 512) && rf32) {  // debug: residual straight from global memory (race localisation)
         const int row = row0 + lane;
         if (row < p.rows_valid) {
           const float4* g = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.res) + (long long)b * p.out_batch_stride +
@@ -285,7 +285,7 @@ struct EpiWarp {
       return;
     }
     math_unit(v, rs, c0);
-    if (of32 && (p.dbg & 1024)) {  // debug: output straight to global memory (race localisation)
+    if (of32 && Q3_DBG(p, 1024)) {  // debug: output straight to global memory (race localisation)
       const int row = row0 + lane;
       if (row < p.rows_valid) {
         float4* g = reinterpret_cast<float4*>(p.out_f32 + (long long)b * p.out_batch_stride + (long long)row * p.out_row_stride + n0);
@@ -351,7 +351,7 @@ struct EpiWarp {
     int row0 = (mt * mt_mul + mt_add) * 128 + quad * 32;
     if (wraps) tile_c0 = (nt * p.bn) % p.ncol_mod;
     if (p.pack_mode) gemm_chunk_coords(p, b, quad, row0, b);  // packed tiles: the scheduler's "batch" is the tile index
-    if (p.dbg & 1) {
+    if (Q3_DBG(p, 1)) {
       uint32_t r[16];
       for (int u = half; u < units; u += nsplit) { tmem_ld16(t0 + u * 16, r); tmem_ld_wait(); }
       return;

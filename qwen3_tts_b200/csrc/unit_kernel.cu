@@ -49,7 +49,7 @@ struct __align__(8) UnitBarriers {
 
 // Debug timeline (Q3TTS_DBG bit 5): clock64 stamps of CTA 0, first 16 tiles: [tile][event]
 __device__ long long g_unit_trace[16 * 16];
-#define UTRACE(it, ev) do { if ((p.dbg & 32) && blockIdx.x == 0 && (it) < 16) g_unit_trace[(it) * 16 + (ev)] = clock64(); } while (0)
+#define UTRACE(it, ev) do { if (Q3_DBG(p, 32) && blockIdx.x == 0 && (it) < 16) g_unit_trace[(it) * 16 + (ev)] = clock64(); } while (0)
 
 struct UnitArgs {
   const float* bias7;
@@ -330,7 +330,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             const uint32_t par = ((uint32_t)(g / NST) & 1u) ^ flip;
             if (!ready) mbar_wait(&bars->wfull[ws], par);
             // poll the next tap's stage now: the ~180-cycle latency of a passing mbarrier test then overlaps the MMA issue below
-            if (tap + 1 < 7 && !(p.dbg & 256)) ready = mbar_try_wait(&bars->wfull[(g + 1) % NST], ((uint32_t)((g + 1) / NST) & 1u) ^ flip);
+            if (tap + 1 < 7 && !Q3_DBG(p, 256)) ready = mbar_try_wait(&bars->wfull[(g + 1) % NST], ((uint32_t)((g + 1) / NST) & 1u) ^ flip);
             const uint32_t wb = w_lo0 + (uint32_t)ws * (stage_bytes >> 4);
             const uint32_t at = slab + (uint32_t)tap * tap_step;
 #pragma unroll
@@ -515,7 +515,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     int pf_j = j0, pf_item = 0;
     uint32_t issued = 0, cons = 0, ob = 0;
     auto prefetch = [&]() {
-      if (pf_j >= my_tiles || (p.dbg & 128)) return;
+      if (pf_j >= my_tiles || Q3_DBG(p, 128)) return;
       if (lane == 0) {
         const int tile = wid + pf_j * nworkers;
         const int b = tile / m_tiles, mt = tile - b * m_tiles;
@@ -544,7 +544,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (quad == 2 && lane == 0) UTRACE(j, 8);
       for (int item = 0; item < nitems; ++item) {
         const uint32_t slot = cons & (URES - 1);
-        if (!(p.dbg & 128)) mbar_wait(&bars->res_bar[pw][slot], (cons / URES) & 1);  // debug bit 7: phase 2 without residual loads
+        if (!Q3_DBG(p, 128)) mbar_wait(&bars->res_bar[pw][slot], (cons / URES) & 1);  // debug bit 7: phase 2 without residual loads
         const uint32_t rs = eb + slot * kEpiSlot;
         uint4 res[4];
 #pragma unroll
@@ -579,7 +579,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
         }
-        const bool do_store = !(p.dbg & 64);  // debug: phase 2 without its output stores
+        const bool do_store = !Q3_DBG(p, 64);  // debug: phase 2 without its output stores
         if (do_store) {
           if (lane == 0) tma_store_wait_read<kUOutBufs - 1>();  // the stores that last used this slot pair have read it
           __syncwarp();
@@ -646,12 +646,12 @@ static size_t unit_smem_bytes(const UnitOp& op) {
 // the in-kernel Snake adds CUDA-core work to the same schedulers.  The streaming plans keep the two-tensor form, so streaming output is
 // not bit-identical to bulk output while the switch is on.
 bool unit_xin_available(int C) {
-  static const bool on = getenv("Q3TTS_XIN") != nullptr && getenv("Q3TTS_XIN")[0] == '1';
-  return on && C == 96 && !getenv("Q3TTS_NO_FUSE") && !getenv("Q3TTS_NO_PAIR");
+  static const bool on = Q3_ENV("Q3TTS_XIN") != nullptr && Q3_ENV("Q3TTS_XIN")[0] == '1';
+  return on && C == 96 && !Q3_ENV("Q3TTS_NO_FUSE") && !Q3_ENV("Q3TTS_NO_PAIR");
 }
 
 bool unit_fusable(int C) {
-  if (getenv("Q3TTS_NO_FUSE")) return false;
+  if (Q3_ENV("Q3TTS_NO_FUSE")) return false;
   return C == 96 || C == 192;  // instantiated shapes (the vocoder's two HBM-bound levels)
 }
 
@@ -676,25 +676,25 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
   const int need = U_BM + 6 * op->dil;
   op->srows = (need + 7) / 8 * 8;
   op->nbox = 1;
-  if (op->srows > 256) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
-  op->pair = getenv("Q3TTS_NO_PAIR") ? 0 : 1;
+  if (op->srows > 256) { if (Q3_ENV("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: srows %d\n", op->srows); return 1; }
+  op->pair = Q3_ENV("Q3TTS_NO_PAIR") ? 0 : 1;
   if (op->xin) { op->pair = 1; op->ks = Cfg96x::KS; op->nstages = Cfg96x::NST; op->nslabs = Cfg96x::NSL; op->nbuf = Cfg96x::NBUF; op->variant = 6; }
   else if (C == 96) {
     op->ks = Cfg96::KS; op->nstages = op->pair ? Cfg96p::NST : Cfg96::NST; op->nslabs = Cfg96::NSL; op->nbuf = Cfg96::NBUF; op->variant = op->pair ? 3 : 0;
-    if (op->pair && !getenv("Q3TTS_NO_P2X")) op->variant = 7;
+    if (op->pair && !Q3_ENV("Q3TTS_NO_P2X")) op->variant = 7;
   }
   else if (op->pair) {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = Cfg192pa::NST; op->variant = 4;
     if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = Cfg192pb::NST; op->variant = 5; }
-    if (!getenv("Q3TTS_NO_P1A")) op->variant += 4;  // 8 / 9: same rings, phase 1 on all 16 epilogue warps
+    if (!Q3_ENV("Q3TTS_NO_P1A")) op->variant += 4;  // 8 / 9: same rings, phase 1 on all 16 epilogue warps
   } else {
     op->ks = 1; op->nslabs = 3; op->nbuf = 1;
     op->nstages = 4; op->variant = 1;
     if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) { op->nstages = 3; op->variant = 2; }
   }
   if (unit_smem_bytes(*op) > (size_t)gemm_smem_optin()) {
-    if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: smem %zu > %d (C %d dil %d srows %d)\n", unit_smem_bytes(*op), gemm_smem_optin(), C, op->dil, op->srows);
+    if (Q3_ENV("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: smem %zu > %d (C %d dil %d srows %d)\n", unit_smem_bytes(*op), gemm_smem_optin(), C, op->dil, op->srows);
     return 1;
   }
   const int et = p.bf16 ? 1 : 0;
@@ -712,27 +712,29 @@ int unit_make(UnitOp* op, const void* a1, const void* w7, const void* w1, int ba
     rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, (uint64_t)C, (uint64_t)rows, (uint64_t)batches, rs,
                                op->snake_batch_stride ? (uint64_t)op->snake_batch_stride : bs, 32, 32);
   else op->tmSnake = op->tmRaw;  // xin, not the last unit of its block: never stored through
-  if (rc) { if (getenv("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: tensor map failed (C %d dil %d srows %d)\n", C, op->dil, op->srows); return -1; }
-  static bool attr_done = false;
-  if (!attr_done) {
-    const int mx = gemm_smem_optin();
-    cudaError_t e = cudaSuccess;
-    auto set = [&](const void* f) { if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx); };
-    set((const void*)unit_kernel<__half, Cfg96>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96>);
-    set((const void*)unit_kernel<__half, Cfg192a>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192a>);
-    set((const void*)unit_kernel<__half, Cfg192b>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192b>);
-    set((const void*)unit_kernel<__half, Cfg96p>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96p>);
-    set((const void*)unit_kernel<__half, Cfg192pa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pa>);
-    set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
-    set((const void*)unit_kernel<__half, Cfg96x>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96x>);
-    set((const void*)unit_kernel<__half, Cfg96q>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96q>);
-    set((const void*)unit_kernel<__half, Cfg192qa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qa>);
-    set((const void*)unit_kernel<__half, Cfg192qb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qb>);
-    if (e != cudaSuccess) return -2;
-    attr_done = true;
-  }
+  if (rc) { if (Q3_ENV("Q3TTS_VERBOSE")) fprintf(stderr, "unit_make: tensor map failed (C %d dil %d srows %d)\n", C, op->dil, op->srows); return -1; }
   op->enabled = 1;
   return 0;
+}
+
+
+// Opt-in to the full dynamic shared memory for every instance.  Function attributes belong to the device the call is made on, so this
+// runs once per handle (engine_finalize, next to gemm_setup), not once per process.
+int unit_setup() {
+  const int mx = gemm_smem_optin();
+  cudaError_t e = cudaSuccess;
+  auto set = [&](const void* f) { if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, mx); };
+  set((const void*)unit_kernel<__half, Cfg96>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96>);
+  set((const void*)unit_kernel<__half, Cfg192a>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192a>);
+  set((const void*)unit_kernel<__half, Cfg192b>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192b>);
+  set((const void*)unit_kernel<__half, Cfg96p>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96p>);
+  set((const void*)unit_kernel<__half, Cfg192pa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pa>);
+  set((const void*)unit_kernel<__half, Cfg192pb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192pb>);
+  set((const void*)unit_kernel<__half, Cfg96x>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96x>);
+  set((const void*)unit_kernel<__half, Cfg96q>); set((const void*)unit_kernel<__nv_bfloat16, Cfg96q>);
+  set((const void*)unit_kernel<__half, Cfg192qa>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qa>);
+  set((const void*)unit_kernel<__half, Cfg192qb>); set((const void*)unit_kernel<__nv_bfloat16, Cfg192qb>);
+  return e == cudaSuccess ? 0 : -2;
 }
 
 // Copies the debug timeline of the last traced launch (Q3TTS_DBG bit 5) to the host.

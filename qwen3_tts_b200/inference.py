@@ -41,26 +41,30 @@ class Qwen3TTSModel:
     # ------------------------------------------------------------------ the hot-path hand-off
     def decode_talker_codes(self, talker_codes_list: Sequence[torch.Tensor],
                             ref_code_list: Optional[Sequence[Optional[torch.Tensor]]] = None) -> Tuple[List[np.ndarray], int]:
-        """model wrapper :612-631: prepend each sample's reference codes (voice clone), decode once, then cut the
-        proportional prefix `int(ref_len / total_len * n_samples)` off the front.  Without ref codes it is
-        model wrapper :727 / :838: one `speech_tokenizer.decode([{"audio_codes": c}, ...])`."""
-        codes_for_decode = []
-        for i, codes in enumerate(talker_codes_list):
-            if ref_code_list is not None and ref_code_list[i] is not None:
-                codes_for_decode.append(torch.cat([ref_code_list[i].to(codes.device), codes], dim=0))
-            else:
-                codes_for_decode.append(codes)
-        wavs_all, fs = self.model.speech_tokenizer.decode([{"audio_codes": c} for c in codes_for_decode])
-        wavs_out: List[np.ndarray] = []
-        for i, wav in enumerate(wavs_all):
-            if ref_code_list is not None and ref_code_list[i] is not None:
-                ref_len = int(ref_code_list[i].shape[0])
-                total_len = int(codes_for_decode[i].shape[0])
-                cut = int(ref_len / max(total_len, 1) * wav.shape[0])
-                wavs_out.append(wav[cut:])
-            else:
-                wavs_out.append(wav)
-        return wavs_out, fs
+        """The decode hand-off of the three generate_* calls.  Without reference codes it is one
+        `speech_tokenizer.decode([{"audio_codes": c}, ...])` (model wrapper :727 / :838).  With them (voice clone, model wrapper
+        :612-631) every item is decoded as reference-prefix + generated codes, and the prefix audio - the first
+        int(ref_len / total_len * n_samples) samples - is cut INSIDE the decode call (`skip_samples`): the output conv never stores
+        it, chunks that lie inside every item's prefix are not computed, nothing is sliced on the host."""
+        tok = self.model.speech_tokenizer
+        n = len(talker_codes_list)
+        refs = list(ref_code_list) if ref_code_list is not None else [None] * n
+        items = [c if r is None else torch.cat([r.to(c.device), c], dim=0) for c, r in zip(talker_codes_list, refs)]
+        payload = [{"audio_codes": c} for c in items]
+        if all(r is None for r in refs):
+            return tok.decode(payload)
+        # n_samples of an item = what decode() returns for it: min(valid frames * upsample, chunked length of the padded batch)
+        padded_T = max(int(c.shape[0]) for c in items)
+        whole = tok.num_decoded_samples(padded_T)
+        up = tok.get_decode_upsample_rate()
+        skips = []
+        for c, r in zip(items, refs):
+            if r is None:
+                skips.append(0)
+                continue
+            n_samples = min(int((c[:, 0] > 0).sum()) * up, whole)
+            skips.append(int(int(r.shape[0]) / max(int(c.shape[0]), 1) * n_samples))   # model wrapper :627-629
+        return tok.decode(payload, skip_samples=skips)
 
     # ------------------------------------------------------------------ generate_* (talker side injected)
     def _ids(self, texts: Union[str, List[str]]):
@@ -113,8 +117,9 @@ class TalkerStreamSink:
     (talker :2280) and only then decodes (model wrapper :838).  This sink takes the same per-step tensor while it is still on
     the device, buffers `packet` frames per stream and runs one `decode_step` for all live streams when a packet is full, so
     audio leaves `packet * 80 ms` after its codes exist.  The concatenated chunks of a stream equal
-    `Decoder.forward(all its codes)` on `[0, T*1920 - 555)` (the streaming contract); nothing here synchronises
-    with the host except the caller's own use of the returned chunk.
+    `Decoder.forward(all its codes)` on `[0, T*1920 - 555)` (the streaming contract), for any utterance length:
+    `finish(row)` / `close()` decode the frames still buffered as one short packet.  `decode_step` does not synchronise with the
+    host (the stream ids travel through a ring of pinned staging blocks), so the sink can be driven from the talker's stream.
     """
 
     def __init__(self, decoder, batch: int, packet: int = 1, reserve: bool = True):
@@ -130,7 +135,7 @@ class TalkerStreamSink:
         self.ids = [decoder.open_stream() for _ in range(batch)]
         self.live = [True] * batch
         self._buf = torch.zeros((batch, self.Q, self.packet), dtype=torch.int64, device=decoder.device)
-        self._fill = 0
+        self._fill = 0   # frames buffered since the last full packet (the same for every live row: one frame per push)
 
     def push(self, codec_ids: torch.Tensor):
         """codec_ids: [B, 16] integer tensor on the decoder's device (one generated frame per stream, finished streams included:
@@ -150,12 +155,38 @@ class TalkerStreamSink:
         wav, n_valid = self.decoder.decode_step([self.ids[i] for i in rows], codes.contiguous())
         return rows, wav, n_valid
 
-    def finish(self, row: int) -> None:
-        """Stream `row` has produced its stop token: its state is released, later frames of that row are ignored."""
-        if self.live[row]:
-            self.live[row] = False
-            self.decoder.close_stream(self.ids[row])
+    def _flush(self, rows: List[int]):
+        """Decode the frames rows `rows` have buffered since the last full packet (a short packet of `_fill` frames)."""
+        if not rows or self._fill == 0:
+            return None
+        codes = self._buf[rows][:, :, : self._fill].contiguous()
+        wav, n_valid = self.decoder.decode_step([self.ids[i] for i in rows], codes)
+        return wav, n_valid
 
-    def close(self) -> None:
-        for i in range(len(self.ids)):
-            self.finish(i)
+    def finish(self, row: int) -> Optional[torch.Tensor]:
+        """Stream `row` has produced its stop token.  The frames it still has buffered (the utterance length need not be a multiple
+        of `packet`) are decoded as one short packet and returned as a 1-D device tensor (None when nothing was pending); then the
+        stream's state is released and later frames of that row are ignored."""
+        if not self.live[row]:
+            return None
+        out = self._flush([row])
+        self.live[row] = False
+        self.decoder.close_stream(self.ids[row])
+        if out is None:
+            return None
+        wav, n_valid = out
+        return wav[0, : n_valid[0]]
+
+    def close(self) -> Dict[int, torch.Tensor]:
+        """Flush and release every stream that is still live: {row: last samples} for the rows that had frames pending."""
+        rows = [i for i, ok in enumerate(self.live) if ok]
+        out = self._flush(rows)
+        tails: Dict[int, torch.Tensor] = {}
+        if out is not None:
+            wav, n_valid = out
+            tails = {r: wav[k, : n_valid[k]] for k, r in enumerate(rows)}
+        for i in rows:
+            self.live[i] = False
+            self.decoder.close_stream(self.ids[i])
+        self._fill = 0
+        return tails

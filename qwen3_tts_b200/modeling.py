@@ -110,6 +110,25 @@ class Qwen3TTSTokenizerV2Decoder:
     def set_engine(self, engine: str):
         _capi.check(self._h, self._lib.q3tts_set_engine(self._h, {"tc": _capi.ENGINE_TC, "simt": _capi.ENGINE_SIMT}[engine]), "set_engine")
 
+    def set_check_codes(self, on: bool):
+        """Opt-in range check for device codes (forward / chunked_decode / decode_step / quantizer.decode): raises IndexError where
+        the reference's F.embedding asserts (modeling :675-678).  Costs a stream synchronise per call, so it is off by default."""
+        _capi.check(self._h, self._lib.q3tts_set_check_codes(self._h, 1 if on else 0), "set_check_codes")
+
+    def activation_range(self, frames: int = 24, seed: int = 0) -> Dict[str, float]:
+        """max |activation| at every oracle tap for one seeded random code sequence.  16-bit operands overflow at 65504 (fp16): a
+        checkpoint whose Snake / ConvNeXt activations get near that must run in bf16 mode (from_pretrained checks this)."""
+        g = torch.Generator().manual_seed(seed)
+        codes = torch.randint(1, self.config.codebook_size, (1, self.config.num_quantizers, frames), generator=g, dtype=torch.int64)
+        stages = ["quantizer", "pre_conv", "pre_transformer"]
+        stages += [f"upsample.{i}.{j}" for i in range(len(self.config.upsampling_ratios)) for j in (0, 1)] + ["decoder.0.snake"]
+        stages += [f"decoder.{i + 1}.block.{j}" for i in range(len(self.config.upsample_rates)) for j in (1, 2, 3, 4)]
+        out = {}
+        for st in stages:
+            v = self.probe(codes, st)
+            out[st] = float(v.abs().max().item()) if bool(torch.isfinite(v).all()) else float("inf")
+        return out
+
     def launch_count(self) -> int:
         return int(self._lib.q3tts_launch_count(self._h))
 
@@ -266,7 +285,12 @@ class Qwen3TTSTokenizerV2Model:
     @classmethod
     def from_pretrained(cls, path: str, device_map: Union[str, torch.device, None] = None, dtype=None, **kwargs):
         """Reads `<path>/config.json` and `*.safetensors` like AutoModel.from_pretrained would (wrapper :88).
-        dtype=torch.bfloat16 selects bf16 tensor-core operands; anything else the fp16 parity mode."""
+        dtype=torch.bfloat16 selects bf16 tensor-core operands; anything else (float32, float16, None) asks for the fp16 parity mode
+        (fp16 operands, fp32 accumulation).  fp16 operands overflow at 65504 and parity has only been measured on synthetic weights
+        (no checkpoint is mounted on the build boxes), so after loading the activation range of every stage is probed once on random
+        codes: if any stage comes within 2x of the fp16 limit the model is rebuilt in bf16 mode and a warning says so."""
+        import warnings
+
         from safetensors import safe_open
 
         config = Qwen3TTSTokenizerV2Config.from_pretrained(path)
@@ -283,6 +307,15 @@ class Qwen3TTSTokenizerV2Model:
                     if k.startswith("decoder."):
                         sd[k] = sf.get_tensor(k)
         model.load_state_dict(sd)
+        if mode == "fp16":
+            rng = model.decoder.activation_range()
+            worst = max(rng, key=rng.get)
+            if not rng[worst] < 0.5 * 65504.0:
+                warnings.warn(f"fp16 operands would overflow on this checkpoint (max |activation| {rng[worst]:.3g} at {worst}); "
+                              "loading in bf16 mode instead (wider range, 8-bit mantissa)")
+                del model
+                model = cls(config, device=device, compute_mode="bf16")
+                model.load_state_dict(sd)
         return model
 
     def encode(self, *args, **kwargs):
@@ -298,9 +331,10 @@ class Qwen3TTSTokenizerV2Model:
             return (audio_values,)
         return Qwen3TTSTokenizerV2DecoderOutput(audio_values)
 
-    def decode_host(self, audio_codes_cpu: torch.Tensor):
+    def decode_host(self, audio_codes_cpu: torch.Tensor, skip_samples=None):
         """End-to-end path used by Qwen3TTSTokenizer.decode: HOST codes [B,T,Q] -> list of HOST fp32
-        waveforms, with the H2D / D2H copies and the length rule inside one C call."""
+        waveforms, with the H2D / D2H copies and the length rule inside one C call.  skip_samples (one int per item,
+        optional): leading samples that are never stored (voice-clone prefix cut, model wrapper :627-630)."""
         import numpy as np
         codes = audio_codes_cpu.to(torch.int64).contiguous()
         if codes.dim() != 3 or codes.shape[2] != self.config.decoder_config.num_quantizers:
@@ -310,23 +344,36 @@ class Qwen3TTSTokenizerV2Model:
         total = int(d._lib.q3tts_chunked_num_samples(d._h, T, 300, 25))
         wav = torch.empty((B, max(total, 1)), dtype=torch.float32, pin_memory=True)
         lengths = (C.c_int64 * B)()
-        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), wav.shape[1], lengths, _stream_ptr(d.device))
+        skip = self._skip_array(skip_samples, B)
+        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), wav.shape[1], lengths, skip, _stream_ptr(d.device))
         _capi.check(d._h, rc, "decode_host")
         arr = wav.numpy()  # fresh pinned buffer per call: the returned rows are views that keep it alive, no extra host copy
         return [arr[b, : lengths[b]] for b in range(B)]
 
-    def decode_host_pcm16(self, audio_codes_cpu: torch.Tensor):
+    @staticmethod
+    def _skip_array(skip_samples, B: int):
+        if skip_samples is None:
+            return None
+        if len(skip_samples) != B:
+            raise ValueError(f"{len(skip_samples)} skip_samples for {B} items")
+        return (C.c_int64 * B)(*[int(v) for v in skip_samples])
+
+    def decode_host_pcm16(self, audio_codes_cpu: torch.Tensor, skip_samples=None):
         """decode_host with the wire formats of SURVEY 8f-3: codes travel as int16, the result is PCM16
         (np.int16 = rint(clamp(wav) * 32767), what sf.write stores for a float waveform), converted in the output conv."""
         if audio_codes_cpu.dim() != 3 or audio_codes_cpu.shape[2] != self.config.decoder_config.num_quantizers:
             raise ValueError(f"Expected {self.config.decoder_config.num_quantizers} layer of codes, got {audio_codes_cpu.shape[-1]}")
+        if audio_codes_cpu.numel() and (int(audio_codes_cpu.min()) < 0 or int(audio_codes_cpu.max()) >= self.config.decoder_config.codebook_size):
+            # checked BEFORE narrowing: .to(int16) would wrap a leaked special / EOS id into a valid-looking index
+            raise IndexError(f"code index outside [0, {self.config.decoder_config.codebook_size}) (reference: F.embedding raises, modeling :675-678)")
         codes = audio_codes_cpu.to(torch.int16).contiguous()
         B, T, _ = codes.shape
         d = self.decoder
         total = int(d._lib.q3tts_chunked_num_samples(d._h, T, 300, 25))
         pcm = torch.empty((B, max(total, 1)), dtype=torch.int16, pin_memory=True)
         lengths = (C.c_int64 * B)()
-        rc = d._lib.q3tts_decode_host_pcm16(d._h, codes.data_ptr(), B, T, pcm.data_ptr(), pcm.shape[1], lengths, _stream_ptr(d.device))
+        skip = self._skip_array(skip_samples, B)
+        rc = d._lib.q3tts_decode_host_pcm16(d._h, codes.data_ptr(), B, T, pcm.data_ptr(), pcm.shape[1], lengths, skip, _stream_ptr(d.device))
         _capi.check(d._h, rc, "decode_host_pcm16")
         arr = pcm.numpy()
         return [arr[b, : lengths[b]] for b in range(B)]

@@ -116,8 +116,13 @@ def _fan_in(key: str, shape: Tuple[int, ...]) -> int:
     return shape[1]
 
 
-def make_decoder_state_dict(cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0) -> Dict[str, torch.Tensor]:
-    """Deterministic fp32 CPU state dict with reference key names."""
+def make_decoder_state_dict(cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0, stress: bool = False) -> Dict[str, torch.Tensor]:
+    """Deterministic fp32 CPU state dict with reference key names.
+
+    stress=True draws Snake beta from N(0, 0.3) exactly as SURVEY 8(c) words it (instead of 1 + N(0, 0.3)): the periodic term
+    of every Snake is then ~2.7x larger and the 29-Snake stack amplifies any perturbation ~10x more (fp32 vs fp64 99 dB instead
+    of 113-121 dB).  It is the ill-conditioned end of what a checkpoint could be; parity numbers are reported for both
+    (profiles/r2_parity.json)."""
     out: Dict[str, torch.Tensor] = OrderedDict()
     for key, shape in decoder_param_shapes(cfg).items():
         g = _gen(seed, key)
@@ -132,7 +137,7 @@ def make_decoder_state_dict(cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0
             # below 1 so the random-init stack amplifies perturbations about as little as the survey's
             # reference run did (fp32 vs fp64 ~ 113-121 dB) -- with mean 0 it is chaotic
             # (fp32 vs fp64 only 99 dB) and no 16-bit operand scheme can be compared meaningfully.
-            t = 1.0 + torch.randn(shape, generator=g) * 0.3
+            t = (0.0 if stress else 1.0) + torch.randn(shape, generator=g) * 0.3
         elif key.endswith("gamma") or key.endswith("layer_scale.scale"):
             t = torch.rand(shape, generator=g) * 0.5 + 0.25
         elif key.endswith("layernorm.weight") or key.endswith("norm.weight"):

@@ -45,8 +45,15 @@ class Qwen3TTSTokenizer:
     def encode(self, *args, **kwargs):
         raise NotImplementedError("encode (wav -> codes) is outside the decode hot path this package accelerates")
 
-    def decode(self, encoded) -> Tuple[List[np.ndarray], int]:
-        """Decode back to waveform (wrapper :259-365)."""
+    def num_decoded_samples(self, frames: int) -> int:
+        """Samples decode() returns for an item that fills a batch padded to `frames` code frames:
+        frames * 1920 - 555 per 300-frame chunk (chunked_decode, modeling :885-895)."""
+        d = self.model.decoder
+        return int(d._lib.q3tts_chunked_num_samples(d._h, int(frames), 300, 25))
+
+    def decode(self, encoded, skip_samples=None) -> Tuple[List[np.ndarray], int]:
+        """Decode back to waveform (wrapper :259-365).  `skip_samples` (additive, one int per item): leading samples of each
+        waveform that are cut inside the decode call (voice-clone prefix, model wrapper :627-630)."""
         model_type = self.model.get_model_type()
 
         def _to_tensor(x, dtype=None):
@@ -77,15 +84,15 @@ class Qwen3TTSTokenizer:
             raise ValueError(f"Unknown model type: {model_type}")
 
         with torch.inference_mode():
-            if audio_codes_padded.is_cuda:
+            if audio_codes_padded.is_cuda and skip_samples is None:
                 dec = self.model.decode(audio_codes_padded, return_dict=True)
                 wavs = [w.to(torch.float32).detach().cpu().numpy() for w in dec.audio_values]
             else:
-                # host payload: one C call does H2D, chunked decode, the length rule and D2H
-                wavs = self.model.decode_host(audio_codes_padded)
+                # host payload: one C call does H2D, chunked decode, the length rule, the prefix cut and D2H
+                wavs = self.model.decode_host(audio_codes_padded.cpu(), skip_samples=skip_samples)
         return wavs, int(self.model.get_output_sample_rate())
 
-    def decode_pcm16(self, encoded) -> Tuple[List[np.ndarray], int]:
+    def decode_pcm16(self, encoded, skip_samples=None) -> Tuple[List[np.ndarray], int]:
         """Additive: same payload forms as decode(), result as PCM16 (np.int16) ready for a WAV writer."""
         if hasattr(encoded, "audio_codes"):
             lst = encoded.audio_codes
@@ -101,7 +108,7 @@ class Qwen3TTSTokenizer:
             padded = pad_sequence([c if isinstance(c, torch.Tensor) else torch.from_numpy(np.asarray(c)) for c in lst], batch_first=True,
                                   padding_value=0)
         with torch.inference_mode():
-            pcm = self.model.decode_host_pcm16(padded.cpu())
+            pcm = self.model.decode_host_pcm16(padded.cpu(), skip_samples=skip_samples)
         return pcm, int(self.model.get_output_sample_rate())
 
     def get_model_type(self) -> str:

@@ -24,6 +24,13 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), name
     assert declared == set(_capi.EXPORTS)      # the ctypes table binds exactly the header
+    # the debug / design-evidence exports live in their own header and are not part of the boundary
+    dbg = open(os.path.join(ROOT, "include", "q3tts_debug.h")).read()
+    declared_dbg = set(re.findall(r"\b(q3tts_[a-z_0-9]+)\s*\(", dbg))
+    assert declared_dbg == set(_capi.DEBUG_EXPORTS) and not (declared_dbg & declared)
+    for name in declared_dbg:
+        assert hasattr(lib, name), name
+    assert not any(w in hdr for w in ("selftest", "bench_mma", "bench_tma", "unit_trace"))
 
 
 def test_config_struct_matches_header_field_order():

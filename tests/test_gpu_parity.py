@@ -100,12 +100,20 @@ def test_chunked_decode_small_chunks_golden(gpu_model):
 
 
 def test_two_chunk_decode_golden(gpu_model):
+    """The real two-chunk path (300 + 10 frames, 25 frames of left context) against the reference: every 8th sample of the whole
+    waveform and EVERY sample of the 16384 around the chunk seam (sample 300*1920 - 555, where chunk 2's first emitted sample
+    follows chunk 1's last)."""
     g = load_golden("chunked_B1_T310.npz")
     out = gpu_model.decode(torch.from_numpy(g["codes"]).cuda(), return_dict=True)
     wav = out.audio_values[0]
     assert wav.shape == (int(g["num_samples"]),) == (310 * 1920 - 2 * 555,)
     mx, snr = _stats(g["wav_sub8"][0, 0], wav[::8])
     print(f"two-chunk T310: max-abs {mx:.3e} snr {snr:.1f} dB")
+    assert mx <= MAX_ABS and snr >= MIN_SNR
+    s0 = int(g["seam_start"])
+    assert s0 < 300 * 1920 - 555 < s0 + g["wav_seam"].shape[-1]
+    mx, snr = _stats(g["wav_seam"][0, 0], wav[s0:s0 + g["wav_seam"].shape[-1]])
+    print(f"two-chunk T310 seam: max-abs {mx:.3e} snr {snr:.1f} dB")
     assert mx <= MAX_ABS and snr >= MIN_SNR
 
 
@@ -161,7 +169,7 @@ def test_decode_host_pageable_and_pinned_buffers_agree(gpu_model, cfg):
     for pinned in (True, False):
         wav = torch.full((B, stride), 7.0, dtype=torch.float32, pin_memory=pinned)
         lengths = (C.c_int64 * B)()
-        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), stride, lengths, _stream_ptr(d.device))
+        rc = d._lib.q3tts_decode_host(d._h, codes.data_ptr(), B, T, wav.data_ptr(), stride, lengths, None, _stream_ptr(d.device))
         _capi.check(d._h, rc, "decode_host")
         assert [int(x) for x in lengths] == [total, total, 7 * 1920]
         outs.append((wav, [int(x) for x in lengths]))
