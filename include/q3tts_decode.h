@@ -122,6 +122,17 @@ int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, i
  * asserts (modeling :675-678).  Off by default: the hot path stays asynchronous ("check on request only"). */
 int q3tts_set_check_codes(q3tts_handle* h, int on);
 
+/* The same gather-sum on int16 code frames (the wire format of q3tts_decode_host_pcm16) with NO allocation anywhere in the call.
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  codes [B,Q,T] int16 (device) -> out [B,codebook_dim,T]
+ * fp32 (device), equal to q3tts_rvq_decode on the widened codes.  The int64 staging the gather kernel reads lives in a file-scope
+ * __device__ array of Q3TTS_STATIC_MAX_CODES entries (4 MiB, held by every GPU that loads the library until the process exits):
+ * B*Q*T beyond that returns Q3TTS_BAD_SHAPE.  All calls on a device share the array and it keeps the last call's contents (each
+ * call overwrites exactly what it reads); calls that overlap on the GPU - two streams, two handles on one device - race on it. */
+#define Q3TTS_STATIC_MAX_CODES (512 * 1024)
+int64_t q3tts_static_max_codes(void);
+int q3tts_rvq_decode_i16_static(q3tts_handle* h, const int16_t* codes, int B, int T, float* out, void* stream);
+
 /* ---- Streaming: stateful per-packet decode.  The reference has NO counterpart: its only streaming-shaped call is
  * chunked_decode's `forward(codes[..., s-25:e])[..., 25*1920:]` (modeling :889-893), which re-decodes 25 frames of left
  * context per chunk and is only approximately equal to the whole-sequence decode.  These entry points keep, per stream, the

@@ -195,6 +195,7 @@ int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);
 int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long long* codes, long long sb, long long sk, long long st, int P, float* wav,
                        long long wav_stride, int32_t* n_valid, cudaStream_t s);
 void engine_stream_free(Engine* e);
+int static_scratch_setup(int device);  // noalloc.cu: device address of the static scratch array on the current device
 
 struct DeviceGuard {
   int prev = -1;

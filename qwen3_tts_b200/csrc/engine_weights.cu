@@ -126,9 +126,9 @@ int engine_finalize(Engine* e, int mode) {
   // kernel attributes (shared-memory opt-ins) are per device: set them for THIS handle's device every time, so a second handle on
   // another GPU of the same process launches with the same limits as the first
   if (gemm_setup(e->device)) return e->fail(Q3TTS_CUDA_ERROR, "gemm_setup failed (cuTensorMapEncodeTiled unavailable or smem opt-in rejected)");
-  if (unit_setup() || tail_setup() || attention_setup() != cudaSuccess || stream_attention_setup() != cudaSuccess) {
+  if (unit_setup() || tail_setup() || attention_setup() != cudaSuccess || stream_attention_setup() != cudaSuccess || static_scratch_setup(e->device)) {
     cudaGetLastError();
-    return e->fail(Q3TTS_CUDA_ERROR, "kernel shared-memory opt-in rejected");
+    return e->fail(Q3TTS_CUDA_ERROR, "per-device kernel set-up failed (shared-memory opt-in or static scratch address)");
   }
 
   if (!e->d_bad_code) {
