@@ -233,7 +233,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16"], help="tensor-core operand type (fp32 accumulate)")
+    ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "fp16-plain", "bf16-plain", "fp16-split-all", "bf16-split-all"],
+                    help="tensor-core operand type (fp32 accumulate) and how many early-stage operands are hi + lo pairs (DESIGN.md Precision)")
     ap.add_argument("--workload", default="bulk10s", choices=sorted(WORKLOADS), help="default = the configuration BASELINE.json's metric is quoted on")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true", help="skip the streaming-chunk latency section (BASELINE config 3)")

@@ -62,7 +62,16 @@ typedef struct {
   float rope_theta;           /* 10000 */
 } q3tts_config;
 
-enum { Q3TTS_MODE_FP16 = 0, Q3TTS_MODE_BF16 = 1 }; /* tensor-core operand type; accumulation is fp32 in both */
+/* compute_mode of q3tts_finalize_weights.  Bit 0 = tensor-core operand type (0 fp16, 1 bf16; accumulation is fp32 in both).  The
+ * upper bits pick how many operands are carried as hi + lo pairs of 16-bit values (fp32-class products from 2-3 MMAs; DESIGN.md
+ * "Precision"): default = the main signal path of the early stages (RVQ -> pre_conv -> input_proj, final norm -> output_proj ->
+ * upsample convs -> decoder[0]; ~3 % of the FLOPs, ~40 % of the rounding noise), _PLAIN = none (every operand one 16-bit value),
+ * _SPLIT_ALL = every GEMM in front of the vocoder blocks. */
+enum {
+  Q3TTS_MODE_FP16 = 0, Q3TTS_MODE_BF16 = 1,
+  Q3TTS_MODE_FP16_PLAIN = 2, Q3TTS_MODE_BF16_PLAIN = 3,
+  Q3TTS_MODE_FP16_SPLIT_ALL = 4, Q3TTS_MODE_BF16_SPLIT_ALL = 5
+};
 enum { Q3TTS_ENGINE_TC = 0, Q3TTS_ENGINE_SIMT = 1 }; /* SIMT = debug cross-check kernels, not a product path */
 
 /* Lifetime.  Replaces Qwen3TTSTokenizerV2Decoder.__init__ (modeling :824-866). */

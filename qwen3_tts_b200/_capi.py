@@ -24,6 +24,8 @@ def set_library_path(path: str) -> None:
 
 OK, BAD_SHAPE, BAD_CONFIG, CODE_OUT_OF_RANGE, CUDA_ERROR, OOM, BAD_STREAM, BAD_KEY, NOT_READY = 0, -1, -2, -3, -4, -5, -6, -7, -8
 MODE_FP16, MODE_BF16 = 0, 1
+# bit 0 = operand type, upper bits = how many operands are hi + lo pairs (include/q3tts_decode.h)
+MODES = {"fp16": 0, "bf16": 1, "fp16-plain": 2, "bf16-plain": 3, "fp16-split-all": 4, "bf16-split-all": 5}
 ENGINE_TC, ENGINE_SIMT = 0, 1
 
 # error code -> Python exception, mirroring what the reference raises on the same condition

@@ -138,15 +138,16 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (!PAIR && p.pack_mode)
           for (int q = 0; q < 4; ++q) gemm_chunk_coords(p, b, q, cr[q], cb[q]);
         for (int kb = 0; kb < kblocks; ++kb) {
+          const int acol = p.a_cols ? (kb * KB) % p.a_cols : kb * KB;  // split-precision operands: K blocks wrap around the A tensor
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
             if (rank == 0) mbar_expect_tx(&bars->full[s], stage_bytes * NCTA);
             if (!PAIR && p.pack_mode) {  // four 32-row chunk boxes fill the 128-row A tile
               for (int q = 0; q < 4; ++q)
-                tma_load_3d(sa + q * (a_bytes >> 2), &tmA, &bars->full[s], kb * KB, cr[q] + p.a_row0 + p.tap_off[tap], cb[q]);
+                tma_load_3d(sa + q * (a_bytes >> 2), &tmA, &bars->full[s], acol, cr[q] + p.a_row0 + p.tap_off[tap], cb[q]);
             } else {
-              load(sa, &tmA, &bars->full[s], kb * KB, m0 + p.a_row0 + p.tap_off[tap], b);
+              load(sa, &tmA, &bars->full[s], acol, m0 + p.a_row0 + p.tap_off[tap], b);
             }
             load(sa + a_bytes, &tmB, &bars->full[s], kb * KB, n0, tap);
             if (++s == nstages) { s = 0; ph ^= 1; }
@@ -249,7 +250,8 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait_backoff(&bars->empty[s], ph ^ 1);
         mbar_expect_tx(&bars->full[s], slab_bytes);
         for (int kb = 0; kb < nkb; ++kb)
-          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], kb * KB, mt * BM + p.a_row0 - halo, b);
+          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], p.a_cols ? (kb * KB) % p.a_cols : kb * KB,
+                      mt * BM + p.a_row0 - halo, b);
         if (++s == nslabs) { s = 0; ph ^= 1; }
       }
     }
@@ -362,7 +364,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
           if (rank == 0) mbar_expect_tx(&bars->sfull[ss], ssub * NCTA);
-          load(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], kb * KB, mt * TM + rank * BM + p.a_row0 - slab_lo, b);
+          load(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], p.a_cols ? (kb * KB) % p.a_cols : kb * KB, mt * TM + rank * BM + p.a_row0 - slab_lo, b);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
@@ -448,10 +450,11 @@ __global__ void conv_gemm_simt_kernel(const GemmParams p) {
     for (int tap = 0; tap < p.ntaps; ++tap) {
       const int r = row + p.a_row0 + p.tap_off[tap];
       if (r < 0 || r >= p.rows) continue;
-      const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * p.cin) + (long long)r * p.cin;
+      const int aw = p.a_cols ? p.a_cols : p.cin;
+      const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * aw) + (long long)r * aw;
       const T* w = W + ((long long)tap * p.n_total + n) * p.cin;
       for (int k = 0; k < p.cin; ++k) {
-        const float av = Elem<T>::to_f(a[k]);
+        const float av = Elem<T>::to_f(a[k % aw]);
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] = fmaf(av, Elem<T>::to_f(w[(long long)i * p.cin + k]), acc[i]);
       }
@@ -645,8 +648,9 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   }
   // the weight map follows the plan: a CTA of a pair loads half of a weight tile
   if (make_tmap_3d(&op->tmB, p.w_ptr, (uint64_t)p.cin, (uint64_t)p.n_total, (uint64_t)p.ntaps, (uint32_t)p.kb, (uint32_t)(op->pair ? p.bn / 2 : p.bn), p.bf16 != 0)) rc |= 1;
-  rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.rows, (uint64_t)p.batches, (uint64_t)p.cin,
-                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * p.cin, (uint32_t)p.kb,
+  const uint64_t aw = p.a_cols ? (uint64_t)p.a_cols : (uint64_t)p.cin;  // width of the A tensor in memory
+  rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, aw, (uint64_t)p.rows, (uint64_t)p.batches, aw,
+                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * aw, (uint32_t)p.kb,
                              p.pack_mode ? br : (uint32_t)(op->variant ? op->srp : BM), bb);
   // unused maps hold a valid placeholder (the kernels take all of them as __grid_constant__ arguments)
   if (!has_res) op->tmRes = op->tmA;

@@ -27,6 +27,9 @@ struct ConvW {
   const float* bias = nullptr;  // fp32 [ncol_mod] or null
   int bn = 0, kb = 0;
   int out_rows_per_row = 1;  // transposed conv: s output rows per accumulator row
+  // split-precision operands (gemm_params.h): cin above is the K the MMAs walk = k_mult x the layer's input channels;
+  // a_cols = width of the A tensor in memory (C for k_mult 2, 2C = [hi | lo] rows for k_mult 3), 0 = plain
+  int k_mult = 1, a_cols = 0;
 };
 
 struct SnakeP { const float* a = nullptr; const float* ib = nullptr; };
@@ -42,7 +45,8 @@ struct UpsampleW {
 struct UnitW { ConvW conv7, conv1; SnakeP act1, act2; };
 struct BlockW { SnakeP act0; ConvW tconv; UnitW unit[3]; int stride = 0, cin = 0, cout = 0; };
 
-enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT, OP_STREAM_ATTN, OP_STATE_LOAD, OP_STATE_SAVE, OP_POS_ADVANCE };
+enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT, OP_STREAM_ATTN, OP_STATE_LOAD, OP_STATE_SAVE, OP_POS_ADVANCE,
+              OP_SPLIT /* fp32 [B][L][C] -> 16-bit [hi | lo] rows: in, out, B, L, C, sp_in_bs / sp_out_bs */ };
 
 struct Op {
   OpType type = OP_GEMM;
@@ -54,6 +58,9 @@ struct Op {
   const float *w0 = nullptr, *w1 = nullptr, *w2 = nullptr, *w3 = nullptr;
   int B = 0, L = 0, C = 0;
   bool drop_raw = false;   // last residual unit of a decoder block: its raw output is dead (only the Snake'd copy is read), skipped unless probing
+  int split = 0;           // OP_RVQ / OP_RMSNORM: write [hi | lo] rows;  OP_DWLN: the input tensor is fp32
+  long long sp_in_bs = 0, sp_out_bs = 0;  // OP_SPLIT: elements between batch items of in / out
+  int probe_ld = 0;        // row pitch of the probe buffer in elements (0 = probe_C)
   int aux0 = 0, aux1 = 0;  // streaming: RVQ output batch stride in rows / dwconv (input batch stride in rows, history rows) / attention layer
   // probe: the buffer that holds an oracle tap once this op has run
   std::string tag;
@@ -105,6 +112,10 @@ struct Engine {
   std::string err;
   bool finalized = false;
   bool bf16 = false;
+  // Split-precision level (DESIGN.md "Precision"): 0 = every operand one 16-bit value (the round-1 scheme); 1 = the main signal
+  // path of the early stages (RVQ -> pre_conv -> in_proj, final norm -> out_proj -> upsample convs -> decoder[0]) runs on hi + lo
+  // operands and keeps its ConvNeXt tensors in fp32; 2 = the transformer's and ConvNeXt's own GEMMs too.
+  int split_level = 1;
   int engine = ENGINE_TC;
   int total_up = 1920;
   int lookahead = 555;

@@ -35,19 +35,28 @@ struct Builder {
     for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
     p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
     p.bias = w.bias; p.bf16 = e->bf16 ? 1 : 0;
+    p.a_cols = w.a_cols; p.k_mult = w.k_mult;
     { const char* d = Q3_ENV("Q3TTS_DBG"); p.dbg = d ? atoi(d) : 0; }
     p.a_ptr = in; p.w_ptr = w.w;
     p.out_row_stride = w.n_total;
     p.out_batch_stride = (long long)rows_valid * w.n_total;
     if (!dry) {
-      if (make_tmap_3d(&op.g.tmA, in, (uint64_t)w.cin, (uint64_t)rows, (uint64_t)batches, (uint32_t)w.kb, 128, e->bf16) ||
+      if (make_tmap_3d(&op.g.tmA, in, (uint64_t)(w.a_cols ? w.a_cols : w.cin), (uint64_t)rows, (uint64_t)batches, (uint32_t)w.kb, 128, e->bf16) ||
           make_tmap_3d(&op.g.tmB, w.w, (uint64_t)w.cin, (uint64_t)w.n_total, (uint64_t)w.taps, (uint32_t)w.kb, (uint32_t)w.bn, e->bf16))
         rc = e->fail(Q3TTS_CUDA_ERROR, "cuTensorMapEncodeTiled failed");
     }
     return op;
   }
-  void tag(Op& op, const char* name, const void* ptr, bool f32, int C, int L) {
-    op.tag = name; op.probe_ptr = ptr; op.probe_f32 = f32; op.probe_C = C; op.probe_L = L;
+  void tag(Op& op, const char* name, const void* ptr, bool f32, int C, int L, int ld = 0) {
+    op.tag = name; op.probe_ptr = ptr; op.probe_f32 = f32; op.probe_C = C; op.probe_L = L; op.probe_ld = ld;
+  }
+  // fp32 [batches][rows][C] -> 16-bit rows [hi | lo]: the split-precision A operand of the next GEMM
+  Op& split(const float* in, void* out, int batches, int rows, int C) {
+    plan->ops.emplace_back();
+    Op& op = plan->ops.back();
+    op.type = OP_SPLIT; op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C;
+    op.sp_in_bs = (long long)rows * C; op.sp_out_bs = (long long)rows * 2 * C;
+    return op;
   }
 };
 
@@ -59,30 +68,37 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   const int M = B * T;
   const size_t es = 2;  // 16-bit activations
 
-  // ---- RVQ -> E [B,T,D]
-  void* E = b.alloc((size_t)M * D * es);
+  // Split-precision plans (e->split_level >= 1, DESIGN.md "Precision"): a layer packed with k_mult 3 reads A rows [hi | lo]; such
+  // tensors are written by the SIMT kernels (RVQ, RMSNorm) or made from an fp32 main-path tensor by OP_SPLIT.
+  const bool sp_main = e->pre_conv.k_mult == 3;
+  const bool sp_xf = !e->layers.empty() && e->layers[0].qkv.k_mult == 3;
+  // ---- RVQ -> E [B,T,D] (rows [hi | lo] when pre_conv takes split operands)
+  void* E = b.alloc((size_t)M * D * es * (sp_main ? 2 : 1));
   {
     plan->ops.emplace_back();
     Op& op = plan->ops.back();
-    op.type = OP_RVQ; op.out = E; op.B = B; op.L = T; op.C = D;
-    b.tag(op, "quantizer", E, false, D, T);
+    op.type = OP_RVQ; op.out = E; op.B = B; op.L = T; op.C = D; op.split = sp_main ? 1 : 0;
+    b.tag(op, "quantizer", E, false, D, T, sp_main ? 2 * D : 0);
   }
-  // ---- pre_conv (k=3 causal) -> P [B,T,Lat]
-  void* P = b.alloc((size_t)M * Lat * es);
+  // ---- pre_conv (k=3 causal) -> P [B,T,Lat]: 16-bit, or fp32 + its [hi | lo] copy for in_proj
+  void* P = b.alloc((size_t)M * Lat * (sp_main ? 4 : es));
+  void* P16 = sp_main ? b.alloc((size_t)M * 2 * Lat * es) : P;
   {
     Op& op = b.gemm(e->pre_conv, E, B, T, T);
-    op.g.p.out_raw = P;
-    b.tag(op, "pre_conv", P, false, Lat, T);
+    if (sp_main) op.g.p.out_f32 = (float*)P; else op.g.p.out_raw = P;
+    b.tag(op, "pre_conv", P, sp_main, Lat, T);
   }
+  if (sp_main) b.split((const float*)P, P16, 1, M, Lat);
   // ---- transformer (reference modeling :500-574); rows = all tokens, residual stream in fp32
   float* X = (float*)b.alloc((size_t)M * H * 4);
-  void* Hn = b.alloc((size_t)M * H * es);
+  void* Hn = b.alloc((size_t)M * H * es * 2);  // RMSNorm output, [hi | lo] rows where the consumer takes split operands
   void* QKV = b.alloc((size_t)M * 3 * H * es);
   void* AO = b.alloc((size_t)M * H * es);
   void* MI = b.alloc((size_t)M * I * es);
-  void* TO = b.alloc((size_t)M * Lat * es);
+  void* TO = b.alloc((size_t)M * Lat * (sp_main ? 4 : es));
+  void* TO16 = sp_main ? b.alloc((size_t)M * 2 * Lat * es) : TO;
   {
-    Op& op = b.gemm(e->in_proj, P, 1, M, M);
+    Op& op = b.gemm(e->in_proj, P16, 1, M, M);
     op.g.p.out_f32 = X;
   }
   {
@@ -92,15 +108,15 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   for (int l = 0; l < c.num_hidden_layers; ++l) {
     const LayerW& W = e->layers[l];
     const std::string L = "transformer." + std::to_string(l) + ".";  // debug probe taps (not oracle taps)
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H;
-      b.tag(op, (L + "ln1").c_str(), Hn, false, H, T); }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H; op.split = sp_xf ? 1 : 0;
+      b.tag(op, (L + "ln1").c_str(), Hn, false, H, T, sp_xf ? 2 * H : 0); }
     { Op& op = b.gemm(W.qkv, Hn, 1, M, M); op.g.p.out_raw = QKV; b.tag(op, (L + "qkv").c_str(), QKV, false, 3 * H, T); }
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = T;
       b.tag(op, (L + "attn").c_str(), AO, false, H, T); }
     { Op& op = b.gemm(W.o, AO, 1, M, M); op.g.p.scale = W.ls1; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X;
       b.tag(op, (L + "o").c_str(), X, true, H, T); }
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H;
-      b.tag(op, (L + "ln2").c_str(), Hn, false, H, T); }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H; op.split = sp_xf ? 1 : 0;
+      b.tag(op, (L + "ln2").c_str(), Hn, false, H, T, sp_xf ? 2 * H : 0); }
     {
       Op& op = b.gemm(W.gateup, Hn, 1, M, M);
       op.g.p.act = ACT_GLU; op.g.p.out_raw = MI; op.g.p.out_row_stride = I; op.g.p.out_batch_stride = (long long)M * I;
@@ -109,42 +125,49 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     { Op& op = b.gemm(W.down, MI, 1, M, M); op.g.p.scale = W.ls2; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X;
       b.tag(op, (L + "down").c_str(), X, true, H, T); }
   }
-  { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; }
+  { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_RMSNORM; op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; op.split = sp_main ? 1 : 0; }
   {
     Op& op = b.gemm(e->out_proj, Hn, 1, M, M);
-    op.g.p.out_raw = TO;
-    b.tag(op, "pre_transformer", TO, false, Lat, T);
+    if (sp_main) op.g.p.out_f32 = (float*)TO; else op.g.p.out_raw = TO;
+    b.tag(op, "pre_transformer", TO, sp_main, Lat, T);
   }
+  if (sp_main) b.split((const float*)TO, TO16, 1, M, Lat);
   // ---- upsample: [TransConv k=s ; ConvNeXt] x n (reference modeling :877-879, :226-242)
-  const void* cur = TO;
+  // Split-precision plans keep the main path (transposed-conv output Uo, block output V = Uo + gamma * ...) in fp32 and hand the
+  // next GEMM a [hi | lo] copy of V; the ConvNeXt's inner tensors (LayerNorm output, GELU output) stay one 16-bit value.
+  const void* cur = TO16;
   int L = T;
   for (size_t i = 0; i < e->ups.size(); ++i) {
     const UpsampleW& U = e->ups[i];
     const int r = c.upsampling_ratios[i];
     const int Lo = L * r;
-    void* Uo = b.alloc((size_t)B * Lo * Lat * es);
+    void* Uo = b.alloc((size_t)B * Lo * Lat * (sp_main ? 4 : es));
     void* Nn = b.alloc((size_t)B * Lo * Lat * es);
     void* G = b.alloc((size_t)B * Lo * 4 * Lat * es);
-    void* V = b.alloc((size_t)B * Lo * Lat * es);
+    void* V = b.alloc((size_t)B * Lo * Lat * (sp_main ? 4 : es));
+    void* V16 = sp_main ? b.alloc((size_t)B * Lo * 2 * Lat * es) : V;
     {
       Op& op = b.gemm(U.tconv, cur, 1, B * L, B * L);  // k == stride: rows are independent, flatten the batch
-      op.g.p.out_raw = Uo;
+      if (sp_main) op.g.p.out_f32 = (float*)Uo; else op.g.p.out_raw = Uo;
       const std::string t = "upsample." + std::to_string(i) + ".0";
-      b.tag(op, t.c_str(), Uo, false, Lat, Lo);
+      b.tag(op, t.c_str(), Uo, sp_main, Lat, Lo);
     }
     {
       plan->ops.emplace_back();
       Op& op = plan->ops.back();
       op.type = OP_DWLN; op.in = Uo; op.out = Nn; op.w0 = U.dww; op.w1 = U.dwb; op.w2 = U.lnw; op.w3 = U.lnb; op.B = B; op.L = Lo; op.C = Lat;
+      op.split = sp_main ? 1 : 0;  // fp32 input
     }
     { Op& op = b.gemm(U.pw1, Nn, 1, B * Lo, B * Lo); op.g.p.act = ACT_GELU; op.g.p.out_raw = G; }
     {
       Op& op = b.gemm(U.pw2, G, 1, B * Lo, B * Lo);
-      op.g.p.scale = U.gamma; op.g.p.res = Uo; op.g.p.out_raw = V;
+      op.g.p.scale = U.gamma; op.g.p.res = Uo;
+      if (sp_main) { op.g.p.res_f32 = 1; op.g.p.out_f32 = (float*)V; } else op.g.p.out_raw = V;
       const std::string t = "upsample." + std::to_string(i) + ".1";
-      b.tag(op, t.c_str(), V, false, Lat, Lo);
+      b.tag(op, t.c_str(), V, sp_main, Lat, Lo);
     }
-    cur = V; L = Lo;
+    if (sp_main) b.split((const float*)V, V16, 1, B * Lo, Lat);
+    cur = V16; L = Lo;
   }
   // ---- vocoder: three rotating buffers sized for the largest stage
   size_t big = (size_t)B * L * c.decoder_dim;
@@ -323,8 +346,10 @@ void prof_account(Engine* e, const Op& op) {
     const GemmParams& p = op.g.p;
     const double rows = (double)p.batches * p.rows_valid;
     dims[0] = p.batches * p.rows_valid; dims[1] = p.n_total; dims[2] = p.cin; dims[3] = p.ntaps;
-    fl = 2.0 * rows * p.n_total * p.cin * p.ntaps;
-    by = 2.0 * ((double)p.batches * p.rows * p.cin + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
+    const int km = p.k_mult > 0 ? p.k_mult : 1;  // split-precision layers walk k_mult x the real K: the extra MMAs are not algorithmic work
+    dims[2] = p.cin / km;
+    fl = 2.0 * rows * p.n_total * (p.cin / km) * p.ntaps;
+    by = 2.0 * ((double)p.batches * p.rows * (p.a_cols ? p.a_cols : p.cin) + (double)p.ntaps * p.n_total * p.cin);  // A once + W once
     const double outw = p.act == ACT_GLU ? p.n_total / 2 : p.n_total;
     if (p.out_raw) by += 2.0 * rows * outw;
     if (p.out_snake) by += 2.0 * rows * outw;
@@ -345,8 +370,10 @@ void prof_account(Engine* e, const Op& op) {
     dims[1] = (int)H;
     fl = 4.0 * rows * H * e->cfg.sliding_window;  // QK^T and PV at a full window, as SURVEY 8(a) counts them
     by = 2.0 * rows * 4.0 * H;                    // q, k, v in, o out (16-bit)
+  } else if (op.type == OP_SPLIT) {
+    by = (4.0 + 4.0) * (double)op.B * op.L * op.C;  // fp32 in, two 16-bit values out
   } else if (op.type == OP_DWLN) {
-    by = 2.0 * 2.0 * (double)op.B * op.L * op.C;  // one read and one write of the token tensor (16-bit)
+    by = (op.split ? 4.0 + 2.0 : 2.0 * 2.0) * (double)op.B * op.L * op.C;  // one read and one write of the token tensor
   }
   e->prof_type.push_back((int)op.type);
   e->prof_flops.push_back(fl);
@@ -372,15 +399,17 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
     else if (op.type == OP_GEMM && drop) op.g.p.out_raw = nullptr;
     switch (op.type) {
       case OP_RVQ:
-        err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s, 0, nullptr, e->d_bad_code);
+        err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s, 0, nullptr,
+                         e->d_bad_code, op.split);
         break;
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
-      case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s); break;
+      case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s, op.split); break;
+      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s); break;
       case OP_ATTN:
         err = sliding_attention(op.in, e->rope_cos, e->rope_sin, op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->bf16, s);
         break;
-      case OP_DWLN: err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s); break;
+      case OP_DWLN: err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s, 0, 0, op.split != 0); break;
       case OP_TAIL:
         if (wav) {
           if (op.t.enabled && e->engine == ENGINE_TC) {
@@ -409,7 +438,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
     if (probe_stage && !op.tag.empty() && op.tag == probe_stage && op.type != OP_TAIL) {
       const long long n = (long long)plan->B * op.probe_C * op.probe_L;
       if (n > probe_cap) return e->fail(Q3TTS_BAD_SHAPE, "probe buffer too small");
-      err = to_channels_first_f32(op.probe_ptr, op.probe_f32, probe_out, plan->B, op.probe_L, op.probe_C, e->bf16, s);
+      err = to_channels_first_f32(op.probe_ptr, op.probe_f32, probe_out, plan->B, op.probe_L, op.probe_C, e->bf16, s, op.probe_ld);
       if (err != cudaSuccess) return e->fail(Q3TTS_CUDA_ERROR, std::string("probe failed: ") + cudaGetErrorString(err));
       if (pc) *pc = op.probe_C;
       if (pl) *pl = op.probe_L;

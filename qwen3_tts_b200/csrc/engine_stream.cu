@@ -30,16 +30,16 @@ struct SBuilder {
     off += bytes;
     return p;
   }
-  // history-prefixed buffer [S][H + n][C] 16-bit, registered for the state load / save kernels
-  void* hist_buf(int S, int H, int n, int C) {
-    void* p = alloc((size_t)S * (H + n) * C * 2);
+  // history-prefixed buffer [S][H + n][C] of `esz`-byte elements (2: 16-bit, 4: fp32), registered for the state load / save kernels
+  void* hist_buf(int S, int H, int n, int C, int esz = 2) {
+    void* p = alloc((size_t)S * (H + n) * C * esz);
     StreamBufDesc d;
-    d.ptr = (unsigned char*)p; d.batch_stride = (long long)(H + n) * C * 2; d.state_off = state_off; d.H = H; d.n = n; d.row_bytes = C * 2; d.pad = 0;
+    d.ptr = (unsigned char*)p; d.batch_stride = (long long)(H + n) * C * esz; d.state_off = state_off; d.H = H; d.n = n; d.row_bytes = C * esz; d.pad = 0;
     plan->descs.push_back(d);
-    state_off += (long long)H * C * 2;
+    state_off += (long long)H * C * esz;
     return p;
   }
-  static void* at_row(void* p, int row, int C) { return p ? (uint8_t*)p + (size_t)row * C * 2 : nullptr; }
+  static void* at_row(void* p, int row, int C, int esz = 2) { return p ? (uint8_t*)p + (size_t)row * C * esz : nullptr; }
 
   // in: [batches][a_rows][cin] (a_rows includes a_row0 history rows), rows_valid accumulator rows per batch item
   Op& gemm(const ConvW& w, const void* in, int batches, int a_rows, int a_row0, int rows_valid) {
@@ -54,12 +54,18 @@ struct SBuilder {
     for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
     p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
     p.bias = w.bias; p.bf16 = e->bf16 ? 1 : 0;
+    p.a_cols = w.a_cols; p.k_mult = w.k_mult;
     p.a_ptr = in; p.w_ptr = w.w;
     p.out_row_stride = w.n_total;
     p.out_batch_stride = (long long)rows_valid * w.n_total;
     // the A map is (re)built from p.a_ptr by gemm_make_epilogue_maps once every pointer of the plan is final
     if (!dry && make_tmap_3d(&op.g.tmB, w.w, (uint64_t)w.cin, (uint64_t)w.n_total, (uint64_t)w.taps, (uint32_t)w.kb, (uint32_t)w.bn, e->bf16))
       rc = e->fail(Q3TTS_CUDA_ERROR, "cuTensorMapEncodeTiled failed (weights)");
+    return op;
+  }
+  Op& split(const float* in, long long in_bs, void* out, long long out_bs, int batches, int rows, int C) {
+    Op& op = simple(OP_SPLIT);
+    op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C; op.sp_in_bs = in_bs; op.sp_out_bs = out_bs;
     return op;
   }
   Op& simple(OpType t) {
@@ -78,59 +84,78 @@ int build_stream(Engine* e, StreamPlan* plan, int S, int P, bool fresh, bool dry
   const int M = S * P;
   const size_t es = 2;
   b.simple(OP_STATE_LOAD);
+  const bool sp_main = e->pre_conv.k_mult == 3;   // split-precision main path (engine_plan.cu build(): same layout rules)
+  const bool sp_xf = !e->layers.empty() && e->layers[0].qkv.k_mult == 3;
+  const int Dw = sp_main ? 2 * D : D;             // width of a row of E: [hi | lo]
   // ---- RVQ -> E [S][2 | P][D]
-  void* E = b.hist_buf(S, 2, P, D);
-  { Op& op = b.simple(OP_RVQ); op.out = SBuilder::at_row(E, 2, D); op.B = S; op.L = P; op.C = D; op.aux0 = 2 + P; }
+  void* E = b.hist_buf(S, 2, P, Dw);
+  { Op& op = b.simple(OP_RVQ); op.out = SBuilder::at_row(E, 2, Dw); op.B = S; op.L = P; op.C = D; op.aux0 = 2 + P; op.split = sp_main ? 1 : 0; }
   // ---- pre_conv (k = 3 causal) -> Pb [S*P][Lat]
-  void* Pb = b.alloc((size_t)M * Lat * es);
-  { Op& op = b.gemm(e->pre_conv, E, S, 2 + P, 2, P); op.g.p.out_raw = Pb; }
+  void* Pb = b.alloc((size_t)M * Lat * (sp_main ? 4 : es));
+  void* Pb16 = sp_main ? b.alloc((size_t)M * 2 * Lat * es) : Pb;
+  {
+    Op& op = b.gemm(e->pre_conv, E, S, 2 + P, 2, P);
+    if (sp_main) op.g.p.out_f32 = (float*)Pb; else op.g.p.out_raw = Pb;
+  }
+  if (sp_main) b.split((const float*)Pb, (long long)M * Lat, Pb16, (long long)M * 2 * Lat, 1, M, Lat);
   // ---- transformer over the S*P new tokens, K/V ring cache per layer
   float* X = (float*)b.alloc((size_t)M * H * 4);
-  void* Hn = b.alloc((size_t)M * H * es);
+  void* Hn = b.alloc((size_t)M * H * es * 2);
   void* QKV = b.alloc((size_t)M * 3 * H * es);
   void* AO = b.alloc((size_t)M * H * es);
   void* MI = b.alloc((size_t)M * I * es);
-  void* TO = b.alloc((size_t)M * Lat * es);
-  { Op& op = b.gemm(e->in_proj, Pb, 1, M, 0, M); op.g.p.out_f32 = X; }
+  void* TO = b.alloc((size_t)M * Lat * (sp_main ? 4 : es));
+  void* TO16 = sp_main ? b.alloc((size_t)M * 2 * Lat * es) : TO;
+  { Op& op = b.gemm(e->in_proj, Pb16, 1, M, 0, M); op.g.p.out_f32 = X; }
   for (int l = 0; l < c.num_hidden_layers; ++l) {
     const LayerW& W = e->layers[l];
-    { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H; }
+    { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = W.ln1; op.B = M; op.C = H; op.split = sp_xf ? 1 : 0; }
     { Op& op = b.gemm(W.qkv, Hn, 1, M, 0, M); op.g.p.out_raw = QKV; }
     { Op& op = b.simple(OP_STREAM_ATTN); op.in = QKV; op.out = AO; op.B = S; op.L = P; op.aux0 = l; }
     { Op& op = b.gemm(W.o, AO, 1, M, 0, M); op.g.p.scale = W.ls1; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
-    { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H; }
+    { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = W.ln2; op.B = M; op.C = H; op.split = sp_xf ? 1 : 0; }
     { Op& op = b.gemm(W.gateup, Hn, 1, M, 0, M); op.g.p.act = ACT_GLU; op.g.p.out_raw = MI; op.g.p.out_row_stride = I; op.g.p.out_batch_stride = (long long)M * I; }
     { Op& op = b.gemm(W.down, MI, 1, M, 0, M); op.g.p.scale = W.ls2; op.g.p.res = X; op.g.p.res_f32 = 1; op.g.p.out_f32 = X; }
   }
-  { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; }
-  { Op& op = b.gemm(e->out_proj, Hn, 1, M, 0, M); op.g.p.out_raw = TO; }
+  { Op& op = b.simple(OP_RMSNORM); op.in = X; op.out = Hn; op.w0 = e->final_norm; op.B = M; op.C = H; op.split = sp_main ? 1 : 0; }
+  { Op& op = b.gemm(e->out_proj, Hn, 1, M, 0, M); if (sp_main) op.g.p.out_f32 = (float*)TO; else op.g.p.out_raw = TO; }
+  if (sp_main) b.split((const float*)TO, (long long)M * Lat, TO16, (long long)M * 2 * Lat, 1, M, Lat);
   // ---- upsample: [TransConv k = s ; ConvNeXt]; the depthwise k7 needs 6 rows of history
-  const void* cur = TO;  // dense [S][L][Lat]
+  const void* cur = TO16;  // dense [S][L][Lat] ([hi | lo] rows in split-precision plans)
+  const int ue = sp_main ? 4 : 2;   // element size of the main-path tensors Uo / V: fp32 in split-precision plans
+  const int Vw = sp_main ? 2 * Lat : Lat;  // row width of the 16-bit tensor the next GEMM reads
   int L = P;
-  void* dec_in = nullptr;  // [S][6 | L][Lat] input of decoder[0]
+  void* dec_in = nullptr;  // [S][6 | L][Vw] input of decoder[0]
   for (size_t i = 0; i < e->ups.size(); ++i) {
     const UpsampleW& U = e->ups[i];
     const int r = c.upsampling_ratios[i];
     const int Lo = L * r;
     const bool last = i + 1 == e->ups.size();
-    void* Uo = b.hist_buf(S, 6, Lo, Lat);
+    void* Uo = b.hist_buf(S, 6, Lo, Lat, ue);
     void* Nn = b.alloc((size_t)S * Lo * Lat * es);
     void* G = b.alloc((size_t)S * Lo * 4 * Lat * es);
-    void* V = last ? b.hist_buf(S, 6, Lo, Lat) : b.alloc((size_t)S * Lo * Lat * es);
+    // block output: dense fp32 + a [hi | lo] copy (split-precision), or 16-bit written straight by the epilogue; the last stage's
+    // 16-bit tensor carries decoder[0]'s 6 history rows
+    void* Vf = sp_main ? b.alloc((size_t)S * Lo * Lat * 4) : nullptr;
+    void* V = last ? b.hist_buf(S, 6, Lo, Vw) : b.alloc((size_t)S * Lo * Vw * es);
+    const long long V_bs = last ? (long long)(6 + Lo) * Vw : (long long)Lo * Vw;
+    void* Vrow0 = last ? SBuilder::at_row(V, 6, Vw) : V;
     {
       Op& op = b.gemm(U.tconv, cur, S, L, 0, L);  // one accumulator row -> r output rows of the stream's own buffer
-      op.g.p.out_raw = SBuilder::at_row(Uo, 6, Lat);
+      if (sp_main) op.g.p.out_f32 = (float*)SBuilder::at_row(Uo, 6, Lat, ue); else op.g.p.out_raw = SBuilder::at_row(Uo, 6, Lat);
       op.g.p.out_batch_stride = (long long)(6 + Lo) * Lat;
     }
-    { Op& op = b.simple(OP_DWLN); op.in = Uo; op.out = Nn; op.w0 = U.dww; op.w1 = U.dwb; op.w2 = U.lnw; op.w3 = U.lnb; op.B = S; op.L = Lo; op.C = Lat; op.aux0 = 6 + Lo; op.aux1 = 6; }
+    { Op& op = b.simple(OP_DWLN); op.in = Uo; op.out = Nn; op.w0 = U.dww; op.w1 = U.dwb; op.w2 = U.lnw; op.w3 = U.lnb; op.B = S; op.L = Lo; op.C = Lat; op.aux0 = 6 + Lo; op.aux1 = 6;
+      op.split = sp_main ? 1 : 0; }
     { Op& op = b.gemm(U.pw1, Nn, 1, S * Lo, 0, S * Lo); op.g.p.act = ACT_GELU; op.g.p.out_raw = G; }
     {
       Op& op = b.gemm(U.pw2, G, S, Lo, 0, Lo);
       op.g.p.scale = U.gamma;
-      op.g.p.res = SBuilder::at_row(Uo, 6, Lat); op.g.p.res_batch_stride = (long long)(6 + Lo) * Lat;
-      op.g.p.out_raw = last ? SBuilder::at_row(V, 6, Lat) : V;
-      op.g.p.out_batch_stride = last ? (long long)(6 + Lo) * Lat : (long long)Lo * Lat;
+      op.g.p.res = SBuilder::at_row(Uo, 6, Lat, ue); op.g.p.res_batch_stride = (long long)(6 + Lo) * Lat;
+      if (sp_main) { op.g.p.res_f32 = 1; op.g.p.out_f32 = (float*)Vf; op.g.p.out_batch_stride = (long long)Lo * Lat; }
+      else { op.g.p.out_raw = Vrow0; op.g.p.out_batch_stride = V_bs; }
     }
+    if (sp_main) b.split((const float*)Vf, (long long)Lo * Lat, Vrow0, V_bs, S, Lo, Lat);
     cur = V; L = Lo;
     if (last) dec_in = V;
   }
@@ -336,17 +361,18 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
       case OP_POS_ADVANCE: err = stream_advance_pos(e->d_slot_pos, d_ids, plan->S, plan->P, s); break;
       case OP_RVQ:
         err = rvq_decode(codes, sb, sk, st, e->rvq_tables, op.out, nullptr, op.B, c.num_quantizers, op.L, c.codebook_size, c.codebook_dim, e->bf16, s,
-                         op.aux0, identity_rows ? nullptr : d_rows, e->d_bad_code);
+                         op.aux0, identity_rows ? nullptr : d_rows, e->d_bad_code, op.split);
         break;
       case OP_GEMM: err = launch_conv_gemm(op.g, ENGINE_TC, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
-      case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s); break;
+      case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s, op.split); break;
+      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s); break;
       case OP_STREAM_ATTN:
         err = stream_attention(op.in, e->kcache[op.aux0], e->vcache[op.aux0], d_ids, e->d_slot_pos, e->rope_cos, e->rope_sin, e->rope_max, c.rope_theta,
                                op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->kv_ring, e->bf16, s);
         break;
       case OP_DWLN:
-        err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s, op.aux0, op.aux1);
+        err = dwconv_layernorm(op.in, op.w0, op.w1, op.w2, op.w3, op.out, op.B, op.L, op.C, 1e-6f, e->bf16, s, op.aux0, op.aux1, op.split != 0);
         break;
       case OP_TAIL:
         if (op.t.enabled) {

@@ -42,52 +42,59 @@ struct Fin {
       if (n % bn == 0) return bn;
     return 0;
   }
+  // k_mult / a_cols of a layer with `c` input channels for split factor sp (1 plain, 2 weights only, 3 weights and activations)
+  static void split_fields(ConvW& w, int c, int sp) {
+    w.k_mult = sp; w.cin = sp * c; w.a_cols = sp == 1 ? 0 : (sp == 2 ? c : 2 * c);
+  }
   void tiles(ConvW& w, int step = 32) {
     w.bn = choose_bn(w.n_total, step);
-    w.kb = (w.cin % 64 == 0) ? 64 : 32;
-    if (!rc && (w.bn == 0 || w.cin % w.kb != 0 || w.ncol_mod % 16 != 0))
+    w.kb = ((w.cin / w.k_mult) % 64 == 0) ? 64 : 32;  // a K block never straddles the hi / lo parts
+    if (!rc && (w.bn == 0 || (w.cin / w.k_mult) % w.kb != 0 || w.ncol_mod % 16 != 0))
       rc = e->fail(Q3TTS_BAD_CONFIG, "layer shape not tileable: n=" + std::to_string(w.n_total) + " cin=" + std::to_string(w.cin));
   }
   // Conv1d [cout][cin][k], dilation d, causal
-  ConvW conv(const std::string& prefix, int cout, int cin, int k, int dil, bool has_bias = true) {
+  ConvW conv(const std::string& prefix, int cout, int cin, int k, int dil, bool has_bias = true, int sp = 1) {
     ConvW w;
     const RawTensor* t = get(prefix + ".weight", {cout, cin, k});
     const RawTensor* b = has_bias ? get(prefix + ".bias", {cout}) : nullptr;
     if (rc) return w;
-    w.taps = k; w.n_total = cout; w.cin = cin; w.ncol_mod = cout;
+    w.taps = k; w.n_total = cout; w.ncol_mod = cout;
+    split_fields(w, cin, sp);
     for (int j = 0; j < k; ++j) w.tap_off[j] = -(k - 1 - j) * dil;
     w.bias = b ? b->d : nullptr;
-    w.w = alloc((size_t)cout * cin * k * 2);
-    if (!rc) check(pack_conv_weight(t->d, w.w, cout, cin, k, e->bf16, s), "pack_conv_weight");
+    w.w = alloc((size_t)cout * cin * k * 2 * sp);
+    if (!rc) check(pack_conv_weight(t->d, w.w, cout, cin, k, e->bf16, s, sp), "pack_conv_weight");
     tiles(w);
     return w;
   }
   // Linear [n][k]
-  ConvW linear(const std::string& prefix, int n, int k, bool has_bias) {
+  ConvW linear(const std::string& prefix, int n, int k, bool has_bias, int sp = 1) {
     ConvW w;
     const RawTensor* t = get(prefix + ".weight", {n, k});
     const RawTensor* b = has_bias ? get(prefix + ".bias", {n}) : nullptr;
     if (rc) return w;
-    w.taps = 1; w.n_total = n; w.cin = k; w.ncol_mod = n;
+    w.taps = 1; w.n_total = n; w.ncol_mod = n;
+    split_fields(w, k, sp);
     w.bias = b ? b->d : nullptr;
-    w.w = alloc((size_t)n * k * 2);
-    if (!rc) check(pack_cast(t->d, w.w, (long long)n * k, e->bf16, s), "pack_cast");
+    w.w = alloc((size_t)n * k * 2 * sp);
+    if (!rc) check(pack_rows(t->d, w.w, n, k, e->bf16, s, sp), "pack_rows");
     tiles(w);
     return w;
   }
   // ConvTranspose1d [cin][cout][k], stride st (k == 2*st or k == st)
-  ConvW tconv(const std::string& prefix, int cin, int cout, int k, int st) {
+  ConvW tconv(const std::string& prefix, int cin, int cout, int k, int st, int sp = 1) {
     ConvW w;
     const RawTensor* t = get(prefix + ".weight", {cin, cout, k});
     const RawTensor* b = get(prefix + ".bias", {cout});
     if (rc) return w;
     if (k != st && k != 2 * st) { rc = e->fail(Q3TTS_BAD_CONFIG, "transposed conv needs k == stride or k == 2*stride"); return w; }
-    w.taps = k / st; w.n_total = st * cout; w.cin = cin; w.ncol_mod = cout;
+    w.taps = k / st; w.n_total = st * cout; w.ncol_mod = cout;
+    split_fields(w, cin, sp);
     w.tap_off[0] = 0; w.tap_off[1] = 1;
     w.bias = b->d;
     w.out_rows_per_row = st;
-    w.w = alloc((size_t)cin * cout * k * 2);
-    if (!rc) check(pack_transconv_weight(t->d, w.w, cin, cout, k, st, e->bf16, s), "pack_transconv_weight");
+    w.w = alloc((size_t)cin * cout * k * 2 * sp);
+    if (!rc) check(pack_transconv_weight(t->d, w.w, cin, cout, k, st, e->bf16, s, sp), "pack_transconv_weight");
     tiles(w);
     return w;
   }
@@ -111,7 +118,12 @@ struct Fin {
 }  // namespace
 
 int engine_finalize(Engine* e, int mode) {
-  if (mode != Q3TTS_MODE_FP16 && mode != Q3TTS_MODE_BF16) return e->fail(Q3TTS_BAD_CONFIG, "unknown compute mode");
+  if (mode < 0 || mode > Q3TTS_MODE_BF16_SPLIT_ALL) return e->fail(Q3TTS_BAD_CONFIG, "unknown compute mode");
+  const int variant = mode >> 1;  // 0 default (main path split), 1 plain, 2 every early-stage GEMM split
+  e->split_level = variant == 0 ? 1 : (variant == 1 ? 0 : 2);
+  const int sp_main = e->split_level >= 1 ? 3 : 1;   // weights + activations hi/lo on the main signal path
+  const int sp_xf_a = e->split_level >= 2 ? 3 : 1;   // transformer GEMMs fed by an RMSNorm (its output can be written hi/lo)
+  const int sp_xf_w = e->split_level >= 2 ? 2 : 1;   // GEMMs whose A comes from a tensor-core epilogue in 16 bit: weights only
   const q3tts_config& c = e->cfg;
   if (c.head_dim != 64) return e->fail(Q3TTS_BAD_CONFIG, "attention kernel is specialised for head_dim 64");
   if (c.num_key_value_heads != c.num_attention_heads) return e->fail(Q3TTS_BAD_CONFIG, "GQA (kv heads != heads) not supported");
@@ -122,7 +134,7 @@ int engine_finalize(Engine* e, int mode) {
   e->owned.clear();
   e->plans.clear();
   e->finalized = false;
-  e->bf16 = (mode == Q3TTS_MODE_BF16);
+  e->bf16 = (mode & 1) != 0;
   // kernel attributes (shared-memory opt-ins) are per device: set them for THIS handle's device every time, so a second handle on
   // another GPU of the same process launches with the same limits as the first
   if (gemm_setup(e->device)) return e->fail(Q3TTS_CUDA_ERROR, "gemm_setup failed (cuTensorMapEncodeTiled unavailable or smem opt-in rejected)");
@@ -154,9 +166,9 @@ int engine_finalize(Engine* e, int mode) {
     f.check(fold_codebook(es->d, cu->d, wo->d, e->rvq_tables + (size_t)k * c.codebook_size * D, c.codebook_size, dq, D, f.s), "fold_codebook");
   }
   // ---- pre_conv + transformer
-  e->pre_conv = f.conv("pre_conv.conv", Lat, D, 3, 1);
-  e->in_proj = f.linear("pre_transformer.input_proj", H, Lat, true);
-  e->out_proj = f.linear("pre_transformer.output_proj", Lat, H, true);
+  e->pre_conv = f.conv("pre_conv.conv", Lat, D, 3, 1, true, sp_main);
+  e->in_proj = f.linear("pre_transformer.input_proj", H, Lat, true, sp_main);
+  e->out_proj = f.linear("pre_transformer.output_proj", Lat, H, true, sp_main);
   e->final_norm = f.vec("pre_transformer.norm.weight", H);
   e->layers.assign(c.num_hidden_layers, LayerW());
   for (int l = 0; l < c.num_hidden_layers && !f.rc; ++l) {
@@ -166,23 +178,26 @@ int engine_finalize(Engine* e, int mode) {
     const RawTensor* k = f.get(p + "self_attn.k_proj.weight", {H, H});
     const RawTensor* v = f.get(p + "self_attn.v_proj.weight", {H, H});
     if (f.rc) break;
-    L.qkv.taps = 1; L.qkv.n_total = 3 * H; L.qkv.cin = H; L.qkv.ncol_mod = 3 * H;
-    L.qkv.w = f.alloc((size_t)3 * H * H * 2);
+    L.qkv.taps = 1; L.qkv.n_total = 3 * H; L.qkv.ncol_mod = 3 * H;
+    Fin::split_fields(L.qkv, H, sp_xf_a);
+    const size_t part = (size_t)H * H * 2 * sp_xf_a;
+    L.qkv.w = f.alloc(3 * part);
     if (f.rc) break;
-    f.check(pack_cast(q->d, L.qkv.w, (long long)H * H, e->bf16, f.s), "pack q");
-    f.check(pack_cast(k->d, (uint8_t*)L.qkv.w + (size_t)H * H * 2, (long long)H * H, e->bf16, f.s), "pack k");
-    f.check(pack_cast(v->d, (uint8_t*)L.qkv.w + (size_t)2 * H * H * 2, (long long)H * H, e->bf16, f.s), "pack v");
+    f.check(pack_rows(q->d, L.qkv.w, H, H, e->bf16, f.s, sp_xf_a), "pack q");
+    f.check(pack_rows(k->d, (uint8_t*)L.qkv.w + part, H, H, e->bf16, f.s, sp_xf_a), "pack k");
+    f.check(pack_rows(v->d, (uint8_t*)L.qkv.w + 2 * part, H, H, e->bf16, f.s, sp_xf_a), "pack v");
     f.tiles(L.qkv);
-    L.o = f.linear(p + "self_attn.o_proj", H, H, false);
+    L.o = f.linear(p + "self_attn.o_proj", H, H, false, sp_xf_w);
     const RawTensor* g = f.get(p + "mlp.gate_proj.weight", {I, H});
     const RawTensor* u = f.get(p + "mlp.up_proj.weight", {I, H});
     if (f.rc) break;
-    L.gateup.taps = 1; L.gateup.n_total = 2 * I; L.gateup.cin = H; L.gateup.ncol_mod = 2 * I;
-    L.gateup.w = f.alloc((size_t)2 * I * H * 2);
+    L.gateup.taps = 1; L.gateup.n_total = 2 * I; L.gateup.ncol_mod = 2 * I;
+    Fin::split_fields(L.gateup, H, sp_xf_a);
+    L.gateup.w = f.alloc((size_t)2 * I * H * 2 * sp_xf_a);
     if (f.rc) break;
-    f.check(pack_interleave2(g->d, u->d, L.gateup.w, I, H, e->bf16, f.s), "pack gate/up");
+    f.check(pack_interleave2(g->d, u->d, L.gateup.w, I, H, e->bf16, f.s, sp_xf_a), "pack gate/up");
     f.tiles(L.gateup, 64);
-    L.down = f.linear(p + "mlp.down_proj", H, I, false);
+    L.down = f.linear(p + "mlp.down_proj", H, I, false, sp_xf_w);
     L.ln1 = f.vec(p + "input_layernorm.weight", H);
     L.ln2 = f.vec(p + "post_attention_layernorm.weight", H);
     L.ls1 = f.vec(p + "self_attn_layer_scale.scale", H);
@@ -194,7 +209,7 @@ int engine_finalize(Engine* e, int mode) {
     const std::string p = "upsample." + std::to_string(i) + ".";
     const int r = c.upsampling_ratios[i];
     UpsampleW& U = e->ups[i];
-    U.tconv = f.tconv(p + "0.conv", Lat, Lat, r, r);
+    U.tconv = f.tconv(p + "0.conv", Lat, Lat, r, r, sp_main);
     const RawTensor* dw = f.get(p + "1.dwconv.conv.weight", {Lat, 1, 7});
     if (f.rc) break;
     float* dww = (float*)f.alloc((size_t)7 * Lat * sizeof(float));
@@ -205,12 +220,12 @@ int engine_finalize(Engine* e, int mode) {
     U.lnw = f.vec(p + "1.norm.weight", Lat);
     U.lnb = f.vec(p + "1.norm.bias", Lat);
     U.gamma = f.vec(p + "1.gamma", Lat);
-    U.pw1 = f.linear(p + "1.pwconv1", 4 * Lat, Lat, true);
-    U.pw2 = f.linear(p + "1.pwconv2", Lat, 4 * Lat, true);
+    U.pw1 = f.linear(p + "1.pwconv1", 4 * Lat, Lat, true, sp_xf_w);
+    U.pw2 = f.linear(p + "1.pwconv2", Lat, 4 * Lat, true, sp_xf_w);
   }
   // ---- vocoder
   const int Dd = c.decoder_dim;
-  e->dec0 = f.conv("decoder.0.conv", Dd, Lat, 7, 1);
+  e->dec0 = f.conv("decoder.0.conv", Dd, Lat, 7, 1, true, sp_main);
   e->blocks.assign(c.num_upsample_rates, BlockW());
   int total_up = 1, look = 0;
   for (int i = 0; i < c.num_upsampling_ratios; ++i) total_up *= c.upsampling_ratios[i];

@@ -50,6 +50,12 @@ struct GemmParams {
   //   mode 2: batch item gc / pack_cpb, rows [(gc % pack_cpb) * 32, +32)
   // so a tile is filled with real rows instead of one batch item's few rows plus padding.  0 = one batch item per tile.
   int pack_mode, pack_rshift, pack_cpb;
+  // Split-precision operands (more mantissa than one 16-bit value where it is cheap: DESIGN.md "Precision").  cin is the K the
+  // MMAs walk (k_mult x the layer's real input channels); the A tensor in memory is a_cols wide and K blocks wrap around it:
+  //   k_mult 2, a_cols = C  :  A = a            W' = [w_hi | w_lo]           (weights carried as hi + lo)
+  //   k_mult 3, a_cols = 2C :  A = [a_hi | a_lo] W' = [w_hi | w_hi | w_lo]   (a_hi w_hi + a_lo w_hi + a_hi w_lo: ~21 bits each side)
+  // a_cols = 0: plain (a_cols = cin, k_mult = 1).
+  int a_cols, k_mult;
   int skip_raw;  // fused unit kernel: y is not stored (last unit of a block: only snake_next(y) is read downstream)
   int dbg;  // debug experiments (env Q3TTS_DBG): bit 0 = epilogue only drains TMEM, bit 1 = MMA thread issues no MMAs
   const float* bias;

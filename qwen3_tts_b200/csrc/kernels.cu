@@ -17,24 +17,37 @@ static inline int nblocks(long long n, int threads, int cap = 148 * 32) {
   } while (0)
 
 // ============================================================================================ packers
+// One packed weight element of row `row`, input channel ci (of cin): plain (m = 1), or carried as hi + lo for the split-precision
+// GEMMs (gemm_params.h): m = 2 -> [hi | lo], m = 3 -> [hi | hi | lo] (the K' order that meets A = [a_hi | a_lo | a_hi]).
 template <typename T>
-__global__ void k_pack_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int k) {
+__device__ __forceinline__ void put_w(T* __restrict__ dst, long long row, int ci, int cin, int m, float v) {
+  T* r = dst + row * (long long)(m * cin);
+  const T hi = Elem<T>::from_f(v);
+  r[ci] = hi;
+  if (m > 1) {
+    const T lo = Elem<T>::from_f(v - Elem<T>::to_f(hi));
+    if (m == 2) r[cin + ci] = lo;
+    else { r[cin + ci] = hi; r[2 * cin + ci] = lo; }
+  }
+}
+template <typename T>
+__global__ void k_pack_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int k, int m) {
   const long long n = (long long)cout * cin * k;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const int ci = (int)(i % cin);
     const int co = (int)((i / cin) % cout);
     const int j = (int)(i / ((long long)cin * cout));
-    dst[i] = Elem<T>::from_f(src[((long long)co * cin + ci) * k + j]);
+    put_w<T>(dst, (long long)j * cout + co, ci, cin, m, src[((long long)co * cin + ci) * k + j]);
   }
 }
-cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s) {
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split) {
   const long long n = (long long)cout * cin * k;
-  Q3_DISPATCH(bf16, (k_pack_conv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cout, cin, k)));
+  Q3_DISPATCH(bf16, (k_pack_conv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cout, cin, k, split)));
   return cudaGetLastError();
 }
 
 template <typename T>
-__global__ void k_pack_transconv(const float* __restrict__ src, T* __restrict__ dst, int cin, int cout, int k, int st) {
+__global__ void k_pack_transconv(const float* __restrict__ src, T* __restrict__ dst, int cin, int cout, int k, int st, int m) {
   const int taps = k / st;  // 2 (k = 2*st) or 1 (k = st)
   const long long n = (long long)taps * st * cout * cin;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -45,27 +58,27 @@ __global__ void k_pack_transconv(const float* __restrict__ src, T* __restrict__ 
     const int tap = (int)(r / ((long long)cout * st));
     // tap 0 multiplies x[q]; for k = 2*st that is kernel index p + st, tap 1 (x[q+1]) is index p
     const int kk = (taps == 2) ? (tap == 0 ? p + st : p) : p;
-    dst[i] = Elem<T>::from_f(src[((long long)ci * cout + co) * k + kk]);
+    put_w<T>(dst, r, ci, cin, m, src[((long long)ci * cout + co) * k + kk]);
   }
 }
-cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s) {
+cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s, int split) {
   const long long n = (long long)cin * cout * k;
-  Q3_DISPATCH(bf16, (k_pack_transconv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cin, cout, k, st)));
+  Q3_DISPATCH(bf16, (k_pack_transconv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cin, cout, k, st, split)));
   return cudaGetLastError();
 }
 
 template <typename T>
-__global__ void k_pack_interleave2(const float* __restrict__ a, const float* __restrict__ b, T* __restrict__ dst, int n, int k) {
+__global__ void k_pack_interleave2(const float* __restrict__ a, const float* __restrict__ b, T* __restrict__ dst, int n, int k, int m) {
   const long long tot = 2ll * n * k;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < tot; i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % k);
     const long long r = i / k;
     const float* src = (r & 1) ? b : a;
-    dst[i] = Elem<T>::from_f(src[(r >> 1) * k + c]);
+    put_w<T>(dst, r, c, k, m, src[(r >> 1) * k + c]);
   }
 }
-cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s) {
-  Q3_DISPATCH(bf16, (k_pack_interleave2<T><<<nblocks(2ll * n * k, 256), 256, 0, s>>>(a, b, (T*)dst, n, k)));
+cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s, int split) {
+  Q3_DISPATCH(bf16, (k_pack_interleave2<T><<<nblocks(2ll * n * k, 256), 256, 0, s>>>(a, b, (T*)dst, n, k, split)));
   return cudaGetLastError();
 }
 
@@ -76,6 +89,18 @@ __global__ void k_pack_cast(const float* __restrict__ src, T* __restrict__ dst, 
 }
 cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaStream_t s) {
   Q3_DISPATCH(bf16, (k_pack_cast<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, n)));
+  return cudaGetLastError();
+}
+
+// [rows][k] fp32 -> [rows][split * k] 16-bit (linear weights; split as in put_w)
+template <typename T>
+__global__ void k_pack_rows(const float* __restrict__ src, T* __restrict__ dst, long long rows, int k, int m) {
+  const long long n = rows * k;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    put_w<T>(dst, i / k, (int)(i % k), k, m, src[i]);
+}
+cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split) {
+  Q3_DISPATCH(bf16, (k_pack_rows<T><<<nblocks(rows * k, 256), 256, 0, s>>>(src, (T*)dst, rows, k, split)));
   return cudaGetLastError();
 }
 

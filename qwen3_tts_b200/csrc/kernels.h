@@ -7,12 +7,16 @@ namespace q3 {
 
 // ---- load-time packers (fp32 reference layouts -> 16-bit K-major GEMM operands)
 // Conv1d weight [Cout][Cin][k] -> [k][Cout][Cin]
-cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s);
+// `split` (every packer below): 1 = one 16-bit value per weight; 2 / 3 = weights carried as hi + lo along K for the split-precision
+// GEMMs (gemm_params.h): rows become split * cin wide, [hi | lo] or [hi | hi | lo].
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split = 1);
 // ConvTranspose1d weight [Cin][Cout][k], stride st.  k == 2*st: two taps, tap0 (x[q]) = W[..., p+st],
 // tap1 (x[q+1]) = W[..., p]; k == st: one tap W[..., p].  dst [taps][st*Cout][Cin], row = p*Cout + co.
-cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s);
+cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s, int split = 1);
 // rows of `a` and `b` ([n][k] each) interleaved: dst[2i] = a[i], dst[2i+1] = b[i]
-cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s);
+cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s, int split = 1);
+// [rows][k] fp32 -> [rows][split * k] 16-bit
+cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split = 1);
 // plain cast [n] fp32 -> 16-bit
 cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaStream_t s);
 // Snake: a = exp(alpha), ib = 1/(exp(beta)+1e-9)
@@ -28,9 +32,14 @@ cudaError_t fold_codebook(const float* embedding_sum, const float* cluster_usage
 cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaStream_t s);
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
                        int Q, int T, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows = 0, const int* src_index = nullptr,
-                       int* bad_code = nullptr);  // bad_code (device int, optional): set to 1 when a code is outside [0, ncodes)
+                       int* bad_code = nullptr,   // bad_code (device int, optional): set to 1 when a code is outside [0, ncodes)
+                       int split = 0);            // 1: out_act rows are [hi | lo] (2 * D wide): the split-precision A operand of pre_conv
 // x fp32 [M][H] -> 16-bit [M][H]: w * x * rsqrt(mean(x^2) + eps)
-cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s);
+// split = 1: out rows are [hi | lo] (2 * H wide)
+cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s, int split = 0);
+// fp32 [B][rows][C] (in_bs elements between items) -> 16-bit [B][.][2C] rows [hi | lo] (out_bs elements between items): turns an fp32
+// main-path tensor into the split-precision A operand of the next GEMM
+cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s);
 // rope table [maxT][hd/2] cos, sin (fp32)
 cudaError_t rope_table(float* cos_t, float* sin_t, int maxT, int hd, float theta, cudaStream_t s);
 // qkv 16-bit [B*T][3*nh*hd] (q | k | v), RoPE applied on the fly with position = t; causal, kv > q - window.
@@ -38,7 +47,7 @@ cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* 
                               bool bf16, cudaStream_t s);
 // ConvNeXt front half: depthwise causal conv k=7 + bias, LayerNorm(eps) over C.  x,out 16-bit [B][L][C]; dw weight [7][C] fp32.
 cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
-                             float eps, bool bf16, cudaStream_t s, int in_bs_rows = 0, int hist = 0);
+                             float eps, bool bf16, cudaStream_t s, int in_bs_rows = 0, int hist = 0, bool x_f32 = false);  // x_f32: x is fp32
 // per-device opt-in to > 48 KB dynamic shared memory for the attention kernels (called once per handle by engine_finalize)
 cudaError_t attention_setup();
 cudaError_t stream_attention_setup();
@@ -62,7 +71,7 @@ cudaError_t stream_advance_pos(int* slot_pos, const int* slot_ids, int S, int P,
 // out[index[b]][0:len] = in[b][0:len]  (fp32 rows)
 cudaError_t scatter_rows_f32(const float* in, long long in_stride, float* out, long long out_stride, const int* index, int B, long long len, cudaStream_t s);
 // probes: activation [B][L][C] (16-bit or fp32) -> fp32 [B][C][L]
-cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s);
+cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s, int ld = 0);  // ld: row pitch (0 = C)
 // dw weight [C][1][7] -> [7][C]
 cudaError_t pack_dw_weight(const float* src, float* dst, int C, int k, cudaStream_t s);
 

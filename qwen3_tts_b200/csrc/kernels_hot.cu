@@ -24,7 +24,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 template <typename T>
 __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long long sk, long long st, const float* __restrict__ tables,
                       T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D, int out_bs_rows,
-                      const int* __restrict__ src_index, int* __restrict__ bad_code) {
+                      const int* __restrict__ src_index, int* __restrict__ bad_code, int split) {
   const int t = blockIdx.x, b = blockIdx.y;
   const int bs = src_index ? src_index[b] : b;  // row of the caller's codes tensor this batch item reads
   const int d = threadIdx.x * 4;
@@ -47,7 +47,15 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
     uint2 o;
     o.x = Elem<T>::pack2(v.x, v.y);
     o.y = Elem<T>::pack2(v.z, v.w);
-    *reinterpret_cast<uint2*>(out_act + ((long long)b * out_bs_rows + t) * D + d) = o;
+    T* row = out_act + ((long long)b * out_bs_rows + t) * (split ? 2 * D : D);
+    *reinterpret_cast<uint2*>(row + d) = o;
+    if (split) {  // rows are [hi | lo]: what the first 16-bit value lost goes into a second one (split-precision A operand)
+      const float2 h0 = Elem<T>::unpack2(o.x), h1 = Elem<T>::unpack2(o.y);
+      uint2 l;
+      l.x = Elem<T>::pack2(v.x - h0.x, v.y - h0.y);
+      l.y = Elem<T>::pack2(v.z - h1.x, v.w - h1.y);
+      *reinterpret_cast<uint2*>(row + D + d) = l;
+    }
   }
   if (out_f32) {
     float* o = out_f32 + ((long long)b * D + d) * Tn + t;
@@ -55,12 +63,12 @@ __global__ void k_rvq(const long long* __restrict__ codes, long long sb, long lo
   }
 }
 cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long long st, const float* tables, void* out_act, float* out_f32, int B,
-                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows, const int* src_index, int* bad_code) {
+                       int Q, int Tn, int ncodes, int D, bool bf16, cudaStream_t s, int out_bs_rows, const int* src_index, int* bad_code, int split) {
   if (B <= 0 || Tn <= 0) return cudaSuccess;
   if (out_bs_rows <= 0) out_bs_rows = Tn;
   dim3 grid(Tn, B);
   const int threads = ((D / 4 + 31) / 32) * 32;
-  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index, bad_code)));
+  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index, bad_code, split)));
   return cudaGetLastError();
 }
 
@@ -78,7 +86,7 @@ cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaSt
 // ============================================================================================ RMSNorm
 // One warp per row (reference modeling :382-387, computed in fp32).
 template <typename T>
-__global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__ w, T* __restrict__ out, int M, int H, float eps) {
+__global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__ w, T* __restrict__ out, int M, int H, float eps, int split) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= M) return;
@@ -95,15 +103,24 @@ __global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__
   for (int i = lane; i < n4; i += 32) {
     const float4 v = xr[i];
     const float4 g = __ldg(wr + i);
+    const float y0 = g.x * (v.x * r), y1 = g.y * (v.y * r), y2 = g.z * (v.z * r), y3 = g.w * (v.w * r);
     uint2 o;
-    o.x = Elem<T>::pack2(g.x * (v.x * r), g.y * (v.y * r));
-    o.y = Elem<T>::pack2(g.z * (v.z * r), g.w * (v.w * r));
-    *reinterpret_cast<uint2*>(out + (long long)row * H + i * 4) = o;
+    o.x = Elem<T>::pack2(y0, y1);
+    o.y = Elem<T>::pack2(y2, y3);
+    T* orow = out + (long long)row * (split ? 2 * H : H);
+    *reinterpret_cast<uint2*>(orow + i * 4) = o;
+    if (split) {
+      const float2 h0 = Elem<T>::unpack2(o.x), h1 = Elem<T>::unpack2(o.y);
+      uint2 l;
+      l.x = Elem<T>::pack2(y0 - h0.x, y1 - h0.y);
+      l.y = Elem<T>::pack2(y2 - h1.x, y3 - h1.y);
+      *reinterpret_cast<uint2*>(orow + H + i * 4) = l;
+    }
   }
 }
-cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s) {
+cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s, int split) {
   if (M <= 0) return cudaSuccess;
-  Q3_DISPATCH(bf16, (k_rmsnorm<T><<<(M + 7) / 8, 256, 0, s>>>(x, w, (T*)out, M, H, eps)));
+  Q3_DISPATCH(bf16, (k_rmsnorm<T><<<(M + 7) / 8, 256, 0, s>>>(x, w, (T*)out, M, H, eps, split)));
   return cudaGetLastError();
 }
 

@@ -19,9 +19,9 @@ __device__ __forceinline__ float warp_sum2(float v) {
 // ============================================================================================ dwconv + LN
 // One warp per output row; lane owns channels {4*lane + 128*i .. +3}.  Depthwise causal conv k=7
 // (left zero padding, reference modeling :213-219, :189-192) then LayerNorm over C (modeling :220, :231).
-template <typename T, int NI>
+template <typename T, int NI, typename XT>
 __global__ void __launch_bounds__(256)
-k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float* __restrict__ dwb, const float* __restrict__ lnw,
+k_dwconv_ln(const XT* __restrict__ x, const float* __restrict__ dww, const float* __restrict__ dwb, const float* __restrict__ lnw,
             const float* __restrict__ lnb, T* __restrict__ out, int B, int L, int C, float eps, int in_bs_rows, int hist) {
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -38,12 +38,18 @@ k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float*
   for (int j = 0; j < 7; ++j) {
     const int lt = hist + l - 6 + j;
     if (lt < 0) continue;
-    const T* xr = x + (in_row - 6 + j) * C;
+    const XT* xr = x + (in_row - 6 + j) * C;
 #pragma unroll
     for (int i = 0; i < NI; ++i) {
       const int c = 4 * lane + 128 * i;
-      const uint2 u = *reinterpret_cast<const uint2*>(xr + c);
-      const float2 a = Elem<T>::unpack2(u.x), bq = Elem<T>::unpack2(u.y);
+      float2 a, bq;
+      if (sizeof(XT) == 4) {  // fp32 main-path tensor (split-precision plans keep the ConvNeXt input in fp32)
+        const float4 f = *reinterpret_cast<const float4*>(xr + c);
+        a = make_float2(f.x, f.y); bq = make_float2(f.z, f.w);
+      } else {
+        const uint2 u = *reinterpret_cast<const uint2*>(xr + c);
+        a = Elem<T>::unpack2(u.x); bq = Elem<T>::unpack2(u.y);
+      }
       const float4 w = __ldg(reinterpret_cast<const float4*>(dww + (long long)j * C + c));
       acc[i][0] = fmaf(w.x, a.x, acc[i][0]);
       acc[i][1] = fmaf(w.y, a.y, acc[i][1]);
@@ -73,19 +79,50 @@ k_dwconv_ln(const T* __restrict__ x, const float* __restrict__ dww, const float*
   }
 }
 cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, const float* lnw, const float* lnb, void* out, int B, int L, int C,
-                             float eps, bool bf16, cudaStream_t s, int in_bs_rows, int hist) {
+                             float eps, bool bf16, cudaStream_t s, int in_bs_rows, int hist, bool x_f32) {
   if (in_bs_rows <= 0) in_bs_rows = L;
   if (C != 1024) return cudaErrorInvalidValue;  // NI = C / 128 is a compile-time unroll
   const long long rows = (long long)B * L;
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)((rows + 7) / 8);
-  Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
+  if (x_f32) Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8, float><<<blocks, 256, 0, s>>>((const float*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
+  else Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8, T><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
+  return cudaGetLastError();
+}
+
+// ============================================================================================ fp32 -> [hi | lo]
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_split_f32(const float* __restrict__ in, long long in_bs, T* __restrict__ out, long long out_bs, int rows, int C) {
+  const int b = blockIdx.y;
+  const int c4 = C >> 2;
+  const long long n = (long long)rows * c4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / c4;
+    const int c = (int)(i - r * c4) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(in + b * in_bs + r * C + c);
+    uint2 h, l;
+    h.x = Elem<T>::pack2(v.x, v.y); h.y = Elem<T>::pack2(v.z, v.w);
+    const float2 h0 = Elem<T>::unpack2(h.x), h1 = Elem<T>::unpack2(h.y);
+    l.x = Elem<T>::pack2(v.x - h0.x, v.y - h0.y); l.y = Elem<T>::pack2(v.z - h1.x, v.w - h1.y);
+    T* o = out + b * out_bs + r * (2ll * C);
+    *reinterpret_cast<uint2*>(o + c) = h;
+    *reinterpret_cast<uint2*>(o + C + c) = l;
+  }
+}
+cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s) {
+  if (B <= 0 || rows <= 0) return cudaSuccess;
+  if (C % 4) return cudaErrorInvalidValue;
+  long long bx = ((long long)rows * (C >> 2) + 255) / 256;
+  if (bx > 148 * 8) bx = 148 * 8;
+  dim3 grid((unsigned)bx, (unsigned)B);
+  Q3_DISPATCH(bf16, (k_split_f32<T><<<grid, 256, 0, s>>>(in, in_bs, (T*)out, out_bs, rows, C)));
   return cudaGetLastError();
 }
 
 // ============================================================================================ probes
 template <typename T>
-__global__ void k_to_cf(const void* __restrict__ x, bool is_f32, float* __restrict__ out, int L, int C) {
+__global__ void k_to_cf(const void* __restrict__ x, bool is_f32, float* __restrict__ out, int L, int C, int ld) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z;
   const int l0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -93,7 +130,7 @@ __global__ void k_to_cf(const void* __restrict__ x, bool is_f32, float* __restri
     const int l = l0 + r, c = c0 + threadIdx.x;
     float v = 0.f;
     if (l < L && c < C) {
-      const long long idx = ((long long)b * L + l) * C + c;
+      const long long idx = ((long long)b * L + l) * ld + c;
       v = is_f32 ? reinterpret_cast<const float*>(x)[idx] : Elem<T>::to_f(reinterpret_cast<const T*>(x)[idx]);
     }
     tile[r][threadIdx.x] = v;
@@ -104,10 +141,11 @@ __global__ void k_to_cf(const void* __restrict__ x, bool is_f32, float* __restri
     if (l < L && c < C) out[((long long)b * C + c) * L + l] = tile[threadIdx.x][r];
   }
 }
-cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s) {
+cudaError_t to_channels_first_f32(const void* x, bool is_f32, float* out, int B, int L, int C, bool bf16, cudaStream_t s, int ld) {
+  if (ld <= 0) ld = C;
   if (B <= 0 || L <= 0) return cudaSuccess;
   dim3 grid((L + 31) / 32, (C + 31) / 32, B), block(32, 8);
-  Q3_DISPATCH(bf16, (k_to_cf<T><<<grid, block, 0, s>>>(x, is_f32, out, L, C)));
+  Q3_DISPATCH(bf16, (k_to_cf<T><<<grid, block, 0, s>>>(x, is_f32, out, L, C, ld)));
   return cudaGetLastError();
 }
 

@@ -65,7 +65,7 @@ class Qwen3TTSTokenizerV2Decoder:
         if not torch.cuda.is_available():
             raise RuntimeError("CUDA is not available; the B200-native decoder has no CPU fallback")
         self.total_upsample = config.total_upsample
-        self.compute_mode = {"fp16": _capi.MODE_FP16, "bf16": _capi.MODE_BF16}[compute_mode]
+        self.compute_mode = _capi.MODES[compute_mode]
         self._lib = _capi.load_library()
         self._h = C.c_void_p()
         dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
