@@ -12,7 +12,13 @@ architecture (no checkpoint is mounted).  With N > 1 every rank decodes its own 
   value  : audio-seconds decoded per second, codes already resident in HBM (CUDA events)
   e2e    : same metric through the public API Qwen3TTSTokenizer.decode with HOST codes in pinned
            memory: pad, H2D, decode, length rule, D2H into host float32 arrays, every step
-  roofline / cpu_baseline / clocks / gpu_launches : see DESIGN.md "Measurement"
+  roofline : per-kernel CUDA-event times recorded INSIDE the timed steps (the engine's accumulating profile), dominant kernel =
+           the one with the largest share of the step; traffic is null here (DRAM bytes need ncu: profiles/r2_ncu_*.txt)
+  cpu_baseline / --impl reference : the UNMODIFIED reference decoder (oracle/_ref staged by oracle/stage_ref.py, imported through
+           oracle/ref_shim.py) on the host cores, 4 utterances of the workload in one batch per step
+  torch_gpu : context only - the same unmodified reference in eager PyTorch on this B200 (bulk decode and the reference-style
+           streaming chunk call), never the product path
+  clocks / gpu_launches : see DESIGN.md "Measurement"
 """
 from __future__ import annotations
 
@@ -37,18 +43,9 @@ WORKLOADS = {  # name -> (utterances per GPU per step, frames per utterance, BAS
     "bulk30s": (64, 375, "Offline bulk decode of 30 s utterances, one batch of 64 per GPU per step (4096 utterances = 64 such steps at N=1, "
                          "utterance-sharded over N GPUs; chunks 300 / 25+75; BASELINE config 5)"),
 }
+WORKLOADS_NAME = WORKLOADS["bulk10s"][2]
 FRAME_SEC = 0.08
 GFLOP_PER_FRAME = 5.1226  # 2 x 2561.30 MMAC per emitted code frame
-
-
-def ncu_traffic(family: str):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch (average over the family's launches of one forward of this workload)
-    from the committed ncu capture profiles/r1_dram_traffic_forward.json (tools/gpu_round_h.sh); None when there is no capture."""
-    p = os.path.join(ROOT, "profiles", "r1_dram_traffic_forward.json")
-    key = {"tcgen05_conv_gemm": "_tcgen05_conv_gemm_family", "tcgen05_fused_unit": "unit_kernel"}.get(family)
-    if B_UTT != 64 or T_FRAMES != 125 or key is None or not os.path.isfile(p):
-        return None
-    return json.load(open(p)).get(key, {}).get("dram_bytes_per_launch_avg")
 
 
 def load_peaks():
@@ -140,46 +137,127 @@ class ClockSampler:
                 "source": self.source}
 
 
-def cpu_reference_run(steps: int, warmup: int, utterances: int = 1):
-    """The reference's algorithm on the host cores: the oracle port (oracle/decoder_oracle.py, pinned to the
-    unmodified reference by tests/golden) decoding `utterances` x 10 s of the same workload per step."""
+# ------------------------------------------------------------------------------------------------ reference (baseline legs only)
+REF_UTTERANCES = 4  # bounded sample of the workload the CPU legs decode per step, in ONE batch
+
+
+def load_reference(device: str = "cpu"):
+    """The reference's own decoder for the baseline legs: the UNMODIFIED reference module (oracle/_ref, staged byte for byte by
+    oracle/stage_ref.py; /root/reference in the build container) through oracle/ref_shim.py -> kind "reference"; the oracle port
+    (pinned to it by tests/golden) only if the staged files are missing -> kind "port".  Returns (decode_fn(codes [B,T,Q]) ->
+    list of waveforms, kind).  Never used by the product path."""
     import torch
 
     from oracle import decoder_oracle as O
+    from oracle import ref_shim
     from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
-    from qwen3_tts_b200.synthetic import make_codes, make_decoder_state_dict
+    from qwen3_tts_b200.synthetic import make_decoder_state_dict
+    import contextlib
+    cfg = Qwen3TTSTokenizerV2DecoderConfig()
+    sd = make_decoder_state_dict(cfg, seed=0)
+    if ref_shim.available():
+        with contextlib.redirect_stdout(sys.stderr):  # transformers prints docstring complaints about the reference on stdout: one JSON line only
+            dec = ref_shim.build_reference_decoder(sd, codebook_dim=cfg.codebook_dim, attn_implementation="sdpa").to(device)
+
+        def decode(codes):
+            with contextlib.redirect_stdout(sys.stderr):
+                return ref_shim.reference_model_decode(dec, codes.to(device))
+        return decode, "reference", dec
+    sd = {k: v.to(device) for k, v in sd.items()}
+
+    def decode_port(codes):
+        with torch.inference_mode():
+            return O.model_decode(sd, cfg, codes.to(device))
+    return decode_port, "port", None
+
+
+def cpu_reference_run(steps: int, warmup: int, utterances: int = REF_UTTERANCES):
+    """The reference's CPU decode of `utterances` items of the workload in one batch per step, on all host cores."""
+    import torch
+
+    from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
+    from qwen3_tts_b200.synthetic import make_codes
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     cfg = Qwen3TTSTokenizerV2DecoderConfig()
-    sd = make_decoder_state_dict(cfg, seed=0)
+    decode, kind, _ = load_reference("cpu")
     codes = make_codes(B_UTT, T_FRAMES, cfg, seed=1)[:utterances]
     times = []
-    with torch.inference_mode():
-        for i in range(warmup + steps):
-            t0 = time.perf_counter()
-            out = O.model_decode(sd, cfg, codes)
-            dt = time.perf_counter() - t0
-            if i >= warmup:
-                times.append(dt)
-    assert out[0].shape[0] == N_SAMPLES
-    sec = statistics.median(times)
-    return {"value": utterances * T_FRAMES * FRAME_SEC / sec, "sec_per_step": sec, "cores": torch.get_num_threads(),
-            "sample": f"{utterances} of the {B_UTT} utterances x {T_FRAMES * FRAME_SEC:g} s per step, median of {steps} after {warmup} warm-up"}
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = decode(codes)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    assert len(out) == utterances and out[0].shape[0] == N_SAMPLES
+    sec = sum(times) / len(times)
+    return {"value": utterances * T_FRAMES * FRAME_SEC / sec, "sec_per_step": sec, "cores": torch.get_num_threads(), "kind": kind,
+            "sample": f"{utterances} of the {B_UTT} utterances x {T_FRAMES * FRAME_SEC:g} s in one batch per step, mean of {steps} steps after {warmup} warm-up"}
 
 
 def run_reference(args, rank: int):
-    """--impl reference: the reference's own CPU implementation of the path on the host cores (oracle port:
-    the reference is a Python package that cannot travel to the GPU box, tests/golden pins the port to it)."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores, same metric / config / unit as
+    our arm; each step is a bounded sample (REF_UTTERANCES utterances in one batch) of the workload."""
     if rank != 0:
         return
-    r = cpu_reference_run(steps=args.steps, warmup=min(args.warmup, 1), utterances=1)
+    r = cpu_reference_run(steps=args.steps, warmup=args.warmup)
     line = {"impl": "reference", "metric": "audio-sec decoded per sec (codes->24kHz)", "value": r["value"], "unit": "audio-s/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": r["sec_per_step"] * 1e3,
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["sec_per_step"] * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][2] + "; bounded sample: 1 utterance per step"},
-            "cpu_baseline": {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "config": bench_config(args.gpus),
+            "cpu_baseline": {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def bench_config(world: int):
+    """`config` of the JSON line: identical for our arm and the reference arm (the driver compares them)."""
+    return {"workload": WORKLOADS_NAME, "frames_per_step_per_gpu": B_UTT * T_FRAMES,
+            "weights": "seeded random-init, reference architecture (195.08 M params)",
+            "l2": "flushed between timed steps (256 MiB write, untimed); activations per step >> 126 MB L2",
+            "parallelism": f"utterance-sharded x{world}, no collective"}
+
+
+def torch_gpu_context(dev, streams: int):
+    """Context numbers SURVEY 8(d) / BASELINE.md 4 ask for: the unmodified reference in eager PyTorch (cuDNN / cuBLAS, fp32) on the
+    SAME B200 - (a) bulk decode of a sub-batch of config 2, (b) the reference-style streaming chunk call
+    forward(codes[..., s-25:e])[..., 25*1920:] (modeling :889-893) for `streams` streams with one new frame.  Baseline only."""
+    import torch
+
+    from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
+    from qwen3_tts_b200.synthetic import make_codes
+    cfg = Qwen3TTSTokenizerV2DecoderConfig()
+    decode, kind, ref_dec = load_reference(str(dev))
+    nb = 16
+    codes = make_codes(B_UTT, T_FRAMES, cfg, seed=1)[:nb].to(dev)
+
+    def timed(fn, reps, warm):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            torch.cuda.synchronize(dev)
+            ts.append(a.elapsed_time(b))
+        return sorted(ts)
+
+    bulk = timed(lambda: decode(codes), 5, 2)
+    out = {"impl": f"{kind} (unmodified reference module, eager PyTorch fp32, library defaults: cuDNN / cuBLAS)" if kind == "reference" else "oracle port, eager PyTorch fp32",
+           "bulk": {"batch": nb, "frames": T_FRAMES, "ms_p50": bulk[len(bulk) // 2], "audio_s_per_s": nb * T_FRAMES * FRAME_SEC / (bulk[len(bulk) // 2] * 1e-3)}}
+    if ref_dec is not None:
+        ch = make_codes(streams, 26, cfg, seed=2).transpose(1, 2).contiguous().to(dev)   # 25 frames of left context + 1 new frame
+
+        def chunk_call():
+            import contextlib
+            with torch.inference_mode(), contextlib.redirect_stdout(sys.stderr):
+                return ref_dec(ch)[..., 25 * 1920:]
+        c = timed(chunk_call, 20, 3)
+        out["stream_chunk_call"] = {"streams": streams, "frames_per_call": 26, "new_frames": 1, "ms_p50": c[len(c) // 2], "ms_p99": c[-1],
+                                    "note": "reference-style chunk: forward(codes[..., s-25:e])[..., 25*1920:], 25 frames recomputed per packet"}
+    del decode, ref_dec
+    torch.cuda.empty_cache()
+    return out
 
 
 def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup: int):
@@ -227,6 +305,11 @@ def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup:
             "h2d_bytes_per_step": streams * 16 * packet * 8, "d2h_bytes_per_step": streams * packet * 1920 * 4}
 
 
+KERNEL_NAMES = {0: "k_rvq", 1: "conv_gemm_tc_kernel", 2: "k_rmsnorm", 3: "k_attention", 4: "k_dwconv_ln", 5: "tail_conv_kernel", 6: "unit_kernel",
+                7: "ws_conv_kernel", 8: "slab_conv_kernel", 9: "k_stream_attention", 10: "k_state_copy", 11: "k_split_f32"}
+TENSOR_KERNELS = ("unit_kernel", "slab_conv_kernel", "conv_gemm_tc_kernel", "ws_conv_kernel")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -238,14 +321,16 @@ def main():
     ap.add_argument("--workload", default="bulk10s", choices=sorted(WORKLOADS), help="default = the configuration BASELINE.json's metric is quoted on")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true", help="skip the streaming-chunk latency section (BASELINE config 3)")
+    ap.add_argument("--no-torch-gpu", action="store_true", help="skip the eager-PyTorch-on-this-GPU context section")
     ap.add_argument("--stream-only", action="store_true", help="print only the streaming-chunk latency section")
     ap.add_argument("--streams", type=int, default=256)
     args = ap.parse_args()
-    global B_UTT, T_FRAMES, N_SAMPLES
-    B_UTT, T_FRAMES, workload_name = WORKLOADS[args.workload]
+    global B_UTT, T_FRAMES, N_SAMPLES, WORKLOADS_NAME
+    B_UTT, T_FRAMES, WORKLOADS_NAME = WORKLOADS[args.workload]
     N_SAMPLES = T_FRAMES * 1920 - 555 * ((T_FRAMES + 299) // 300)
     if args.workload != "bulk10s":
-        args.no_streaming = True  # the streaming section rides on the default line only
+        args.no_streaming = True  # the streaming and context sections ride on the default line only
+        args.no_torch_gpu = True
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -296,22 +381,31 @@ def main():
     def step_device():
         return dec.chunked_decode(codes_dev)
 
-    # ---------------- device-resident throughput
+    # ---------------- device-resident throughput.  The per-kernel profile is recorded INSIDE these timed steps: the engine brackets every
+    # launch with a CUDA-event pair on the launch stream (two event records per kernel; their cost is inside `value`, not hidden).
     for _ in range(args.warmup):
         step_device()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    dec.set_profile(True)
     l0 = dec.launch_count()
-    for a, b in ev:
+    step_ms, acc = [], {}
+    for _ in range(args.steps):
         flush.zero_()                                                       # L2 flush between timed iterations (untimed)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         wav = step_device()
         b.record()
+        prof = dec.get_profile()                                            # synchronises; read-and-clear
+        step_ms.append(a.elapsed_time(b))
+        for code, t_ms, fl, by, dims in prof:
+            k = acc.setdefault(KERNEL_NAMES.get(code, str(code)), {"ms": 0.0, "launches": 0, "flops": 0.0, "min_bytes": 0.0})
+            k["ms"] += t_ms; k["launches"] += 1; k["flops"] += fl; k["min_bytes"] += by
+    dec.set_profile(False)
     barrier()
     launches = dec.launch_count() - l0
-    ms = sum(a.elapsed_time(b) for a, b in ev)
+    ms = sum(step_ms)
     # ---------------- end to end through the public API (host codes -> host float32 waveforms)
     for _ in range(max(3, args.warmup)):                                     # results held as in the timed loop, so the two pinned
         wavs, sr = tok.decode(host_items)                                    # result buffers that alternate there exist before timing starts
@@ -330,50 +424,48 @@ def main():
     audio_s = world * B_UTT * T_FRAMES * FRAME_SEC * args.steps
     value = audio_s / (ms / 1e3)
     e2e_value = audio_s / e2e_s
-    # ---------------- per-kernel profile of one step (separate, untimed pass)
-    dec.set_profile(True)
-    step_device()
-    prof = dec.get_profile()
-    dec.set_profile(False)
-    tot_ms = sum(p[1] for p in prof)
-    names = {0: "rvq_gather", 1: "tcgen05_conv_gemm", 2: "rmsnorm", 3: "attention", 4: "dwconv_ln", 5: "tail_conv", 6: "tcgen05_fused_unit"}
-    kernel_fn = {"tcgen05_conv_gemm": "conv_gemm_tc_kernel / slab_conv_kernel / ws_conv_kernel (tcgen05 implicit-GEMM conv/linear)",
-                 "tcgen05_fused_unit": "unit_kernel (tcgen05 fused residual unit: conv7 -> Snake -> conv1 + residual, intermediate in TMEM)"}
-    by_kernel = {}
-    for ty, t_ms, fl, by, _dims in prof:
-        k = by_kernel.setdefault(names[ty], {"ms": 0.0, "launches": 0, "min_bytes": 0.0, "flops": 0.0})
-        k["ms"] += t_ms; k["launches"] += 1; k["min_bytes"] += by; k["flops"] += fl
+    # ---------------- roofline: per-kernel numbers averaged over the timed steps themselves
     peaks = load_peaks()
-    # dominant kernel = the tensor-core kernel family with the largest share of the step
-    dom = max((n for n in by_kernel if n in kernel_fn), key=lambda n: by_kernel[n]["ms"])
-    d = by_kernel[dom]
-    roof = {"bound": "tensor", "kernel": kernel_fn[dom],
-            "achieved": d["flops"] / (d["ms"] * 1e-3) / 1e12,
-            "peak": peaks["tflops_sustained"], "unit": "TFLOP/s", "traffic": ncu_traffic(dom),
-            "peak_source": f"{peaks['source']} sustained bf16 cuBLAS (kernel timed inside a long step)",
-            "share_of_step": d["ms"] / tot_ms, "flops_per_launch_avg": d["flops"] / d["launches"], "ms_per_launch_avg": d["ms"] / d["launches"]}
-    roof["frac"] = roof["achieved"] / roof["peak"]
+    ksum_ms = sum(k["ms"] for k in acc.values())
+    kernels = {}
+    for name, k in sorted(acc.items(), key=lambda kv: -kv[1]["ms"]):
+        per_step = k["ms"] / args.steps
+        tfl = k["flops"] / (k["ms"] * 1e-3) / 1e12 if k["ms"] > 0 else 0.0
+        gbs = k["min_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else 0.0
+        tensor = name in TENSOR_KERNELS
+        kernels[name] = {"ms_per_step": round(per_step, 4), "launches_per_step": k["launches"] // args.steps, "share_of_step": round(k["ms"] / ksum_ms, 4),
+                         "bound": "tensor" if tensor else "hbm",
+                         "achieved": round(tfl if tensor else gbs, 1), "unit": "TFLOP/s" if tensor else "GB/s",
+                         "frac": round((tfl / peaks["tflops_sustained"]) if tensor else (gbs / peaks["hbm_gbs"]), 4)}
+        if tensor:
+            kernels[name]["min_hbm_gbs"] = round(gbs, 1)
+    dom = max(acc, key=lambda n: acc[n]["ms"])                               # dominant kernel = largest share of the timed steps
+    d = acc[dom]
+    dom_tensor = dom in TENSOR_KERNELS
+    achieved = (d["flops"] if dom_tensor else d["min_bytes"]) / (d["ms"] * 1e-3) / (1e12 if dom_tensor else 1e9)
+    peak = peaks["tflops_sustained"] if dom_tensor else peaks["hbm_gbs"]
+    roof = {"bound": "tensor" if dom_tensor else "hbm", "kernel": dom, "achieved": achieved, "peak": peak,
+            "unit": "TFLOP/s" if dom_tensor else "GB/s", "frac": achieved / peak,
+            "traffic": None,  # DRAM bytes per launch need ncu (dram__bytes_read.sum + dram__bytes_write.sum): profiles/r2_ncu_*.txt of this commit
+            "peak_source": f"{peaks['source']} " + ("sustained bf16 cuBLAS (kernel timed inside a long step; fp16 has the same pipe rate)" if dom_tensor else "copy bandwidth"),
+            "share_of_step": d["ms"] / ksum_ms, "launches_per_step": d["launches"] // args.steps,
+            "algorithmic_per_launch": (d["flops"] if dom_tensor else d["min_bytes"]) / d["launches"], "ms_per_launch_avg": d["ms"] / d["launches"],
+            "measured": f"CUDA-event pairs around every launch inside the {args.steps} timed steps",
+            "sum_kernel_ms_per_step": ksum_ms / args.steps, "sum_kernel_over_step": ksum_ms / sum(step_ms)}
     path_frac = (B_UTT * T_FRAMES * GFLOP_PER_FRAME * 1e9) / (ms / args.steps * 1e-3) / 1e12 / peaks["tflops_sustained"]
-    for k in by_kernel.values():
-        k["ms"] = round(k["ms"], 4)
-        k["min_hbm_gbs"] = round(k.pop("min_bytes") / max(k["ms"], 1e-9) / 1e6, 1)
-        k["tflops"] = round(k.pop("flops") / max(k["ms"], 1e-9) / 1e9, 1)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     line = {"metric": "audio-sec decoded per sec (codes->24kHz)", "value": value, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": f"{args.mode} operands, fp32 accumulate", "data": "synthetic",
-            "config": {"workload": workload_name,
-                       "frames_per_step_per_gpu": B_UTT * T_FRAMES, "weights": "seeded random-init, reference architecture (195.08 M params)",
-                       "l2": "flushed between timed steps (256 MiB write, untimed); activations per step >> 126 MB L2",
-                       "parallelism": f"utterance-sharded x{world}, no collective"},
+            "dtype": f"{args.mode} tensor-core operands, fp32 accumulate", "data": "synthetic",
+            "config": bench_config(world),
             "e2e": {"value": e2e_value, "unit": "audio-s/s", "h2d_bytes_per_step": world * B_UTT * T_FRAMES * 16 * 8,
                     "d2h_bytes_per_step": world * B_UTT * N_SAMPLES * 4, "ms_per_step": e2e_s / args.steps * 1e3,
                     "api": "Qwen3TTSTokenizer.decode(list of {'audio_codes': pinned host int64 [T,16]}) -> host float32 arrays"},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
-            "path_frac_of_tensor_roofline": path_frac, "kernels": by_kernel}
+            "path_frac_of_tensor_roofline": path_frac, "kernels": kernels}
     if world == 1:
         # SURVEY 8f-3 wire formats (additive API, informational): int16 code frames in, PCM16 out, conversion fused into the output conv
         items16 = [{"audio_codes": codes_host[b].to(torch.int16)} for b in range(B_UTT)]
@@ -394,9 +486,19 @@ def main():
         dec.reserve_streams(args.streams, 4)
         line["streaming"] = [stream_latency(dec, cfg, dev, args.streams, 1, steps=2000, warmup=200),
                              stream_latency(dec, cfg, dev, args.streams, 4, steps=500, warmup=50)]
+    if not args.no_torch_gpu and world == 1:
+        del model, dec, tok
+        torch.cuda.empty_cache()
+        try:
+            line["torch_gpu"] = torch_gpu_context(dev, args.streams)
+            line["torch_gpu"]["ours_over_eager_bulk"] = value / line["torch_gpu"]["bulk"]["audio_s_per_s"]
+            if "stream_chunk_call" in line["torch_gpu"] and "streaming" in line:
+                line["torch_gpu"]["eager_chunk_call_over_ours_p50"] = line["torch_gpu"]["stream_chunk_call"]["ms_p50"] / line["streaming"][0]["device_ms"]["p50"]
+        except Exception as ex:  # context only: never fail the bench line over it
+            line["torch_gpu"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
     if not args.no_cpu_baseline and world == 1:
-        r = cpu_reference_run(steps=3, warmup=1, utterances=1)
-        line["cpu_baseline"] = {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+        r = cpu_reference_run(steps=3, warmup=1)
+        line["cpu_baseline"] = {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

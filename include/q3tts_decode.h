@@ -174,12 +174,14 @@ int q3tts_forward_probe(q3tts_handle* h, const int64_t* codes, int B, int T, con
 /* Bench support: number of kernel launches issued by this handle since creation. */
 int64_t q3tts_launch_count(q3tts_handle* h);
 
-/* Per-op profile of the LAST engine launch (one forward on one sub-batch) when profiling is on:
- * a CUDA-event pair is recorded around every op on the launch stream.  q3tts_get_profile
- * synchronises the device and returns the number of ops; types[i] is 0 RVQ gather, 1 tcgen05 GEMM,
- * 2 RMSNorm, 3 attention, 4 dwconv+LayerNorm, 5 tail conv; flops[i] = algorithmic 2*MACs (GEMM ops),
- * bytes[i] = minimum HBM bytes (operands and outputs once); dims (optional, 4 per op) = rows over all batch
- * items, N, Cin, taps for GEMM ops. */
+/* Per-op profile.  While profiling is on, a CUDA-event pair is recorded around every op on the launch stream and the profile
+ * ACCUMULATES over every engine launch (all chunks / sub-batches / stream plans) until q3tts_get_profile reads it:
+ * q3tts_get_profile synchronises the device, returns the number of ops recorded since the last read (fill at most max_ops
+ * entries) and clears the profile.  types[i] = kernel: 0 RVQ gather-sum, 1 conv_gemm_tc_kernel (1-tap GEMMs), 2 RMSNorm,
+ * 3 attention, 4 dwconv + LayerNorm, 5 output conv, 6 unit_kernel (fused residual unit), 7 ws_conv_kernel, 8 slab_conv_kernel
+ * (multi-tap convs), 9 streaming attention, 10 stream state copies, 11 fp32 -> [hi | lo] split; flops[i] = ALGORITHMIC 2 * MACs
+ * (the extra MMAs of split-precision operands are not counted), bytes[i] = minimum HBM bytes (operands and outputs once);
+ * dims (optional, 4 per op) = rows over all batch items, N, input channels, taps for GEMM ops. */
 int q3tts_set_profile(q3tts_handle* h, int on);
 int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, double* flops, double* bytes, int32_t* dims);
 

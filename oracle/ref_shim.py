@@ -1,8 +1,8 @@
 """ORACLE — test infrastructure.  Imports the UNMODIFIED reference decoder from /root/reference.
 
-Only usable in the build container (the GPU box has no /root/reference): used by
-oracle/make_golden.py to write tests/golden/ and by tests/test_oracle_vs_reference.py (skipped
-when the reference tree is absent).  Two shims are needed because the reference pins
+Reads /root/reference in the build container; on the GPU box (no /root/reference) the same two files staged byte for byte under
+the git-ignored oracle/_ref/ by oracle/stage_ref.py.  Used by oracle/make_golden.py to write tests/golden/, by
+tests/test_oracle_vs_reference.py and by bench.py's baseline legs (--impl reference, cpu_baseline, torch_gpu context).  Two shims are needed because the reference pins
 transformers==4.57.3 (pyproject.toml:23) and this image has 5.5.0:
   1. `@check_model_inputs()` (modeling :498) — 5.x decorator takes the function directly;
   2. `ROPE_INIT_FUNCTIONS["default"]` (modeling :259) — dropped in 5.x.
@@ -20,6 +20,9 @@ import torch
 
 REF_ROOT = os.environ.get("Q3TTS_REFERENCE_ROOT", "/root/reference")
 _T12 = os.path.join(REF_ROOT, "qwen_tts", "core", "tokenizer_12hz")
+if not os.path.isfile(os.path.join(_T12, "modeling_qwen3_tts_tokenizer_v2.py")):
+    # GPU box: no /root/reference; the same two files, staged byte for byte by oracle/stage_ref.py (git-ignored oracle/_ref/)
+    _T12 = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "qwen_tts", "core", "tokenizer_12hz")
 _cache = {}
 
 

@@ -135,6 +135,7 @@ int64_t q3tts_launch_count(q3tts_handle* h) { return h ? h->e.launches : 0; }
 int q3tts_set_profile(q3tts_handle* h, int on) {
   if (!h) return Q3TTS_BAD_CONFIG;
   h->e.profile = on != 0;
+  prof_clear(&h->e);
   return Q3TTS_OK;
 }
 
@@ -150,6 +151,7 @@ int q3tts_get_profile(q3tts_handle* h, int max_ops, int32_t* types, float* ms, d
     types[i] = e.prof_type[i]; ms[i] = t; flops[i] = e.prof_flops[i]; bytes[i] = e.prof_bytes[i];
     if (dims) for (int d = 0; d < 4; ++d) dims[4 * i + d] = e.prof_dims[4 * i + d];
   }
+  prof_clear(&e);  // read-and-clear: the next launches start a new profile
   return n;
 }
 

@@ -200,7 +200,8 @@ int engine_forward_batched(Engine* e, const long long* codes, long long sb, long
 void engine_free(Engine* e);
 // Reads and clears the bad-code flag; synchronises the stream.  Returns Q3TTS_CODE_OUT_OF_RANGE when a code was out of range.
 int engine_check_codes(Engine* e, cudaStream_t s);
-void prof_reset(Engine* e, size_t nops);
+size_t prof_begin(Engine* e, size_t nops);
+void prof_clear(Engine* e);
 void prof_account(Engine* e, const Op& op);
 int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);
 int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long long* codes, long long sb, long long sk, long long st, int P, float* wav,

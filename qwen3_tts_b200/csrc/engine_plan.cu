@@ -329,14 +329,18 @@ int engine_get_plan(Engine* e, int B, int T, Plan** out) {
   return 0;
 }
 
-void prof_reset(Engine* e, size_t nops) {
-  while (e->prof_events.size() < 2 * nops) {
+// The profile ACCUMULATES over every engine launch (all chunks and sub-batches of a step) until q3tts_get_profile reads and clears
+// it, so per-kernel times come from the same launches that a timed step consists of.  Returns the index of this run's first op.
+size_t prof_begin(Engine* e, size_t nops) {
+  const size_t first = e->prof_type.size();
+  while (e->prof_events.size() < 2 * (first + nops)) {
     cudaEvent_t ev;
     cudaEventCreate(&ev);
     e->prof_events.push_back(ev);
   }
-  e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear(); e->prof_dims.clear();
+  return first;
 }
+void prof_clear(Engine* e) { e->prof_type.clear(); e->prof_flops.clear(); e->prof_bytes.clear(); e->prof_dims.clear(); }
 
 // algorithmic FLOPs and minimum HBM bytes of one op, appended to the profile of the current run
 void prof_account(Engine* e, const Op& op) {
@@ -375,7 +379,15 @@ void prof_account(Engine* e, const Op& op) {
   } else if (op.type == OP_DWLN) {
     by = (op.split ? 4.0 + 2.0 : 2.0 * 2.0) * (double)op.B * op.L * op.C;  // one read and one write of the token tensor
   }
-  e->prof_type.push_back((int)op.type);
+  // profile kernel codes (include/q3tts_decode.h q3tts_get_profile): the three implicit-GEMM kernels are told apart
+  int code = (int)op.type;
+  if (op.type == OP_GEMM) code = op.g.variant == 1 ? 7 : (op.g.variant == 2 ? 8 : 1);
+  else if (op.type == OP_TAIL) code = 5;
+  else if (op.type == OP_UNIT) code = 6;
+  else if (op.type == OP_STREAM_ATTN) code = 9;
+  else if (op.type == OP_STATE_LOAD || op.type == OP_STATE_SAVE || op.type == OP_POS_ADVANCE) code = 10;
+  else if (op.type == OP_SPLIT) code = 11;
+  e->prof_type.push_back(code);
   e->prof_flops.push_back(fl);
   e->prof_bytes.push_back(by);
   for (int d = 0; d < 4; ++d) e->prof_dims.push_back(dims[d]);
@@ -385,10 +397,9 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
                int skip, const char* probe_stage, float* probe_out, long long probe_cap, int* pc, int* pl, cudaStream_t s,
                long long out_pos0, const long long* item_skip) {
   const q3tts_config& c = e->cfg;
-  size_t pi = 0;
+  size_t pi = e->profile ? prof_begin(e, plan->ops.size()) : 0;
   static const bool sync_each = Q3_ENV("Q3TTS_SYNC") != nullptr;  // debug: serialise ops with the host
   static const bool keep_raw = Q3_ENV("Q3TTS_KEEP_RAW") != nullptr;  // debug / A-B: store the dead raw outputs too
-  if (e->profile) prof_reset(e, plan->ops.size());
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);

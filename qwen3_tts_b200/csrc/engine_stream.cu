@@ -346,8 +346,7 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
   float* tail_out = identity_rows ? wav : plan->wav_tmp;
   const long long tail_stride = identity_rows ? wav_stride : plan->out_len;
   static const bool sync_each = Q3_ENV("Q3TTS_SYNC") != nullptr;  // debugging: attribute an asynchronous fault to its op
-  size_t pi = 0;
-  if (e->profile) prof_reset(e, plan->ops.size());  // the profile holds the last plan that ran
+  size_t pi = e->profile ? prof_begin(e, plan->ops.size()) : 0;  // accumulates until q3tts_get_profile reads it
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);

@@ -136,8 +136,9 @@ class Qwen3TTSTokenizerV2Decoder:
         _capi.check(self._h, self._lib.q3tts_set_profile(self._h, 1 if on else 0), "set_profile")
 
     def get_profile(self):
-        """[(type, ms, flops, bytes, (rows, n, cin, taps))] for every op of the last launch (profiling must be on)."""
-        n = 512
+        """[(kernel code, ms, flops, bytes, (rows, n, cin, taps))] for every op launched since the last call (profiling must be on);
+        reading clears the profile.  Kernel codes: include/q3tts_decode.h q3tts_get_profile."""
+        n = 4096
         ty, ms = (C.c_int32 * n)(), (C.c_float * n)()
         fl, by = (C.c_double * n)(), (C.c_double * n)()
         dm = (C.c_int32 * (4 * n))()

@@ -28,7 +28,7 @@ for _ in range(reps):
     acc = [list(x) for x in pr] if acc is None else [[a[0], a[1] + b[1], a[2], a[3], a[4]] for a, b in zip(acc, pr)]
 prof = [(a[0], a[1] / reps, a[2], a[3], a[4]) for a in acc]
 dec.set_profile(False)
-names = {0: "rvq", 1: "gemm", 2: "rmsnorm", 3: "attn", 4: "dwln", 5: "tail", 6: "unit"}
+names = {0: "rvq", 1: "gemm", 2: "rmsnorm", 3: "attn", 4: "dwln", 5: "tail", 6: "unit", 7: "wsconv", 8: "slabconv", 9: "sattn", 10: "state", 11: "split"}
 tot = sum(p[1] for p in prof)
 print(f"B={B} T={T} mode={mode} total {tot:.3f} ms over {len(prof)} launches")
 print(f"{'#':>3} {'op':8} {'rows':>9} {'N':>5} {'Cin':>5} {'k':>2} {'ms':>8} {'%':>5} {'TFLOP/s':>8} {'minGB/s':>8}")
