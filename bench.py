@@ -40,6 +40,7 @@ N_SAMPLES = 239445  # T*1920 - 555 per 300-frame chunk (modeling :885-895)
 WORKLOADS = {  # name -> (utterances per GPU per step, frames per utterance, BASELINE.json config it stands for)
     "bulk10s": (64, 125, "Tokenizer-12Hz non-streaming bulk decode, batch 64 x 10 s synthetic 16-codebook codes per GPU (BASELINE config 2)"),
     "longform60s": (32, 750, "Long-form decode, batch 32 x 60 s codes per GPU through chunked_decode (chunks 300 / 25+300 / 25+150; BASELINE config 4)"),
+    "sharded30s": (64, 375, "strong-scaling form of BASELINE config 5: see run_sharded"),
     "bulk30s": (64, 375, "Offline bulk decode of 30 s utterances, one batch of 64 per GPU per step (4096 utterances = 64 such steps at N=1, "
                          "utterance-sharded over N GPUs; chunks 300 / 25+75; BASELINE config 5)"),
 }
@@ -305,6 +306,81 @@ def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup:
             "h2d_bytes_per_step": streams * 16 * packet * 8, "d2h_bytes_per_step": streams * packet * 1920 * 4}
 
 
+def run_sharded(args, rank, local_rank, world):
+    """--workload sharded30s: BASELINE config 5 as STRONG scaling - a FIXED set of `--utterances` ragged utterances (true lengths
+    U[0.5, 1] x 375 frames, seeded) is partitioned over the ranks by qwen3_tts_b200.sharding (longest-first, then length buckets);
+    every rank decodes its shard end to end (host codes -> host waveforms through Qwen3TTSTokenizer.decode); no data-path collective.
+    A step = the whole set once; value = audio-seconds of the whole set / max-over-ranks wall time of the step."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from qwen3_tts_b200 import Qwen3TTSTokenizer, synthetic_model
+    from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
+    from qwen3_tts_b200.sharding import bucket_by_length, decode_shard, frames_cost, shard_utterances
+    from qwen3_tts_b200.synthetic import make_codes
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=dev)   # timing barrier / max only (the launch contract); the decode path uses no collective
+    cfg = Qwen3TTSTokenizerV2DecoderConfig()
+    n_utt, Tmax = args.utterances, 375
+    lengths = [int(v) for v in np.random.default_rng(5).integers(Tmax // 2, Tmax + 1, n_utt)]
+    mine = shard_utterances(lengths, world, rank)
+    max_frames = 64 * Tmax
+    model = synthetic_model(seed=0, device=dev, compute_mode=args.mode)
+    model.decoder.reserve(64 * 325)
+    tok = Qwen3TTSTokenizer.from_model(model)
+    codes = {i: make_codes(1, lengths[i], cfg, seed=1000 + i)[0].pin_memory() for i in mine}
+    dense = [codes[i] for i in mine]
+    batches = bucket_by_length(list(range(len(dense))), [lengths[i] for i in mine], max_frames)
+    decode_shard(tok, dense, batches[0], max_frames)                     # warm-up: plans and buffers of the largest batch shape
+    if len(batches) > 1:
+        decode_shard(tok, dense, batches[-1], max_frames)
+    times = []
+    l0 = model.decoder.launch_count()
+    for _ in range(args.steps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        n_out = 0
+        for bt in batches:
+            out = decode_shard(tok, dense, bt, max_frames)
+            n_out += sum(int(w.shape[0]) for w in out.values())
+        torch.cuda.synchronize(dev)
+        times.append(time.perf_counter() - t0)
+    launches = model.decoder.launch_count() - l0
+    tt = torch.tensor(times, dtype=torch.float64, device=dev)
+    load = torch.tensor([float(sum(frames_cost(lengths[i]) for i in mine))], dtype=torch.float64, device=dev)
+    loads = [load.clone() for _ in range(world)]
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_gather(loads, load)
+    if rank == 0:
+        sec = float(tt.sum().item())
+        audio_s = sum(lengths) * FRAME_SEC * args.steps
+        ld = [float(x.item()) for x in loads]
+        h2d = sum(lengths) * 16 * 8
+        line = {"metric": "audio-sec decoded per sec (codes->24kHz)", "value": audio_s / sec, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
+                "warmup": 2, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": f"{args.mode} tensor-core operands, fp32 accumulate", "data": "synthetic",
+                "config": {"workload": f"Offline bulk decode of a FIXED set of {n_utt} ragged utterances (true lengths U[0.5,1] x 30 s, 16-codebook codes) "
+                                       f"sharded by utterance over {world} GPU(s): longest-first partition + length buckets (BASELINE config 5)",
+                           "audio_seconds_per_step": sum(lengths) * FRAME_SEC, "batches_rank0": len(batches),
+                           "frames_cost_max_over_mean": max(ld) / (sum(ld) / len(ld)), "parallelism": f"utterance-sharded x{world}, no collective",
+                           "l2": "inputs and activations per step >> 126 MB L2"},
+                "e2e": {"value": audio_s / sec, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(n_out) * 4 * world,
+                        "api": "qwen3_tts_b200.sharding.decode_shard -> Qwen3TTSTokenizer.decode (pinned host codes -> host float32 arrays), the whole step"},
+                "gpu_launches": launches}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 KERNEL_NAMES = {0: "k_rvq", 1: "conv_gemm_tc_kernel", 2: "k_rmsnorm", 3: "k_attention", 4: "k_dwconv_ln", 5: "tail_conv_kernel", 6: "unit_kernel",
                 7: "ws_conv_kernel", 8: "slab_conv_kernel", 9: "k_stream_attention", 10: "k_state_copy", 11: "k_split_f32"}
 TENSOR_KERNELS = ("unit_kernel", "slab_conv_kernel", "conv_gemm_tc_kernel", "ws_conv_kernel")
@@ -324,7 +400,13 @@ def main():
     ap.add_argument("--no-torch-gpu", action="store_true", help="skip the eager-PyTorch-on-this-GPU context section")
     ap.add_argument("--stream-only", action="store_true", help="print only the streaming-chunk latency section")
     ap.add_argument("--streams", type=int, default=256)
+    ap.add_argument("--utterances", type=int, default=4096, help="size of the fixed utterance set of --workload sharded30s")
     args = ap.parse_args()
+    if args.workload == "sharded30s":
+        if args.impl == "reference":
+            raise SystemExit("--workload sharded30s has no reference arm: use the default workload")
+        run_sharded(args, int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
+        return
     global B_UTT, T_FRAMES, N_SAMPLES, WORKLOADS_NAME
     B_UTT, T_FRAMES, WORKLOADS_NAME = WORKLOADS[args.workload]
     N_SAMPLES = T_FRAMES * 1920 - 555 * ((T_FRAMES + 299) // 300)

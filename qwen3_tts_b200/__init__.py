@@ -8,6 +8,7 @@ from .configuration import Qwen3TTSTokenizerV2Config, Qwen3TTSTokenizerV2Decoder
 from .modeling import (Qwen3TTSTokenizerV2Decoder, Qwen3TTSTokenizerV2DecoderOutput,
                        Qwen3TTSTokenizerV2Model)
 from .inference import Qwen3TTSModel, TalkerStreamSink
+from .sharding import ShardedDecoder
 from .tokenizer import Qwen3TTSTokenizer
 
 
@@ -21,5 +22,5 @@ def synthetic_model(seed: int = 0, device="cuda:0", compute_mode: str = "fp16", 
     return model
 
 
-__all__ = ["Qwen3TTSModel", "TalkerStreamSink", "Qwen3TTSTokenizer", "Qwen3TTSTokenizerV2Model", "Qwen3TTSTokenizerV2Decoder", "Qwen3TTSTokenizerV2DecoderOutput",
+__all__ = ["ShardedDecoder", "Qwen3TTSModel", "TalkerStreamSink", "Qwen3TTSTokenizer", "Qwen3TTSTokenizerV2Model", "Qwen3TTSTokenizerV2Decoder", "Qwen3TTSTokenizerV2DecoderOutput",
            "Qwen3TTSTokenizerV2Config", "Qwen3TTSTokenizerV2DecoderConfig", "synthetic_model"]

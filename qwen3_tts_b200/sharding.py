@@ -55,3 +55,138 @@ def bucket_by_length(indices: Sequence[int], lengths: Sequence[int], max_frames:
     if cur:
         batches.append(cur)
     return batches
+
+
+# ------------------------------------------------------------------------------------------------ dispatcher
+def plan_batches(lengths: Sequence[int], world_size: int, max_frames: int) -> List[List[List[int]]]:
+    """Per rank, the decode batches (lists of utterance indices) of a job: LPT partition, then length buckets."""
+    return [bucket_by_length(shard_utterances(lengths, world_size, r), lengths, max_frames) for r in range(world_size)]
+
+
+def decode_shard(tokenizer, codes_list, indices: Sequence[int], max_frames: int = 8192, pcm16: bool = False):
+    """Decode the utterances `indices` of `codes_list` on THIS process's GPU: length-bucketed batches through
+    Qwen3TTSTokenizer.decode (host codes in, host waveforms out).  Returns {index: waveform}.  This is what one rank of a
+    torchrun job runs on its shard (bench.py --workload sharded30s) and what every ShardedDecoder worker runs."""
+    lengths = [int(c.shape[0]) for c in codes_list]
+    out = {}
+    for batch in bucket_by_length(indices, lengths, max_frames):
+        payload = [{"audio_codes": codes_list[i]} for i in batch]
+        wavs, _sr = tokenizer.decode_pcm16(payload) if pcm16 else tokenizer.decode(payload)
+        for i, w in zip(batch, wavs):
+            out[i] = w
+    return out
+
+
+def _gpu_worker(rank: int, device: str, model_spec: dict, jobs, results):
+    """Worker process: builds the decoder on its GPU once, then serves (job id, indices, codes) requests until None arrives."""
+    import torch
+
+    from . import Qwen3TTSTokenizer, synthetic_model
+    try:
+        if model_spec.get("path"):
+            tok = Qwen3TTSTokenizer.from_pretrained(model_spec["path"], device_map=device, dtype=model_spec.get("dtype"))
+        else:
+            model = synthetic_model(seed=model_spec.get("seed", 0), device=device, compute_mode=model_spec.get("compute_mode", "fp16"),
+                                    state_dict=model_spec.get("state_dict"))
+            tok = Qwen3TTSTokenizer.from_model(model)
+        if model_spec.get("reserve_frames"):
+            tok.model.decoder.reserve(int(model_spec["reserve_frames"]))
+        results.put(("ready", rank, None))
+    except Exception as ex:  # the parent turns this into a RuntimeError
+        results.put(("error", rank, f"{type(ex).__name__}: {ex}"))
+        return
+    while True:
+        job = jobs.get()
+        if job is None:
+            return
+        job_id, indices, codes, max_frames, pcm16 = job
+        try:
+            local = {i: c for i, c in zip(indices, codes)}
+            order = sorted(local)
+            dense = [local[i] for i in order]
+            got = decode_shard(tok, dense, list(range(len(dense))), max_frames, pcm16)
+            # waveforms travel back as CPU tensors: torch.multiprocessing moves their storage to shared memory (no pickling of samples)
+            results.put(("done", rank, (job_id, [(order[k], torch.from_numpy(w.copy())) for k, w in got.items()])))
+        except Exception as ex:
+            results.put(("error", rank, f"{type(ex).__name__}: {ex}"))
+
+
+class ShardedDecoder:
+    """One worker process per GPU, utterance-sharded bulk decode, results gathered host-side; no collective, no NCCL.
+
+        sd = ShardedDecoder(devices=["cuda:0", "cuda:1"], model_spec={"seed": 0})      # or {"path": checkpoint_dir}
+        wavs, sr = sd.decode_sharded(list_of_codes)                                     # list of (T_i, 16) integer arrays / tensors
+        sd.close()
+
+    `worker` (default: the GPU worker above) is injectable so that the dispatch / gather logic is testable on CPU."""
+
+    def __init__(self, devices: Sequence[str], model_spec: dict | None = None, max_frames: int = 8192, worker=None):
+        import torch.multiprocessing as mp
+        if not devices:
+            raise ValueError("ShardedDecoder needs at least one device")
+        self.devices = list(devices)
+        self.max_frames = int(max_frames)
+        ctx = mp.get_context("spawn")
+        self._results = ctx.Queue()
+        self._jobs = [ctx.Queue() for _ in self.devices]
+        self._procs = []
+        self._next_job = 0
+        spec = dict(model_spec or {})
+        for r, dev in enumerate(self.devices):
+            p = ctx.Process(target=worker or _gpu_worker, args=(r, dev, spec, self._jobs[r], self._results), daemon=True)
+            p.start()
+            self._procs.append(p)
+        ready = 0
+        while ready < len(self.devices):
+            kind, rank, payload = self._results.get(timeout=600)
+            if kind == "error":
+                self.close()
+                raise RuntimeError(f"worker {rank} ({self.devices[rank]}) failed to start: {payload}")
+            ready += 1
+
+    def decode_sharded(self, codes_list, pcm16: bool = False):
+        """codes_list: utterances as (T_i, Q) integer tensors / arrays.  Returns (list of waveforms in the input order, sample rate)."""
+        import numpy as np
+        import torch
+        codes = [c if isinstance(c, torch.Tensor) else torch.from_numpy(np.asarray(c)) for c in codes_list]
+        lengths = [int(c.shape[0]) for c in codes]
+        world = len(self.devices)
+        job_id = self._next_job
+        self._next_job += 1
+        busy = 0
+        for r in range(world):
+            idx = shard_utterances(lengths, world, r)
+            if not idx:
+                continue
+            self._jobs[r].put((job_id, idx, [codes[i].cpu() for i in idx], self.max_frames, pcm16))
+            busy += 1
+        out = [None] * len(codes)
+        while busy:
+            kind, rank, payload = self._results.get(timeout=3600)
+            if kind == "error":
+                raise RuntimeError(f"worker {rank} ({self.devices[rank]}): {payload}")
+            jid, items = payload
+            if jid != job_id:
+                continue
+            for i, w in items:
+                out[i] = w.numpy()
+            busy -= 1
+        return out, 24000
+
+    def close(self):
+        for q in self._jobs:
+            try:
+                q.put(None)
+            except Exception:
+                pass
+        for p in self._procs:
+            p.join(timeout=10)
+            if p.is_alive():
+                p.terminate()
+        self._procs = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
