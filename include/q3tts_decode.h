@@ -131,6 +131,14 @@ int q3tts_decode_host_pcm16(q3tts_handle* h, const int16_t* codes_host, int B, i
  * asserts (modeling :675-678).  Off by default: the hot path stays asynchronous ("check on request only"). */
 int q3tts_set_check_codes(q3tts_handle* h, int on);
 
+/* Encode side, first stage built: the residual-vector-quantiser search at the end of
+ * Qwen3TTSTokenizerV2Model.encode (modeling :960-990 -> transformers MimiSplitResidualVectorQuantizer.encode): latents
+ * [B,codebook_dim,T] fp32 (device; the Mimi encoder's output) -> codes [B,Q,T] int64 (device), Q = num_quantizers (the reference
+ * keeps the first encoder_valid_num_quantizers = 16, modeling :982).  Needs the reference model's `encoder.quantizer.*` tensors
+ * loaded before q3tts_finalize_weights (semantic / acoustic input_proj.weight, layers.N.codebook.{embed_sum, cluster_usage});
+ * Q3TTS_NOT_READY otherwise.  The conv / transformer front of the encoder is not built: encode() as a whole still raises. */
+int q3tts_rvq_encode(q3tts_handle* h, const float* latents, int B, int T, int64_t* codes, void* stream);
+
 /* The same gather-sum on int16 code frames (the wire format of q3tts_decode_host_pcm16) with NO allocation anywhere in the call.
  * No counterpart in the reference; added for callers that cannot call cudaMalloc (code under
  * CUDA graph capture, tight serving loops, harnesses that forbid it).  codes [B,Q,T] int16 (device) -> out [B,codebook_dim,T]

@@ -65,6 +65,7 @@ EXPORTS = {
     "q3tts_forward_num_samples": (C.c_int64, [C.c_void_p, C.c_int]),
     "q3tts_chunked_num_samples": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "q3tts_rvq_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "q3tts_rvq_encode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_static_max_codes": (C.c_int64, []),
     "q3tts_rvq_decode_i16_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

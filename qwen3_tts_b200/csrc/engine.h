@@ -165,6 +165,12 @@ struct Engine {
   long long* item_skip_stage = nullptr;  // device copy of decode_host's per-item skip_samples
   size_t item_skip_elems = 0;
 
+  // ---- encoder quantiser (q3tts_rvq_encode): packed when `encoder.quantizer.*` tensors were loaded
+  float* enc_tables = nullptr;  // [Q][codes][codebook_dim / 2] fp32: embed_sum / clamp(cluster_usage, 1e-5)
+  float* enc_norms = nullptr;   // [Q][codes] squared norms
+  float* enc_win = nullptr;     // [2][codebook_dim / 2][codebook_dim] input_proj of the semantic / acoustic group
+  bool enc_ready = false;
+
   // ---- streaming state (q3tts_stream_*)
   int max_slots = 0, stream_max_frames = 0, kv_ring = 128;
   long long state_bytes = 0;             // history rows of every stage, per slot
@@ -207,6 +213,7 @@ int engine_stream_reserve(Engine* e, int max_streams, int max_frames_per_step);
 int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long long* codes, long long sb, long long sk, long long st, int P, float* wav,
                        long long wav_stride, int32_t* n_valid, cudaStream_t s);
 void engine_stream_free(Engine* e);
+int encode_finalize(Engine* e);  // rvq_encode.cu
 int static_scratch_setup(int device);  // noalloc.cu: device address of the static scratch array on the current device
 
 struct DeviceGuard {

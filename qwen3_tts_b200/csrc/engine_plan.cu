@@ -499,6 +499,9 @@ void engine_free(Engine* e) {
   if (e->wav_stage) cudaFree(e->wav_stage);
   if (e->codes16_stage) cudaFree(e->codes16_stage);
   if (e->item_skip_stage) cudaFree(e->item_skip_stage);
+  if (e->enc_tables) cudaFree(e->enc_tables);
+  if (e->enc_norms) cudaFree(e->enc_norms);
+  if (e->enc_win) cudaFree(e->enc_win);
   if (e->d_bad_code) cudaFree(e->d_bad_code);
   if (e->h_bad_code) cudaFreeHost(e->h_bad_code);
 }

@@ -43,6 +43,19 @@ class _Quantizer:
     def __init__(self, dec: "Qwen3TTSTokenizerV2Decoder"):
         self._dec = dec
 
+    def encode(self, latents: torch.Tensor) -> torch.Tensor:
+        """The encoder's quantiser stage (MimiSplitResidualVectorQuantizer.encode, the tail of modeling :960-990): latents
+        [B, codebook_dim, T] fp32 -> codes [B, Q, T] int64.  Needs the model's `encoder.quantizer.*` tensors (load_state_dict)."""
+        d = self._dec
+        if latents.dim() != 3 or latents.shape[1] != d.config.codebook_dim:
+            raise ValueError(f"Expected latents of shape (B, {d.config.codebook_dim}, T), got {tuple(latents.shape)}")
+        x = latents.to(device=d.device, dtype=torch.float32).contiguous()
+        B, _, T = x.shape
+        codes = torch.empty((B, d.config.num_quantizers, T), dtype=torch.int64, device=d.device)
+        rc = d._lib.q3tts_rvq_encode(d._h, x.data_ptr(), B, T, codes.data_ptr(), _stream_ptr(d.device))
+        _capi.check(d._h, rc, "rvq_encode")
+        return codes
+
     def decode(self, codes: torch.Tensor) -> torch.Tensor:
         d = self._dec
         codes = d._check_codes(codes)
@@ -276,10 +289,13 @@ class Qwen3TTSTokenizerV2Model:
         return self.decode_upsample_rate
 
     def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True):
-        """Accepts the reference model's state_dict: `decoder.*` keys are consumed, `encoder.*` ignored."""
+        """Accepts the reference model's state_dict: `decoder.*` keys are consumed; of `encoder.*` only the quantiser
+        (`encoder.quantizer.*`, used by decoder.quantizer.encode) - the rest of the Mimi encoder is not built here."""
         dec = {k[len("decoder."):]: v for k, v in state_dict.items() if k.startswith("decoder.")}
         if not dec:  # already decoder-level keys
             dec = {k: v for k, v in state_dict.items() if not k.startswith("encoder.")}
+        dec.update({k: v for k, v in state_dict.items() if k.startswith("encoder.quantizer.") and (
+            k.endswith("input_proj.weight") or k.endswith("embed_sum") or k.endswith("cluster_usage"))})
         self.decoder.load_state_dict(dec, strict=strict)
         return self
 
@@ -305,7 +321,7 @@ class Qwen3TTSTokenizerV2Model:
         for f in files:
             with safe_open(f, framework="pt", device="cpu") as sf:
                 for k in sf.keys():
-                    if k.startswith("decoder."):
+                    if k.startswith("decoder.") or k.startswith("encoder.quantizer."):
                         sd[k] = sf.get_tensor(k)
         model.load_state_dict(sd)
         if mode == "fp16":
