@@ -21,6 +21,9 @@ int q3tts_selftest_gemm(int device, int rows, int cin, int n, int ntaps, int dil
  * Returns Q3TTS_BAD_CONFIG when the channel count cannot be fused. */
 int q3tts_selftest_unit(int device, int rows, int channels, int dilation, int bf16, float* out4);
 
+/* Process-wide switch for programmatic dependent launch between the library's kernels (default on): same-box A/B only. */
+int q3tts_debug_set_pdl(int on);
+
 /* SnakeBeta exactly as the epilogues evaluate it (cosine form, MUFU.COS): out[i] = (x + h) - h cos(a2 x[i]) with a2 = 2 exp(alpha),
  * h = 0.5 / (exp(beta) + 1e-9), host arrays of n floats.  Lets a test bound the error of __cosf at large arguments. */
 int q3tts_selftest_snake(int device, const float* x_host, int n, float a2, float h, float* out_host);

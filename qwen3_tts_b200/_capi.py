@@ -89,6 +89,7 @@ EXPORTS = {
 
 # include/q3tts_debug.h: self-tests, microbenchmarks, timeline (tests/ and tools/ only)
 DEBUG_EXPORTS = {
+    "q3tts_debug_set_pdl": (C.c_int, [C.c_int]),
     "q3tts_selftest_snake": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "q3tts_unit_trace": (C.c_int, [C.POINTER(C.c_longlong)]),
     "q3tts_bench_mma": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),

@@ -15,6 +15,7 @@
 // Operand tiles are K-major, written by TMA with 128B (KB = 64) or 64B (KB = 32) swizzle; rows
 // outside [0, rows) are zero-filled by TMA (= the reference's causal left padding).
 #include "conv_gemm.h"
+#include "launch.cuh"
 #include "pair_ptx.cuh"
 #include "tc_epilogue.cuh"
 
@@ -61,6 +62,11 @@ __device__ __forceinline__ void init_common(GemmBarriers* bars, int nring, int w
   __syncthreads();
   if (pair) cluster_sync_all();  // the peer's barriers exist before anything arrives on them
   tc_fence_after();
+  // Programmatic dependent launch (launch.cuh).  Trigger only now, AFTER this CTA holds its tensor memory: a kernel two launches ahead
+  // could otherwise allocate TMEM on this SM first and then wait for us forever.  Everything above ran in the shadow of the previous
+  // kernel; after the wait its outputs may be read and its inputs overwritten.
+  pdl_trigger();
+  pdl_wait();
 }
 
 template <typename T>
@@ -679,6 +685,13 @@ int gemm_setup(int device) {
   return tmap_init();
 }
 
+static bool g_pdl = true;
+static thread_local bool t_pdl_scope = false;
+bool pdl_enabled() { return g_pdl && t_pdl_scope; }
+void pdl_set(bool on) { g_pdl = on; }
+PdlScope::PdlScope(bool on) : prev(t_pdl_scope) { t_pdl_scope = on; }
+PdlScope::~PdlScope() { t_pdl_scope = prev; }
+
 int gemm_num_sms() { return g_num_sms; }
 int gemm_smem_optin() { return g_smem_optin; }
 
@@ -704,34 +717,23 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
   const int threads = 64 + 32 * p.epi_warps;
   if (op.ws) {
     const size_t smem = (size_t)p.ntaps * p.cin * p.bn * 2 + (size_t)op.nslabs * op.srp * p.cin * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
-    if (p.bf16)
-      ws_conv_kernel<__nv_bfloat16><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
-    else
-      ws_conv_kernel<__half><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
-    return cudaGetLastError();
+    if (p.bf16) return launch_k(ws_conv_kernel<__nv_bfloat16>, dim3(grid), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
+    return launch_k(ws_conv_kernel<__half>, dim3(grid), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.srp);
   }
   if (op.variant == 2) {
     const size_t smem = (size_t)op.nslabs * op.srp * p.kb * 2 + (size_t)op.nstages * (op.pair ? p.bn / 2 : p.bn) * p.kb * 2 + epi_bytes(p) + sizeof(GemmBarriers) + 1024;
+    int g2 = grid, cl = 1;
     if (op.pair) {
       const int tiles2 = p.batches * ((p.rows_valid + 2 * BM - 1) / (2 * BM)) * (p.n_total / p.bn);
       const int pairs = g_num_sms / 2;
-      cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3((unsigned)(2 * (tiles2 < pairs ? tiles2 : pairs))); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr; cfg.numAttrs = 1;
-      if (p.bf16)
-        return cudaLaunchKernelEx(&cfg, slab_conv_kernel<__nv_bfloat16, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
-      return cudaLaunchKernelEx(&cfg, slab_conv_kernel<__half, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+      g2 = 2 * (tiles2 < pairs ? tiles2 : pairs); cl = 2;
     }
-    if (p.bf16)
-      slab_conv_kernel<__nv_bfloat16, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages,
-                                                                              op.srp, op.slab_lo);
-    else
-      slab_conv_kernel<__half, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp,
-                                                                       op.slab_lo);
-    return cudaGetLastError();
+    if (op.pair) {
+      if (p.bf16) return launch_k(slab_conv_kernel<__nv_bfloat16, true>, dim3(g2), dim3(threads), smem, stream, cl, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+      return launch_k(slab_conv_kernel<__half, true>, dim3(g2), dim3(threads), smem, stream, cl, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+    }
+    if (p.bf16) return launch_k(slab_conv_kernel<__nv_bfloat16, false>, dim3(g2), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
+    return launch_k(slab_conv_kernel<__half, false>, dim3(g2), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, op.nslabs, op.nstages, op.srp, op.slab_lo);
   }
   const int nstages = gemm_stage_count(p, op.pair != 0);
   if (nstages < 2) return cudaErrorInvalidConfiguration;
@@ -739,20 +741,12 @@ cudaError_t launch_conv_gemm(const GemmOp& op, int engine, cudaStream_t stream) 
   if (op.pair) {
     const int tiles2 = p.batches * ((p.rows_valid + 2 * BM - 1) / (2 * BM)) * (p.n_total / p.bn);
     const int pairs = g_num_sms / 2;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(2 * (tiles2 < pairs ? tiles2 : pairs))); cfg.blockDim = dim3((unsigned)threads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    if (p.bf16) return cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel<__nv_bfloat16, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
-    return cudaLaunchKernelEx(&cfg, conv_gemm_tc_kernel<__half, true>, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+    const int g2 = 2 * (tiles2 < pairs ? tiles2 : pairs);
+    if (p.bf16) return launch_k(conv_gemm_tc_kernel<__nv_bfloat16, true>, dim3(g2), dim3(threads), smem, stream, 2, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+    return launch_k(conv_gemm_tc_kernel<__half, true>, dim3(g2), dim3(threads), smem, stream, 2, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
   }
-  if (p.bf16)
-    conv_gemm_tc_kernel<__nv_bfloat16, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
-  else
-    conv_gemm_tc_kernel<__half, false><<<grid, threads, smem, stream>>>(op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
-  return cudaGetLastError();
+  if (p.bf16) return launch_k(conv_gemm_tc_kernel<__nv_bfloat16, false>, dim3(grid), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
+  return launch_k(conv_gemm_tc_kernel<__half, false>, dim3(grid), dim3(threads), smem, stream, 1, op.tmA, op.tmB, op.tmRes, op.tmRaw, op.tmSnake, op.tmF32, p, nstages);
 }
 
 }  // namespace q3

@@ -10,6 +10,7 @@
 
 #include "engine.h"
 #include "kernels.h"
+#include "launch.cuh"
 
 namespace q3 {
 
@@ -343,6 +344,7 @@ int run_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long lo
 int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long long sb, long long sk, long long st, const int* d_ids, const int* d_rows,
                        bool identity_rows, float* wav, long long wav_stride, cudaStream_t s) {
   const q3tts_config& c = e->cfg;
+  PdlScope pdl(!e->profile);  // programmatic dependent launch between the step's ~100 short kernels (launch.cuh); not under per-op events
   float* tail_out = identity_rows ? wav : plan->wav_tmp;
   const long long tail_stride = identity_rows ? wav_stride : plan->out_len;
   static const bool sync_each = Q3_ENV("Q3TTS_SYNC") != nullptr;  // debugging: attribute an asynchronous fault to its op

@@ -1,6 +1,7 @@
 // Bandwidth-bound stages of the decode path: RVQ gather-sum, RMSNorm, RoPE + sliding-window
 // attention, depthwise conv + LayerNorm, tail conv + clamp, layout probes.
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 #include "attention_mma.cuh"
 
@@ -31,6 +32,7 @@ k_rvq(const long long* __restrict__ codes, long long sb, long long sk, long long
                       T* __restrict__ out_act, float* __restrict__ out_f32, int Q, int Tn, int ncodes, int D, int out_bs_rows,
                       const int* __restrict__ src_index, int* __restrict__ bad_code, int split) {
   __shared__ int s_code[64];  // Q <= 64 (q3tts_create)
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int t = blockIdx.x, b = blockIdx.y;
   const int bs = src_index ? src_index[b] : b;  // row of the caller's codes tensor this batch item reads
   if ((int)threadIdx.x < Q) {
@@ -86,8 +88,10 @@ cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long 
   dim3 grid(Tn, B);
   int threads = ((D / 4 + 31) / 32) * 32;
   if (threads < ((Q + 31) / 32) * 32) threads = ((Q + 31) / 32) * 32;  // the first Q threads stage the frame's codes
-  Q3_DISPATCH(bf16, (k_rvq<T><<<grid, threads, 0, s>>>(codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index, bad_code, split)));
-  return cudaGetLastError();
+  cudaError_t err;
+  Q3_DISPATCH(bf16, (err = launch_k(k_rvq<T>, grid, dim3(threads), 0, s, 1, codes, sb, sk, st, tables, (T*)out_act, out_f32, Q, Tn, ncodes, D, out_bs_rows, src_index,
+                                    bad_code, split)));
+  return err;
 }
 
 __global__ void k_widen_i16(const short* __restrict__ in, long long* __restrict__ out, long long n) {
@@ -105,6 +109,7 @@ cudaError_t widen_codes_i16(const short* in, long long* out, long long n, cudaSt
 // One warp per row (reference modeling :382-387, computed in fp32).
 template <typename T>
 __global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__ w, T* __restrict__ out, int M, int H, float eps, int split) {
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= M) return;
@@ -138,8 +143,9 @@ __global__ void k_rmsnorm(const float* __restrict__ x, const float* __restrict__
 }
 cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s, int split) {
   if (M <= 0) return cudaSuccess;
-  Q3_DISPATCH(bf16, (k_rmsnorm<T><<<(M + 7) / 8, 256, 0, s>>>(x, w, (T*)out, M, H, eps, split)));
-  return cudaGetLastError();
+  cudaError_t err;
+  Q3_DISPATCH(bf16, (err = launch_k(k_rmsnorm<T>, dim3((M + 7) / 8), dim3(256), 0, s, 1, x, w, (T*)out, M, H, eps, split)));
+  return err;
 }
 
 // ============================================================================================ RoPE table
@@ -171,6 +177,7 @@ __global__ void __launch_bounds__(128)
 k_attention(const T* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t, T* __restrict__ out, int Tn, int nh,
             int window) {
   extern __shared__ __align__(16) uint8_t att_smem[];
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int q0 = blockIdx.x * ATT_QT, h = blockIdx.y, b = blockIdx.z;
   const int k_lo = max(0, q0 - window + 1);
   const int k_hi = min(Tn, q0 + ATT_QT);  // exclusive
@@ -238,8 +245,9 @@ cudaError_t sliding_attention(const void* qkv, const float* cos_t, const float* 
   if (B <= 0 || Tn <= 0) return cudaSuccess;
   const size_t smem = ATT_SMEM;
   dim3 grid((Tn + ATT_QT - 1) / ATT_QT, nh, B);
-  Q3_DISPATCH(bf16, (k_attention<T><<<grid, 128, smem, s>>>((const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
-  return cudaGetLastError();
+  cudaError_t err;
+  Q3_DISPATCH(bf16, (err = launch_k(k_attention<T>, grid, dim3(128), smem, s, 1, (const T*)qkv, cos_t, sin_t, (T*)out, Tn, nh, window)));
+  return err;
 }
 
 }  // namespace q3

@@ -1,5 +1,6 @@
 // ConvNeXt depthwise conv + LayerNorm, layout probes.
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace q3 {
@@ -23,6 +24,7 @@ template <typename T, int NI, typename XT>
 __global__ void __launch_bounds__(256)
 k_dwconv_ln(const XT* __restrict__ x, const float* __restrict__ dww, const float* __restrict__ dwb, const float* __restrict__ lnw,
             const float* __restrict__ lnb, T* __restrict__ out, int B, int L, int C, float eps, int in_bs_rows, int hist) {
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= (long long)B * L) return;
@@ -85,15 +87,17 @@ cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, 
   const long long rows = (long long)B * L;
   if (rows <= 0) return cudaSuccess;
   const int blocks = (int)((rows + 7) / 8);
-  if (x_f32) Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8, float><<<blocks, 256, 0, s>>>((const float*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
-  else Q3_DISPATCH(bf16, (k_dwconv_ln<T, 8, T><<<blocks, 256, 0, s>>>((const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
-  return cudaGetLastError();
+  cudaError_t err;
+  if (x_f32) Q3_DISPATCH(bf16, (err = launch_k(k_dwconv_ln<T, 8, float>, dim3(blocks), dim3(256), 0, s, 1, (const float*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
+  else Q3_DISPATCH(bf16, (err = launch_k(k_dwconv_ln<T, 8, T>, dim3(blocks), dim3(256), 0, s, 1, (const T*)x, dww, dwb, lnw, lnb, (T*)out, B, L, C, eps, in_bs_rows, hist)));
+  return err;
 }
 
 // ============================================================================================ fp32 -> [hi | lo]
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_split_f32(const float* __restrict__ in, long long in_bs, T* __restrict__ out, long long out_bs, int rows, int C) {
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int b = blockIdx.y;
   const int c4 = C >> 2;
   const long long n = (long long)rows * c4;
@@ -116,8 +120,9 @@ cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out
   long long bx = ((long long)rows * (C >> 2) + 255) / 256;
   if (bx > 148 * 8) bx = 148 * 8;
   dim3 grid((unsigned)bx, (unsigned)B);
-  Q3_DISPATCH(bf16, (k_split_f32<T><<<grid, 256, 0, s>>>(in, in_bs, (T*)out, out_bs, rows, C)));
-  return cudaGetLastError();
+  cudaError_t err;
+  Q3_DISPATCH(bf16, (err = launch_k(k_split_f32<T>, grid, dim3(256), 0, s, 1, in, in_bs, (T*)out, out_bs, rows, C)));
+  return err;
 }
 
 // ============================================================================================ probes

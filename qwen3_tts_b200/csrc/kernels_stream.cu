@@ -3,6 +3,7 @@
 // modeling :885-895); these kernels make every stage causal-with-state so that the concatenated stream output equals
 // Decoder.forward(whole sequence) (DESIGN.md "Streaming").
 #include "kernels.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 #include "attention_mma.cuh"
 
@@ -38,6 +39,7 @@ k_stream_attention(const T* __restrict__ qkv, T* __restrict__ kc, T* __restrict_
                    const float* __restrict__ cos_t, const float* __restrict__ sin_t, int rope_max, float theta, T* __restrict__ out, int P, int nh,
                    int window, int ring, int krows) {
   extern __shared__ __align__(16) uint8_t sa_smem[];
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int h = blockIdx.x, s = blockIdx.y;
   const int slot = slot_ids[s];
   const int pos0 = slot_pos[slot];
@@ -123,15 +125,17 @@ cudaError_t stream_attention(const void* qkv, void* kc, void* vc, const int* slo
   const size_t smem = (size_t)(2 * krows + ((P + 15) & ~15)) * AM_PITCH * 2;
   if (smem > SA_SMEM_MAX) return cudaErrorInvalidValue;
   dim3 grid(nh, S);
-  Q3_DISPATCH(bf16, (k_stream_attention<T><<<grid, SA_WARPS * 32, smem, s>>>((const T*)qkv, (T*)kc, (T*)vc, slot_ids, slot_pos, cos_t, sin_t, rope_max, theta,
-                                                                               (T*)out, P, nh, window, ring, krows)));
-  return cudaGetLastError();
+  cudaError_t err;
+  Q3_DISPATCH(bf16, (err = launch_k(k_stream_attention<T>, grid, dim3(SA_WARPS * 32), smem, s, 1, (const T*)qkv, (T*)kc, (T*)vc, slot_ids, slot_pos, cos_t, sin_t, rope_max,
+                                    theta, (T*)out, P, nh, window, ring, krows)));
+  return err;
 }
 
 // ---------------------------------------------------------------------------------------------------------------- state copies
 // grid (stream, buffer); 16-byte chunks.  save = 0: state -> rows [0, H);  save = 1: rows [n, n + H) -> state.
 __global__ void __launch_bounds__(256)
 k_state_copy(const StreamBufDesc* __restrict__ descs, unsigned char* __restrict__ state, long long state_bytes, const int* __restrict__ slot_ids, int save) {
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const StreamBufDesc d = descs[blockIdx.y];
   const int s = blockIdx.x;
   const long long bytes = (long long)d.H * d.row_bytes;
@@ -145,18 +149,17 @@ cudaError_t stream_state_copy(const StreamBufDesc* descs, int ndesc, unsigned ch
                               cudaStream_t s) {
   if (S <= 0 || ndesc <= 0) return cudaSuccess;
   dim3 grid(S, ndesc);
-  k_state_copy<<<grid, 256, 0, s>>>(descs, state, state_bytes, slot_ids, save);
-  return cudaGetLastError();
+  return launch_k(k_state_copy, grid, dim3(256), 0, s, 1, descs, state, state_bytes, slot_ids, save);
 }
 
 __global__ void k_advance_pos(int* slot_pos, const int* slot_ids, int S, int P) {
+  pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < S) slot_pos[slot_ids[i]] += P;
 }
 cudaError_t stream_advance_pos(int* slot_pos, const int* slot_ids, int S, int P, cudaStream_t s) {
   if (S <= 0) return cudaSuccess;
-  k_advance_pos<<<(S + 127) / 128, 128, 0, s>>>(slot_pos, slot_ids, S, P);
-  return cudaGetLastError();
+  return launch_k(k_advance_pos, dim3((S + 127) / 128), dim3(128), 0, s, 1, slot_pos, slot_ids, S, P);
 }
 
 __global__ void __launch_bounds__(256)

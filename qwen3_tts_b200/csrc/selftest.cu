@@ -309,6 +309,10 @@ extern "C" int q3tts_selftest_snake(int device, const float* x_host, int n, floa
   return e == cudaSuccess ? Q3TTS_OK : Q3TTS_CUDA_ERROR;
 }
 
+#include "launch.cuh"
+// Same-box A/B of programmatic dependent launch: 0 = every kernel serialises on the previous one (plain stream order), 1 = default.
+extern "C" int q3tts_debug_set_pdl(int on) { q3::pdl_set(on != 0); return Q3TTS_OK; }
+
 extern "C" int q3tts_unit_trace(long long* out256) { return unit_trace_read(out256); }
 
 // ---------------------------------------------------------------------------------------------------------------------

@@ -12,6 +12,7 @@
 // Roles: warp 0 TMA producer (ring of input tiles), warp 1 MMA issuer (ring of 16-column accumulators in tensor memory),
 // warps 2..5 epilogue.  HBM-bound by construction: 24.6 KB in, 0.5 KB out per tile.
 #include "conv_gemm.h"
+#include "launch.cuh"
 #include "ptx.cuh"
 
 namespace q3 {
@@ -55,6 +56,8 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_trigger();  // programmatic dependent launch (launch.cuh): after the TMEM allocation
+  pdl_wait();
   const uint32_t tmem_base = bars->tmem_base;
 
   if (warp == 0) {
@@ -173,9 +176,8 @@ cudaError_t launch_tail(const TailOp& op, cudaStream_t stream) {
   if (tiles <= 0) return cudaSuccess;
   const int grid = tiles < gemm_num_sms() ? tiles : gemm_num_sms();
   const size_t smem = tail_smem(p.C, op.nstages);
-  if (p.bf16) tail_conv_kernel<__nv_bfloat16><<<grid, 192, smem, stream>>>(op.tmA, op.tmW, p, op.nstages);
-  else tail_conv_kernel<__half><<<grid, 192, smem, stream>>>(op.tmA, op.tmW, p, op.nstages);
-  return cudaGetLastError();
+  if (p.bf16) return launch_k(tail_conv_kernel<__nv_bfloat16>, dim3(grid), dim3(192), smem, stream, 1, op.tmA, op.tmW, p, op.nstages);
+  return launch_k(tail_conv_kernel<__half>, dim3(grid), dim3(192), smem, stream, 1, op.tmA, op.tmW, p, op.nstages);
 }
 
 }  // namespace q3

@@ -18,6 +18,7 @@
 // so a C = 96 layer cannot exceed 41 % of the tensor peak in this operand arrangement; the kernel is built to sit on
 // that floor (DESIGN.md "Fused residual unit").
 #include "conv_gemm.h"
+#include "launch.cuh"
 #include "pair_ptx.cuh"
 #include "tc_epilogue.cuh"
 
@@ -184,6 +185,8 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   __syncthreads();
   if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
   tc_fence_after();
+  pdl_trigger();  // programmatic dependent launch (launch.cuh): after the TMEM allocation, see conv_gemm.cu init_common
+  pdl_wait();     // the parameter tables above are weights; activations are only touched below
   const uint32_t tmem_base = bars->tmem_base;
   // TMEM column map inside one stage; stage s starts at column s * 256
   constexpr uint32_t c_acc1 = 0, c_acc2 = C, c_a2 = 2 * C;
@@ -742,13 +745,8 @@ int unit_trace_read(long long* out256) { return cudaMemcpyFromSymbol(out256, g_u
 
 template <typename T, typename Cfg>
 static cudaError_t launch_one(const UnitOp& op, const UnitArgs& u, int grid, size_t smem, cudaStream_t stream) {
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kUnitThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = Cfg::PAIR ? 2 : 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, unit_kernel<T, Cfg>, op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw, op.tmSnake, op.p, u);
+  return launch_k(unit_kernel<T, Cfg>, dim3((unsigned)grid), dim3(kUnitThreads), smem, stream, Cfg::PAIR ? 2 : 1, op.tmA, op.tmW7, op.tmW1, op.tmRes, op.tmRaw,
+                  op.tmSnake, op.p, u);
 }
 template <typename Cfg>
 static cudaError_t launch_cfg(const UnitOp& op, const UnitArgs& u, int grid, size_t smem, cudaStream_t stream) {
