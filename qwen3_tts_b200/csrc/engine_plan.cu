@@ -51,11 +51,11 @@ struct Builder {
     op.tag = name; op.probe_ptr = ptr; op.probe_f32 = f32; op.probe_C = C; op.probe_L = L; op.probe_ld = ld;
   }
   // fp32 [batches][rows][C] -> 16-bit rows [hi | lo]: the split-precision A operand of the next GEMM
-  Op& split(const float* in, void* out, int batches, int rows, int C) {
+  Op& split(const float* in, void* out, int batches, int rows, int C, bool with_lo = true) {
     plan->ops.emplace_back();
     Op& op = plan->ops.back();
-    op.type = OP_SPLIT; op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C;
-    op.sp_in_bs = (long long)rows * C; op.sp_out_bs = (long long)rows * 2 * C;
+    op.type = OP_SPLIT; op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C; op.split = with_lo ? 1 : 0;
+    op.sp_in_bs = (long long)rows * C; op.sp_out_bs = (long long)rows * (with_lo ? 2 : 1) * C;
     return op;
   }
 };
@@ -145,7 +145,10 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     void* Nn = b.alloc((size_t)B * Lo * Lat * es);
     void* G = b.alloc((size_t)B * Lo * 4 * Lat * es);
     void* V = b.alloc((size_t)B * Lo * Lat * (sp_main ? 4 : es));
-    void* V16 = sp_main ? b.alloc((size_t)B * Lo * 2 * Lat * es) : V;
+    // the 16-bit copy the next GEMM reads: [hi | lo] rows when it takes split operands (the next upsample conv always does; decoder[0]
+    // only in the split-all mode), else the fp32 tensor rounded once
+    const bool next_split = i + 1 < e->ups.size() ? e->ups[i + 1].tconv.k_mult == 3 : e->dec0.k_mult == 3;
+    void* V16 = sp_main ? b.alloc((size_t)B * Lo * (next_split ? 2 : 1) * Lat * es) : V;
     {
       Op& op = b.gemm(U.tconv, cur, 1, B * L, B * L);  // k == stride: rows are independent, flatten the batch
       if (sp_main) op.g.p.out_f32 = (float*)Uo; else op.g.p.out_raw = Uo;
@@ -166,7 +169,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
       const std::string t = "upsample." + std::to_string(i) + ".1";
       b.tag(op, t.c_str(), V, sp_main, Lat, Lo);
     }
-    if (sp_main) b.split((const float*)V, V16, 1, B * Lo, Lat);
+    if (sp_main) b.split((const float*)V, V16, 1, B * Lo, Lat, next_split);
     cur = V16; L = Lo;
   }
   // ---- vocoder: three rotating buffers sized for the largest stage
@@ -375,7 +378,7 @@ void prof_account(Engine* e, const Op& op) {
     fl = 4.0 * rows * H * e->cfg.sliding_window;  // QK^T and PV at a full window, as SURVEY 8(a) counts them
     by = 2.0 * rows * 4.0 * H;                    // q, k, v in, o out (16-bit)
   } else if (op.type == OP_SPLIT) {
-    by = (4.0 + 4.0) * (double)op.B * op.L * op.C;  // fp32 in, two 16-bit values out
+    by = (4.0 + (op.split ? 4.0 : 2.0)) * (double)op.B * op.L * op.C;  // fp32 in, one or two 16-bit values out
   } else if (op.type == OP_DWLN) {
     by = (op.split ? 4.0 + 2.0 : 2.0 * 2.0) * (double)op.B * op.L * op.C;  // one read and one write of the token tensor
   }
@@ -416,7 +419,7 @@ int engine_run(Engine* e, Plan* plan, const long long* codes, long long sb, long
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
       case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s, op.split); break;
-      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s); break;
+      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s, op.split); break;
       case OP_ATTN:
         err = sliding_attention(op.in, e->rope_cos, e->rope_sin, op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->bf16, s);
         break;

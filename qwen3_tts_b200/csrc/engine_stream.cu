@@ -64,9 +64,9 @@ struct SBuilder {
       rc = e->fail(Q3TTS_CUDA_ERROR, "cuTensorMapEncodeTiled failed (weights)");
     return op;
   }
-  Op& split(const float* in, long long in_bs, void* out, long long out_bs, int batches, int rows, int C) {
+  Op& split(const float* in, long long in_bs, void* out, long long out_bs, int batches, int rows, int C, bool with_lo = true) {
     Op& op = simple(OP_SPLIT);
-    op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C; op.sp_in_bs = in_bs; op.sp_out_bs = out_bs;
+    op.in = in; op.out = out; op.B = batches; op.L = rows; op.C = C; op.sp_in_bs = in_bs; op.sp_out_bs = out_bs; op.split = with_lo ? 1 : 0;
     return op;
   }
   Op& simple(OpType t) {
@@ -124,7 +124,7 @@ int build_stream(Engine* e, StreamPlan* plan, int S, int P, bool fresh, bool dry
   // ---- upsample: [TransConv k = s ; ConvNeXt]; the depthwise k7 needs 6 rows of history
   const void* cur = TO16;  // dense [S][L][Lat] ([hi | lo] rows in split-precision plans)
   const int ue = sp_main ? 4 : 2;   // element size of the main-path tensors Uo / V: fp32 in split-precision plans
-  const int Vw = sp_main ? 2 * Lat : Lat;  // row width of the 16-bit tensor the next GEMM reads
+  const bool sp_dec0 = e->dec0.k_mult == 3;  // decoder[0] takes split operands only in the split-all mode
   int L = P;
   void* dec_in = nullptr;  // [S][6 | L][Vw] input of decoder[0]
   for (size_t i = 0; i < e->ups.size(); ++i) {
@@ -132,6 +132,8 @@ int build_stream(Engine* e, StreamPlan* plan, int S, int P, bool fresh, bool dry
     const int r = c.upsampling_ratios[i];
     const int Lo = L * r;
     const bool last = i + 1 == e->ups.size();
+    const bool next_split = sp_main && (last ? sp_dec0 : true);
+    const int Vw = next_split ? 2 * Lat : Lat;  // row width of the 16-bit tensor the next GEMM reads
     void* Uo = b.hist_buf(S, 6, Lo, Lat, ue);
     void* Nn = b.alloc((size_t)S * Lo * Lat * es);
     void* G = b.alloc((size_t)S * Lo * 4 * Lat * es);
@@ -156,7 +158,7 @@ int build_stream(Engine* e, StreamPlan* plan, int S, int P, bool fresh, bool dry
       if (sp_main) { op.g.p.res_f32 = 1; op.g.p.out_f32 = (float*)Vf; op.g.p.out_batch_stride = (long long)Lo * Lat; }
       else { op.g.p.out_raw = Vrow0; op.g.p.out_batch_stride = V_bs; }
     }
-    if (sp_main) b.split((const float*)Vf, (long long)Lo * Lat, Vrow0, V_bs, S, Lo, Lat);
+    if (sp_main) b.split((const float*)Vf, (long long)Lo * Lat, Vrow0, V_bs, S, Lo, Lat, next_split);
     cur = V; L = Lo;
     if (last) dec_in = V;
   }
@@ -367,7 +369,7 @@ int launch_stream_plan(Engine* e, StreamPlan* plan, const long long* codes, long
       case OP_GEMM: err = launch_conv_gemm(op.g, ENGINE_TC, s); break;
       case OP_UNIT: err = launch_unit(op.u, s); break;
       case OP_RMSNORM: err = rmsnorm((const float*)op.in, op.w0, op.out, op.B, op.C, c.rms_norm_eps, e->bf16, s, op.split); break;
-      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s); break;
+      case OP_SPLIT: err = split_f32((const float*)op.in, op.sp_in_bs, op.out, op.sp_out_bs, op.B, op.L, op.C, e->bf16, s, op.split); break;
       case OP_STREAM_ATTN:
         err = stream_attention(op.in, e->kcache[op.aux0], e->vcache[op.aux0], d_ids, e->d_slot_pos, e->rope_cos, e->rope_sin, e->rope_max, c.rope_theta,
                                op.out, op.B, op.L, c.num_attention_heads, c.head_dim, c.sliding_window, e->kv_ring, e->bf16, s);

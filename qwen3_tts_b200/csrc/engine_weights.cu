@@ -225,7 +225,9 @@ int engine_finalize(Engine* e, int mode) {
   }
   // ---- vocoder
   const int Dd = c.decoder_dim;
-  e->dec0 = f.conv("decoder.0.conv", Dd, Lat, 7, 1, true, sp_main);
+  // decoder[0] is the one big GEMM of the early stages (44 MMAC/frame): 3x its MMAs cost 1.0 ms per 64 x 10 s step for ~4 % of the noise,
+  // so it takes split operands only at level 2; at level 1 it reads the fp32 main-path tensor rounded once to 16 bit
+  e->dec0 = f.conv("decoder.0.conv", Dd, Lat, 7, 1, true, e->split_level >= 2 ? 3 : 1);
   e->blocks.assign(c.num_upsample_rates, BlockW());
   int total_up = 1, look = 0;
   for (int i = 0; i < c.num_upsampling_ratios; ++i) total_up *= c.upsampling_ratios[i];

@@ -39,7 +39,8 @@ cudaError_t rvq_decode(const long long* codes, long long sb, long long sk, long 
 cudaError_t rmsnorm(const float* x, const float* w, void* out, int M, int H, float eps, bool bf16, cudaStream_t s, int split = 0);
 // fp32 [B][rows][C] (in_bs elements between items) -> 16-bit [B][.][2C] rows [hi | lo] (out_bs elements between items): turns an fp32
 // main-path tensor into the split-precision A operand of the next GEMM
-cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s);
+// with_lo = 0: plain 16-bit rows (C wide): the fp32 tensor rounded once, for a consumer with plain operands
+cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s, int with_lo = 1);
 // rope table [maxT][hd/2] cos, sin (fp32)
 cudaError_t rope_table(float* cos_t, float* sin_t, int maxT, int hd, float theta, cudaStream_t s);
 // qkv 16-bit [B*T][3*nh*hd] (q | k | v), RoPE applied on the fly with position = t; causal, kv > q - window.

@@ -96,7 +96,7 @@ cudaError_t dwconv_layernorm(const void* x, const float* dww, const float* dwb, 
 // ============================================================================================ fp32 -> [hi | lo]
 template <typename T>
 __global__ void __launch_bounds__(256)
-k_split_f32(const float* __restrict__ in, long long in_bs, T* __restrict__ out, long long out_bs, int rows, int C) {
+k_split_f32(const float* __restrict__ in, long long in_bs, T* __restrict__ out, long long out_bs, int rows, int C, int with_lo) {
   pdl_trigger(); pdl_wait();  // programmatic dependent launch (launch.cuh): no prologue worth overlapping, only the launch latency
   const int b = blockIdx.y;
   const int c4 = C >> 2;
@@ -109,19 +109,19 @@ k_split_f32(const float* __restrict__ in, long long in_bs, T* __restrict__ out, 
     h.x = Elem<T>::pack2(v.x, v.y); h.y = Elem<T>::pack2(v.z, v.w);
     const float2 h0 = Elem<T>::unpack2(h.x), h1 = Elem<T>::unpack2(h.y);
     l.x = Elem<T>::pack2(v.x - h0.x, v.y - h0.y); l.y = Elem<T>::pack2(v.z - h1.x, v.w - h1.y);
-    T* o = out + b * out_bs + r * (2ll * C);
+    T* o = out + b * out_bs + r * (with_lo ? 2ll * C : (long long)C);
     *reinterpret_cast<uint2*>(o + c) = h;
-    *reinterpret_cast<uint2*>(o + C + c) = l;
+    if (with_lo) *reinterpret_cast<uint2*>(o + C + c) = l;
   }
 }
-cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s) {
+cudaError_t split_f32(const float* in, long long in_bs, void* out, long long out_bs, int B, int rows, int C, bool bf16, cudaStream_t s, int with_lo) {
   if (B <= 0 || rows <= 0) return cudaSuccess;
   if (C % 4) return cudaErrorInvalidValue;
   long long bx = ((long long)rows * (C >> 2) + 255) / 256;
   if (bx > 148 * 8) bx = 148 * 8;
   dim3 grid((unsigned)bx, (unsigned)B);
   cudaError_t err;
-  Q3_DISPATCH(bf16, (err = launch_k(k_split_f32<T>, grid, dim3(256), 0, s, 1, in, in_bs, (T*)out, out_bs, rows, C)));
+  Q3_DISPATCH(bf16, (err = launch_k(k_split_f32<T>, grid, dim3(256), 0, s, 1, in, in_bs, (T*)out, out_bs, rows, C, with_lo)));
   return err;
 }
 
