@@ -122,6 +122,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   ts.m_tiles = p.pack_mode ? 1 : (p.rows_valid + TM - 1) / TM;  // packed: decode() returns the tile index as "batch"
   ts.n_tiles = p.n_total / p.bn;
   ts.total_tiles = (PAIR ? p.batches * ts.m_tiles : gemm_m_tiles_total(p)) * ts.n_tiles;
+  ts.init();
   const int kblocks = p.cin / KB;
   const int ksteps = kblocks * p.ntaps;
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
@@ -240,6 +241,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   ts.m_tiles = (p.rows_valid + BM - 1) / BM;
   ts.n_tiles = 1;
   ts.total_tiles = p.batches * ts.m_tiles;
+  ts.init();
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
   init_common(bars, nslabs, warp, p.epi_warps);
   const uint32_t tmem_base = bars->tmem_base;
@@ -351,6 +353,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   ts.m_tiles = (p.rows_valid + TM - 1) / TM;
   ts.n_tiles = p.n_total / p.bn;
   ts.total_tiles = p.batches * ts.m_tiles * ts.n_tiles;
+  ts.init();
   if (threadIdx.x == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
   init_common(bars, nstages, warp, p.epi_warps, PAIR);
   const uint32_t tmem_base = bars->tmem_base;

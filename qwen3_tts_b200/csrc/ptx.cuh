@@ -23,6 +23,27 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---------------------------------------------------------------- division by a loop-invariant integer
+// tile -> (batch item, M tile, N tile) decodes run once per tile AND once per epilogue item / residual prefetch; as runtime
+// divisions (IABS / I2F.RP / MUFU.RCP / F2I ...: ~50 instructions each) they were 11 % of the samples of an epilogue-bound layer
+// (profiles/r1_ncu_tconv96_12warps.txt).  q = umulhi(n, mul) >> shr is exact for 0 <= n < 2^31 (round-up method: mul =
+// ceil(2^(31 + ceil(log2 d)) / d)); the constants are computed once per thread at kernel start.
+struct FastDiv {
+  uint32_t mul, shr, d;
+  __host__ __device__ FastDiv() : mul(0), shr(0), d(1) {}
+  __host__ __device__ explicit FastDiv(uint32_t dv) : mul(0), shr(0), d(dv ? dv : 1u) {
+    if (d != 1u) {
+      uint32_t lg = 0;
+      while ((1u << lg) < d) ++lg;
+      const uint32_t p = 31u + lg;
+      mul = (uint32_t)((((unsigned long long)1 << p) + d - 1) / d);
+      shr = p - 32u;
+    }
+  }
+  __device__ __forceinline__ int div(int n) const { return d == 1u ? n : (int)(__umulhi((uint32_t)n, mul) >> shr); }
+  __device__ __forceinline__ void divmod(int n, int& q, int& r) const { q = div(n); r = n - q * (int)d; }
+};
+
 // ---------------------------------------------------------------- programmatic dependent launch (launch.cuh)
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

@@ -45,6 +45,7 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_per_item = (p.rows_valid + T_OUT - 1) / T_OUT;
   const int total_tiles = p.batches * tiles_per_item;
+  const FastDiv fdt((uint32_t)tiles_per_item);
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmW);
     for (int s = 0; s < nstages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
@@ -66,7 +67,7 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int kk = 0; kk < KS; ++kk) tma_load_3d(sW + kk * 1024, &tmW, &bars->w_full, kk * 32, 0, 0);
       int s = 0; uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int b = tile / tiles_per_item, t0 = (tile - b * tiles_per_item) * T_OUT;
+        int b, t0; fdt.divmod(tile, b, t0); t0 *= T_OUT;
         mbar_wait_backoff(&bars->empty[s], ph ^ 1);
         mbar_expect_tx(&bars->full[s], stage_bytes);
         for (int kk = 0; kk < KS; ++kk)
@@ -103,7 +104,7 @@ tail_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     int it = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int b = tile / tiles_per_item, t0 = (tile - b * tiles_per_item) * T_OUT;
+      int b, t0; fdt.divmod(tile, b, t0); t0 *= T_OUT;
       const int a = it & (T_NACC - 1);
       const long long cut = p.item_skip ? __ldg(p.item_skip + b) : 0;
       mbar_wait(&bars->acc_full[a], (uint32_t)(it / T_NACC) & 1u);

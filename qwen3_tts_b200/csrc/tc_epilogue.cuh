@@ -37,12 +37,13 @@ __device__ __forceinline__ uint32_t slot_off(int lane, int c) { return (uint32_t
 
 struct TileSched {
   int m_tiles, n_tiles, total_tiles;
+  FastDiv fn, fm;  // division by n_tiles / m_tiles as multiply-shift (set by init())
+  __device__ __forceinline__ void init() { fn = FastDiv((uint32_t)n_tiles); fm = FastDiv((uint32_t)m_tiles); }
   __device__ __forceinline__ void decode(int tile, int& nt, int& mt, int& b) const {  // 32-bit: total_tiles < 2^31
     int q = tile;
     nt = 0;
-    if (n_tiles > 1) { q = tile / n_tiles; nt = tile - q * n_tiles; }
-    b = q / m_tiles;
-    mt = q - b * m_tiles;
+    if (n_tiles > 1) fn.divmod(tile, q, nt);
+    fm.divmod(q, b, mt);
   }
 };
 
@@ -244,7 +245,8 @@ struct EpiWarp {
   // ---- fp32 flow: 16 accumulator columns; residual and/or output are fp32 (transformer residual stream)
   __device__ __forceinline__ void item_f32(uint32_t t0, int nt, int row0, int b, int item) {
     const int n0 = nt * p.bn + item * 16;
-    const int c0 = wraps ? n0 % p.ncol_mod : n0;
+    int c0 = n0;
+    if (wraps) { c0 = tile_c0 + item * 16; while (c0 >= p.ncol_mod) c0 -= p.ncol_mod; }  // tile_c0: one modulo per tile, not per item
     float rs[16];
     if (has_res) {
       const uint32_t slot = rb_cons & (rd - 1);

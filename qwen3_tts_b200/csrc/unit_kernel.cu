@@ -153,6 +153,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   UnitBarriers* bars = reinterpret_cast<UnitBarriers*>(prm + 8 * C);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (p.rows_valid + TM - 1) / TM;
+  const FastDiv fdm((uint32_t)m_tiles);  // tile -> (batch item, M tile) by multiply-shift (ptx.cuh): the decode runs per tile and per residual prefetch
   const int total_tiles = p.batches * m_tiles;
   const int my_tiles = total_tiles > wid ? (total_tiles - wid + nworkers - 1) / nworkers : 0;
   constexpr int grp_warps = NBUF == 2 ? 4 : 8;  // epilogue warps that serve one TMEM stage
@@ -245,7 +246,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int wrow = PAIR ? rank * (C / 2) : 0;  // this CTA's output-channel rows of a weight stage
       auto load_m1 = [&](int j) {  // slabs and W7 stages of this CTA's j-th tile
         const int tile = wid + j * nworkers;
-        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        int b, mt; fdm.divmod(tile, b, mt);
         for (int kg = 0; kg < NKG; ++kg) {
           if (!XIN) {
             mbar_wait(&bars->sempty[ss], sph ^ 1);
@@ -269,7 +270,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // tile's MMAs), so they are issued on their own, not in MMA order; each lands on this CTA's own barrier.
       auto load_slab_x = [&](int j) {
         const int tile = wid + j * nworkers;
-        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        int b, mt; fdm.divmod(tile, b, mt);
         mbar_wait(&bars->sempty[ss], sph ^ 1);
         mbar_expect_tx(&bars->sland[ss], slab_bytes);
         for (int kk = 0; kk < KS; ++kk)
@@ -521,7 +522,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (pf_j >= my_tiles || Q3_DBG(p, 128)) return;
       if (lane == 0) {
         const int tile = wid + pf_j * nworkers;
-        const int b = tile / m_tiles, mt = tile - b * m_tiles;
+        int b, mt; fdm.divmod(tile, b, mt);
         const uint32_t slot = issued & (URES - 1);
         const uint32_t bar = rbar + slot * 8u;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)kEpiSlot) : "memory");
@@ -535,7 +536,7 @@ unit_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int sb = NBUF == 2 ? (P2X ? (j & 1) : grp) : 0;
       const uint32_t acc = tmem_base + lane_base + (uint32_t)(sb * 256) + c_acc2 + tcol + (uint32_t)(32 * item0);
       const int tile = wid + j * nworkers;
-      const int b = tile / m_tiles, mt = tile - b * m_tiles;
+      int b, mt; fdm.divmod(tile, b, mt);
       const int row0 = mt * TM + rsub;
       if (P1A) {  // this warp's slice of phase 1 first: the tensor pipe waits for it
         mbar_wait(&bars->acc1_full[0], (uint32_t)j & 1);
