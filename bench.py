@@ -308,7 +308,8 @@ def stream_latency(dec, cfg, dev, streams: int, packet: int, steps: int, warmup:
 
 def run_sharded(args, rank, local_rank, world):
     """--workload sharded30s: BASELINE config 5 as STRONG scaling - a FIXED set of `--utterances` ragged utterances (true lengths
-    U[0.5, 1] x 375 frames, seeded) is partitioned over the ranks by qwen3_tts_b200.sharding (longest-first, then length buckets);
+    U[0.5, 1] x 375 frames, seeded) is bucketed by length GLOBALLY and the batches are dealt to the ranks longest-first
+    queue order (qwen3_tts_b200.sharding.global_batches); the ranks PULL batches through an atomic counter in the launcher's store;
     every rank decodes its shard end to end (host codes -> host waveforms through Qwen3TTSTokenizer.decode); no data-path collective.
     A step = the whole set once; value = audio-seconds of the whole set / max-over-ranks wall time of the step."""
     import numpy as np
@@ -317,7 +318,7 @@ def run_sharded(args, rank, local_rank, world):
 
     from qwen3_tts_b200 import Qwen3TTSTokenizer, synthetic_model
     from qwen3_tts_b200.configuration import Qwen3TTSTokenizerV2DecoderConfig
-    from qwen3_tts_b200.sharding import bucket_by_length, decode_shard, frames_cost, shard_utterances
+    from qwen3_tts_b200.sharding import batch_cost, decode_shard, global_batches
     from qwen3_tts_b200.synthetic import make_codes
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -329,32 +330,49 @@ def run_sharded(args, rank, local_rank, world):
     cfg = Qwen3TTSTokenizerV2DecoderConfig()
     n_utt, Tmax = args.utterances, 375
     lengths = [int(v) for v in np.random.default_rng(5).integers(Tmax // 2, Tmax + 1, n_utt)]
-    mine = shard_utterances(lengths, world, rank)
     max_frames = 64 * Tmax
+    batches = global_batches(lengths, world, max_frames)            # global length buckets, most expensive first: the shared work queue
     model = synthetic_model(seed=0, device=dev, compute_mode=args.mode)
     model.decoder.reserve(64 * 325)
     tok = Qwen3TTSTokenizer.from_model(model)
-    codes = {i: make_codes(1, lengths[i], cfg, seed=1000 + i)[0].pin_memory() for i in mine}
-    dense = [codes[i] for i in mine]
-    batches = bucket_by_length(list(range(len(dense))), [lengths[i] for i in mine], max_frames)
+    # every rank may pull any batch, so every rank holds all codes (147 MB of int64 for 4096 utterances) in pinned memory
+    dense = [make_codes(1, lengths[i], cfg, seed=1000 + i)[0].pin_memory() for i in range(n_utt)]
     for bt in batches:                                                   # warm-up: one untimed pass over every batch shape (launch plans,
-        decode_shard(tok, dense, bt, max_frames)                         # workspace, pinned result buffers of the host allocator)
+        decode_shard(tok, dense, [], max_frames, batches=[bt])           # workspace, pinned result buffers of the host allocator)
+    store = dist.distributed_c10d._get_default_store() if world > 1 else None   # the launcher's key-value store: host-side, no collective
     times = []
     l0 = model.decoder.launch_count()
-    for _ in range(args.steps):
+    # breakdown: seconds inside the C decode call (H2D, kernels, direct D2H, synchronise) vs the whole Python step of this rank
+    in_call = [0.0]
+    _orig_decode_host = model.decode_host
+
+    def _timed_decode_host(*a, **k):
+        t = time.perf_counter()
+        r = _orig_decode_host(*a, **k)
+        in_call[0] += time.perf_counter() - t
+        return r
+    model.decode_host = _timed_decode_host
+    my_cost, n_out = 0.0, 0
+    for step in range(args.steps):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
-        n_out = 0
-        for bt in batches:
-            out = decode_shard(tok, dense, bt, max_frames)
+        taken = 0
+        while True:
+            # pull the next batch: an atomic counter per step (rank order does not matter, a faster GPU simply takes more batches)
+            k = (store.add(f"q3tts_step{step}", 1) - 1) if store is not None else taken
+            if k >= len(batches):
+                break
+            out = decode_shard(tok, dense, [], max_frames, batches=[batches[k]])
             n_out += sum(int(w.shape[0]) for w in out.values())
+            my_cost += batch_cost(batches[k], lengths)
+            taken += 1
         torch.cuda.synchronize(dev)
         times.append(time.perf_counter() - t0)
     launches = model.decoder.launch_count() - l0
     tt = torch.tensor(times, dtype=torch.float64, device=dev)
-    load = torch.tensor([float(sum(frames_cost(lengths[i]) for i in mine))], dtype=torch.float64, device=dev)
+    load = torch.tensor([my_cost / max(1, args.steps), in_call[0], float(sum(times))], dtype=torch.float64, device=dev)
     loads = [load.clone() for _ in range(world)]
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -362,19 +380,23 @@ def run_sharded(args, rank, local_rank, world):
     if rank == 0:
         sec = float(tt.sum().item())
         audio_s = sum(lengths) * FRAME_SEC * args.steps
-        ld = [float(x.item()) for x in loads]
+        ld = [float(x[0].item()) for x in loads]
+        call_frac = [float(x[1].item()) / max(float(x[2].item()), 1e-9) for x in loads]
         h2d = sum(lengths) * 16 * 8
         line = {"metric": "audio-sec decoded per sec (codes->24kHz)", "value": audio_s / sec, "unit": "audio-s/s", "n_gpus": world, "steps": args.steps,
                 "warmup": 1, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": f"{args.mode} tensor-core operands, fp32 accumulate", "data": "synthetic",
                 "config": {"workload": f"Offline bulk decode of a FIXED set of {n_utt} ragged utterances (true lengths U[0.5,1] x 30 s, 16-codebook codes) "
-                                       f"sharded by utterance over {world} GPU(s): longest-first partition + length buckets (BASELINE config 5)",
-                           "audio_seconds_per_step": sum(lengths) * FRAME_SEC, "batches_rank0": len(batches),
+                                       f"sharded by utterance over {world} GPU(s): global length buckets pulled longest-first from one queue (BASELINE config 5)",
+                           "audio_seconds_per_step": sum(lengths) * FRAME_SEC, "batches": len(batches),
                            "frames_cost_max_over_mean": max(ld) / (sum(ld) / len(ld)), "parallelism": f"utterance-sharded x{world}, no collective",
                            "l2": "inputs and activations per step >> 126 MB L2"},
-                "e2e": {"value": audio_s / sec, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(n_out) * 4 * world,
+                "e2e": {"value": audio_s / sec, "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(sum(min(n * 1920, 375 * 1920 - 1110) for n in lengths)) * 4,
                         "api": "qwen3_tts_b200.sharding.decode_shard -> Qwen3TTSTokenizer.decode (pinned host codes -> host float32 arrays), the whole step"},
-                "gpu_launches": launches}
+                "gpu_launches": launches,
+                "per_rank": {"seconds": [float(x[2].item()) for x in loads],
+                             "fraction_inside_decode_call": [round(v, 4) for v in call_frac],
+                             "note": "decode call = q3tts_decode_host (H2D, kernels, direct D2H, synchronise); the rest is Python host work between batches"}}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 def test_sharded_decoder_matches_direct_decode(gpu_model, cfg):
     from qwen3_tts_b200 import Qwen3TTSTokenizer, ShardedDecoder
-    from qwen3_tts_b200.sharding import decode_shard, shard_utterances
+    from qwen3_tts_b200.sharding import decode_shard, global_batches
     from qwen3_tts_b200.synthetic import make_codes
     ndev = min(2, torch.cuda.device_count())
     devices = [f"cuda:{i}" for i in range(ndev)]
@@ -20,13 +20,13 @@ def test_sharded_decoder_matches_direct_decode(gpu_model, cfg):
         wavs, sr = sd.decode_sharded(codes)
         pcm, _ = sd.decode_sharded(codes[:3], pcm16=True)
     assert sr == 24000 and len(wavs) == len(codes)
-    # the same shards, same buckets, decoded in this process on the session's model (same seeded weights)
+    # the same global buckets, dealt the same way, decoded in this process on the session's model (same seeded weights); an item's
+    # waveform depends on the padded length of its batch (length rule, modeling :1012-1015), so the batches must be the same ones
     tok = Qwen3TTSTokenizer.from_model(gpu_model)
-    for r in range(ndev):
-        idx = shard_utterances(lengths, ndev, r)
-        dense = [codes[i] for i in idx]
-        want = decode_shard(tok, dense, list(range(len(dense))), 96)
-        for k, i in enumerate(idx):
-            assert wavs[i].dtype == np.float32 and wavs[i].shape == want[k].shape
-            np.testing.assert_array_equal(wavs[i], want[k])
+    batches = global_batches(lengths, ndev, 96)
+    assert sorted(i for b in batches for i in b) == list(range(len(codes)))
+    want = decode_shard(tok, codes, [], 96, batches=batches)
+    for i, w in want.items():
+        assert wavs[i].dtype == np.float32 and wavs[i].shape == w.shape
+        np.testing.assert_array_equal(wavs[i], w)
     assert pcm[0].dtype == np.int16 and pcm[0].shape[0] > 0

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 import torch
 
-from qwen3_tts_b200.sharding import ShardedDecoder, decode_shard, plan_batches, shard_utterances
+from qwen3_tts_b200.sharding import ShardedDecoder, batch_cost, decode_shard, global_batches, plan_batches, shard_batches, shard_utterances
 
 
 def _fake_worker(rank, device, spec, jobs, results):
@@ -13,8 +13,8 @@ def _fake_worker(rank, device, spec, jobs, results):
         job = jobs.get()
         if job is None:
             return
-        job_id, indices, codes, max_frames, pcm16 = job
-        if spec.get("fail_on") == rank:
+        job_id, indices, codes, pcm16 = job
+        if spec.get("fail_on") is not None and len(indices) and spec["fail_on"] in indices:
             results.put(("error", rank, "boom"))
             continue
         # "waveform" of an utterance: its first codebook column repeated `up` times, tagged with the rank that decoded it
@@ -35,8 +35,10 @@ def test_dispatcher_gathers_in_input_order_and_balances():
                 rank = int(round(float(w[0] - c[0, 0]) / 1000.0))
                 owners.append(rank)
                 np.testing.assert_array_equal(w - 1000.0 * rank, np.repeat(c[:, 0].numpy().astype(np.float32), 3))
-            for r in (0, 1):
-                assert sorted(i for i, o in enumerate(owners) if o == r) == shard_utterances(lengths, 2, r)
+            # pull-based: which worker took which batch is not fixed, but every batch was decoded whole by ONE worker
+            for b in global_batches(lengths, 2, 64):
+                assert len({owners[i] for i in b}) == 1
+            assert set(owners) <= {0, 1}
     plans = plan_batches(lengths, 2, 64)
     assert sorted(i for rank in plans for b in rank for i in b) == list(range(len(lengths)))
     assert all(max(lengths[i] for i in b) * len(b) <= 64 or len(b) == 1 for rank in plans for b in rank)
@@ -44,7 +46,7 @@ def test_dispatcher_gathers_in_input_order_and_balances():
 
 def test_dispatcher_propagates_worker_errors():
     codes = [torch.ones((5, 16), dtype=torch.long) for _ in range(4)]
-    with ShardedDecoder(["cpu:0", "cpu:1"], {"up": 2, "fail_on": 1}, worker=_fake_worker) as sd:
+    with ShardedDecoder(["cpu:0", "cpu:1"], {"up": 2, "fail_on": 3}, worker=_fake_worker) as sd:
         with pytest.raises(RuntimeError, match="boom"):
             sd.decode_sharded(codes)
 
@@ -61,3 +63,24 @@ def test_decode_shard_buckets_through_the_tokenizer_interface():
     out = decode_shard(tok, codes, [0, 2, 3, 4], max_frames=20)
     assert sorted(out) == [0, 2, 3, 4] and all(out[i].shape == (codes[i].shape[0],) and out[i][0] == codes[i].shape[0] for i in out)
     assert tok.calls == [2, 2]                               # (10, 10) then (7, 2): each at most 20 padded frames
+
+
+def test_shard_batches_padding_is_independent_of_world_size():
+    """Global buckets first, then deal: the padded frames decoded are (almost) the same for every N and the deal balances."""
+    rng = np.random.default_rng(5)
+    lengths = [int(v) for v in rng.integers(187, 376, 4096)]
+    real = sum(lengths)
+    waste = {}
+    for world in (1, 2, 4, 8):
+        plan = shard_batches(lengths, world, 64 * 375)
+        assert sorted(i for r in plan for b in r for i in b) == list(range(4096))
+        padded = [sum(len(b) * max(lengths[i] for i in b) for b in r) for r in plan]
+        cost = [sum(batch_cost(b, lengths) for b in r) for r in plan]
+        waste[world] = sum(padded) / real - 1.0
+        assert max(cost) / (sum(cost) / world) < 1.04, (world, cost)
+        assert all(len(r) >= min(8, 52 // world) for r in plan)
+    assert waste[8] < 0.03 and waste[8] <= waste[1] + 0.005, waste
+    # the old scheme (shard first, bucket per rank) for comparison: its padding grows with N
+    old8 = plan_batches(lengths, 8, 64 * 375)
+    old_waste = sum(len(b) * max(lengths[i] for i in b) for r in old8 for b in r) / real - 1.0
+    assert old_waste > waste[8]
