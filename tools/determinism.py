@@ -23,4 +23,4 @@ for r in range(runs):
         idx = torch.nonzero(d.view(64, -1) > 0)
         print(f"run {r}: {idx.shape[0]} samples differ, max {d.max().item():.3e}; first at item {idx[0,0].item()} sample {idx[0,1].item()}, last at item {idx[-1,0].item()} sample {idx[-1,1].item()}")
         bad += 1
-print(f"dbg={os.environ.get('Q3TTS_DBG','0')} fuse={'off' if os.environ.get('Q3TTS_NO_FUSE') else 'on'}: {bad} of {runs} runs differ")
+print(f"{bad} of {runs} runs differ")

@@ -5,7 +5,10 @@ import sys
 
 os.environ["Q3TTS_DBG"] = str(32 | int(os.environ.get("UT_EXTRA", "0")))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from qwen3_tts_b200 import _capi
+# The GemmParams::dbg experiment bits and the Q3TTS_* switches exist only in the -DQ3TTS_DEBUG build:
+#     python -m qwen3_tts_b200.build --debug      ->  qwen3_tts_b200/lib/libq3tts_decode_dbg.so
+from qwen3_tts_b200 import _capi, build as _build
+_capi.set_library_path(_build.LIB_PATH_DEBUG)
 
 lib = _capi.load_library()
 rows, ch, dil = (int(v) for v in sys.argv[1:4])

@@ -6,6 +6,10 @@ import sys
 
 os.environ["Q3TTS_DBG"] = "32"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+# The GemmParams::dbg experiment bits and the Q3TTS_* switches exist only in the -DQ3TTS_DEBUG build:
+#     python -m qwen3_tts_b200.build --debug      ->  qwen3_tts_b200/lib/libq3tts_decode_dbg.so
+from qwen3_tts_b200 import _capi, build as _build
+_capi.set_library_path(_build.LIB_PATH_DEBUG)
 import torch
 
 from qwen3_tts_b200 import _capi, synthetic_model
