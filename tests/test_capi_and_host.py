@@ -94,3 +94,11 @@ def test_tokenizer_rejects_bad_payload_like_reference():
     t.model.get_model_type = lambda: "something_else"
     with pytest.raises(ValueError, match="Unknown model type"):
         t.decode({"audio_codes": torch.zeros(4, 16, dtype=torch.long)})
+
+
+def test_compute_mode_table_matches_header():
+    """_capi.MODES (what compute_mode= accepts) must be exactly the Q3TTS_MODE_* enum of the header."""
+    hdr = open(os.path.join(ROOT, "include", "q3tts_decode.h")).read()
+    enum = {m.group(1).lower().replace("_", "-"): int(m.group(2)) for m in re.finditer(r"Q3TTS_MODE_([A-Z0-9_]+)\s*=\s*(\d+)", hdr)}
+    assert enum == _capi.MODES and len(enum) == 6
+    assert all((v & 1) == (1 if k.startswith("bf16") else 0) for k, v in enum.items())     # bit 0 = operand type

@@ -268,3 +268,34 @@ def test_two_handles_on_two_devices(sd, cfg):
     sid = b.decoder.open_stream()
     w, nv = b.decoder.decode_step([sid], codes[:1, :, :2])
     assert torch.equal(w[0, :nv[0]].cpu(), wb[0, 0, :nv[0]].cpu())
+
+
+@pytest.mark.parametrize("mode,max_abs,min_snr", [("fp16", 2e-3, 40.0), ("fp16-plain", 2e-3, 40.0), ("fp16-split-all", 2e-3, 40.0),
+                                                   ("bf16", 5e-2, 30.0), ("bf16-split-all", 5e-2, 30.0)])
+def test_every_compute_mode_on_the_reference_golden(sd, mode, max_abs, min_snr):
+    """Every compute mode (operand type x how many early-stage operands are hi + lo pairs) against the reference-written golden,
+    bulk and streamed (the streaming plans mirror the split layout: [hi | lo] history rows, fp32 ConvNeXt main path), plus the
+    ordering the split is for: more split operands must not be worse than fewer."""
+    from conftest import load_golden
+    from qwen3_tts_b200 import synthetic_model
+    g = load_golden("forward_B2_T12.npz")
+    codes = torch.from_numpy(g["codes"]).transpose(1, 2).contiguous()
+    m = synthetic_model(state_dict=sd, compute_mode=mode)
+    dec = m.decoder
+    wav = dec(codes)
+    mx, snr = _stats(g["wav"], wav)
+    print(f"mode {mode}: max-abs {mx:.3e} snr {snr:.1f} dB")
+    assert mx <= max_abs and snr >= min_snr, (mode, mx, snr)
+    dec.reserve_streams(2, 3)
+    ids = [dec.open_stream(), dec.open_stream()]
+    parts = []
+    for t in range(0, 12, 3):
+        w, nv = dec.decode_step(ids, codes[:, :, t:t + 3].cuda())
+        parts.append(w[:, :nv[0]].clone())
+    assert torch.equal(torch.cat(parts, dim=1), wav[:, 0])          # streaming == whole-sequence forward, bit for bit, in every mode
+    test_every_compute_mode_on_the_reference_golden.snr = getattr(test_every_compute_mode_on_the_reference_golden, "snr", {})
+    test_every_compute_mode_on_the_reference_golden.snr[mode] = snr
+    s = test_every_compute_mode_on_the_reference_golden.snr
+    if "fp16-plain" in s and "fp16" in s:
+        assert s["fp16"] >= s["fp16-plain"] + 1.0                    # the default's split main path buys at least 1 dB
+    del m
