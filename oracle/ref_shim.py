@@ -88,3 +88,34 @@ def reference_model_decode(dec, audio_codes: torch.Tensor, decode_upsample_rate:
         wav = dec.chunked_decode(audio_codes.transpose(1, 2)).squeeze(1)
     lengths = (audio_codes[..., 0] > 0).sum(1) * decode_upsample_rate
     return [a[:l] for a, l in zip(wav, lengths)]
+
+
+def build_reference_encoder(state_dict, attn_implementation: str = "eager"):
+    """The reference's own `Qwen3TTSTokenizerV2Encoder` (modeling :898-907: HF MimiModel, decoder parts nulled) with MimiConfig
+    defaults (what `Qwen3TTSTokenizerV2Config(encoder_config=None)` builds, configuration :155-158), loaded with the `encoder.*` keys
+    of `state_dict`.  Codebooks beyond the ones in `state_dict` keep their (unused) initial values: the reference reads only the
+    first encoder_valid_num_quantizers = 16 (modeling :982)."""
+    from transformers import MimiConfig
+    _, mod = load_reference_modules()
+    cfg = MimiConfig()
+    cfg._attn_implementation = attn_implementation
+    enc = mod.Qwen3TTSTokenizerV2Encoder._from_config(cfg).eval()
+    own = enc.state_dict()
+    for k, v in state_dict.items():
+        if not k.startswith("encoder."):
+            continue
+        kk = k[len("encoder."):]
+        if kk not in own or own[kk].shape != v.shape:
+            raise RuntimeError(f"state_dict mismatch at {kk}: {tuple(v.shape)}")
+        own[kk] = v.clone()
+    enc.load_state_dict(own)
+    return enc
+
+
+def reference_model_encode(enc, input_values: torch.Tensor, padding_mask: torch.Tensor, valid_num_quantizers: int = 16,
+                           encode_downsample_rate: int = 1920):
+    """`Qwen3TTSTokenizerV2Model.encode` body (modeling :979-985) over a reference encoder -> list of [T_i, 16] LongTensors."""
+    with torch.inference_mode():
+        frames = enc.encode(input_values=input_values.unsqueeze(1), return_dict=True)
+    codes = frames.audio_codes[:, :valid_num_quantizers]
+    return [c[..., :-(-m.sum() // encode_downsample_rate)].transpose(0, 1) for c, m in zip(codes, padding_mask)]

@@ -167,6 +167,103 @@ def _GAIN(key: str) -> float:
     return 1.0
 
 
+ENCODER_RATIOS = (4, 5, 6, 8)     # reversed(MimiConfig.upsampling_ratios): strides of the encoder's four down-sampling convs
+
+
+def encoder_param_shapes(num_filters: int = 64, hidden: int = 512, layers: int = 8, intermediate: int = 2048, codebook_size: int = 2048,
+                         codebook_dim: int = 512, num_quantizers: int = 16) -> "OrderedDict[str, Tuple[int, ...]]":
+    """Key names and shapes of `Qwen3TTSTokenizerV2Model.encoder` (reference modeling :898-907: HF MimiModel with the decoder parts
+    nulled; MimiConfig defaults), prefixed `encoder.` as in the model's state dict.  Only the first `num_quantizers` codebooks are
+    listed: the reference keeps `encoder_valid_num_quantizers` = 16 of Mimi's 32 (modeling :982)."""
+    s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
+    e = "encoder.encoder.layers."
+    s[e + "0.conv.weight"] = (num_filters, 1, 7)
+    s[e + "0.conv.bias"] = (num_filters,)
+    c, i = num_filters, 1
+    for r in ENCODER_RATIOS:
+        s[e + f"{i}.block.1.conv.weight"] = (c // 2, c, 3)
+        s[e + f"{i}.block.1.conv.bias"] = (c // 2,)
+        s[e + f"{i}.block.3.conv.weight"] = (c, c // 2, 1)
+        s[e + f"{i}.block.3.conv.bias"] = (c,)
+        s[e + f"{i + 2}.conv.weight"] = (2 * c, c, 2 * r)
+        s[e + f"{i + 2}.conv.bias"] = (2 * c,)
+        c, i = 2 * c, i + 3
+    s[e + f"{i + 1}.conv.weight"] = (hidden, c, 3)
+    s[e + f"{i + 1}.conv.bias"] = (hidden,)
+    for l in range(layers):
+        p = f"encoder.encoder_transformer.layers.{l}."
+        for n in ("q_proj", "k_proj", "v_proj", "o_proj"):
+            s[p + f"self_attn.{n}.weight"] = (hidden, hidden)
+        s[p + "mlp.fc1.weight"] = (intermediate, hidden)
+        s[p + "mlp.fc2.weight"] = (hidden, intermediate)
+        for n in ("input_layernorm", "post_attention_layernorm"):
+            s[p + n + ".weight"] = (hidden,)
+            s[p + n + ".bias"] = (hidden,)
+        s[p + "self_attn_layer_scale.scale"] = (hidden,)
+        s[p + "mlp_layer_scale.scale"] = (hidden,)
+    s["encoder.downsample.conv.weight"] = (hidden, hidden, 4)
+    dq = codebook_dim // 2
+    for grp, n in (("semantic", 1), ("acoustic", num_quantizers - 1)):
+        q = f"encoder.quantizer.{grp}_residual_vector_quantizer."
+        s[q + "input_proj.weight"] = (dq, codebook_dim, 1)
+        for l in range(n):
+            s[q + f"layers.{l}.codebook.embed_sum"] = (codebook_size, dq)
+            s[q + f"layers.{l}.codebook.cluster_usage"] = (codebook_size,)
+    return s
+
+
+def make_encoder_state_dict(seed: int = 0, **shape_kwargs) -> Dict[str, torch.Tensor]:
+    """Deterministic fp32 CPU state dict of the 12 Hz ENCODER with the reference's key names (no checkpoint is mounted).  Gains keep
+    the activations O(1) from a waveform of amplitude ~0.1 to the 512-d latents, so the RVQ search sees latents of the scale its
+    (synthetic) codebooks were drawn at."""
+    out: Dict[str, torch.Tensor] = OrderedDict()
+    for key, shape in encoder_param_shapes(**shape_kwargs).items():
+        g = _gen(seed + 7919, key)
+        if key.endswith("embed_sum"):
+            layer = int(key.split("layers.")[1].split(".")[0])
+            t = torch.randn(shape, generator=g) * (0.7 ** layer)            # later layers quantise ever smaller residuals
+        elif key.endswith("cluster_usage"):
+            t = torch.rand(shape, generator=g) * 2.0 + 0.5
+        elif key.endswith("layer_scale.scale"):
+            t = torch.rand(shape, generator=g) * 0.3 + 0.1
+        elif key.endswith("layernorm.weight"):
+            t = 1.0 + 0.1 * torch.randn(shape, generator=g)
+        elif key.endswith(".bias"):
+            t = 0.02 * torch.randn(shape, generator=g)
+        elif key.endswith(".weight"):
+            fan_in = shape[1] * (shape[2] if len(shape) == 3 else 1)
+            # measured on make_audio(): every stage's std stays between 1.1 and 1.3, the transformer changes the signal by ~0.7 std
+            if key.endswith("layers.0.conv.weight"):
+                gain = 6.0
+            elif "_proj" in key or "mlp." in key or "downsample" in key:
+                gain = 1.0
+            else:
+                gain = 0.6 if "block.3" in key else 1.2
+            t = torch.randn(shape, generator=g) * (gain / math.sqrt(fan_in))
+        else:  # pragma: no cover
+            raise KeyError(key)
+        out[key] = t.contiguous()
+    return out
+
+
+def make_audio(batch: int, samples: int, seed: int = 0, lengths=None) -> torch.Tensor:
+    """Seeded synthetic 24 kHz audio [batch, samples] in (-1, 1): a few drifting partials plus noise, zero beyond every item's length
+    (the reference's feature extractor pads with zeros)."""
+    g = torch.Generator().manual_seed(99991 + seed)
+    t = torch.arange(samples, dtype=torch.float32) / 24000.0
+    wav = torch.zeros((batch, samples))
+    for b in range(batch):
+        f0 = 90.0 + 160.0 * torch.rand((), generator=g)
+        for h in range(1, 6):
+            ph = 2 * math.pi * torch.rand((), generator=g)
+            wav[b] += (0.25 / h) * torch.sin(2 * math.pi * f0 * h * t * (1.0 + 0.02 * torch.sin(2 * math.pi * 0.7 * t)) + ph)
+        wav[b] += 0.03 * torch.randn((samples,), generator=g)
+        wav[b] *= 0.5 + 0.5 * torch.sin(2 * math.pi * 1.3 * t + b) ** 2
+        if lengths is not None:
+            wav[b, int(lengths[b]):] = 0.0
+    return wav.clamp_(-1.0, 1.0)
+
+
 def make_codes(batch: int, frames: int, cfg: Qwen3TTSTokenizerV2DecoderConfig, seed: int = 0,
                lengths: List[int] | None = None) -> torch.Tensor:
     """[B, T, Q] int64.  Codebook 0 is drawn from [1, size) because the reference counts a 0 in
