@@ -136,8 +136,37 @@ int q3tts_set_check_codes(q3tts_handle* h, int on);
  * [B,codebook_dim,T] fp32 (device; the Mimi encoder's output) -> codes [B,Q,T] int64 (device), Q = num_quantizers (the reference
  * keeps the first encoder_valid_num_quantizers = 16, modeling :982).  Needs the reference model's `encoder.quantizer.*` tensors
  * loaded before q3tts_finalize_weights (semantic / acoustic input_proj.weight, layers.N.codebook.{embed_sum, cluster_usage});
- * Q3TTS_NOT_READY otherwise.  The conv / transformer front of the encoder is not built: encode() as a whole still raises. */
+ * Q3TTS_NOT_READY otherwise. */
 int q3tts_rvq_encode(q3tts_handle* h, const float* latents, int B, int T, int64_t* codes, void* stream);
+
+/* The whole encode path.  Replaces Qwen3TTSTokenizerV2Model.encode (modeling :960-990), i.e. MimiModel.encode of the
+ * `transformers` package as the reference instantiates it (Qwen3TTSTokenizerV2Encoder, modeling :898-907): SEANet conv stack
+ * (k7 conv 1 -> 64; four [ResnetBlock, ELU, stride-r conv], r = 4, 5, 6, 8; ELU, k3 conv -> 512), 8-layer causal sliding-window
+ * transformer (LayerNorm, RoPE, GELU MLP, layer scale), replicate-padded stride-2 conv to 12.5 Hz, RVQ search.  Needs the reference
+ * model's `encoder.*` tensors (encoder.encoder.layers.*, encoder.encoder_transformer.layers.*, encoder.downsample.conv.weight,
+ * encoder.quantizer.*) loaded before q3tts_finalize_weights; Q3TTS_NOT_READY otherwise.  Channel counts, strides and the layer count
+ * are read from the tensor shapes; what shapes cannot tell comes from the q3tts_encoder_config struct, whose defaults are MimiConfig()'s.
+ * Arithmetic: every GEMM runs on the tensor cores with BOTH operands carried as fp16 hi + lo pairs (3 MMAs per product, fp32
+ * accumulate: ~22 bits per operand) whatever the handle's compute mode; activations stay fp32 in HBM.  The output is integer: the
+ * bar is identical indices wherever the float64 oracle's two best codes are not tied to fp32 rounding (tests/test_gpu_encode.py). */
+typedef struct {
+  int32_t num_attention_heads;     /* 8 (head_dim must be 64) */
+  int32_t sliding_window;          /* 250 */
+  int32_t max_position_embeddings; /* 8000 frames at 25 Hz per item */
+  float rope_theta;                /* 10000 */
+  float norm_eps;                  /* 1e-5 */
+} q3tts_encoder_config;
+int q3tts_set_encoder_config(q3tts_handle* h, const q3tts_encoder_config* cfg);   /* before q3tts_finalize_weights */
+/* frames MimiModel.encode emits for `samples` input samples (every strided conv rounds up): ceil-chain over 4, 5, 6, 8, 2 */
+int64_t q3tts_encode_num_frames(q3tts_handle* h, int64_t samples);
+/* wav [B, wav_stride] fp32 (device; row b = item b's T samples, zero-padded like the reference's feature extractor pads) ->
+ * codes [B, Q, F] int64 (device), F = q3tts_encode_num_frames(T).  latents (optional, device, [B, codebook_dim, F] fp32): the
+ * quantiser's input, for parity checks.  The caller cuts item b to ceil(valid_samples[b] / 1920) frames (modeling :983). */
+int q3tts_encode(q3tts_handle* h, const float* wav, int B, int64_t T, int64_t wav_stride, int64_t* codes, float* latents, void* stream);
+/* Host form: wav_host [B, wav_stride] fp32 -> codes_host [B, F, Q] int64 (the layout q3tts_decode_host reads); valid_samples (host,
+ * [B], may be NULL = T) -> lengths[b] = ceil(valid_samples[b] / 1920) frames of row b are item b's codes.  Synchronises. */
+int q3tts_encode_host(q3tts_handle* h, const float* wav_host, int B, int64_t T, int64_t wav_stride, const int64_t* valid_samples,
+                      int64_t* codes_host, int64_t* lengths, void* stream);
 
 /* The same gather-sum on int16 code frames (the wire format of q3tts_decode_host_pcm16) with NO allocation anywhere in the call.
  * No counterpart in the reference; added for callers that cannot call cudaMalloc (code under

@@ -53,6 +53,11 @@ class q3tts_config(C.Structure):
     ]
 
 
+class q3tts_encoder_config(C.Structure):
+    _fields_ = [("num_attention_heads", C.c_int32), ("sliding_window", C.c_int32), ("max_position_embeddings", C.c_int32),
+                ("rope_theta", C.c_float), ("norm_eps", C.c_float)]
+
+
 EXPORTS = {
     # name: (restype, argtypes)
     "q3tts_create": (C.c_int, [C.POINTER(q3tts_config), C.c_int, C.POINTER(C.c_void_p)]),
@@ -66,6 +71,10 @@ EXPORTS = {
     "q3tts_chunked_num_samples": (C.c_int64, [C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "q3tts_rvq_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_rvq_encode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "q3tts_set_encoder_config": (C.c_int, [C.c_void_p, C.POINTER(q3tts_encoder_config)]),
+    "q3tts_encode_num_frames": (C.c_int64, [C.c_void_p, C.c_int64]),
+    "q3tts_encode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "q3tts_encode_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "q3tts_static_max_codes": (C.c_int64, []),
     "q3tts_rvq_decode_i16_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "q3tts_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),

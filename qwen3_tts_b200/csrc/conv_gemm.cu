@@ -460,12 +460,13 @@ __global__ void conv_gemm_simt_kernel(const GemmParams p) {
       const int r = row + p.a_row0 + p.tap_off[tap];
       if (r < 0 || r >= p.rows) continue;
       const int aw = p.a_cols ? p.a_cols : p.cin;
-      const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * aw) + (long long)r * aw;
-      const T* w = W + ((long long)tap * p.n_total + n) * p.cin;
+      const long long ars = p.a_row_stride ? p.a_row_stride : aw, wrs = p.w_row_stride ? p.w_row_stride : p.cin;
+      const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * ars) + (long long)r * ars;
+      const T* w = W + ((long long)tap * p.n_total + n) * wrs;
       for (int k = 0; k < p.cin; ++k) {
         const float av = Elem<T>::to_f(a[k % aw]);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) acc[i] = fmaf(av, Elem<T>::to_f(w[(long long)i * p.cin + k]), acc[i]);
+        for (int i = 0; i < 16; ++i) acc[i] = fmaf(av, Elem<T>::to_f(w[(long long)i * wrs + k]), acc[i]);
       }
     }
     if (p.act == ACT_TAIL) {
@@ -511,6 +512,12 @@ int make_tmap_3d_strided(CUtensorMap* out, const void* base, int etype, uint64_t
 // 3-D tensor map over a dense 16-bit tensor [d2][d1][d0] (d0 contiguous), box [1][box1][box0].
 int make_tmap_3d(CUtensorMap* out, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint32_t box0, uint32_t box1, bool bf16) {
   return make_tmap_3d_strided(out, base, bf16 ? 1 : 0, d0, d1, d2, d0, d0 * d1, box0, box1, 1);
+}
+
+// weight map [taps][n_total][cin] with an optional row pitch (K groups of wider packed rows)
+static int make_tmap_w(CUtensorMap* out, const GemmParams& p, uint32_t box_n) {
+  const uint64_t wrs = p.w_row_stride ? (uint64_t)p.w_row_stride : (uint64_t)p.cin;
+  return make_tmap_3d_strided(out, p.w_ptr, p.bf16 ? 1 : 0, (uint64_t)p.cin, (uint64_t)p.n_total, (uint64_t)p.ntaps, wrs, wrs * (uint64_t)p.n_total, (uint32_t)p.kb, box_n, 1);
 }
 
 static int g_num_sms = 0;
@@ -601,7 +608,7 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
       }
       if (best != q.bn) {
         q.bn = best;
-        if (make_tmap_3d(&op->tmB, q.w_ptr, (uint64_t)q.cin, (uint64_t)q.n_total, (uint64_t)q.ntaps, (uint32_t)q.kb, (uint32_t)q.bn, q.bf16 != 0)) return -3;
+        if (make_tmap_w(&op->tmB, q, (uint32_t)q.bn)) return -3;
       }
     }
   }
@@ -656,10 +663,11 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
                 p.rows_valid * 10 >= mt2 * 2 * BM * 9 && p.ntaps * p.cin >= 3072) ? 1 : 0;  // measured: -32 % at K = 3072, neutral or worse at K <= 1024
   }
   // the weight map follows the plan: a CTA of a pair loads half of a weight tile
-  if (make_tmap_3d(&op->tmB, p.w_ptr, (uint64_t)p.cin, (uint64_t)p.n_total, (uint64_t)p.ntaps, (uint32_t)p.kb, (uint32_t)(op->pair ? p.bn / 2 : p.bn), p.bf16 != 0)) rc |= 1;
+  if (make_tmap_w(&op->tmB, p, (uint32_t)(op->pair ? p.bn / 2 : p.bn))) rc |= 1;
   const uint64_t aw = p.a_cols ? (uint64_t)p.a_cols : (uint64_t)p.cin;  // width of the A tensor in memory
-  rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, aw, (uint64_t)p.rows, (uint64_t)p.batches, aw,
-                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * aw, (uint32_t)p.kb,
+  const uint64_t ars = p.a_row_stride ? (uint64_t)p.a_row_stride : aw;  // row pitch (wider than aw when this launch walks one K group)
+  rc |= make_tmap_3d_strided(&op->tmA, p.a_ptr, p.bf16 ? 1 : 0, aw, (uint64_t)p.rows, (uint64_t)p.batches, ars,
+                             p.a_batch_stride ? (uint64_t)p.a_batch_stride : (uint64_t)p.rows * ars, (uint32_t)p.kb,
                              p.pack_mode ? br : (uint32_t)(op->variant ? op->srp : BM), bb);
   // unused maps hold a valid placeholder (the kernels take all of them as __grid_constant__ arguments)
   if (!has_res) op->tmRes = op->tmA;

@@ -1,0 +1,21 @@
+// SIMT kernels of the 12 Hz encode path (encode_kernels.cu); the GEMMs between them are conv_gemm.cu's tensor-core kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace q3 {
+
+// first conv 1 -> C0 (k = 7, causal): wav [B][wav_bs] fp32 -> out [B][T][C0] fp32
+cudaError_t enc_conv0(const float* wav, long long wav_bs, const float* w, const float* bias, float* out, int B, int T, int C0, cudaStream_t s);
+// act(in) fp32 [B][L][C] -> fp16 [B][lead + ceil(L / r)][2 r C] super-rows [hi | lo]; act 0 none / 1 ELU / 2 GELU(erf); rows outside
+// [0, L) are zero, or the nearest valid row when replicate != 0; cg (0 = r * C): K group size, every group its own [hi | lo] pair
+cudaError_t enc_act_split(const float* in, void* out, int B, int L, int C, int act, int r, int lead, int replicate, int cg, cudaStream_t s);
+// LayerNorm with bias over H, fp32 [M][H] -> fp16 [M][2H] rows [hi | lo]
+cudaError_t enc_layernorm_split(const float* x, const float* w, const float* bias, void* out, long long M, int H, float eps, cudaStream_t s);
+// cos / sin [maxT][hd / 2] from float32 inverse frequencies (device array of hd / 2)
+cudaError_t enc_rope_table(float* cos_t, float* sin_t, const float* inv_freq_dev, int maxT, int hd, cudaStream_t s);
+// causal sliding-window attention in fp32 with RoPE: qkv fp32 [B*T][3 nh hd] -> out fp16 [B*T][2 nh hd] rows [hi | lo]
+cudaError_t enc_attention(const float* qkv, const float* cos_t, const float* sin_t, void* out, int B, int T, int nh, int hd, int window, cudaStream_t s);
+// fp32 [B][L][C] -> fp32 [B][C][L]
+cudaError_t enc_to_channels_first(const float* in, float* out, int B, int L, int C, cudaStream_t s);
+
+}  // namespace q3

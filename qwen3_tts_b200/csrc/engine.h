@@ -30,6 +30,9 @@ struct ConvW {
   // split-precision operands (gemm_params.h): cin above is the K the MMAs walk = k_mult x the layer's input channels;
   // a_cols = width of the A tensor in memory (C for k_mult 2, 2C = [hi | lo] rows for k_mult 3), 0 = plain
   int k_mult = 1, a_cols = 0;
+  // encode path: K group size in real input values (0 = one group): the layer runs as kreal / cg launches that accumulate into the
+  // fp32 output, so that no tensor-core accumulation chain is longer than taps * 3 * cg (encode_plan.cu)
+  int cg = 0;
 };
 
 struct SnakeP { const float* a = nullptr; const float* ib = nullptr; };
@@ -45,8 +48,18 @@ struct UpsampleW {
 struct UnitW { ConvW conv7, conv1; SnakeP act1, act2; };
 struct BlockW { SnakeP act0; ConvW tconv; UnitW unit[3]; int stride = 0, cin = 0, cout = 0; };
 
+// ---- 12 Hz encoder (encode_plan.cu): HF MimiModel's encoder side as the reference instantiates it (modeling :898-907)
+struct EncStageW { ConvW c3, c1, down; int C = 0, r = 0; };   // ResnetBlock (k3: C -> C/2, k1: C/2 -> C) + stride-r conv C -> 2C
+struct EncLayerW {
+  ConvW qkv, o, fc1, fc2;
+  const float *ln1w = nullptr, *ln1b = nullptr, *ln2w = nullptr, *ln2b = nullptr, *ls1 = nullptr, *ls2 = nullptr;
+};
+
 enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT, OP_STREAM_ATTN, OP_STATE_LOAD, OP_STATE_SAVE, OP_POS_ADVANCE,
-              OP_SPLIT /* fp32 [B][L][C] -> 16-bit [hi | lo] rows: in, out, B, L, C, sp_in_bs / sp_out_bs */ };
+              OP_SPLIT /* fp32 [B][L][C] -> 16-bit [hi | lo] rows: in, out, B, L, C, sp_in_bs / sp_out_bs */,
+              // encode path (encode_plan.cu): first conv; act + split (aux0 = act, aux1 = r, split = lead rows | replicate << 8, probe_ld = K group);
+              // LayerNorm -> [hi | lo]; fp32 attention; RVQ search (aux0 = 1: codes [B][T][Q])
+              OP_ENC_CONV0, OP_ENC_ACT, OP_ENC_LN, OP_ENC_ATTN, OP_ENC_RVQ };
 
 struct Op {
   OpType type = OP_GEMM;
@@ -171,6 +184,24 @@ struct Engine {
   float* enc_win = nullptr;     // [2][codebook_dim / 2][codebook_dim] input_proj of the semantic / acoustic group
   bool enc_ready = false;
 
+  // ---- encoder front (q3tts_encode): packed when the `encoder.encoder.*` tensors were loaded
+  q3tts_encoder_config enc_cfg{8, 250, 8000, 10000.0f, 1e-5f};   // MimiConfig defaults
+  bool enc_front_ready = false;
+  int enc_c0 = 0, enc_hidden = 0, enc_inter = 0;
+  const float *enc_conv0_w = nullptr, *enc_conv0_b = nullptr;
+  std::vector<EncStageW> enc_stages;
+  ConvW enc_last, enc_down;
+  std::vector<EncLayerW> enc_layers;
+  float *enc_rope_cos = nullptr, *enc_rope_sin = nullptr;
+  uint8_t* enc_ws = nullptr;
+  size_t enc_ws_bytes = 0;
+  long long enc_max_samples = 4ll << 20;       // samples per launch (B * T): bounds the workspace (~1.9 KB per sample)
+  std::map<std::pair<int, int>, Plan> enc_plans;  // (B, T samples)
+  float* enc_wav_stage = nullptr;              // device staging of q3tts_encode_host
+  size_t enc_wav_stage_elems = 0;
+  long long* enc_codes_stage = nullptr;
+  size_t enc_codes_stage_elems = 0;
+
   // ---- streaming state (q3tts_stream_*)
   int max_slots = 0, stream_max_frames = 0, kv_ring = 128;
   long long state_bytes = 0;             // history rows of every stage, per slot
@@ -214,6 +245,10 @@ int engine_stream_step(Engine* e, const int32_t* stream_ids, int S, const long l
                        long long wav_stride, int32_t* n_valid, cudaStream_t s);
 void engine_stream_free(Engine* e);
 int encode_finalize(Engine* e);  // rvq_encode.cu
+int encoder_front_finalize(Engine* e);  // encode_plan.cu: packs encoder.encoder.* / encoder_transformer.* / downsample (no-op when absent)
+void encoder_free(Engine* e);
+// rvq_encode.cu: latents channels-first [B][D][T] (x_cl = 0) or channels-last [B][T][D] (x_cl = 1) -> codes [B][Q][T] or (codes_tq = 1) [B][T][Q]
+cudaError_t rvq_encode_launch(Engine* e, const float* latents, int B, int T, long long* codes, int x_cl, int codes_tq, cudaStream_t s);
 int static_scratch_setup(int device);  // noalloc.cu: device address of the static scratch array on the current device
 
 struct DeviceGuard {

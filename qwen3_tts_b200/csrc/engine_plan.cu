@@ -379,6 +379,20 @@ void prof_account(Engine* e, const Op& op) {
     by = 2.0 * rows * 4.0 * H;                    // q, k, v in, o out (16-bit)
   } else if (op.type == OP_SPLIT) {
     by = (4.0 + (op.split ? 4.0 : 2.0)) * (double)op.B * op.L * op.C;  // fp32 in, one or two 16-bit values out
+  } else if (op.type == OP_ENC_CONV0) {
+    by = (double)op.B * op.L * (4.0 + 4.0 * op.C);                       // samples in, fp32 rows out
+    fl = 2.0 * 7.0 * (double)op.B * op.L * op.C;
+  } else if (op.type == OP_ENC_ACT) {
+    by = 8.0 * (double)op.B * op.L * op.C;                                 // fp32 in, [hi | lo] fp16 out
+  } else if (op.type == OP_ENC_LN) {
+    by = 8.0 * (double)op.B * op.C;                                        // op.B = rows
+  } else if (op.type == OP_ENC_ATTN) {
+    const double rows = (double)op.B * op.L;
+    fl = 4.0 * rows * op.C * (op.L < e->enc_cfg.sliding_window ? op.L : e->enc_cfg.sliding_window);
+    by = rows * op.C * (12.0 + 4.0);                                       // q, k, v fp32 in, [hi | lo] out
+  } else if (op.type == OP_ENC_RVQ) {
+    by = (double)op.B * op.L * (4.0 * op.C + 8.0 * e->cfg.num_quantizers); // latents in, codes out; the tables stay in L2
+    fl = 2.0 * (double)op.B * op.L * e->cfg.num_quantizers * e->cfg.codebook_size * (e->cfg.codebook_dim / 2);
   } else if (op.type == OP_DWLN) {
     by = (op.split ? 4.0 + 2.0 : 2.0 * 2.0) * (double)op.B * op.L * op.C;  // one read and one write of the token tensor
   }
@@ -494,6 +508,7 @@ int engine_check_codes(Engine* e, cudaStream_t s) {
 
 void engine_free(Engine* e) {
   engine_stream_free(e);
+  encoder_free(e);
   for (cudaEvent_t ev : e->prof_events) cudaEventDestroy(ev);
   for (void* p : e->owned) cudaFree(p);
   for (auto& kv : e->raw) cudaFree(kv.second.d);

@@ -292,6 +292,7 @@ int engine_finalize(Engine* e, int mode) {
   if (!f.rc) f.check(cudaDeviceSynchronize(), "finalize sync");
   if (f.rc) return f.rc;
   if (int rc = encode_finalize(e)) return rc;
+  if (int rc = encoder_front_finalize(e)) return rc;
   // big fp32 sources are no longer needed; keep vectors (biases, norms, scales) that kernels read directly
   for (auto it = e->raw.begin(); it != e->raw.end();) {
     if (it->second.shape.size() >= 2) {

@@ -67,7 +67,9 @@ struct GemmParams {
   const float* snake_a;
   const float* snake_ib;
   long long out_batch_stride;  // elements
-  long long a_batch_stride;    // elements between batch items of A (0: rows * cin)
+  long long a_batch_stride;    // elements between batch items of A (0: rows * a_row_stride)
+  long long a_row_stride;      // elements between rows of A (0: dense, = a_cols or cin); > a_cols when the launch walks one K group of wider rows
+  long long w_row_stride;      // elements between rows of W (0: dense, = cin)
   long long res_batch_stride;  // residual tensor (0: same as out_batch_stride)
   long long snake_batch_stride;  // Snake'd output tensor (0: same as out_batch_stride)
   long long out_row_stride;    // elements

@@ -19,9 +19,12 @@ static inline int nblocks(long long n, int threads, int cap = 148 * 32) {
 // ============================================================================================ packers
 // One packed weight element of row `row`, input channel ci (of cin): plain (m = 1), or carried as hi + lo for the split-precision
 // GEMMs (gemm_params.h): m = 2 -> [hi | lo], m = 3 -> [hi | hi | lo] (the K' order that meets A = [a_hi | a_lo | a_hi]).
+// cg (K group, 0 = cin): the row is cin / cg groups, each packed on its own as above - [hi(g) | hi(g) | lo(g)] per group - so that a
+// launch can walk ONE group (a shorter accumulation chain, encode_plan.cu) through a tensor map with the full row pitch.
 template <typename T>
-__device__ __forceinline__ void put_w(T* __restrict__ dst, long long row, int ci, int cin, int m, float v) {
+__device__ __forceinline__ void put_w(T* __restrict__ dst, long long row, int ci, int cin, int m, float v, int cg = 0) {
   T* r = dst + row * (long long)(m * cin);
+  if (cg > 0 && cg < cin) { r += (long long)(ci / cg) * (m * cg); ci %= cg; cin = cg; }
   const T hi = Elem<T>::from_f(v);
   r[ci] = hi;
   if (m > 1) {
@@ -31,18 +34,18 @@ __device__ __forceinline__ void put_w(T* __restrict__ dst, long long row, int ci
   }
 }
 template <typename T>
-__global__ void k_pack_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int k, int m) {
+__global__ void k_pack_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int cin, int k, int m, int cg) {
   const long long n = (long long)cout * cin * k;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const int ci = (int)(i % cin);
     const int co = (int)((i / cin) % cout);
     const int j = (int)(i / ((long long)cin * cout));
-    put_w<T>(dst, (long long)j * cout + co, ci, cin, m, src[((long long)co * cin + ci) * k + j]);
+    put_w<T>(dst, (long long)j * cout + co, ci, cin, m, src[((long long)co * cin + ci) * k + j], cg);
   }
 }
-cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split) {
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split, int group) {
   const long long n = (long long)cout * cin * k;
-  Q3_DISPATCH(bf16, (k_pack_conv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cout, cin, k, split)));
+  Q3_DISPATCH(bf16, (k_pack_conv<T><<<nblocks(n, 256), 256, 0, s>>>(src, (T*)dst, cout, cin, k, split, group)));
   return cudaGetLastError();
 }
 
@@ -94,13 +97,32 @@ cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaS
 
 // [rows][k] fp32 -> [rows][split * k] 16-bit (linear weights; split as in put_w)
 template <typename T>
-__global__ void k_pack_rows(const float* __restrict__ src, T* __restrict__ dst, long long rows, int k, int m) {
+__global__ void k_pack_rows(const float* __restrict__ src, T* __restrict__ dst, long long rows, int k, int m, int cg) {
   const long long n = rows * k;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-    put_w<T>(dst, i / k, (int)(i % k), k, m, src[i]);
+    put_w<T>(dst, i / k, (int)(i % k), k, m, src[i], cg);
 }
-cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split) {
-  Q3_DISPATCH(bf16, (k_pack_rows<T><<<nblocks(rows * k, 256), 256, 0, s>>>(src, (T*)dst, rows, k, split)));
+cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split, int group) {
+  Q3_DISPATCH(bf16, (k_pack_rows<T><<<nblocks(rows * k, 256), 256, 0, s>>>(src, (T*)dst, rows, k, split, group)));
+  return cudaGetLastError();
+}
+
+// Strided Conv1d [cout][c][2r] (stride r, causal) as a two-tap GEMM over super-rows of r input rows (encode path): dst [2][cout][m * r * c],
+// tap = j / r, K index = (j % r) * c + ci.
+template <typename T>
+__global__ void k_pack_strided_conv(const float* __restrict__ src, T* __restrict__ dst, int cout, int c, int r, int m, int cg) {
+  const long long n = 2ll * r * cout * c;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % c);
+    long long q = i / c;
+    const int p = (int)(q % r); q /= r;
+    const int co = (int)(q % cout);
+    const int tap = (int)(q / cout);
+    put_w<T>(dst, (long long)tap * cout + co, p * c + ci, r * c, m, src[((long long)co * c + ci) * (2 * r) + tap * r + p], cg);
+  }
+}
+cudaError_t pack_strided_conv_weight(const float* src, void* dst, int cout, int c, int r, bool bf16, cudaStream_t s, int split, int group) {
+  Q3_DISPATCH(bf16, (k_pack_strided_conv<T><<<nblocks(2ll * r * cout * c, 256), 256, 0, s>>>(src, (T*)dst, cout, c, r, split, group)));
   return cudaGetLastError();
 }
 

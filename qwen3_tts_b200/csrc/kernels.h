@@ -9,14 +9,19 @@ namespace q3 {
 // Conv1d weight [Cout][Cin][k] -> [k][Cout][Cin]
 // `split` (every packer below): 1 = one 16-bit value per weight; 2 / 3 = weights carried as hi + lo along K for the split-precision
 // GEMMs (gemm_params.h): rows become split * cin wide, [hi | lo] or [hi | hi | lo].
-cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split = 1);
+// `group` (pack_conv_weight, pack_rows, pack_strided_conv_weight; 0 = the whole row): K group size in input channels - every group of a
+// row is packed on its own ([hi(g) | hi(g) | lo(g)] ...), so that one launch can walk one group (encode_plan.cu: short accumulation chains)
+cudaError_t pack_conv_weight(const float* src, void* dst, int cout, int cin, int k, bool bf16, cudaStream_t s, int split = 1, int group = 0);
 // ConvTranspose1d weight [Cin][Cout][k], stride st.  k == 2*st: two taps, tap0 (x[q]) = W[..., p+st],
 // tap1 (x[q+1]) = W[..., p]; k == st: one tap W[..., p].  dst [taps][st*Cout][Cin], row = p*Cout + co.
 cudaError_t pack_transconv_weight(const float* src, void* dst, int cin, int cout, int k, int st, bool bf16, cudaStream_t s, int split = 1);
 // rows of `a` and `b` ([n][k] each) interleaved: dst[2i] = a[i], dst[2i+1] = b[i]
 cudaError_t pack_interleave2(const float* a, const float* b, void* dst, int n, int k, bool bf16, cudaStream_t s, int split = 1);
 // [rows][k] fp32 -> [rows][split * k] 16-bit
-cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split = 1);
+cudaError_t pack_rows(const float* src, void* dst, long long rows, int k, bool bf16, cudaStream_t s, int split = 1, int group = 0);
+// Conv1d weight [Cout][C][2r] of a stride-r causal conv -> [2][Cout][split * r * C]: two taps over super-rows of r input rows
+// (encode path: tap = j / r, K index (j % r) * C + ci)
+cudaError_t pack_strided_conv_weight(const float* src, void* dst, int cout, int c, int r, bool bf16, cudaStream_t s, int split = 1, int group = 0);
 // plain cast [n] fp32 -> 16-bit
 cudaError_t pack_cast(const float* src, void* dst, long long n, bool bf16, cudaStream_t s);
 // Snake: a = exp(alpha), ib = 1/(exp(beta)+1e-9)

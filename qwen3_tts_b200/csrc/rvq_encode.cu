@@ -25,7 +25,7 @@ static constexpr int ENC_THREADS = 256;
 // tables [K][ncodes][dq] fp32, norms [K][ncodes] = ||e||^2, win [2][dq][D] (semantic, acoustic input_proj)
 __global__ void __launch_bounds__(ENC_THREADS)
 k_rvq_encode(const float* __restrict__ x, const float* __restrict__ tables, const float* __restrict__ norms, const float* __restrict__ win,
-             long long* __restrict__ codes, int B, int T, int D, int dq, int ncodes, int K, int n_sem) {
+             long long* __restrict__ codes, int B, int T, int D, int dq, int ncodes, int K, int n_sem, int x_cl, int codes_tq) {
   extern __shared__ float sm[];
   float* r = sm;                         // [ENC_FR][dq] residuals
   float* xs = r + ENC_FR * dq;           // [ENC_FR][D] latents of the block's frames
@@ -39,7 +39,7 @@ k_rvq_encode(const float* __restrict__ x, const float* __restrict__ tables, cons
     const int f = i / D, c = i - f * D;
     const long long g = f0 + f;
     float v = 0.f;
-    if (g < nfr) { const long long b = g / T, t = g - b * T; v = x[(b * D + c) * T + t]; }
+    if (g < nfr) { const long long b = g / T, t = g - b * T; v = x_cl ? x[g * D + c] : x[(b * D + c) * T + t]; }
     xs[f * D + c] = v;
   }
   __syncthreads();
@@ -102,7 +102,7 @@ k_rvq_encode(const float* __restrict__ x, const float* __restrict__ tables, cons
         if (s_best[tid][w] < s || (s_best[tid][w] == s && s_idx[tid][w] < ix)) { s = s_best[tid][w]; ix = s_idx[tid][w]; }
       s_code[tid] = ix;
       const long long g = f0 + tid;
-      if (g < nfr) { const long long b = g / T, t = g - b * T; codes[(b * K + k) * T + t] = ix; }
+      if (g < nfr) { const long long b = g / T, t = g - b * T; codes[codes_tq ? g * K + k : (b * K + k) * T + t] = ix; }
     }
     __syncthreads();
     for (int i = tid; i < ENC_FR * dq; i += ENC_THREADS) {   // residual = residual - quantized
@@ -166,6 +166,17 @@ int encode_finalize(Engine* e) {
   return Q3TTS_OK;
 }
 
+cudaError_t rvq_encode_launch(Engine* e, const float* latents, int B, int T, long long* codes, int x_cl, int codes_tq, cudaStream_t s) {
+  const q3tts_config& c = e->cfg;
+  const int dq = c.codebook_dim / 2;
+  const long long nfr = (long long)B * T;
+  const int blocks = (int)((nfr + ENC_FR - 1) / ENC_FR);
+  const size_t smem = (size_t)ENC_FR * (dq + c.codebook_dim) * sizeof(float);
+  k_rvq_encode<<<blocks, ENC_THREADS, smem, s>>>(latents, e->enc_tables, e->enc_norms, e->enc_win, codes, B, T, c.codebook_dim, dq, c.codebook_size,
+                                                 c.num_quantizers, 1, x_cl, codes_tq);
+  return cudaGetLastError();
+}
+
 }  // namespace q3
 
 extern "C" int q3tts_rvq_encode(q3tts_handle* h, const float* latents, int B, int T, int64_t* codes, void* stream) {
@@ -177,13 +188,8 @@ extern "C" int q3tts_rvq_encode(q3tts_handle* h, const float* latents, int B, in
   const int dq = c.codebook_dim / 2;
   if (dq % 4) return e.fail(Q3TTS_BAD_CONFIG, "rvq_encode: codebook_dim / 2 must be a multiple of 4");
   q3::DeviceGuard g(e.device);
-  const long long nfr = (long long)B * T;
-  const int blocks = (int)((nfr + q3::ENC_FR - 1) / q3::ENC_FR);
-  const size_t smem = (size_t)q3::ENC_FR * (dq + c.codebook_dim) * sizeof(float);
-  q3::k_rvq_encode<<<blocks, q3::ENC_THREADS, smem, (cudaStream_t)stream>>>(latents, e.enc_tables, e.enc_norms, e.enc_win, (long long*)codes, B, T,
-                                                                              c.codebook_dim, dq, c.codebook_size, c.num_quantizers, 1);
+  const cudaError_t err = q3::rvq_encode_launch(&e, latents, B, T, (long long*)codes, 0, 0, (cudaStream_t)stream);
   ++e.launches;
-  const cudaError_t err = cudaGetLastError();
   if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("rvq_encode: ") + cudaGetErrorString(err));
   return Q3TTS_OK;
 }

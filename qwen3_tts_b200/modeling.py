@@ -15,6 +15,7 @@ import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Union
 
+import numpy as np
 import torch
 
 from . import _capi
@@ -31,6 +32,18 @@ class Qwen3TTSTokenizerV2DecoderOutput:
 
     def to_tuple(self):
         return (self.audio_values,)
+
+
+@dataclass
+class Qwen3TTSTokenizerV2EncoderOutput:
+    """audio_codes: List[LongTensor (codes_length_i, num_quantizers)] - reference modeling :50-60."""
+    audio_codes: List[torch.Tensor] = None
+
+    def __getitem__(self, i):
+        return (self.audio_codes,)[i]
+
+    def to_tuple(self):
+        return (self.audio_codes,)
 
 
 def _stream_ptr(device: torch.device) -> int:
@@ -257,9 +270,10 @@ class Qwen3TTSTokenizerV2Decoder:
 
 
 class Qwen3TTSTokenizerV2Model:
-    """Drop-in for the reference model shell (modeling :927-1022): decode() + the five getters.
+    """Drop-in for the reference model shell (modeling :927-1022): decode(), encode() and the five getters.
 
-    encode() (wav -> codes, HF MimiModel) is outside the hot path this package accelerates."""
+    encode() (wav -> codes; the reference delegates to HF MimiModel, modeling :898-907, :960-990) runs on the same handle when the
+    state dict carries the `encoder.*` tensors; SURVEY 8(f)-2."""
 
     def __init__(self, config: Qwen3TTSTokenizerV2Config, device: Union[str, torch.device] = "cuda:0", compute_mode: str = "fp16"):
         self.config = config
@@ -289,15 +303,29 @@ class Qwen3TTSTokenizerV2Model:
         return self.decode_upsample_rate
 
     def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True):
-        """Accepts the reference model's state_dict: `decoder.*` keys are consumed; of `encoder.*` only the quantiser
-        (`encoder.quantizer.*`, used by decoder.quantizer.encode) - the rest of the Mimi encoder is not built here."""
+        """Accepts the reference model's state_dict: `decoder.*` keys feed the decode path, `encoder.*` keys the encode path
+        (conv stack, transformer, down-sampling conv, and the first `num_quantizers` codebooks of the quantiser: the reference keeps
+        encoder_valid_num_quantizers = 16 of Mimi's 32, modeling :982).  A state dict without `encoder.*` gives a decode-only model."""
         dec = {k[len("decoder."):]: v for k, v in state_dict.items() if k.startswith("decoder.")}
         if not dec:  # already decoder-level keys
             dec = {k: v for k, v in state_dict.items() if not k.startswith("encoder.")}
-        dec.update({k: v for k, v in state_dict.items() if k.startswith("encoder.quantizer.") and (
-            k.endswith("input_proj.weight") or k.endswith("embed_sum") or k.endswith("cluster_usage"))})
+        dec.update({k: v for k, v in state_dict.items() if self._wants_encoder_key(k)})
         self.decoder.load_state_dict(dec, strict=strict)
+        self._has_encoder = any(k.startswith("encoder.encoder.") for k in state_dict)
         return self
+
+    def _wants_encoder_key(self, k: str) -> bool:
+        if not k.startswith("encoder."):
+            return False
+        if k.startswith("encoder.quantizer."):
+            if not (k.endswith("input_proj.weight") or k.endswith("embed_sum") or k.endswith("cluster_usage")):
+                return False
+            if ".layers." in k:   # acoustic codebooks beyond the ones the reference reads are not uploaded
+                layer = int(k.split(".layers.")[1].split(".")[0])
+                limit = 1 if "semantic_" in k else self.config.decoder_config.num_quantizers - 1
+                return layer < limit
+            return True
+        return k.startswith(("encoder.encoder.", "encoder.encoder_transformer.", "encoder.downsample.")) and not k.endswith("inv_freq")
 
     @classmethod
     def from_pretrained(cls, path: str, device_map: Union[str, torch.device, None] = None, dtype=None, **kwargs):
@@ -321,7 +349,7 @@ class Qwen3TTSTokenizerV2Model:
         for f in files:
             with safe_open(f, framework="pt", device="cpu") as sf:
                 for k in sf.keys():
-                    if k.startswith("decoder.") or k.startswith("encoder.quantizer."):
+                    if k.startswith("decoder.") or model._wants_encoder_key(k):
                         sd[k] = sf.get_tensor(k)
         model.load_state_dict(sd)
         if mode == "fp16":
@@ -335,8 +363,65 @@ class Qwen3TTSTokenizerV2Model:
                 model.load_state_dict(sd)
         return model
 
-    def encode(self, *args, **kwargs):
-        raise NotImplementedError("encode (wav -> codes) is outside the decode hot path; use the reference encoder")
+    def encode_num_frames(self, samples: int) -> int:
+        """Code frames the encoder emits for `samples` input samples (every strided conv rounds up, modeling_mimi.py:273-285)."""
+        d = self.decoder
+        n = int(d._lib.q3tts_encode_num_frames(d._h, int(samples)))
+        _capi.check(d._h, min(n, 0), "encode_num_frames")
+        return n
+
+    def encode(self, input_values: torch.Tensor, padding_mask: Optional[torch.Tensor] = None, return_dict: Optional[bool] = None,
+               return_latents: bool = False):
+        """input_values [B, T] float waveform (zero-padded), padding_mask [B, T] (1 = real sample) ->
+        Qwen3TTSTokenizerV2EncoderOutput(audio_codes=List[LongTensor (ceil(mask_i.sum() / 1920), 16)]) (modeling :960-990).
+        return_latents (additive): also return the quantiser's input [B, 512, F] for parity checks."""
+        return_dict = return_dict if return_dict is not None else self.config.return_dict
+        if input_values.dim() != 2:
+            raise ValueError(f"Expected input_values of shape (B, T), got {tuple(input_values.shape)}")
+        d = self.decoder
+        wav = input_values.to(device=d.device, dtype=torch.float32).contiguous()
+        B, T = wav.shape
+        F = self.encode_num_frames(T)
+        Q = d.config.num_quantizers
+        codes = torch.empty((B, Q, F), dtype=torch.int64, device=d.device)
+        lat = torch.empty((B, d.config.codebook_dim, F), dtype=torch.float32, device=d.device) if return_latents else None
+        rc = d._lib.q3tts_encode(d._h, wav.data_ptr(), B, T, T, codes.data_ptr(), lat.data_ptr() if return_latents else None, _stream_ptr(d.device))
+        _capi.check(d._h, rc, "encode")
+        if padding_mask is None:
+            padding_mask = torch.ones((B, T), dtype=torch.long)
+        n = padding_mask.to("cpu").sum(dim=-1).tolist()
+        rate = self.encode_downsample_rate
+        audio_codes = [codes[b, :self.encoder_valid_num_quantizers, :-(-int(n[b]) // rate)].transpose(0, 1) for b in range(B)]
+        if return_latents:
+            return audio_codes, lat
+        if not return_dict:
+            return (audio_codes,)
+        return Qwen3TTSTokenizerV2EncoderOutput(audio_codes)
+
+    def encode_host(self, wavs: List[np.ndarray]) -> List[np.ndarray]:
+        """Host form (additive): list of 1-D float32 waveforms at 24 kHz -> list of int64 arrays [frames_i, 16] in host memory, through
+        q3tts_encode_host (one pinned staging buffer each way; the layout q3tts_decode_host reads)."""
+        d = self.decoder
+        B = len(wavs)
+        T = max(int(w.shape[0]) for w in wavs)
+        F = self.encode_num_frames(T)
+        Q = d.config.num_quantizers
+        stage = getattr(self, "_enc_stage", None)
+        if stage is None or stage[0].numel() < B * T or stage[1].numel() < B * F * Q:
+            stage = (torch.empty(B * T, dtype=torch.float32).pin_memory(), torch.empty(B * F * Q, dtype=torch.int64).pin_memory())
+            self._enc_stage = stage
+        wav = stage[0][:B * T].view(B, T)
+        valid = np.empty(B, dtype=np.int64)
+        for b, w in enumerate(wavs):
+            n = int(w.shape[0])
+            wav[b, :n] = torch.from_numpy(np.ascontiguousarray(w, dtype=np.float32))
+            wav[b, n:] = 0.0
+            valid[b] = n
+        codes = stage[1][:B * F * Q].view(B, F, Q)
+        lengths = np.empty(B, dtype=np.int64)
+        rc = d._lib.q3tts_encode_host(d._h, wav.data_ptr(), B, T, T, valid.ctypes.data, codes.data_ptr(), lengths.ctypes.data, _stream_ptr(d.device))
+        _capi.check(d._h, rc, "encode_host")
+        return [codes[b, :int(lengths[b]), :self.encoder_valid_num_quantizers].numpy().copy() for b in range(B)]
 
     def decode(self, audio_codes: torch.Tensor, return_dict: Optional[bool] = None):
         """audio_codes [B, T, Q] -> Qwen3TTSTokenizerV2DecoderOutput(audio_values=List[Tensor]) (modeling :992-1022)."""

@@ -1,8 +1,9 @@
 """`Qwen3TTSTokenizer` — drop-in for qwen_tts/inference/qwen3_tts_tokenizer.py ("wrapper"), decode side.
 
 Same constructor-less class, `from_pretrained`, `decode(encoded) -> (List[np.float32 1-D], sr)` accepting
-the reference's payload forms (wrapper :298-329) and the five getters (wrapper :367-411).  `encode`
-and audio I/O (librosa / soundfile) are outside the accelerated hot path and are not provided here.
+the reference's payload forms (wrapper :298-329), `encode(audios, sr)` for numpy waveforms (wrapper :208-257) and the five getters
+(wrapper :367-411).  Audio file I/O and resampling (librosa / soundfile, wrapper :122-206) are not part of this package: encode takes
+waveforms that are already at the model's input rate.
 """
 from __future__ import annotations
 
@@ -42,8 +43,44 @@ class Qwen3TTSTokenizer:
         inst.device = model.device
         return inst
 
-    def encode(self, *args, **kwargs):
-        raise NotImplementedError("encode (wav -> codes) is outside the decode hot path this package accelerates")
+    def _normalize_audio_inputs(self, audios, sr) -> List[np.ndarray]:
+        """wrapper :162-206 for numpy input: list of 1-D float32 waveforms at the model's input rate.  Paths / base64 strings need
+        soundfile + librosa (file decoding, resampling), which this package does not ship: load them with the reference's
+        `load_audio` and pass the arrays."""
+        target_sr = int(self.model.get_input_sample_rate())
+        if isinstance(audios, (str, np.ndarray)):
+            audios = [audios]
+        if len(audios) == 0:
+            return []
+        if isinstance(audios[0], str):
+            raise NotImplementedError("audio paths / base64 strings need soundfile + librosa; pass numpy waveforms and `sr`")
+        if sr is None:
+            raise ValueError("For numpy waveform input, you must provide `sr` (original sampling rate).")
+        out = []
+        for a in audios:
+            if not isinstance(a, np.ndarray):
+                raise TypeError("Mixed input types are not supported. Use all paths/base64 or all numpy arrays.")
+            if a.ndim > 1:
+                a = np.mean(a, axis=-1)
+            if int(sr) != target_sr:
+                raise NotImplementedError(f"resampling {sr} -> {target_sr} Hz needs librosa; resample before calling encode")
+            out.append(a.astype(np.float32))
+        return out
+
+    def encode(self, audios, sr=None, return_dict: bool = True):
+        """Batch-encode audio into discrete codes (wrapper :208-257): numpy waveform(s) + `sr` -> Qwen3TTSTokenizerV2EncoderOutput with
+        audio_codes = List[LongTensor (codes_len_i, 16)].  Padding follows the reference's feature extractor (EncodecFeatureExtractor,
+        padding=True): zeros up to the longest item, padding_mask = 1 on real samples."""
+        wavs = self._normalize_audio_inputs(audios, sr=sr)
+        if not wavs:
+            raise ValueError("encode: no audio given")
+        T = max(int(w.shape[0]) for w in wavs)
+        input_values = torch.zeros((len(wavs), T), dtype=torch.float32)
+        padding_mask = torch.zeros((len(wavs), T), dtype=torch.long)
+        for b, w in enumerate(wavs):
+            input_values[b, :w.shape[0]] = torch.from_numpy(w)
+            padding_mask[b, :w.shape[0]] = 1
+        return self.model.encode(input_values.to(self.device), padding_mask, return_dict=return_dict)
 
     def num_decoded_samples(self, frames: int) -> int:
         """Samples decode() returns for an item that fills a batch padded to `frames` code frames:

@@ -1,0 +1,103 @@
+"""-m gpu: the whole 12 Hz encode path through the C-ABI: q3tts_encode / q3tts_encode_host behind
+Qwen3TTSTokenizerV2Model.encode and Qwen3TTSTokenizer.encode, against the golden the reference's own encoder class wrote
+(tests/golden/encode_B2.npz) and the float64 oracle (oracle/encoder_oracle.py).
+
+Bars: latents within 1e-4 of the largest latent (the reference's own fp32 run sits at 7e-7 from the float64 oracle; this path
+multiplies fp16 hi + lo pairs on the tensor cores, ~2e-6); codes identical wherever the oracle's two best codes are further apart
+than that error can bridge (relative margin >= 1e-4), and then only up to a frame's first near-tie that went the other way."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import encoder_oracle as XO
+from oracle.make_golden_encoder import LENGTHS, golden_inputs
+from qwen3_tts_b200.synthetic import make_audio, make_encoder_state_dict
+
+pytestmark = pytest.mark.gpu
+LATENT_TOL = 1e-4
+MARGIN_TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def enc_model(sd):
+    from qwen3_tts_b200 import synthetic_model
+    return synthetic_model(state_dict=sd, device="cuda:0", with_encoder=True)
+
+
+def _check_codes(got, want, margin, what):
+    """got / want [T, K]; margin [K, T]"""
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    compared, wrong = XO.decidable(got.T, want.T, margin[:, :want.shape[0]], MARGIN_TOL)
+    same = float((got == want).mean())
+    print(f"{what}: {compared} decidable codes, {wrong} wrong, {same:.4f} of all codes identical")
+    assert wrong == 0 and compared >= 0.9 * want.size and same >= 0.98, (what, compared, wrong, same)
+
+
+def test_encode_matches_reference_golden(enc_model):
+    g = load_golden("encode_B2.npz")
+    wav, mask = golden_inputs()
+    codes, lat = enc_model.encode(wav, mask, return_latents=True)
+    lat = lat.cpu().numpy()
+    want_lat = g["latents"]
+    assert lat.shape == want_lat.shape
+    err = float(np.abs(lat - want_lat).max() / np.abs(want_lat).max())
+    print(f"latents vs the reference's fp32 run: max-abs error {err:.2e} of the largest latent")
+    assert err <= LATENT_TOL
+    sd = make_encoder_state_dict(seed=0)
+    _o, _l, margin = XO.model_encode(sd, wav, mask)
+    for b, want in enumerate((g["codes0"], g["codes1"])):
+        assert codes[b].shape == (-(-LENGTHS[b] // 1920), 16) and codes[b].dtype == torch.int64
+        _check_codes(codes[b].cpu().numpy(), want.astype(np.int64), margin[b], f"golden item {b}")
+
+
+def test_encode_output_forms_and_host_entry(enc_model):
+    """Qwen3TTSTokenizer.encode (wrapper :208-257) and the host entry give the same codes as model.encode; return forms as the reference."""
+    from qwen3_tts_b200 import Qwen3TTSTokenizer, Qwen3TTSTokenizerV2EncoderOutput
+    tok = Qwen3TTSTokenizer.from_model(enc_model)
+    lengths = (30000, 24000 + 77, 1)
+    wav = make_audio(3, max(lengths), seed=3, lengths=lengths)
+    arrays = [wav[b, :n].numpy() for b, n in enumerate(lengths)]
+    out = tok.encode(arrays, sr=24000)
+    assert isinstance(out, Qwen3TTSTokenizerV2EncoderOutput) and len(out.audio_codes) == 3
+    assert [tuple(c.shape) for c in out.audio_codes] == [(16, 16), (13, 16), (1, 16)]
+    tup = tok.encode(arrays, sr=24000, return_dict=False)
+    assert isinstance(tup, tuple) and all(torch.equal(a, b) for a, b in zip(tup[0], out.audio_codes))
+    host = enc_model.encode_host(arrays)
+    assert all(np.array_equal(h, c.cpu().numpy()) for h, c in zip(host, out.audio_codes))
+    one = tok.encode(arrays[1], sr=24000)                                   # a single ndarray is a batch of one
+    # batch of one: the same item without the batch's zero padding behind it.  Everything is causal, so every frame that ends inside
+    # the real samples is unchanged; the last, partial frame sees the conv stack's own right padding instead of padded samples pushed
+    # through the biases - in the reference too (it encodes the padded batch as it is, modeling :979-980)
+    assert one.audio_codes[0].shape == out.audio_codes[1].shape and torch.equal(one.audio_codes[0][:-1], out.audio_codes[1][:-1])
+    with pytest.raises(ValueError):
+        tok.encode(arrays)                                                  # numpy input needs sr (wrapper :195-196)
+    with pytest.raises(TypeError):
+        tok.encode([arrays[0], "x.wav"], sr=24000)                          # mixed input types (wrapper :199-200)
+    # encode -> decode round trip runs end to end (different random codebooks either side: no identity expected)
+    wavs, sr = tok.decode(out)
+    assert sr == 24000 and [w.shape[0] for w in wavs] == [min(int((c[:, 0] > 0).sum()) * 1920, tok.num_decoded_samples(16)) for c in out.audio_codes]
+
+
+def test_encode_matches_oracle_on_a_ragged_batch_at_size(enc_model):
+    """12 items of 0.5 .. 14 s in one call (sub-batched by the engine), against the float64 oracle item by item.  The oracle gets
+    the item as the batch holds it - zero-padded to the longest item - because the reference encodes the padded batch as it is
+    (modeling :979-980): an item's last, partial frame sees the padding."""
+    rng = np.random.default_rng(11)
+    lengths = [int(x) for x in rng.integers(12000, 336000, size=12)]
+    lengths[3] = 24000 * 14                                                  # 350 frames at 25 Hz: past the attention window
+    wav = make_audio(12, max(lengths), seed=11, lengths=lengths)
+    mask = torch.zeros_like(wav, dtype=torch.long)
+    for b, n in enumerate(lengths):
+        mask[b, :n] = 1
+    codes = enc_model.encode(wav, mask).audio_codes
+    sd = make_encoder_state_dict(seed=0)
+    for b in (3, 0, 7):
+        n = lengths[b]
+        want, _lat, margin = XO.model_encode(sd, wav[b:b + 1], mask[b:b + 1])
+        _check_codes(codes[b].cpu().numpy(), want[0], margin[0], f"ragged item {b} ({n} samples)")
+
+
+def test_encode_needs_encoder_weights(gpu_model):
+    with pytest.raises(RuntimeError, match="not loaded"):
+        gpu_model.encode(torch.zeros(1, 4800))
