@@ -403,8 +403,180 @@ def run_sharded(args, rank, local_rank, world):
 
 
 KERNEL_NAMES = {0: "k_rvq", 1: "conv_gemm_tc_kernel", 2: "k_rmsnorm", 3: "k_attention", 4: "k_dwconv_ln", 5: "tail_conv_kernel", 6: "unit_kernel",
-                7: "ws_conv_kernel", 8: "slab_conv_kernel", 9: "k_stream_attention", 10: "k_state_copy", 11: "k_split_f32"}
+                7: "ws_conv_kernel", 8: "slab_conv_kernel", 9: "k_stream_attention", 10: "k_state_copy", 11: "k_split_f32",
+                12: "k_enc_conv0", 13: "k_act_split", 14: "k_layernorm_split", 15: "k_enc_attention", 16: "k_enc_to_cf", 17: "k_enc_split_cols",
+                18: "k_enc_argmin_update"}
 TENSOR_KERNELS = ("unit_kernel", "slab_conv_kernel", "conv_gemm_tc_kernel", "ws_conv_kernel")
+
+
+
+# ------------------------------------------------------------------------------------------------ encode path
+ENC_UTT, ENC_SEC = 64, 10.0
+ENC_NAME = "Tokenizer-12Hz encode, batch 64 x 10 s synthetic 24 kHz audio per GPU -> 16-codebook codes (the mirror of BASELINE config 2)"
+ENC_METRIC = "audio-sec encoded per sec (24kHz->codes)"
+
+
+def encode_reference_cpu(steps: int, warmup: int, utterances: int = REF_UTTERANCES):
+    """The reference's own encoder class (Qwen3TTSTokenizerV2Encoder = HF MimiModel, through oracle/ref_shim.py) + the reference's
+    model.encode post-processing on the host cores: `utterances` items of the workload in one batch per step."""
+    import torch
+
+    from oracle import ref_shim
+    from qwen3_tts_b200.synthetic import make_audio, make_encoder_state_dict
+    torch.set_num_threads(os.cpu_count() or 1)
+    enc = ref_shim.build_reference_encoder(make_encoder_state_dict(seed=0), attn_implementation="sdpa")
+    T = int(ENC_SEC * 24000)
+    wav = make_audio(utterances, T, seed=1)
+    mask = torch.ones_like(wav, dtype=torch.long)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = ref_shim.reference_model_encode(enc, wav, mask)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    assert len(out) == utterances and tuple(out[0].shape) == (int(ENC_SEC * 12.5), 16)
+    sec = sum(times) / len(times)
+    return {"value": utterances * ENC_SEC / sec, "sec_per_step": sec, "cores": torch.get_num_threads(), "kind": "reference",
+            "sample": f"{utterances} of the {ENC_UTT} utterances x {ENC_SEC:g} s in one batch per step, mean of {steps} steps after {warmup} warm-up"}
+
+
+def encode_config(world: int):
+    return {"workload": ENC_NAME, "samples_per_step_per_gpu": int(ENC_UTT * ENC_SEC * 24000),
+            "weights": "seeded random-init, Mimi encoder architecture (MimiConfig defaults, 16 of 32 codebooks)",
+            "l2": "flushed between timed steps (256 MiB write, untimed); activations per step >> 126 MB L2",
+            "parallelism": f"utterance-sharded x{world}, no collective"}
+
+
+def encode_section(model, dev, steps: int, warmup: int, world: int = 1, rank: int = 0):
+    """Times encode on `model` (needs the encoder weights): device-resident value with the per-kernel profile recorded inside the
+    timed steps, and e2e through the host call (pinned host waveforms in, host codes out)."""
+    import torch
+
+    from qwen3_tts_b200.synthetic import make_audio
+    T = int(ENC_SEC * 24000)
+    wav_host = make_audio(ENC_UTT, T, seed=1 + rank)
+    wav = wav_host.to(dev)
+    arrays = [wav_host[b].numpy() for b in range(ENC_UTT)]
+    dec = model.decoder
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(max(3, warmup)):
+        model.encode(wav)
+    torch.cuda.synchronize(dev)
+    dec.set_profile(True)
+    dec.get_profile()
+    l0 = dec.launch_count()
+    step_ms, acc = [], {}
+    for _ in range(steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        model.encode(wav)
+        b.record()
+        prof = dec.get_profile()
+        step_ms.append(a.elapsed_time(b))
+        for code, t_ms, fl, by, dims in prof:
+            k = acc.setdefault(KERNEL_NAMES.get(code, str(code)), {"ms": 0.0, "launches": 0, "flops": 0.0, "min_bytes": 0.0})
+            k["ms"] += t_ms; k["launches"] += 1; k["flops"] += fl; k["min_bytes"] += by
+    dec.set_profile(False)
+    launches = dec.launch_count() - l0
+    for _ in range(3):
+        codes = model.encode_host(arrays)
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        codes = model.encode_host(arrays)
+    e2e_s = time.perf_counter() - t0
+    assert len(codes) == ENC_UTT and codes[0].shape == (int(ENC_SEC * 12.5), 16)
+    return {"step_ms": step_ms, "acc": acc, "launches": launches, "e2e_s": e2e_s, "frames": int(ENC_SEC * 12.5)}
+
+
+def kernel_table(acc, steps, peaks):
+    ksum = sum(k["ms"] for k in acc.values())
+    out = {}
+    for name, k in sorted(acc.items(), key=lambda kv: -kv[1]["ms"]):
+        sec = k["ms"] * 1e-3
+        tfl = k["flops"] / sec / 1e12 if sec > 0 else 0.0
+        gbs = k["min_bytes"] / sec / 1e9 if sec > 0 else 0.0
+        ft, fh = tfl / peaks["tflops_sustained"], gbs / peaks["hbm_gbs"]
+        tensor = name in TENSOR_KERNELS and ft >= fh
+        out[name] = {"ms_per_step": round(k["ms"] / steps, 4), "launches_per_step": k["launches"] // steps, "share_of_step": round(k["ms"] / ksum, 4),
+                     "bound": "tensor" if tensor else "hbm", "achieved": round(tfl if tensor else gbs, 1), "unit": "TFLOP/s" if tensor else "GB/s",
+                     "frac": round(ft if tensor else fh, 4)}
+    return out, ksum
+
+
+def run_encode(args, rank, local_rank, world):
+    """--workload encode10s: one JSON line for the ENCODE path (same contract as the decode line; its own metric)."""
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        r = encode_reference_cpu(steps=args.steps, warmup=args.warmup)
+        print(json.dumps({"impl": "reference", "metric": ENC_METRIC, "value": r["value"], "unit": "audio-s/s", "n_gpus": args.gpus, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": r["sec_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                          "dtype": "fp32", "data": "synthetic", "config": encode_config(args.gpus),
+                          "cpu_baseline": {"value": r["value"], "unit": "audio-s/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+                          "e2e": {"value": r["value"], "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}), flush=True)
+        return
+    import torch
+    import torch.distributed as dist
+
+    from qwen3_tts_b200 import synthetic_model
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the encode path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
+        dist.init_process_group("nccl", device_id=dev)
+    args.warmup = max(args.warmup, 3)
+    model = synthetic_model(device=dev, with_encoder=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    r = encode_section(model, dev, args.steps, args.warmup, world, rank)
+    clocks = sampler.stop()
+    ms, e2e_s = sum(r["step_ms"]), r["e2e_s"]
+    if world > 1:
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = t[0].item(), t[1].item()
+    peaks = load_peaks()
+    kernels, ksum = kernel_table(r["acc"], args.steps, peaks)
+    if rank == 0:
+        audio_s = world * ENC_UTT * ENC_SEC * args.steps
+        dom = next(iter(kernels))
+        d, kd = r["acc"][dom], kernels[dom]
+        tensor = kd["bound"] == "tensor"
+        alg = d["flops"] if tensor else d["min_bytes"]
+        roof = {"bound": kd["bound"], "kernel": dom, "achieved": alg / (d["ms"] * 1e-3) / (1e12 if tensor else 1e9),
+                "peak": peaks["tflops_sustained"] if tensor else peaks["hbm_gbs"], "unit": kd["unit"], "frac": kd["frac"], "traffic": None,
+                "peak_source": f"{peaks['source']} " + ("sustained bf16 cuBLAS" if tensor else "copy bandwidth"),
+                "share_of_step": d["ms"] / ksum, "launches_per_step": d["launches"] // args.steps,
+                "algorithmic_per_launch": alg / d["launches"], "ms_per_launch_avg": d["ms"] / d["launches"],
+                "measured": f"CUDA-event pairs around every launch inside the {args.steps} timed steps",
+                "sum_kernel_ms_per_step": ksum / args.steps, "sum_kernel_over_step": ksum / sum(r["step_ms"])}
+        total_bytes = sum(k["min_bytes"] for k in r["acc"].values()) / args.steps
+        line = {"metric": ENC_METRIC, "value": audio_s / (ms * 1e-3), "unit": "audio-s/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "fp16 hi + lo operand pairs on the tensor cores (3 MMAs per product), fp32 accumulate, fp32 activations", "data": "synthetic",
+                "config": encode_config(world),
+                "e2e": {"value": audio_s / e2e_s, "unit": "audio-s/s", "ms_per_step": e2e_s / args.steps * 1e3,
+                        "h2d_bytes_per_step": world * ENC_UTT * int(ENC_SEC * 24000) * 4, "d2h_bytes_per_step": world * ENC_UTT * r["frames"] * 16 * 8,
+                        "api": "Qwen3TTSTokenizerV2Model.encode_host(list of float32 waveforms) -> list of int64 [frames, 16] arrays (q3tts_encode_host)"},
+                "gpu_launches": r["launches"], "clocks": clocks, "roofline": roof,
+                "path_frac_of_hbm_roofline": total_bytes / (ms / args.steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "min_hbm_gb_per_step": total_bytes / 1e9,
+                "kernels": kernels}
+        if not args.no_cpu_baseline and world == 1:
+            c = encode_reference_cpu(steps=3, warmup=1)
+            line["cpu_baseline"] = {"value": c["value"], "unit": "audio-s/s", "cores": c["cores"], "kind": c["kind"], "sample": c["sample"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():
@@ -415,14 +587,19 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="fp16", choices=["fp16", "bf16", "fp16-plain", "bf16-plain", "fp16-split-all", "bf16-split-all"],
                     help="tensor-core operand type (fp32 accumulate) and how many early-stage operands are hi + lo pairs (DESIGN.md Precision)")
-    ap.add_argument("--workload", default="bulk10s", choices=sorted(WORKLOADS), help="default = the configuration BASELINE.json's metric is quoted on")
+    ap.add_argument("--workload", default="bulk10s", choices=sorted(WORKLOADS) + ["encode10s"],
+                    help="default = the configuration BASELINE.json's metric is quoted on; encode10s = the encode path (SURVEY 8(f)-2), its own metric")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-streaming", action="store_true", help="skip the streaming-chunk latency section (BASELINE config 3)")
     ap.add_argument("--no-torch-gpu", action="store_true", help="skip the eager-PyTorch-on-this-GPU context section")
+    ap.add_argument("--no-encode", action="store_true", help="skip the encode-path section of the default line (its full line: --workload encode10s)")
     ap.add_argument("--stream-only", action="store_true", help="print only the streaming-chunk latency section")
     ap.add_argument("--streams", type=int, default=256)
     ap.add_argument("--utterances", type=int, default=4096, help="size of the fixed utterance set of --workload sharded30s")
     args = ap.parse_args()
+    if args.workload == "encode10s":
+        run_encode(args, int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
+        return
     if args.workload == "sharded30s":
         if args.impl == "reference":
             raise SystemExit("--workload sharded30s has no reference arm: use the default workload")
@@ -434,6 +611,7 @@ def main():
     if args.workload != "bulk10s":
         args.no_streaming = True  # the streaming and context sections ride on the default line only
         args.no_torch_gpu = True
+        args.no_encode = True
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -466,7 +644,7 @@ def main():
 
     cfg = Qwen3TTSTokenizerV2DecoderConfig()
     sd = make_decoder_state_dict(cfg, seed=0)
-    model = synthetic_model(state_dict=sd, device=dev, compute_mode=args.mode)
+    model = synthetic_model(state_dict=sd, device=dev, compute_mode=args.mode, with_encoder=(world == 1 and not args.no_encode))
     del sd
     dec = model.decoder
     if args.stream_only:
@@ -589,6 +767,17 @@ def main():
         dec.reserve_streams(args.streams, 4)
         line["streaming"] = [stream_latency(dec, cfg, dev, args.streams, 1, steps=2000, warmup=200),
                              stream_latency(dec, cfg, dev, args.streams, 4, steps=500, warmup=50)]
+    if not args.no_encode and world == 1:
+        # SURVEY 8(f)-2 (informational on this line; `--workload encode10s` prints the encode path's own full line)
+        try:
+            r = encode_section(model, dev, steps=5, warmup=3)
+            ek, eks = kernel_table(r["acc"], 5, peaks)
+            top = next(iter(ek))
+            line["encode"] = {"metric": ENC_METRIC, "workload": ENC_NAME, "value": ENC_UTT * ENC_SEC * 5 / (sum(r["step_ms"]) * 1e-3), "unit": "audio-s/s",
+                              "ms_per_step": sum(r["step_ms"]) / 5, "e2e": {"value": ENC_UTT * ENC_SEC * 5 / r["e2e_s"], "ms_per_step": r["e2e_s"] / 5 * 1e3},
+                              "gpu_launches_per_step": r["launches"] // 5, "top_kernel": {"name": top, **ek[top]}}
+        except Exception as ex:  # informational: never fail the bench line over it
+            line["encode"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
     if not args.no_torch_gpu and world == 1:
         del model, dec, tok
         torch.cuda.empty_cache()

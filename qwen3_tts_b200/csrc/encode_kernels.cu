@@ -25,37 +25,74 @@ __device__ __forceinline__ void split_hi_lo(float v, __half& hi, __half& lo) {
   hi = __float2half_rn(v);
   lo = __float2half_rn(v - __half2float(hi));
 }
+// four values at once with the packed converts: hi[0..3] and lo[0..3] as two 8-byte words each
+__device__ __forceinline__ void split4(const float4 v, uint2& hi, uint2& lo) {
+  const __half2 h01 = __floats2half2_rn(v.x, v.y), h23 = __floats2half2_rn(v.z, v.w);
+  const float2 b01 = __half22float2(h01), b23 = __half22float2(h23);
+  const __half2 l01 = __floats2half2_rn(v.x - b01.x, v.y - b01.y), l23 = __floats2half2_rn(v.z - b23.x, v.w - b23.y);
+  hi.x = *reinterpret_cast<const unsigned*>(&h01); hi.y = *reinterpret_cast<const unsigned*>(&h23);
+  lo.x = *reinterpret_cast<const unsigned*>(&l01); lo.y = *reinterpret_cast<const unsigned*>(&l23);
+}
 
+template <int ACT>
+__device__ __forceinline__ float enc_act(float v) {
+  // ELU (alpha 1).  exp(v) - 1 with the hardware exponential: absolute error <= ~2.4e-7 (2 ulp of a value below 1), the level of the
+  // fp16 hi + lo pair the result is stored as; expm1f costs ~10x the instructions and made these passes instruction-bound (2.9 TB/s)
+  if (ACT == 1) return v > 0.f ? v : __expf(v) - 1.0f;
+  if (ACT == 2) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f));
+  return v;
+}
 // ------------------------------------------------------------------------------------------------ first conv: 1 -> C0 channels, k = 7
 // wav [B][wav_bs] fp32 (samples beyond T are not read), w [C0][1][7], out [B][T][C0] fp32.  Causal: x[t - 6 + j] (MimiConv1d :331-352).
 __global__ void __launch_bounds__(256) k_enc_conv0(const float* __restrict__ wav, long long wav_bs, const float* __restrict__ w,
-                                                    const float* __restrict__ bias, float* __restrict__ out, int B, int T, int C0) {
-  extern __shared__ float sw[];  // [7][C0] + [C0]
+                                                    const float* __restrict__ bias, float* __restrict__ out, __half* __restrict__ elu_split, int T,
+                                                    int C0) {
+  // grid (sample tiles, items); a block = (256 / (C0 / 4)) * 8 consecutive samples of one item; thread = 4 channels, 8 samples apart
+  extern __shared__ float sw[];  // [7][C0] weights, [C0] bias, then the block's input samples (+ 6 of history)
+  const int c4n = C0 >> 2, spb = 256 / c4n, tile = spb * 8;
+  float* sx = sw + 8 * C0;
   for (int i = threadIdx.x; i < 7 * C0; i += blockDim.x) { const int co = i % C0, j = i / C0; sw[i] = w[co * 7 + j]; }
   for (int i = threadIdx.x; i < C0; i += blockDim.x) sw[7 * C0 + i] = bias[i];
+  const long long b = blockIdx.y;
+  const int t0 = blockIdx.x * tile;
+  const float* x = wav + b * wav_bs;
+  for (int i = threadIdx.x; i < tile + 6; i += blockDim.x) {
+    const int ts = t0 - 6 + i;
+    sx[i] = (ts >= 0 && ts < T) ? __ldg(x + ts) : 0.f;     // causal left padding (MimiConv1d :331-352)
+  }
   __syncthreads();
-  const int c4n = C0 >> 2;
-  const long long n = (long long)B * T * c4n;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const int c4 = (int)(i % c4n);
-    const long long bt = i / c4n;
-    const int t = (int)(bt % T);
-    const long long b = bt / T;
-    const float* x = wav + b * wav_bs;
-    float4 acc = *reinterpret_cast<const float4*>(sw + 7 * C0 + 4 * c4);
+  const int c4 = threadIdx.x % c4n, s0 = threadIdx.x / c4n;
+  float4 wv[7];
+#pragma unroll
+  for (int j = 0; j < 7; ++j) wv[j] = *reinterpret_cast<const float4*>(sw + j * C0 + 4 * c4);
+  const float4 bv = *reinterpret_cast<const float4*>(sw + 7 * C0 + 4 * c4);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int ls = s0 + k * spb, t = t0 + ls;
+    if (t >= T) break;
+    float4 acc = bv;
 #pragma unroll
     for (int j = 0; j < 7; ++j) {
-      const int ts = t - 6 + j;
-      const float xv = ts >= 0 ? __ldg(x + ts) : 0.f;
-      const float4 wv = *reinterpret_cast<const float4*>(sw + j * C0 + 4 * c4);
-      acc.x = fmaf(xv, wv.x, acc.x); acc.y = fmaf(xv, wv.y, acc.y); acc.z = fmaf(xv, wv.z, acc.z); acc.w = fmaf(xv, wv.w, acc.w);
+      const float xv = sx[ls + j];
+      acc.x = fmaf(xv, wv[j].x, acc.x); acc.y = fmaf(xv, wv[j].y, acc.y); acc.z = fmaf(xv, wv[j].z, acc.z); acc.w = fmaf(xv, wv[j].w, acc.w);
     }
+    const long long bt = b * T + t;
     *reinterpret_cast<float4*>(out + bt * C0 + 4 * c4) = acc;
+    if (elu_split) {  // the first ResnetBlock's conv operand: ELU(x) as [hi | lo] (saves a pass over the largest tensor of the path)
+      uint2 h, l;
+      split4(make_float4(enc_act<1>(acc.x), enc_act<1>(acc.y), enc_act<1>(acc.z), enc_act<1>(acc.w)), h, l);
+      __half* o = elu_split + bt * 2 * C0 + 4 * c4;
+      *reinterpret_cast<uint2*>(o) = h;
+      *reinterpret_cast<uint2*>(o + C0) = l;
+    }
   }
 }
-cudaError_t enc_conv0(const float* wav, long long wav_bs, const float* w, const float* bias, float* out, int B, int T, int C0, cudaStream_t s) {
-  const long long n = (long long)B * T * (C0 / 4);
-  k_enc_conv0<<<enc_blocks(n, 256), 256, (size_t)8 * C0 * sizeof(float), s>>>(wav, wav_bs, w, bias, out, B, T, C0);
+cudaError_t enc_conv0(const float* wav, long long wav_bs, const float* w, const float* bias, float* out, void* elu_split, int B, int T, int C0,
+                      cudaStream_t s) {
+  if (C0 % 4 || 256 % (C0 / 4) || B > 65535) return cudaErrorInvalidValue;
+  const int tile = 256 / (C0 / 4) * 8;
+  dim3 grid((T + tile - 1) / tile, B);
+  k_enc_conv0<<<grid, 256, (size_t)(8 * C0 + tile + 6) * sizeof(float), s>>>(wav, wav_bs, w, bias, out, (__half*)elu_split, T, C0);
   return cudaGetLastError();
 }
 
@@ -67,48 +104,49 @@ cudaError_t enc_conv0(const float* wav, long long wav_bs, const float* w, const 
 // cg (K group, a divisor of r * C): the super-row is written group by group, [hi(g) | lo(g)] for every cg input values, matching the
 // grouped weight rows (kernels.cu put_w) - one GEMM launch then walks one group.  cg = r * C: a single [hi | lo] pair per row.
 template <int ACT>
-__device__ __forceinline__ float enc_act(float v) {
-  if (ACT == 1) return v > 0.f ? v : expm1f(v);
-  if (ACT == 2) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f));
-  return v;
-}
-template <int ACT>
 __global__ void __launch_bounds__(256) k_act_split(const float* __restrict__ in, __half* __restrict__ out, int B, int L, int C, int r, int lead,
-                                                    int replicate, int cg) {
-  const int c4n = C >> 2;
+                                                    int replicate, int cg, int rows_per_block) {
+  // a block owns rows_per_block consecutive super-rows; inside a super-row everything is 32-bit arithmetic
   const int ns = lead + (L + r - 1) / r;
-  const long long n = (long long)B * ns * r * c4n;
-  const long long ow = 2ll * r * C;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const int c4 = (int)(i % c4n);
-    long long q = i / c4n;
-    const int p = (int)(q % r); q /= r;
-    const int sr = (int)(q % ns);
-    const long long b = q / ns;
+  const int w4 = (r * C) >> 2;                 // float4 groups per super-row
+  const long long nrows = (long long)B * ns;
+  const long long row0 = (long long)blockIdx.x * rows_per_block;
+  for (int i = threadIdx.x; i < rows_per_block * w4; i += blockDim.x) {
+    const int lr = i / w4, j4 = i - lr * w4;
+    const long long srow = row0 + lr;
+    if (srow >= nrows) break;
+    const long long b = srow / ns;
+    const int sr = (int)(srow - b * ns);
+    const int j = j4 << 2, p = j / C;
     int row = (sr - lead) * r + p;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     bool valid = row >= 0 && row < L;
     if (!valid && replicate) { row = row < 0 ? 0 : L - 1; valid = true; }
     if (valid) {
-      v = *reinterpret_cast<const float4*>(in + ((b * L + row) * (long long)C + 4 * c4));
+      v = __ldcs(reinterpret_cast<const float4*>(in + ((b * L + row) * (long long)C + (j - p * C))));
       v.x = enc_act<ACT>(v.x); v.y = enc_act<ACT>(v.y); v.z = enc_act<ACT>(v.z); v.w = enc_act<ACT>(v.w);
     }
-    __half h[4], l[4];
-    split_hi_lo(v.x, h[0], l[0]); split_hi_lo(v.y, h[1], l[1]); split_hi_lo(v.z, h[2], l[2]); split_hi_lo(v.w, h[3], l[3]);
-    const int j = p * C + 4 * c4, g = j / cg;
-    __half* o = out + (b * ns + sr) * ow + (long long)g * 2 * cg + (j - g * cg);
-    *reinterpret_cast<uint2*>(o) = *reinterpret_cast<const uint2*>(h);
-    *reinterpret_cast<uint2*>(o + cg) = *reinterpret_cast<const uint2*>(l);
+    uint2 h, l;
+    split4(v, h, l);
+    const int g = j / cg;
+    __half* o = out + srow * (2ll * r * C) + g * 2 * cg + (j - g * cg);
+    *reinterpret_cast<uint2*>(o) = h;
+    *reinterpret_cast<uint2*>(o + cg) = l;
   }
 }
 cudaError_t enc_act_split(const float* in, void* out, int B, int L, int C, int act, int r, int lead, int replicate, int cg, cudaStream_t s) {
   if (cg <= 0) cg = r * C;
-  if ((r * C) % cg || cg % 4) return cudaErrorInvalidValue;
-  const long long n = (long long)B * (lead + (L + r - 1) / r) * r * (C / 4);
-  const int g = enc_blocks(n, 256, 148 * 32);
-  if (act == 1) k_act_split<1><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg);
-  else if (act == 2) k_act_split<2><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg);
-  else k_act_split<0><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg);
+  if ((r * C) % cg || cg % 4 || C % 4) return cudaErrorInvalidValue;
+  const long long nrows = (long long)B * (lead + (L + r - 1) / r);
+  const int w4 = (r * C) / 4;
+  int rpb = 2048 / w4;                         // ~8 float4 groups per thread
+  if (rpb < 1) rpb = 1;
+  const long long blocks = (nrows + rpb - 1) / rpb;
+  if (blocks > 0x7fffffffll) return cudaErrorInvalidValue;
+  const unsigned g = (unsigned)(blocks < 1 ? 1 : blocks);
+  if (act == 1) k_act_split<1><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
+  else if (act == 2) k_act_split<2><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
+  else k_act_split<0><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
   return cudaGetLastError();
 }
 
@@ -178,12 +216,12 @@ cudaError_t enc_rope_table(float* cos_t, float* sin_t, const float* inv_freq_dev
 // qkv fp32 [B*T][3*H] (q | k | v, H = nh * 64) -> out fp16 [B*T][2H] rows [hi | lo] (the A operand of o_proj).
 // Block = (32-query tile, head, item), 8 warps x 4 queries.  Keys are walked in chunks of 64 staged in shared memory (RoPE applied on
 // the way in), with a running max / sum per query (the usual online softmax); query i sees keys j with 0 <= i - j < window.
-static constexpr int EA_Q = 32, EA_K = 64, EA_HD = 64, EA_PAD = EA_HD + 1;
+static constexpr int EA_Q = 32, EA_K = 64, EA_HD = 64, EA_PAD = EA_HD + 4;  // row pitch 68 floats: float4 reads of 8 consecutive rows hit 8 different bank groups
 __global__ void __launch_bounds__(256) k_enc_attention(const float* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
                                                         __half* __restrict__ out, int T, int nh, int window) {
-  __shared__ float sq[EA_Q][EA_HD];
-  __shared__ float sk[EA_K][EA_PAD];
-  __shared__ float sv[EA_K][EA_HD];
+  __shared__ __align__(16) float sq[EA_Q][EA_HD];
+  __shared__ __align__(16) float sk[EA_K][EA_PAD];
+  __shared__ __align__(16) float sv[EA_K][EA_HD];
   const int q0 = blockIdx.x * EA_Q, head = blockIdx.y, b = blockIdx.z;
   const int H = nh * EA_HD;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -222,15 +260,22 @@ __global__ void __launch_bounds__(256) k_enc_attention(const float* __restrict__
     }
     __syncthreads();
     float pr0[4], pr1[4];  // this lane's two probabilities per query (keys k0 + lane, k0 + lane + 32); broadcast by shuffle below
+    float sc0[4] = {0.f, 0.f, 0.f, 0.f}, sc1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int d = 0; d < EA_HD; d += 4) {      // one float4 of each of this lane's two keys against the warp's four queries
+      const float4 ka = *reinterpret_cast<const float4*>(&sk[lane][d]);
+      const float4 kb = *reinterpret_cast<const float4*>(&sk[lane + 32][d]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 qv = *reinterpret_cast<const float4*>(&sq[warp * 4 + i][d]);
+        sc0[i] = fmaf(qv.x, ka.x, sc0[i]); sc0[i] = fmaf(qv.y, ka.y, sc0[i]); sc0[i] = fmaf(qv.z, ka.z, sc0[i]); sc0[i] = fmaf(qv.w, ka.w, sc0[i]);
+        sc1[i] = fmaf(qv.x, kb.x, sc1[i]); sc1[i] = fmaf(qv.y, kb.y, sc1[i]); sc1[i] = fmaf(qv.z, kb.z, sc1[i]); sc1[i] = fmaf(qv.w, kb.w, sc1[i]);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int qi = warp * 4 + i, t = q0 + qi;
-      float s0 = 0.f, s1 = 0.f;
-      for (int d = 0; d < EA_HD; ++d) {
-        const float qv = sq[qi][d];
-        s0 = fmaf(qv, sk[lane][d], s0);
-        s1 = fmaf(qv, sk[lane + 32][d], s1);
-      }
+      float s0 = sc0[i], s1 = sc1[i];
       const int j0 = k0 + lane, j1 = k0 + lane + 32;
       const bool ok0 = t < T && j0 <= t && t - j0 < window, ok1 = t < T && j1 <= t && t - j1 < window;
       s0 = ok0 ? s0 * 0.125f : -3.0e38f;   // scaling = 1 / sqrt(head_dim) (:665)
@@ -247,16 +292,15 @@ __global__ void __launch_bounds__(256) k_enc_attention(const float* __restrict__
       m[i] = mnew;
       pr0[i] = p0; pr1[i] = p1;
     }
+#pragma unroll 4
+    for (int k = 0; k < 32; ++k) {            // two value rows per step, shared by the warp's four queries
+      const float va0 = sv[k][lane], va1 = sv[k][lane + 32], vb0 = sv[k + 32][lane], vb1 = sv[k + 32][lane + 32];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      float a0 = acc0[i], a1 = acc1[i];
-#pragma unroll 8
-      for (int k = 0; k < 32; ++k) {
+      for (int i = 0; i < 4; ++i) {
         const float p = __shfl_sync(0xffffffffu, pr0[i], k), pb = __shfl_sync(0xffffffffu, pr1[i], k);
-        a0 = fmaf(p, sv[k][lane], a0);           a1 = fmaf(p, sv[k][lane + 32], a1);
-        a0 = fmaf(pb, sv[k + 32][lane], a0);     a1 = fmaf(pb, sv[k + 32][lane + 32], a1);
+        acc0[i] = fmaf(p, va0, acc0[i]); acc1[i] = fmaf(p, va1, acc1[i]);
+        acc0[i] = fmaf(pb, vb0, acc0[i]); acc1[i] = fmaf(pb, vb1, acc1[i]);
       }
-      acc0[i] = a0; acc1[i] = a1;
     }
   }
 #pragma unroll
@@ -276,6 +320,76 @@ cudaError_t enc_attention(const float* qkv, const float* cos_t, const float* sin
   if (hd != EA_HD) return cudaErrorInvalidValue;
   dim3 grid((T + EA_Q - 1) / EA_Q, nh, B);
   k_enc_attention<<<grid, 256, 0, s>>>(qkv, cos_t, sin_t, (__half*)out, T, nh, window);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ RVQ search, step 2 of a layer
+// The layer's scores come from a tensor-core GEMM (encode_plan.cu): S[m][c] = r_m . e_c, fp32 [M][NC].  One warp per frame m:
+// code = argmin_c (|e_c|^2 - 2 S[m][c]) with the LOWEST index winning ties (torch.argmin over torch.cdist, modeling_mimi.py:1205-1219;
+// the |r|^2 term is the same for every code), r_m -= e_code in fp32, and the next layer's GEMM operand [hi | lo] of the new residual.
+__global__ void __launch_bounds__(256) k_enc_argmin_update(const float* __restrict__ S, const float* __restrict__ n2, const float* __restrict__ table,
+                                                            float* __restrict__ r, int ldr, __half* __restrict__ a_next, long long* __restrict__ codes,
+                                                            long long code_stride_m, long long code_stride_b, long long code_off, int M, int F, int NC,
+                                                            int dq) {
+  const int lane = threadIdx.x & 31;
+  const long long m = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (m >= M) return;
+  const float* s = S + m * NC;
+  float best = 3.4e38f;
+  int bidx = 0x7fffffff;
+  for (int c = lane * 4; c < NC; c += 128) {   // indices ascend per lane: strict < keeps the lowest
+    const float4 sv = __ldcs(reinterpret_cast<const float4*>(s + c));
+    const float4 nv = *reinterpret_cast<const float4*>(n2 + c);
+    const float v0 = fmaf(-2.f, sv.x, nv.x), v1 = fmaf(-2.f, sv.y, nv.y), v2 = fmaf(-2.f, sv.z, nv.z), v3 = fmaf(-2.f, sv.w, nv.w);
+    if (v0 < best) { best = v0; bidx = c; }
+    if (v1 < best) { best = v1; bidx = c + 1; }
+    if (v2 < best) { best = v2; bidx = c + 2; }
+    if (v3 < best) { best = v3; bidx = c + 3; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float b2 = __shfl_xor_sync(0xffffffffu, best, o);
+    const int i2 = __shfl_xor_sync(0xffffffffu, bidx, o);
+    if (b2 < best || (b2 == best && i2 < bidx)) { best = b2; bidx = i2; }
+  }
+  if (lane == 0) codes[(m / F) * code_stride_b + (m % F) * code_stride_m + code_off] = bidx;
+  float* rr = r + m * ldr;
+  const float* e = table + (long long)bidx * dq;
+  for (int j = lane * 4; j < dq; j += 128) {
+    float4 rv = *reinterpret_cast<const float4*>(rr + j);
+    const float4 ev = *reinterpret_cast<const float4*>(e + j);
+    rv.x -= ev.x; rv.y -= ev.y; rv.z -= ev.z; rv.w -= ev.w;
+    *reinterpret_cast<float4*>(rr + j) = rv;
+    if (a_next) {
+      __half h[4], l[4];
+      split_hi_lo(rv.x, h[0], l[0]); split_hi_lo(rv.y, h[1], l[1]); split_hi_lo(rv.z, h[2], l[2]); split_hi_lo(rv.w, h[3], l[3]);
+      *reinterpret_cast<uint2*>(a_next + m * 2 * dq + j) = *reinterpret_cast<const uint2*>(h);
+      *reinterpret_cast<uint2*>(a_next + m * 2 * dq + dq + j) = *reinterpret_cast<const uint2*>(l);
+    }
+  }
+}
+cudaError_t enc_argmin_update(const float* S, const float* n2, const float* table, float* r, int ldr, void* a_next, long long* codes,
+                              long long code_stride_m, long long code_stride_b, long long code_off, int M, int F, int NC, int dq, cudaStream_t s) {
+  if (NC % 128 || dq % 4 || ldr % 4) return cudaErrorInvalidValue;
+  k_enc_argmin_update<<<(unsigned)((M + 7) / 8), 256, 0, s>>>(S, n2, table, r, ldr, (__half*)a_next, codes, code_stride_m, code_stride_b, code_off, M, F, NC, dq);
+  return cudaGetLastError();
+}
+// fp32 [M][ld] columns [c0, c0 + C) -> fp16 [M][2C] rows [hi | lo] (first operand of a quantiser group: its projected latents)
+__global__ void k_enc_split_cols(const float* __restrict__ in, int ld, int c0, __half* __restrict__ out, long long M, int C) {
+  const int c4n = C >> 2;
+  const long long n = M * c4n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long m = i / c4n;
+    const int c = (int)(i - m * c4n) << 2;
+    const float4 v = *reinterpret_cast<const float4*>(in + m * ld + c0 + c);
+    __half h[4], l[4];
+    split_hi_lo(v.x, h[0], l[0]); split_hi_lo(v.y, h[1], l[1]); split_hi_lo(v.z, h[2], l[2]); split_hi_lo(v.w, h[3], l[3]);
+    *reinterpret_cast<uint2*>(out + m * 2 * C + c) = *reinterpret_cast<const uint2*>(h);
+    *reinterpret_cast<uint2*>(out + m * 2 * C + C + c) = *reinterpret_cast<const uint2*>(l);
+  }
+}
+cudaError_t enc_split_cols(const float* in, int ld, int c0, void* out, long long M, int C, cudaStream_t s) {
+  k_enc_split_cols<<<enc_blocks(M * (C / 4), 256), 256, 0, s>>>(in, ld, c0, (__half*)out, M, C);
   return cudaGetLastError();
 }
 

@@ -53,10 +53,10 @@ struct EncFin {
     if (!rc && err != cudaSuccess) rc = e->fail(Q3TTS_CUDA_ERROR, std::string(what) + ": " + cudaGetErrorString(err));
   }
   // The tensor cores add into their fp32 accumulators with truncation, so the error of a dot product grows linearly with the
-  // number of MMA instructions chained on one accumulator (measured: latents 7e-5 off with chains of up to 1536 instructions, against
-  // 6e-6 for the same operands summed with fmaf).  A layer whose K' = taps * 3 * kreal exceeds kMaxChain is therefore cut into K
+  // number of MMA instructions chained on one accumulator (measured: latents 7e-5 off with chains of up to 1536 instructions, 1.2e-5 with chains
+  // of at most 96, against 3e-6 for the same operands summed with fmaf).  A layer whose K' = taps * 3 * kreal exceeds kMaxChain is therefore cut into K
   // groups of cg input values: one launch per group, each adding its partial sum to the fp32 output in the epilogue (a rounded add).
-  static constexpr int kMaxChain = 1536;   // K' per launch = 96 MMA instructions of K = 16
+  static constexpr int kMaxChain = 2048;   // K' per launch = 128 MMA instructions of K = 16
   static int group_size(int kreal, int taps, int kb) {
     if (taps * 3 * kreal <= kMaxChain) return 0;
     int best = kb;
@@ -142,7 +142,9 @@ struct EncBuilder {
   // A [batches][rows][2 kreal] fp16 -> fp32 out [batches][rows_valid][n] (+ bias, * scale, + fp32 residual).  A layer with K groups
   // (ConvW::cg) is one launch per group: group g reads A columns [2 g cg, 2 (g + 1) cg) and weight columns [3 g cg, 3 (g + 1) cg) of
   // the full-pitch rows, and from the second group on adds to what the earlier groups stored.
-  void gemm(const ConvW& w, const void* in, int batches, int rows, int rows_valid, float* out, const float* res = nullptr, const float* scale = nullptr) {
+  // elu_split_out (single-group layers only): instead of fp32, ELU(acc + bias) goes out as the fp16 [hi | lo] rows of the next layer
+  void gemm(const ConvW& w, const void* in, int batches, int rows, int rows_valid, float* out, const float* res = nullptr, const float* scale = nullptr,
+            void* elu_split_out = nullptr) {
     const int kreal = w.a_cols / 2;
     const int cg = w.cg > 0 ? w.cg : kreal, G = kreal / cg;
     for (int g = 0; g < G; ++g) {
@@ -164,6 +166,12 @@ struct EncBuilder {
       p.out_f32 = out; p.scale = scale;
       const float* r = g == 0 ? res : out;
       if (r) { p.res = r; p.res_f32 = 1; }
+      if (elu_split_out) {
+        p.out_f32 = nullptr; p.act = ACT_ELU_SPLIT;
+        p.out_raw = elu_split_out; p.out_snake = (char*)elu_split_out + (size_t)w.n_total * 2;
+        p.out_row_stride = 2 * w.n_total; p.out_batch_stride = (long long)rows_valid * 2 * w.n_total;
+      }
+      op.g.retile = 1;   // few rows (the 25 Hz stages): shrink the N tile until the grid covers the SMs
     }
   }
   // act(in) fp32 [B][L][C] -> fp16 super-rows (encode_kernels.cu enc_act_split)
@@ -183,26 +191,46 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   EncBuilder b{e, plan, e->enc_ws, 0, dry};
   plan->B = B; plan->T = T; plan->ops.clear();
   const int C0 = e->enc_c0, H = e->enc_hidden, I = e->enc_inter;
-  // ---- conv k7: wav -> X [B][T][C0]
-  int L = T, C = C0;
-  float* X = (float*)b.alloc((size_t)B * L * C * 4);
-  { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_CONV0; op.out = X; op.B = B; op.L = L; op.C = C; }
-  // ---- four stages: ResnetBlock, ELU, strided conv
-  for (const EncStageW& S : e->enc_stages) {
-    const int r = S.r, Ln = cdiv(L, r);
-    void* A1 = b.alloc((size_t)B * L * 2 * C * 2);             // ELU(x) [hi | lo]; reused for the strided conv's super-rows
-    float* Hh = (float*)b.alloc((size_t)B * L * (C / 2) * 4);
-    void* A2 = b.alloc((size_t)B * L * C * 2);
-    b.act(S.c3, X, A1, B, L, C, 1);
-    b.gemm(S.c3, A1, B, L, L, Hh);
-    b.act(S.c1, Hh, A2, B, L, C / 2, 1);
-    b.gemm(S.c1, A2, 1, B * L, B * L, X, X);                    // x += conv_k1(...): residual read and written in place, fp32
-    void* A3 = b.alloc((size_t)B * Ln * 2 * r * C * 2);
-    float* Xn = (float*)b.alloc((size_t)B * Ln * 2 * C * 4);
-    b.act(S.down, X, A3, B, L, C, 1, r);
-    b.gemm(S.down, A3, B, Ln, Ln, Xn);
-    X = Xn; L = Ln; C = 2 * C;
+  // Workspace: the fp32 main-path tensor of every stage is kept (X0, X1, ...: ~460 B per sample in all); the per-stage operands
+  // (ELU'd [hi | lo] copies, the ResnetBlock's hidden tensor) live in a scratch region that every stage reuses (~512 B per sample).
+  std::vector<size_t> xbytes;
+  {
+    int L = T, C = C0;
+    xbytes.push_back((size_t)B * L * C * 4);
+    for (const EncStageW& S : e->enc_stages) { L = cdiv(L, S.r); C *= 2; xbytes.push_back((size_t)B * L * C * 4); }
   }
+  std::vector<float*> Xs;
+  for (size_t n : xbytes) Xs.push_back((float*)b.alloc(n));
+  const size_t scratch0 = b.off;
+  size_t scratch_max = b.off;
+  // ---- conv k7: wav -> X0 [B][T][C0], and ELU(X0) [hi | lo] for the first ResnetBlock
+  int L = T, C = C0;
+  float* X = Xs[0];
+  size_t si = 0;
+  for (const EncStageW& S : e->enc_stages) {
+    b.off = scratch0;
+    const int r = S.r, Ln = cdiv(L, r);
+    const size_t a1 = (size_t)B * L * 2 * C * 2, a3 = (size_t)B * Ln * 2 * r * C * 2;
+    void* A1 = b.alloc(a1 > a3 ? a1 : a3);                     // ELU(x) [hi | lo]; later the strided conv's super-rows (A1 is dead by then)
+    const bool fused = S.c3.cg == 0 && S.c1.cg == 0 && (C / 2) % 32 == 0;   // ELU(conv_k3) leaves the epilogue as the k1 conv's operand
+    float* Hh = fused ? nullptr : (float*)b.alloc((size_t)B * L * (C / 2) * 4);
+    void* A2 = b.alloc((size_t)B * L * C * 2);
+    if (si == 0) { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_CONV0; op.out = X; op.w0 = (const float*)A1; op.B = B; op.L = L; op.C = C; }
+    else b.act(S.c3, X, A1, B, L, C, 1);
+    if (fused) {
+      b.gemm(S.c3, A1, B, L, L, nullptr, nullptr, nullptr, A2);
+    } else {
+      b.gemm(S.c3, A1, B, L, L, Hh);
+      b.act(S.c1, Hh, A2, B, L, C / 2, 1);
+    }
+    b.gemm(S.c1, A2, 1, B * L, B * L, X, X);                    // x += conv_k1(...): residual read and written in place, fp32
+    b.act(S.down, X, A1, B, L, C, 1, r);
+    float* Xn = Xs[si + 1];
+    b.gemm(S.down, A1, B, Ln, Ln, Xn);
+    if (b.off > scratch_max) scratch_max = b.off;
+    X = Xn; L = Ln; C = 2 * C; ++si;
+  }
+  b.off = scratch0;
   // ---- ELU, conv k3 -> Y [B][L][H]: the transformer's residual stream
   const int M = B * L;
   float* Y = (float*)b.alloc((size_t)M * H * 4);
@@ -227,18 +255,35 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     b.gemm(W.fc2, G, 1, M, M, Y, Y, W.ls2);
   }
   // ---- down-sampling conv (stride 2, kernel 4, replicate padding, no bias) -> latents [B][F][H]
-  const int F = cdiv(L, 2);
+  const int F = cdiv(L, 2), MF = B * F;
   void* AD = b.alloc((size_t)B * (F + 1) * 4 * H * 2);
-  float* LAT = (float*)b.alloc((size_t)B * F * H * 4);
+  float* LAT = (float*)b.alloc((size_t)MF * H * 4);
   b.act(e->enc_down, Y, AD, B, L, H, 0, 2, 1, 1);
   b.gemm(e->enc_down, AD, B, F + 1, F, LAT);
   { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_RVQ; op.in = LAT; op.B = B; op.L = F; op.C = H; op.tag = "latents"; }
+  // ---- RVQ search (MimiSplitResidualVectorQuantizer.encode :1296-1350) on the tensor cores: per codebook one GEMM residual x codes
+  // (fp16 hi + lo operands: K' = 3 * 256) and one SIMT pass that takes the argmin and updates the fp32 residual
+  const int dq = e->cfg.codebook_dim / 2, NC = e->cfg.codebook_size, K = e->cfg.num_quantizers;
+  void* AL = b.alloc((size_t)MF * 2 * H * 2);
+  float* R = (float*)b.alloc((size_t)MF * 2 * dq * 4);          // [semantic residual | acoustic residual]
+  void* AR = b.alloc((size_t)MF * 2 * dq * 2);
+  float* SC = (float*)b.alloc((size_t)MF * NC * 4);
+  b.act(e->enc_qin, LAT, AL, 1, MF, H, 0);
+  b.gemm(e->enc_qin, AL, 1, MF, MF, R);
+  for (int k = 0; k < K; ++k) {
+    if (k <= 1) { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_SPLITCOLS; op.in = R; op.out = AR; op.B = MF; op.C = dq; op.aux0 = k * dq; op.aux1 = 2 * dq; }
+    b.gemm(e->enc_cb[k], AR, 1, MF, MF, SC);
+    plan->ops.emplace_back();
+    Op& op = plan->ops.back();
+    op.type = OP_ENC_ARGMIN; op.w0 = SC; op.w1 = R; op.out = (k == 0 || k == K - 1) ? nullptr : AR; op.B = B; op.L = F; op.C = NC; op.aux0 = k; op.aux1 = k == 0 ? 0 : dq;
+  }
+  if (b.off > scratch_max) scratch_max = b.off;
   plan->out_len = F;
   if (!dry) {
     for (Op& op : plan->ops)
       if (op.type == OP_GEMM && gemm_make_epilogue_maps(&op.g)) b.rc = e->fail(Q3TTS_CUDA_ERROR, "epilogue tensor map failed (encoder)");
   }
-  if (bytes) *bytes = b.off + 1024;
+  if (bytes) *bytes = scratch_max + 1024;
   return b.rc;
 }
 
@@ -268,11 +313,15 @@ int get_plan(Engine* e, int B, int T, Plan** out) {
 // codes: [B][Q][F] (codes_tq = 0) or [B][F][Q]; latents (optional) [B][H][F]
 int run(Engine* e, Plan* plan, const float* wav, long long wav_stride, long long* codes, int codes_tq, float* latents, cudaStream_t s) {
   size_t pi = e->profile ? prof_begin(e, plan->ops.size()) : 0;
+  bool searching = false;
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
+    if (searching && !codes) break;   // latents only: the search is not run
+    if (op.type == OP_ENC_RVQ && !latents) { searching = true; continue; }   // the parity tap is a no-op unless asked for
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
+    if (op.type == OP_ENC_RVQ) searching = true;
     switch (op.type) {
-      case OP_ENC_CONV0: err = enc_conv0(wav, wav_stride, e->enc_conv0_w, e->enc_conv0_b, (float*)op.out, op.B, op.L, op.C, s); break;
+      case OP_ENC_CONV0: err = enc_conv0(wav, wav_stride, e->enc_conv0_w, e->enc_conv0_b, (float*)op.out, (void*)op.w0, op.B, op.L, op.C, s); break;
       case OP_ENC_ACT: err = enc_act_split((const float*)op.in, op.out, op.B, op.L, op.C, op.aux0, op.aux1, op.split & 0xff, op.split >> 8, op.probe_ld, s); break;
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_ENC_LN: err = enc_layernorm_split((const float*)op.in, op.w0, op.w1, op.out, op.B, op.C, e->enc_cfg.norm_eps, s); break;
@@ -280,10 +329,17 @@ int run(Engine* e, Plan* plan, const float* wav, long long wav_stride, long long
         err = enc_attention((const float*)op.in, e->enc_rope_cos, e->enc_rope_sin, op.out, op.B, op.L, e->enc_cfg.num_attention_heads, 64,
                             e->enc_cfg.sliding_window, s);
         break;
-      case OP_ENC_RVQ:
+      case OP_ENC_RVQ:   // parity tap: the quantiser's input in the reference's layout
         if (latents) err = enc_to_channels_first((const float*)op.in, latents, op.B, op.L, op.C, s);
-        if (err == cudaSuccess && codes) err = rvq_encode_launch(e, (const float*)op.in, op.B, op.L, codes, 1, codes_tq, s);
         break;
+      case OP_ENC_SPLITCOLS: err = enc_split_cols((const float*)op.in, op.aux1, op.aux0, op.out, op.B, op.C, s); break;
+      case OP_ENC_ARGMIN: {
+        const int K = e->cfg.num_quantizers, dq = e->cfg.codebook_dim / 2, k = op.aux0;
+        // codes [B][K][F] (stride between frames 1, between items K * F, offset k * F) or [B][F][K] (K, F * K, k)
+        err = enc_argmin_update(op.w0, e->enc_norms + (size_t)k * op.C, e->enc_tables + (size_t)k * op.C * dq, const_cast<float*>(op.w1) + op.aux1, 2 * dq, op.out,
+                                codes, codes_tq ? K : 1, (long long)K * op.L, codes_tq ? k : (long long)k * op.L, op.B * op.L, op.L, op.C, dq, s);
+        break;
+      }
       default: err = cudaErrorInvalidValue; break;
     }
     ++e->launches;
@@ -356,6 +412,26 @@ int encoder_front_finalize(Engine* e) {
     e->enc_layers.push_back(W);
   }
   e->enc_down = f.strided("encoder.downsample.conv", H, H, 2, false, 0);
+  if (f.rc) return f.rc;
+  // quantiser as GEMM operands: the two input projections stacked (H -> 2 dq), and every codebook [codes][dq] (rvq_encode.cu packed
+  // embed = embed_sum / clamp(cluster_usage) in fp32 just before this call)
+  if (!e->enc_ready) return e->fail(Q3TTS_BAD_KEY, "the encoder front needs the encoder.quantizer.* tensors too");
+  {
+    const int dq = e->cfg.codebook_dim / 2, NC = e->cfg.codebook_size, K = e->cfg.num_quantizers;
+    auto operand = [&](const float* src, int n, int kdim) {
+      ConvW w;
+      w.taps = 1; w.n_total = n; w.ncol_mod = n;
+      w.kb = EncFin::kblock(kdim); w.cg = EncFin::group_size(kdim, 1, w.kb);
+      w.w = f.alloc((size_t)n * kdim * 2 * 3);
+      if (!f.rc) f.check(pack_rows(src, w.w, n, kdim, false, f.s, 3, w.cg), "pack_rows (quantiser)");
+      f.finish(w, kdim);
+      return w;
+    };
+    e->enc_qin = operand(e->enc_win, 2 * dq, H);
+    e->enc_cb.clear();
+    for (int k = 0; k < K && !f.rc; ++k) e->enc_cb.push_back(operand(e->enc_tables + (size_t)k * NC * dq, NC, dq));
+    if (NC % 128 || dq % 4) return e->fail(Q3TTS_BAD_CONFIG, "quantiser shape not supported by the search kernels");
+  }
   if (f.rc) return f.rc;
   // RoPE tables with the reference's float32 arithmetic: inv_freq = 1 / theta^(2i / 64) evaluated in float32 (:550-553)
   float inv[32];

@@ -59,7 +59,10 @@ enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNI
               OP_SPLIT /* fp32 [B][L][C] -> 16-bit [hi | lo] rows: in, out, B, L, C, sp_in_bs / sp_out_bs */,
               // encode path (encode_plan.cu): first conv; act + split (aux0 = act, aux1 = r, split = lead rows | replicate << 8, probe_ld = K group);
               // LayerNorm -> [hi | lo]; fp32 attention; RVQ search (aux0 = 1: codes [B][T][Q])
-              OP_ENC_CONV0, OP_ENC_ACT, OP_ENC_LN, OP_ENC_ATTN, OP_ENC_RVQ };
+              OP_ENC_CONV0, OP_ENC_ACT, OP_ENC_LN, OP_ENC_ATTN, OP_ENC_RVQ,
+              // RVQ search on the tensor cores: split a column range of the projected latents (aux0 = first column, aux1 = row pitch);
+              // argmin over a layer's scores + residual update (aux0 = codebook, aux1 = residual column offset, w0 = scores, w1 = residuals)
+              OP_ENC_SPLITCOLS, OP_ENC_ARGMIN };
 
 struct Op {
   OpType type = OP_GEMM;
@@ -191,11 +194,13 @@ struct Engine {
   const float *enc_conv0_w = nullptr, *enc_conv0_b = nullptr;
   std::vector<EncStageW> enc_stages;
   ConvW enc_last, enc_down;
+  ConvW enc_qin;                 // semantic | acoustic input_proj stacked: 512 -> 2 x 256
+  std::vector<ConvW> enc_cb;     // per codebook: [codes][dq] as a GEMM operand (scores = residual . code)
   std::vector<EncLayerW> enc_layers;
   float *enc_rope_cos = nullptr, *enc_rope_sin = nullptr;
   uint8_t* enc_ws = nullptr;
   size_t enc_ws_bytes = 0;
-  long long enc_max_samples = 4ll << 20;       // samples per launch (B * T): bounds the workspace (~1.9 KB per sample)
+  long long enc_max_samples = 16ll << 20;      // samples per launch (B * T): bounds the workspace (~1 KB per sample)
   std::map<std::pair<int, int>, Plan> enc_plans;  // (B, T samples)
   float* enc_wav_stage = nullptr;              // device staging of q3tts_encode_host
   size_t enc_wav_stage_elems = 0;

@@ -391,8 +391,11 @@ void prof_account(Engine* e, const Op& op) {
     fl = 4.0 * rows * op.C * (op.L < e->enc_cfg.sliding_window ? op.L : e->enc_cfg.sliding_window);
     by = rows * op.C * (12.0 + 4.0);                                       // q, k, v fp32 in, [hi | lo] out
   } else if (op.type == OP_ENC_RVQ) {
-    by = (double)op.B * op.L * (4.0 * op.C + 8.0 * e->cfg.num_quantizers); // latents in, codes out; the tables stay in L2
-    fl = 2.0 * (double)op.B * op.L * e->cfg.num_quantizers * e->cfg.codebook_size * (e->cfg.codebook_dim / 2);
+    by = 0.0;                                                              // parity tap (only when the caller asks for latents)
+  } else if (op.type == OP_ENC_SPLITCOLS) {
+    by = 8.0 * (double)op.B * op.C;
+  } else if (op.type == OP_ENC_ARGMIN) {
+    by = (double)op.B * op.L * (4.0 * op.C + 8.0 + 3.0 * 4.0 * (e->cfg.codebook_dim / 2));   // scores in, code out, residual in / out + operand out
   } else if (op.type == OP_DWLN) {
     by = (op.split ? 4.0 + 2.0 : 2.0 * 2.0) * (double)op.B * op.L * op.C;  // one read and one write of the token tensor
   }

@@ -8,6 +8,8 @@ namespace q3 {
 
 __device__ __forceinline__ float gelu_erf(float v) { return 0.5f * v * (1.0f + erff(v * 0.70710678118654752440f)); }
 __device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
+// ELU (alpha 1) of the encode path; exp(v) - 1 with the hardware exponential (absolute error ~2e-7, the level of the fp16 pair it is stored as)
+__device__ __forceinline__ float elu_fast(float v) { return v > 0.f ? v : __expf(v) - 1.0f; }
 // SnakeBeta (reference modeling :601-615): x + 1/(exp(beta)+1e-9) * sin(x*exp(alpha))^2, evaluated as
 //   (x + h) - h * cos(a2 * x),  a2 = 2 exp(alpha), h = (1/2) / (exp(beta)+1e-9)   (tables from pack_snake)
 // which is one multiply less per element and has a packed two-lane form (snake2) of FMUL2 / FADD2 / FFMA2.
@@ -65,6 +67,15 @@ __device__ __forceinline__ void epilogue16(const GemmParams& p, float (&v)[16], 
   if (p.act == ACT_GELU) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+  }
+  if (p.act == ACT_ELU_SPLIT) {
+    const long long o = (long long)b * p.out_batch_stride + (long long)row * p.out_row_stride + n;
+    float lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
+    store16<T>(reinterpret_cast<T*>(p.out_raw) + o, v);
+    store16<T>(reinterpret_cast<T*>(p.out_snake) + o, lo);
+    return;
   }
   if (p.scale) {
     float t[16]; load16f(p.scale + c0, t);

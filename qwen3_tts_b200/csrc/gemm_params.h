@@ -23,7 +23,9 @@
 
 namespace q3 {
 
-enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3 };
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3, ACT_ELU_SPLIT = 4 };
+// ACT_ELU_SPLIT (encode path): v = ELU(acc + bias) leaves as an fp16 pair, out_raw <- hi = fp16(v), out_snake <- lo = fp16(v - hi): the
+// [hi | lo] operand row of the next split-precision GEMM (out_snake = out_raw + n_total, out_row_stride = 2 * n_total).
 // ACT_TAIL: accumulator column 0 + bias[0], clamp(-1, 1), stored as fp32 to out_f32[b*out_batch_stride + row - tail_skip]
 // for row >= tail_skip (the 96 -> 1 output conv + clamp, reference modeling :862, :883; skip = chunk left context).
 

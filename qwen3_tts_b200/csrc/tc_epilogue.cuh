@@ -158,6 +158,10 @@ struct EpiWarp {
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
     }
+    if (p.act == ACT_ELU_SPLIT) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = elu_fast(v[i]);
+    }
     if (p.scale) {
       float t[16]; load16f(p.scale + c0, t);
 #pragma unroll
@@ -169,6 +173,11 @@ struct EpiWarp {
     }
   }
   __device__ __forceinline__ void snake_unit(float (&v)[16], int c0) {
+    if (p.act == ACT_ELU_SPLIT) {  // second tensor = the low half of the fp16 pair (gemm_params.h)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] -= Elem<T>::to_f(Elem<T>::from_f(v[i]));
+      return;
+    }
     float sa[16], sib[16];
     load16f(p.snake_a + c0, sa);
     load16f(p.snake_ib + c0, sib);
