@@ -216,7 +216,8 @@ int64_t q3tts_launch_count(q3tts_handle* h);
  * q3tts_get_profile synchronises the device, returns the number of ops recorded since the last read (fill at most max_ops
  * entries) and clears the profile.  types[i] = kernel: 0 RVQ gather-sum, 1 conv_gemm_tc_kernel (1-tap GEMMs), 2 RMSNorm,
  * 3 attention, 4 dwconv + LayerNorm, 5 output conv, 6 unit_kernel (fused residual unit), 7 ws_conv_kernel, 8 slab_conv_kernel
- * (multi-tap convs), 9 streaming attention, 10 stream state copies, 11 fp32 -> [hi | lo] split; flops[i] = ALGORITHMIC 2 * MACs
+ * (multi-tap convs), 9 streaming attention, 10 stream state copies, 11 fp32 -> [hi | lo] split; encode path: 12 first conv, 13 activation +
+ * split pass, 14 LayerNorm, 15 fp32 attention, 16 latents tap, 17 column split, 18 argmin + residual update; flops[i] = ALGORITHMIC 2 * MACs
  * (the extra MMAs of split-precision operands are not counted), bytes[i] = minimum HBM bytes (operands and outputs once);
  * dims (optional, 4 per op) = rows over all batch items, N, input channels, taps for GEMM ops. */
 int q3tts_set_profile(q3tts_handle* h, int on);
