@@ -7,6 +7,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from qwen3_tts_b200 import _capi
 
 _capi.set_library_path(sys.argv[1])
+import ctypes
+_probe = ctypes.CDLL(sys.argv[1])
+for _n in list(_capi.EXPORTS) + list(_capi.DEBUG_EXPORTS):   # an older build under test may lack the newest entry points
+    if not hasattr(_probe, _n):
+        _capi.EXPORTS.pop(_n, None); _capi.DEBUG_EXPORTS.pop(_n, None)
 import torch
 
 from qwen3_tts_b200 import synthetic_model
