@@ -387,9 +387,7 @@ class Qwen3TTSTokenizerV2Model:
         lat = torch.empty((B, d.config.codebook_dim, F), dtype=torch.float32, device=d.device) if return_latents else None
         rc = d._lib.q3tts_encode(d._h, wav.data_ptr(), B, T, T, codes.data_ptr(), lat.data_ptr() if return_latents else None, _stream_ptr(d.device))
         _capi.check(d._h, rc, "encode")
-        if padding_mask is None:
-            padding_mask = torch.ones((B, T), dtype=torch.long)
-        n = padding_mask.to("cpu").sum(dim=-1).tolist()
+        n = [T] * B if padding_mask is None else padding_mask.sum(dim=-1).tolist()   # no mask: every sample is real
         rate = self.encode_downsample_rate
         audio_codes = [codes[b, :self.encoder_valid_num_quantizers, :-(-int(n[b]) // rate)].transpose(0, 1) for b in range(B)]
         if return_latents:

@@ -130,7 +130,7 @@ def _gpu_worker(rank: int, device: str, model_spec: dict, jobs, results):
             tok = Qwen3TTSTokenizer.from_pretrained(model_spec["path"], device_map=device, dtype=model_spec.get("dtype"))
         else:
             model = synthetic_model(seed=model_spec.get("seed", 0), device=device, compute_mode=model_spec.get("compute_mode", "fp16"),
-                                    state_dict=model_spec.get("state_dict"))
+                                    state_dict=model_spec.get("state_dict"), with_encoder=bool(model_spec.get("with_encoder")))
             tok = Qwen3TTSTokenizer.from_model(model)
         if model_spec.get("reserve_frames"):
             tok.model.decoder.reserve(int(model_spec["reserve_frames"]))
@@ -144,6 +144,10 @@ def _gpu_worker(rank: int, device: str, model_spec: dict, jobs, results):
             return
         job_id, indices, codes, pcm16 = job
         try:
+            if pcm16 == "encode":                                 # `codes` holds the batch's waveforms (1-D float32 tensors)
+                out = tok.model.encode_host([w.numpy() for w in codes])
+                results.put(("done", rank, (job_id, [(i, torch.from_numpy(c)) for i, c in zip(indices, out)])))
+                continue
             payload = [{"audio_codes": c} for c in codes]
             wavs, _sr = tok.decode_pcm16(payload) if pcm16 else tok.decode(payload)
             # waveforms travel back as CPU tensors: torch.multiprocessing moves their storage to shared memory (no pickling of samples)
@@ -198,8 +202,26 @@ class ShardedDecoder:
         batches = global_batches(lengths, world, self.max_frames)  # global length buckets, most expensive first
         for b in batches:
             self._jobs.put((job_id, b, [codes[i].cpu() for i in b], pcm16))
-        out = [None] * len(codes)
-        pending = len(batches)
+        return self._gather(job_id, len(codes), len(batches)), 24000
+
+    def encode_sharded(self, wavs, max_samples: int = 4 << 20):
+        """wavs: utterances as 1-D float32 waveforms at 24 kHz.  Returns the list of int64 code arrays [frames_i, 16] in the input
+        order.  Same dispatch as decode_sharded: global length buckets (an item is padded to its batch's longest waveform, and - as in
+        the reference, modeling :979-983 - its last partial frame sees that padding), most expensive first, pulled by whichever
+        GPU is free.  The workers need the encoder weights (model_spec {"with_encoder": True} or a checkpoint path)."""
+        import numpy as np
+        import torch
+        items = [w if isinstance(w, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(w, dtype=np.float32)) for w in wavs]
+        lengths = [-(-int(w.shape[0]) // 1920) for w in items]                   # bucket by code frames, like the decode side
+        job_id = self._next_job
+        self._next_job += 1
+        batches = global_batches(lengths, len(self.devices), max(1, int(max_samples) // 1920))
+        for b in batches:
+            self._jobs.put((job_id, b, [items[i].cpu() for i in b], "encode"))
+        return self._gather(job_id, len(items), len(batches))
+
+    def _gather(self, job_id: int, n_items: int, pending: int):
+        out = [None] * n_items
         while pending:
             kind, rank, payload = self._results.get(timeout=3600)
             if kind == "error":
@@ -211,7 +233,7 @@ class ShardedDecoder:
             for i, w in items:
                 out[i] = w.numpy()
             pending -= 1
-        return out, 24000
+        return out
 
     def _drain(self):
         """Drop the batches of a failed job that no worker has taken yet."""

@@ -30,3 +30,25 @@ def test_sharded_decoder_matches_direct_decode(gpu_model, cfg):
         assert wavs[i].dtype == np.float32 and wavs[i].shape == w.shape
         np.testing.assert_array_equal(wavs[i], w)
     assert pcm[0].dtype == np.int16 and pcm[0].shape[0] > 0
+
+
+def test_sharded_encode_matches_direct_encode():
+    """encode_sharded on one / two GPUs returns, in input order, what model.encode_host returns for the same global buckets."""
+    from qwen3_tts_b200 import ShardedDecoder, synthetic_model
+    from qwen3_tts_b200.sharding import global_batches
+    from qwen3_tts_b200.synthetic import make_audio
+    ndev = min(2, torch.cuda.device_count())
+    lengths = [30000, 4000, 52000, 24000, 9000, 52000, 1]
+    wav = make_audio(len(lengths), max(lengths), seed=21, lengths=lengths)
+    wavs = [wav[b, :n].numpy() for b, n in enumerate(lengths)]
+    with ShardedDecoder([f"cuda:{i}" for i in range(ndev)], {"seed": 0, "with_encoder": True}) as sd:
+        got = sd.encode_sharded(wavs, max_samples=120000)
+    model = synthetic_model(seed=0, device="cuda:0", with_encoder=True)
+    frames = [-(-n // 1920) for n in lengths]
+    batches = global_batches(frames, ndev, 120000 // 1920)
+    assert sorted(i for b in batches for i in b) == list(range(len(lengths)))
+    for b in batches:
+        want = model.encode_host([wavs[i] for i in b])
+        for i, w in zip(b, want):
+            assert got[i].dtype == np.int64 and got[i].shape == (frames[i], 16)
+            np.testing.assert_array_equal(got[i], w)

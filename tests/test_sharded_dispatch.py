@@ -17,6 +17,10 @@ def _fake_worker(rank, device, spec, jobs, results):
         if spec.get("fail_on") is not None and len(indices) and spec["fail_on"] in indices:
             results.put(("error", rank, "boom"))
             continue
+        if pcm16 == "encode":   # "codes" of a waveform: one row per 1920 samples holding the frame's first sample, tagged with the rank
+            items = [(i, torch.stack([w[::1920].to(torch.float32) + 1000.0 * rank] * 16, dim=1).to(torch.int64)) for i, w in zip(indices, codes)]
+            results.put(("done", rank, (job_id, items)))
+            continue
         # "waveform" of an utterance: its first codebook column repeated `up` times, tagged with the rank that decoded it
         items = [(i, torch.repeat_interleave(c[:, 0].to(torch.float32), spec["up"]) + 1000.0 * rank) for i, c in zip(indices, codes)]
         results.put(("done", rank, (job_id, items)))
@@ -84,3 +88,18 @@ def test_shard_batches_padding_is_independent_of_world_size():
     old8 = plan_batches(lengths, 8, 64 * 375)
     old_waste = sum(len(b) * max(lengths[i] for i in b) for r in old8 for b in r) / real - 1.0
     assert old_waste > waste[8]
+
+
+def test_dispatcher_encode_side_gathers_in_input_order():
+    """encode_sharded: the same pull-based dispatch for waveforms -> codes (bucketed by code frames, results in input order)."""
+    rng = np.random.default_rng(5)
+    lengths = [int(v) for v in rng.integers(1, 30000, 17)]
+    wavs = [np.arange(n, dtype=np.float32) % 97 for n in lengths]
+    with ShardedDecoder(["cpu:0", "cpu:1"], {"up": 1}, worker=_fake_worker) as sd:
+        codes = sd.encode_sharded(wavs, max_samples=60000)
+        assert len(codes) == len(wavs)
+        for c, w in zip(codes, wavs):
+            assert c.dtype == np.int64 and c.shape == (-(-len(w) // 1920), 16)
+            np.testing.assert_array_equal(c[:, 0] % 1000, w[::1920].astype(np.int64))
+        wav2, sr = sd.decode_sharded([torch.ones((4, 16), dtype=torch.long)])          # the pool still serves decode jobs
+        assert sr == 24000 and wav2[0].shape == (4,)
