@@ -106,32 +106,39 @@ cudaError_t enc_conv0(const float* wav, long long wav_bs, const float* w, const 
 template <int ACT>
 __global__ void __launch_bounds__(256) k_act_split(const float* __restrict__ in, __half* __restrict__ out, int B, int L, int C, int r, int lead,
                                                     int replicate, int cg, int rows_per_block) {
-  // a block owns rows_per_block consecutive super-rows; inside a super-row everything is 32-bit arithmetic
+  // block (tx, ty): tx walks the float4 groups of a super-row, ty the block's rows_per_block consecutive super-rows.  Every division
+  // sits outside the row loop (this pass was bound by its index arithmetic): a thread's column decomposition is fixed, its
+  // (item, row) pair is advanced incrementally.  32-bit arithmetic: B * ns < 2^31 is checked by the launcher.
   const int ns = lead + (L + r - 1) / r;
-  const int w4 = (r * C) >> 2;                 // float4 groups per super-row
-  const long long nrows = (long long)B * ns;
-  const long long row0 = (long long)blockIdx.x * rows_per_block;
-  for (int i = threadIdx.x; i < rows_per_block * w4; i += blockDim.x) {
-    const int lr = i / w4, j4 = i - lr * w4;
-    const long long srow = row0 + lr;
-    if (srow >= nrows) break;
-    const long long b = srow / ns;
-    const int sr = (int)(srow - b * ns);
-    const int j = j4 << 2, p = j / C;
-    int row = (sr - lead) * r + p;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    bool valid = row >= 0 && row < L;
-    if (!valid && replicate) { row = row < 0 ? 0 : L - 1; valid = true; }
-    if (valid) {
-      v = __ldcs(reinterpret_cast<const float4*>(in + ((b * L + row) * (long long)C + (j - p * C))));
-      v.x = enc_act<ACT>(v.x); v.y = enc_act<ACT>(v.y); v.z = enc_act<ACT>(v.z); v.w = enc_act<ACT>(v.w);
+  const int rc = r * C, w4 = rc >> 2;
+  const int nrows = B * ns;
+  const int row_end = min(nrows, ((int)blockIdx.x + 1) * rows_per_block);
+  const bool one_group = cg >= rc;
+  for (int j4 = threadIdx.x; j4 < w4; j4 += blockDim.x) {
+    const int j = j4 << 2;
+    const int p = r == 1 ? 0 : j / C;
+    const int c = j - p * C;
+    const int g = one_group ? 0 : j / cg;
+    const int ocol = g * 2 * cg + (j - g * cg);
+    int srow = blockIdx.x * rows_per_block + threadIdx.y;
+    int b = srow / ns, sr = srow - b * ns;
+    for (; srow < row_end; srow += blockDim.y) {
+      int row = (sr - lead) * r + p;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      bool valid = row >= 0 && row < L;
+      if (!valid && replicate) { row = row < 0 ? 0 : L - 1; valid = true; }
+      if (valid) {
+        v = __ldcs(reinterpret_cast<const float4*>(in + (((long long)b * L + row) * C + c)));
+        v.x = enc_act<ACT>(v.x); v.y = enc_act<ACT>(v.y); v.z = enc_act<ACT>(v.z); v.w = enc_act<ACT>(v.w);
+      }
+      uint2 h, l;
+      split4(v, h, l);
+      __half* o = out + (long long)srow * (2 * rc) + ocol;
+      *reinterpret_cast<uint2*>(o) = h;
+      *reinterpret_cast<uint2*>(o + cg) = l;
+      sr += blockDim.y;
+      while (sr >= ns) { sr -= ns; ++b; }
     }
-    uint2 h, l;
-    split4(v, h, l);
-    const int g = j / cg;
-    __half* o = out + srow * (2ll * r * C) + g * 2 * cg + (j - g * cg);
-    *reinterpret_cast<uint2*>(o) = h;
-    *reinterpret_cast<uint2*>(o + cg) = l;
   }
 }
 cudaError_t enc_act_split(const float* in, void* out, int B, int L, int C, int act, int r, int lead, int replicate, int cg, cudaStream_t s) {
@@ -139,14 +146,17 @@ cudaError_t enc_act_split(const float* in, void* out, int B, int L, int C, int a
   if ((r * C) % cg || cg % 4 || C % 4) return cudaErrorInvalidValue;
   const long long nrows = (long long)B * (lead + (L + r - 1) / r);
   const int w4 = (r * C) / 4;
-  int rpb = 2048 / w4;                         // ~8 float4 groups per thread
-  if (rpb < 1) rpb = 1;
+  int tx = 1;
+  while (tx < w4 && tx < 256) tx <<= 1;        // power of two >= min(w4, 256): idle lanes only when w4 is not one (r = 5, 6)
+  const int ty = 256 / tx;
+  const int rpb = ty * 8;                      // eight rows per thread
   const long long blocks = (nrows + rpb - 1) / rpb;
-  if (blocks > 0x7fffffffll) return cudaErrorInvalidValue;
+  if (blocks > 0x7fffffffll || nrows > 0x7fffffffll) return cudaErrorInvalidValue;
+  const dim3 block(tx, ty);
   const unsigned g = (unsigned)(blocks < 1 ? 1 : blocks);
-  if (act == 1) k_act_split<1><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
-  else if (act == 2) k_act_split<2><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
-  else k_act_split<0><<<g, 256, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
+  if (act == 1) k_act_split<1><<<g, block, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
+  else if (act == 2) k_act_split<2><<<g, block, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
+  else k_act_split<0><<<g, block, 0, s>>>(in, (__half*)out, B, L, C, r, lead, replicate, cg, rpb);
   return cudaGetLastError();
 }
 
