@@ -148,7 +148,10 @@ int q3tts_rvq_encode(q3tts_handle* h, const float* latents, int B, int T, int64_
  * are read from the tensor shapes; what shapes cannot tell comes from the q3tts_encoder_config struct, whose defaults are MimiConfig()'s.
  * Arithmetic: every GEMM runs on the tensor cores with BOTH operands carried as fp16 hi + lo pairs (3 MMAs per product, fp32
  * accumulate: ~22 bits per operand) whatever the handle's compute mode; activations stay fp32 in HBM.  The output is integer: the
- * bar is identical indices wherever the float64 oracle's two best codes are not tied to fp32 rounding (tests/test_gpu_encode.py). */
+ * bar is identical indices wherever the float64 oracle's two best codes are not tied to fp32 rounding (tests/test_gpu_encode.py).
+ * Memory: the encode workspace (~1 KB per sample of a launch; batches above 16 M samples run as several launches) is allocated by the
+ * first call that needs it and kept; q3tts_reserve() does not cover it.  Range: operands are fp16 pairs, so |activation| must stay
+ * below 65504 inside the encoder (true by a wide margin for audio in [-1, 1] through LayerNorm'd / ELU'd stages; not checked). */
 typedef struct {
   int32_t num_attention_heads;     /* 8 (head_dim must be 64) */
   int32_t sliding_window;          /* 250 */

@@ -180,7 +180,7 @@ struct EncBuilder {
     plan->ops.emplace_back();
     Op& op = plan->ops.back();
     op.type = OP_ENC_ACT; op.in = in; op.out = out; op.B = B; op.L = L; op.C = C; op.aux0 = act_id; op.aux1 = r; op.split = lead | (replicate << 8);
-    op.probe_ld = next.cg;
+    op.kgroup = next.cg;
     return op;
   }
 };
@@ -215,7 +215,7 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     const bool fused = S.c3.cg == 0 && S.c1.cg == 0 && (C / 2) % 32 == 0;   // ELU(conv_k3) leaves the epilogue as the k1 conv's operand
     float* Hh = fused ? nullptr : (float*)b.alloc((size_t)B * L * (C / 2) * 4);
     void* A2 = b.alloc((size_t)B * L * C * 2);
-    if (si == 0) { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_CONV0; op.out = X; op.w0 = (const float*)A1; op.B = B; op.L = L; op.C = C; }
+    if (si == 0) { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_CONV0; op.out = X; op.out2 = A1; op.B = B; op.L = L; op.C = C; }
     else b.act(S.c3, X, A1, B, L, C, 1);
     if (fused) {
       b.gemm(S.c3, A1, B, L, L, nullptr, nullptr, nullptr, A2);
@@ -321,8 +321,8 @@ int run(Engine* e, Plan* plan, const float* wav, long long wav_stride, long long
     if (e->profile) cudaEventRecord(e->prof_events[2 * pi], s);
     if (op.type == OP_ENC_RVQ) searching = true;
     switch (op.type) {
-      case OP_ENC_CONV0: err = enc_conv0(wav, wav_stride, e->enc_conv0_w, e->enc_conv0_b, (float*)op.out, (void*)op.w0, op.B, op.L, op.C, s); break;
-      case OP_ENC_ACT: err = enc_act_split((const float*)op.in, op.out, op.B, op.L, op.C, op.aux0, op.aux1, op.split & 0xff, op.split >> 8, op.probe_ld, s); break;
+      case OP_ENC_CONV0: err = enc_conv0(wav, wav_stride, e->enc_conv0_w, e->enc_conv0_b, (float*)op.out, op.out2, op.B, op.L, op.C, s); break;
+      case OP_ENC_ACT: err = enc_act_split((const float*)op.in, op.out, op.B, op.L, op.C, op.aux0, op.aux1, op.split & 0xff, op.split >> 8, op.kgroup, s); break;
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_ENC_LN: err = enc_layernorm_split((const float*)op.in, op.w0, op.w1, op.out, op.B, op.C, e->enc_cfg.norm_eps, s); break;
       case OP_ENC_ATTN:

@@ -57,7 +57,7 @@ struct EncLayerW {
 
 enum OpType { OP_RVQ = 0, OP_GEMM, OP_RMSNORM, OP_ATTN, OP_DWLN, OP_TAIL, OP_UNIT, OP_STREAM_ATTN, OP_STATE_LOAD, OP_STATE_SAVE, OP_POS_ADVANCE,
               OP_SPLIT /* fp32 [B][L][C] -> 16-bit [hi | lo] rows: in, out, B, L, C, sp_in_bs / sp_out_bs */,
-              // encode path (encode_plan.cu): first conv; act + split (aux0 = act, aux1 = r, split = lead rows | replicate << 8, probe_ld = K group);
+              // encode path (encode_plan.cu): first conv; act + split (aux0 = act, aux1 = r, split = lead rows | replicate << 8, kgroup);
               // LayerNorm -> [hi | lo]; fp32 attention; RVQ search (aux0 = 1: codes [B][T][Q])
               OP_ENC_CONV0, OP_ENC_ACT, OP_ENC_LN, OP_ENC_ATTN, OP_ENC_RVQ,
               // RVQ search on the tensor cores: split a column range of the projected latents (aux0 = first column, aux1 = row pitch);
@@ -77,6 +77,8 @@ struct Op {
   int split = 0;           // OP_RVQ / OP_RMSNORM: write [hi | lo] rows;  OP_DWLN: the input tensor is fp32
   long long sp_in_bs = 0, sp_out_bs = 0;  // OP_SPLIT: elements between batch items of in / out
   int probe_ld = 0;        // row pitch of the probe buffer in elements (0 = probe_C)
+  void* out2 = nullptr;    // encode path, OP_ENC_CONV0: second output (ELU(x) as [hi | lo] rows)
+  int kgroup = 0;          // encode path, OP_ENC_ACT: K group size of the layer that reads the result (0 = one group)
   int aux0 = 0, aux1 = 0;  // streaming: RVQ output batch stride in rows / dwconv (input batch stride in rows, history rows) / attention layer
   // probe: the buffer that holds an oracle tap once this op has run
   std::string tag;
