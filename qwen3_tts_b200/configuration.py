@@ -106,7 +106,9 @@ class Qwen3TTSTokenizerV2Config:
             self.decoder_config = decoder_config
         else:
             self.decoder_config = Qwen3TTSTokenizerV2DecoderConfig(**(decoder_config or {}))
-        self.encoder_config = encoder_config or {}  # encode path is out of scope; kept opaque
+        # MimiConfig fields as a plain dict (the reference builds transformers' MimiConfig from it, configuration :155-158); the encode
+        # path reads what tensor shapes cannot tell from here: num_attention_heads, sliding_window, max_position_embeddings, rope_theta, norm_eps
+        self.encoder_config = encoder_config or {}
         self.encoder_valid_num_quantizers = int(encoder_valid_num_quantizers)
         self.input_sample_rate = int(input_sample_rate)
         self.output_sample_rate = int(output_sample_rate)

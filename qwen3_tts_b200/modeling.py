@@ -283,8 +283,21 @@ class Qwen3TTSTokenizerV2Model:
         self.decode_upsample_rate = config.decode_upsample_rate
         self.encode_downsample_rate = config.encode_downsample_rate
         self.decoder = Qwen3TTSTokenizerV2Decoder(config.decoder_config, device=device, compute_mode=compute_mode)
+        self._apply_encoder_config(config.encoder_config)
         self.device = self.decoder.device
         self.dtype = torch.float32
+
+    def _apply_encoder_config(self, enc: Optional[dict]):
+        """Hands the encoder's non-shape hyper-parameters (MimiConfig fields; defaults = MimiConfig()) to the handle before the weights
+        are finalised.  Shapes (filters, ratios, layer count, widths) are read from the tensors themselves."""
+        enc = dict(enc or {})
+        rope = enc.get("rope_parameters") or {}
+        s = _capi.q3tts_encoder_config(
+            num_attention_heads=int(enc.get("num_attention_heads", 8)), sliding_window=int(enc.get("sliding_window", 250)),
+            max_position_embeddings=int(enc.get("max_position_embeddings", 8000)),
+            rope_theta=float(rope.get("rope_theta", enc.get("rope_theta", 10000.0))), norm_eps=float(enc.get("norm_eps", 1e-5)))
+        d = self.decoder
+        _capi.check(d._h, d._lib.q3tts_set_encoder_config(d._h, C.byref(s)), "set_encoder_config")
 
     # ---- getters (modeling :945-958)
     def get_model_type(self):

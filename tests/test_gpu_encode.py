@@ -116,6 +116,26 @@ def test_encode_edge_lengths_match_oracle(enc_model, samples):
     _check_codes(codes[0].cpu().numpy(), want[0], margin[0], f"{samples} samples")
 
 
+def test_encoder_config_reaches_the_kernels(sd):
+    """encoder_config of the model config (MimiConfig fields) is what the encode path runs with: a 60-frame attention window must
+    reproduce the oracle run with that window, and differ from the default 250-frame one on an item longer than the window."""
+    from qwen3_tts_b200 import Qwen3TTSTokenizerV2Config, Qwen3TTSTokenizerV2Model
+    esd = make_encoder_state_dict(seed=0)
+    cfg = Qwen3TTSTokenizerV2Config(encoder_config={"sliding_window": 60})
+    model = Qwen3TTSTokenizerV2Model(cfg, device="cuda:0")
+    model.decoder.load_state_dict({**sd, **esd})
+    wav = make_audio(1, 24000 * 6, seed=9)
+    _codes, lat = model.encode(wav, return_latents=True)
+    with torch.inference_mode():
+        x = XO.seanet_encoder(esd, wav.double().unsqueeze(1)).transpose(1, 2)
+        w = esd["encoder.downsample.conv.weight"].double()
+        want60 = XO.causal_conv1d(XO.encoder_transformer(esd, x, sliding_window=60).transpose(1, 2), w, None, stride=2, pad_mode="replicate").numpy()
+        want250 = XO.causal_conv1d(XO.encoder_transformer(esd, x, sliding_window=250).transpose(1, 2), w, None, stride=2, pad_mode="replicate").numpy()
+    got = lat.cpu().numpy()
+    scale = np.abs(want60).max()
+    assert np.abs(got - want60).max() <= LATENT_TOL * scale and np.abs(got - want250).max() > 1e-3 * scale
+
+
 def test_encode_needs_encoder_weights(gpu_model):
     with pytest.raises(RuntimeError, match="not loaded"):
         gpu_model.encode(torch.zeros(1, 4800))
