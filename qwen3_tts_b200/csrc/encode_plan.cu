@@ -468,8 +468,9 @@ static int encode_batched(Engine* e, const float* wav, int B, long long T, long 
   long long fr = T;
   for (const EncStageW& S : e->enc_stages) fr = (fr + S.r - 1) / S.r;
   if (fr > e->enc_cfg.max_position_embeddings) return e->fail(Q3TTS_BAD_SHAPE, "encode: item longer than max_position_embeddings frames at 25 Hz");
-  int per = (int)(e->enc_max_samples / T);
-  if (per < 1) per = 1;
+  long long per_ll = e->enc_max_samples / T;
+  if (per_ll > 32768) per_ll = 32768;   // the first conv's grid carries the item index in its y dimension
+  int per = per_ll < 1 ? 1 : (int)per_ll;
   const int Q = e->cfg.num_quantizers;
   for (int b0 = 0; b0 < B; b0 += per) {
     const int nb = B - b0 < per ? B - b0 : per;

@@ -136,6 +136,21 @@ def test_encoder_config_reaches_the_kernels(sd):
     assert np.abs(got - want60).max() <= LATENT_TOL * scale and np.abs(got - want250).max() > 1e-3 * scale
 
 
+def test_encode_is_independent_of_the_decode_compute_mode(sd, enc_model):
+    """The encoder always multiplies fp16 hi + lo pairs, whatever operand type the handle's DECODE path was built with: a bf16-mode
+    model must return the very same codes and latents."""
+    from qwen3_tts_b200 import synthetic_model
+    wav = make_audio(2, 30000, seed=4)
+    a_codes, a_lat = enc_model.encode(wav, return_latents=True)
+    other = synthetic_model(state_dict=sd, device="cuda:0", compute_mode="bf16", with_encoder=True)
+    b_codes, b_lat = other.encode(wav, return_latents=True)
+    assert torch.equal(a_lat, b_lat) and all(torch.equal(x, y) for x, y in zip(a_codes, b_codes))
+    many = make_audio(300, 1921, seed=5)                       # many short items in one call: 2 frames each
+    out = enc_model.encode(many).audio_codes
+    assert len(out) == 300 and all(c.shape == (2, 16) for c in out)
+    assert torch.equal(out[7], enc_model.encode(many[7:8]).audio_codes[0])
+
+
 def test_encode_needs_encoder_weights(gpu_model):
     with pytest.raises(RuntimeError, match="not loaded"):
         gpu_model.encode(torch.zeros(1, 4800))
