@@ -145,7 +145,7 @@ conv_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (!PAIR && p.pack_mode)
           for (int q = 0; q < 4; ++q) gemm_chunk_coords(p, b, q, cr[q], cb[q]);
         for (int kb = 0; kb < kblocks; ++kb) {
-          const int acol = p.a_cols ? (kb * KB) % p.a_cols : kb * KB;  // split-precision operands: K blocks wrap around the A tensor
+          const int acol = gemm_a_col(p, kb * KB);  // split-precision operands: K blocks wrap around the A tensor (per K group)
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
             uint8_t* sa = smem + (size_t)s * stage_bytes;
@@ -258,7 +258,7 @@ ws_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_wait_backoff(&bars->empty[s], ph ^ 1);
         mbar_expect_tx(&bars->full[s], slab_bytes);
         for (int kb = 0; kb < nkb; ++kb)
-          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], p.a_cols ? (kb * KB) % p.a_cols : kb * KB,
+          tma_load_3d(slabs + (size_t)s * slab_bytes + (size_t)kb * ssub, &tmA, &bars->full[s], gemm_a_col(p, kb * KB),
                       mt * BM + p.a_row0 - halo, b);
         if (++s == nslabs) { s = 0; ph ^= 1; }
       }
@@ -373,7 +373,7 @@ slab_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait_backoff(&bars->sempty[ss], sph ^ 1);
           if (rank == 0) mbar_expect_tx(&bars->sfull[ss], ssub * NCTA);
-          load(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], p.a_cols ? (kb * KB) % p.a_cols : kb * KB, mt * TM + rank * BM + p.a_row0 - slab_lo, b);
+          load(slabs + (size_t)ss * ssub, &tmA, &bars->sfull[ss], gemm_a_col(p, kb * KB), mt * TM + rank * BM + p.a_row0 - slab_lo, b);
           if (++ss == nslabs) { ss = 0; sph ^= 1; }
           for (int tap = 0; tap < p.ntaps; ++tap) {
             mbar_wait_backoff(&bars->empty[s], ph ^ 1);
@@ -464,7 +464,7 @@ __global__ void conv_gemm_simt_kernel(const GemmParams p) {
       const T* a = A + (long long)b * (p.a_batch_stride ? p.a_batch_stride : (long long)p.rows * ars) + (long long)r * ars;
       const T* w = W + ((long long)tap * p.n_total + n) * wrs;
       for (int k = 0; k < p.cin; ++k) {
-        const float av = Elem<T>::to_f(a[k % aw]);
+        const float av = Elem<T>::to_f(a[gemm_a_col(p, k)]);
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc[i] = fmaf(av, Elem<T>::to_f(w[(long long)i * wrs + k]), acc[i]);
       }
@@ -650,8 +650,17 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   bool has_res = false, has_raw = false, has_snake = false, has_f32 = false;
   if (p.act != ACT_TAIL) {
     if (p.res) { has_res = true; rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, br, bb); }
-    if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, br, bb); }
-    if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, br, bb); }
+    if (p.act == ACT_ELU_SPLIT) {
+      // the two halves of the fp16 pair tensor (its own pitches); 16-column boxes inside the fp32 epilogue flow, 32 in the 16-bit one
+      const uint64_t prs = p.pair_row_stride ? (uint64_t)p.pair_row_stride : rs, pbs = p.pair_batch_stride ? (uint64_t)p.pair_batch_stride : bs;
+      const uint32_t pbox = epi_pair16(p) ? 16 : 32;
+      has_raw = has_snake = true;
+      rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, prs, pbs, pbox, br, bb);
+      rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, prs, pbs, pbox, br, bb);
+    } else {
+      if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, br, bb); }
+      if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, br, bb); }
+    }
     if (p.out_f32) { has_f32 = true; rc |= make_tmap_3d_strided(&op->tmF32, p.out_f32, 2, width, rows, nb, rs, bs, 16, br, bb); }
   }
   plan_variant(op, allow);

@@ -97,6 +97,11 @@ struct EncFin {
     w.tap_off[0] = first_off; w.tap_off[1] = first_off + 1;
     w.bias = b ? b->d : nullptr;
     w.kb = kblock(r * c); w.cg = group_size(r * c, 2, w.kb);
+    if (first_off < 0 && 2 * 3 * c <= kMaxChain && c % w.kb == 0) {
+      // one K group per input row of the super-row: the operand is then simply every input row as its own [hi | lo] pair - what a
+      // producing GEMM's epilogue can write directly (ACT_ELU_SPLIT) - and a launch walks as many groups as the chain limit allows
+      w.cg = c; w.gl = kMaxChain / (2 * 3 * c);
+    }
     w.w = alloc((size_t)2 * cout * r * c * 2 * 3);
     if (!rc) check(pack_strided_conv_weight(t->d, w.w, cout, c, r, false, s, 3, w.cg), "pack_strided_conv_weight");
     finish(w, r * c);
@@ -140,41 +145,44 @@ struct EncBuilder {
     return p;
   }
   // A [batches][rows][2 kreal] fp16 -> fp32 out [batches][rows_valid][n] (+ bias, * scale, + fp32 residual).  A layer with K groups
-  // (ConvW::cg) is one launch per group: group g reads A columns [2 g cg, 2 (g + 1) cg) and weight columns [3 g cg, 3 (g + 1) cg) of
-  // the full-pitch rows, and from the second group on adds to what the earlier groups stored.
-  // elu_split_out (single-group layers only): instead of fp32, ELU(acc + bias) goes out as the fp16 [hi | lo] rows of the next layer
+  // (ConvW::cg) runs as one launch per `gl` groups: a launch reads A columns [2 g0 cg, 2 (g0 + ng) cg) and weight columns
+  // [3 g0 cg, 3 (g0 + ng) cg) of the full-pitch rows, and from the second launch on adds to what the earlier ones stored.
+  // pair_out: the (last) launch also / instead writes ELU(result) as fp16 [hi | lo] rows [batches][rows_valid][2 n] (ACT_ELU_SPLIT);
+  // `out` may then be null when the fp32 result itself has no reader (single-launch layers only).
   void gemm(const ConvW& w, const void* in, int batches, int rows, int rows_valid, float* out, const float* res = nullptr, const float* scale = nullptr,
-            void* elu_split_out = nullptr) {
+            void* pair_out = nullptr) {
     const int kreal = w.a_cols / 2;
-    const int cg = w.cg > 0 ? w.cg : kreal, G = kreal / cg;
-    for (int g = 0; g < G; ++g) {
+    const int cg = w.cg > 0 ? w.cg : kreal, G = kreal / cg, gl = w.gl > 0 ? w.gl : 1;
+    for (int g0 = 0; g0 < G; g0 += gl) {
+      const int ng = G - g0 < gl ? G - g0 : gl;
+      const bool last = g0 + ng >= G;
       plan->ops.emplace_back();
       Op& op = plan->ops.back();
       op.type = OP_GEMM;
       GemmParams& p = op.g.p;
       memset(&p, 0, sizeof(p));
       p.batches = batches; p.rows = rows; p.rows_valid = rows_valid;
-      p.cin = 3 * cg; p.ntaps = w.taps;
+      p.cin = 3 * cg * ng; p.ntaps = w.taps;
       for (int i = 0; i < 8; ++i) p.tap_off[i] = w.tap_off[i];
       p.n_total = w.n_total; p.bn = w.bn; p.kb = w.kb; p.ncol_mod = w.ncol_mod;
-      p.bias = g == 0 ? w.bias : nullptr; p.bf16 = 0;   // the encoder's operands are always fp16 pairs
-      p.a_cols = 2 * cg; p.k_mult = 3;
+      p.bias = g0 == 0 ? w.bias : nullptr; p.bf16 = 0;   // the encoder's operands are always fp16 pairs
+      p.a_cols = 2 * cg * ng; p.k_mult = 3; p.kgroup = ng > 1 ? cg : 0;
       p.a_row_stride = 2 * kreal; p.w_row_stride = 3 * kreal;
-      p.a_ptr = (const char*)in + (size_t)g * 2 * cg * 2; p.w_ptr = (const char*)w.w + (size_t)g * 3 * cg * 2;
+      p.a_ptr = (const char*)in + (size_t)g0 * 2 * cg * 2; p.w_ptr = (const char*)w.w + (size_t)g0 * 3 * cg * 2;
       p.out_row_stride = w.n_total;
       p.out_batch_stride = (long long)rows_valid * w.n_total;
       p.out_f32 = out; p.scale = scale;
-      const float* r = g == 0 ? res : out;
+      const float* r = g0 == 0 ? res : out;
       if (r) { p.res = r; p.res_f32 = 1; }
-      if (elu_split_out) {
-        p.out_f32 = nullptr; p.act = ACT_ELU_SPLIT;
-        p.out_raw = elu_split_out; p.out_snake = (char*)elu_split_out + (size_t)w.n_total * 2;
-        p.out_row_stride = 2 * w.n_total; p.out_batch_stride = (long long)rows_valid * 2 * w.n_total;
+      if (pair_out && last) {
+        p.act = ACT_ELU_SPLIT;
+        p.out_raw = pair_out; p.out_snake = (char*)pair_out + (size_t)w.n_total * 2;
+        p.pair_row_stride = 2 * w.n_total; p.pair_batch_stride = (long long)rows_valid * 2 * w.n_total;
       }
+      if (!out && (G > gl || !pair_out)) rc = e->fail(Q3TTS_BAD_CONFIG, "encoder plan: a layer without an fp32 output must be a single launch with a pair output");
       op.g.retile = 1;   // few rows (the 25 Hz stages): shrink the N tile until the grid covers the SMs
     }
   }
-  // act(in) fp32 [B][L][C] -> fp16 super-rows (encode_kernels.cu enc_act_split)
   // `next`: the layer that reads the result (its K group size decides the layout)
   Op& act(const ConvW& next, const float* in, void* out, int B, int L, int C, int act_id, int r = 1, int lead = 0, int replicate = 0) {
     plan->ops.emplace_back();
@@ -199,34 +207,57 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     xbytes.push_back((size_t)B * L * C * 4);
     for (const EncStageW& S : e->enc_stages) { L = cdiv(L, S.r); C *= 2; xbytes.push_back((size_t)B * L * C * 4); }
   }
+  // The fp32 main-path tensors X0, X1, ... persist (~460 B per sample in all); a stage's operands live in a scratch region every stage
+  // reuses (~512 B per sample) - except an operand that the PREVIOUS stage's strided conv writes from its epilogue while it still reads
+  // its own scratch: that one is persistent too.
+  const size_t ns_ = e->enc_stages.size();
+  std::vector<char> pre(ns_ + 1, 0);   // pre[s]: stage s gets ELU(X_s) [hi | lo] from its producer's epilogue
+  pre[0] = 1;                          // the first conv writes it
+  for (size_t s = 1; s < ns_; ++s) pre[s] = e->enc_stages[s].c3.cg == 0 ? 1 : 0;
   std::vector<float*> Xs;
-  for (size_t n : xbytes) Xs.push_back((float*)b.alloc(n));
+  std::vector<void*> A1pre(ns_ + 1, nullptr);
+  {
+    int L = T, C = C0;
+    for (size_t s = 0; s <= ns_; ++s) {
+      Xs.push_back((float*)b.alloc(xbytes[s]));
+      if (s < ns_ && s >= 1 && pre[s]) A1pre[s] = b.alloc((size_t)B * L * 2 * C * 2);
+      if (s < ns_) { L = cdiv(L, e->enc_stages[s].r); C *= 2; }
+    }
+  }
   const size_t scratch0 = b.off;
   size_t scratch_max = b.off;
-  // ---- conv k7: wav -> X0 [B][T][C0], and ELU(X0) [hi | lo] for the first ResnetBlock
   int L = T, C = C0;
   float* X = Xs[0];
   size_t si = 0;
   for (const EncStageW& S : e->enc_stages) {
     b.off = scratch0;
     const int r = S.r, Ln = cdiv(L, r);
+    // per-row operand layout of the strided conv (one K group per input row): the k1 conv's epilogue can then write it directly
+    const bool rowwise = S.down.cg == C && S.c1.cg == 0;
     const size_t a1 = (size_t)B * L * 2 * C * 2, a3 = (size_t)B * Ln * 2 * r * C * 2;
-    void* A1 = b.alloc(a1 > a3 ? a1 : a3);                     // ELU(x) [hi | lo]; later the strided conv's super-rows (A1 is dead by then)
+    void* A1 = A1pre[si] ? A1pre[si] : b.alloc(a1);
+    void* A3 = b.alloc(a3);                                      // the strided conv's operand (super-rows of r input rows)
     const bool fused = S.c3.cg == 0 && S.c1.cg == 0 && (C / 2) % 32 == 0;   // ELU(conv_k3) leaves the epilogue as the k1 conv's operand
     float* Hh = fused ? nullptr : (float*)b.alloc((size_t)B * L * (C / 2) * 4);
     void* A2 = b.alloc((size_t)B * L * C * 2);
     if (si == 0) { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_CONV0; op.out = X; op.out2 = A1; op.B = B; op.L = L; op.C = C; }
-    else b.act(S.c3, X, A1, B, L, C, 1);
+    else if (!pre[si]) b.act(S.c3, X, A1, B, L, C, 1);
     if (fused) {
       b.gemm(S.c3, A1, B, L, L, nullptr, nullptr, nullptr, A2);
     } else {
       b.gemm(S.c3, A1, B, L, L, Hh);
       b.act(S.c1, Hh, A2, B, L, C / 2, 1);
     }
-    b.gemm(S.c1, A2, 1, B * L, B * L, X, X);                    // x += conv_k1(...): residual read and written in place, fp32
-    b.act(S.down, X, A1, B, L, C, 1, r);
+    if (rowwise && L % r == 0) {
+      // x + conv_k1(...) is only ever read through the ELU in front of the strided conv: it leaves the k1 conv's epilogue as that
+      // conv's operand (rows of [hi | lo] = super-rows of r such rows) and is never stored as fp32
+      b.gemm(S.c1, A2, 1, B * L, B * L, nullptr, X, nullptr, A3);
+    } else {
+      b.gemm(S.c1, A2, 1, B * L, B * L, X, X);                  // x += conv_k1(...): residual read and written in place, fp32
+      b.act(S.down, X, A3, B, L, C, 1, r);
+    }
     float* Xn = Xs[si + 1];
-    b.gemm(S.down, A1, B, Ln, Ln, Xn);
+    b.gemm(S.down, A3, B, Ln, Ln, Xn, nullptr, nullptr, si + 1 < ns_ && pre[si + 1] ? A1pre[si + 1] : nullptr);
     if (b.off > scratch_max) scratch_max = b.off;
     X = Xn; L = Ln; C = 2 * C; ++si;
   }

@@ -33,6 +33,7 @@ struct ConvW {
   // encode path: K group size in real input values (0 = one group): the layer runs as kreal / cg launches that accumulate into the
   // fp32 output, so that no tensor-core accumulation chain is longer than taps * 3 * cg (encode_plan.cu)
   int cg = 0;
+  int gl = 1;   // K groups per launch (the kernel walks them through GemmParams.kgroup)
 };
 
 struct SnakeP { const float* a = nullptr; const float* ib = nullptr; };

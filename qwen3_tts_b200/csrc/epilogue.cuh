@@ -68,15 +68,6 @@ __device__ __forceinline__ void epilogue16(const GemmParams& p, float (&v)[16], 
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
   }
-  if (p.act == ACT_ELU_SPLIT) {
-    const long long o = (long long)b * p.out_batch_stride + (long long)row * p.out_row_stride + n;
-    float lo[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
-    store16<T>(reinterpret_cast<T*>(p.out_raw) + o, v);
-    store16<T>(reinterpret_cast<T*>(p.out_snake) + o, lo);
-    return;
-  }
   if (p.scale) {
     float t[16]; load16f(p.scale + c0, t);
 #pragma unroll
@@ -106,6 +97,16 @@ __device__ __forceinline__ void epilogue16(const GemmParams& p, float (&v)[16], 
     float4* d = reinterpret_cast<float4*>(p.out_f32 + off);
 #pragma unroll
     for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  }
+  if (p.act == ACT_ELU_SPLIT) {  // ELU(x) as an fp16 pair (gemm_params.h); the pair tensor has its own pitches
+    const long long o = (long long)b * (p.pair_batch_stride ? p.pair_batch_stride : p.out_batch_stride) +
+                        (long long)row * (p.pair_row_stride ? p.pair_row_stride : p.out_row_stride) + n;
+    float lo[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
+    store16<T>(reinterpret_cast<T*>(p.out_raw) + o, v);
+    store16<T>(reinterpret_cast<T*>(p.out_snake) + o, lo);
+    return;
   }
   if (p.out_raw) store16<T>(reinterpret_cast<T*>(p.out_raw) + off, v);
   if (p.out_snake) {

@@ -24,8 +24,10 @@
 namespace q3 {
 
 enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3, ACT_ELU_SPLIT = 4 };
-// ACT_ELU_SPLIT (encode path): v = ELU(acc + bias) leaves as an fp16 pair, out_raw <- hi = fp16(v), out_snake <- lo = fp16(v - hi): the
-// [hi | lo] operand row of the next split-precision GEMM (out_snake = out_raw + n_total, out_row_stride = 2 * n_total).
+// ACT_ELU_SPLIT (encode path): x = acc + bias (+ fp32 residual) and ELU(x) leaves as an fp16 pair, out_raw <- hi = fp16(ELU(x)),
+// out_snake <- lo = fp16(ELU(x) - hi): the [hi | lo] operand row of the next split-precision GEMM (out_snake = out_raw + n_total,
+// pair_row_stride = 2 * n_total).  Without fp32 tensors it is a 16-bit epilogue; with an fp32 residual and / or out_f32 (which
+// receives x itself, before the ELU) it is the fp32 epilogue with one more 16-column store per half (epi_pair16).
 // ACT_TAIL: accumulator column 0 + bias[0], clamp(-1, 1), stored as fp32 to out_f32[b*out_batch_stride + row - tail_skip]
 // for row >= tail_skip (the 96 -> 1 output conv + clamp, reference modeling :862, :883; skip = chunk left context).
 
@@ -58,6 +60,10 @@ struct GemmParams {
   //   k_mult 3, a_cols = 2C :  A = [a_hi | a_lo] W' = [w_hi | w_hi | w_lo]   (a_hi w_hi + a_lo w_hi + a_hi w_lo: ~21 bits each side)
   // a_cols = 0: plain (a_cols = cin, k_mult = 1).
   int a_cols, k_mult;
+  // kgroup > 0 (k_mult 3 only): A rows are GROUPS of kgroup input values, each its own pair [hi(g) | lo(g)], and weight rows the matching
+  // [hi(g) | hi(g) | lo(g)] (kernels.cu put_w): K' block k walks group k / (3 kgroup), A column g * 2 kgroup + (k % (3 kgroup)) % (2 kgroup).
+  // a_cols is then the width of the groups this launch walks (2 kgroup * number of groups).  0: one group = the whole row.
+  int kgroup;
   int skip_raw;  // fused unit kernel: y is not stored (last unit of a block: only snake_next(y) is read downstream)
   int dbg;  // debug experiments (env Q3TTS_DBG): bit 0 = epilogue only drains TMEM, bit 1 = MMA thread issues no MMAs
   const float* bias;
@@ -74,6 +80,8 @@ struct GemmParams {
   long long w_row_stride;      // elements between rows of W (0: dense, = cin)
   long long res_batch_stride;  // residual tensor (0: same as out_batch_stride)
   long long snake_batch_stride;  // Snake'd output tensor (0: same as out_batch_stride)
+  long long pair_row_stride;     // ACT_ELU_SPLIT: row pitch / batch pitch of the 16-bit pair tensor (0: out_row_stride / out_batch_stride);
+  long long pair_batch_stride;   //   they differ from the fp32 output's when both are written
   long long out_row_stride;    // elements
   // raw operand pointers, used only by the SIMT cross-check kernel
   const void* a_ptr;
@@ -94,6 +102,17 @@ __host__ __device__ inline void gemm_chunk_coords(const GemmParams& p, int mtile
   const int gc = mtile * 4 + q;
   if (p.pack_mode == 1) { row0 = 0; b = gc << (5 - p.pack_rshift); }
   else { b = gc / p.pack_cpb; row0 = (gc - b * p.pack_cpb) * 32; }
+}
+
+// ACT_ELU_SPLIT inside the fp32 epilogue flow (fp32 residual in and / or fp32 out next to the 16-bit pair)
+__host__ __device__ inline bool epi_pair16(const GemmParams& p) { return p.act == ACT_ELU_SPLIT && (p.out_f32 != nullptr || (p.res != nullptr && p.res_f32)); }
+
+// A-tensor column of K' position k (elements): the split-precision wrap, per K group when kgroup is set
+__host__ __device__ inline int gemm_a_col(const GemmParams& p, int k) {
+  if (!p.a_cols) return k;
+  if (!p.kgroup) return k % p.a_cols;
+  const int g = k / (3 * p.kgroup);
+  return g * 2 * p.kgroup + (k - g * 3 * p.kgroup) % (2 * p.kgroup);
 }
 
 }  // namespace q3

@@ -26,6 +26,7 @@ __host__ __device__ inline int epi_slots_per_warp(const GemmParams& p) {
   if (p.act == ACT_TAIL) return 0;
   int n = epi_res_depth(p);
   if (p.act == ACT_GLU) return n + 2;
+  if (epi_pair16(p)) return n + 2 + (p.out_f32 ? 2 : 0);   // pair ring and fp32 ring, two slots each (one store group per item)
   if (p.out_raw) n += epi_out_bufs(p);
   if (p.out_snake) n += epi_out_bufs(p);
   if (p.out_f32) n += 4;
@@ -55,7 +56,7 @@ struct EpiWarp {
   uint64_t* rbar;     // this warp's residual barriers
   TileSched ts;
   int lane, quad, half, nsplit;
-  bool has_res, rf32, glu, tail, of32, o16;
+  bool has_res, rf32, glu, tail, of32, o16, pair16;
   int units, item_units, nitems, rd, rd_shift;
   bool wraps;  // a tile's columns can wrap around ncol_mod (transposed convs: n_total = stride * cout)
   int tile_c0 = 0;  // (first column of the current tile) % ncol_mod: one division per tile instead of one per item
@@ -76,6 +77,7 @@ struct EpiWarp {
     tail = p.act == ACT_TAIL;
     of32 = p.out_f32 != nullptr && !tail;
     o16 = !glu && (p.out_raw != nullptr || p.out_snake != nullptr);
+    pair16 = epi_pair16(p);
     units = p.bn >> 4;
     item_units = glu ? 4 : ((of32 || (has_res && rf32) || tail) ? 1 : 2);
     nitems = units / item_units;
@@ -85,9 +87,10 @@ struct EpiWarp {
     int nslot = rd;
     s_raw = nslot;
     obufs = epi_out_bufs(p);
-    if (glu || p.out_raw) nslot += glu ? 2 : obufs;
+    if (pair16) nslot += 2;   // one slot per item holds both halves of the pair (hi in its first KB, lo in its second)
+    else if (glu || p.out_raw) nslot += glu ? 2 : obufs;
     s_snake = nslot;
-    if (!glu && p.out_snake) nslot += obufs;
+    if (!glu && !pair16 && p.out_snake) nslot += obufs;
     s_f32 = nslot;
   }
 
@@ -158,10 +161,6 @@ struct EpiWarp {
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
     }
-    if (p.act == ACT_ELU_SPLIT) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = elu_fast(v[i]);
-    }
     if (p.scale) {
       float t[16]; load16f(p.scale + c0, t);
 #pragma unroll
@@ -219,6 +218,10 @@ struct EpiWarp {
     for (int i = 0; i < 16; ++i) { va[i] = __uint_as_float(ra[i]); vb[i] = __uint_as_float(rb[i]); }
     math_unit(va, rsa, c0);
     math_unit(vb, rsb, c0 + 16);
+    if (p.act == ACT_ELU_SPLIT) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { va[i] = elu_fast(va[i]); vb[i] = elu_fast(vb[i]); }
+    }
     const uint32_t sl = ob & (uint32_t)(obufs - 1);
     const bool st = !Q3_DBG(p, 4);
     if (st) {
@@ -303,6 +306,47 @@ struct EpiWarp {
 #pragma unroll
         for (int c = 0; c < 4; ++c) g[c] = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
       }
+      if (has_res) res_consumed();
+      return;
+    }
+    if (pair16) {
+      // fp32 flow of ACT_ELU_SPLIT: x goes out as fp32 (when asked for) and ELU(x) as the fp16 pair, all in ONE store group per item;
+      // both rings have two slots, so "at most one group still reading" frees the slots written two items ago.
+      // The pair boxes are 32 rows x 16 columns (32 bytes, SWIZZLE_32B: 16-byte chunk c of row r sits at r * 32 + ((c ^ (r >> 2 & 1)) << 4)).
+      const uint32_t sl = fb & 1;
+      uint8_t* f8 = eb + (s_f32 + sl) * kEpiSlot;
+      uint8_t* h8 = eb + (s_raw + sl) * kEpiSlot;
+      if (lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+      if (of32) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          *reinterpret_cast<float4*>(f8 + slot_off(lane, c)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+      }
+      float lo[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
+      const uint32_t sw = (uint32_t)((lane >> 2) & 1);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint4 a, l4;
+        a.x = Elem<T>::pack2(v[8 * c], v[8 * c + 1]);      a.y = Elem<T>::pack2(v[8 * c + 2], v[8 * c + 3]);
+        a.z = Elem<T>::pack2(v[8 * c + 4], v[8 * c + 5]);  a.w = Elem<T>::pack2(v[8 * c + 6], v[8 * c + 7]);
+        l4.x = Elem<T>::pack2(lo[8 * c], lo[8 * c + 1]);     l4.y = Elem<T>::pack2(lo[8 * c + 2], lo[8 * c + 3]);
+        l4.z = Elem<T>::pack2(lo[8 * c + 4], lo[8 * c + 5]); l4.w = Elem<T>::pack2(lo[8 * c + 6], lo[8 * c + 7]);
+        const uint32_t off = (uint32_t)(lane * 32 + (((uint32_t)c ^ sw) << 4));
+        *reinterpret_cast<uint4*>(h8 + off) = a;
+        *reinterpret_cast<uint4*>(h8 + 1024 + off) = l4;
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (of32) tma_store_3d(tmF32, f8, n0, row0, b);
+        tma_store_3d(tmRaw, h8, n0, row0, b);
+        tma_store_3d(tmSnake, h8 + 1024, n0, row0, b);
+        tma_store_commit();
+      }
+      ++fb;
       if (has_res) res_consumed();
       return;
     }
