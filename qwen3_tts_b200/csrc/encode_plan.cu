@@ -199,8 +199,6 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   EncBuilder b{e, plan, e->enc_ws, 0, dry};
   plan->B = B; plan->T = T; plan->ops.clear();
   const int C0 = e->enc_c0, H = e->enc_hidden, I = e->enc_inter;
-  // Workspace: the fp32 main-path tensor of every stage is kept (X0, X1, ...: ~460 B per sample in all); the per-stage operands
-  // (ELU'd [hi | lo] copies, the ResnetBlock's hidden tensor) live in a scratch region that every stage reuses (~512 B per sample).
   std::vector<size_t> xbytes;
   {
     int L = T, C = C0;
