@@ -1,11 +1,11 @@
 """GPU debug tool: run-to-run determinism of the encode path on the golden input (latents must be bit-identical between runs)."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from oracle.make_golden_encoder import golden_inputs
 from qwen3_tts_b200 import synthetic_model
 
-g = np.load(os.path.join(os.path.dirname(__file__), "..", "tests", "golden", "encode_B2.npz"))
+g = np.load(os.path.join(os.path.dirname(__file__), "..", "golden", "encode_B2.npz"))
 wav, mask = golden_inputs()
 m = synthetic_model(device="cuda:0", with_encoder=True)
 eng = sys.argv[1] if len(sys.argv) > 1 else "tc"

@@ -1,9 +1,9 @@
 """GPU debug tool: the encode path stage by stage against the float64 oracle, on the TC engine and on the SIMT cross-check engine.
-    python tools/encode_stages.py [samples]
+    python tests/tools/encode_stages.py [samples]
 Prints, per engine: latent error, codes agreement; then (TC vs SIMT) the latent difference, which isolates tensor-core kernel bugs
 from plan / packing bugs (both engines share the plan and the packed weights)."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from oracle import encoder_oracle as XO
 from qwen3_tts_b200 import synthetic_model

@@ -1,11 +1,11 @@
 """GPU bring-up script: tcgen05 GEMM self-tests, then stage-by-stage parity against the oracle.
-Run on the GPU box:  python tools/gpu_debug.py [T] [B]   (writes gpurun_out/debug.log too)."""
+Run on the GPU box:  python tests/tools/gpu_debug.py [T] [B]   (writes gpurun_out/debug.log too)."""
 import ctypes as C
 import os
 import sys
 import time
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 
 from oracle import decoder_oracle as O

@@ -1,6 +1,6 @@
 """Parity numbers per BASELINE.json config and compute mode -> JSON (copied to profiles/r2_parity.json).
 
-    python tools/parity_report.py [--out gpurun_out/r2_parity.json] [--modes fp16,bf16]
+    python tests/tools/parity_report.py [--out gpurun_out/r2_parity.json] [--modes fp16,bf16]
 
 For every config the CUDA path (through the reference-shaped Python classes over the C-ABI) is compared with the CPU oracle
 (oracle/decoder_oracle.py, fp32, pinned to the unmodified reference by tests/golden): max-abs error and SNR =
@@ -14,7 +14,7 @@ import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
