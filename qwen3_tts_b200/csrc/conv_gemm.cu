@@ -650,13 +650,14 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
   bool has_res = false, has_raw = false, has_snake = false, has_f32 = false;
   if (p.act != ACT_TAIL) {
     if (p.res) { has_res = true; rc |= make_tmap_3d_strided(&op->tmRes, p.res, p.res_f32 ? 2 : et, width, rows, nb, rs, p.res_batch_stride ? (uint64_t)p.res_batch_stride : bs, p.res_f32 ? 16 : 32, br, bb); }
-    if (p.act == ACT_ELU_SPLIT) {
-      // the two halves of the fp16 pair tensor (its own pitches); 16-column boxes inside the fp32 epilogue flow, 32 in the 16-bit one
+    if (act_is_split(p.act)) {
+      // the fp16 pair tensor (2 * n_total wide, its own pitches): both halves are stored through the same map; 16-column boxes inside
+      // the fp32 epilogue flow, 32 in the 16-bit one
       const uint64_t prs = p.pair_row_stride ? (uint64_t)p.pair_row_stride : rs, pbs = p.pair_batch_stride ? (uint64_t)p.pair_batch_stride : bs;
       const uint32_t pbox = epi_pair16(p) ? 16 : 32;
       has_raw = has_snake = true;
-      rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, prs, pbs, pbox, br, bb);
-      rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, prs, pbs, pbox, br, bb);
+      rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, 2 * width, rows, nb, prs, pbs, pbox, br, bb);
+      op->tmSnake = op->tmRaw;
     } else {
       if (p.out_raw) { has_raw = true; rc |= make_tmap_3d_strided(&op->tmRaw, p.out_raw, et, width, rows, nb, rs, bs, 32, br, bb); }
       if (p.out_snake) { has_snake = true; rc |= make_tmap_3d_strided(&op->tmSnake, p.out_snake, et, width, rows, nb, rs, p.snake_batch_stride ? (uint64_t)p.snake_batch_stride : bs, 32, br, bb); }

@@ -150,7 +150,7 @@ struct EncBuilder {
   // pair_out: the (last) launch also / instead writes ELU(result) as fp16 [hi | lo] rows [batches][rows_valid][2 n] (ACT_ELU_SPLIT);
   // `out` may then be null when the fp32 result itself has no reader (single-launch layers only).
   void gemm(const ConvW& w, const void* in, int batches, int rows, int rows_valid, float* out, const float* res = nullptr, const float* scale = nullptr,
-            void* pair_out = nullptr) {
+            void* pair_out = nullptr, int pair_act = ACT_ELU_SPLIT, int pair_group = 0) {
     const int kreal = w.a_cols / 2;
     const int cg = w.cg > 0 ? w.cg : kreal, G = kreal / cg, gl = w.gl > 0 ? w.gl : 1;
     for (int g0 = 0; g0 < G; g0 += gl) {
@@ -175,9 +175,10 @@ struct EncBuilder {
       const float* r = g0 == 0 ? res : out;
       if (r) { p.res = r; p.res_f32 = 1; }
       if (pair_out && last) {
-        p.act = ACT_ELU_SPLIT;
-        p.out_raw = pair_out; p.out_snake = (char*)pair_out + (size_t)w.n_total * 2;
+        p.act = pair_act;
+        p.out_raw = pair_out; p.out_snake = pair_out;   // one tensor; out_snake only selects the two-output epilogue paths
         p.pair_row_stride = 2 * w.n_total; p.pair_batch_stride = (long long)rows_valid * 2 * w.n_total;
+        p.pair_group = pair_group > 0 && pair_group < w.n_total ? pair_group : 0;
       }
       if (!out && (G > gl || !pair_out)) rc = e->fail(Q3TTS_BAD_CONFIG, "encoder plan: a layer without an fp32 output must be a single launch with a pair output");
       op.g.retile = 1;   // few rows (the 25 Hz stages): shrink the N tile until the grid covers the SMs
@@ -271,7 +272,8 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   void* Hn = b.alloc((size_t)M * 2 * H * 2);
   float* QKV = (float*)b.alloc((size_t)M * 3 * H * 4);
   void* AO = b.alloc((size_t)M * 2 * H * 2);
-  float* F1 = (float*)b.alloc((size_t)M * I * 4);
+  const bool mlp_fused = !e->enc_layers.empty() && e->enc_layers[0].fc1.cg == 0;   // GELU(fc1) leaves the epilogue as fc2's operand
+  float* F1 = mlp_fused ? nullptr : (float*)b.alloc((size_t)M * I * 4);
   void* G = b.alloc((size_t)M * 2 * I * 2);
   for (const EncLayerW& W : e->enc_layers) {
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_LN; op.in = Y; op.out = Hn; op.w0 = W.ln1w; op.w1 = W.ln1b; op.B = M; op.C = H; }
@@ -279,8 +281,12 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = L; op.C = H; }
     b.gemm(W.o, AO, 1, M, M, Y, Y, W.ls1);
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_LN; op.in = Y; op.out = Hn; op.w0 = W.ln2w; op.w1 = W.ln2b; op.B = M; op.C = H; }
-    b.gemm(W.fc1, Hn, 1, M, M, F1);
-    b.act(W.fc2, F1, G, 1, M, I, 2);
+    if (mlp_fused) {
+      b.gemm(W.fc1, Hn, 1, M, M, nullptr, nullptr, nullptr, G, ACT_GELU_SPLIT, W.fc2.cg);
+    } else {
+      b.gemm(W.fc1, Hn, 1, M, M, F1);
+      b.act(W.fc2, F1, G, 1, M, I, 2);
+    }
     b.gemm(W.fc2, G, 1, M, M, Y, Y, W.ls2);
   }
   // ---- down-sampling conv (stride 2, kernel 4, replicate padding, no bias) -> latents [B][F][H]

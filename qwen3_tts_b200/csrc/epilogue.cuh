@@ -98,14 +98,17 @@ __device__ __forceinline__ void epilogue16(const GemmParams& p, float (&v)[16], 
 #pragma unroll
     for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
   }
-  if (p.act == ACT_ELU_SPLIT) {  // ELU(x) as an fp16 pair (gemm_params.h); the pair tensor has its own pitches
+  if (act_is_split(p.act)) {  // f(x) as an fp16 pair (gemm_params.h); the pair tensor has its own pitches and column map
     const long long o = (long long)b * (p.pair_batch_stride ? p.pair_batch_stride : p.out_batch_stride) +
-                        (long long)row * (p.pair_row_stride ? p.pair_row_stride : p.out_row_stride) + n;
+                        (long long)row * (p.pair_row_stride ? p.pair_row_stride : p.out_row_stride) + pair_hi_col(p, n);
     float lo[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
+    for (int i = 0; i < 16; ++i) {
+      if (p.act == ACT_ELU_SPLIT) v[i] = elu_fast(v[i]); else v[i] = gelu_erf(v[i]);
+      lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i]));
+    }
     store16<T>(reinterpret_cast<T*>(p.out_raw) + o, v);
-    store16<T>(reinterpret_cast<T*>(p.out_snake) + o, lo);
+    store16<T>(reinterpret_cast<T*>(p.out_raw) + o + pair_lo_off(p), lo);
     return;
   }
   if (p.out_raw) store16<T>(reinterpret_cast<T*>(p.out_raw) + off, v);

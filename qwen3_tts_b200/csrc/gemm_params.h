@@ -23,10 +23,12 @@
 
 namespace q3 {
 
-enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3, ACT_ELU_SPLIT = 4 };
-// ACT_ELU_SPLIT (encode path): x = acc + bias (+ fp32 residual) and ELU(x) leaves as an fp16 pair, out_raw <- hi = fp16(ELU(x)),
-// out_snake <- lo = fp16(ELU(x) - hi): the [hi | lo] operand row of the next split-precision GEMM (out_snake = out_raw + n_total,
-// pair_row_stride = 2 * n_total).  Without fp32 tensors it is a 16-bit epilogue; with an fp32 residual and / or out_f32 (which
+enum { ACT_NONE = 0, ACT_GELU = 1, ACT_GLU = 2, ACT_TAIL = 3, ACT_ELU_SPLIT = 4, ACT_GELU_SPLIT = 5 };
+__host__ __device__ inline bool act_is_split(int act) { return act == ACT_ELU_SPLIT || act == ACT_GELU_SPLIT; }
+// ACT_ELU_SPLIT / ACT_GELU_SPLIT (encode path): x = acc + bias (+ fp32 residual) and f(x), f = ELU or erf-GELU, leaves as an fp16 pair
+// hi = fp16(f(x)), lo = fp16(f(x) - hi) in the operand layout of the next split-precision GEMM: out_raw is that tensor, rows of
+// 2 * n_total values (pair_row_stride), column n + (n / pair_group) * pair_group for hi and pair_group further for lo (pair_group = the
+// consumer's K group size, 0 = n_total: [hi(all) | lo(all)]).  out_snake must be non-null (it only selects the two-output paths).  Without fp32 tensors it is a 16-bit epilogue; with an fp32 residual and / or out_f32 (which
 // receives x itself, before the ELU) it is the fp32 epilogue with one more 16-column store per half (epi_pair16).
 // ACT_TAIL: accumulator column 0 + bias[0], clamp(-1, 1), stored as fp32 to out_f32[b*out_batch_stride + row - tail_skip]
 // for row >= tail_skip (the 96 -> 1 output conv + clamp, reference modeling :862, :883; skip = chunk left context).
@@ -82,6 +84,7 @@ struct GemmParams {
   long long snake_batch_stride;  // Snake'd output tensor (0: same as out_batch_stride)
   long long pair_row_stride;     // ACT_ELU_SPLIT: row pitch / batch pitch of the 16-bit pair tensor (0: out_row_stride / out_batch_stride);
   long long pair_batch_stride;   //   they differ from the fp32 output's when both are written
+  int pair_group;                // split acts: K group size of the consumer (0 = n_total)
   long long out_row_stride;    // elements
   // raw operand pointers, used only by the SIMT cross-check kernel
   const void* a_ptr;
@@ -105,7 +108,10 @@ __host__ __device__ inline void gemm_chunk_coords(const GemmParams& p, int mtile
 }
 
 // ACT_ELU_SPLIT inside the fp32 epilogue flow (fp32 residual in and / or fp32 out next to the 16-bit pair)
-__host__ __device__ inline bool epi_pair16(const GemmParams& p) { return p.act == ACT_ELU_SPLIT && (p.out_f32 != nullptr || (p.res != nullptr && p.res_f32)); }
+// hi column of accumulator column n in the pair tensor (lo sits pair_group further)
+__host__ __device__ inline int pair_hi_col(const GemmParams& p, int n) { return p.pair_group ? n + (n / p.pair_group) * p.pair_group : n; }
+__host__ __device__ inline int pair_lo_off(const GemmParams& p) { return p.pair_group ? p.pair_group : p.n_total; }
+__host__ __device__ inline bool epi_pair16(const GemmParams& p) { return act_is_split(p.act) && (p.out_f32 != nullptr || (p.res != nullptr && p.res_f32)); }
 
 // A-tensor column of K' position k (elements): the split-precision wrap, per K group when kgroup is set
 __host__ __device__ inline int gemm_a_col(const GemmParams& p, int k) {

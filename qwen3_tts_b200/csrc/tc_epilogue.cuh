@@ -172,7 +172,7 @@ struct EpiWarp {
     }
   }
   __device__ __forceinline__ void snake_unit(float (&v)[16], int c0) {
-    if (p.act == ACT_ELU_SPLIT) {  // second tensor = the low half of the fp16 pair (gemm_params.h)
+    if (act_is_split(p.act)) {  // second tensor = the low half of the fp16 pair (gemm_params.h)
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] -= Elem<T>::to_f(Elem<T>::from_f(v[i]));
       return;
@@ -221,6 +221,9 @@ struct EpiWarp {
     if (p.act == ACT_ELU_SPLIT) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) { va[i] = elu_fast(va[i]); vb[i] = elu_fast(vb[i]); }
+    } else if (p.act == ACT_GELU_SPLIT) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { va[i] = gelu_erf(va[i]); vb[i] = gelu_erf(vb[i]); }
     }
     const uint32_t sl = ob & (uint32_t)(obufs - 1);
     const bool st = !Q3_DBG(p, 4);
@@ -242,8 +245,10 @@ struct EpiWarp {
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        if (p.out_raw) tma_store_3d(tmRaw, eb + (s_raw + sl) * kEpiSlot, n0, row0, b);
-        if (p.out_snake) tma_store_3d(tmSnake, eb + (s_snake + sl) * kEpiSlot, n0, row0, b);
+        int craw = n0, csnake = n0;
+        if (act_is_split(p.act)) { craw = pair_hi_col(p, n0); csnake = craw + pair_lo_off(p); }   // both halves go through the pair tensor's map
+        if (p.out_raw) tma_store_3d(tmRaw, eb + (s_raw + sl) * kEpiSlot, craw, row0, b);
+        if (p.out_snake) tma_store_3d(tmSnake, eb + (s_snake + sl) * kEpiSlot, csnake, row0, b);
         tma_store_commit();
       }
     }
@@ -324,8 +329,15 @@ struct EpiWarp {
           *reinterpret_cast<float4*>(f8 + slot_off(lane, c)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
       }
       float lo[16];
+      if (p.act == ACT_ELU_SPLIT) {   // the branch stays outside the loops: a select inside them evaluates erff for every element
 #pragma unroll
-      for (int i = 0; i < 16; ++i) { v[i] = elu_fast(v[i]); lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i])); }
+        for (int i = 0; i < 16; ++i) v[i] = elu_fast(v[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = gelu_erf(v[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) lo[i] = v[i] - Elem<T>::to_f(Elem<T>::from_f(v[i]));
       const uint32_t sw = (uint32_t)((lane >> 2) & 1);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
@@ -342,8 +354,9 @@ struct EpiWarp {
       __syncwarp();
       if (lane == 0) {
         if (of32) tma_store_3d(tmF32, f8, n0, row0, b);
-        tma_store_3d(tmRaw, h8, n0, row0, b);
-        tma_store_3d(tmSnake, h8 + 1024, n0, row0, b);
+        const int chi = pair_hi_col(p, n0);
+        tma_store_3d(tmRaw, h8, chi, row0, b);
+        tma_store_3d(tmSnake, h8 + 1024, chi + pair_lo_off(p), row0, b);
         tma_store_commit();
       }
       ++fb;
