@@ -10,6 +10,7 @@
 // operand directly, so each activation makes one fp32 round trip per layer.
 #include <cuda_fp16.h>
 
+#include "attention_mma.cuh"
 #include "encode_kernels.h"
 #include "launch.cuh"
 
@@ -330,6 +331,206 @@ cudaError_t enc_attention(const float* qkv, const float* cos_t, const float* sin
   if (hd != EA_HD) return cudaErrorInvalidValue;
   dim3 grid((T + EA_Q - 1) / EA_Q, nh, B);
   k_enc_attention<<<grid, 256, 0, s>>>(qkv, cos_t, sin_t, (__half*)out, T, nh, window);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------ attention on mma.sync, fp32 level
+// The same attention with the two contractions on the warp-level tensor cores (mma.sync m16n8k16, fp32 accumulate) and every operand an
+// fp16 hi + lo pair, three MMAs per product (q_hi k_hi + q_lo k_hi + q_hi k_lo; p_hi v_hi + p_lo v_hi + p_hi v_lo): ~22 bits per
+// operand, like the path's GEMMs.  Block = 64 queries of one (item, head), four warps of 16 queries; keys / values are staged 64 at a
+// time as four fp16 arrays (K hi / lo with RoPE applied, V hi / lo); a warp walks the 16-key sub-chunks its queries can see with a
+// running max / sum per query row (fragment layouts as in attention_mma.cuh).
+// Pre-pass: qkv fp32 [M][3H] -> fp16 [M][6H] = [q_hi | q_lo | k_hi | k_lo | v_hi | v_lo] with RoPE applied to q and k, so that the
+// attention blocks stage plain 16-byte copies (every key / value row is staged by ~5 query blocks; rotating and splitting it there
+// made the staging the larger half of the kernel).
+__global__ void __launch_bounds__(256) k_enc_rope_split(const float* __restrict__ qkv, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+                                                         __half* __restrict__ out, long long M, int T, int nh) {
+  const int H = nh * EA_HD;
+  const long long n = M * nh * 8;                        // (row, head, group of 4 channels d..d+3 with their partners d+32..)
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i & 7) << 2;
+    const long long rh = i >> 3;
+    const int head = (int)(rh % nh);
+    const long long row = rh / nh;
+    const int t = (int)(row % T);
+    const float* src = qkv + row * 3 * H + head * EA_HD + d;
+    const float4 cs = *reinterpret_cast<const float4*>(cos_t + t * 32 + d), sn = *reinterpret_cast<const float4*>(sin_t + t * 32 + d);
+    __half* dst = out + row * 6 * H + head * EA_HD + d;
+#pragma unroll
+    for (int w = 0; w < 3; ++w) {                        // q, k, v
+      const float4 x1 = *reinterpret_cast<const float4*>(src + w * H), x2 = *reinterpret_cast<const float4*>(src + w * H + 32);
+      float4 a = x1, bb = x2;
+      if (w < 2) {   // rotate_half (:579-584): out[d] = x[d] cos - x[d + 32] sin, out[d + 32] = x[d + 32] cos + x[d] sin
+        a = make_float4(x1.x * cs.x - x2.x * sn.x, x1.y * cs.y - x2.y * sn.y, x1.z * cs.z - x2.z * sn.z, x1.w * cs.w - x2.w * sn.w);
+        bb = make_float4(x2.x * cs.x + x1.x * sn.x, x2.y * cs.y + x1.y * sn.y, x2.z * cs.z + x1.z * sn.z, x2.w * cs.w + x1.w * sn.w);
+      }
+      uint2 h, l;
+      split4(a, h, l);
+      *reinterpret_cast<uint2*>(dst + (2 * w) * H) = h;
+      *reinterpret_cast<uint2*>(dst + (2 * w + 1) * H) = l;
+      split4(bb, h, l);
+      *reinterpret_cast<uint2*>(dst + (2 * w) * H + 32) = h;
+      *reinterpret_cast<uint2*>(dst + (2 * w + 1) * H + 32) = l;
+    }
+  }
+}
+cudaError_t enc_rope_split(const float* qkv, const float* cos_t, const float* sin_t, void* out, long long M, int T, int nh, cudaStream_t s) {
+  k_enc_rope_split<<<enc_blocks(M * nh * 8, 256, 148 * 32), 256, 0, s>>>(qkv, cos_t, sin_t, (__half*)out, M, T, nh);
+  return cudaGetLastError();
+}
+
+static constexpr int EM_Q = 64, EM_K = 64, EM_THREADS = 128;
+static constexpr int EM_SMEM = (2 * EM_Q + 4 * EM_K) * AM_PITCH * 2;   // bytes: Q hi / lo, K hi / lo, V hi / lo
+
+__global__ void __launch_bounds__(EM_THREADS) k_enc_attention_mma(const __half* __restrict__ qkvs, __half* __restrict__ out, int T, int nh, int window) {
+  extern __shared__ __align__(16) unsigned char em_smem[];
+  __half* sQh = reinterpret_cast<__half*>(em_smem);
+  __half* sQl = sQh + EM_Q * AM_PITCH;
+  __half* sKh = sQl + EM_Q * AM_PITCH;
+  __half* sKl = sKh + EM_K * AM_PITCH;
+  __half* sVh = sKl + EM_K * AM_PITCH;
+  __half* sVl = sVh + EM_K * AM_PITCH;
+  const int q0 = blockIdx.x * EM_Q, head = blockIdx.y, b = blockIdx.z;
+  const int H = nh * EA_HD;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, c = lane & 3;
+  const __half* base = qkvs + (long long)b * T * 6 * H + head * EA_HD;   // rows of [q_hi | q_lo | k_hi | k_lo | v_hi | v_lo] (k_enc_rope_split)
+  // ---- queries: 64 rows x (hi, lo) x 8 chunks of 16 bytes
+  for (int i = tid; i < EM_Q * 16; i += EM_THREADS) {
+    const int qi = i >> 4, part = (i >> 3) & 1, ch = i & 7, t = q0 + qi;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (t < T) v = *reinterpret_cast<const uint4*>(base + (long long)t * 6 * H + part * H + ch * 8);
+    *reinterpret_cast<uint4*>((part ? sQl : sQh) + qi * AM_PITCH + ch * 8) = v;
+  }
+  __syncthreads();
+  const int tq0 = q0 + warp * 16;                       // this warp's first query
+  uint32_t qh[4][4], ql[4][4];
+  {
+    const int off = (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AM_PITCH + (lane >> 4) * 8;
+    const uint32_t ah = smem_u32(sQh + off), al = smem_u32(sQl + off);
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) { ldsm_x4(ah + ks * 32, qh[ks]); ldsm_x4(al + ks * 32, ql[ks]); }
+  }
+  const int row_lo = tq0 + g, row_hi = tq0 + g + 8;     // the two query rows this lane's accumulators belong to
+  float m_lo = -1.0e30f, m_hi = -1.0e30f, l_lo = 0.f, l_hi = 0.f;
+  float o[8][4];
+#pragma unroll
+  for (int n = 0; n < 8; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+  const int qlast = min(q0 + EM_Q - 1, T - 1);
+  int kbeg = q0 - window + 1;
+  kbeg = kbeg < 0 ? 0 : (kbeg & ~15);
+  for (int k0 = kbeg; k0 <= qlast; k0 += EM_K) {
+    __syncthreads();                                    // the previous chunk has been consumed by every warp
+    for (int i = tid; i < EM_K * 32; i += EM_THREADS) {   // 64 rows x (K hi, K lo, V hi, V lo) x 8 chunks of 16 bytes
+      const int ki = i >> 5, arr = (i >> 3) & 3, ch = i & 7, t = k0 + ki;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (t <= qlast) v = *reinterpret_cast<const uint4*>(base + (long long)t * 6 * H + (2 + arr) * H + ch * 8);
+      __half* dst = arr == 0 ? sKh : (arr == 1 ? sKl : (arr == 2 ? sVh : sVl));
+      *reinterpret_cast<uint4*>(dst + ki * AM_PITCH + ch * 8) = v;
+    }
+    __syncthreads();
+    if (tq0 >= T) continue;                             // a warp without queries only helps with the staging
+#pragma unroll 1
+    for (int sc = 0; sc < EM_K / 16; ++sc) {
+      const int ks0 = k0 + sc * 16;                     // absolute position of the sub-chunk's first key
+      if (ks0 > tq0 + 15 || ks0 + 15 < tq0 - window + 1) continue;   // nothing the warp's queries can see (warp-uniform)
+      // ---- scores of 16 queries x 16 keys: two 8-key tiles, 12 MMAs each
+      float s[2][4];
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        const int koff = (sc * 16 + hf * 8 + (lane & 7)) * AM_PITCH + (lane >> 3) * 8;
+        uint32_t kh0[4], kh1[4], kl0[4], kl1[4];
+        ldsm_x4(smem_u32(sKh + koff), kh0); ldsm_x4(smem_u32(sKh + koff) + 64, kh1);
+        ldsm_x4(smem_u32(sKl + koff), kl0); ldsm_x4(smem_u32(sKl + koff) + 64, kl1);
+        float (&d)[4] = s[hf];
+        d[0] = d[1] = d[2] = d[3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint32_t bh0 = ks < 2 ? kh0[2 * ks] : kh1[2 * ks - 4], bh1 = ks < 2 ? kh0[2 * ks + 1] : kh1[2 * ks - 3];
+          const uint32_t bl0 = ks < 2 ? kl0[2 * ks] : kl1[2 * ks - 4], bl1 = ks < 2 ? kl0[2 * ks + 1] : kl1[2 * ks - 3];
+          MmaOp<__half>::mma(d, ql[ks], bh0, bh1);      // small terms first
+          MmaOp<__half>::mma(d, qh[ks], bl0, bl1);
+          MmaOp<__half>::mma(d, qh[ks], bh0, bh1);
+        }
+      }
+      // ---- mask, running max
+      bool ok[2][4];
+      float cm_lo = -1.0e30f, cm_hi = -1.0e30f;
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int key = ks0 + hf * 8 + 2 * c + (e & 1), tq = e < 2 ? row_lo : row_hi;
+          ok[hf][e] = tq < T && key <= tq && tq - key < window;
+          s[hf][e] = ok[hf][e] ? s[hf][e] * 0.125f : -1.0e30f;   // scaling = 1 / sqrt(head_dim) (:665)
+          if (e < 2) cm_lo = fmaxf(cm_lo, s[hf][e]); else cm_hi = fmaxf(cm_hi, s[hf][e]);
+        }
+      }
+      cm_lo = fmaxf(cm_lo, __shfl_xor_sync(0xffffffffu, cm_lo, 1)); cm_lo = fmaxf(cm_lo, __shfl_xor_sync(0xffffffffu, cm_lo, 2));
+      cm_hi = fmaxf(cm_hi, __shfl_xor_sync(0xffffffffu, cm_hi, 1)); cm_hi = fmaxf(cm_hi, __shfl_xor_sync(0xffffffffu, cm_hi, 2));
+      const float mn_lo = fmaxf(m_lo, cm_lo), mn_hi = fmaxf(m_hi, cm_hi);
+      const float cr_lo = expf(m_lo - mn_lo), cr_hi = expf(m_hi - mn_hi);   // 1 while nothing has been seen yet (both -1e30)
+      m_lo = mn_lo; m_hi = mn_hi;
+      l_lo *= cr_lo; l_hi *= cr_hi;
+#pragma unroll
+      for (int n = 0; n < 8; ++n) { o[n][0] *= cr_lo; o[n][1] *= cr_lo; o[n][2] *= cr_hi; o[n][3] *= cr_hi; }
+      // ---- probabilities as fp16 pairs (A fragments of P . V)
+      uint32_t ph[4], pl[4];
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {
+        float p[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) p[e] = ok[hf][e] ? expf(s[hf][e] - (e < 2 ? mn_lo : mn_hi)) : 0.f;
+        l_lo += p[0] + p[1];
+        l_hi += p[2] + p[3];
+        const __half2 h01 = __floats2half2_rn(p[0], p[1]), h23 = __floats2half2_rn(p[2], p[3]);
+        const float2 b01 = __half22float2(h01), b23 = __half22float2(h23);
+        const __half2 l01 = __floats2half2_rn(p[0] - b01.x, p[1] - b01.y), l23 = __floats2half2_rn(p[2] - b23.x, p[3] - b23.y);
+        ph[2 * hf] = *reinterpret_cast<const uint32_t*>(&h01); ph[2 * hf + 1] = *reinterpret_cast<const uint32_t*>(&h23);
+        pl[2 * hf] = *reinterpret_cast<const uint32_t*>(&l01); pl[2 * hf + 1] = *reinterpret_cast<const uint32_t*>(&l23);
+      }
+      // ---- P . V: 8 output tiles of 8 channels, three MMAs each
+      const int voff = (sc * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AM_PITCH + (lane >> 4) * 8;
+#pragma unroll
+      for (int n2 = 0; n2 < 4; ++n2) {
+        uint32_t vh[4], vl[4];
+        ldsm_x4_t(smem_u32(sVh + voff) + n2 * 32, vh);
+        ldsm_x4_t(smem_u32(sVl + voff) + n2 * 32, vl);
+        MmaOp<__half>::mma(o[2 * n2], pl, vh[0], vh[1]);
+        MmaOp<__half>::mma(o[2 * n2], ph, vl[0], vl[1]);
+        MmaOp<__half>::mma(o[2 * n2], ph, vh[0], vh[1]);
+        MmaOp<__half>::mma(o[2 * n2 + 1], pl, vh[2], vh[3]);
+        MmaOp<__half>::mma(o[2 * n2 + 1], ph, vl[2], vl[3]);
+        MmaOp<__half>::mma(o[2 * n2 + 1], ph, vh[2], vh[3]);
+      }
+    }
+  }
+  if (tq0 >= T) return;
+  l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 1); l_lo += __shfl_xor_sync(0xffffffffu, l_lo, 2);
+  l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 1); l_hi += __shfl_xor_sync(0xffffffffu, l_hi, 2);
+  const float inv_lo = 1.0f / l_lo, inv_hi = 1.0f / l_hi;
+#pragma unroll
+  for (int n = 0; n < 8; ++n) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int t = r ? row_hi : row_lo;
+      if (t >= T) continue;
+      const float v0 = o[n][2 * r] * (r ? inv_hi : inv_lo), v1 = o[n][2 * r + 1] * (r ? inv_hi : inv_lo);
+      const __half2 h = __floats2half2_rn(v0, v1);
+      const float2 bk = __half22float2(h);
+      const __half2 l = __floats2half2_rn(v0 - bk.x, v1 - bk.y);
+      __half* op = out + ((long long)b * T + t) * 2 * H + head * EA_HD + n * 8 + 2 * c;
+      *reinterpret_cast<__half2*>(op) = h;
+      *reinterpret_cast<__half2*>(op + H) = l;
+    }
+  }
+}
+cudaError_t enc_attention_setup() {
+  return cudaFuncSetAttribute(k_enc_attention_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, EM_SMEM);
+}
+cudaError_t enc_attention_mma(const void* qkvs, void* out, int B, int T, int nh, int hd, int window, cudaStream_t s) {
+  if (hd != EA_HD) return cudaErrorInvalidValue;
+  dim3 grid((T + EM_Q - 1) / EM_Q, nh, B);
+  k_enc_attention_mma<<<grid, EM_THREADS, EM_SMEM, s>>>((const __half*)qkvs, (__half*)out, T, nh, window);
   return cudaGetLastError();
 }
 

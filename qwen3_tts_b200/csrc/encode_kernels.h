@@ -23,6 +23,12 @@ cudaError_t enc_argmin_update(const float* S, const float* n2, const float* tabl
                               long long code_stride_m, long long code_stride_b, long long code_off, int M, int F, int NC, int dq, cudaStream_t s);
 // fp32 [M][ld] columns [c0, c0 + C) -> fp16 [M][2C] rows [hi | lo]
 cudaError_t enc_split_cols(const float* in, int ld, int c0, void* out, long long M, int C, cudaStream_t s);
+// the same attention with both contractions on mma.sync tensor cores, every operand an fp16 hi + lo pair (three MMAs per product)
+// qkvs: fp16 [B*T][6 nh hd] = [q_hi | q_lo | k_hi | k_lo | v_hi | v_lo], RoPE applied (enc_rope_split)
+cudaError_t enc_attention_mma(const void* qkvs, void* out, int B, int T, int nh, int hd, int window, cudaStream_t s);
+// qkv fp32 [M][3 nh hd] -> the fp16 operand rows above (M = B * T rows, position = row % T)
+cudaError_t enc_rope_split(const float* qkv, const float* cos_t, const float* sin_t, void* out, long long M, int T, int nh, cudaStream_t s);
+cudaError_t enc_attention_setup();   // per-device opt-in to its dynamic shared memory (encoder_front_finalize)
 // fp32 [B][L][C] -> fp32 [B][C][L]
 cudaError_t enc_to_channels_first(const float* in, float* out, int B, int L, int C, cudaStream_t s);
 

@@ -272,13 +272,14 @@ int build(Engine* e, Plan* plan, int B, int T, bool dry, size_t* bytes) {
   void* Hn = b.alloc((size_t)M * 2 * H * 2);
   float* QKV = (float*)b.alloc((size_t)M * 3 * H * 4);
   void* AO = b.alloc((size_t)M * 2 * H * 2);
+  void* QKVS = b.alloc((size_t)M * 6 * H * 2);               // q, k (RoPE applied), v as fp16 pairs: the attention kernel's operands
   const bool mlp_fused = !e->enc_layers.empty() && e->enc_layers[0].fc1.cg == 0;   // GELU(fc1) leaves the epilogue as fc2's operand
   float* F1 = mlp_fused ? nullptr : (float*)b.alloc((size_t)M * I * 4);
   void* G = b.alloc((size_t)M * 2 * I * 2);
   for (const EncLayerW& W : e->enc_layers) {
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_LN; op.in = Y; op.out = Hn; op.w0 = W.ln1w; op.w1 = W.ln1b; op.B = M; op.C = H; }
     b.gemm(W.qkv, Hn, 1, M, M, QKV);
-    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_ATTN; op.in = QKV; op.out = AO; op.B = B; op.L = L; op.C = H; }
+    { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_ATTN; op.in = QKV; op.out = AO; op.out2 = QKVS; op.B = B; op.L = L; op.C = H; }
     b.gemm(W.o, AO, 1, M, M, Y, Y, W.ls1);
     { plan->ops.emplace_back(); Op& op = plan->ops.back(); op.type = OP_ENC_LN; op.in = Y; op.out = Hn; op.w0 = W.ln2w; op.w1 = W.ln2b; op.B = M; op.C = H; }
     if (mlp_fused) {
@@ -361,8 +362,14 @@ int run(Engine* e, Plan* plan, const float* wav, long long wav_stride, long long
       case OP_GEMM: err = launch_conv_gemm(op.g, e->engine, s); break;
       case OP_ENC_LN: err = enc_layernorm_split((const float*)op.in, op.w0, op.w1, op.out, op.B, op.C, e->enc_cfg.norm_eps, s); break;
       case OP_ENC_ATTN:
-        err = enc_attention((const float*)op.in, e->enc_rope_cos, e->enc_rope_sin, op.out, op.B, op.L, e->enc_cfg.num_attention_heads, 64,
-                            e->enc_cfg.sliding_window, s);
+        if (e->engine == ENGINE_TC) {   // tensor-core form: rotate + split once, then mma.sync attention over fp16 pairs
+          err = enc_rope_split((const float*)op.in, e->enc_rope_cos, e->enc_rope_sin, op.out2, (long long)op.B * op.L, op.L, e->enc_cfg.num_attention_heads, s);
+          if (err == cudaSuccess) err = enc_attention_mma(op.out2, op.out, op.B, op.L, e->enc_cfg.num_attention_heads, 64, e->enc_cfg.sliding_window, s);
+          ++e->launches;
+        } else {                        // the cross-check engine (Q3TTS_ENGINE_SIMT): fp32 SIMT attention
+          err = enc_attention((const float*)op.in, e->enc_rope_cos, e->enc_rope_sin, op.out, op.B, op.L, e->enc_cfg.num_attention_heads, 64,
+                              e->enc_cfg.sliding_window, s);
+        }
         break;
       case OP_ENC_RVQ:   // parity tap: the quantiser's input in the reference's layout
         if (latents) err = enc_to_channels_first((const float*)op.in, latents, op.B, op.L, op.C, s);
@@ -477,6 +484,7 @@ int encoder_front_finalize(Engine* e) {
   if (f.rc) return f.rc;
   f.check(cudaMemcpy(d_inv, inv, sizeof(inv), cudaMemcpyHostToDevice), "rope inv_freq copy");
   f.check(enc_rope_table(e->enc_rope_cos, e->enc_rope_sin, d_inv, ec.max_position_embeddings, 64, f.s), "enc_rope_table");
+  f.check(enc_attention_setup(), "enc_attention_setup");
   f.check(cudaDeviceSynchronize(), "encoder weight packing");
   if (f.rc) return f.rc;
   e->enc_front_ready = true;
