@@ -182,7 +182,7 @@ int run_unit_selftest(int rows, int C, int dil, float* out4) {
     UnitOp op;
     memset(&op.p, 0, sizeof(op.p));
     op.C = C; op.dil = dil; op.bias7 = b7; op.snake2_a = s2a; op.snake2_ib = s2ib;
-    { const char* d = getenv("Q3TTS_DBG"); op.p.dbg = d ? atoi(d) : 0; }
+    { const char* d = Q3_ENV("Q3TTS_DBG"); op.p.dbg = d ? atoi(d) : 0; }
     op.p.bf16 = bf16; op.p.bias = b1; op.p.res = x; op.p.out_raw = y1; op.p.out_snake = s1; op.p.snake_a = sna; op.p.snake_ib = snib;
     const int mk = unit_make(&op, a1, w7, w1, batches, rows);
     cudaError_t e3 = mk == 0 ? launch_unit(op, 0) : cudaErrorInvalidConfiguration;
