@@ -151,6 +151,24 @@ def test_encode_is_independent_of_the_decode_compute_mode(sd, enc_model):
     assert torch.equal(out[7], enc_model.encode(many[7:8]).audio_codes[0])
 
 
+def test_encode_long_item_and_sub_batching_are_prefix_consistent(enc_model):
+    """Size-independent property at sizes the oracle does not reach: everything in the path is causal, so the codes of a 5-minute
+    item (7500 frames at 25 Hz, 30 attention windows; the largest single launch) must START with the codes of its first 20 s, bit
+    for bit, except the prefix's last, partial-context frame; and a batch larger than one launch's sample budget (sub-batched by
+    the engine) must give every item the codes it gets alone."""
+    long_wav = make_audio(1, 24000 * 300, seed=31)
+    full = enc_model.encode(long_wav).audio_codes[0]
+    assert full.shape == (3750, 16)
+    head = enc_model.encode(long_wav[:, :24000 * 20]).audio_codes[0]
+    assert head.shape == (250, 16) and torch.equal(head[:-1], full[:249])
+    with pytest.raises(ValueError):
+        enc_model.encode(make_audio(1, 24000 * 321, seed=1))            # 8025 frames at 25 Hz: past max_position_embeddings
+    many = make_audio(40, 24000 * 20, seed=32)                            # 19.2 M samples: two launches of at most 16 M
+    out = enc_model.encode(many).audio_codes
+    for b in (0, 33, 34, 39):
+        assert torch.equal(out[b], enc_model.encode(many[b:b + 1]).audio_codes[0])
+
+
 def test_encode_needs_encoder_weights(gpu_model):
     with pytest.raises(RuntimeError, match="not loaded"):
         gpu_model.encode(torch.zeros(1, 4800))
