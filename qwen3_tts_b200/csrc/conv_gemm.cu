@@ -623,7 +623,10 @@ int gemm_make_epilogue_maps(GemmOp* op, int allow) {
     // (ConvNeXt pw1: the erf GELU epilogue outweighs K = 1024 of MMAs per tile too: 0.70 -> 0.56 ms)
     q.epi_warps = ew ? atoi(ew) : ((short_k && q.out_snake) || q.act == ACT_GELU ? 12 : 8);
     if (q.epi_warps != 4 && q.epi_warps != 8 && q.epi_warps != 12) q.epi_warps = 8;
-    if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || q.res_f32 || q.pack_mode)) q.epi_warps = 8;  // 12 warps: 16-bit vocoder epilogues only
+    // 12 warps: 16-bit epilogues, and the encode path's pair epilogue with an fp32 residual but no fp32 output (its items are short
+    // dependent chains: ncu had the k1 conv + residual at 37 % issue-slot use with 8 warps)
+    const bool pair_res_only = epi_pair16(q) && !q.out_f32;   // (with an fp32 output as well, 12 warps measured neutral)
+    if (q.epi_warps == 12 && (q.act == ACT_TAIL || q.act == ACT_GLU || q.out_f32 || (q.res_f32 && !pair_res_only) || q.pack_mode)) q.epi_warps = 8;
     q.res_depth = q.res ? (q.epi_warps == 12 ? 2 : 4) : 0;
     if (q.epi_warps == 12 && q.res && gemm_stage_count(q) < 3) {
       // the extra slots would starve the operand pipeline: try a narrower N tile (three items per warp trio), else stay at 8 warps
