@@ -102,3 +102,36 @@ def test_compute_mode_table_matches_header():
     enum = {m.group(1).lower().replace("_", "-"): int(m.group(2)) for m in re.finditer(r"Q3TTS_MODE_([A-Z0-9_]+)\s*=\s*(\d+)", hdr)}
     assert enum == _capi.MODES and len(enum) == 6
     assert all((v & 1) == (1 if k.startswith("bf16") else 0) for k, v in enum.items())     # bit 0 = operand type
+
+
+def test_encoder_key_filter_and_audio_input_rules():
+    """Host logic of the encode side that needs no GPU: which `encoder.*` checkpoint keys are uploaded (the reference reads 16 of
+    Mimi's 32 codebooks, modeling :982; decoder-side parts of MimiModel are nulled, :898-907) and the wrapper's input rules
+    (wrapper :162-206)."""
+    import types
+
+    import numpy as np
+
+    from qwen3_tts_b200 import Qwen3TTSTokenizer, Qwen3TTSTokenizerV2Model
+    from qwen3_tts_b200.synthetic import encoder_param_shapes, make_encoder_state_dict
+    m = object.__new__(Qwen3TTSTokenizerV2Model)
+    m.config = Qwen3TTSTokenizerV2Config()
+    sd = make_encoder_state_dict(seed=0)
+    assert set(sd) == set(encoder_param_shapes()) and all(m._wants_encoder_key(k) for k in sd)
+    q = "encoder.quantizer.acoustic_residual_vector_quantizer."
+    assert m._wants_encoder_key(q + "layers.14.codebook.embed_sum") and not m._wants_encoder_key(q + "layers.15.codebook.embed_sum")
+    assert not m._wants_encoder_key(q + "output_proj.weight") and not m._wants_encoder_key(q + "layers.0.codebook.initialized")
+    assert not m._wants_encoder_key("encoder.quantizer.semantic_residual_vector_quantizer.layers.1.codebook.embed_sum")
+    assert not m._wants_encoder_key("encoder.decoder_transformer.layers.0.mlp.fc1.weight") and not m._wants_encoder_key("decoder.pre_conv.conv.weight")
+    tok = object.__new__(Qwen3TTSTokenizer)
+    tok.model = types.SimpleNamespace(get_input_sample_rate=lambda: 24000)
+    a = np.zeros((100, 2), dtype=np.float64)
+    out = tok._normalize_audio_inputs(a, sr=24000)                   # a single array is a batch of one; channels are averaged; float32
+    assert len(out) == 1 and out[0].shape == (100,) and out[0].dtype == np.float32
+    with pytest.raises(ValueError):
+        tok._normalize_audio_inputs([np.zeros(10, dtype=np.float32)], sr=None)
+    with pytest.raises(TypeError):
+        tok._normalize_audio_inputs([np.zeros(10, dtype=np.float32), "a.wav"], sr=24000)
+    with pytest.raises(NotImplementedError):
+        tok._normalize_audio_inputs([np.zeros(10, dtype=np.float32)], sr=16000)   # resampling needs librosa: not shipped
+    assert tok._normalize_audio_inputs([], sr=24000) == []
