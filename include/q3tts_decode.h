@@ -167,7 +167,8 @@ int64_t q3tts_encode_num_frames(q3tts_handle* h, int64_t samples);
  * quantiser's input, for parity checks.  The caller cuts item b to ceil(valid_samples[b] / 1920) frames (modeling :983). */
 int q3tts_encode(q3tts_handle* h, const float* wav, int B, int64_t T, int64_t wav_stride, int64_t* codes, float* latents, void* stream);
 /* Host form: wav_host [B, wav_stride] fp32 -> codes_host [B, F, Q] int64 (the layout q3tts_decode_host reads); valid_samples (host,
- * [B], may be NULL = T) -> lengths[b] = ceil(valid_samples[b] / 1920) frames of row b are item b's codes.  Synchronises. */
+ * [B], may be NULL = T) -> lengths[b] = ceil(valid_samples[b] / 1920) frames of row b are item b's codes.  Synchronises.
+ * A page-locked wav_host is read in place by the first conv over PCIe (no separate host-to-device copy); a pageable one is staged. */
 int q3tts_encode_host(q3tts_handle* h, const float* wav_host, int B, int64_t T, int64_t wav_stride, const int64_t* valid_samples,
                       int64_t* codes_host, int64_t* lengths, void* stream);
 

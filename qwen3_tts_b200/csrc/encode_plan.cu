@@ -571,7 +571,19 @@ int q3tts_encode_host(q3tts_handle* h, const float* wav_host, int B, int64_t T, 
   const long long F = q3::enc_frames(e, T);
   const int Q = e.cfg.num_quantizers;
   const size_t nw = (size_t)B * T, nc = (size_t)B * F * Q;
-  if (nw > e.enc_wav_stage_elems) {
+  // Page-locked waveform buffer: the first conv reads it in place over PCIe (unified addressing gives the device an alias of the host
+  // pointer; the kernel stages every sample into shared memory once, so each is fetched ~1.05 times) - no separate host-to-device copy.
+  const float* wav_dev = nullptr;
+  long long wav_dev_stride = T;
+  {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, wav_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+      wav_dev = (const float*)at.devicePointer; wav_dev_stride = wav_stride;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  if (!wav_dev && nw > e.enc_wav_stage_elems) {
     cudaStreamSynchronize(s);
     if (e.enc_wav_stage) cudaFree(e.enc_wav_stage);
     e.enc_wav_stage = nullptr; e.enc_wav_stage_elems = 0;
@@ -585,10 +597,14 @@ int q3tts_encode_host(q3tts_handle* h, const float* wav_host, int B, int64_t T, 
     if (cudaMalloc((void**)&e.enc_codes_stage, nc * sizeof(long long)) != cudaSuccess) { cudaGetLastError(); return e.fail(Q3TTS_OOM, "encode_host: staging cudaMalloc failed"); }
     e.enc_codes_stage_elems = nc;
   }
-  cudaError_t err = cudaMemcpy2DAsync(e.enc_wav_stage, (size_t)T * sizeof(float), wav_host, (size_t)wav_stride * sizeof(float), (size_t)T * sizeof(float), B,
-                                      cudaMemcpyHostToDevice, s);
-  if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("encode_host: H2D failed: ") + cudaGetErrorString(err));
-  const int rc = q3::encode_batched(&e, e.enc_wav_stage, B, T, T, e.enc_codes_stage, 1, nullptr, s);
+  cudaError_t err = cudaSuccess;
+  if (!wav_dev) {
+    err = cudaMemcpy2DAsync(e.enc_wav_stage, (size_t)T * sizeof(float), wav_host, (size_t)wav_stride * sizeof(float), (size_t)T * sizeof(float), B,
+                            cudaMemcpyHostToDevice, s);
+    if (err != cudaSuccess) return e.fail(Q3TTS_CUDA_ERROR, std::string("encode_host: H2D failed: ") + cudaGetErrorString(err));
+    wav_dev = e.enc_wav_stage;
+  }
+  const int rc = q3::encode_batched(&e, wav_dev, B, T, wav_dev_stride, e.enc_codes_stage, 1, nullptr, s);
   if (rc) return rc;
   err = cudaMemcpyAsync(codes_host, e.enc_codes_stage, nc * sizeof(long long), cudaMemcpyDeviceToHost, s);
   if (err == cudaSuccess) err = cudaStreamSynchronize(s);
