@@ -21,6 +21,7 @@
 
 #include "encode_kernels.h"
 #include "engine.h"
+#include "launch.cuh"
 
 namespace q3 {
 
@@ -349,6 +350,9 @@ int get_plan(Engine* e, int B, int T, Plan** out) {
 // codes: [B][Q][F] (codes_tq = 0) or [B][F][Q]; latents (optional) [B][H][F]
 int run(Engine* e, Plan* plan, const float* wav, long long wav_stride, long long* codes, int codes_tq, float* latents, cudaStream_t s) {
   size_t pi = e->profile ? prof_begin(e, plan->ops.size()) : 0;
+  // programmatic dependent launch between consecutive tensor-core kernels (k3 -> k1 -> strided conv, the K-group launches): the next
+  // kernel's prologue overlaps the previous one's tail; off while profiling (the event pairs would time the overlap)
+  PdlScope pdl(!e->profile);
   bool searching = false;
   for (Op& op : plan->ops) {
     cudaError_t err = cudaSuccess;
