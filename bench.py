@@ -23,6 +23,7 @@ architecture (no checkpoint is mounted).  With N > 1 every rank decodes its own 
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 import statistics
@@ -424,14 +425,16 @@ def encode_reference_cpu(steps: int, warmup: int, utterances: int = REF_UTTERANC
     from oracle import ref_shim
     from qwen3_tts_b200.synthetic import make_audio, make_encoder_state_dict
     torch.set_num_threads(os.cpu_count() or 1)
-    enc = ref_shim.build_reference_encoder(make_encoder_state_dict(seed=0), attn_implementation="sdpa")
+    with contextlib.redirect_stdout(sys.stderr):  # transformers prints docstring complaints about the reference on stdout: one JSON line only
+        enc = ref_shim.build_reference_encoder(make_encoder_state_dict(seed=0), attn_implementation="sdpa")
     T = int(ENC_SEC * 24000)
     wav = make_audio(utterances, T, seed=1)
     mask = torch.ones_like(wav, dtype=torch.long)
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        out = ref_shim.reference_model_encode(enc, wav, mask)
+        with contextlib.redirect_stdout(sys.stderr):
+            out = ref_shim.reference_model_encode(enc, wav, mask)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
@@ -571,6 +574,45 @@ def run_encode(args, rank, local_rank, world):
                 "gpu_launches": r["launches"], "clocks": clocks, "roofline": roof,
                 "path_frac_of_hbm_roofline": total_bytes / (ms / args.steps * 1e-3) / 1e9 / peaks["hbm_gbs"], "min_hbm_gb_per_step": total_bytes / 1e9,
                 "kernels": kernels}
+        if world == 1:
+            # latency of ONE 10 s item (the voice-clone reference clip, model wrapper :427): launch-bound, not throughput-bound
+            from qwen3_tts_b200.synthetic import make_audio
+            one = make_audio(1, int(ENC_SEC * 24000), seed=5).to(dev)
+            for _ in range(5):
+                model.encode(one)
+            lat = []
+            for _ in range(30):
+                a, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); model.encode(one); b2.record(); torch.cuda.synchronize(dev)
+                lat.append(a.elapsed_time(b2))
+            lat.sort()
+            line["single_item"] = {"seconds": ENC_SEC, "device_ms_p50": lat[len(lat) // 2], "device_ms_max": lat[-1]}
+        if not args.no_torch_gpu and world == 1:
+            try:   # context: the reference's own encoder class in eager PyTorch (fp32, library defaults) on this GPU
+                from oracle import ref_shim
+                from qwen3_tts_b200.synthetic import make_encoder_state_dict
+                del model
+                torch.cuda.empty_cache()
+                with contextlib.redirect_stdout(sys.stderr):
+                    enc = ref_shim.build_reference_encoder(make_encoder_state_dict(seed=0), attn_implementation="sdpa").to(dev)
+                nb = 16
+                w = make_audio(nb, int(ENC_SEC * 24000), seed=1).to(dev)
+                msk = torch.ones_like(w, dtype=torch.long)
+                ts = []
+                for i in range(7):
+                    a, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    with contextlib.redirect_stdout(sys.stderr):
+                        ref_shim.reference_model_encode(enc, w, msk)
+                    b2.record(); torch.cuda.synchronize(dev)
+                    if i >= 2:
+                        ts.append(a.elapsed_time(b2))
+                ts.sort()
+                line["torch_gpu"] = {"impl": "reference encoder class (unmodified, eager PyTorch fp32, library defaults: cuDNN / cuBLAS)", "batch": nb,
+                                     "ms_p50": ts[len(ts) // 2], "audio_s_per_s": nb * ENC_SEC / (ts[len(ts) // 2] * 1e-3)}
+                line["torch_gpu"]["ours_over_eager"] = line["value"] / line["torch_gpu"]["audio_s_per_s"]
+            except Exception as ex:  # context only
+                line["torch_gpu"] = {"unavailable": f"{type(ex).__name__}: {ex}"[:300]}
         if not args.no_cpu_baseline and world == 1:
             c = encode_reference_cpu(steps=3, warmup=1)
             line["cpu_baseline"] = {"value": c["value"], "unit": "audio-s/s", "cores": c["cores"], "kind": c["kind"], "sample": c["sample"]}
